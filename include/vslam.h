@@ -1,0 +1,165 @@
+/*
+ * vslam.h -- C ABI of the B200-native KeyPointDetection hot path (libvslam_b200.so).
+ *
+ * The reference (JacobYoung115/VisualSLAM, KeyPointDetection/) has no FFI layer: its surface is a C++ class and
+ * free functions compiled into the executables.  This header is the boundary a maintainer binds
+ * instead of OpenCV; each entry point cites the reference interface it replaces (paths relative to
+ * KeyPointDetection/).  The C++17 mirror of the reference's own names lives in visualslam_b200/host/.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; the caller owns every host buffer; the library owns device memory inside
+ *     opaque handles released by the matching *_destroy.
+ *   - every function returns 0 (VSLAM_OK) or a negative vslam_status; vslam_last_error() gives the text.
+ *   - a context is bound to one GPU and one CUDA stream and is not thread-safe: one context per (thread, GPU).
+ *   - images are single-channel uint8, row-major, `pitch` bytes between rows (pitch >= width).
+ *   - there is no CPU fallback: without a CUDA device vslam_ctx_create fails with VSLAM_E_CUDA.
+ */
+#ifndef VSLAM_H_
+#define VSLAM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define VSLAM_API
+#else
+#define VSLAM_API __attribute__((visibility("default")))
+#endif
+
+typedef enum vslam_status {
+    VSLAM_OK = 0,
+    VSLAM_E_INVALID = -1,  /* bad argument (null pointer, non-positive size, unsupported kernel width ...) */
+    VSLAM_E_CUDA = -2,     /* a CUDA call failed; see vslam_last_error */
+    VSLAM_E_CAPACITY = -3, /* output list too small; counts[] hold the true sizes, lists hold the first `capacity` */
+    VSLAM_E_NOMEM = -4     /* device or host allocation failed */
+} vslam_status;
+
+typedef struct vslam_ctx vslam_ctx;         /* one GPU + one stream + reusable workspaces */
+typedef struct vslam_pyramid vslam_pyramid; /* device-resident GaussPyramid of a batch of frames */
+
+/* SLAM::point (Diff_of_Gauss.cpp:27-35): six int32, same order. row/col are the PADDED coordinates the reference
+ * stores (Diff_of_Gauss.cpp:289). */
+typedef struct vslam_keypoint {
+    int32_t row, col, value, padding, octave, level;
+} vslam_keypoint;
+
+/* One NMS2 corner (Harris_corners.cpp:116-118): position and response value. */
+typedef struct vslam_corner {
+    int32_t row, col;
+    float value;
+} vslam_corner;
+
+/* GaussPyramid ctor arguments + constants (GaussPyramid.hpp:17-21,65-69). */
+typedef struct vslam_pyramid_params {
+    int32_t num_octaves;   /* 4 in Diff_of_Gauss.cpp:742; <=0 -> floor(log2(min(rows,cols)))-4 (GaussPyramid.cpp:150-152) */
+    int32_t scale_samples; /* scaleSamples_ = 3 -> numLevels_ = 6 (only 3 is supported) */
+    double sigma0;         /* 1.6 in Diff_of_Gauss.cpp:743 */
+    uint32_t materialise;  /* bit mask of vslam_map_kind to keep in HBM; gauss and DoG are always kept */
+} vslam_pyramid_params;
+
+/* initialKeypointDetection / FeaturePointLocalization / filterKeypoints constants
+ * (Diff_of_Gauss.cpp:772 windowSize=3, :245 0.03f, :332 r=10). */
+typedef struct vslam_dog_params {
+    int32_t window;
+    float contrast_thr;
+    float edge_r;
+} vslam_dog_params;
+
+/* HarrisCorner / NMS constants (Harris_corners.cpp:34-36 window 3, k 0.04; :178 window 3; :179 window 5). */
+typedef struct vslam_harris_params {
+    float k;
+    int32_t nms2_window;
+} vslam_harris_params;
+
+typedef enum vslam_map_kind {
+    VSLAM_MAP_BASE = 0,   /* octaveImage / imagePyramid           u8   (GaussPyramid.hpp:29,38) level ignored  */
+    VSLAM_MAP_GAUSS = 1,  /* octaveBlur / pyramidGauss            u8   (:31,39)  level 0..5                     */
+    VSLAM_MAP_DOG = 2,    /* octaveDiff / pyramidDiff             u8   (:32,40)  level 0..4                     */
+    VSLAM_MAP_GRADX = 3,  /* octaveGradX / pyramidGradX           f32  (:33,41)  level 0..5                     */
+    VSLAM_MAP_GRADY = 4,  /* octaveGradY / pyramidGradY           f32  (:34,42)                                 */
+    VSLAM_MAP_MAG = 5,    /* octaveGradMag / pyramidGradMag       f32  (:35,43)                                 */
+    VSLAM_MAP_ORIENT = 6  /* octaveGradOrient / pyramidGradOrient f32  (:36,44)  degrees [0,360)                */
+} vslam_map_kind;
+
+#define VSLAM_MATERIALISE_GRAD (1u << VSLAM_MAP_GRADX | 1u << VSLAM_MAP_GRADY)
+#define VSLAM_MATERIALISE_MAGORIENT (1u << VSLAM_MAP_MAG | 1u << VSLAM_MAP_ORIENT)
+#define VSLAM_MATERIALISE_ALL (VSLAM_MATERIALISE_GRAD | VSLAM_MATERIALISE_MAGORIENT)
+
+/* memory space of a caller buffer */
+#define VSLAM_HOST 0
+#define VSLAM_DEVICE 1
+
+/* ---- context ------------------------------------------------------------------------------------------------ */
+VSLAM_API int vslam_ctx_create(int device, vslam_ctx **out);
+/* Same, but work is enqueued on a caller-owned CUDA stream (cudaStream_t / CUstream passed as void*). */
+VSLAM_API int vslam_ctx_create_on_stream(int device, void *cuda_stream, vslam_ctx **out);
+VSLAM_API void vslam_ctx_destroy(vslam_ctx *ctx);
+VSLAM_API const char *vslam_last_error(const vslam_ctx *ctx); /* ctx may be NULL: last process-wide error */
+VSLAM_API int vslam_sync(vslam_ctx *ctx);
+VSLAM_API const char *vslam_version(void);
+/* number of kernel launches this context has enqueued since creation (bench.py's gpu_launches) */
+VSLAM_API long long vslam_launch_count(const vslam_ctx *ctx);
+
+/* ---- sigma table: GaussPyramid::calculateSigma / calculateNumOctaves (GaussPyramid.cpp:150-162) --------------- */
+VSLAM_API double vslam_calculate_sigma(int octave, int level, double sigma0, int scale_samples);
+VSLAM_API int vslam_calculate_num_octaves(int rows, int cols);
+/* OpenCV's 8U Gaussian kernel as GaussianBlur(Size(0,0), sigma) builds it (GaussPyramid.cpp:177): ksize and the
+ * 8.8 fixed-point taps (sum 256).  taps must hold vslam_gauss_ksize(sigma) ints. */
+VSLAM_API int vslam_gauss_ksize(double sigma);
+VSLAM_API int vslam_gauss_taps(double sigma, int ksize, int32_t *taps);
+
+/* ---- GaussPyramid: createPyramid (GaussPyramid.cpp:106-131) ---------------------------------------------------- */
+/* Replaces the GaussPyramid constructors (GaussPyramid.hpp:17-21) for a batch of n_frames equally sized frames.
+ * frames: n_frames images, frame f at frames + f*frame_stride.  `space` says where `frames` lives. */
+VSLAM_API int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols,
+                                  size_t pitch, size_t frame_stride, int space,
+                                  const vslam_pyramid_params *params, vslam_pyramid **out);
+VSLAM_API void vslam_pyramid_destroy(vslam_pyramid *pyr);
+VSLAM_API int vslam_pyramid_num_octaves(const vslam_pyramid *pyr);
+VSLAM_API int vslam_pyramid_num_frames(const vslam_pyramid *pyr);
+VSLAM_API int vslam_pyramid_octave_size(const vslam_pyramid *pyr, int octave, int *rows, int *cols);
+/* getSigmaAt (GaussPyramid.cpp:187-189) */
+VSLAM_API int vslam_pyramid_sigma(const vslam_pyramid *pyr, int octave, int level, double *sigma);
+/* octaveBlur/octaveDiff/... getters (GaussPyramid.hpp:29-36): copy one map to a caller buffer (host or device).
+ * dst_pitch in bytes.  Maps outside `materialise` (gradients) are computed on demand from the Gaussian level. */
+VSLAM_API int vslam_pyramid_get(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int kind, int octave,
+                                int level, void *dst, size_t dst_pitch, int space);
+/* device pointer + pitch of a resident u8 map (BASE, GAUSS, DOG) for zero-copy consumers; NULL if not resident */
+VSLAM_API const uint8_t *vslam_pyramid_device_map(const vslam_pyramid *pyr, int frame, int kind, int octave,
+                                                  int level, size_t *pitch);
+
+/* ---- DoG keypoints: initialKeypointDetection + FeaturePointLocalization + filterKeypoints' edge test
+ *      (Diff_of_Gauss.cpp:254-297, 223-251, 79-109, 326-338) ----------------------------------------------------- */
+/* All frames and octaves of `pyr`; keypoints in the reference's emission order (frame, octave, level, row, col).
+ * out:        capacity entries (host or device per `space`)
+ * counts:     n_frames ints (host): keypoints per frame
+ * stage_counts: optional n_frames*num_octaves*4 int64 (host): tested, candidates, after contrast, after edge */
+VSLAM_API int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_params *params,
+                               vslam_keypoint *out, int capacity, int space, int *counts,
+                               long long *stage_counts);
+
+/* Throughput path of ./DoG up to Diff_of_Gauss.cpp:336: frames -> keypoints with a per-context workspace that is
+ * reused frame after frame (nothing but keypoints leaves the GPU).  Same results and order as
+ * vslam_pyramid_build + vslam_dog_detect. */
+VSLAM_API int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols,
+                                  size_t pitch, size_t frame_stride, int space,
+                                  const vslam_pyramid_params *pparams, const vslam_dog_params *dparams,
+                                  vslam_keypoint *out, int capacity, int out_space, int *counts);
+
+/* ---- Harris: main's pre-blur + Sobel, HarrisCorner, convertScaleAbs + NonMaximumSuppression, NMS2
+ *      (Harris_corners.cpp:158-164, 31-68, 176-178, 83-129) ------------------------------------------------------ */
+/* Any of response / r8 / mask3 may be NULL (not materialised).  Maps are dense n_frames x rows x cols in `space`.
+ * corners: capacity entries in row-major order per frame, frames concatenated; counts: n_frames ints (host). */
+VSLAM_API int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
+                           size_t frame_stride, int space, const vslam_harris_params *params, float *response,
+                           uint8_t *r8, uint8_t *mask3, vslam_corner *corners, int capacity, int out_space,
+                           int *counts);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VSLAM_H_ */

@@ -1,0 +1,125 @@
+"""CPU tests: the plain-C oracle (oracle/vslam_oracle.c) against the fixtures generated from the reference's own
+OpenCV calls (tools/make_golden.py -> tests/golden/), and against cv2 live where it is importable."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from conftest import image_for
+from oracle import c_oracle as O
+
+
+def md5(a):
+    return hashlib.md5(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_reference_pins_pyramid_test(golden):
+    """The only values the reference's own tests print (tests/GaussPyramid_Test.cpp:88-110) on building.jpg."""
+    L = O.lib()
+    assert O.pyramid_sizes(600, 868, 4) == [(1200, 1736), (600, 868), (300, 434), (150, 217)]
+    assert L.vo_calculate_sigma(0, 0, 1.6, 3) == 1.6
+    assert abs(L.vo_calculate_sigma(0, 5, 1.6, 3) - 1.6 * 2 ** (5 / 3)) < 1e-12
+    assert abs(L.vo_calculate_sigma(0, 3, 1.6, 3) - 3.2) < 1e-12
+    assert L.vo_calculate_num_octaves(600, 868) == 5      # floor(log2(600)) - 4, GaussPyramid.cpp:151
+    assert golden["pyramid"]["building"]["sizes"] == [[1200, 1736], [600, 868], [300, 434], [150, 217]]
+
+
+def test_taps_match_cv2_impulse_tables(golden):
+    for key, e in golden["taps"].items():
+        t = O.gauss_taps(e["sigma"])
+        assert len(t) == e["n"], key
+        assert t.tolist() == e["taps"], key
+        assert t.sum() == 256
+    for e in golden["taps_sweep"]:
+        assert O.gauss_taps(e["sigma"]).tolist() == e["taps"], e["sigma"]
+    assert O.gauss_taps(0.0, 3).tolist() == [64, 128, 64]
+
+
+@pytest.mark.parametrize("stem", ["home", "building", "blox"])
+def test_pyramid_and_keypoints_match_golden(stem, golden, images, golden_lists):
+    g = golden["pyramid"][stem]
+    img = image_for(images, stem, "cvt")
+    kp, counts, pyr = O.dog_keypoints(img, 4, 1.6, 3)
+    assert [list(b.shape) for b in pyr["base"]] == g["sizes"]
+    assert [md5(b) for b in pyr["base"]] == g["base"]
+    assert [[md5(m) for m in o] for o in pyr["gauss"]] == g["gauss"]
+    assert [[md5(m) for m in o] for o in pyr["dog"]] == g["dog"]
+    assert counts == g["counts"]
+    assert len(kp) == g["n_keypoints"]
+    assert np.array_equal(kp, golden_lists["dog_" + stem])
+
+
+def test_known_counts(golden):
+    """Totals the survey recorded from the cv2 run of the reference's calls."""
+    assert golden["pyramid"]["home"]["n_keypoints"] == 91
+    assert golden["pyramid"]["building"]["n_keypoints"] == 735
+    assert [c["edge"] for c in golden["pyramid"]["home"]["counts"]] == [58, 32, 1, 0]
+    assert golden["harris"]["blox"]["n_corners"] == 1328
+    assert golden["harris"]["chessboard"]["n_corners"] == 283
+
+
+def test_gradients_match_golden(golden, images, golden_lists):
+    img = image_for(images, "home", "cvt")
+    pyr = O.build_pyramid(img, 4, 1.6, gradients=True, mag_orient=True)
+    g = golden["pyramid"]["home"]
+    assert [[md5(m) for m in o] for o in pyr["gx"]] == g["gx"]
+    assert [[md5(m) for m in o] for o in pyr["gy"]] == g["gy"]
+    # magnitude: <= 1 ulp of sqrtf; phase: OpenCV fastAtan polynomial, SIMD rounding differs by < 1e-3 deg
+    assert np.allclose(pyr["mag"][3][1], golden_lists["mag_o3l1_home"], rtol=2e-7, atol=0)
+    assert np.abs(pyr["orient"][3][1] - golden_lists["orient_o3l1_home"]).max() < 1e-3
+
+
+def test_localize_known_answers(golden):
+    L = O.lib()
+    for dx, dy, ds, val, want in golden["localize"]:
+        got = L.vo_localize(dx, dy, ds, val)
+        assert np.float32(got) == np.float32(want) or (np.isnan(got) and np.isnan(want)), (dx, dy, ds, val)
+
+
+@pytest.mark.parametrize("stem", ["blox", "chessboard", "building", "home"])
+def test_harris_matches_golden(stem, golden, images, golden_lists):
+    g = golden["harris"][stem]
+    h = O.harris(image_for(images, stem, "gray"))
+    assert md5(h["blurred"]) == g["blurred"]
+    assert md5(h["response"]) == g["response"]
+    assert md5(h["r8"]) == g["r8"]
+    assert md5(h["mask3"]) == g["mask3"]
+    assert int((h["mask3"] > 0).sum()) == g["mask3_count"]
+    assert len(h["corners"]) == g["n_corners"]
+    assert np.array_equal(h["corners"], golden_lists["harris_" + stem])
+    assert np.array_equal(h["corner_values"], golden_lists["harris_val_" + stem])
+    assert h["true_max"] == g["true_max"]
+
+
+def test_oracle_vs_cv2_live_on_awkward_sizes():
+    """The C restatement against cv2 itself on seeded images: odd sizes, kernel wider than the image, 1-pixel rows."""
+    cv2 = pytest.importorskip("cv2")
+    from oracle import cv2_reference as R
+    rng = np.random.default_rng(5)
+    for (h, w) in [(1, 37), (37, 1), (2, 2), (5, 7), (33, 64), (48, 31), (97, 131)]:
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        assert np.array_equal(O.upsample2x(img), cv2.resize(img, None, fx=2, fy=2, interpolation=cv2.INTER_LINEAR)), (h, w)
+        for s in (1.6, 3.2, 12.8, 40.63):
+            assert np.array_equal(O.gaussian_blur(img, s), cv2.GaussianBlur(img, (0, 0), s, sigmaY=0)), (h, w, s)
+        hc, hr = O.harris(img), R.harris(img)
+        for k in ("blurred", "response", "r8", "mask3", "corners", "corner_values"):
+            assert np.array_equal(hc[k], hr[k]), (h, w, k)
+    for (h, w) in [(24, 40), (33, 47), (64, 64)]:
+        img = (rng.integers(0, 256, (h, w)) // 3 + np.linspace(0, 120, w)[None, :]).astype(np.uint8)
+        kc, cc, _ = O.dog_keypoints(img, 3, 1.6, 3)
+        kr, cr, _ = R.dog_keypoints(img, 3, 1.6, 3)
+        assert cc == cr and np.array_equal(kc, kr), (h, w)
+
+
+def test_localize_numpy_vs_literal_cv2():
+    pytest.importorskip("cv2")
+    from oracle import cv2_reference as R
+    rng = np.random.default_rng(11)
+    L = O.lib()
+    for _ in range(300):
+        dx, dy, ds = (int(v) for v in rng.integers(-60, 61, 3))
+        val = int(rng.integers(0, 80))
+        lit = np.float32(R.localize_literal_cv2(dx, dy, ds, val))
+        vec = np.float32(R.localize_numpy(dx, dy, ds, val))
+        c = np.float32(L.vo_localize(dx, dy, ds, val))
+        assert (lit == vec == c) or (np.isnan(lit) and np.isnan(vec) and np.isnan(c)), (dx, dy, ds, val)

@@ -1,0 +1,273 @@
+"""ctypes binding of libvslam_b200.so (include/vslam.h) -- the same calls a C++ / cgo / JNI host would make.
+
+Host-side mirror of the reference's surface for Python callers (tests, bench):
+    Context.build_pyramid(img)   <-> GaussPyramid(img, numOctaves, sigma)            GaussPyramid.hpp:17
+    Pyramid.octave_blur(o) ...   <-> GaussPyramid::octaveBlur / octaveDiff / ...     GaussPyramid.hpp:29-36
+    Context.dog_detect(pyr)      <-> initialKeypointDetection + contrast + edge      Diff_of_Gauss.cpp:254,223,79,326
+    Context.dog_keypoints(imgs)  <-> ./DoG up to Diff_of_Gauss.cpp:336 (throughput path)
+    Context.harris(imgs)         <-> ./Harris up to Harris_corners.cpp:179
+
+There is no CPU fallback: if the shared library is missing or no CUDA device is present, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HOST, DEVICE = 0, 1
+MAP_BASE, MAP_GAUSS, MAP_DOG, MAP_GRADX, MAP_GRADY, MAP_MAG, MAP_ORIENT = range(7)
+OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM = 0, -1, -2, -3, -4
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvslam_b200.so")
+
+KEYPOINT_DTYPE = np.dtype([("row", "<i4"), ("col", "<i4"), ("value", "<i4"), ("padding", "<i4"),
+                           ("octave", "<i4"), ("level", "<i4")])
+CORNER_DTYPE = np.dtype([("row", "<i4"), ("col", "<i4"), ("value", "<f4")])
+
+
+class PyramidParams(C.Structure):
+    _fields_ = [("num_octaves", C.c_int32), ("scale_samples", C.c_int32), ("sigma0", C.c_double),
+                ("materialise", C.c_uint32)]
+
+
+class DogParams(C.Structure):
+    _fields_ = [("window", C.c_int32), ("contrast_thr", C.c_float), ("edge_r", C.c_float)]
+
+
+class HarrisParams(C.Structure):
+    _fields_ = [("k", C.c_float), ("nms2_window", C.c_int32)]
+
+
+class VslamError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"vslam error {code}: {msg}")
+        self.code = code
+
+
+# every symbol include/vslam.h declares (tests check that the library exports all of them)
+EXPORTS = [
+    "vslam_ctx_create", "vslam_ctx_create_on_stream", "vslam_ctx_destroy", "vslam_last_error", "vslam_sync",
+    "vslam_version", "vslam_launch_count", "vslam_calculate_sigma", "vslam_calculate_num_octaves",
+    "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_destroy",
+    "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
+    "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
+]
+
+_lib = None
+
+
+def load():
+    """Load the shared library (raises if it has not been built: no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise VslamError(E_CUDA, f"{LIB_PATH} is missing -- run `python -m visualslam_b200.build`; there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, i, sz = C.c_void_p, C.c_int, C.c_size_t
+    L.vslam_ctx_create.argtypes = [i, C.POINTER(vp)]
+    L.vslam_ctx_create_on_stream.argtypes = [i, vp, C.POINTER(vp)]
+    L.vslam_ctx_destroy.argtypes = [vp]; L.vslam_ctx_destroy.restype = None
+    L.vslam_last_error.argtypes = [vp]; L.vslam_last_error.restype = C.c_char_p
+    L.vslam_sync.argtypes = [vp]
+    L.vslam_version.restype = C.c_char_p
+    L.vslam_launch_count.argtypes = [vp]; L.vslam_launch_count.restype = C.c_longlong
+    L.vslam_calculate_sigma.argtypes = [i, i, C.c_double, i]; L.vslam_calculate_sigma.restype = C.c_double
+    L.vslam_calculate_num_octaves.argtypes = [i, i]
+    L.vslam_gauss_ksize.argtypes = [C.c_double]
+    L.vslam_gauss_taps.argtypes = [C.c_double, i, C.POINTER(C.c_int32)]
+    L.vslam_pyramid_build.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(vp)]
+    L.vslam_pyramid_destroy.argtypes = [vp]; L.vslam_pyramid_destroy.restype = None
+    L.vslam_pyramid_num_octaves.argtypes = [vp]
+    L.vslam_pyramid_num_frames.argtypes = [vp]
+    L.vslam_pyramid_octave_size.argtypes = [vp, i, C.POINTER(i), C.POINTER(i)]
+    L.vslam_pyramid_sigma.argtypes = [vp, i, i, C.POINTER(C.c_double)]
+    L.vslam_pyramid_get.argtypes = [vp, vp, i, i, i, i, vp, sz, i]
+    L.vslam_pyramid_device_map.argtypes = [vp, i, i, i, i, C.POINTER(sz)]; L.vslam_pyramid_device_map.restype = vp
+    L.vslam_dog_detect.argtypes = [vp, vp, C.POINTER(DogParams), vp, i, i, C.POINTER(i), C.POINTER(C.c_longlong)]
+    L.vslam_dog_keypoints.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(DogParams),
+                                      vp, i, i, C.POINTER(i)]
+    L.vslam_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(HarrisParams), vp, vp, vp, vp, i, i, C.POINTER(i)]
+    _lib = L
+    return L
+
+
+def calculate_sigma(octave, level, sigma0=1.6, scale_samples=3):
+    return load().vslam_calculate_sigma(octave, level, sigma0, scale_samples)
+
+
+def gauss_taps(sigma, ksize=None):
+    L = load()
+    if ksize is None:
+        ksize = L.vslam_gauss_ksize(sigma)
+    t = (C.c_int32 * ksize)()
+    rc = L.vslam_gauss_taps(sigma, ksize, t)
+    if rc:
+        raise VslamError(rc, "vslam_gauss_taps")
+    return np.array(t[:], np.int32)
+
+
+def _frames_arg(frames):
+    """numpy uint8 [n,h,w] / [h,w] (host) or a torch cuda uint8 tensor (device) -> (ptr, n, h, w, pitch, stride, space, keepalive)."""
+    if isinstance(frames, np.ndarray):
+        a = np.ascontiguousarray(frames, np.uint8)
+        if a.ndim == 2:
+            a = a[None]
+        n, h, w = a.shape
+        return a.ctypes.data, n, h, w, w, h * w, HOST, a
+    # torch tensor on a CUDA device
+    t = frames
+    if t.dim() == 2:
+        t = t[None]
+    t = t.contiguous()
+    n, h, w = t.shape
+    return t.data_ptr(), n, h, w, w, h * w, DEVICE, t
+
+
+class Pyramid:
+    """Device-resident GaussPyramid of a batch (GaussPyramid.hpp:14-71)."""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self.h = ctx, handle
+        L = load()
+        self.num_octaves = L.vslam_pyramid_num_octaves(handle)
+        self.n_frames = L.vslam_pyramid_num_frames(handle)
+        self.num_levels = 6
+        self.num_scale_samples = 3
+
+    def close(self):
+        if self.h:
+            load().vslam_pyramid_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def octave_size(self, octave):
+        r, c = C.c_int(), C.c_int()
+        self.ctx._chk(load().vslam_pyramid_octave_size(self.h, octave, C.byref(r), C.byref(c)))
+        return r.value, c.value
+
+    def sigma_at(self, octave, level):                       # getSigmaAt, GaussPyramid.cpp:187
+        s = C.c_double()
+        rc = load().vslam_pyramid_sigma(self.h, octave, level, C.byref(s))
+        if rc:
+            raise IndexError(f"octave {octave} level {level}")  # std::out_of_range in the reference (map::at)
+        return s.value
+
+    def get(self, kind, octave, level=0, frame=0):
+        r, c = self.octave_size(octave)
+        dt = np.uint8 if kind <= MAP_DOG else np.float32
+        out = np.empty((r, c), dt)
+        self.ctx._chk(load().vslam_pyramid_get(self.ctx.h, self.h, frame, kind, octave, level, out.ctypes.data,
+                                               out.strides[0], HOST))
+        return out
+
+    def octave_image(self, o, frame=0): return self.get(MAP_BASE, o, 0, frame)
+    def octave_blur(self, o, frame=0): return [self.get(MAP_GAUSS, o, l, frame) for l in range(6)]
+    def octave_diff(self, o, frame=0): return [self.get(MAP_DOG, o, l, frame) for l in range(5)]
+    def octave_grad_x(self, o, frame=0): return [self.get(MAP_GRADX, o, l, frame) for l in range(6)]
+    def octave_grad_y(self, o, frame=0): return [self.get(MAP_GRADY, o, l, frame) for l in range(6)]
+    def octave_grad_mag(self, o, frame=0): return [self.get(MAP_MAG, o, l, frame) for l in range(6)]
+    def octave_grad_orient(self, o, frame=0): return [self.get(MAP_ORIENT, o, l, frame) for l in range(6)]
+    def octave_sigma(self, o): return [self.sigma_at(o, l) for l in range(6)]
+
+
+class Context:
+    def __init__(self, device=0, stream=None):
+        L = load()
+        h = C.c_void_p()
+        rc = L.vslam_ctx_create_on_stream(device, stream, C.byref(h)) if stream else L.vslam_ctx_create(device, C.byref(h))
+        if rc:
+            raise VslamError(rc, L.vslam_last_error(None).decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            load().vslam_ctx_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _chk(self, rc):
+        if rc:
+            raise VslamError(rc, load().vslam_last_error(self.h).decode())
+
+    def sync(self):
+        self._chk(load().vslam_sync(self.h))
+
+    @property
+    def launches(self):
+        return load().vslam_launch_count(self.h)
+
+    def build_pyramid(self, frames, num_octaves=4, sigma0=1.6, materialise=0):
+        ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
+        pp = PyramidParams(num_octaves, 3, sigma0, materialise)
+        ph = C.c_void_p()
+        self._chk(load().vslam_pyramid_build(self.h, ptr, n, h, w, pitch, stride, space, C.byref(pp), C.byref(ph)))
+        self.sync()
+        return Pyramid(self, ph)
+
+    def dog_detect(self, pyr, window=3, contrast_thr=0.03, edge_r=10.0, capacity=1 << 20, stage_counts=True):
+        dp = DogParams(window, contrast_thr, edge_r)
+        out = np.zeros(capacity, KEYPOINT_DTYPE)
+        counts = (C.c_int * pyr.n_frames)()
+        sc = (C.c_longlong * (pyr.n_frames * pyr.num_octaves * 4))() if stage_counts else None
+        rc = load().vslam_dog_detect(self.h, pyr.h, C.byref(dp), out.ctypes.data, capacity, HOST, counts, sc)
+        if rc and rc != E_CAPACITY:
+            self._chk(rc)
+        cl = list(counts)
+        res = {"keypoints": out[:min(sum(cl), capacity)], "counts": cl, "overflow": rc == E_CAPACITY}
+        if stage_counts:
+            res["stage_counts"] = np.array(sc[:], np.int64).reshape(pyr.n_frames, pyr.num_octaves, 4)
+        return res
+
+    def dog_keypoints(self, frames, num_octaves=4, sigma0=1.6, window=3, contrast_thr=0.03, edge_r=10.0,
+                      capacity=1 << 20, out=None):
+        """Throughput path. `out` may be a torch cuda tensor viewed as int32 [capacity,6] to keep results on device."""
+        ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
+        pp = PyramidParams(num_octaves, 3, sigma0, 0)
+        dp = DogParams(window, contrast_thr, edge_r)
+        counts = (C.c_int * n)()
+        if out is None:
+            host = np.zeros(capacity, KEYPOINT_DTYPE)
+            optr, ospace = host.ctypes.data, HOST
+        else:
+            host = None
+            optr, ospace = out.data_ptr(), DEVICE
+            capacity = out.shape[0]
+        rc = load().vslam_dog_keypoints(self.h, ptr, n, h, w, pitch, stride, space, C.byref(pp), C.byref(dp), optr,
+                                        capacity, ospace, counts)
+        if rc and rc != E_CAPACITY:
+            self._chk(rc)
+        cl = list(counts)
+        return {"keypoints": host[:min(sum(cl), capacity)] if host is not None else out, "counts": cl,
+                "overflow": rc == E_CAPACITY}
+
+    def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None):
+        ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
+        hp = HarrisParams(k, nms2_window)
+        counts = (C.c_int * n)()
+        if device_out is not None:      # dict of torch cuda tensors: response/r8/mask3 (optional), corners (required)
+            g = lambda name: device_out[name].data_ptr() if device_out.get(name) is not None else None
+            capacity = device_out["corners"].shape[0]
+            rc = load().vslam_harris(self.h, ptr, n, h, w, pitch, stride, space, C.byref(hp), g("response"), g("r8"),
+                                     g("mask3"), g("corners"), capacity, DEVICE, counts)
+            if rc and rc != E_CAPACITY:
+                self._chk(rc)
+            return {"counts": list(counts), "overflow": rc == E_CAPACITY}
+        resp = np.empty((n, h, w), np.float32) if want_maps else None
+        r8 = np.empty((n, h, w), np.uint8) if want_maps else None
+        m3 = np.empty((n, h, w), np.uint8) if want_maps else None
+        corners = np.zeros(capacity, CORNER_DTYPE)
+        p = lambda a: a.ctypes.data if a is not None else None
+        rc = load().vslam_harris(self.h, ptr, n, h, w, pitch, stride, space, C.byref(hp), p(resp), p(r8), p(m3),
+                                 corners.ctypes.data, capacity, HOST, counts)
+        if rc and rc != E_CAPACITY:
+            self._chk(rc)
+        cl = list(counts)
+        return {"response": resp, "r8": r8, "mask3": m3, "corners": corners[:min(sum(cl), capacity)], "counts": cl,
+                "overflow": rc == E_CAPACITY}

@@ -1,0 +1,532 @@
+// capi.cu -- the C ABI of include/vslam.h: contexts, GaussPyramid build/getters, DoG detection, Harris.
+// Host orchestration only; kernels live in pyramid.cu, detect.cu, harris.cu, compaction.cu.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "detect.cuh"
+#include "harris.cuh"
+#include "pyramid.cuh"
+
+using namespace vslam;
+
+namespace vslam {
+static std::mutex g_err_mu;
+static std::string g_err;
+void set_global_error(const std::string &s) {
+    std::lock_guard<std::mutex> l(g_err_mu);
+    g_err = s;
+}
+}  // namespace vslam
+
+struct vslam_pyramid {
+    int device = 0;
+    int n_frames = 0, rows = 0, cols = 0, num_octaves = 0, scale_samples = 3;
+    double sigma0 = 0;
+    uint32_t materialise = 0;
+    int orows[16], ocols[16];
+    size_t opitch[16], ooff[16], oplane[16];   // pitch, byte offset of the octave inside a frame block, plane bytes
+    size_t frame_bytes = 0;
+    double sigma[16][6];
+    DevBuf maps;                                // n_frames x [octave][base, gauss0..5, dog0..4]
+    u8 *plane(int f, int o, int idx) const { return maps.as<u8>() + (size_t)f * frame_bytes + ooff[o] + oplane[o] * idx; }
+};
+
+static const int kCounterBase = 16;             // counters: [0] staging cursor, [2] running total, [16+f] per frame
+
+extern "C" {
+
+const char *vslam_version(void) { return "visualslam_b200 0.1 (sm_100a)"; }
+
+const char *vslam_last_error(const vslam_ctx *ctx) {
+    if (ctx) return ctx->err.c_str();
+    static thread_local std::string copy;
+    std::lock_guard<std::mutex> l(g_err_mu);
+    copy = g_err;
+    return copy.c_str();
+}
+
+int vslam_ctx_create_on_stream(int device, void *cuda_stream, vslam_ctx **out) {
+    if (!out) VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_INVALID, "vslam_ctx_create: out is null");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_CUDA, "no CUDA device available (%s); this library has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    }
+    if (device < 0 || device >= n) VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_INVALID, "device %d out of range [0,%d)", device, n);
+    vslam_ctx *ctx = new (std::nothrow) vslam_ctx();
+    if (!ctx) return VSLAM_E_NOMEM;
+    ctx->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { delete ctx; VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_CUDA, "cudaSetDevice(%d) failed", device); }
+    if (cuda_stream) {
+        ctx->stream = (cudaStream_t)cuda_stream;
+    } else {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+            delete ctx;
+            VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_CUDA, "cudaStreamCreate failed");
+        }
+        ctx->own_stream = true;
+    }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    ctx->pinned_cap = 1 << 20;
+    if (cudaMallocHost(&ctx->pinned, ctx->pinned_cap) != cudaSuccess) { ctx->pinned = nullptr; ctx->pinned_cap = 0; cudaGetLastError(); }
+    *out = ctx;
+    return VSLAM_OK;
+}
+
+int vslam_ctx_create(int device, vslam_ctx **out) { return vslam_ctx_create_on_stream(device, nullptr, out); }
+
+void vslam_ctx_destroy(vslam_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    DevBuf *bufs[] = {&ctx->seg_off, &ctx->seg_cnt, &ctx->seg_dst, &ctx->staging, &ctx->counters, &ctx->stage_counts,
+                      &ctx->ingest, &ctx->taps, &ctx->hbuf, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev};
+    for (DevBuf *b : bufs) b->release();
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    free(ctx->h_taps);
+    delete ctx;
+}
+
+int vslam_sync(vslam_ctx *ctx) {
+    if (!ctx) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VSLAM_OK;
+}
+
+long long vslam_launch_count(const vslam_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+double vslam_calculate_sigma(int octave, int level, double sigma0, int scale_samples) {
+    const double k = pow(2.0, 1.0 / (double)scale_samples);      // GaussPyramid.hpp:69
+    return pow(2, octave) * sigma0 * pow(k, level);               // GaussPyramid.cpp:157,161
+}
+int vslam_calculate_num_octaves(int rows, int cols) {              // GaussPyramid.cpp:150-152
+    return (int)floor(log2((double)(rows < cols ? rows : cols))) - 4;
+}
+int vslam_gauss_ksize(double sigma) { return host_gauss_ksize(sigma); }
+int vslam_gauss_taps(double sigma, int ksize, int32_t *taps) {
+    if (!taps) return VSLAM_E_INVALID;
+    return host_gauss_taps(sigma, ksize, taps);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// internals
+// ---------------------------------------------------------------------------------------------------------------
+static int ensure_taps(vslam_ctx *ctx, int num_octaves, double sigma0, int scale_samples) {
+    if (ctx->h_taps && ctx->taps_octaves == num_octaves && ctx->taps_sigma0 == sigma0 && ctx->taps_scale_samples == scale_samples)
+        return VSLAM_OK;
+    free(ctx->h_taps);
+    ctx->h_taps = malloc(sizeof(OctaveTaps) * (size_t)num_octaves);
+    if (!ctx->h_taps) return VSLAM_E_NOMEM;
+    ctx->taps_octaves = 0;
+    OctaveTaps *h = (OctaveTaps *)ctx->h_taps;
+    for (int o = 0; o < num_octaves; ++o) {
+        const int rc = build_octave_taps(sigma0, scale_samples, o, &h[o]);
+        if (rc) VS_FAIL(ctx, rc, "octave %d: Gaussian kernel wider than %d taps is not supported (sigma0=%g)", o, kMaxKsize, sigma0);
+    }
+    if (ctx->taps.reserve(sizeof(OctaveTaps) * (size_t)num_octaves)) VS_FAIL(ctx, VSLAM_E_NOMEM, "tap table allocation failed");
+    VS_CUDA(ctx, cudaMemcpyAsync(ctx->taps.p, h, sizeof(OctaveTaps) * (size_t)num_octaves, cudaMemcpyHostToDevice, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->taps_octaves = num_octaves; ctx->taps_sigma0 = sigma0; ctx->taps_scale_samples = scale_samples;
+    return VSLAM_OK;
+}
+
+struct Geometry {
+    int num_octaves;
+    int orows[16], ocols[16];
+    size_t opitch[16], ooff[16], oplane[16];
+    size_t frame_bytes;
+};
+
+static int make_geometry(vslam_ctx *ctx, int rows, int cols, const vslam_pyramid_params *pp, Geometry *g, int *num_octaves,
+                         double *sigma0) {
+    if (rows <= 0 || cols <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
+    if (rows > (1 << 15) || cols > (1 << 15)) VS_FAIL(ctx, VSLAM_E_INVALID, "image larger than 32768 on a side");
+    const int ss = pp ? pp->scale_samples : 3;
+    if (ss != 3 && ss != 0) VS_FAIL(ctx, VSLAM_E_INVALID, "scale_samples must be 3 (numLevels_ = 6)");
+    int no = pp ? pp->num_octaves : 4;
+    if (no <= 0) no = vslam_calculate_num_octaves(rows, cols);
+    if (no <= 0 || no > 12) VS_FAIL(ctx, VSLAM_E_INVALID, "num_octaves %d", no);
+    *sigma0 = pp && pp->sigma0 > 0 ? pp->sigma0 : 1.6;
+    *num_octaves = no;
+    g->num_octaves = no;
+    int r = 2 * rows, c = 2 * cols;
+    size_t off = 0;
+    for (int o = 0; o < no; ++o) {
+        if (r <= 0 || c <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "octave %d would be empty (%dx%d input)", o, rows, cols);
+        g->orows[o] = r; g->ocols[o] = c;
+        g->opitch[o] = plane_pitch(c);
+        g->oplane[o] = round_up(plane_bytes(r, c), 256);
+        g->ooff[o] = off;
+        off += g->oplane[o] * 12;
+        half_size(r, c, &r, &c);
+    }
+    g->frame_bytes = off;
+    return VSLAM_OK;
+}
+
+static void octave_planes(const Geometry &g, u8 *frame_block, int o, OctavePlanes *op) {
+    u8 *b = frame_block + g.ooff[o];
+    op->rows = g.orows[o]; op->cols = g.ocols[o]; op->pitch = g.opitch[o];
+    op->base = b;
+    for (int l = 0; l < 6; ++l) op->gauss[l] = b + g.oplane[o] * (1 + l);
+    for (int l = 0; l < 5; ++l) op->dog[l] = b + g.oplane[o] * (7 + l);
+    if (o + 1 < g.num_octaves) {
+        op->next_base = frame_block + g.ooff[o + 1];
+        op->next_rows = g.orows[o + 1]; op->next_cols = g.ocols[o + 1]; op->next_pitch = g.opitch[o + 1];
+    } else {
+        op->next_base = nullptr; op->next_rows = op->next_cols = 0; op->next_pitch = 0;
+    }
+}
+
+// Frames that live on the host are copied into ctx->ingest (pitch = multiple of 256); device frames are used in place.
+static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int cols, size_t pitch, size_t frame_stride,
+                         int space, const u8 **d_frames, size_t *d_pitch, size_t *d_stride) {
+    if (!frames || n <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "frames null or n_frames <= 0");
+    if (pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch %zu < cols %d", pitch, cols);
+    if (n > 1 && frame_stride < pitch * (size_t)rows) VS_FAIL(ctx, VSLAM_E_INVALID, "frame_stride too small");
+    if (space == VSLAM_DEVICE) {
+        *d_frames = frames; *d_pitch = pitch; *d_stride = frame_stride;
+        return VSLAM_OK;
+    }
+    const size_t dp = round_up((size_t)cols, 256), ds = dp * (size_t)rows;
+    if (ctx->ingest.reserve(ds * (size_t)n)) VS_FAIL(ctx, VSLAM_E_NOMEM, "ingest buffer (%zu bytes)", ds * (size_t)n);
+    for (int f = 0; f < n; ++f)
+        VS_CUDA(ctx, cudaMemcpy2DAsync(ctx->ingest.as<u8>() + ds * f, dp, frames + frame_stride * f, pitch, (size_t)cols,
+                                       (size_t)rows, cudaMemcpyHostToDevice, ctx->stream));
+    *d_frames = ctx->ingest.as<u8>(); *d_pitch = dp; *d_stride = ds;
+    return VSLAM_OK;
+}
+
+// rows A-D for one frame into `block` (laid out by Geometry)
+static int build_frame(vslam_ctx *ctx, const Geometry &g, const u8 *frame, int rows, int cols, size_t pitch, u8 *block) {
+    const OctaveTaps *h = (const OctaveTaps *)ctx->h_taps;
+    VS_TRY(launch_upsample2x(ctx, frame, rows, cols, pitch, block + g.ooff[0], g.opitch[0]));
+    const size_t hpitch = round_up((size_t)g.ocols[0], 128);
+    for (int o = 0; o < g.num_octaves; ++o) {
+        OctavePlanes op;
+        octave_planes(g, block, o, &op);
+        const size_t hp_o = round_up((size_t)g.ocols[o], 128);
+        (void)hpitch;
+        VS_TRY(launch_octave_blur(ctx, op, ctx->taps.as<OctaveTaps>() + o, h[o], ctx->hbuf.as<u16>(), hp_o));
+    }
+    return VSLAM_OK;
+}
+
+static int reserve_hbuf(vslam_ctx *ctx, const Geometry &g) {
+    const size_t need = round_up((size_t)g.ocols[0], 128) * (size_t)g.orows[0] * 6 * sizeof(u16);
+    if (ctx->hbuf.reserve(need)) VS_FAIL(ctx, VSLAM_E_NOMEM, "H-pass workspace (%zu bytes)", need);
+    return VSLAM_OK;
+}
+
+static size_t detect_segments(const Geometry &g, int window, int *seg_base /*[num_octaves]*/) {
+    size_t n = 0;
+    for (int o = 0; o < g.num_octaves; ++o) {
+        int ni, nj, nc;
+        detect_grid(g.orows[o], g.ocols[o], window, &ni, &nj, &nc);
+        seg_base[o] = (int)n;
+        n += (size_t)3 * ni * nc;
+    }
+    return n;
+}
+
+// rows G-J for one frame whose planes are in `block`; appends to d_out in emission order.
+static int detect_frame(vslam_ctx *ctx, const Geometry &g, u8 *block, const vslam_dog_params &dp, const int *seg_base,
+                        size_t n_seg, vslam_keypoint *d_out, int capacity, int frame, unsigned long long *d_stage) {
+    int *cnt = ctx->counters.as<int>();
+    VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
+    for (int o = 0; o < g.num_octaves; ++o) {
+        OctavePlanes op;
+        octave_planes(g, block, o, &op);
+        DetectArgs a;
+        for (int l = 0; l < 5; ++l) a.dog[l] = op.dog[l];
+        for (int l = 0; l < 6; ++l) a.gauss[l] = op.gauss[l];
+        a.rows = op.rows; a.cols = op.cols; a.pitch = op.pitch; a.octave = o;
+        detect_grid(op.rows, op.cols, dp.window, &a.ni, &a.nj, &a.nchunks);
+        if (a.ni == 0 || a.nchunks == 0) continue;
+        a.seg_base = seg_base[o];
+        a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
+        a.cursor = cnt;
+        a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = capacity;
+        a.stage_counts = d_stage ? d_stage + ((size_t)frame * g.num_octaves + o) * 4 : nullptr;
+        VS_TRY(launch_detect(ctx, a, dp));
+    }
+    return seg_finalise(ctx, n_seg, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + frame);
+}
+
+static int finish_counts(vslam_ctx *ctx, int n_frames, int capacity, int *counts, long long *total_out) {
+    std::vector<int> h((size_t)n_frames);
+    VS_CUDA(ctx, cudaMemcpyAsync(h.data(), ctx->counters.as<int>() + kCounterBase, sizeof(int) * (size_t)n_frames,
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    long long total = 0;
+    for (int f = 0; f < n_frames; ++f) { if (counts) counts[f] = h[f]; total += h[f]; }
+    *total_out = total;
+    (void)capacity;
+    return VSLAM_OK;
+}
+
+static int reserve_counters(vslam_ctx *ctx, int n_frames) {
+    const size_t bytes = sizeof(int) * (size_t)(kCounterBase + n_frames);
+    if (ctx->counters.reserve(bytes)) VS_FAIL(ctx, VSLAM_E_NOMEM, "counter buffer");
+    VS_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, bytes, ctx->stream));
+    return VSLAM_OK;
+}
+
+extern "C" {
+
+int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
+                        size_t frame_stride, int space, const vslam_pyramid_params *params, vslam_pyramid **out) {
+    if (!ctx || !out) return VSLAM_E_INVALID;
+    *out = nullptr;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    Geometry g;
+    int no; double s0;
+    VS_TRY(make_geometry(ctx, rows, cols, params, &g, &no, &s0));
+    VS_TRY(ensure_taps(ctx, no, s0, 3));
+    const u8 *d_frames; size_t d_pitch, d_stride;
+    VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
+    VS_TRY(reserve_hbuf(ctx, g));
+    vslam_pyramid *p = new (std::nothrow) vslam_pyramid();
+    if (!p) return VSLAM_E_NOMEM;
+    p->device = ctx->device; p->n_frames = n_frames; p->rows = rows; p->cols = cols; p->num_octaves = no;
+    p->sigma0 = s0; p->materialise = params ? params->materialise : 0;
+    for (int o = 0; o < no; ++o) {
+        p->orows[o] = g.orows[o]; p->ocols[o] = g.ocols[o]; p->opitch[o] = g.opitch[o]; p->ooff[o] = g.ooff[o];
+        p->oplane[o] = g.oplane[o];
+        for (int l = 0; l < 6; ++l) p->sigma[o][l] = vslam_calculate_sigma(o, l, s0, 3);
+    }
+    p->frame_bytes = g.frame_bytes;
+    if (p->maps.reserve(g.frame_bytes * (size_t)n_frames)) {
+        delete p;
+        VS_FAIL(ctx, VSLAM_E_NOMEM, "pyramid of %d frames needs %zu bytes", n_frames, g.frame_bytes * (size_t)n_frames);
+    }
+    for (int f = 0; f < n_frames; ++f) {
+        const int rc = build_frame(ctx, g, d_frames + d_stride * f, rows, cols, d_pitch, p->maps.as<u8>() + g.frame_bytes * f);
+        if (rc) { cudaStreamSynchronize(ctx->stream); p->maps.release(); delete p; return rc; }
+    }
+    *out = p;
+    return VSLAM_OK;
+}
+
+void vslam_pyramid_destroy(vslam_pyramid *pyr) {
+    if (!pyr) return;
+    cudaSetDevice(pyr->device);
+    cudaDeviceSynchronize();
+    pyr->maps.release();
+    delete pyr;
+}
+int vslam_pyramid_num_octaves(const vslam_pyramid *pyr) { return pyr ? pyr->num_octaves : VSLAM_E_INVALID; }
+int vslam_pyramid_num_frames(const vslam_pyramid *pyr) { return pyr ? pyr->n_frames : VSLAM_E_INVALID; }
+int vslam_pyramid_octave_size(const vslam_pyramid *pyr, int octave, int *rows, int *cols) {
+    if (!pyr || octave < 0 || octave >= pyr->num_octaves) return VSLAM_E_INVALID;
+    if (rows) *rows = pyr->orows[octave];
+    if (cols) *cols = pyr->ocols[octave];
+    return VSLAM_OK;
+}
+int vslam_pyramid_sigma(const vslam_pyramid *pyr, int octave, int level, double *sigma) {
+    if (!pyr || !sigma || octave < 0 || octave >= pyr->num_octaves || level < 0 || level >= 6) return VSLAM_E_INVALID;
+    *sigma = pyr->sigma[octave][level];
+    return VSLAM_OK;
+}
+
+static int map_plane_index(int kind, int level) {
+    if (kind == VSLAM_MAP_BASE) return 0;
+    if (kind == VSLAM_MAP_GAUSS && level >= 0 && level < 6) return 1 + level;
+    if (kind == VSLAM_MAP_DOG && level >= 0 && level < 5) return 7 + level;
+    return -1;
+}
+
+const uint8_t *vslam_pyramid_device_map(const vslam_pyramid *pyr, int frame, int kind, int octave, int level, size_t *pitch) {
+    if (!pyr || frame < 0 || frame >= pyr->n_frames || octave < 0 || octave >= pyr->num_octaves) return nullptr;
+    const int idx = map_plane_index(kind, level);
+    if (idx < 0) return nullptr;
+    if (pitch) *pitch = pyr->opitch[octave];
+    return pyr->plane(frame, octave, idx);
+}
+
+int vslam_pyramid_get(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int kind, int octave, int level, void *dst,
+                      size_t dst_pitch, int space) {
+    if (!ctx || !pyr || !dst) return VSLAM_E_INVALID;
+    if (frame < 0 || frame >= pyr->n_frames || octave < 0 || octave >= pyr->num_octaves)
+        VS_FAIL(ctx, VSLAM_E_INVALID, "frame %d / octave %d out of range", frame, octave);
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int r = pyr->orows[octave], c = pyr->ocols[octave];
+    const cudaMemcpyKind mk = space == VSLAM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    if (kind <= VSLAM_MAP_DOG) {
+        const int idx = map_plane_index(kind, level);
+        if (idx < 0) VS_FAIL(ctx, VSLAM_E_INVALID, "kind %d level %d", kind, level);
+        if (dst_pitch < (size_t)c) VS_FAIL(ctx, VSLAM_E_INVALID, "dst_pitch %zu < %d", dst_pitch, c);
+        VS_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_pitch, pyr->plane(frame, octave, idx), pyr->opitch[octave], (size_t)c, (size_t)r, mk, ctx->stream));
+    } else if (kind <= VSLAM_MAP_ORIENT) {
+        if (level < 0 || level >= 6) VS_FAIL(ctx, VSLAM_E_INVALID, "level %d", level);
+        if (dst_pitch < (size_t)c * 4) VS_FAIL(ctx, VSLAM_E_INVALID, "dst_pitch %zu < %d floats", dst_pitch, c);
+        // gradient maps are formed from the resident Gaussian level (row E); one dense fp32 scratch plane
+        float *tmp = (float *)dst;
+        size_t tp = dst_pitch / 4;
+        if (space != VSLAM_DEVICE || (dst_pitch & 3)) {
+            if (ctx->maps_dev.reserve((size_t)r * c * 4)) VS_FAIL(ctx, VSLAM_E_NOMEM, "gradient scratch");
+            tmp = ctx->maps_dev.as<float>(); tp = (size_t)c;
+        }
+        const u8 *gl = pyr->plane(frame, octave, 1 + level);
+        VS_TRY(launch_gradients(ctx, gl, r, c, pyr->opitch[octave], kind == VSLAM_MAP_GRADX ? tmp : nullptr,
+                                kind == VSLAM_MAP_GRADY ? tmp : nullptr, kind == VSLAM_MAP_MAG ? tmp : nullptr,
+                                kind == VSLAM_MAP_ORIENT ? tmp : nullptr, tp));
+        if ((void *)tmp != dst)
+            VS_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_pitch, tmp, tp * 4, (size_t)c * 4, (size_t)r, mk, ctx->stream));
+    } else {
+        VS_FAIL(ctx, VSLAM_E_INVALID, "unknown map kind %d", kind);
+    }
+    if (space != VSLAM_DEVICE) VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VSLAM_OK;
+}
+
+static int check_dog_params(vslam_ctx *ctx, const vslam_dog_params *in, vslam_dog_params *dp) {
+    dp->window = in ? in->window : 3;
+    dp->contrast_thr = in ? in->contrast_thr : 0.03f;
+    dp->edge_r = in ? in->edge_r : 10.0f;
+    if (dp->window < 1 || dp->window > 15) VS_FAIL(ctx, VSLAM_E_INVALID, "window %d", dp->window);
+    if (!(dp->edge_r > 0)) VS_FAIL(ctx, VSLAM_E_INVALID, "edge_r %g", dp->edge_r);
+    return VSLAM_OK;
+}
+
+static int emit_list(vslam_ctx *ctx, void *out, int out_space, const void *d_list, size_t entry, long long total, int capacity) {
+    if (out_space != VSLAM_DEVICE && out) {
+        const size_t n = (size_t)(total < capacity ? total : capacity);
+        if (n) VS_CUDA(ctx, cudaMemcpyAsync(out, d_list, n * entry, cudaMemcpyDeviceToHost, ctx->stream));
+        VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    if (total > capacity) VS_FAIL(ctx, VSLAM_E_CAPACITY, "output list holds %d entries, %lld produced", capacity, total);
+    return VSLAM_OK;
+}
+
+int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_params *params, vslam_keypoint *out,
+                     int capacity, int space, int *counts, long long *stage_counts) {
+    if (!ctx || !pyr || capacity < 0 || (!out && capacity > 0)) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    vslam_dog_params dp;
+    VS_TRY(check_dog_params(ctx, params, &dp));
+    Geometry g;
+    g.num_octaves = pyr->num_octaves; g.frame_bytes = pyr->frame_bytes;
+    for (int o = 0; o < g.num_octaves; ++o) {
+        g.orows[o] = pyr->orows[o]; g.ocols[o] = pyr->ocols[o]; g.opitch[o] = pyr->opitch[o]; g.ooff[o] = pyr->ooff[o];
+        g.oplane[o] = pyr->oplane[o];
+    }
+    int seg_base[16];
+    const size_t n_seg = detect_segments(g, dp.window, seg_base);
+    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint) * (size_t)(capacity + 1)));
+    VS_TRY(reserve_counters(ctx, pyr->n_frames));
+    vslam_keypoint *d_out = out;
+    if (space != VSLAM_DEVICE) {
+        if (ctx->out_dev.reserve(sizeof(vslam_keypoint) * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device keypoint list");
+        d_out = ctx->out_dev.as<vslam_keypoint>();
+    }
+    unsigned long long *d_stage = nullptr;
+    const size_t stage_n = (size_t)pyr->n_frames * g.num_octaves * 4;
+    if (stage_counts) {
+        if (ctx->stage_counts.reserve(stage_n * 8)) VS_FAIL(ctx, VSLAM_E_NOMEM, "stage counters");
+        d_stage = ctx->stage_counts.as<unsigned long long>();
+        VS_CUDA(ctx, cudaMemsetAsync(d_stage, 0, stage_n * 8, ctx->stream));
+    }
+    for (int f = 0; f < pyr->n_frames; ++f)
+        VS_TRY(detect_frame(ctx, g, pyr->maps.as<u8>() + pyr->frame_bytes * f, dp, seg_base, n_seg, d_out, capacity, f, d_stage));
+    long long total = 0;
+    if (stage_counts) VS_CUDA(ctx, cudaMemcpyAsync(stage_counts, d_stage, stage_n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_TRY(finish_counts(ctx, pyr->n_frames, capacity, counts, &total));
+    return emit_list(ctx, out, space, d_out, sizeof(vslam_keypoint), total, capacity);
+}
+
+int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
+                        size_t frame_stride, int space, const vslam_pyramid_params *pparams,
+                        const vslam_dog_params *dparams, vslam_keypoint *out, int capacity, int out_space, int *counts) {
+    if (!ctx || capacity < 0 || (!out && capacity > 0)) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    vslam_dog_params dp;
+    VS_TRY(check_dog_params(ctx, dparams, &dp));
+    Geometry g;
+    int no; double s0;
+    VS_TRY(make_geometry(ctx, rows, cols, pparams, &g, &no, &s0));
+    VS_TRY(ensure_taps(ctx, no, s0, 3));
+    const u8 *d_frames; size_t d_pitch, d_stride;
+    VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
+    VS_TRY(reserve_hbuf(ctx, g));
+    if (ctx->ws_maps.reserve(g.frame_bytes)) VS_FAIL(ctx, VSLAM_E_NOMEM, "frame workspace (%zu bytes)", g.frame_bytes);
+    int seg_base[16];
+    const size_t n_seg = detect_segments(g, dp.window, seg_base);
+    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint) * (size_t)(capacity + 1)));
+    VS_TRY(reserve_counters(ctx, n_frames));
+    vslam_keypoint *d_out = out;
+    if (out_space != VSLAM_DEVICE) {
+        if (ctx->out_dev.reserve(sizeof(vslam_keypoint) * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device keypoint list");
+        d_out = ctx->out_dev.as<vslam_keypoint>();
+    }
+    for (int f = 0; f < n_frames; ++f) {
+        VS_TRY(build_frame(ctx, g, d_frames + d_stride * f, rows, cols, d_pitch, ctx->ws_maps.as<u8>()));
+        VS_TRY(detect_frame(ctx, g, ctx->ws_maps.as<u8>(), dp, seg_base, n_seg, d_out, capacity, f, nullptr));
+    }
+    long long total = 0;
+    VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
+    return emit_list(ctx, out, out_space, d_out, sizeof(vslam_keypoint), total, capacity);
+}
+
+int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
+                 size_t frame_stride, int space, const vslam_harris_params *params, float *response, uint8_t *r8,
+                 uint8_t *mask3, vslam_corner *corners, int capacity, int out_space, int *counts) {
+    if (!ctx || capacity < 0 || (!corners && capacity > 0)) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (rows <= 0 || cols <= 0 || rows > (1 << 15) || cols > (1 << 15)) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
+    const float k = params ? params->k : 0.04f;
+    const int w2 = params ? params->nms2_window : 5;
+    if (w2 != 3 && w2 != 5) VS_FAIL(ctx, VSLAM_E_INVALID, "nms2_window must be 3 or 5 (got %d)", w2);
+    const u8 *d_frames; size_t d_pitch, d_stride;
+    VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
+    int ntx, nty;
+    harris_grid(rows, cols, &ntx, &nty);
+    const size_t n_seg = (size_t)rows * ntx;
+    VS_TRY(seg_prepare(ctx, n_seg, sizeof(vslam_corner) * (size_t)(capacity + 1)));
+    VS_TRY(reserve_counters(ctx, n_frames));
+    vslam_corner *d_out = corners;
+    if (out_space != VSLAM_DEVICE) {
+        if (ctx->out_dev.reserve(sizeof(vslam_corner) * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device corner list");
+        d_out = ctx->out_dev.as<vslam_corner>();
+    }
+    const size_t px = (size_t)rows * cols;
+    float *d_resp = response; u8 *d_r8 = r8, *d_m3 = mask3;
+    if (out_space != VSLAM_DEVICE && (response || r8 || mask3)) {
+        if (ctx->maps_dev.reserve(px * 6 * (size_t)n_frames)) VS_FAIL(ctx, VSLAM_E_NOMEM, "device maps (%zu bytes)", px * 6 * (size_t)n_frames);
+        d_resp = response ? ctx->maps_dev.as<float>() : nullptr;
+        d_r8 = r8 ? ctx->maps_dev.as<u8>() + px * 4 * n_frames : nullptr;
+        d_m3 = mask3 ? ctx->maps_dev.as<u8>() + px * 5 * n_frames : nullptr;
+    }
+    int *cnt = ctx->counters.as<int>();
+    for (int f = 0; f < n_frames; ++f) {
+        VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
+        HarrisArgs a;
+        a.frame = d_frames + d_stride * f; a.rows = rows; a.cols = cols; a.pitch = d_pitch; a.k = k; a.nms2_pad = (w2 - 1) / 2;
+        a.response = d_resp ? d_resp + px * f : nullptr;
+        a.r8 = d_r8 ? d_r8 + px * f : nullptr;
+        a.mask3 = d_m3 ? d_m3 + px * f : nullptr;
+        a.seg_base = 0; a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
+        a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = capacity;
+        VS_TRY(launch_harris(ctx, a));
+        VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f));
+    }
+    if (out_space != VSLAM_DEVICE) {
+        if (response) VS_CUDA(ctx, cudaMemcpyAsync(response, d_resp, px * 4 * n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+        if (r8) VS_CUDA(ctx, cudaMemcpyAsync(r8, d_r8, px * n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+        if (mask3) VS_CUDA(ctx, cudaMemcpyAsync(mask3, d_m3, px * n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    long long total = 0;
+    VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
+    return emit_list(ctx, corners, out_space, d_out, sizeof(vslam_corner), total, capacity);
+}
+
+}  // extern "C"

@@ -1,0 +1,136 @@
+// common.cuh -- context, error plumbing and small device helpers shared by every kernel file.
+// Product code: never includes or links anything from oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/vslam.h"
+
+typedef uint8_t u8;
+typedef uint16_t u16;
+typedef uint32_t u32;
+
+namespace vslam {
+
+void set_global_error(const std::string &s);
+
+// A grow-only device buffer owned by a context / pyramid.
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return VSLAM_OK;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { cudaGetLastError(); p = nullptr; return VSLAM_E_NOMEM; }
+        cap = want;
+        return VSLAM_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return (T *)p; }
+};
+
+}  // namespace vslam
+
+struct vslam_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    long long launches = 0;
+    int sm_count = 148;
+    // segment-ordered compaction workspace (detect + harris corners)
+    vslam::DevBuf seg_off, seg_cnt, seg_dst, staging, counters, stage_counts;
+    // throughput-path workspace: one frame's pyramid, reused
+    vslam::DevBuf ingest;          // aligned copy of the input frame(s)
+    vslam::DevBuf taps;            // OctaveTaps[num_octaves]
+    vslam::DevBuf hbuf;            // 6 x u16 H-pass planes of the largest octave
+    vslam::DevBuf ws_maps;         // base/gauss/dog planes of one frame
+    vslam::DevBuf out_dev;         // device output list when the caller's list is on the host
+    vslam::DevBuf maps_dev;        // device response/r8/mask when the caller's maps are on the host
+    void *pinned = nullptr;        // small pinned host scratch for counters
+    size_t pinned_cap = 0;
+    // cached tap tables (host copy mirrors the device copy in `taps`)
+    int taps_octaves = 0; double taps_sigma0 = 0; int taps_scale_samples = 0;
+    void *h_taps = nullptr;        // OctaveTaps[taps_octaves], malloc'd
+};
+
+#define VS_FAIL(ctx, code, ...)                                  \
+    do {                                                         \
+        char _b[512];                                            \
+        snprintf(_b, sizeof _b, __VA_ARGS__);                    \
+        if (ctx) (ctx)->err = _b;                                \
+        vslam::set_global_error(_b);                             \
+        return (code);                                           \
+    } while (0)
+
+#define VS_CUDA(ctx, call)                                                                        \
+    do {                                                                                          \
+        cudaError_t _e = (call);                                                                  \
+        if (_e != cudaSuccess) {                                                                  \
+            cudaGetLastError();                                                                   \
+            VS_FAIL(ctx, VSLAM_E_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+        }                                                                                         \
+    } while (0)
+
+#define VS_TRY(expr)                      \
+    do {                                  \
+        int _rc = (expr);                 \
+        if (_rc != VSLAM_OK) return _rc;  \
+    } while (0)
+
+#define VS_LAUNCH_CHECK(ctx)                       \
+    do {                                           \
+        (ctx)->launches++;                         \
+        VS_CUDA(ctx, cudaGetLastError());          \
+    } while (0)
+
+namespace vslam {
+
+// cv::borderInterpolate(p, len, BORDER_REFLECT_101) incl. repeated bouncing (kernel wider than the image).
+__host__ __device__ __forceinline__ int refl101(int p, int len) {
+    if ((unsigned)p < (unsigned)len) return p;
+    if (len == 1) return 0;
+    do {
+        if (p < 0) p = -p;
+        else p = 2 * (len - 1) - p;
+    } while ((unsigned)p >= (unsigned)len);
+    return p;
+}
+__host__ __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ---- fixed-point Gaussian taps prepared for the two blur kernels -------------------------------------------
+constexpr int kMaxKsize = 255;              // radius <= 127
+constexpr int kHWords = 68;                 // ceil((255+3)/4)=65 -> padded to a multiple of 4
+constexpr int kVPairs = 128;                // r+1 <= 128, padded to a multiple of 8
+struct LevelTaps {
+    int n, r;
+    int delta, wofs;                        // H pass: leading zero taps / first staged word (see pyramid.cu)
+    int kq;                                 // H pass: tap words, multiple of 4
+    int jp;                                 // V pass: tap pairs, multiple of 8
+    u32 hq[kHWords];                        // 4 byte taps per word
+    u32 eo[kVPairs];                        // E pair | O pair << 16
+};
+struct OctaveTaps {
+    LevelTaps lv[6];
+    int rmax, hp;                           // max radius, halo in pixels (multiple of 4)
+};
+
+int host_gauss_ksize(double sigma);
+int host_gauss_taps(double sigma, int n, int32_t *taps);
+int build_octave_taps(double sigma0, int scale_samples, int octave, OctaveTaps *out);
+
+// ---- segment-ordered compaction (compaction.cu) -------------------------------------------------------------
+int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t staging_bytes);
+// after the producer kernel: order the staged entries of n_segments segments into dst[dst_base ...];
+// d_total[0] accumulates the number written so far (device counter); entry_bytes 12 or 24.
+int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, int capacity, int *d_total,
+                 int *d_frame_count);
+
+}  // namespace vslam

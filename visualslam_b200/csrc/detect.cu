@@ -1,0 +1,172 @@
+// detect.cu -- scale-space extrema + contrast + edge tests.
+//
+//   initialKeypointDetection   Diff_of_Gauss.cpp:254-297   stride-`window` grid, half-open 2x2x3 window, ties kept
+//   FeaturePointLocalization   Diff_of_Gauss.cpp:223-251   exact IEEE sequence of OpenCV's gemm / invert(3x3)
+//   computeEdgeResponse + threshold  :79-109, :326-338     2x2 structure sums on the level's gradients, tr^2/det < 12.1
+//
+// One block = one segment = 256 consecutive grid samples of one (level, sample row): survivors are compacted in
+// j order with ballots, one atomicAdd per block reserves staging space, compaction.cu orders the segments.
+// Every float/double operation below uses the round-to-nearest intrinsics so that nvcc cannot contract to FMA.
+#include "detect.cuh"
+
+namespace vslam {
+
+// FeaturePointLocalization's value: dog_zhat = value/255 + 0.5 * A^T * (-(A A^T)^-1) * A   (row H)
+__device__ float localize(int dx, int dy, int ds, int value) {
+    const float v = __fdiv_rn((float)value, 255.0f);
+    // any zero derivative -> a zero row and column in B -> det3 == 0 exactly -> cv::invert yields zeros
+    if (dx == 0 || dy == 0 || ds == 0) return v;
+    const float a0 = __fdiv_rn((float)dx, 255.0f), a1 = __fdiv_rn((float)dy, 255.0f), a2 = __fdiv_rn((float)ds, 255.0f);
+    const double A0 = (double)a0, A1 = (double)a1, A2 = (double)a2;
+    // B = A * A^T through gemm's generic path: double product, stored as float
+    const double b00 = (double)__double2float_rn(__dmul_rn(A0, A0)), b01 = (double)__double2float_rn(__dmul_rn(A0, A1)),
+                 b02 = (double)__double2float_rn(__dmul_rn(A0, A2)), b11 = (double)__double2float_rn(__dmul_rn(A1, A1)),
+                 b12 = (double)__double2float_rn(__dmul_rn(A1, A2)), b22 = (double)__double2float_rn(__dmul_rn(A2, A2));
+    const double b10 = b01, b20 = b02, b21 = b12;
+#define MUL(a, b) __dmul_rn(a, b)
+#define SUB(a, b) __dsub_rn(a, b)
+    // det3, left to right (OpenCV lapack.cpp)
+    double d = __dadd_rn(SUB(MUL(b00, SUB(MUL(b11, b22), MUL(b12, b21))), MUL(b01, SUB(MUL(b10, b22), MUL(b12, b20)))),
+                         MUL(b02, SUB(MUL(b10, b21), MUL(b11, b20))));
+    if (d == 0.0) return v;
+    d = __ddiv_rn(1.0, d);
+    // M = -(B^-1), entries rounded to float (negation is exact)
+    const float m0 = -__double2float_rn(MUL(SUB(MUL(b11, b22), MUL(b12, b21)), d));
+    const float m1 = -__double2float_rn(MUL(SUB(MUL(b02, b21), MUL(b01, b22)), d));
+    const float m2 = -__double2float_rn(MUL(SUB(MUL(b01, b12), MUL(b02, b11)), d));
+    const float m3 = -__double2float_rn(MUL(SUB(MUL(b12, b20), MUL(b10, b22)), d));
+    const float m4 = -__double2float_rn(MUL(SUB(MUL(b00, b22), MUL(b02, b20)), d));
+    const float m5 = -__double2float_rn(MUL(SUB(MUL(b02, b10), MUL(b00, b12)), d));
+    const float m6 = -__double2float_rn(MUL(SUB(MUL(b10, b21), MUL(b11, b20)), d));
+    const float m7 = -__double2float_rn(MUL(SUB(MUL(b01, b20), MUL(b00, b21)), d));
+    const float m8 = -__double2float_rn(MUL(SUB(MUL(b00, b11), MUL(b01, b10)), d));
+#undef MUL
+#undef SUB
+    // z = M * A through gemm's small-matrix path: float accumulate
+    const float z0 = __fadd_rn(__fadd_rn(__fmul_rn(m0, a0), __fmul_rn(m1, a1)), __fmul_rn(m2, a2));
+    const float z1 = __fadd_rn(__fadd_rn(__fmul_rn(m3, a0), __fmul_rn(m4, a1)), __fmul_rn(m5, a2));
+    const float z2 = __fadd_rn(__fadd_rn(__fmul_rn(m6, a0), __fmul_rn(m7, a1)), __fmul_rn(m8, a2));
+    // 0.5 * A^T * z through gemm's generic path: double accumulate, alpha = 0.5
+    const double acc = __dadd_rn(__dadd_rn(__dmul_rn(A0, (double)z0), __dmul_rn(A1, (double)z1)), __dmul_rn(A2, (double)z2));
+    const float q = __double2float_rn(__dmul_rn(0.5, acc));
+    return __fadd_rn(v, q);
+}
+
+// computeEdgeResponse on the gradients of Gaussian level g (Sobel ksize=1 of row E formed on the fly)
+__device__ float edge_response(const u8 *__restrict__ g, int rows, int cols, size_t pitch, int y, int x, int pad) {
+    float ix2 = 0.f, iy2 = 0.f, ixy = 0.f;
+    for (int u = y - pad; u < y + pad; ++u)
+        for (int v = x - pad; v < x + pad; ++v) {
+            const u8 *row = g + (size_t)u * pitch;
+            const float a = (float)((int)row[refl101(v + 1, cols)] - (int)row[refl101(v - 1, cols)]);
+            const float b = (float)((int)g[(size_t)refl101(u + 1, rows) * pitch + v] - (int)g[(size_t)refl101(u - 1, rows) * pitch + v]);
+            ix2 = __fadd_rn(ix2, __fmul_rn(a, a));
+            iy2 = __fadd_rn(iy2, __fmul_rn(b, b));
+            ixy = __fadd_rn(ixy, __fmul_rn(a, b));
+        }
+    const float det = __double2float_rn(__dsub_rn(__dmul_rn((double)ix2, (double)iy2), __dmul_rn((double)ixy, (double)ixy)));
+    const float tr = __fadd_rn(ix2, iy2);
+    return __fdiv_rn(__fmul_rn(tr, tr), det);
+}
+
+__global__ void __launch_bounds__(256) dog_detect_k(DetectArgs a) {
+    __shared__ int s_wcnt[8];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int level = blockIdx.z + 1;
+    const int pad = a.pad, win = a.window;
+    const int i = pad + blockIdx.y * win;
+    const int jj = blockIdx.x * 256 + tid;
+    const int j = pad + jj * win;
+    const int rows = a.rows, cols = a.cols;
+    const size_t pitch = a.pitch;
+    const bool valid = j < cols;            // i < rows by construction of the grid
+
+    bool cand = false, pass_c = false, pass_e = false;
+    int value = 0;
+    if (valid && pad > 0) {
+        const u8 *d0 = a.dog[level - 1], *d1 = a.dog[level], *d2 = a.dog[level + 1];
+        // padded (u,v) <-> original (clamp(u-pad), clamp(v-pad))   (padOctave = replicate, Diff_of_Gauss.cpp:260)
+#define PAD_AT(m, u, v) ((int)(m)[(size_t)clampi((u) - pad, 0, rows - 1) * pitch + clampi((v) - pad, 0, cols - 1)])
+        const int c = PAD_AT(d1, i, j);
+        int mn = c, mx = c;
+        for (int u = i - pad; u < i + pad; ++u)
+            for (int v = j - pad; v < j + pad; ++v) {
+                const int t0 = PAD_AT(d0, u, v), t1 = PAD_AT(d1, u, v), t2 = PAD_AT(d2, u, v);
+                mn = min(mn, min(t0, min(t1, t2)));
+                mx = max(mx, max(t0, max(t1, t2)));
+            }
+        cand = (c == mn) || (c == mx);
+        if (cand) {
+            const int dx = PAD_AT(d1, i, j - 1) - PAD_AT(d1, i, j + 1);
+            const int dy = PAD_AT(d1, i - 1, j) - PAD_AT(d1, i + 1, j);
+            const int ds = PAD_AT(d0, i, j) - PAD_AT(d2, i, j);
+            const float zhat = localize(dx, dy, ds, c);
+            pass_c = zhat > a.contrast_thr;
+            if (pass_c) {
+                value = (int)__fmul_rn(zhat, 255.0f);                       // Diff_of_Gauss.cpp:246
+                const float resp = edge_response(a.gauss[level], rows, cols, pitch, i, j, pad);
+                pass_e = resp < a.edge_thr;                                  // :336 (NaN and +inf fail)
+            }
+        }
+#undef PAD_AT
+    }
+    // ordered compaction inside the block
+    const unsigned bal = __ballot_sync(0xffffffffu, pass_e);
+    const int n_cand = __syncthreads_count(cand);
+    const int n_con = __syncthreads_count(pass_c);
+    if (lane == 0) s_wcnt[wid] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        const int c = s_wcnt[w];
+        if (w < wid) before += c;
+        total += c;
+    }
+    const int seg = a.seg_base + ((level - 1) * a.ni + blockIdx.y) * a.nchunks + blockIdx.x;
+    if (tid == 0) {
+        int off = 0;
+        if (total) off = atomicAdd(a.cursor, total);
+        s_base = off;
+        a.seg_off[seg] = off;
+        a.seg_cnt[seg] = total;
+        if (a.stage_counts) {
+            const int n_valid = min(256, a.nj - blockIdx.x * 256);
+            atomicAdd(&a.stage_counts[0], (unsigned long long)n_valid);
+            if (n_cand) atomicAdd(&a.stage_counts[1], (unsigned long long)n_cand);
+            if (n_con) atomicAdd(&a.stage_counts[2], (unsigned long long)n_con);
+            if (total) atomicAdd(&a.stage_counts[3], (unsigned long long)total);
+        }
+    }
+    __syncthreads();
+    if (pass_e) {
+        const int pos = s_base + before + __popc(bal & ((1u << lane) - 1u));
+        if (pos < a.staging_cap) {
+            vslam_keypoint k;
+            k.row = i; k.col = j; k.value = value; k.padding = pad; k.octave = a.octave; k.level = level;
+            a.staging[pos] = k;
+        }
+    }
+}
+
+int launch_detect(vslam_ctx *ctx, DetectArgs &a, const vslam_dog_params &p) {
+    a.window = p.window;
+    a.pad = (p.window - 1) / 2;
+    a.contrast_thr = p.contrast_thr;
+    const float rp1 = p.edge_r + 1.0f;
+    a.edge_thr = (rp1 * rp1) / p.edge_r;                                    // Diff_of_Gauss.cpp:332-333
+    dim3 g(a.nchunks, a.ni, 3);
+    dog_detect_k<<<g, 256, 0, ctx->stream>>>(a);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
+
+void detect_grid(int rows, int cols, int window, int *ni, int *nj, int *nchunks) {
+    const int pad = (window - 1) / 2;
+    *ni = rows > pad ? (rows - pad + window - 1) / window : 0;
+    *nj = cols > pad ? (cols - pad + window - 1) / window : 0;
+    *nchunks = (*nj + 255) / 256;
+}
+
+}  // namespace vslam

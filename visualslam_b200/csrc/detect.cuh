@@ -1,0 +1,27 @@
+// detect.cuh -- arguments of the DoG detector kernel (detect.cu)
+#pragma once
+#include "common.cuh"
+
+namespace vslam {
+
+struct DetectArgs {
+    const u8 *dog[5];
+    const u8 *gauss[6];
+    int rows, cols;
+    size_t pitch;
+    int octave;
+    int window, pad;
+    float contrast_thr, edge_thr;
+    int ni, nj, nchunks;              // sample rows, sample columns, 256-sample chunks per row
+    int seg_base;                     // first segment index of this octave
+    int *seg_off, *seg_cnt;
+    int *cursor;                      // staging cursor (atomic)
+    vslam_keypoint *staging;
+    int staging_cap;
+    unsigned long long *stage_counts; // 4 counters of this (frame, octave) or nullptr
+};
+
+void detect_grid(int rows, int cols, int window, int *ni, int *nj, int *nchunks);
+int launch_detect(vslam_ctx *ctx, DetectArgs &a, const vslam_dog_params &p);
+
+}  // namespace vslam

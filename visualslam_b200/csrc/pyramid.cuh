@@ -1,0 +1,37 @@
+// pyramid.cuh -- device-side description of one octave and the launchers in pyramid.cu
+#pragma once
+#include "common.cuh"
+
+namespace vslam {
+
+// u8 planes of one octave of one frame, all with the same pitch.
+struct OctavePlanes {
+    int rows, cols;
+    size_t pitch;            // bytes between rows of every u8 plane (multiple of 128)
+    u8 *base;                // octave input  (GaussPyramid::octaveImage)
+    u8 *gauss[6];            // octaveBlur
+    u8 *dog[5];              // octaveDiff
+    u8 *next_base;           // level-3 Gaussian decimated by 2 (nullptr on the last octave)
+    int next_rows, next_cols;
+    size_t next_pitch;
+};
+
+inline size_t plane_pitch(int cols) { return round_up((size_t)cols, 128); }
+inline size_t plane_bytes(int rows, int cols) { return plane_pitch(cols) * (size_t)rows; }
+inline void half_size(int r, int c, int *orows, int *ocols) {
+    // cv::resize dsize = saturate_cast<int>(size*0.5) = cvRound: round half to even (GaussPyramid.cpp:126)
+    auto rne = [](int v) { int q = v / 2; return (v & 1) ? ((q & 1) ? q + 1 : q) : q; };
+    *orows = rne(r); *ocols = rne(c);
+}
+
+// row A
+int launch_upsample2x(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t src_pitch, u8 *dst, size_t dst_pitch);
+// rows B, C, D for one octave: 6 blurs from the octave base + 5 saturating differences + decimated level 3.
+// hbuf: 6 planes of u16, each hpitch elements x rows.
+int launch_octave_blur(vslam_ctx *ctx, const OctavePlanes &op, const OctaveTaps *d_taps, const OctaveTaps &h_taps,
+                       u16 *hbuf, size_t hpitch);
+// row E on demand: any output may be null.
+int launch_gradients(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pitch, float *gx, float *gy, float *mag,
+                     float *orient, size_t out_pitch_elems);
+
+}  // namespace vslam

@@ -104,6 +104,16 @@ VSLAM_API const char *vslam_version(void);
 /* number of kernel launches this context has enqueued since creation (bench.py's gpu_launches) */
 VSLAM_API long long vslam_launch_count(const vslam_ctx *ctx);
 
+/* Per-kernel device timing with CUDA events on the context's stream (used by bench.py's roofline leg).
+ * vslam_profile(ctx, 1) clears the accumulators and starts bracketing every launch; vslam_profile_read syncs the
+ * stream and returns the summed duration and launch count of one kernel class. */
+typedef enum vslam_kernel_id {
+    VSLAM_K_UPSAMPLE = 0, VSLAM_K_HBLUR = 1, VSLAM_K_VBLUR = 2, VSLAM_K_DETECT = 3, VSLAM_K_COMPACT = 4,
+    VSLAM_K_HARRIS = 5, VSLAM_K_GRAD = 6, VSLAM_KERNEL_COUNT = 7
+} vslam_kernel_id;
+VSLAM_API int vslam_profile(vslam_ctx *ctx, int enable);
+VSLAM_API int vslam_profile_read(vslam_ctx *ctx, int kernel_id, double *total_ms, long long *launches);
+
 /* ---- sigma table: GaussPyramid::calculateSigma / calculateNumOctaves (GaussPyramid.cpp:150-162) --------------- */
 VSLAM_API double vslam_calculate_sigma(int octave, int level, double sigma0, int scale_samples);
 VSLAM_API int vslam_calculate_num_octaves(int rows, int cols);

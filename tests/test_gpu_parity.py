@@ -1,0 +1,177 @@
+"""GPU parity tests (run on the B200 box): the CUDA path through the C ABI against the plain-C oracle on the same
+inputs, and against the committed golden fixtures.  Integer / byte / index work is compared bit-exactly; the two fp32
+maps that are not hot-path decisions (magnitude, phase) carry a stated tolerance."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import visualslam_b200 as vs
+from conftest import image_for
+from oracle import c_oracle as O
+from visualslam_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def md5(a):
+    return hashlib.md5(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def kp_array(k):
+    return np.stack([k[n] for n in ("row", "col", "value", "padding", "octave", "level")], 1).astype(np.int32)
+
+
+def check_pyramid_against_oracle(ctx, img, num_octaves=4):
+    pyr = ctx.build_pyramid(img, num_octaves, 1.6)
+    ref = O.build_pyramid(img, num_octaves, 1.6)
+    for o in range(num_octaves):
+        assert pyr.octave_size(o) == ref["base"][o].shape
+        assert np.array_equal(pyr.octave_image(o), ref["base"][o]), ("base", o)
+        for l, (a, b) in enumerate(zip(pyr.octave_blur(o), ref["gauss"][o])):
+            assert np.array_equal(a, b), ("gauss", o, l, int((a != b).sum()))
+        for l, (a, b) in enumerate(zip(pyr.octave_diff(o), ref["dog"][o])):
+            assert np.array_equal(a, b), ("dog", o, l)
+    return pyr, ref
+
+
+@pytest.mark.parametrize("stem", ["home", "building", "blox"])
+def test_pyramid_golden_md5(ctx, stem, golden, images):
+    g = golden["pyramid"][stem]
+    pyr = ctx.build_pyramid(image_for(images, stem, "cvt"), 4, 1.6)
+    assert pyr.num_octaves == 4 and pyr.num_levels == 6
+    assert [list(pyr.octave_size(o)) for o in range(4)] == g["sizes"]
+    assert [md5(pyr.octave_image(o)) for o in range(4)] == g["base"]
+    assert [[md5(m) for m in pyr.octave_blur(o)] for o in range(4)] == g["gauss"]
+    assert [[md5(m) for m in pyr.octave_diff(o)] for o in range(4)] == g["dog"]
+    assert [[md5(m) for m in pyr.octave_grad_x(o)] for o in range(4)] == g["gx"]
+    assert [[md5(m) for m in pyr.octave_grad_y(o)] for o in range(4)] == g["gy"]
+    assert [pyr.octave_sigma(o) for o in range(4)] == g["sigma"]
+    with pytest.raises(IndexError):
+        pyr.sigma_at(4, 0)
+
+
+def test_mag_orient_tolerance(ctx, images, golden_lists):
+    pyr = ctx.build_pyramid(image_for(images, "home", "cvt"), 4, 1.6)
+    mag = pyr.get(vs.MAP_MAG, 3, 1)
+    ori = pyr.get(vs.MAP_ORIENT, 3, 1)
+    assert np.allclose(mag, golden_lists["mag_o3l1_home"], rtol=2e-7, atol=0)         # <= 1 ulp
+    assert np.abs(ori - golden_lists["orient_o3l1_home"]).max() < 1e-3                 # degrees
+
+
+@pytest.mark.parametrize("shape", [(1, 37), (37, 1), (2, 2), (5, 7), (33, 64), (48, 31), (97, 131), (130, 258)])
+def test_pyramid_awkward_sizes(ctx, shape):
+    rng = np.random.default_rng(shape[0] * 1000 + shape[1])
+    img = rng.integers(0, 256, shape, dtype=np.uint8)
+    no = 4 if min(shape) >= 8 else 1
+    check_pyramid_against_oracle(ctx, img, no)
+
+
+@pytest.mark.parametrize("stem", ["home", "building", "blox"])
+def test_dog_keypoints_golden(ctx, stem, golden, images, golden_lists):
+    g = golden["pyramid"][stem]
+    img = image_for(images, stem, "cvt")
+    pyr = ctx.build_pyramid(img, 4, 1.6)
+    res = ctx.dog_detect(pyr)
+    want = golden_lists["dog_" + stem]
+    assert res["counts"] == [len(want)]
+    assert np.array_equal(kp_array(res["keypoints"]), want)            # same points, same emission order
+    sc = res["stage_counts"][0]
+    for o in range(4):
+        c = g["counts"][o]
+        assert sc[o].tolist() == [c["tested"], c["candidates"], c["contrast"], c["edge"]], o
+    # the throughput path gives the same list
+    res2 = ctx.dog_keypoints(img)
+    assert np.array_equal(kp_array(res2["keypoints"]), want)
+
+
+def test_dog_keypoints_synthetic_vs_oracle(ctx):
+    frames = np.stack([synth.frame(i, 270, 480) for i in (0, 4, 7)], 0)
+    res = ctx.dog_keypoints(frames)
+    start = 0
+    for f in range(len(frames)):
+        kc, _, _ = O.dog_keypoints(frames[f])
+        n = res["counts"][f]
+        assert n == len(kc), f
+        assert np.array_equal(kp_array(res["keypoints"][start:start + n]), kc), f
+        start += n
+
+
+def test_dog_capacity_overflow(ctx, images):
+    img = image_for(images, "building", "cvt")
+    res = ctx.dog_keypoints(img, capacity=100)
+    assert res["overflow"] and res["counts"] == [735] and len(res["keypoints"]) == 100
+    full = ctx.dog_keypoints(img)
+    assert np.array_equal(res["keypoints"], full["keypoints"][:100])
+
+
+def test_dog_window_sizes(ctx):
+    img = synth.frame(1, 96, 160)
+    pyr = ctx.build_pyramid(img, 3, 1.6)
+    ref = O.build_pyramid(img, 3, 1.6)
+    for window in (3, 5):
+        res = ctx.dog_detect(pyr, window=window)
+        want = np.concatenate([O.detect_octave(ref["dog"][o], ref["gauss"][o], o, window)[0] for o in range(3)], 0)
+        assert np.array_equal(kp_array(res["keypoints"]), want), window
+
+
+@pytest.mark.parametrize("stem", ["blox", "chessboard", "building", "home"])
+def test_harris_golden(ctx, stem, golden, images, golden_lists):
+    g = golden["harris"][stem]
+    h = ctx.harris(image_for(images, stem, "gray"))
+    assert md5(h["response"][0]) == g["response"]
+    assert md5(h["r8"][0]) == g["r8"]
+    assert md5(h["mask3"][0]) == g["mask3"]
+    assert h["counts"] == [g["n_corners"]]
+    c = h["corners"]
+    assert np.array_equal(np.stack([c["row"], c["col"]], 1), golden_lists["harris_" + stem])    # row-major order
+    assert np.array_equal(c["value"], golden_lists["harris_val_" + stem])
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (1, 9), (9, 1), (2, 3), (4, 4), (5, 5), (31, 65), (64, 64), (100, 257)])
+def test_harris_awkward_sizes(ctx, shape):
+    rng = np.random.default_rng(shape[0] * 7 + shape[1])
+    img = rng.integers(0, 256, shape, dtype=np.uint8)
+    h = ctx.harris(img)
+    ref = O.harris(img)
+    assert np.array_equal(h["response"][0], ref["response"])
+    assert np.array_equal(h["r8"][0], ref["r8"])
+    assert np.array_equal(h["mask3"][0], ref["mask3"])
+    c = h["corners"]
+    assert np.array_equal(np.stack([c["row"], c["col"]], 1).reshape(-1, 2), ref["corners"].reshape(-1, 2))
+    assert np.array_equal(c["value"], ref["corner_values"])
+
+
+def test_harris_batch_and_nms3_window(ctx):
+    frames = synth.batch(5, 120, 200)
+    h = ctx.harris(frames, nms2_window=3)
+    start = 0
+    for f in range(5):
+        ref = O.harris(frames[f], nms_window=3)
+        n = h["counts"][f]
+        assert np.array_equal(h["response"][f], ref["response"])
+        c = h["corners"][start:start + n]
+        assert n == len(ref["corners"]) and np.array_equal(np.stack([c["row"], c["col"]], 1), ref["corners"])
+        start += n
+
+
+def test_full_size_properties(ctx):
+    """BASELINE.json sizes (1080p): size-independent properties instead of a full oracle run.
+    - determinism / batch independence: a frame gives the same keypoints alone and inside a batch
+    - the DoG of a constant frame is empty; Harris of a constant frame has no corner
+    - a 1080p crop-consistent check: the oracle on one frame (seconds) equals the GPU list."""
+    frames = np.stack([synth.frame(i, 1080, 1920) for i in (0, 5)], 0)
+    both = ctx.dog_keypoints(frames)
+    one = ctx.dog_keypoints(frames[1])
+    n0, n1 = both["counts"]
+    assert one["counts"] == [n1]
+    assert np.array_equal(one["keypoints"], both["keypoints"][n0:n0 + n1])
+    kc, _, _ = O.dog_keypoints(frames[0])
+    assert n0 == len(kc) and np.array_equal(kp_array(both["keypoints"][:n0]), kc)
+    flat = np.full((1080, 1920), 77, np.uint8)
+    assert ctx.dog_keypoints(flat)["counts"] == [0]
+    hf = ctx.harris(flat)
+    assert hf["counts"] == [0] and not hf["response"].any()
+    hr = ctx.harris(frames[0])
+    ref = O.harris(frames[0])
+    assert np.array_equal(hr["response"][0], ref["response"]) and hr["counts"] == [len(ref["corners"])]

@@ -54,6 +54,7 @@ EXPORTS = [
     "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_destroy",
     "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
     "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
+    "vslam_profile", "vslam_profile_read",
 ]
 
 _lib = None
@@ -75,6 +76,8 @@ def load():
     L.vslam_sync.argtypes = [vp]
     L.vslam_version.restype = C.c_char_p
     L.vslam_launch_count.argtypes = [vp]; L.vslam_launch_count.restype = C.c_longlong
+    L.vslam_profile.argtypes = [vp, i]
+    L.vslam_profile_read.argtypes = [vp, i, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
     L.vslam_calculate_sigma.argtypes = [i, i, C.c_double, i]; L.vslam_calculate_sigma.restype = C.c_double
     L.vslam_calculate_num_octaves.argtypes = [i, i]
     L.vslam_gauss_ksize.argtypes = [C.c_double]
@@ -198,6 +201,19 @@ class Context:
 
     def sync(self):
         self._chk(load().vslam_sync(self.h))
+
+    KERNELS = ["upsample2x_k", "hblur6_k", "vblur6_k", "dog_detect_k", "seg_scan_k+seg_gather_k", "harris_fused_k", "grad_k"]
+
+    def profile(self, enable=True):
+        self._chk(load().vslam_profile(self.h, 1 if enable else 0))
+
+    def profile_read(self):
+        out = {}
+        for kid, name in enumerate(self.KERNELS):
+            ms, n = C.c_double(), C.c_longlong()
+            self._chk(load().vslam_profile_read(self.h, kid, C.byref(ms), C.byref(n)))
+            out[name] = {"ms": ms.value, "launches": n.value}
+        return out
 
     @property
     def launches(self):

@@ -89,6 +89,7 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
                       &ctx->ingest, &ctx->taps, &ctx->hbuf, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev};
     for (DevBuf *b : bufs) b->release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     free(ctx->h_taps);
     delete ctx;
@@ -101,6 +102,33 @@ int vslam_sync(vslam_ctx *ctx) {
 }
 
 long long vslam_launch_count(const vslam_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+static void drain_spans(vslam_ctx *ctx) {
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &s : ctx->spans) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) { ctx->prof_ms[s.id] += ms; ctx->prof_n[s.id]++; }
+    }
+    cudaGetLastError();
+    ctx->spans.clear();
+    ctx->ev_used = 0;
+}
+
+int vslam_profile(vslam_ctx *ctx, int enable) {
+    if (!ctx) return VSLAM_E_INVALID;
+    drain_spans(ctx);
+    for (int i = 0; i < VSLAM_KERNEL_COUNT; ++i) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
+    ctx->profiling = enable != 0;
+    return VSLAM_OK;
+}
+
+int vslam_profile_read(vslam_ctx *ctx, int kernel_id, double *total_ms, long long *launches) {
+    if (!ctx || kernel_id < 0 || kernel_id >= VSLAM_KERNEL_COUNT) return VSLAM_E_INVALID;
+    drain_spans(ctx);
+    if (total_ms) *total_ms = ctx->prof_ms[kernel_id];
+    if (launches) *launches = ctx->prof_n[kernel_id];
+    return VSLAM_OK;
+}
 
 double vslam_calculate_sigma(int octave, int level, double sigma0, int scale_samples) {
     const double k = pow(2.0, 1.0 / (double)scale_samples);      // GaussPyramid.hpp:69

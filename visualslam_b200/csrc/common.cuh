@@ -58,7 +58,34 @@ struct vslam_ctx {
     // cached tap tables (host copy mirrors the device copy in `taps`)
     int taps_octaves = 0; double taps_sigma0 = 0; int taps_scale_samples = 0;
     void *h_taps = nullptr;        // OctaveTaps[taps_octaves], malloc'd
+    // optional per-kernel CUDA-event timing (vslam_profile): events bracket every launch on ctx->stream
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev_pool;
+    size_t ev_used = 0;
+    struct Span { int id; cudaEvent_t a, b; };
+    std::vector<Span> spans;
+    double prof_ms[VSLAM_KERNEL_COUNT] = {0};
+    long long prof_n[VSLAM_KERNEL_COUNT] = {0};
 };
+
+namespace vslam {
+// RAII bracket around one kernel launch; free when profiling is off.
+struct KernelSpan {
+    vslam_ctx *c; int id; cudaEvent_t stop = nullptr;
+    KernelSpan(vslam_ctx *ctx, int kid) : c(ctx), id(kid) {
+        if (!c->profiling) return;
+        cudaEvent_t ev[2];
+        for (int i = 0; i < 2; ++i) {
+            if (c->ev_used == c->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); c->ev_pool.push_back(e); }
+            ev[i] = c->ev_pool[c->ev_used++];
+        }
+        cudaEventRecord(ev[0], c->stream);
+        stop = ev[1];
+        c->spans.push_back({id, ev[0], ev[1]});
+    }
+    ~KernelSpan() { if (stop) cudaEventRecord(stop, c->stream); }
+};
+}  // namespace vslam
 
 #define VS_FAIL(ctx, code, ...)                                  \
     do {                                                         \

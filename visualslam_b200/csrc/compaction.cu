@@ -82,6 +82,7 @@ int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t staging_bytes) {
 int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, int capacity, int *d_total,
                  int *d_frame_count) {
     const int n = (int)n_segments;
+    KernelSpan span(ctx, VSLAM_K_COMPACT);
     seg_scan_k<<<1, 1024, 0, ctx->stream>>>(ctx->seg_cnt.as<int>(), ctx->seg_dst.as<int>(), n, d_total, d_frame_count);
     VS_LAUNCH_CHECK(ctx);
     seg_gather_k<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->seg_off.as<int>(), ctx->seg_cnt.as<int>(),

@@ -157,6 +157,7 @@ int launch_detect(vslam_ctx *ctx, DetectArgs &a, const vslam_dog_params &p) {
     const float rp1 = p.edge_r + 1.0f;
     a.edge_thr = (rp1 * rp1) / p.edge_r;                                    // Diff_of_Gauss.cpp:332-333
     dim3 g(a.nchunks, a.ni, 3);
+    KernelSpan span(ctx, VSLAM_K_DETECT);
     dog_detect_k<<<g, 256, 0, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;

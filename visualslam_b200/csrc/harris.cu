@@ -165,6 +165,7 @@ void harris_grid(int rows, int cols, int *ntx, int *nty) { *ntx = (cols + TW - 1
 int launch_harris(vslam_ctx *ctx, const HarrisArgs &a) {
     int ntx, nty;
     harris_grid(a.rows, a.cols, &ntx, &nty);
+    KernelSpan span(ctx, VSLAM_K_HARRIS);
     harris_fused_k<<<dim3(ntx, nty), 256, 0, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;

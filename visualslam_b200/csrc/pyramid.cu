@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(256) upsample2x_k(const u8 *__restrict__ src, 
 
 int launch_upsample2x(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t sp, u8 *dst, size_t dp) {
     dim3 b(64, 4), g((2 * cols + 255) / 256, (2 * rows + 3) / 4);
+    KernelSpan span(ctx, VSLAM_K_UPSAMPLE);
     upsample2x_k<<<g, b, 0, ctx->stream>>>(src, rows, cols, sp, dst, dp);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
@@ -233,6 +234,7 @@ int launch_octave_blur(vslam_ctx *ctx, const OctavePlanes &op, const OctaveTaps 
         const int sw = h_taps.hp / 2 + 40, stride = sw | 1;
         const size_t sm = (size_t)HB_ROWS * stride * sizeof(u32);
         dim3 g((op.cols + HB_COLS - 1) / HB_COLS, (op.rows + HB_ROWS - 1) / HB_ROWS);
+        KernelSpan span(ctx, VSLAM_K_HBLUR);
         hblur6_k<<<g, 128, sm, ctx->stream>>>(op.base, op.rows, op.cols, op.pitch, hbuf, hpitch, hplane, d_taps, sw,
                                               stride);
         VS_LAUNCH_CHECK(ctx);
@@ -244,6 +246,7 @@ int launch_octave_blur(vslam_ctx *ctx, const OctavePlanes &op, const OctaveTaps 
         if (sm > 48 * 1024)
             VS_CUDA(ctx, cudaFuncSetAttribute(vblur6_k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         dim3 g((op.cols + VB_COLS - 1) / VB_COLS, (op.rows + VB_ROWS - 1) / VB_ROWS);
+        KernelSpan span(ctx, VSLAM_K_VBLUR);
         vblur6_k<<<g, 128, sm, ctx->stream>>>(hbuf, hpitch, hplane, op, d_taps);
         VS_LAUNCH_CHECK(ctx);
     }
@@ -293,6 +296,7 @@ __global__ void __launch_bounds__(256) grad_k(const u8 *__restrict__ g, int rows
 int launch_gradients(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pitch, float *gx, float *gy, float *mag,
                      float *orient, size_t op) {
     dim3 grid((cols + 63) / 64, (rows + 3) / 4);
+    KernelSpan span(ctx, VSLAM_K_GRAD);
     grad_k<<<grid, 256, 0, ctx->stream>>>(g, rows, cols, pitch, gx, gy, mag, orient, op);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;

@@ -255,6 +255,14 @@ static int reserve_hbuf(vslam_ctx *ctx, const Geometry &g) {
     return VSLAM_OK;
 }
 
+// Per-frame staging list: producers reserve space in arbitrary block order, so the staged set must be complete for the
+// ordered gather to return the FIRST `capacity` entries.  Sized max(capacity, 1M) entries, never more than the frame can emit.
+static size_t staging_entries(int capacity, size_t frame_bound) {
+    size_t want = (size_t)capacity > ((size_t)1 << 20) ? (size_t)capacity : ((size_t)1 << 20);
+    if (want > frame_bound) want = frame_bound;
+    return want + 1;
+}
+
 static size_t detect_segments(const Geometry &g, int window, int *seg_base /*[num_octaves]*/) {
     size_t n = 0;
     for (int o = 0; o < g.num_octaves; ++o) {
@@ -283,7 +291,7 @@ static int detect_frame(vslam_ctx *ctx, const Geometry &g, u8 *block, const vsla
         a.seg_base = seg_base[o];
         a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
         a.cursor = cnt;
-        a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = capacity;
+        a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = ctx->staging_entries;
         a.stage_counts = d_stage ? d_stage + ((size_t)frame * g.num_octaves + o) * 4 : nullptr;
         VS_TRY(launch_detect(ctx, a, dp));
     }
@@ -450,7 +458,7 @@ int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_p
     }
     int seg_base[16];
     const size_t n_seg = detect_segments(g, dp.window, seg_base);
-    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint) * (size_t)(capacity + 1)));
+    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256)));
     VS_TRY(reserve_counters(ctx, pyr->n_frames));
     vslam_keypoint *d_out = out;
     if (space != VSLAM_DEVICE) {
@@ -489,7 +497,7 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
     if (ctx->ws_maps.reserve(g.frame_bytes)) VS_FAIL(ctx, VSLAM_E_NOMEM, "frame workspace (%zu bytes)", g.frame_bytes);
     int seg_base[16];
     const size_t n_seg = detect_segments(g, dp.window, seg_base);
-    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint) * (size_t)(capacity + 1)));
+    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256)));
     VS_TRY(reserve_counters(ctx, n_frames));
     vslam_keypoint *d_out = out;
     if (out_space != VSLAM_DEVICE) {
@@ -519,7 +527,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     int ntx, nty;
     harris_grid(rows, cols, &ntx, &nty);
     const size_t n_seg = (size_t)rows * ntx;
-    VS_TRY(seg_prepare(ctx, n_seg, sizeof(vslam_corner) * (size_t)(capacity + 1)));
+    VS_TRY(seg_prepare(ctx, n_seg, sizeof(vslam_corner), staging_entries(capacity, (size_t)rows * cols)));
     VS_TRY(reserve_counters(ctx, n_frames));
     vslam_corner *d_out = corners;
     if (out_space != VSLAM_DEVICE) {
@@ -543,7 +551,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         a.r8 = d_r8 ? d_r8 + px * f : nullptr;
         a.mask3 = d_m3 ? d_m3 + px * f : nullptr;
         a.seg_base = 0; a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
-        a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = capacity;
+        a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = ctx->staging_entries;
         VS_TRY(launch_harris(ctx, a));
         VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f));
     }

@@ -46,6 +46,7 @@ struct vslam_ctx {
     int sm_count = 148;
     // segment-ordered compaction workspace (detect + harris corners)
     vslam::DevBuf seg_off, seg_cnt, seg_dst, staging, counters, stage_counts;
+    int staging_entries = 0;       // capacity of `staging` in entries (per frame)
     // throughput-path workspace: one frame's pyramid, reused
     vslam::DevBuf ingest;          // aligned copy of the input frame(s)
     vslam::DevBuf taps;            // OctaveTaps[num_octaves]
@@ -154,7 +155,7 @@ int host_gauss_taps(double sigma, int n, int32_t *taps);
 int build_octave_taps(double sigma0, int scale_samples, int octave, OctaveTaps *out);
 
 // ---- segment-ordered compaction (compaction.cu) -------------------------------------------------------------
-int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t staging_bytes);
+int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t entry_bytes, size_t entries);
 // after the producer kernel: order the staged entries of n_segments segments into dst[dst_base ...];
 // d_total[0] accumulates the number written so far (device counter); entry_bytes 12 or 24.
 int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, int capacity, int *d_total,

@@ -70,7 +70,9 @@ __global__ void __launch_bounds__(256) seg_gather_k(const int *__restrict__ off,
     }
 }
 
-int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t staging_bytes) {
+int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t entry_bytes, size_t entries) {
+    const size_t staging_bytes = entry_bytes * entries;
+    ctx->staging_entries = (int)entries;
     if (ctx->seg_off.reserve(n_segments * 4) || ctx->seg_cnt.reserve(n_segments * 4) ||
         ctx->seg_dst.reserve(n_segments * 4) || ctx->staging.reserve(staging_bytes))
         VS_FAIL(ctx, VSLAM_E_NOMEM, "segment workspace allocation failed (%zu segments)", n_segments);
@@ -87,7 +89,7 @@ int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, 
     VS_LAUNCH_CHECK(ctx);
     seg_gather_k<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->seg_off.as<int>(), ctx->seg_cnt.as<int>(),
                                                            ctx->seg_dst.as<int>(), n, entry_bytes / 4,
-                                                           ctx->staging.as<u32>(), capacity, (u32 *)dst, capacity);
+                                                           ctx->staging.as<u32>(), ctx->staging_entries, (u32 *)dst, capacity);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

@@ -7,6 +7,7 @@
 #include <mutex>
 
 #include "detect.cuh"
+#include "fused.cuh"
 #include "harris.cuh"
 #include "pyramid.cuh"
 
@@ -34,7 +35,8 @@ struct vslam_pyramid {
     u8 *plane(int f, int o, int idx) const { return maps.as<u8>() + (size_t)f * frame_bytes + ooff[o] + oplane[o] * idx; }
 };
 
-static const int kCounterBase = 16;             // counters: [0] staging cursor, [2] running total, [16+f] per frame
+static const int kCounterBase = 16;
+static const int FWO_SAMPLES = kFusedWO / 3;   // sample columns per strip             // counters: [0] staging cursor, [2] running total, [16+f] per frame
 
 extern "C" {
 
@@ -85,8 +87,8 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf *bufs[] = {&ctx->seg_off, &ctx->seg_cnt, &ctx->seg_dst, &ctx->staging, &ctx->counters, &ctx->stage_counts,
-                      &ctx->ingest, &ctx->taps, &ctx->hbuf, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev};
+    DevBuf *bufs[] = {&ctx->seg_off, &ctx->seg_cnt, &ctx->seg_dst, &ctx->seg_partial, &ctx->staging, &ctx->counters, &ctx->stage_counts,
+                      &ctx->ingest, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev};
     for (DevBuf *b : bufs) b->release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
@@ -152,17 +154,16 @@ static int ensure_taps(vslam_ctx *ctx, int num_octaves, double sigma0, int scale
     if (ctx->h_taps && ctx->taps_octaves == num_octaves && ctx->taps_sigma0 == sigma0 && ctx->taps_scale_samples == scale_samples)
         return VSLAM_OK;
     free(ctx->h_taps);
-    ctx->h_taps = malloc(sizeof(OctaveTaps) * (size_t)num_octaves);
+    ctx->h_taps = malloc(sizeof(FusedTaps) * (size_t)num_octaves);
     if (!ctx->h_taps) return VSLAM_E_NOMEM;
     ctx->taps_octaves = 0;
-    OctaveTaps *h = (OctaveTaps *)ctx->h_taps;
+    FusedTaps *h = (FusedTaps *)ctx->h_taps;
     for (int o = 0; o < num_octaves; ++o) {
-        const int rc = build_octave_taps(sigma0, scale_samples, o, &h[o]);
-        if (rc) VS_FAIL(ctx, rc, "octave %d: Gaussian kernel wider than %d taps is not supported (sigma0=%g)", o, kMaxKsize, sigma0);
+        const int rc = build_fused_taps(sigma0, scale_samples, o, &h[o]);
+        if (rc) VS_FAIL(ctx, rc, "octave %d: Gaussian kernel wider than %d taps is not supported (sigma0=%g)", o, kMaxKsize - 8, sigma0);
+        if (fused_smem_bytes(h[o]) > 227 * 1024)
+            VS_FAIL(ctx, VSLAM_E_INVALID, "octave %d: the Gaussian stack needs %zu bytes of shared memory (sigma0=%g)", o, fused_smem_bytes(h[o]), sigma0);
     }
-    if (ctx->taps.reserve(sizeof(OctaveTaps) * (size_t)num_octaves)) VS_FAIL(ctx, VSLAM_E_NOMEM, "tap table allocation failed");
-    VS_CUDA(ctx, cudaMemcpyAsync(ctx->taps.p, h, sizeof(OctaveTaps) * (size_t)num_octaves, cudaMemcpyHostToDevice, ctx->stream));
-    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->taps_octaves = num_octaves; ctx->taps_sigma0 = sigma0; ctx->taps_scale_samples = scale_samples;
     return VSLAM_OK;
 }
@@ -234,24 +235,31 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
     return VSLAM_OK;
 }
 
-// rows A-D for one frame into `block` (laid out by Geometry)
-static int build_frame(vslam_ctx *ctx, const Geometry &g, const u8 *frame, int rows, int cols, size_t pitch, u8 *block) {
-    const OctaveTaps *h = (const OctaveTaps *)ctx->h_taps;
-    VS_TRY(launch_upsample2x(ctx, frame, rows, cols, pitch, block + g.ooff[0], g.opitch[0]));
-    const size_t hpitch = round_up((size_t)g.ocols[0], 128);
-    for (int o = 0; o < g.num_octaves; ++o) {
-        OctavePlanes op;
-        octave_planes(g, block, o, &op);
-        const size_t hp_o = round_up((size_t)g.ocols[o], 128);
-        (void)hpitch;
-        VS_TRY(launch_octave_blur(ctx, op, ctx->taps.as<OctaveTaps>() + o, h[o], ctx->hbuf.as<u16>(), hp_o));
+// rows A-D for n_frames frames into consecutive blocks laid out by Geometry (frame f at block + f * g.frame_bytes):
+// one batched upsample launch, then one fused launch per octave with every map materialised.
+static int build_frames(vslam_ctx *ctx, const Geometry &g, const u8 *frames, int n_frames, int rows, int cols, size_t pitch,
+                        size_t stride, u8 *block) {
+    const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
+    for (int f0 = 0; f0 < n_frames; f0 += 32768) {
+        const int nf = n_frames - f0 < 32768 ? n_frames - f0 : 32768;
+        u8 *blk = block + g.frame_bytes * (size_t)f0;
+        VS_TRY(launch_upsample2x(ctx, frames + stride * f0, rows, cols, pitch, stride, blk + g.ooff[0], g.opitch[0], g.frame_bytes, nf));
+        for (int o = 0; o < g.num_octaves; ++o) {
+            OctavePlanes op;
+            octave_planes(g, blk, o, &op);
+            FusedArgs a;
+            memset(&a, 0, sizeof a);
+            a.taps = h[o];
+            a.base = op.base; a.base_pitch = op.pitch; a.base_stride = g.frame_bytes;
+            a.rows = op.rows; a.cols = op.cols; a.octave = o;
+            a.next_base = op.next_base; a.next_pitch = op.next_pitch; a.next_stride = g.frame_bytes;
+            a.next_rows = op.next_rows; a.next_cols = op.next_cols;
+            for (int l = 0; l < 6; ++l) a.gauss[l] = op.gauss[l];
+            for (int l = 0; l < 5; ++l) a.dog[l] = op.dog[l];
+            a.map_pitch = op.pitch; a.map_stride = g.frame_bytes;
+            VS_TRY(launch_octave_fused(ctx, a, nf));
+        }
     }
-    return VSLAM_OK;
-}
-
-static int reserve_hbuf(vslam_ctx *ctx, const Geometry &g) {
-    const size_t need = round_up((size_t)g.ocols[0], 128) * (size_t)g.orows[0] * 6 * sizeof(u16);
-    if (ctx->hbuf.reserve(need)) VS_FAIL(ctx, VSLAM_E_NOMEM, "H-pass workspace (%zu bytes)", need);
     return VSLAM_OK;
 }
 
@@ -295,7 +303,7 @@ static int detect_frame(vslam_ctx *ctx, const Geometry &g, u8 *block, const vsla
         a.stage_counts = d_stage ? d_stage + ((size_t)frame * g.num_octaves + o) * 4 : nullptr;
         VS_TRY(launch_detect(ctx, a, dp));
     }
-    return seg_finalise(ctx, n_seg, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + frame);
+    return seg_finalise(ctx, n_seg, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + frame, 1);
 }
 
 static int finish_counts(vslam_ctx *ctx, int n_frames, int capacity, int *counts, long long *total_out) {
@@ -330,7 +338,6 @@ int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
     VS_TRY(ensure_taps(ctx, no, s0, 3));
     const u8 *d_frames; size_t d_pitch, d_stride;
     VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
-    VS_TRY(reserve_hbuf(ctx, g));
     vslam_pyramid *p = new (std::nothrow) vslam_pyramid();
     if (!p) return VSLAM_E_NOMEM;
     p->device = ctx->device; p->n_frames = n_frames; p->rows = rows; p->cols = cols; p->num_octaves = no;
@@ -345,8 +352,8 @@ int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
         delete p;
         VS_FAIL(ctx, VSLAM_E_NOMEM, "pyramid of %d frames needs %zu bytes", n_frames, g.frame_bytes * (size_t)n_frames);
     }
-    for (int f = 0; f < n_frames; ++f) {
-        const int rc = build_frame(ctx, g, d_frames + d_stride * f, rows, cols, d_pitch, p->maps.as<u8>() + g.frame_bytes * f);
+    {
+        const int rc = build_frames(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, p->maps.as<u8>());
         if (rc) { cudaStreamSynchronize(ctx->stream); p->maps.release(); delete p; return rc; }
     }
     *out = p;
@@ -480,6 +487,63 @@ int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_p
     return emit_list(ctx, out, space, d_out, sizeof(vslam_keypoint), total, capacity);
 }
 
+// Throughput path: batched fused pipeline.  Per chunk of frames: one upsample launch, one fused launch per octave
+// (blur + DoG + detector; only the octave bases live in HBM), then the segment scan / ordered gather.
+static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_frames, int n_frames, int rows, int cols,
+                               size_t d_pitch, size_t d_stride, const vslam_dog_params &dp, vslam_keypoint *d_out, int capacity) {
+    const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
+    // bases-only workspace layout of one frame
+    size_t boff[16], bbytes = 0;
+    for (int o = 0; o < g.num_octaves; ++o) { boff[o] = bbytes; bbytes += g.oplane[o]; }
+    // segments of one frame: (octave, level 1..3, sample row, strip)
+    int seg_base[16], ni[16], nj[16];
+    long long spf = 0;
+    for (int o = 0; o < g.num_octaves; ++o) {
+        int nc;
+        detect_grid(g.orows[o], g.ocols[o], 3, &ni[o], &nj[o], &nc);
+        seg_base[o] = (int)spf;
+        spf += 3LL * ni[o] * fused_strips(g.ocols[o]);
+    }
+    if (spf == 0) spf = 1;
+    // chunk size: workspace <= 6 GB, segment arrays <= 2^30 entries
+    long long fb = (long long)(6e9 / (double)(bbytes + spf * 12));
+    if (fb > (1LL << 30) / spf) fb = (1LL << 30) / spf;
+    if (fb > 32768) fb = 32768;
+    if (fb > n_frames) fb = n_frames;
+    if (fb < 1) fb = 1;
+    if (ctx->ws_maps.reserve(bbytes * (size_t)fb)) VS_FAIL(ctx, VSLAM_E_NOMEM, "octave-base workspace (%zu bytes)", bbytes * (size_t)fb);
+    const size_t bound = (size_t)spf * (FWO_SAMPLES) * (size_t)fb;
+    VS_TRY(seg_prepare(ctx, (size_t)spf * fb, sizeof(vslam_keypoint), staging_entries(capacity, bound)));
+    int *cnt = ctx->counters.as<int>();
+    const float rp1 = dp.edge_r + 1.0f;
+    for (int f0 = 0; f0 < n_frames; f0 += (int)fb) {
+        const int nf = n_frames - f0 < fb ? n_frames - f0 : (int)fb;
+        const size_t n_seg = (size_t)spf * nf;
+        if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, n_seg * 4, ctx->stream));
+        VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
+        u8 *ws = ctx->ws_maps.as<u8>();
+        VS_TRY(launch_upsample2x(ctx, d_frames + d_stride * f0, rows, cols, d_pitch, d_stride, ws + boff[0], g.opitch[0], bbytes, nf));
+        for (int o = 0; o < g.num_octaves; ++o) {
+            FusedArgs a;
+            memset(&a, 0, sizeof a);
+            a.taps = h[o];
+            a.base = ws + boff[o]; a.base_pitch = g.opitch[o]; a.base_stride = bbytes;
+            a.rows = g.orows[o]; a.cols = g.ocols[o]; a.octave = o;
+            if (o + 1 < g.num_octaves) {
+                a.next_base = ws + boff[o + 1]; a.next_pitch = g.opitch[o + 1]; a.next_stride = bbytes;
+                a.next_rows = g.orows[o + 1]; a.next_cols = g.ocols[o + 1];
+            }
+            a.detect = 1; a.contrast_thr = dp.contrast_thr; a.edge_thr = (rp1 * rp1) / dp.edge_r;   // Diff_of_Gauss.cpp:332-333
+            a.ni = ni[o]; a.nj = nj[o]; a.seg_base = seg_base[o]; a.segs_per_frame = (int)spf;
+            a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
+            a.cursor = cnt; a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = ctx->staging_entries;
+            VS_TRY(launch_octave_fused(ctx, a, nf));
+        }
+        VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf));
+    }
+    return VSLAM_OK;
+}
+
 int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
                         size_t frame_stride, int space, const vslam_pyramid_params *pparams,
                         const vslam_dog_params *dparams, vslam_keypoint *out, int capacity, int out_space, int *counts) {
@@ -493,20 +557,24 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
     VS_TRY(ensure_taps(ctx, no, s0, 3));
     const u8 *d_frames; size_t d_pitch, d_stride;
     VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
-    VS_TRY(reserve_hbuf(ctx, g));
-    if (ctx->ws_maps.reserve(g.frame_bytes)) VS_FAIL(ctx, VSLAM_E_NOMEM, "frame workspace (%zu bytes)", g.frame_bytes);
-    int seg_base[16];
-    const size_t n_seg = detect_segments(g, dp.window, seg_base);
-    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256)));
     VS_TRY(reserve_counters(ctx, n_frames));
     vslam_keypoint *d_out = out;
     if (out_space != VSLAM_DEVICE) {
         if (ctx->out_dev.reserve(sizeof(vslam_keypoint) * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device keypoint list");
         d_out = ctx->out_dev.as<vslam_keypoint>();
     }
-    for (int f = 0; f < n_frames; ++f) {
-        VS_TRY(build_frame(ctx, g, d_frames + d_stride * f, rows, cols, d_pitch, ctx->ws_maps.as<u8>()));
-        VS_TRY(detect_frame(ctx, g, ctx->ws_maps.as<u8>(), dp, seg_base, n_seg, d_out, capacity, f, nullptr));
+    if (dp.window == 3) {
+        VS_TRY(dog_keypoints_fused(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, dp, d_out, capacity));
+    } else {
+        // other grid strides: materialise one frame at a time and run the stand-alone detector (detect.cu)
+        if (ctx->ws_maps.reserve(g.frame_bytes)) VS_FAIL(ctx, VSLAM_E_NOMEM, "frame workspace (%zu bytes)", g.frame_bytes);
+        int seg_base[16];
+        const size_t n_seg = detect_segments(g, dp.window, seg_base);
+        VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256)));
+        for (int f = 0; f < n_frames; ++f) {
+            VS_TRY(build_frames(ctx, g, d_frames + d_stride * f, 1, rows, cols, d_pitch, d_stride, ctx->ws_maps.as<u8>()));
+            VS_TRY(detect_frame(ctx, g, ctx->ws_maps.as<u8>(), dp, seg_base, n_seg, d_out, capacity, f, nullptr));
+        }
     }
     long long total = 0;
     VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
@@ -553,7 +621,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         a.seg_base = 0; a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
         a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = ctx->staging_entries;
         VS_TRY(launch_harris(ctx, a));
-        VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f));
+        VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f, 1));
     }
     if (out_space != VSLAM_DEVICE) {
         if (response) VS_CUDA(ctx, cudaMemcpyAsync(response, d_resp, px * 4 * n_frames, cudaMemcpyDeviceToHost, ctx->stream));

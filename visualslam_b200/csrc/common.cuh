@@ -45,20 +45,18 @@ struct vslam_ctx {
     long long launches = 0;
     int sm_count = 148;
     // segment-ordered compaction workspace (detect + harris corners)
-    vslam::DevBuf seg_off, seg_cnt, seg_dst, staging, counters, stage_counts;
+    vslam::DevBuf seg_off, seg_cnt, seg_dst, seg_partial, staging, counters, stage_counts;
     int staging_entries = 0;       // capacity of `staging` in entries (per frame)
     // throughput-path workspace: one frame's pyramid, reused
     vslam::DevBuf ingest;          // aligned copy of the input frame(s)
-    vslam::DevBuf taps;            // OctaveTaps[num_octaves]
-    vslam::DevBuf hbuf;            // 6 x u16 H-pass planes of the largest octave
-    vslam::DevBuf ws_maps;         // base/gauss/dog planes of one frame
+    vslam::DevBuf ws_maps;         // octave bases of a chunk of frames (or all planes of one frame)
     vslam::DevBuf out_dev;         // device output list when the caller's list is on the host
     vslam::DevBuf maps_dev;        // device response/r8/mask when the caller's maps are on the host
     void *pinned = nullptr;        // small pinned host scratch for counters
     size_t pinned_cap = 0;
-    // cached tap tables (host copy mirrors the device copy in `taps`)
+    // cached tap tables of the fused octave kernel (passed by value as kernel parameters)
     int taps_octaves = 0; double taps_sigma0 = 0; int taps_scale_samples = 0;
-    void *h_taps = nullptr;        // OctaveTaps[taps_octaves], malloc'd
+    void *h_taps = nullptr;        // FusedTaps[taps_octaves], malloc'd
     // optional per-kernel CUDA-event timing (vslam_profile): events bracket every launch on ctx->stream
     bool profiling = false;
     std::vector<cudaEvent_t> ev_pool;
@@ -133,32 +131,17 @@ __host__ __device__ __forceinline__ int refl101(int p, int len) {
 __host__ __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// ---- fixed-point Gaussian taps prepared for the two blur kernels -------------------------------------------
+// ---- fixed-point Gaussian taps (taps.cu) ---------------------------------------------------------------------
 constexpr int kMaxKsize = 255;              // radius <= 127
-constexpr int kHWords = 68;                 // ceil((255+3)/4)=65 -> padded to a multiple of 4
-constexpr int kVPairs = 128;                // r+1 <= 128, padded to a multiple of 8
-struct LevelTaps {
-    int n, r;
-    int delta, wofs;                        // H pass: leading zero taps / first staged word (see pyramid.cu)
-    int kq;                                 // H pass: tap words, multiple of 4
-    int jp;                                 // V pass: tap pairs, multiple of 8
-    u32 hq[kHWords];                        // 4 byte taps per word
-    u32 eo[kVPairs];                        // E pair | O pair << 16
-};
-struct OctaveTaps {
-    LevelTaps lv[6];
-    int rmax, hp;                           // max radius, halo in pixels (multiple of 4)
-};
-
 int host_gauss_ksize(double sigma);
 int host_gauss_taps(double sigma, int n, int32_t *taps);
-int build_octave_taps(double sigma0, int scale_samples, int octave, OctaveTaps *out);
 
 // ---- segment-ordered compaction (compaction.cu) -------------------------------------------------------------
 int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t entry_bytes, size_t entries);
 // after the producer kernel: order the staged entries of n_segments segments into dst[dst_base ...];
 // d_total[0] accumulates the number written so far (device counter); entry_bytes 12 or 24.
+// n_segments = n_frames * segments per frame; d_frame_count (n_frames ints) receives the per-frame counts.
 int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, int capacity, int *d_total,
-                 int *d_frame_count);
+                 int *d_frame_count, int n_frames);
 
 }  // namespace vslam

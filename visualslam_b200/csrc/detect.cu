@@ -8,49 +8,9 @@
 // j order with ballots, one atomicAdd per block reserves staging space, compaction.cu orders the segments.
 // Every float/double operation below uses the round-to-nearest intrinsics so that nvcc cannot contract to FMA.
 #include "detect.cuh"
+#include "detect_math.cuh"
 
 namespace vslam {
-
-// FeaturePointLocalization's value: dog_zhat = value/255 + 0.5 * A^T * (-(A A^T)^-1) * A   (row H)
-__device__ float localize(int dx, int dy, int ds, int value) {
-    const float v = __fdiv_rn((float)value, 255.0f);
-    // any zero derivative -> a zero row and column in B -> det3 == 0 exactly -> cv::invert yields zeros
-    if (dx == 0 || dy == 0 || ds == 0) return v;
-    const float a0 = __fdiv_rn((float)dx, 255.0f), a1 = __fdiv_rn((float)dy, 255.0f), a2 = __fdiv_rn((float)ds, 255.0f);
-    const double A0 = (double)a0, A1 = (double)a1, A2 = (double)a2;
-    // B = A * A^T through gemm's generic path: double product, stored as float
-    const double b00 = (double)__double2float_rn(__dmul_rn(A0, A0)), b01 = (double)__double2float_rn(__dmul_rn(A0, A1)),
-                 b02 = (double)__double2float_rn(__dmul_rn(A0, A2)), b11 = (double)__double2float_rn(__dmul_rn(A1, A1)),
-                 b12 = (double)__double2float_rn(__dmul_rn(A1, A2)), b22 = (double)__double2float_rn(__dmul_rn(A2, A2));
-    const double b10 = b01, b20 = b02, b21 = b12;
-#define MUL(a, b) __dmul_rn(a, b)
-#define SUB(a, b) __dsub_rn(a, b)
-    // det3, left to right (OpenCV lapack.cpp)
-    double d = __dadd_rn(SUB(MUL(b00, SUB(MUL(b11, b22), MUL(b12, b21))), MUL(b01, SUB(MUL(b10, b22), MUL(b12, b20)))),
-                         MUL(b02, SUB(MUL(b10, b21), MUL(b11, b20))));
-    if (d == 0.0) return v;
-    d = __ddiv_rn(1.0, d);
-    // M = -(B^-1), entries rounded to float (negation is exact)
-    const float m0 = -__double2float_rn(MUL(SUB(MUL(b11, b22), MUL(b12, b21)), d));
-    const float m1 = -__double2float_rn(MUL(SUB(MUL(b02, b21), MUL(b01, b22)), d));
-    const float m2 = -__double2float_rn(MUL(SUB(MUL(b01, b12), MUL(b02, b11)), d));
-    const float m3 = -__double2float_rn(MUL(SUB(MUL(b12, b20), MUL(b10, b22)), d));
-    const float m4 = -__double2float_rn(MUL(SUB(MUL(b00, b22), MUL(b02, b20)), d));
-    const float m5 = -__double2float_rn(MUL(SUB(MUL(b02, b10), MUL(b00, b12)), d));
-    const float m6 = -__double2float_rn(MUL(SUB(MUL(b10, b21), MUL(b11, b20)), d));
-    const float m7 = -__double2float_rn(MUL(SUB(MUL(b01, b20), MUL(b00, b21)), d));
-    const float m8 = -__double2float_rn(MUL(SUB(MUL(b00, b11), MUL(b01, b10)), d));
-#undef MUL
-#undef SUB
-    // z = M * A through gemm's small-matrix path: float accumulate
-    const float z0 = __fadd_rn(__fadd_rn(__fmul_rn(m0, a0), __fmul_rn(m1, a1)), __fmul_rn(m2, a2));
-    const float z1 = __fadd_rn(__fadd_rn(__fmul_rn(m3, a0), __fmul_rn(m4, a1)), __fmul_rn(m5, a2));
-    const float z2 = __fadd_rn(__fadd_rn(__fmul_rn(m6, a0), __fmul_rn(m7, a1)), __fmul_rn(m8, a2));
-    // 0.5 * A^T * z through gemm's generic path: double accumulate, alpha = 0.5
-    const double acc = __dadd_rn(__dadd_rn(__dmul_rn(A0, (double)z0), __dmul_rn(A1, (double)z1)), __dmul_rn(A2, (double)z2));
-    const float q = __double2float_rn(__dmul_rn(0.5, acc));
-    return __fadd_rn(v, q);
-}
 
 // computeEdgeResponse on the gradients of Gaussian level g (Sobel ksize=1 of row E formed on the fly)
 __device__ float edge_response(const u8 *__restrict__ g, int rows, int cols, size_t pitch, int y, int x, int pad) {

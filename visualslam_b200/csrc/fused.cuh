@@ -1,0 +1,66 @@
+// fused.cuh -- arguments of the fused octave kernel (fused.cu): rows B, C, D, G, H, I, J of SURVEY.md 8(a) in one pass.
+#pragma once
+#include "common.cuh"
+
+namespace vslam {
+
+constexpr int kFusedHWords = 64;    // ceil(245 / 4) = 62, padded to a multiple of 2 (+ slack)
+constexpr int kFusedVPairs = 128;   // r + 1 <= 123, padded to a multiple of 2 (+ slack)
+
+// One Gaussian level, packed for the two passes of octave_fused_k.
+struct FusedLevel {
+    int n, r;
+    int nw;                         // H pass: tap words (4 byte taps each), padded to a multiple of 2
+    int jp;                         // V pass: tap pairs, padded to a multiple of 2
+    int hoff;                       // word offset of this level's h buffer inside the CTA's shared memory
+    int np;                         // pairs of 8.8 rows the buffer holds: r + R/2
+    u32 hq[kFusedHWords];           // taps t[4w .. 4w+3], zero padded
+    u32 eo[kFusedVPairs];           // (t[2j], t[2j+1]) | (t[2j-1], t[2j]) << 16
+};
+
+struct FusedTaps {
+    FusedLevel lv[6];
+    int rmin, rmax, rpad;           // rpad >= rmax, rpad == 2 (mod 4): left halo of the staged base rows
+    int stage_rows, stage_pitch;    // staged base tile: rows, bytes between rows (multiple of 4)
+    int hbuf_words;                 // total words of the six h buffers (+ one spare pair row)
+};
+
+// Launch description.  All planes of one octave share `pitch`; frame f's plane is at ptr + f * frame_stride.
+struct FusedArgs {
+    FusedTaps taps;
+    const u8 *base;                 // octave input
+    size_t base_pitch, base_stride;
+    int rows, cols, octave;
+    int n_strips, n_segs, seg_rows; // grid = (strips, vertical segments, frames); seg_rows is a multiple of R
+    // next octave's base: level 3 decimated by two (GaussPyramid.cpp:123-126), or nullptr
+    u8 *next_base;
+    size_t next_pitch, next_stride;
+    int next_rows, next_cols;
+    // optional materialised planes (GaussPyramid::octaveBlur / octaveDiff), or nullptr
+    u8 *gauss[6];
+    u8 *dog[5];
+    size_t map_pitch, map_stride;
+    // keypoint detection (window 3 only), or detect == 0
+    int detect;
+    float contrast_thr, edge_thr;
+    int ni, nj;                     // sample rows / columns of this octave
+    int seg_base;                   // first segment of this octave inside a frame's segment block
+    int segs_per_frame;
+    int *seg_off, *seg_cnt;
+    int *cursor;                    // staging cursor (one per launch batch)
+    vslam_keypoint *staging;
+    int staging_cap;
+};
+
+// geometry shared by host and device
+constexpr int kFusedW = 64;         // columns a CTA computes
+constexpr int kFusedWO = 60;        // columns a CTA owns (2 halo columns each side; 60 = 20 sample columns of stride 3)
+constexpr int kFusedR = 32;         // rows per marching step
+
+int build_fused_taps(double sigma0, int scale_samples, int octave, FusedTaps *out);
+size_t fused_smem_bytes(const FusedTaps &t);
+int fused_strips(int cols);
+// Launch one octave for n_frames frames.  The kernel is chosen by the shared-memory footprint of the octave.
+int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames);
+
+}  // namespace vslam

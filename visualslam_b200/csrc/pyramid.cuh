@@ -25,11 +25,9 @@ inline void half_size(int r, int c, int *orows, int *ocols) {
 }
 
 // row A
-int launch_upsample2x(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t src_pitch, u8 *dst, size_t dst_pitch);
-// rows B, C, D for one octave: 6 blurs from the octave base + 5 saturating differences + decimated level 3.
-// hbuf: 6 planes of u16, each hpitch elements x rows.
-int launch_octave_blur(vslam_ctx *ctx, const OctavePlanes &op, const OctaveTaps *d_taps, const OctaveTaps &h_taps,
-                       u16 *hbuf, size_t hpitch);
+// n_frames frames per launch: frame f at src + f * src_stride -> dst + f * dst_stride
+int launch_upsample2x(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t src_pitch, size_t src_stride, u8 *dst,
+                      size_t dst_pitch, size_t dst_stride, int n_frames);
 // row E on demand: any output may be null.
 int launch_gradients(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pitch, float *gx, float *gy, float *mag,
                      float *orient, size_t out_pitch_elems);

@@ -161,7 +161,7 @@ static int ensure_taps(vslam_ctx *ctx, int num_octaves, double sigma0, int scale
     for (int o = 0; o < num_octaves; ++o) {
         const int rc = build_fused_taps(sigma0, scale_samples, o, &h[o]);
         if (rc) VS_FAIL(ctx, rc, "octave %d: Gaussian kernel wider than %d taps is not supported (sigma0=%g)", o, kMaxKsize - 8, sigma0);
-        if (fused_smem_bytes(h[o]) > 227 * 1024)
+        if (fused_smem_bytes(h[o]) > 223 * 1024)
             VS_FAIL(ctx, VSLAM_E_INVALID, "octave %d: the Gaussian stack needs %zu bytes of shared memory (sigma0=%g)", o, fused_smem_bytes(h[o]), sigma0);
     }
     ctx->taps_octaves = num_octaves; ctx->taps_sigma0 = sigma0; ctx->taps_scale_samples = scale_samples;
@@ -516,6 +516,16 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
     VS_TRY(seg_prepare(ctx, (size_t)spf * fb, sizeof(vslam_keypoint), staging_entries(capacity, bound)));
     int *cnt = ctx->counters.as<int>();
     const float rp1 = dp.edge_r + 1.0f;
+    // FeaturePointLocalization with a singular A*A^T (any zero derivative): dog_zhat = float(value)/255f, kept iff
+    // > contrast_thr, new value (int)(dog_zhat*255f) -- tabulated with the same IEEE float ops (Diff_of_Gauss.cpp:243-246)
+    int cmin = 256;
+    u8 val_lut[256];
+    for (int c = 255; c >= 0; --c) {
+        volatile float v = (float)c / 255.0f;
+        volatile float w = v * 255.0f;
+        val_lut[c] = (u8)(int)w;
+        if (v > dp.contrast_thr) cmin = c;
+    }
     for (int f0 = 0; f0 < n_frames; f0 += (int)fb) {
         const int nf = n_frames - f0 < fb ? n_frames - f0 : (int)fb;
         const size_t n_seg = (size_t)spf * nf;
@@ -533,7 +543,7 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
                 a.next_base = ws + boff[o + 1]; a.next_pitch = g.opitch[o + 1]; a.next_stride = bbytes;
                 a.next_rows = g.orows[o + 1]; a.next_cols = g.ocols[o + 1];
             }
-            a.detect = 1; a.contrast_thr = dp.contrast_thr; a.edge_thr = (rp1 * rp1) / dp.edge_r;   // Diff_of_Gauss.cpp:332-333
+            a.detect = 1; a.cmin = cmin; memcpy(a.val_lut, val_lut, 256); a.contrast_thr = dp.contrast_thr; a.edge_thr = (rp1 * rp1) / dp.edge_r;   // Diff_of_Gauss.cpp:332-333
             a.ni = ni[o]; a.nj = nj[o]; a.seg_base = seg_base[o]; a.segs_per_frame = (int)spf;
             a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
             a.cursor = cnt; a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = ctx->staging_entries;

@@ -82,7 +82,7 @@ int build_fused_taps(double sigma0, int scale_samples, int octave, FusedTaps *ou
 }
 
 size_t fused_smem_bytes(const FusedTaps &t) {
-    return (size_t)t.hbuf_words * 4 + (size_t)t.stage_rows * t.stage_pitch + (size_t)(F_NG + F_ND) * FW * FTR;
+    return (size_t)t.hbuf_words * 4 + (size_t)t.stage_rows * t.stage_pitch + (size_t)(F_NG + F_ND) * FW * FTR;   // + 2880 static
 }
 
 int fused_strips(int cols) { return (cols + FWO - 1) / FWO; }
@@ -168,6 +168,7 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
     u8 *tiles = stage + T.stage_rows * SP;
     u32 *tiles32 = (u32 *)tiles;
     u8 *gt = tiles, *dt = tiles + F_NG * FW * FTR;
+    __shared__ int s_res[3 * (FR / 3 + 2) * (FWO / 3)];   // detector results of one step
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int strip = blockIdx.x, seg = blockIdx.y, frame = blockIdx.z;
@@ -179,25 +180,31 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
     const int yv = seg > 0 ? ys - FR : 0;       // first step with a V pass (one extra step feeds the detector's history)
     const int K = (2 * T.rmax + FR - 1) / FR;   // warm-up steps: H pass only
 
-    for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
-        const bool do_v = y0 >= yv;
-        // ---- 1. stage base rows y0 + rmin ..., columns xs ..., reflect-101 resolved -------------------------
+    // stage base rows y0 + rmin ..., columns xs ..., reflect-101 resolved.  Interior words go through cp.async so the
+    // copy of step c+1 overlaps the V pass and the detector of step c; border words are gathered byte by byte.
+    auto issue_stage = [&](int y0n) {
         for (int row = warp; row < T.stage_rows; row += NW) {
-            const int y = refl101(y0 + T.rmin + row, rows);
+            const int y = refl101(y0n + T.rmin + row, rows);
             const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
             u32 *dst = (u32 *)(stage + row * SP);
             for (int w = lane; w < SPW; w += 32) {
                 const int x = xs + 4 * w;
-                u32 v;
                 if (x >= 0 && x + 3 < cols) {
-                    v = *(const u32 *)(src + x);
+                    const u32 sa = (u32)__cvta_generic_to_shared(dst + w);
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src + x) : "memory");
                 } else {
-                    v = (u32)src[refl101(x, cols)] | (u32)src[refl101(x + 1, cols)] << 8 |
-                        (u32)src[refl101(x + 2, cols)] << 16 | (u32)src[refl101(x + 3, cols)] << 24;
+                    dst[w] = (u32)src[refl101(x, cols)] | (u32)src[refl101(x + 1, cols)] << 8 |
+                             (u32)src[refl101(x + 2, cols)] << 16 | (u32)src[refl101(x + 3, cols)] << 24;
                 }
-                dst[w] = v;
             }
         }
+    };
+    issue_stage(yv - K * FR);
+
+    for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
+        const bool do_v = y0 >= yv;
+        // ---- 1. the staged rows of this step have landed ------------------------------------------------------
+        asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();
         // ---- 2. H pass: rows y0 + r_l .. y0 + r_l + 31 of every level -> pairs r_l .. r_l + 15 ----------------
         for (int t = tid; t < 6 * 64; t += NT) {
@@ -227,6 +234,7 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
             }
         }
         __syncthreads();
+        if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
         // ---- 3. V pass + rounding + DoG -> tiles (column-major: tile k, column x, rows contiguous) -------------
         if (do_v) {
             const int x = tid & (FW - 1), rg = tid / FW;
@@ -278,75 +286,69 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
             }
         }
         __syncthreads();
-        // ---- 4a. detector: one warp per (level, sample row); lanes = the strip's 20 sample columns ------------
+        // ---- 4a. detector, test: every thread takes samples of the flattened (sample row, level, column) list ------
+        // Result per sample in s_res: the keypoint's value, or -1.  Emission (ordered, per segment) follows in step 5.
         const bool own_step = do_v && y0 >= ys;
+        int si_lo = 0, n_srow = 0;
         if (own_step && a.detect) {
             const int yc_lo = y0 == 0 ? 0 : y0 - 2;
             const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;   // centre row yc needs rows up to yc + 2
-            const int si_lo = (yc_lo + 2) / 3, si_hi = yc_hi >= 0 ? yc_hi / 3 : -1;
-            const int ntask = 3 * (si_hi - si_lo + 1);
-#define DT(k, x, y) ((int)dt[((k)*FW + ((x)-X0c)) * FTR + ((y)-y0 + 4)])
-#define GT(k, x, y) ((int)gt[((k)*FW + ((x)-X0c)) * FTR + ((y)-y0 + 4)])
-            for (int task = warp; task < ntask; task += NW) {
-                const int level = 1 + task % 3, si = si_lo + task / 3;
-                const int yc = 3 * si, xc = X0 + 3 * lane;
-                bool pass = false;
-                int value = 0;
-                if (lane < FWO / 3 && xc <= cols - 2) {
-                    const int ym = max(yc - 1, 0), xm = max(xc - 1, 0);
-                    const int c = DT(level, xc, yc);
-                    int mn = c, mx = c;
-#pragma unroll
-                    for (int k = -1; k <= 1; ++k) {
-                        const int t0 = DT(level + k, xm, ym), t1 = DT(level + k, xc, ym), t2 = DT(level + k, xm, yc),
-                                  t3 = DT(level + k, xc, yc);
-                        mn = min(min(mn, min(t0, t1)), min(t2, t3));
-                        mx = max(max(mx, max(t0, t1)), max(t2, t3));
-                    }
+            si_lo = (yc_lo + 2) / 3;
+            n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
+            if (n_srow < 0) n_srow = 0;
+            constexpr int NS = FWO / 3;                                       // 20 sample columns per strip
+            const int total = n_srow * 3 * NS;
+            for (int s = tid; s < total; s += NT) {
+                const int k = s % NS, t = s / NS;
+                const int level = 1 + t % 3, sr = t / 3;
+                const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
+                int res = -1;
+                if (xc <= cols - 2) {
+                    // D tile of DoG `level` at (xc, yc); neighbours at constant strides, clamped at the image border
+                    const u8 *p = dt + (level * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
+                    const int oxm = xc > 0 ? -FTR : 0, oym = yc > 0 ? -1 : 0;
+                    const int oxp = xc + 1 < cols ? FTR : 0, oyp = yc + 1 < rows ? 1 : 0;
+                    constexpr int LS = FW * FTR;
+                    const int c = p[0];
+                    const int a0 = p[oxm + oym], a1 = p[oym], a2 = p[oxm];                    // level
+                    const int b0 = p[-LS + oxm + oym], b1 = p[-LS + oym], b2 = p[-LS + oxm], b3 = p[-LS];   // level - 1
+                    const int c0 = p[LS + oxm + oym], c1 = p[LS + oym], c2 = p[LS + oxm], c3 = p[LS];       // level + 1
+                    const int mn = min(min(min(a0, a1), min(a2, c)), min(min(min(b0, b1), min(b2, b3)), min(min(c0, c1), min(c2, c3))));
+                    const int mx = max(max(max(a0, a1), max(a2, c)), max(max(max(b0, b1), max(b2, b3)), max(max(c0, c1), max(c2, c3))));
                     if (c == mn || c == mx) {                                            // Diff_of_Gauss.cpp:287
-                        const int dx = DT(level, xm, yc) - DT(level, min(xc + 1, cols - 1), yc);
-                        const int dy = DT(level, xc, ym) - DT(level, xc, min(yc + 1, rows - 1));
-                        const int ds = DT(level - 1, xc, yc) - DT(level + 1, xc, yc);
-                        const float zhat = localize(dx, dy, ds, c);
-                        if (zhat > a.contrast_thr) {                                     // :245
+                        const int dx = a2 - (int)p[oxp], dy = a1 - (int)p[oyp], ds = b3 - c3;   // :226-228
+                        bool pass_c;
+                        int value;
+                        if (dx == 0 || dy == 0 || ds == 0) {
+                            // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the host
+                            // with the same float ops: a.cmin, a.val_lut)
+                            pass_c = c >= a.cmin;
+                            value = a.val_lut[c];
+                        } else {
+                            const float zhat = localize(dx, dy, ds, c);
+                            pass_c = zhat > a.contrast_thr;                              // :245
                             value = (int)__fmul_rn(zhat, 255.0f);                        // :246
+                        }
+                        if (pass_c) {
+                            const u8 *g = gt + ((level - 1) * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
                             int ix2 = 0, iy2 = 0, ixy = 0;
 #pragma unroll
-                            for (int u = yc; u <= yc + 1; ++u)
+                            for (int u = 0; u <= 1; ++u)
 #pragma unroll
-                                for (int v = xc; v <= xc + 1; ++v) {
-                                    const int gxv = GT(level - 1, refl101(v + 1, cols), u) - GT(level - 1, refl101(v - 1, cols), u);
-                                    const int gyv = GT(level - 1, v, refl101(u + 1, rows)) - GT(level - 1, v, refl101(u - 1, rows));
+                                for (int v = 0; v <= 1; ++v) {
+                                    const int yy = yc + u, xx = xc + v;
+                                    const int xr = refl101(xx + 1, cols) - xc, xl = refl101(xx - 1, cols) - xc;
+                                    const int yd = refl101(yy + 1, rows) - yc, yu = refl101(yy - 1, rows) - yc;
+                                    const int gxv = (int)g[xr * FTR + u] - (int)g[xl * FTR + u];
+                                    const int gyv = (int)g[v * FTR + yd] - (int)g[v * FTR + yu];
                                     ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
                                 }
-                            pass = edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // :336
+                            if (edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr) res = value;   // :336
                         }
                     }
                 }
-                const unsigned bal = __ballot_sync(0xffffffffu, pass);
-                if (bal) {
-                    const int cnt = __popc(bal);
-                    const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
-                    int off = 0;
-                    if (lane == 0) {
-                        off = atomicAdd(a.cursor, cnt);
-                        a.seg_off[sg] = off;
-                        a.seg_cnt[sg] = cnt;
-                    }
-                    off = __shfl_sync(0xffffffffu, off, 0);
-                    if (pass) {
-                        const int pos = off + __popc(bal & ((1u << lane) - 1u));
-                        if (pos < a.staging_cap) {
-                            vslam_keypoint kp;
-                            kp.row = yc + 1; kp.col = xc + 1; kp.value = value; kp.padding = 1; kp.octave = a.octave;
-                            kp.level = level;
-                            a.staging[pos] = kp;
-                        }
-                    }
-                }
+                s_res[s] = res;
             }
-#undef DT
-#undef GT
         }
         // ---- 4b. next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126) ------------------
         if (own_step && a.next_base) {
@@ -376,9 +378,35 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
             }
         }
         __syncthreads();
-        // ---- 5. tiles: the last 4 rows become the next step's history --------------------------------------------
+        // ---- 5. tiles: the last 4 rows become the next step's history; ordered emission of the step's keypoints ----
         if (do_v)
             for (int t = tid; t < (F_NG + F_ND) * FW; t += NT) tiles32[t * FTW] = tiles32[t * FTW + FTW - 1];
+        for (int task = warp; task < 3 * n_srow; task += NW) {       // one warp per segment (level, sample row, strip)
+            constexpr int NS = FWO / 3;
+            const int res = lane < NS ? s_res[task * NS + lane] : -1;
+            const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
+            if (bal) {
+                const int level = 1 + task % 3, si = si_lo + task / 3;
+                const int cnt = __popc(bal);
+                const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
+                int off = 0;
+                if (lane == 0) {
+                    off = atomicAdd(a.cursor, cnt);
+                    a.seg_off[sg] = off;
+                    a.seg_cnt[sg] = cnt;
+                }
+                off = __shfl_sync(0xffffffffu, off, 0);
+                if (res >= 0) {
+                    const int pos = off + __popc(bal & ((1u << lane) - 1u));
+                    if (pos < a.staging_cap) {
+                        vslam_keypoint kp;
+                        kp.row = 3 * si + 1; kp.col = X0 + 3 * lane + 1; kp.value = res; kp.padding = 1; kp.octave = a.octave;
+                        kp.level = level;
+                        a.staging[pos] = kp;
+                    }
+                }
+            }
+        }
     }
 }
 
@@ -390,7 +418,7 @@ int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames) {
     if ((a.base_pitch & 3) || ((uintptr_t)a.base & 3) || (a.base_stride & 3))
         VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: base plane must be 4-byte aligned (pitch %zu)", a.base_pitch);
     const size_t sm = fused_smem_bytes(a.taps);
-    if (sm > 227 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave %d needs %zu bytes of shared memory", a.octave, sm);
+    if (sm > 223 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave %d needs %zu bytes of shared memory", a.octave, sm);
     a.n_strips = fused_strips(a.cols);
     // vertical split only when the batch alone cannot fill the machine: every extra segment repeats the H-pass
     // warm-up and one V step
@@ -406,8 +434,11 @@ int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames) {
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
     static bool attr_done = false;
     if (!attr_done) {
-        VS_CUDA(ctx, cudaFuncSetAttribute(octave_fused_k<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        VS_CUDA(ctx, cudaFuncSetAttribute(octave_fused_k<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        cudaFuncAttributes fa;
+        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_fused_k<128>));
+        VS_CUDA(ctx, cudaFuncSetAttribute(octave_fused_k<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes));
+        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_fused_k<256>));
+        VS_CUDA(ctx, cudaFuncSetAttribute(octave_fused_k<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes));
         attr_done = true;
     }
     KernelSpan span(ctx, VSLAM_K_FUSED);

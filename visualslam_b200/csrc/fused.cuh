@@ -43,6 +43,8 @@ struct FusedArgs {
     // keypoint detection (window 3 only), or detect == 0
     int detect;
     float contrast_thr, edge_thr;
+    int cmin;                       // zero-derivative contrast test: value/255 > contrast_thr  <=>  value >= cmin
+    u8 val_lut[256];                // (int)((value/255f) * 255f), Diff_of_Gauss.cpp:246, for the same case
     int ni, nj;                     // sample rows / columns of this octave
     int seg_base;                   // first segment of this octave inside a frame's segment block
     int segs_per_frame;

@@ -14,5 +14,5 @@ for r in rows:
     except ValueError: pass
 ti = sum(o[3] for o in out); ts = sum(o[4] for o in out)
 print(f"total warp-instr {ti}  samples {ts}")
-for f, ln, src, n, s in sorted(out, key=lambda o: -o[4])[:N]:
+for f, ln, src, n, s in sorted(out, key=lambda o: -o[3])[:N]:
     print(f"{f}:{ln:4d} inst {n/ti:6.3f} samp {s/ts:6.3f} | {src}")

@@ -6,11 +6,8 @@
 namespace vslam {
 
 // FeaturePointLocalization's value: dog_zhat = value/255 + 0.5 * A^T * (-(A A^T)^-1) * A   (row H)
-static __device__ __noinline__ float localize(int dx, int dy, int ds, int value) {
-    const float v = __fdiv_rn((float)value, 255.0f);
-    // any zero derivative -> a zero row and column in B -> det3 == 0 exactly -> cv::invert yields zeros
-    if (dx == 0 || dy == 0 || ds == 0) return v;
-    const float a0 = __fdiv_rn((float)dx, 255.0f), a1 = __fdiv_rn((float)dy, 255.0f), a2 = __fdiv_rn((float)ds, 255.0f);
+// a0, a1, a2 = float(dx)/255f, float(dy)/255f, float(ds)/255f (all non-zero), v = float(value)/255f
+static __device__ __noinline__ float localize_f(float a0, float a1, float a2, float v) {
     const double A0 = (double)a0, A1 = (double)a1, A2 = (double)a2;
     // B = A * A^T through gemm's generic path: double product, stored as float
     const double b00 = (double)__double2float_rn(__dmul_rn(A0, A0)), b01 = (double)__double2float_rn(__dmul_rn(A0, A1)),
@@ -44,6 +41,13 @@ static __device__ __noinline__ float localize(int dx, int dy, int ds, int value)
     const double acc = __dadd_rn(__dadd_rn(__dmul_rn(A0, (double)z0), __dmul_rn(A1, (double)z1)), __dmul_rn(A2, (double)z2));
     const float q = __double2float_rn(__dmul_rn(0.5, acc));
     return __fadd_rn(v, q);
+}
+
+static __device__ __forceinline__ float localize(int dx, int dy, int ds, int value) {
+    const float v = __fdiv_rn((float)value, 255.0f);
+    // any zero derivative -> a zero row and column in B -> det3 == 0 exactly -> cv::invert yields zeros
+    if (dx == 0 || dy == 0 || ds == 0) return v;
+    return localize_f(__fdiv_rn((float)dx, 255.0f), __fdiv_rn((float)dy, 255.0f), __fdiv_rn((float)ds, 255.0f), v);
 }
 
 

@@ -77,7 +77,14 @@ int build_fused_taps(double sigma0, int scale_samples, int octave, FusedTaps *ou
     }
     const int wmin = (FW + 2 * rpad + 3) / 4 + 1;
     if (need < wmin) need = wmin;
-    out->stage_pitch = need * 4;
+    need += 3;                                                       // the 16-byte alignment shift of the origin
+    out->stage_pitch = (need * 4 + 15) & ~15;
+    {   // row = (q * magic) >> 20 for q < stage_rows * (pitch / 16): checked exhaustively
+        const int spq = out->stage_pitch >> 4, nq = out->stage_rows * spq;
+        out->spq_magic = ((1 << 20) + spq - 1) / spq;
+        for (int q = 0; q < nq; ++q)
+            if ((int)(((unsigned)q * (unsigned)out->spq_magic) >> 20) != q / spq) return VSLAM_E_INVALID;
+    }
     return VSLAM_OK;
 }
 
@@ -164,42 +171,53 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
     const FusedTaps &T = a.taps;
     u32 *hbuf = smem;
     u8 *stage = (u8 *)(smem + T.hbuf_words);
-    const int SP = T.stage_pitch, SPW = SP >> 2;
+    const int SP = T.stage_pitch, SPW = SP >> 2;   // SP is a multiple of 16
     u8 *tiles = stage + T.stage_rows * SP;
     u32 *tiles32 = (u32 *)tiles;
     u8 *gt = tiles, *dt = tiles + F_NG * FW * FTR;
-    __shared__ int s_res[3 * (FR / 3 + 2) * (FWO / 3)];   // detector results of one step
+    __shared__ int s_res[3 * (FR / 3 + 2) * (FWO / 3)];              // detector results of one step
+    __shared__ unsigned short s_queue[3 * (FR / 3 + 2) * (FWO / 3)];  // samples that need the full localisation
+    __shared__ int s_nq;
+    __shared__ float s_div[511];                                      // float(i - 255) / 255f, the reference's divisions
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int strip = blockIdx.x, seg = blockIdx.y, frame = blockIdx.z;
     const int rows = a.rows, cols = a.cols;
     const int X0 = strip * FWO, X0c = X0 - 2, xs = X0c - T.rpad;
+    const int xs16 = xs & ~15, xshift = xs - xs16;   // staged rows start on a 16-byte boundary of the plane
     const u8 *__restrict__ base = a.base + (size_t)frame * a.base_stride;
     const int ys = seg * a.seg_rows;
     const int ye = min(ys + a.seg_rows, rows);
     const int yv = seg > 0 ? ys - FR : 0;       // first step with a V pass (one extra step feeds the detector's history)
     const int K = (2 * T.rmax + FR - 1) / FR;   // warm-up steps: H pass only
 
-    // stage base rows y0 + rmin ..., columns xs ..., reflect-101 resolved.  Interior words go through cp.async so the
-    // copy of step c+1 overlaps the V pass and the detector of step c; border words are gathered byte by byte.
+    // stage base rows y0 + rmin ..., columns xs16 ..., reflect-101 resolved.  16-byte groups inside the image go through
+    // cp.async so the copy of step c+1 overlaps the V pass and the detector of step c; border groups are gathered byte
+    // by byte.  One thread per (row, group) of the flattened tile.
+    const int SPQ = SP >> 4, n_stage = T.stage_rows * SPQ;
     auto issue_stage = [&](int y0n) {
-        for (int row = warp; row < T.stage_rows; row += NW) {
+        for (int q = tid; q < n_stage; q += NT) {
+            const int row = (int)(((u32)q * (u32)T.spq_magic) >> 20), j = q - row * SPQ;
             const int y = refl101(y0n + T.rmin + row, rows);
             const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
-            u32 *dst = (u32 *)(stage + row * SP);
-            for (int w = lane; w < SPW; w += 32) {
-                const int x = xs + 4 * w;
-                if (x >= 0 && x + 3 < cols) {
-                    const u32 sa = (u32)__cvta_generic_to_shared(dst + w);
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src + x) : "memory");
-                } else {
-                    dst[w] = (u32)src[refl101(x, cols)] | (u32)src[refl101(x + 1, cols)] << 8 |
-                             (u32)src[refl101(x + 2, cols)] << 16 | (u32)src[refl101(x + 3, cols)] << 24;
+            u32 *dst = (u32 *)(stage + row * SP) + 4 * j;
+            const int x = xs16 + 16 * j;
+            if (x >= 0 && x + 15 < cols) {
+                const u32 sa = (u32)__cvta_generic_to_shared(dst);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src + x) : "memory");
+            } else {
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const int xw = x + 4 * w;
+                    dst[w] = (u32)src[refl101(xw, cols)] | (u32)src[refl101(xw + 1, cols)] << 8 |
+                             (u32)src[refl101(xw + 2, cols)] << 16 | (u32)src[refl101(xw + 3, cols)] << 24;
                 }
             }
         }
     };
     issue_stage(yv - K * FR);
+    for (int i = threadIdx.x; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
+    if (threadIdx.x == 0) s_nq = 0;
 
     for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
         const bool do_v = y0 >= yv;
@@ -212,7 +230,7 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
             const FusedLevel &lv = T.lv[l];
             if (y0 + FR <= yv - 2 * lv.r) continue;          // warm-up: this level's rows are not needed yet
             const int p = (t & 63) >> 2, cg = t & 3;
-            const int boff = 16 * cg + T.rpad - lv.r;
+            const int boff = 16 * cg + T.rpad - lv.r + xshift;
             const u32 sel = 0x3210u + 0x1111u * (u32)(boff & 3);
             const u32 *rowA = (const u32 *)(stage + (lv.r - T.rmin + 2 * p) * SP) + (boff >> 2);
             const u32 *rowB = rowA + SPW;
@@ -287,16 +305,36 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
         }
         __syncthreads();
         // ---- 4a. detector, test: every thread takes samples of the flattened (sample row, level, column) list ------
-        // Result per sample in s_res: the keypoint's value, or -1.  Emission (ordered, per segment) follows in step 5.
+        // Result per sample in s_res: the keypoint's value, or -1.  Samples whose three derivatives are all non-zero need
+        // the full 3x3 inverse (rare): they are queued and evaluated densely in step 5a.  Emission follows in step 5b.
         const bool own_step = do_v && y0 >= ys;
         int si_lo = 0, n_srow = 0;
+        constexpr int NS = FWO / 3;                                           // 20 sample columns per strip
+        constexpr int LS = FW * FTR;                                          // bytes between tiles
+        // computeEdgeResponse + threshold on the G tile of `level` around sample (xc, yc)
+        auto edge_pass = [&](int level, int xc, int yc) -> bool {
+            const u8 *g = gt + ((level - 1) * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
+            int ix2 = 0, iy2 = 0, ixy = 0;
+#pragma unroll
+            for (int u = 0; u <= 1; ++u)
+#pragma unroll
+                for (int v = 0; v <= 1; ++v) {
+                    // reflect-101 of an index at most one outside [0, len): a single bounce (len == 1 -> 0)
+                    const int xx = xc + v, yy = yc + u;
+                    const int xr = (xx + 1 < cols ? xx + 1 : max(cols - 2, 0)) - xc, xl = (xx > 0 ? xx - 1 : min(1, cols - 1)) - xc;
+                    const int yd = (yy + 1 < rows ? yy + 1 : max(rows - 2, 0)) - yc, yu = (yy > 0 ? yy - 1 : min(1, rows - 1)) - yc;
+                    const int gxv = (int)g[xr * FTR + u] - (int)g[xl * FTR + u];
+                    const int gyv = (int)g[v * FTR + yd] - (int)g[v * FTR + yu];
+                    ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
+                }
+            return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // Diff_of_Gauss.cpp:336
+        };
         if (own_step && a.detect) {
             const int yc_lo = y0 == 0 ? 0 : y0 - 2;
             const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;   // centre row yc needs rows up to yc + 2
             si_lo = (yc_lo + 2) / 3;
             n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
             if (n_srow < 0) n_srow = 0;
-            constexpr int NS = FWO / 3;                                       // 20 sample columns per strip
             const int total = n_srow * 3 * NS;
             for (int s = tid; s < total; s += NT) {
                 const int k = s % NS, t = s / NS;
@@ -308,7 +346,6 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
                     const u8 *p = dt + (level * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
                     const int oxm = xc > 0 ? -FTR : 0, oym = yc > 0 ? -1 : 0;
                     const int oxp = xc + 1 < cols ? FTR : 0, oyp = yc + 1 < rows ? 1 : 0;
-                    constexpr int LS = FW * FTR;
                     const int c = p[0];
                     const int a0 = p[oxm + oym], a1 = p[oym], a2 = p[oxm];                    // level
                     const int b0 = p[-LS + oxm + oym], b1 = p[-LS + oym], b2 = p[-LS + oxm], b3 = p[-LS];   // level - 1
@@ -317,33 +354,12 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
                     const int mx = max(max(max(a0, a1), max(a2, c)), max(max(max(b0, b1), max(b2, b3)), max(max(c0, c1), max(c2, c3))));
                     if (c == mn || c == mx) {                                            // Diff_of_Gauss.cpp:287
                         const int dx = a2 - (int)p[oxp], dy = a1 - (int)p[oyp], ds = b3 - c3;   // :226-228
-                        bool pass_c;
-                        int value;
                         if (dx == 0 || dy == 0 || ds == 0) {
                             // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the host
                             // with the same float ops: a.cmin, a.val_lut)
-                            pass_c = c >= a.cmin;
-                            value = a.val_lut[c];
+                            if (c >= a.cmin && edge_pass(level, xc, yc)) res = a.val_lut[c];
                         } else {
-                            const float zhat = localize(dx, dy, ds, c);
-                            pass_c = zhat > a.contrast_thr;                              // :245
-                            value = (int)__fmul_rn(zhat, 255.0f);                        // :246
-                        }
-                        if (pass_c) {
-                            const u8 *g = gt + ((level - 1) * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
-                            int ix2 = 0, iy2 = 0, ixy = 0;
-#pragma unroll
-                            for (int u = 0; u <= 1; ++u)
-#pragma unroll
-                                for (int v = 0; v <= 1; ++v) {
-                                    const int yy = yc + u, xx = xc + v;
-                                    const int xr = refl101(xx + 1, cols) - xc, xl = refl101(xx - 1, cols) - xc;
-                                    const int yd = refl101(yy + 1, rows) - yc, yu = refl101(yy - 1, rows) - yc;
-                                    const int gxv = (int)g[xr * FTR + u] - (int)g[xl * FTR + u];
-                                    const int gyv = (int)g[v * FTR + yd] - (int)g[v * FTR + yu];
-                                    ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
-                                }
-                            if (edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr) res = value;   // :336
+                            s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)s;
                         }
                     }
                 }
@@ -378,11 +394,30 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
             }
         }
         __syncthreads();
-        // ---- 5. tiles: the last 4 rows become the next step's history; ordered emission of the step's keypoints ----
+        // ---- 5a. queued samples: FeaturePointLocalization's full sequence, all lanes busy -------------------------
+        {
+            const int nq = s_nq;
+            for (int i = tid; i < nq; i += NT) {
+                const int s = s_queue[i];
+                const int k = s % NS, t = s / NS;
+                const int level = 1 + t % 3, sr = t / 3;
+                const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
+                const u8 *p = dt + (level * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
+                const int oxm = xc > 0 ? -FTR : 0, oym = yc > 0 ? -1 : 0;
+                const int oxp = xc + 1 < cols ? FTR : 0, oyp = yc + 1 < rows ? 1 : 0;
+                const int c = p[0];
+                const int dx = (int)p[oxm] - (int)p[oxp], dy = (int)p[oym] - (int)p[oyp], ds = (int)p[-LS] - (int)p[LS];
+                const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
+                if (zhat > a.contrast_thr && edge_pass(level, xc, yc))                   // :245
+                    s_res[s] = (int)__fmul_rn(zhat, 255.0f);                             // :246
+            }
+            __syncthreads();
+            if (tid == 0) s_nq = 0;
+        }
+        // ---- 5b. tiles: the last 4 rows become the next step's history; ordered emission of the step's keypoints ---
         if (do_v)
             for (int t = tid; t < (F_NG + F_ND) * FW; t += NT) tiles32[t * FTW] = tiles32[t * FTW + FTW - 1];
         for (int task = warp; task < 3 * n_srow; task += NW) {       // one warp per segment (level, sample row, strip)
-            constexpr int NS = FWO / 3;
             const int res = lane < NS ? s_res[task * NS + lane] : -1;
             const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
             if (bal) {
@@ -415,8 +450,8 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
 // ---------------------------------------------------------------------------------------------------------------
 int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames) {
     if (n_frames <= 0 || n_frames > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: %d frames per launch", n_frames);
-    if ((a.base_pitch & 3) || ((uintptr_t)a.base & 3) || (a.base_stride & 3))
-        VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: base plane must be 4-byte aligned (pitch %zu)", a.base_pitch);
+    if ((a.base_pitch & 15) || ((uintptr_t)a.base & 15) || (a.base_stride & 15))
+        VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: base plane must be 16-byte aligned (pitch %zu)", a.base_pitch);
     const size_t sm = fused_smem_bytes(a.taps);
     if (sm > 223 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave %d needs %zu bytes of shared memory", a.octave, sm);
     a.n_strips = fused_strips(a.cols);

@@ -21,8 +21,9 @@ struct FusedLevel {
 struct FusedTaps {
     FusedLevel lv[6];
     int rmin, rmax, rpad;           // rpad >= rmax, rpad == 2 (mod 4): left halo of the staged base rows
-    int stage_rows, stage_pitch;    // staged base tile: rows, bytes between rows (multiple of 4)
-    int hbuf_words;                 // total words of the six h buffers (+ one spare pair row)
+    int stage_rows, stage_pitch;    // staged base tile: rows, bytes between rows (multiple of 16)
+    int spq_magic;                  // ceil(2^20 / (stage_pitch / 16)): flattened index -> row without a division
+    int hbuf_words;                 // total words of the six h buffers (+ spare pair rows); multiple of 4
 };
 
 // Launch description.  All planes of one octave share `pitch`; frame f's plane is at ptr + f * frame_stride.

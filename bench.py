@@ -25,6 +25,7 @@ sys.path.insert(0, ROOT)
 
 WORKLOADS = {"1080p": (1080, 1920, 256), "4k": (2160, 3840, 64), "8k": (4320, 7680, 16)}
 MAC_PER_PX = 1738.0            # blur MACs per input pixel (both passes, 4 octaves x 6 levels)
+ALU_PEAK_T = 18.58             # measured IDP.4A / IDP.2A peak, T lane-instr/s (tools/alu_peak.cu, profiles/alu_peak_r1.json)
 KP_CAP_PER_MPX = 40000         # output list capacity (entries per input Mpix), generous: ~1.2k/Mpx expected
 METRIC = "Mpix/s (frames/s) DoG+Harris at 1/2/4/8 B200; % HBM roofline vs host CPU"
 
@@ -257,24 +258,36 @@ def main():
     if prof:
         tot = sum(v["ms"] for v in prof.values()) or 1.0
         dom = max(prof, key=lambda k: prof[k]["ms"])
-        blur_ms = prof["hblur6_k"]["ms"] + prof["vblur6_k"]["ms"]
         dlaunch = prof[dom]["launches"] or 1
-        # algorithmic bytes of one blur-pass launch (one octave of one frame), DESIGN.md section 4:
-        #   hblur6_k: read base 1 B + write 6 x u16 = 13 B per octave pixel; vblur6_k: read 12 B + write 6+5 u8 (+1/4) = 23.25 B
-        oct_px = [4 * h * w / 4 ** o for o in range(4)]
-        per_launch = {"hblur6_k": 13.0 * sum(oct_px) / 4, "vblur6_k": 23.25 * sum(oct_px) / 4,
-                      "harris_fused_k": 6.0 * h * w, "dog_detect_k": 11.0 * sum(oct_px) / 4}
+        # ALGORITHMIC HBM bytes per launch of each kernel, launches cover the whole batch:
+        #   octave_fused_k (keypoints-only mode): read the octave base 1 B/px, write the next base 1/4 B/px (none after the
+        #     last octave), 24 B per keypoint; 4 launches per step, one per octave -> average over the 4
+        #   harris_fused_k (pipeline mode): read 1 B, write response 4 B + mask 1 B per pixel, 12 B per corner
+        #   upsample2x_k: read 1 B, write 4 B per input pixel
+        oct_px = [4.0 * h * w / 4 ** o for o in range(4)]
+        fused_bytes = nf * (sum(oct_px) + sum(oct_px[1:])) / 4 + 24.0 * nk / 4
+        per_launch = {"octave_fused_k": fused_bytes, "harris_fused_k": 6.0 * h * w + 12.0 * nc / max(nf, 1),
+                      "upsample2x_k": 5.0 * h * w * nf}
         alg = per_launch.get(dom, 0.0)
         ach = alg / 1e9 / (prof[dom]["ms"] / dlaunch * 1e-3) if alg else None
-        mac_s = MAC_PER_PX * px_step * args.steps / (blur_ms * 1e-3) if blur_ms else None
+        fused_ms = prof["octave_fused_k"]["ms"]
+        # the Gaussian stack is integer-ALU bound: packed dot-product instructions against the measured
+        # IDP.4A / IDP.2A issue peak (tools/alu_peak.cu on this pool's B200: 18.58 T lane-instr/s)
+        idp_per_px = MAC_PER_PX / 2 / 4 + MAC_PER_PX / 2 / 2          # H pass dp4a + V pass dp2a, exact tap counts
+        idp_s = idp_per_px * px_step * args.steps / (fused_ms * 1e-3) if fused_ms else None
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                             "frac": ach / hbm_peak if ach else None, "traffic": None, "peak_source": peak_src,
-                            "mode": "hot-path materialise (H-pass 8.8 planes + gauss + DoG in HBM)",
-                            "note": "the blur pair is integer-ALU bound (SURVEY.md 8(d)); see alu",
-                            "alu": {"blur_TMAC_s": mac_s / 1e12 if mac_s else None, "mac_per_input_px": MAC_PER_PX,
-                                    "blur_ms_per_step": blur_ms / args.steps},
-                            "kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in prof.items()},
-                            "kernel_share": {k: v["ms"] / tot for k, v in prof.items()}}
+                            "mode": "keypoints-only (fused): octave bases are the only maps in HBM",
+                            "note": "octave_fused_k is integer-ALU bound, not HBM bound (1738 MAC per input pixel, SURVEY.md 8(d)): "
+                                    "its meaningful fraction is alu.frac; the HBM fraction is reported because the contract asks for it",
+                            "alu": {"bound": "IDP (dp4a/dp2a) issue", "achieved": idp_s / 1e12 if idp_s else None, "peak": ALU_PEAK_T,
+                                    "unit": "T lane-instr/s", "frac": idp_s / 1e12 / ALU_PEAK_T if idp_s else None,
+                                    "peak_source": "measured with tools/alu_peak.cu on a B200 of this pool (profiles/alu_peak_r1.json)",
+                                    "idp_per_input_px": idp_per_px, "mac_per_input_px": MAC_PER_PX,
+                                    "TMAC_s": MAC_PER_PX * px_step * args.steps / (fused_ms * 1e-3) / 1e12 if fused_ms else None},
+                            "kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in prof.items() if v["launches"]},
+                            "kernel_launches_per_step": {k: v["launches"] / args.steps for k, v in prof.items() if v["launches"]},
+                            "kernel_share": {k: v["ms"] / tot for k, v in prof.items() if v["launches"]}}
     if not args.no_cpu_baseline:
         n_sample = 2 if h * w <= 2.1e6 else 1
         dt, kind, cores, _, _ = cpu_reference_frames([uniq[i] for i in range(min(n_sample, len(uniq)))])

@@ -202,7 +202,7 @@ class Context:
     def sync(self):
         self._chk(load().vslam_sync(self.h))
 
-    KERNELS = ["upsample2x_k", "hblur6_k", "vblur6_k", "dog_detect_k", "seg_scan_k+seg_gather_k", "harris_fused_k", "grad_k", "octave_fused_k"]
+    KERNELS = ["upsample2x_k", "(unused)", "(unused2)", "dog_detect_k", "segment scan+gather", "harris_fused_k", "grad_k", "octave_fused_k"]
 
     def profile(self, enable=True):
         self._chk(load().vslam_profile(self.h, 1 if enable else 0))

@@ -78,7 +78,9 @@ int build_fused_taps(double sigma0, int scale_samples, int octave, FusedTaps *ou
     const int wmin = (FW + 2 * rpad + 3) / 4 + 1;
     if (need < wmin) need = wmin;
     need += 3;                                                       // the 16-byte alignment shift of the origin
+    need += 4;                                                       // LDS.128 reads whole 16-byte blocks
     out->stage_pitch = (need * 4 + 15) & ~15;
+    while ((out->stage_pitch & 63) != 32) out->stage_pitch += 16;   // conflict-free LDS.128 across the row pairs of a warp
     {   // row = (q * magic) >> 20 for q < stage_rows * (pitch / 16): checked exhaustively
         const int spq = out->stage_pitch >> 4, nq = out->stage_rows * spq;
         out->spq_magic = ((1 << 20) + spq - 1) / spq;
@@ -97,23 +99,28 @@ int fused_strips(int cols) { return (cols + FWO - 1) / FWO; }
 // ---------------------------------------------------------------------------------------------------------------
 // device: the two blur passes
 // ---------------------------------------------------------------------------------------------------------------
-// H pass body: UH tap words (4 taps each) for 2 rows x 4 groups x 4 byte alignments.  The staged words are first
-// re-aligned by the level's byte offset (sel), then the three shifted views of every word come from PRMT (ALU pipe),
-// so the dot-product pipe sees exactly one IDP.4A per 4 taps per output.
-template <int UH>
-__device__ __forceinline__ void hbody(const u32 *__restrict__ rowA, const u32 *__restrict__ rowB,
+// H pass body: UH tap words (4 taps each) for 2 rows x 4 groups x 4 byte alignments.  The thread's window of staged
+// words starts WS words into a 16-byte aligned block, so the loads are three conflict-free LDS.128 per row (the staged
+// pitch is 32 mod 64 bytes).  The words are first re-aligned by the level's byte offset (sel), then the three shifted
+// views of every word come from PRMT (ALU pipe), so the dot-product pipe sees exactly one IDP.4A per 4 taps per output.
+template <int UH, int WS>
+__device__ __forceinline__ void hbody(const uint4 *__restrict__ rowA, const uint4 *__restrict__ rowB,
                                       const u32 *__restrict__ hq, int it, u32 sel, u32 (&acc)[2][4][4]) {
     u32 t[UH];
 #pragma unroll
     for (int u = 0; u < UH; ++u) t[u] = hq[it + u];
 #pragma unroll
     for (int row = 0; row < 2; ++row) {
-        const u32 *p = (row ? rowB : rowA) + it;
-        u32 d[UH + 5], e[UH + 4];
+        const uint4 *p = (row ? rowB : rowA) + (it >> 2);
+        constexpr int NQ = (WS + UH + 5 + 3) / 4;
+        u32 raw[4 * NQ], e[UH + 4];
 #pragma unroll
-        for (int j = 0; j < UH + 5; ++j) d[j] = p[j];
+        for (int q = 0; q < NQ; ++q) {
+            const uint4 v = p[q];
+            raw[4 * q] = v.x; raw[4 * q + 1] = v.y; raw[4 * q + 2] = v.z; raw[4 * q + 3] = v.w;
+        }
 #pragma unroll
-        for (int j = 0; j < UH + 4; ++j) e[j] = __byte_perm(d[j], d[j + 1], sel);
+        for (int j = 0; j < UH + 4; ++j) e[j] = __byte_perm(raw[WS + j], raw[WS + j + 1], sel);
 #pragma unroll
         for (int j = 0; j < UH + 3; ++j) {
             const u32 v0 = e[j];
@@ -132,6 +139,14 @@ __device__ __forceinline__ void hbody(const u32 *__restrict__ rowA, const u32 *_
             }
         }
     }
+}
+
+template <int WS>
+__device__ __forceinline__ void hloop(const uint4 *__restrict__ rowA, const uint4 *__restrict__ rowB, const u32 *__restrict__ hq,
+                                      int nw, u32 sel, u32 (&acc)[2][4][4]) {
+    int it = 0;
+    for (; it + 4 <= nw; it += 4) hbody<4, WS>(rowA, rowB, hq, it, sel, acc);
+    if (nw & 2) hbody<2, WS>(rowA, rowB, hq, it, sel, acc);
 }
 
 // V pass body: UV tap pairs for RB output rows of one column.  d[] are packed row pairs (2p | 2p+1 << 16); even
@@ -232,14 +247,18 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
             const int p = (t & 63) >> 2, cg = t & 3;
             const int boff = 16 * cg + T.rpad - lv.r + xshift;
             const u32 sel = 0x3210u + 0x1111u * (u32)(boff & 3);
-            const u32 *rowA = (const u32 *)(stage + (lv.r - T.rmin + 2 * p) * SP) + (boff >> 2);
-            const u32 *rowB = rowA + SPW;
+            const int wl = boff >> 2;                            // first staged word of the thread's window
+            const uint4 *rowA = (const uint4 *)(stage + (lv.r - T.rmin + 2 * p) * SP) + (wl >> 2);
+            const uint4 *rowB = rowA + (SP >> 4);
             u32 acc[2][4][4];
 #pragma unroll
             for (int i = 0; i < 32; ++i) (&acc[0][0][0])[i] = 0;
-            int it = 0;
-            for (; it + 4 <= lv.nw; it += 4) hbody<4>(rowA, rowB, lv.hq, it, sel, acc);
-            if (lv.nw & 2) hbody<2>(rowA, rowB, lv.hq, it, sel, acc);
+            switch (wl & 3) {                                    // warp-uniform (same level, 16-column groups)
+            case 0: hloop<0>(rowA, rowB, lv.hq, lv.nw, sel, acc); break;
+            case 1: hloop<1>(rowA, rowB, lv.hq, lv.nw, sel, acc); break;
+            case 2: hloop<2>(rowA, rowB, lv.hq, lv.nw, sel, acc); break;
+            default: hloop<3>(rowA, rowB, lv.hq, lv.nw, sel, acc); break;
+            }
             uint4 *o = (uint4 *)(hbuf + lv.hoff + (lv.r + p) * FW + 16 * cg);
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
@@ -477,7 +496,8 @@ int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames) {
         attr_done = true;
     }
     KernelSpan span(ctx, VSLAM_K_FUSED);
-    if (sm <= 75 * 1024) octave_fused_k<128><<<grid, 128, sm, ctx->stream>>>(a);
+    static const long nt128_max = getenv("VSLAM_NT128_MAX") ? atol(getenv("VSLAM_NT128_MAX")) : 75 * 1024;
+    if ((long)sm <= nt128_max) octave_fused_k<128><<<grid, 128, sm, ctx->stream>>>(a);
     else octave_fused_k<256><<<grid, 256, sm, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;

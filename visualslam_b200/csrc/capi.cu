@@ -602,10 +602,13 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     if (w2 != 3 && w2 != 5) VS_FAIL(ctx, VSLAM_E_INVALID, "nms2_window must be 3 or 5 (got %d)", w2);
     const u8 *d_frames; size_t d_pitch, d_stride;
     VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
-    int ntx, nty;
-    harris_grid(rows, cols, &ntx, &nty);
-    const size_t n_seg = (size_t)rows * ntx;
-    VS_TRY(seg_prepare(ctx, n_seg, sizeof(vslam_corner), staging_entries(capacity, (size_t)rows * cols)));
+    const int n_strips = harris_strips(cols);
+    const size_t spf = (size_t)rows * n_strips;                  // segments per frame: (row, strip)
+    size_t fb = ((size_t)1 << 30) / spf;                         // frames per launch
+    if (fb > 32768) fb = 32768;
+    if (fb > (size_t)n_frames) fb = (size_t)n_frames;
+    if (fb < 1) VS_FAIL(ctx, VSLAM_E_INVALID, "image too large for the segment table");
+    VS_TRY(seg_prepare(ctx, spf * fb, sizeof(vslam_corner), staging_entries(capacity, (size_t)rows * cols * fb)));
     VS_TRY(reserve_counters(ctx, n_frames));
     vslam_corner *d_out = corners;
     if (out_space != VSLAM_DEVICE) {
@@ -621,17 +624,22 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         d_m3 = mask3 ? ctx->maps_dev.as<u8>() + px * 5 * n_frames : nullptr;
     }
     int *cnt = ctx->counters.as<int>();
-    for (int f = 0; f < n_frames; ++f) {
+    for (int f0 = 0; f0 < n_frames; f0 += (int)fb) {
+        const int nf = n_frames - f0 < (int)fb ? n_frames - f0 : (int)fb;
+        if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, spf * nf * 4, ctx->stream));
         VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
         HarrisArgs a;
-        a.frame = d_frames + d_stride * f; a.rows = rows; a.cols = cols; a.pitch = d_pitch; a.k = k; a.nms2_pad = (w2 - 1) / 2;
-        a.response = d_resp ? d_resp + px * f : nullptr;
-        a.r8 = d_r8 ? d_r8 + px * f : nullptr;
-        a.mask3 = d_m3 ? d_m3 + px * f : nullptr;
-        a.seg_base = 0; a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
+        memset(&a, 0, sizeof a);
+        a.frames = d_frames + d_stride * f0; a.pitch = d_pitch; a.frame_stride = d_stride;
+        a.rows = rows; a.cols = cols; a.k = k; a.nms2_pad = (w2 - 1) / 2;
+        a.response = d_resp ? d_resp + px * f0 : nullptr;
+        a.r8 = d_r8 ? d_r8 + px * f0 : nullptr;
+        a.mask3 = d_m3 ? d_m3 + px * f0 : nullptr;
+        a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
         a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = ctx->staging_entries;
-        VS_TRY(launch_harris(ctx, a));
-        VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f, 1));
+        a.want_corners = 1;
+        VS_TRY(launch_harris(ctx, a, nf));
+        VS_TRY(seg_finalise(ctx, spf * nf, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf));
     }
     if (out_space != VSLAM_DEVICE) {
         if (response) VS_CUDA(ctx, cudaMemcpyAsync(response, d_resp, px * 4 * n_frames, cudaMemcpyDeviceToHost, ctx->stream));

@@ -1,4 +1,4 @@
-// harris.cu -- fused Harris corner path: one kernel from the 8-bit frame to the response
+// harris.cu -- fused Harris corner path: one kernel from the 8-bit frames to the response
 // map, the 8-bit response, the 3x3 NMS mask and the ordered NMS2 corner list.
 //
 //   row K  Harris_corners.cpp:158      GaussianBlur(3x3, sigma 0) 8U  == (S121x121 + 8) >> 4, reflect-101
@@ -8,165 +8,289 @@
 //   row O  :176, :70-81                convertScaleAbs, centre-excluded 3x3 dilate, strict '>'
 //   row P  :83-129                     NMS2: 4x4 half-open window, '>=', interior only, row-major emission
 //
-// Tile = 32 x 64 pixels per 256-thread block.  Halo budget: NMS2 reads R at offsets -2..+1, R needs gradients at
-// +-1, gradients need the blurred image at +-1, the blur needs the frame at +-1 -> the frame tile is (32+9)x(64+9).
-// All sums are small integers, so they are accumulated in int32 / int64 and converted once; the float steps use
-// round-to-nearest intrinsics (no FMA contraction) to reproduce the reference's three separately rounded ops.
+// Design: a streaming register pipeline.  A warp owns a strip of 112 columns (lane = 4 adjacent pixels; two halo
+// lanes on each side) and marches down a band of rows.  Every stage keeps its sliding window of rows in registers
+// (packed 16x2 where the values allow it), horizontal neighbours come from the adjacent lanes with SHFL, so each frame
+// byte is loaded once (plus band/strip halos) and nothing but the requested outputs is written: the kernel moves the
+// algorithmic 6 B per pixel in pipeline mode (1 read + 4 response + 1 mask).  All sums are exact integers; det is
+// formed in int64 and rounded once (== OpenCV's double det2 -> float); the three float steps of the response use
+// round-to-nearest intrinsics (no FMA contraction).  Corners are staged per warp in shared memory and flushed with
+// one atomic per 8 rows; compaction.cu orders the (frame, row, strip) segments.
 #include "harris.cuh"
 
 namespace vslam {
 
-constexpr int TH = 32, TW = 64;
-constexpr int RAW_H = TH + 9, RAW_W = TW + 9, RAW_S = 76;
-constexpr int BL_H = TH + 7, BL_W = TW + 7, BL_S = 72;
-constexpr int GR_H = TH + 5, GR_W = TW + 5, GR_S = 70;
-constexpr int RS_H = TH + 3, RS_W = TW + 3, RS_S = 68;
+constexpr int HS = kHarrisStrip, HB = kHarrisBand;
+constexpr int H_WARPS = 4;                 // warps per CTA, each an independent (strip, band)
+constexpr int H_CAP = 256;                 // staged corners per warp before a flush
+constexpr int H_ROWS = 8;                  // rows per flush
 
+__device__ __forceinline__ u32 pk(u32 lo, u32 hi, u32 sel) { return __byte_perm(lo, hi, sel); }
+
+// saturate_cast<uchar>(cvRound(|r|)) for r >= 0; cvRound returns INT_MIN for r >= 2^31, which saturates to 0
 __device__ __forceinline__ int r8_of(float r) {
-    // saturate_cast<uchar>(cvRound(|r|)); cvtss2si returns INT_MIN for |r| >= 2^31, which saturates to 0
-    const float a = fabsf(r);
-    if (a >= 2147483648.f) return 0;
-    return min(__float2int_rn(a), 255);
+    const float m = __fadd_rn(fminf(r, 255.0f), 12582912.0f);          // round half to even in the low mantissa bits
+    return r >= 2147483648.f ? 0 : (__float_as_int(m) & 0xff);
 }
 
-__global__ void __launch_bounds__(256) harris_fused_k(HarrisArgs a) {
-    __shared__ u8 s_raw[RAW_H * RAW_S];
-    __shared__ u8 s_bl[BL_H * BL_S];
-    __shared__ short s_ix[GR_H * GR_S], s_iy[GR_H * GR_S];
-    __shared__ float s_r[RS_H * RS_S];
-    __shared__ u32 s_flag[TH][2];
-    __shared__ int s_rowoff[TH];
-    __shared__ int s_base;
-    const int tid = threadIdx.x;
-    const int X0 = blockIdx.x * TW, Y0 = blockIdx.y * TH;
+template <int P2>
+__global__ void __launch_bounds__(32 * H_WARPS) harris_march_k(const HarrisArgs a) {
+    __shared__ vslam_corner s_buf[H_WARPS][H_CAP];
+    __shared__ int s_rowoff[H_WARPS][H_ROWS], s_rowcnt[H_WARPS][H_ROWS];
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int unit = blockIdx.x * H_WARPS + warp;
+    if (unit >= a.n_strips * a.n_bands) return;                 // warps are independent: no block-wide barrier below
+    const int strip = unit % a.n_strips, band = unit / a.n_strips, frame = blockIdx.z;
     const int rows = a.rows, cols = a.cols;
-    const u8 *__restrict__ img = a.frame;
+    const int X0 = strip * HS, c = X0 - 8 + 4 * lane;           // this lane's 4 pixels: columns c .. c+3
+    const int Y0 = band * HB, Y1 = min(Y0 + HB, rows);
+    const u8 *__restrict__ img = a.frames + (size_t)frame * a.frame_stride;
+    const bool fast_ld = c >= 0 && c + 3 < cols && !(a.pitch & 3) && !((uintptr_t)img & 3);
+    const bool own = lane >= 2 && lane < 30;
+    bool inx[4], nmsx[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        inx[j] = (unsigned)(c + j) < (unsigned)cols;
+        nmsx[j] = own && c + j >= P2 && c + j < cols - P2;      // NMS2 interior columns (Harris_corners.cpp:95)
+    }
+    // replicate padding of the GRADIENT maps (row M): column -1 := column 0, column cols := column cols-1
+    const bool repL = c == 0, rep0 = c + 1 == cols, rep1 = c + 2 == cols, rep2 = c + 3 == cols, repR = c + 4 == cols;
+    const bool vec_out = !(cols & 3) && !((uintptr_t)a.response & 15) && !((uintptr_t)a.r8 & 3) && !((uintptr_t)a.mask3 & 3);
+    const size_t fpx = (size_t)frame * rows * cols;
 
-    // frame tile, reflect-101 extension: origin (Y0-5, X0-5)
-    for (int idx = tid; idx < RAW_H * RAW_W; idx += 256) {
-        const int ly = idx / RAW_W, lx = idx - ly * RAW_W;
-        const int gy = refl101(Y0 - 5 + ly, rows), gx = refl101(X0 - 5 + lx, cols);
-        s_raw[ly * RAW_S + lx] = img[(size_t)gy * a.pitch + gx];
-    }
-    __syncthreads();
-    // row K: blurred, origin (Y0-4, X0-4)
-    for (int idx = tid; idx < BL_H * BL_W; idx += 256) {
-        const int ly = idx / BL_W, lx = idx - ly * BL_W;
-        const u8 *p = s_raw + ly * RAW_S + lx;       // top-left of the 3x3 window
-        const int s = p[0] + 2 * p[1] + p[2] + 2 * (p[RAW_S] + 2 * p[RAW_S + 1] + p[RAW_S + 2]) + p[2 * RAW_S] +
-                      2 * p[2 * RAW_S + 1] + p[2 * RAW_S + 2];
-        s_bl[ly * BL_S + lx] = (u8)((s + 8) >> 4);
-    }
-    __syncthreads();
-    // row L on replicate-clamped coordinates (row M pads the GRADIENT maps by replication), origin (Y0-3, X0-3)
-    for (int idx = tid; idx < GR_H * GR_W; idx += 256) {
-        const int ly = idx / GR_W, lx = idx - ly * GR_W;
-        const int cy = clampi(Y0 - 3 + ly, 0, rows - 1) - (Y0 - 4), cx = clampi(X0 - 3 + lx, 0, cols - 1) - (X0 - 4);
-        const u8 *p = s_bl + cy * BL_S + cx;
-        s_ix[ly * GR_S + lx] = (short)((int)p[1] - (int)p[-1]);
-        s_iy[ly * GR_S + lx] = (short)((int)p[BL_S] - (int)p[-BL_S]);
-    }
-    __syncthreads();
-    // rows M, N: response, origin (Y0-2, X0-2); zero outside the image
-    for (int idx = tid; idx < RS_H * RS_W; idx += 256) {
-        const int ly = idx / RS_W, lx = idx - ly * RS_W;
-        const int gy = Y0 - 2 + ly, gx = X0 - 2 + lx;
-        float resp = 0.f;
-        if (gy >= 0 && gy < rows && gx >= 0 && gx < cols) {
-            int ix2 = 0, iy2 = 0, ixy = 0;
+    u32 ra0 = 0, ra1 = 0, rb0 = 0, rb1 = 0;                     // raw rows yr-2, yr-1 (16x2)
+    u32 bA0 = 0, bA1 = 0, bB0 = 0, bB1 = 0;                     // blurred rows yr-3, yr-2 (16x2)
+    int hs[4][3][4];                                            // horizontal 3-sums of xx, yy, xy; ring by row & 3
+    float hmax[4][4];                                           // horizontal window maxima of R; ring by row & 3
+    int m3[4][4];                                               // 3-wide maxima of the 8-bit response; ring by row & 3
+    float Rp[4];                                                // R of row yr-4 (the output row)
+    int q8p[4], m2p[4];                                         // 8-bit response of row yr-4 and its left/right maximum
 #pragma unroll
-            for (int u = 0; u < 3; ++u)
+    for (int s = 0; s < 4; ++s)
 #pragma unroll
-                for (int v = 0; v < 3; ++v) {
-                    const int x = s_ix[(ly + u) * GR_S + lx + v], y = s_iy[(ly + u) * GR_S + lx + v];
-                    ix2 += x * x; iy2 += y * y; ixy += x * y;
+        for (int j = 0; j < 4; ++j) {
+            hs[s][0][j] = hs[s][1][j] = hs[s][2][j] = 0; hmax[s][j] = 0.f; m3[s][j] = 0;
+            Rp[j] = 0.f; q8p[j] = 0; m2p[j] = 0;
+        }
+    int cur = 0, ri = 0, batch_y0 = Y0;                         // staged corners / rows of the current flush batch
+
+    auto flush = [&]() {
+        __syncwarp();
+        if (cur > 0) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(a.cursor, cur);
+            base = __shfl_sync(FULL, base, 0);
+            for (int i = lane; i < cur; i += 32)
+                if (base + i < a.staging_cap) a.staging[base + i] = s_buf[warp][i];
+            if (lane < ri && s_rowcnt[warp][lane] > 0) {
+                const size_t sg = ((size_t)frame * rows + (batch_y0 + lane)) * a.n_strips + strip;
+                a.seg_off[sg] = base + s_rowoff[warp][lane];
+                a.seg_cnt[sg] = s_rowcnt[warp][lane];
+            }
+        }
+        __syncwarp();
+        cur = 0; ri = 0;
+    };
+
+    const int yr_begin = (Y0 - 5) & ~3;                         // ring slots are compile-time: start on a multiple of 4
+    for (int yr4 = yr_begin; yr4 <= Y1 + 3; yr4 += 4) {
+#pragma unroll
+        for (int ph = 0; ph < 4; ++ph) {
+            const int yr = yr4 + ph;                            // (yr & 3) == ph
+            // ---- raw row yr, reflect-101 --------------------------------------------------------------------
+            u32 w;
+            {
+                const u8 *__restrict__ src = img + (size_t)refl101(yr, rows) * a.pitch;
+                if (fast_ld) w = *(const u32 *)(src + c);
+                else w = (u32)src[refl101(c, cols)] | (u32)src[refl101(c + 1, cols)] << 8 |
+                         (u32)src[refl101(c + 2, cols)] << 16 | (u32)src[refl101(c + 3, cols)] << 24;
+            }
+            const u32 n0 = pk(w, 0, 0x4140), n1 = pk(w, 0, 0x4342);
+            // ---- row K: blurred row yr-1 = (121 x 121 + 8) >> 4 -----------------------------------------------
+            const u32 V0 = ra0 + 2 * rb0 + n0, V1 = ra1 + 2 * rb1 + n1;
+            ra0 = rb0; ra1 = rb1; rb0 = n0; rb1 = n1;
+            u32 Bn0, Bn1;
+            {
+                const u32 L = __shfl_up_sync(FULL, V1, 1), R = __shfl_down_sync(FULL, V0, 1);
+                const u32 Vm = pk(L, V0, 0x5432), Vc = pk(V0, V1, 0x5432), Vp = pk(V1, R, 0x5432);
+                Bn0 = ((Vm + 2 * V0 + Vc + 0x00080008u) >> 4) & 0x00ff00ffu;
+                Bn1 = ((Vc + 2 * V1 + Vp + 0x00080008u) >> 4) & 0x00ff00ffu;
+            }
+            // ---- row L: gradients of row yr-2 (biased by 256, 16x2) --------------------------------------------
+            u32 e[6];                                           // per pixel ix | iy << 16 for columns c-1 .. c+4
+            {
+                const u32 L = __shfl_up_sync(FULL, bB1, 1), R = __shfl_down_sync(FULL, bB0, 1);
+                const u32 Bm = pk(L, bB0, 0x5432), Bc = pk(bB0, bB1, 0x5432), Bp = pk(bB1, R, 0x5432);
+                const u32 IX01 = Bc + 0x01000100u - Bm, IX23 = Bp + 0x01000100u - Bc;
+                const u32 IY01 = Bn0 + 0x01000100u - bA0, IY23 = Bn1 + 0x01000100u - bA1;
+                e[1] = pk(IX01, IY01, 0x5410); e[2] = pk(IX01, IY01, 0x7632);
+                e[3] = pk(IX23, IY23, 0x5410); e[4] = pk(IX23, IY23, 0x7632);
+                e[0] = __shfl_up_sync(FULL, e[4], 1); e[5] = __shfl_down_sync(FULL, e[1], 1);
+                if (repL) e[0] = e[1];
+                if (rep0) e[2] = e[1];
+                if (rep1) e[3] = e[2];
+                if (rep2) e[4] = e[3];
+                if (repR) e[5] = e[4];
+            }
+            bA0 = bB0; bA1 = bB1; bB0 = Bn0; bB1 = Bn1;
+            // ---- row M, horizontal part: 3-sums of the products, row yr-2 -> ring slot (ph + 2) & 3 ---------------
+            {
+                int xx[6], yy[6], xy[6];
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    const int ix = (int)(e[i] & 0xffffu) - 256, iy = (int)(e[i] >> 16) - 256;
+                    xx[i] = ix * ix; yy[i] = iy * iy; xy[i] = ix * iy;
                 }
-            const long long det_i = (long long)ix2 * iy2 - (long long)ixy * ixy;   // exact; == double det2
-            const float det = __ll2float_rn(det_i);
-            const float tr = (float)(ix2 + iy2);                                     // exact (< 2^24)
-            const float r = __fsub_rn(det, __fmul_rn(a.k, __fmul_rn(tr, tr)));       // Harris_corners.cpp:57
-            resp = r > 0.f ? r : 0.f;
-        }
-        s_r[ly * RS_S + lx] = resp;
-    }
-    __syncthreads();
-    // outputs + NMS, 4 rows per pass; a warp covers half a tile row
-    const int p2 = a.nms2_pad;
-    const int lane = tid & 31;
-    for (int pass = 0; pass < TH / 4; ++pass) {
-        const int ty = pass * 4 + (tid >> 6), tx = tid & 63;
-        const int gy = Y0 + ty, gx = X0 + tx;
-        const bool in = gy < rows && gx < cols;
-        const float *c = s_r + (ty + 2) * RS_S + tx + 2;
-        const float r = *c;
-        bool corner = false;
-        if (in) {
-            const size_t o = (size_t)gy * cols + gx;
-            if (a.response) a.response[o] = r;
-            const int v8 = r8_of(r);
-            if (a.r8) a.r8[o] = (u8)v8;
-            if (a.mask3) {
-                int m = 0;
+                const int S = (ph + 2) & 3;
 #pragma unroll
-                for (int u = -1; u <= 1; ++u)
+                for (int j = 0; j < 4; ++j) {
+                    hs[S][0][j] = xx[j] + xx[j + 1] + xx[j + 2];
+                    hs[S][1][j] = yy[j] + yy[j + 1] + yy[j + 2];
+                    hs[S][2][j] = xy[j] + xy[j + 1] + xy[j + 2];
+                }
+            }
+            // ---- rows M (vertical part), N: response of row rb = yr-3 ----------------------------------------------
+            const int rb = yr - 3;
+            float Rn[4];
+            if (rb >= 0 && rb < rows) {
+                // replicate padding in y: rows -1 and `rows` of the gradient maps repeat rows 0 and rows-1
+                const int SM = (ph + 1) & 3, ST = ph & 3, SB = (ph + 2) & 3;
+                int sx[4], sy[4], sxy[4];
+                if (rb == 0 && rb == rows - 1) {
 #pragma unroll
-                    for (int v = -1; v <= 1; ++v)
-                        if (u || v) m = max(m, r8_of(c[u * RS_S + v]));
-                a.mask3[o] = v8 > m ? 255 : 0;
-            }
-            if (r > 0.f && gy >= p2 && gy < rows - p2 && gx >= p2 && gx < cols - p2) {
-                float m = 0.f;
-                for (int u = -p2; u < p2; ++u)
-                    for (int v = -p2; v < p2; ++v) m = fmaxf(m, c[u * RS_S + v]);
-                corner = r >= m;
-            }
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, corner);
-        if (lane == 0) s_flag[ty][tx >> 5] = bal;
-    }
-    __syncthreads();
-    if (tid < 32) {
-        const int cnt = __popc(s_flag[tid][0]) + __popc(s_flag[tid][1]);
-        int incl = cnt;
+                    for (int j = 0; j < 4; ++j) { sx[j] = 3 * hs[SM][0][j]; sy[j] = 3 * hs[SM][1][j]; sxy[j] = 3 * hs[SM][2][j]; }
+                } else if (rb == 0) {
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (tid >= d) incl += t;
-        }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        int base = 0;
-        if (tid == 0 && total) base = atomicAdd(a.cursor, total);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        s_rowoff[tid] = base + incl - cnt;
-        if (Y0 + tid < rows) {
-            const int seg = a.seg_base + (Y0 + tid) * gridDim.x + blockIdx.x;
-            a.seg_off[seg] = base + incl - cnt;
-            a.seg_cnt[seg] = cnt;
-        }
-    }
-    __syncthreads();
-    for (int pass = 0; pass < TH / 4; ++pass) {
-        const int ty = pass * 4 + (tid >> 6), tx = tid & 63;
-        const u32 f = s_flag[ty][tx >> 5];
-        if (f >> (tx & 31) & 1u) {
-            int pos = s_rowoff[ty] + __popc(f & ((1u << (tx & 31)) - 1u));
-            if (tx >= 32) pos += __popc(s_flag[ty][0]);
-            if (pos < a.staging_cap) {
-                vslam_corner k;
-                k.row = Y0 + ty; k.col = X0 + tx; k.value = s_r[(ty + 2) * RS_S + tx + 2];
-                a.staging[pos] = k;
+                    for (int j = 0; j < 4; ++j) { sx[j] = 2 * hs[SM][0][j] + hs[SB][0][j]; sy[j] = 2 * hs[SM][1][j] + hs[SB][1][j]; sxy[j] = 2 * hs[SM][2][j] + hs[SB][2][j]; }
+                } else if (rb == rows - 1) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { sx[j] = 2 * hs[SM][0][j] + hs[ST][0][j]; sy[j] = 2 * hs[SM][1][j] + hs[ST][1][j]; sxy[j] = 2 * hs[SM][2][j] + hs[ST][2][j]; }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { sx[j] = hs[ST][0][j] + hs[SM][0][j] + hs[SB][0][j]; sy[j] = hs[ST][1][j] + hs[SM][1][j] + hs[SB][1][j]; sxy[j] = hs[ST][2][j] + hs[SM][2][j] + hs[SB][2][j]; }
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const long long det_i = (long long)sx[j] * sy[j] - (long long)sxy[j] * sxy[j];   // exact; == double det2
+                    const float det = __ll2float_rn(det_i);
+                    const float tr = __fsub_rn(__int_as_float(0x4B000000 | (sx[j] + sy[j])), 8388608.0f);   // exact int -> float
+                    const float r = __fsub_rn(det, __fmul_rn(a.k, __fmul_rn(tr, tr)));                 // Harris_corners.cpp:57
+                    Rn[j] = inx[j] ? fmaxf(r, 0.f) : 0.f;                                               // :60-62
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) Rn[j] = 0.f;
             }
+            // ---- row P, horizontal part: window maxima of row rb -> ring slot (ph + 1) & 3 ---------------------------
+            {
+                const int S = (ph + 1) & 3;
+                const float l3 = __shfl_up_sync(FULL, Rn[3], 1);
+                if (P2 == 2) {
+                    const float l2 = __shfl_up_sync(FULL, Rn[2], 1), r0 = __shfl_down_sync(FULL, Rn[0], 1);
+                    const float q0 = fmaxf(l2, l3), q1 = fmaxf(l3, Rn[0]), q2 = fmaxf(Rn[0], Rn[1]), q3 = fmaxf(Rn[1], Rn[2]),
+                                q4 = fmaxf(Rn[2], Rn[3]), q5 = fmaxf(Rn[3], r0);
+                    hmax[S][0] = fmaxf(q0, q2); hmax[S][1] = fmaxf(q1, q3); hmax[S][2] = fmaxf(q2, q4); hmax[S][3] = fmaxf(q3, q5);
+                } else {
+                    hmax[S][0] = fmaxf(l3, Rn[0]); hmax[S][1] = fmaxf(Rn[0], Rn[1]); hmax[S][2] = fmaxf(Rn[1], Rn[2]);
+                    hmax[S][3] = fmaxf(Rn[2], Rn[3]);
+                }
+            }
+            // ---- row O, horizontal part: 8-bit response of row rb, its 3-wide maxima -> ring slot (ph + 1) & 3 ----------
+            int q8n[4], m2n[4];
+            const bool want8 = a.r8 || a.mask3;
+            if (want8) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) q8n[j] = r8_of(Rn[j]);
+                const int l = __shfl_up_sync(FULL, q8n[3], 1), r = __shfl_down_sync(FULL, q8n[0], 1);
+                m2n[0] = max(l, q8n[1]); m2n[1] = max(q8n[0], q8n[2]); m2n[2] = max(q8n[1], q8n[3]); m2n[3] = max(q8n[2], r);
+                const int S = (ph + 1) & 3;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) m3[S][j] = max(m2n[j], q8n[j]);
+            }
+            // ---- outputs of row yo = yr-4 ---------------------------------------------------------------------------
+            const int yo = yr - 4;
+            if (yo >= Y0 && yo < Y1) {
+                const size_t o = fpx + (size_t)yo * cols + c;
+                if (own && inx[0]) {
+                    if (a.response) {
+                        if (vec_out && inx[3]) *(float4 *)(a.response + o) = make_float4(Rp[0], Rp[1], Rp[2], Rp[3]);
+                        else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) if (inx[j]) a.response[o + j] = Rp[j];
+                        }
+                    }
+                    if (want8) {
+                        u32 w8 = 0, wm = 0;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            // centre-excluded 3x3 dilate of the 8-bit response, strict '>' (Harris_corners.cpp:76-79)
+                            const int d = max(max(m3[(ph + 3) & 3][j], m3[(ph + 1) & 3][j]), m2p[j]);
+                            w8 |= (u32)q8p[j] << (8 * j);
+                            wm |= (q8p[j] > d ? 255u : 0u) << (8 * j);
+                        }
+                        if (vec_out && inx[3]) {
+                            if (a.r8) *(u32 *)(a.r8 + o) = w8;
+                            if (a.mask3) *(u32 *)(a.mask3 + o) = wm;
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (inx[j]) {
+                                    if (a.r8) a.r8[o + j] = (u8)(w8 >> (8 * j));
+                                    if (a.mask3) a.mask3[o + j] = (u8)(wm >> (8 * j));
+                                }
+                        }
+                    }
+                }
+                // NMS2 (Harris_corners.cpp:94-118): R >= max of the half-open window, interior pixels, positive responses
+                if (a.want_corners) {
+                    bool cr[4];
+                    const bool rowok = yo >= P2 && yo < rows - P2;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        float m = fmaxf(hmax[(ph + 3) & 3][j], hmax[ph & 3][j]);                 // rows yo-1, yo
+                        if (P2 == 2) m = fmaxf(m, fmaxf(hmax[(ph + 2) & 3][j], hmax[(ph + 1) & 3][j]));   // rows yo-2, yo+1
+                        cr[j] = rowok && nmsx[j] && Rp[j] > 0.f && Rp[j] >= m;
+                    }
+                    if (cur + HS > H_CAP || ri == H_ROWS) flush();
+                    if (ri == 0) batch_y0 = yo;
+                    const unsigned b0 = __ballot_sync(FULL, cr[0]), b1 = __ballot_sync(FULL, cr[1]),
+                                   b2 = __ballot_sync(FULL, cr[2]), b3 = __ballot_sync(FULL, cr[3]);
+                    const int total = __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
+                    if (total) {
+                        const unsigned lt = (1u << lane) - 1u;
+                        int pos = cur + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (cr[j]) {
+                                vslam_corner k;
+                                k.row = yo; k.col = c + j; k.value = Rp[j];
+                                s_buf[warp][pos++] = k;
+                            }
+                    }
+                    if (lane == 0) { s_rowoff[warp][ri] = cur; s_rowcnt[warp][ri] = total; }
+                    cur += total;
+                    ++ri;
+                }
+            }
+            // the new row becomes the output row of the next step
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { Rp[j] = Rn[j]; if (want8) { q8p[j] = q8n[j]; m2p[j] = m2n[j]; } }
         }
     }
+    if (a.want_corners) flush();
 }
 
-void harris_grid(int rows, int cols, int *ntx, int *nty) { *ntx = (cols + TW - 1) / TW; *nty = (rows + TH - 1) / TH; }
+int harris_strips(int cols) { return (cols + HS - 1) / HS; }
 
-int launch_harris(vslam_ctx *ctx, const HarrisArgs &a) {
-    int ntx, nty;
-    harris_grid(a.rows, a.cols, &ntx, &nty);
+int launch_harris(vslam_ctx *ctx, HarrisArgs &a, int n_frames) {
+    if (n_frames <= 0 || n_frames > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "harris: %d frames per launch", n_frames);
+    a.n_strips = harris_strips(a.cols);
+    a.n_bands = (a.rows + HB - 1) / HB;
+    const dim3 grid((a.n_strips * a.n_bands + H_WARPS - 1) / H_WARPS, 1, n_frames);
     KernelSpan span(ctx, VSLAM_K_HARRIS);
-    harris_fused_k<<<dim3(ntx, nty), 256, 0, ctx->stream>>>(a);
+    if (a.nms2_pad == 2) harris_march_k<2><<<grid, 32 * H_WARPS, 0, ctx->stream>>>(a);
+    else harris_march_k<1><<<grid, 32 * H_WARPS, 0, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

@@ -18,7 +18,7 @@ __device__ __forceinline__ void up_coef(int d, int &s, int &c0, int &c1) {
     c0 = 2048 - c1;
 }
 
-__global__ void __launch_bounds__(256) upsample2x_k(const u8 *__restrict__ src, int rows, int cols, size_t sp, size_t sstride,
+__global__ void __launch_bounds__(256) upsample2x_generic_k(const u8 *__restrict__ src, int rows, int cols, size_t sp, size_t sstride,
                                                     u8 *__restrict__ dst, size_t dp, size_t dstride) {
     src += (size_t)blockIdx.z * sstride;
     dst += (size_t)blockIdx.z * dstride;
@@ -49,11 +49,68 @@ __global__ void __launch_bounds__(256) upsample2x_k(const u8 *__restrict__ src, 
     else for (int i = 0; x4 + i < dcols; ++i) o[i] = (u8)(packed >> (8 * i));
 }
 
+// Fast path (cols % 4 == 0, 4-byte aligned rows): a thread owns 4 source columns = 8 output columns and marches down
+// UP_ROWS source rows.  With q = 3*near + far (the horizontal pass, 512*q == the 11-bit fixed-point row sum, so
+// (row sum >> 4) == 32*q exactly), an output pixel is ((3*q_near_row >> 2) + (q_far_row >> 2) + 2) >> 2: the two
+// separately truncated vertical products of OpenCV.  Everything is evaluated on 16x2 packed halves; border clamps of
+// the coefficients are index clamps here (3*p + p == 4*p).
+constexpr int UP_ROWS = 16;
+
+__device__ __forceinline__ void up_q(const u8 *__restrict__ row, int x4, int cols, u32 (&f1)[4], u32 (&f3)[4]) {
+    const u32 w = *(const u32 *)(row + x4);
+    const u32 pm = row[max(x4 - 1, 0)], pp = row[min(x4 + 4, cols - 1)];
+    const u32 q0 = 3 * __byte_perm(w, pm, 0x5050) + __byte_perm(w, pm, 0x5154);    // (pm + 3 p0, 3 p0 + p1)
+    const u32 q1 = 3 * __byte_perm(w, pm, 0x5151) + __byte_perm(w, pm, 0x5250);    // (p0 + 3 p1, 3 p1 + p2)
+    const u32 q2 = 3 * __byte_perm(w, pm, 0x5252) + __byte_perm(w, pm, 0x5351);    // (p1 + 3 p2, 3 p2 + p3)
+    const u32 q3 = 3 * __byte_perm(w, pm, 0x5353) + __byte_perm(w, pp, 0x5452);    // (p2 + 3 p3, 3 p3 + pp)
+    const u32 q[4] = {q0, q1, q2, q3};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        f1[i] = (q[i] >> 2) & 0x3fff3fffu;              // floor(q / 4)      <- coefficient 512
+        f3[i] = ((3 * q[i]) >> 2) & 0x3fff3fffu;        // floor(3 q / 4)    <- coefficient 1536
+    }
+}
+
+__device__ __forceinline__ void up_store(u8 *__restrict__ o, const u32 (&near3)[4], const u32 (&far1)[4]) {
+    u32 v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = ((near3[i] + far1[i] + 0x00020002u) >> 2) & 0x00ff00ffu;
+    uint2 r;
+    r.x = __byte_perm(v[0], v[1], 0x6420);
+    r.y = __byte_perm(v[2], v[3], 0x6420);
+    *(uint2 *)o = r;
+}
+
+__global__ void __launch_bounds__(128) upsample2x_k(const u8 *__restrict__ src, int rows, int cols, size_t sp, size_t sstride,
+                                                    u8 *__restrict__ dst, size_t dp, size_t dstride) {
+    src += (size_t)blockIdx.z * sstride;
+    dst += (size_t)blockIdx.z * dstride;
+    const int x4 = (blockIdx.x * 128 + threadIdx.x) * 4;
+    if (x4 >= cols) return;
+    const int k0 = blockIdx.y * UP_ROWS, k1 = min(k0 + UP_ROWS, rows);
+    u32 p1[4], p3[4], c1[4], c3[4], n1[4], n3[4];       // rows k-1, k, k+1
+    up_q(src + (size_t)max(k0 - 1, 0) * sp, x4, cols, p1, p3);
+    up_q(src + (size_t)k0 * sp, x4, cols, c1, c3);
+    for (int k = k0; k < k1; ++k) {
+        up_q(src + (size_t)min(k + 1, rows - 1) * sp, x4, cols, n1, n3);
+        u8 *o = dst + (size_t)(2 * k) * dp + 2 * x4;
+        up_store(o, c3, p1);                             // output row 2k:   rows (k-1, k) with coefficients (512, 1536)
+        up_store(o + dp, c3, n1);                        // output row 2k+1: rows (k, k+1) with coefficients (1536, 512)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { p1[i] = c1[i]; p3[i] = c3[i]; c1[i] = n1[i]; c3[i] = n3[i]; }
+    }
+}
+
 int launch_upsample2x(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t sp, size_t sstride, u8 *dst, size_t dp,
                       size_t dstride, int n_frames) {
-    dim3 b(64, 4), g((2 * cols + 255) / 256, (2 * rows + 3) / 4, n_frames);
     KernelSpan span(ctx, VSLAM_K_UPSAMPLE);
-    upsample2x_k<<<g, b, 0, ctx->stream>>>(src, rows, cols, sp, sstride, dst, dp, dstride);
+    if (!(cols & 3) && !(sp & 3) && !(sstride & 3) && !((uintptr_t)src & 3) && !(dp & 7) && !(dstride & 7) && !((uintptr_t)dst & 7)) {
+        dim3 g((cols / 4 + 127) / 128, (rows + UP_ROWS - 1) / UP_ROWS, n_frames);
+        upsample2x_k<<<g, 128, 0, ctx->stream>>>(src, rows, cols, sp, sstride, dst, dp, dstride);
+    } else {
+        dim3 b(64, 4), g((2 * cols + 255) / 256, (2 * rows + 3) / 4, n_frames);
+        upsample2x_generic_k<<<g, b, 0, ctx->stream>>>(src, rows, cols, sp, sstride, dst, dp, dstride);
+    }
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

@@ -234,11 +234,82 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
     for (int i = threadIdx.x; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
     if (threadIdx.x == 0) s_nq = 0;
 
+    constexpr int NS = FWO / 3;                                               // 20 sample columns per strip
+    constexpr int LS = FW * FTR;                                              // bytes between tiles
+    // computeEdgeResponse + threshold on the G tile of `level` around sample (xc, yc); yb = first row of the tiles' step
+    auto edge_pass = [&](int level, int xc, int yc, int yb) -> bool {
+        const u8 *g = gt + ((level - 1) * FW + (xc - X0c)) * FTR + (yc - yb + 4);
+        int ix2 = 0, iy2 = 0, ixy = 0;
+#pragma unroll
+        for (int u = 0; u <= 1; ++u)
+#pragma unroll
+            for (int v = 0; v <= 1; ++v) {
+                // reflect-101 of an index at most one outside [0, len): a single bounce (len == 1 -> 0)
+                const int xx = xc + v, yy = yc + u;
+                const int xr = (xx + 1 < cols ? xx + 1 : max(cols - 2, 0)) - xc, xl = (xx > 0 ? xx - 1 : min(1, cols - 1)) - xc;
+                const int yd = (yy + 1 < rows ? yy + 1 : max(rows - 2, 0)) - yc, yu = (yy > 0 ? yy - 1 : min(1, rows - 1)) - yc;
+                const int gxv = (int)g[xr * FTR + u] - (int)g[xl * FTR + u];
+                const int gyv = (int)g[v * FTR + yd] - (int)g[v * FTR + yu];
+                ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
+            }
+        return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // Diff_of_Gauss.cpp:336
+    };
+    // queued samples of the step whose tiles start at row yb: FeaturePointLocalization's full sequence, all lanes busy
+    auto run_queue = [&](int yb, int si_lo) {
+        const int nq = s_nq;
+        for (int i = tid; i < nq; i += NT) {
+            const int s = s_queue[i];
+            const int k = s % NS, t = s / NS;
+            const int level = 1 + t % 3, sr = t / 3;
+            const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
+            const u8 *p = dt + (level * FW + (xc - X0c)) * FTR + (yc - yb + 4);
+            const int oxm = xc > 0 ? -FTR : 0, oym = yc > 0 ? -1 : 0;
+            const int oxp = xc + 1 < cols ? FTR : 0, oyp = yc + 1 < rows ? 1 : 0;
+            const int c = p[0];
+            const int dx = (int)p[oxm] - (int)p[oxp], dy = (int)p[oym] - (int)p[oyp], ds = (int)p[-LS] - (int)p[LS];
+            const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
+            if (zhat > a.contrast_thr && edge_pass(level, xc, yc, yb))               // :245
+                s_res[s] = (int)__fmul_rn(zhat, 255.0f);                             // :246
+        }
+    };
+    // ordered emission: one warp per segment (level, sample row, strip) of a finished step
+    auto emit = [&](int si_lo, int n_srow) {
+        for (int task = warp; task < 3 * n_srow; task += NW) {
+            const int res = lane < NS ? s_res[task * NS + lane] : -1;
+            const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
+            if (bal) {
+                const int level = 1 + task % 3, si = si_lo + task / 3;
+                const int cnt = __popc(bal);
+                const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
+                int off = 0;
+                if (lane == 0) {
+                    off = atomicAdd(a.cursor, cnt);
+                    a.seg_off[sg] = off;
+                    a.seg_cnt[sg] = cnt;
+                }
+                off = __shfl_sync(0xffffffffu, off, 0);
+                if (res >= 0) {
+                    const int pos = off + __popc(bal & ((1u << lane) - 1u));
+                    if (pos < a.staging_cap) {
+                        vslam_keypoint kp;
+                        kp.row = 3 * si + 1; kp.col = X0 + 3 * lane + 1; kp.value = res; kp.padding = 1; kp.octave = a.octave;
+                        kp.level = level;
+                        a.staging[pos] = kp;
+                    }
+                }
+            }
+        }
+    };
+
+    // Per step three barriers.  Small jobs of the PREVIOUS step ride along with the two blur passes:
+    //   P1 (after B1)  H pass of step c            + queued localisations of step c-1 (its tiles are still intact)
+    //   P2 (after B2)  V pass of step c -> tiles   + ordered emission of step c-1, prefetch of step c+1's base rows
+    //   P3 (after B3)  detector tests of step c, decimated level 3 -> next base, slide of the h buffers
+    int p_y0 = 0, p_si_lo = 0, p_nsrow = 0;                                   // the previous step's detector state
     for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
         const bool do_v = y0 >= yv;
-        // ---- 1. the staged rows of this step have landed ------------------------------------------------------
         asm volatile("cp.async.wait_all;" ::: "memory");
-        __syncthreads();
+        __syncthreads();                                                      // B1: staged rows landed; P3 of c-1 done
         // ---- 2. H pass: rows y0 + r_l .. y0 + r_l + 31 of every level -> pairs r_l .. r_l + 15 ----------------
         for (int t = tid; t < 6 * 64; t += NT) {
             const int l = hperm<NT>(t >> 6);
@@ -270,7 +341,8 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
                 o[g] = v;
             }
         }
-        __syncthreads();
+        if (p_nsrow) run_queue(p_y0, p_si_lo);
+        __syncthreads();                                                      // B2
         if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
         // ---- 3. V pass + rounding + DoG -> tiles (column-major: tile k, column x, rows contiguous) -------------
         if (do_v) {
@@ -295,6 +367,7 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
                 const int wofs = 1 + rg * (RB / 4);
                 if (l >= 1 && l <= 3) {
                     u32 *g = tiles32 + ((l - 1) * FW + x) * FTW + wofs;
+                    if (rg == RG - 1) g[-wofs] = g[FTW - 1 - wofs];       // the last 4 rows become the next step's history
 #pragma unroll
                     for (int k = 0; k < RB / 4; ++k) g[k] = __byte_perm(cur[2 * k], cur[2 * k + 1], 0x6420);
                 }
@@ -303,6 +376,7 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
                 for (int q = 0; q < RB / 2; ++q) dg[q] = __vmaxu2(cur[q], prev[q]) - prev[q];   // max(cur - prev, 0)
                 if (l >= 1) {
                     u32 *d = tiles32 + ((F_NG + l - 1) * FW + x) * FTW + wofs;
+                    if (rg == RG - 1) d[-wofs] = d[FTW - 1 - wofs];
 #pragma unroll
                     for (int k = 0; k < RB / 4; ++k) d[k] = __byte_perm(dg[2 * k], dg[2 * k + 1], 0x6420);
                 }
@@ -322,67 +396,55 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
                 for (int q = 0; q < RB / 2; ++q) prev[q] = cur[q];
             }
         }
-        __syncthreads();
-        // ---- 4a. detector, test: every thread takes samples of the flattened (sample row, level, column) list ------
-        // Result per sample in s_res: the keypoint's value, or -1.  Samples whose three derivatives are all non-zero need
-        // the full 3x3 inverse (rare): they are queued and evaluated densely in step 5a.  Emission follows in step 5b.
+        if (p_nsrow) emit(p_si_lo, p_nsrow);
+        if (tid == 0) s_nq = 0;
+        __syncthreads();                                                      // B3
+        // ---- 4a. detector, test.  Thread = (sample column, level), marching over the step's sample rows.  Result per
+        // sample in s_res: the keypoint's value, or -1; samples whose three derivatives are all non-zero need the full
+        // 3x3 inverse (rare) and are queued for P1 of the next step.
         const bool own_step = do_v && y0 >= ys;
         int si_lo = 0, n_srow = 0;
-        constexpr int NS = FWO / 3;                                           // 20 sample columns per strip
-        constexpr int LS = FW * FTR;                                          // bytes between tiles
-        // computeEdgeResponse + threshold on the G tile of `level` around sample (xc, yc)
-        auto edge_pass = [&](int level, int xc, int yc) -> bool {
-            const u8 *g = gt + ((level - 1) * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
-            int ix2 = 0, iy2 = 0, ixy = 0;
-#pragma unroll
-            for (int u = 0; u <= 1; ++u)
-#pragma unroll
-                for (int v = 0; v <= 1; ++v) {
-                    // reflect-101 of an index at most one outside [0, len): a single bounce (len == 1 -> 0)
-                    const int xx = xc + v, yy = yc + u;
-                    const int xr = (xx + 1 < cols ? xx + 1 : max(cols - 2, 0)) - xc, xl = (xx > 0 ? xx - 1 : min(1, cols - 1)) - xc;
-                    const int yd = (yy + 1 < rows ? yy + 1 : max(rows - 2, 0)) - yc, yu = (yy > 0 ? yy - 1 : min(1, rows - 1)) - yc;
-                    const int gxv = (int)g[xr * FTR + u] - (int)g[xl * FTR + u];
-                    const int gyv = (int)g[v * FTR + yd] - (int)g[v * FTR + yu];
-                    ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
-                }
-            return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // Diff_of_Gauss.cpp:336
-        };
         if (own_step && a.detect) {
             const int yc_lo = y0 == 0 ? 0 : y0 - 2;
             const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;   // centre row yc needs rows up to yc + 2
             si_lo = (yc_lo + 2) / 3;
             n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
             if (n_srow < 0) n_srow = 0;
-            const int total = n_srow * 3 * NS;
-            for (int s = tid; s < total; s += NT) {
-                const int k = s % NS, t = s / NS;
-                const int level = 1 + t % 3, sr = t / 3;
-                const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
-                int res = -1;
-                if (xc <= cols - 2) {
-                    // D tile of DoG `level` at (xc, yc); neighbours at constant strides, clamped at the image border
-                    const u8 *p = dt + (level * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
-                    const int oxm = xc > 0 ? -FTR : 0, oym = yc > 0 ? -1 : 0;
-                    const int oxp = xc + 1 < cols ? FTR : 0, oyp = yc + 1 < rows ? 1 : 0;
-                    const int c = p[0];
-                    const int a0 = p[oxm + oym], a1 = p[oym], a2 = p[oxm];                    // level
-                    const int b0 = p[-LS + oxm + oym], b1 = p[-LS + oym], b2 = p[-LS + oxm], b3 = p[-LS];   // level - 1
-                    const int c0 = p[LS + oxm + oym], c1 = p[LS + oym], c2 = p[LS + oxm], c3 = p[LS];       // level + 1
-                    const int mn = min(min(min(a0, a1), min(a2, c)), min(min(min(b0, b1), min(b2, b3)), min(min(c0, c1), min(c2, c3))));
-                    const int mx = max(max(max(a0, a1), max(a2, c)), max(max(max(b0, b1), max(b2, b3)), max(max(c0, c1), max(c2, c3))));
-                    if (c == mn || c == mx) {                                            // Diff_of_Gauss.cpp:287
-                        const int dx = a2 - (int)p[oxp], dy = a1 - (int)p[oyp], ds = b3 - c3;   // :226-228
-                        if (dx == 0 || dy == 0 || ds == 0) {
-                            // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the host
-                            // with the same float ops: a.cmin, a.val_lut)
-                            if (c >= a.cmin && edge_pass(level, xc, yc)) res = a.val_lut[c];
-                        } else {
-                            s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)s;
+            constexpr int NG = NT / (3 * NS);                                 // sample-row groups
+            if (tid < NG * 3 * NS) {
+                const int id = tid % (3 * NS), grp = tid / (3 * NS);
+                const int k = id % NS, level = 1 + id / NS;
+                const int xc = X0 + 3 * k;
+                const bool colok = xc <= cols - 2;
+                const int oxm = xc > 0 ? -FTR : 0, oxp = xc + 1 < cols ? FTR : 0;
+                const u8 *pc = dt + (level * FW + (xc - X0c)) * FTR + 4 - y0;
+                for (int sr = grp; sr < n_srow; sr += NG) {
+                    const int yc = 3 * (si_lo + sr);
+                    const int s = (sr * 3 + level - 1) * NS + k;
+                    int res = -1;
+                    if (colok) {
+                        // D tile of DoG `level` at (xc, yc); neighbours at constant strides, clamped at the image border
+                        const u8 *p = pc + yc;
+                        const int oym = yc > 0 ? -1 : 0, oyp = yc + 1 < rows ? 1 : 0;
+                        const int c = p[0];
+                        const int a0 = p[oxm + oym], a1 = p[oym], a2 = p[oxm];                    // level
+                        const int b0 = p[-LS + oxm + oym], b1 = p[-LS + oym], b2 = p[-LS + oxm], b3 = p[-LS];   // level - 1
+                        const int c0 = p[LS + oxm + oym], c1 = p[LS + oym], c2 = p[LS + oxm], c3 = p[LS];       // level + 1
+                        const int mn = min(min(min(a0, a1), min(a2, c)), min(min(min(b0, b1), min(b2, b3)), min(min(c0, c1), min(c2, c3))));
+                        const int mx = max(max(max(a0, a1), max(a2, c)), max(max(max(b0, b1), max(b2, b3)), max(max(c0, c1), max(c2, c3))));
+                        if (c == mn || c == mx) {                                            // Diff_of_Gauss.cpp:287
+                            const int dx = a2 - (int)p[oxp], dy = a1 - (int)p[oyp], ds = b3 - c3;   // :226-228
+                            if (dx == 0 || dy == 0 || ds == 0) {
+                                // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the
+                                // host with the same float ops: a.cmin, a.val_lut)
+                                if (c >= a.cmin && edge_pass(level, xc, yc, y0)) res = a.val_lut[c];
+                            } else {
+                                s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)s;
+                            }
                         }
                     }
+                    s_res[s] = res;
                 }
-                s_res[s] = res;
             }
         }
         // ---- 4b. next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126) ------------------
@@ -412,55 +474,14 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
                     if (i + k < lv.r) p[(i + k) * (FW / 4)] = v[k];
             }
         }
+        p_y0 = y0; p_si_lo = si_lo; p_nsrow = n_srow;
+    }
+    // drain: the last step's queue and emission
+    __syncthreads();
+    if (p_nsrow) {
+        run_queue(p_y0, p_si_lo);
         __syncthreads();
-        // ---- 5a. queued samples: FeaturePointLocalization's full sequence, all lanes busy -------------------------
-        {
-            const int nq = s_nq;
-            for (int i = tid; i < nq; i += NT) {
-                const int s = s_queue[i];
-                const int k = s % NS, t = s / NS;
-                const int level = 1 + t % 3, sr = t / 3;
-                const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
-                const u8 *p = dt + (level * FW + (xc - X0c)) * FTR + (yc - y0 + 4);
-                const int oxm = xc > 0 ? -FTR : 0, oym = yc > 0 ? -1 : 0;
-                const int oxp = xc + 1 < cols ? FTR : 0, oyp = yc + 1 < rows ? 1 : 0;
-                const int c = p[0];
-                const int dx = (int)p[oxm] - (int)p[oxp], dy = (int)p[oym] - (int)p[oyp], ds = (int)p[-LS] - (int)p[LS];
-                const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
-                if (zhat > a.contrast_thr && edge_pass(level, xc, yc))                   // :245
-                    s_res[s] = (int)__fmul_rn(zhat, 255.0f);                             // :246
-            }
-            __syncthreads();
-            if (tid == 0) s_nq = 0;
-        }
-        // ---- 5b. tiles: the last 4 rows become the next step's history; ordered emission of the step's keypoints ---
-        if (do_v)
-            for (int t = tid; t < (F_NG + F_ND) * FW; t += NT) tiles32[t * FTW] = tiles32[t * FTW + FTW - 1];
-        for (int task = warp; task < 3 * n_srow; task += NW) {       // one warp per segment (level, sample row, strip)
-            const int res = lane < NS ? s_res[task * NS + lane] : -1;
-            const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
-            if (bal) {
-                const int level = 1 + task % 3, si = si_lo + task / 3;
-                const int cnt = __popc(bal);
-                const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
-                int off = 0;
-                if (lane == 0) {
-                    off = atomicAdd(a.cursor, cnt);
-                    a.seg_off[sg] = off;
-                    a.seg_cnt[sg] = cnt;
-                }
-                off = __shfl_sync(0xffffffffu, off, 0);
-                if (res >= 0) {
-                    const int pos = off + __popc(bal & ((1u << lane) - 1u));
-                    if (pos < a.staging_cap) {
-                        vslam_keypoint kp;
-                        kp.row = 3 * si + 1; kp.col = X0 + 3 * lane + 1; kp.value = res; kp.padding = 1; kp.octave = a.octave;
-                        kp.level = level;
-                        a.staging[pos] = kp;
-                    }
-                }
-            }
-        }
+        emit(p_si_lo, p_nsrow);
     }
 }
 

@@ -547,7 +547,9 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
             a.ni = ni[o]; a.nj = nj[o]; a.seg_base = seg_base[o]; a.segs_per_frame = (int)spf;
             a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
             a.cursor = cnt; a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = ctx->staging_entries;
-            VS_TRY(launch_octave_fused(ctx, a, nf));
+            const int rc = launch_octave_mma(ctx, a, nf, ctx->taps_sigma0, ctx->taps_scale_samples);   // tensor-pipe blur
+            if (rc < 0) return rc;
+            if (rc == 1) VS_TRY(launch_octave_fused(ctx, a, nf));                                         // dp4a/dp2a blur
         }
         VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf));
     }

@@ -27,8 +27,7 @@ struct FusedTaps {
 };
 
 // Launch description.  All planes of one octave share `pitch`; frame f's plane is at ptr + f * frame_stride.
-struct FusedArgs {
-    FusedTaps taps;
+struct OctaveIO {
     const u8 *base;                 // octave input
     size_t base_pitch, base_stride;
     int rows, cols, octave;
@@ -54,6 +53,9 @@ struct FusedArgs {
     vslam_keypoint *staging;
     int staging_cap;
 };
+struct FusedArgs : OctaveIO {
+    FusedTaps taps;
+};
 
 // geometry shared by host and device
 constexpr int kFusedW = 64;         // columns a CTA computes
@@ -65,5 +67,8 @@ size_t fused_smem_bytes(const FusedTaps &t);
 int fused_strips(int cols);
 // Launch one octave for n_frames frames.  The kernel is chosen by the shared-memory footprint of the octave.
 int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames);
+// Tensor-pipe variant (fused_mma.cu): same results; used for keypoints-only launches whose tap tables fit.
+// Returns 1 when the launch was not taken (caller falls back to launch_octave_fused), 0 on success, < 0 on error.
+int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
 
 }  // namespace vslam

@@ -1,0 +1,506 @@
+// fused_mma.cu -- the fused octave kernel with both blur passes on the integer tensor pipe (IMMA.16832.U8.U8).
+//
+// Same rows of SURVEY.md 8(a) as fused.cu (B, C, D, G, H, I, J) and the same marching scheme; what changes is how the
+// 1738 MAC per input pixel of the Gaussian stack are issued.  OpenCV's 8U GaussianBlur is exact integer arithmetic
+// (u8 pixels x 8-bit taps -> 8.8 sums, 8.8 sums x 8-bit taps -> 16.16 sums), so each pass is a product with a banded
+// Toeplitz matrix of taps that mma.sync.m16n8k32 (u8 x u8 -> s32) evaluates exactly -- bit-identical to the dp4a/dp2a
+// kernel and to OpenCV, at 569 TMAC/s instead of 74 / 37 TMAC/s (profiles/imma_peak_r1.json vs alu_peak_r1.json).
+//
+//   H pass   D[16 rows x 8 cols] = Img[16 rows x 32 staged cols] * T[32 x 8],  T[k][n] = tap[col_k - (col_n - r)]
+//            The image fragment of a 32-byte chunk is two LDS.64 per row pair and is shared by every 8-column block
+//            whose band touches the chunk.  Two M blocks give a thread four consecutive rows of two columns, which it
+//            stores as one 16-byte word {lo bytes, hi bytes} x 2 columns of the row quad (the "h plane").
+//   V pass   D[16 cols x 8 rows] = H^T[16 cols x 32 rows] * T'[32 x 8], once for the low and once for the high bytes
+//            of the 8.8 sums (out = (256 * hi + lo + 32768) >> 16).  The h plane is a ring of row quads per level, so
+//            the A fragment is two LDS.128 per K step; the B fragment (taps) is one pair of words per level and K step.
+//            Epilogue in registers: rounding, saturating DoG against the previous level, 2x2 packed tile words.
+//   The detector, localisation, edge test, ordered emission and decimation are those of fused.cu on the new tile layout.
+//
+// Tensor cores on a "stencil": the north star expected these kernels to be memory bound; the survey showed the Gaussian
+// stack is ALU bound by a factor of ~50.  The MMA form removes that bound without touching exactness.
+#include <math.h>
+#include <string.h>
+
+#include "detect_math.cuh"
+#include "fused_mma.cuh"
+
+namespace vslam {
+
+namespace {
+constexpr int FW = kFusedW, FWO = kFusedWO, FR = kFusedR;
+constexpr int PPW = 4 * (FW / 2) + 8;       // words per quad PAIR of an h plane: 32 column pairs x 16 bytes, + 8 (== 8 mod 32: conflict-free LDS.128)
+constexpr int TRP = 20;                     // words per column pair of a tile: 2 history + 16 row pairs (+2: conflict-free STS)
+constexpr int TILE_W = (FW / 2) * TRP;      // words per tile
+constexpr int N_G = 3, N_D = 5;             // G tiles: Gaussian levels 1..3; D tiles: DoG levels 0..4
+constexpr int NS = FWO / 3;                 // 20 sample columns per strip
+constexpr int MAX_SROW = FR / 3 + 2;
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+// host: tables
+// ---------------------------------------------------------------------------------------------------------------
+int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
+    memset(out, 0, sizeof *out);
+    int32_t t[kMaxKsize];
+    const double k = pow(2.0, 1.0 / (double)scale_samples);          // GaussPyramid.hpp:69
+    int rmin = 1 << 30, rmax = 0, poff = 0, toff = 0;
+    for (int l = 0; l < 6; ++l) {
+        const double sig = pow(2, octave) * sigma0 * pow(k, l);      // GaussPyramid.cpp:157
+        const int n = host_gauss_ksize(sig);
+        if (n > 247) return VSLAM_E_INVALID;
+        int rc = host_gauss_taps(sig, n, t);
+        if (rc) return rc;
+        MmaLevel &lv = out->lv[l];
+        lv.n = n; lv.r = n / 2;
+        for (int i = 0; i < n; ++i) {
+            if (t[i] < 0 || t[i] > 255) return VSLAM_E_INVALID;
+            out->taps[l][i] = (u8)t[i];
+        }
+        lv.sv = (4 - (2 * lv.r) % 4) % 4;
+        lv.ksv = (n + 7 + lv.sv + 31) / 32;
+        lv.cq = (2 * lv.r + lv.sv) / 4;
+        lv.np = (lv.cq + 8 + 2) / 2;                                 // quads Q = q + cq of a step: 8i .. 8i + 7 + cq
+        if (lv.np < 8) lv.np = 8;                                    // single-step wrap of every slot computation (needs >= 6)
+        lv.plane_off = poff;
+        poff += 2 * lv.np * PPW;
+        lv.tab_off = toff;
+        lv.tab_cp = (kMmaPadL + 32 * lv.ksv + 48 + 3) & ~3;          // V pass reads up to idx 32 ksv + 31; H pass up to n + 37
+        if (lv.tab_cp < ((kMmaPadL + n + kMmaPadR + 3) & ~3)) lv.tab_cp = (kMmaPadL + n + kMmaPadR + 3) & ~3;
+        lv.tab_cp += 32;                                             // copies 32 bytes apart modulo 128: fewer bank conflicts
+        toff += 4 * lv.tab_cp;
+        if (lv.r < rmin) rmin = lv.r;
+        if (lv.r > rmax) rmax = lv.r;
+    }
+    out->rmin = rmin; out->rmax = rmax;
+    out->stage_rows = FR + rmax - rmin;
+    out->stage_pitch = (2 * rmax + 15 + FW + 127) / 128 * 128;       // left halo rmax (+ up to 15 alignment), 64 columns, right halo
+    out->plane_words = poff;
+    out->tab_bytes = (toff + 15) & ~15;
+    return VSLAM_OK;
+}
+
+size_t mma_smem_bytes(const MmaTaps &t) {
+    return (size_t)t.plane_words * 4 + (size_t)t.stage_rows * t.stage_pitch + (size_t)(N_G + N_D) * TILE_W * 4 + (size_t)t.tab_bytes;
+}
+
+int mma_strips(int cols) { return (cols + FWO - 1) / FWO; }
+
+// ---------------------------------------------------------------------------------------------------------------
+// device
+// ---------------------------------------------------------------------------------------------------------------
+struct MmaArgs : OctaveIO {
+    MmaTaps mt;
+};
+
+namespace {
+
+__device__ __forceinline__ void imma(int (&d)[4], u32 a0, u32 a1, u32 a2, u32 a3, u32 b0, u32 b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// byte offset of pixel (x, ty) inside a tile: words of 2 x 2 pixels [x even/odd][row even/odd], column pairs TRP words apart
+__device__ __forceinline__ int tcol(int x) { return (x >> 1) * (TRP * 4) + ((x & 1) << 1); }
+__device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1); }
+
+}  // namespace
+
+template <int NT>
+__global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaArgs a) {
+    extern __shared__ __align__(16) u32 smem[];
+    constexpr int NW = NT / 32;
+    constexpr int RBW = 16 / NW;                // 8-row blocks of one 16-column block a warp owns in the V pass
+    const MmaTaps &T = a.mt;
+    u32 *planes = smem;
+    u8 *stage = (u8 *)(smem + T.plane_words);
+    const int SP = T.stage_pitch;
+    u32 *tiles32 = (u32 *)(stage + T.stage_rows * SP);
+    const u8 *tiles = (const u8 *)tiles32;
+    u8 *tab = (u8 *)(tiles32 + (N_G + N_D) * TILE_W);
+    __shared__ int s_res[3 * MAX_SROW * NS];                 // detector results of one step
+    __shared__ unsigned short s_queue[3 * MAX_SROW * NS];     // samples that need the full localisation
+    __shared__ int s_nq;
+    __shared__ int s_hb[6];                                   // ring slot of the step's first quad pair, per level
+    __shared__ float s_div[511];                              // float(i - 255) / 255f, the reference's divisions
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int strip = blockIdx.x, seg = blockIdx.y, frame = blockIdx.z;
+    const int rows = a.rows, cols = a.cols;
+    const int X0 = strip * FWO, X0c = X0 - 2, xs = X0c - T.rmax;
+    const int xs16 = xs & ~15;                   // staged rows start on a 16-byte boundary of the plane
+    const int cboff = X0c - xs16;                // staged column of the strip's first computed column
+    const u8 *__restrict__ base = a.base + (size_t)frame * a.base_stride;
+    const int ys = seg * a.seg_rows;
+    const int ye = min(ys + a.seg_rows, rows);
+    const int yv = seg > 0 ? ys - FR : 0;        // first step with a V pass (one extra step feeds the detector's history)
+    const int K = (2 * T.rmax + FR - 1) / FR;    // warm-up steps: H pass only
+
+    // ---- stage base rows y0 + rmin ..., columns xs16 ..., reflect-101 resolved (16-byte cp.async inside the image) ----
+    const int SPQ = SP >> 4, n_stage = T.stage_rows * SPQ;
+    auto issue_stage = [&](int y0n) {
+        for (int q = tid; q < n_stage; q += NT) {
+            const int row = q / SPQ, j = q - row * SPQ;
+            const int y = refl101(y0n + T.rmin + row, rows);
+            const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
+            u32 *dst = (u32 *)(stage + row * SP) + 4 * (j ^ ((row >> 2) & 7));   // 16-byte groups XOR-swizzled by the row quad
+            const int x = xs16 + 16 * j;
+            if (x >= 0 && x + 15 < cols) {
+                const u32 sa = (u32)__cvta_generic_to_shared(dst);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src + x) : "memory");
+            } else {
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const int xw = x + 4 * w;
+                    dst[w] = (u32)src[refl101(xw, cols)] | (u32)src[refl101(xw + 1, cols)] << 8 |
+                             (u32)src[refl101(xw + 2, cols)] << 16 | (u32)src[refl101(xw + 3, cols)] << 24;
+                }
+            }
+        }
+    };
+    issue_stage(yv - K * FR);
+    // ---- tables: four byte-shifted, zero-padded copies of every level's taps; the division table; ring bases ----
+    for (int l = 0; l < 6; ++l) {
+        const MmaLevel &lv = T.lv[l];
+        for (int s = 0; s < 4; ++s)
+            for (int j = tid; j < lv.tab_cp; j += NT) {
+                const int idx = j + s - kMmaPadL;
+                tab[lv.tab_off + s * lv.tab_cp + j] = (idx >= 0 && idx < lv.n) ? T.taps[l][idx] : (u8)0;
+            }
+    }
+    for (int i = tid; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
+    if (tid < 6) s_hb[tid] = 0;
+    if (tid == 0) s_nq = 0;
+
+    constexpr int DT0 = N_G * TILE_W * 4;                                     // byte offset of the first D tile
+    constexpr int LS = TILE_W * 4;                                            // bytes between tiles
+    // computeEdgeResponse + threshold on the G tile of `level` around sample (xc, yc); yb = first row of the tiles' step
+    auto edge_pass = [&](int level, int xc, int yc, int yb) -> bool {
+        const u8 *gt = tiles + (level - 1) * LS;
+        int ix2 = 0, iy2 = 0, ixy = 0;
+#pragma unroll
+        for (int u = 0; u <= 1; ++u)
+#pragma unroll
+            for (int v = 0; v <= 1; ++v) {
+                // reflect-101 of an index at most one outside [0, len): a single bounce (len == 1 -> 0)
+                const int xx = xc + v, yy = yc + u;
+                const int xr = (xx + 1 < cols ? xx + 1 : max(cols - 2, 0)), xl = (xx > 0 ? xx - 1 : min(1, cols - 1));
+                const int yd = (yy + 1 < rows ? yy + 1 : max(rows - 2, 0)), yu = (yy > 0 ? yy - 1 : min(1, rows - 1));
+                const int ty = trow(yy - yb + 4), tx = tcol(xx - X0c);
+                const int gxv = (int)gt[tcol(xr - X0c) + ty] - (int)gt[tcol(xl - X0c) + ty];
+                const int gyv = (int)gt[tx + trow(yd - yb + 4)] - (int)gt[tx + trow(yu - yb + 4)];
+                ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
+            }
+        return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // Diff_of_Gauss.cpp:336
+    };
+    // queued samples of the step whose tiles start at row yb: FeaturePointLocalization's full sequence, all lanes busy
+    auto run_queue = [&](int yb, int si_lo) {
+        const int nq = s_nq;
+        for (int i = tid; i < nq; i += NT) {
+            const int s = s_queue[i];
+            const int k = s % NS, tt = s / NS;
+            const int level = 1 + tt % 3, sr = tt / 3;
+            const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
+            const u8 *d = tiles + DT0 + level * LS;
+            const int x = xc - X0c, ty = yc - yb + 4;
+            const int cx = tcol(x), cy = trow(ty);
+            const int cxm = xc > 0 ? tcol(x - 1) : cx, cym = yc > 0 ? trow(ty - 1) : cy;
+            const int cxp = xc + 1 < cols ? tcol(x + 1) : cx, cyp = yc + 1 < rows ? trow(ty + 1) : cy;
+            const int c = d[cx + cy];
+            const int dx = (int)d[cxm + cy] - (int)d[cxp + cy], dy = (int)d[cx + cym] - (int)d[cx + cyp];
+            const int ds = (int)d[cx + cy - LS] - (int)d[cx + cy + LS];
+            const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
+            if (zhat > a.contrast_thr && edge_pass(level, xc, yc, yb))               // :245
+                s_res[s] = (int)__fmul_rn(zhat, 255.0f);                             // :246
+        }
+    };
+    // ordered emission: one warp per segment (level, sample row, strip) of a finished step
+    auto emit = [&](int si_lo, int n_srow) {
+        for (int task = warp; task < 3 * n_srow; task += NW) {
+            const int res = lane < NS ? s_res[task * NS + lane] : -1;
+            const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
+            if (bal) {
+                const int level = 1 + task % 3, si = si_lo + task / 3;
+                const int cnt = __popc(bal);
+                const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
+                int off = 0;
+                if (lane == 0) {
+                    off = atomicAdd(a.cursor, cnt);
+                    a.seg_off[sg] = off;
+                    a.seg_cnt[sg] = cnt;
+                }
+                off = __shfl_sync(0xffffffffu, off, 0);
+                if (res >= 0) {
+                    const int pos = off + __popc(bal & ((1u << lane) - 1u));
+                    if (pos < a.staging_cap) {
+                        vslam_keypoint kp;
+                        kp.row = 3 * si + 1; kp.col = X0 + 3 * lane + 1; kp.value = res; kp.padding = 1; kp.octave = a.octave;
+                        kp.level = level;
+                        a.staging[pos] = kp;
+                    }
+                }
+            }
+        }
+    };
+
+    // ---- lane constants of the two passes ----
+    // H pass, A fragment through ldmatrix.x4: lane L supplies the address of row (L & 7) of matrix (L >> 3); matrices 0/1
+    // are the M rows 0-7 / 8-15 of K bytes 0-15, matrices 2/3 the same rows of K bytes 16-31.  M row m <-> image row
+    // 4 pi(m & 7) + (m >> 3) (+2 for the second M block), so that a thread ends up with four consecutive rows of a quad.
+    const int h_pi = ((lane & 7) >> 1) + 4 * (lane & 1);                      // quad of the chunk this lane addresses
+    const int h_row = 4 * h_pi + ((lane >> 3) & 1);                           // image row inside the chunk, M block 0
+    const int h_kh = lane >> 4;                                               // K half
+    const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the chunk this thread's D rows belong to
+    const u32 stage_sa = (u32)__cvta_generic_to_shared(stage);
+    // Per step three barriers.  Small jobs of the PREVIOUS step ride along with the two blur passes:
+    //   P1 (after B1)  H pass of step c            + queued localisations of step c-1 (its tiles are still intact)
+    //   P2 (after B2)  V pass of step c -> tiles   + ordered emission of step c-1, prefetch of step c+1's base rows
+    //   P3 (after B3)  detector tests of step c, decimated level 3 -> next base, ring bases advance
+    int p_y0 = 0, p_si_lo = 0, p_nsrow = 0;                                   // the previous step's detector state
+    for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
+        const bool do_v = y0 >= yv;
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncthreads();                                                      // B1: staged rows landed; P3 of c-1 done
+        // ---- 2. H pass: rows y0 + r_l .. y0 + r_l + 31 of every level -> 8 quads of the level's ring ----
+        // unit = (level, 16 output columns); levels in descending cost so the warps' shares are similar
+        for (int u = warp; u < 24; u += NW) {
+            const int l = 5 - (u >> 2), cgp = u & 3;
+            const MmaLevel &lv = T.lv[l];
+            const int r = lv.r, n = lv.n;
+            if (y0 + FR <= yv - 2 * r) continue;                 // warm-up: this level's rows are not needed yet
+            const int cb0 = cboff + 16 * cgp;                    // staged column of the unit's first output column
+            const int c_lo = (cb0 - r) >> 5, c_hi = (cb0 + 15 + r) >> 5;
+            const int rowA = r - T.rmin + h_row, rowB = rowA + 2;
+            const u32 saA = stage_sa + rowA * SP, saB = stage_sa + rowB * SP;
+            const int keyA = (rowA >> 2) & 7, keyB = (rowB >> 2) & 7;
+            // B fragment of (chunk c, block bb): b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 ..,
+            // idx0 = r + 32 c - (cb0 + 8 bb) + 4 t - g
+            const int p0 = r - cb0 + 4 * t - g + kMmaPadL;
+            const u8 *tb = tab + lv.tab_off + (p0 & 3) * lv.tab_cp + (p0 - (p0 & 3));   // two's complement: fine for p0 < 0
+            int acc[2][2][4];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) (&acc[0][0][0])[i] = 0;
+            for (int c = c_lo; c <= c_hi; ++c) {
+                u32 a0[4], a1[4];
+                const int ch = 2 * c + h_kh;
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(a0[0]), "=r"(a0[1]), "=r"(a0[2]), "=r"(a0[3]) : "r"(saA + ((ch ^ keyA) << 4)));
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(a1[0]), "=r"(a1[1]), "=r"(a1[2]), "=r"(a1[3]) : "r"(saB + ((ch ^ keyB) << 4)));
+#pragma unroll
+                for (int bb = 0; bb < 2; ++bb) {
+                    const int bs = r + 32 * c - cb0 - 8 * bb;                 // tap index of (k = 0, n = 0): warp-uniform
+                    if (bs < -31 || bs > n + 6) continue;                     // the band misses this chunk
+                    const u32 b0 = *(const u32 *)(tb + 32 * c - 8 * bb), b1 = *(const u32 *)(tb + 32 * c - 8 * bb + 16);
+                    imma(acc[bb][0], a0[0], a0[1], a0[2], a0[3], b0, b1);
+                    imma(acc[bb][1], a1[0], a1[1], a1[2], a1[3], b0, b1);
+                }
+            }
+            // thread: rows 4 d_pi .. + 3 of columns 2t, 2t + 1 of each block -> low bytes {c0, c1} and high bytes {c0, c1}
+            // of one quad, in the pair-aligned planes (aligned quad Q = q + cq, pair Q >> 1, position Q & 1)
+            const int Q = d_pi + lv.cq;
+            int slot = s_hb[l] + (Q >> 1);
+            if (slot >= lv.np) slot -= lv.np;
+            u32 *plo = planes + lv.plane_off + slot * PPW + 4 * (8 * cgp + t) + 2 * (Q & 1);
+            u32 *phi = plo + lv.np * PPW;
+#pragma unroll
+            for (int bb = 0; bb < 2; ++bb) {
+                const u32 e01 = __byte_perm(acc[bb][0][0], acc[bb][0][2], 0x5410), e23 = __byte_perm(acc[bb][1][0], acc[bb][1][2], 0x5410);
+                const u32 o01 = __byte_perm(acc[bb][0][1], acc[bb][0][3], 0x5410), o23 = __byte_perm(acc[bb][1][1], acc[bb][1][3], 0x5410);
+                uint2 vl, vh;
+                vl.x = __byte_perm(e01, e23, 0x6420); vh.x = __byte_perm(e01, e23, 0x7531);
+                vl.y = __byte_perm(o01, o23, 0x6420); vh.y = __byte_perm(o01, o23, 0x7531);
+                *(uint2 *)(plo + 16 * bb) = vl;
+                *(uint2 *)(phi + 16 * bb) = vh;
+            }
+        }
+        if (p_nsrow) run_queue(p_y0, p_si_lo);
+        __syncthreads();                                                      // B2
+        if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
+        // ---- 3. V pass + rounding + DoG -> tiles.  warp = (16-column block, RBW blocks of 8 rows), levels in order ----
+        if (do_v) {
+            const int cb = warp % 4, jb = (warp / 4) * RBW;
+            u32 prev0[RBW], prev1[RBW];                          // previous level, columns 2g and 2g + 1, rows as 16-bit halves
+#pragma unroll
+            for (int rb = 0; rb < RBW; ++rb) prev0[rb] = prev1[rb] = 0;
+#pragma unroll 1
+            for (int l = 0; l < 6; ++l) {
+                const MmaLevel &lv = T.lv[l];
+                const u32 ring = (u32)lv.np * (PPW * 4), hi_off = ring;       // bytes of one plane
+                const int ksv = lv.ksv;
+                const u8 *plane = (const u8 *)(planes + lv.plane_off) + 16 * (8 * cb + g);
+                // pair of (row block j, K step k, lane t): 4i + j + 4k + t; slot = that modulo np
+                u32 off[RBW];
+                {
+                    int s0 = s_hb[l] + jb + t;
+                    if (s0 >= lv.np) s0 -= lv.np;
+#pragma unroll
+                    for (int rb = 0; rb < RBW; ++rb) {
+                        int s1 = s0 + rb;
+                        if (s1 >= lv.np) s1 -= lv.np;
+                        off[rb] = (u32)s1 * (PPW * 4);
+                    }
+                }
+                const int p0 = 8 * t - g + kMmaPadL - lv.sv;     // >= 40 - 7 - 3
+                const u8 *tb = tab + lv.tab_off + (p0 & 3) * lv.tab_cp + (p0 & ~3);
+                int lo[RBW][4], hi[RBW][4];
+#pragma unroll
+                for (int rb = 0; rb < RBW; ++rb)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { lo[rb][i] = 32768; hi[rb][i] = 0; }
+#pragma unroll 1
+                for (int k = 0; k < ksv; ++k) {
+                    const u32 b0 = *(const u32 *)(tb + 32 * k), b1 = *(const u32 *)(tb + 32 * k + 4);
+#pragma unroll
+                    for (int rb = 0; rb < RBW; ++rb) {
+                        const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + hi_off);
+                        imma(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1);
+                        imma(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1);
+                        const u32 nx = off[rb] + 4 * (PPW * 4);
+                        off[rb] = min(nx, nx - ring);            // wrap: nx - ring is huge (unsigned) unless nx >= ring
+                    }
+                }
+#pragma unroll
+                for (int rb = 0; rb < RBW; ++rb) {
+                    // (256 hi + lo + 32768) >> 16 lands in byte 2; rows 2t, 2t+1 of a column share a register as 16-bit halves
+                    const u32 v0 = (u32)(hi[rb][0] << 8) + (u32)lo[rb][0], v1 = (u32)(hi[rb][1] << 8) + (u32)lo[rb][1];
+                    const u32 v2 = (u32)(hi[rb][2] << 8) + (u32)lo[rb][2], v3 = (u32)(hi[rb][3] << 8) + (u32)lo[rb][3];
+                    const u32 c0 = __byte_perm(v0, v1, 0x7632), c1 = __byte_perm(v2, v3, 0x7632);
+                    const int wi = (8 * cb + g) * TRP + 2 + 4 * (jb + rb) + t;
+                    if (jb + rb == 3 && t >= 2 && l >= 1) {      // rows y0+28 .. y0+31 of the last step become the history
+                        if (l <= 3) tiles32[(l - 1) * TILE_W + wi - 16] = tiles32[(l - 1) * TILE_W + wi];
+                        tiles32[(N_G + l - 1) * TILE_W + wi - 16] = tiles32[(N_G + l - 1) * TILE_W + wi];
+                    }
+                    if (l >= 1 && l <= 3) tiles32[(l - 1) * TILE_W + wi] = __byte_perm(c0, c1, 0x6420);
+                    if (l >= 1) {
+                        const u32 d0 = __vmaxu2(c0, prev0[rb]) - prev0[rb], d1 = __vmaxu2(c1, prev1[rb]) - prev1[rb];   // max(cur - prev, 0)
+                        tiles32[(N_G + l - 1) * TILE_W + wi] = __byte_perm(d0, d1, 0x6420);
+                    }
+                    prev0[rb] = c0; prev1[rb] = c1;
+                }
+            }
+        }
+        if (p_nsrow) emit(p_si_lo, p_nsrow);
+        if (tid == 0) s_nq = 0;
+        __syncthreads();                                                      // B3
+        // ---- 4a. detector, test.  Thread = (sample column, level), marching over the step's sample rows.  Result per
+        // sample in s_res: the keypoint's value, or -1; samples whose three derivatives are all non-zero need the full
+        // 3x3 inverse (rare) and are queued for P1 of the next step.
+        const bool own_step = do_v && y0 >= ys;
+        int si_lo = 0, n_srow = 0;
+        if (own_step && a.detect) {
+            const int yc_lo = y0 == 0 ? 0 : y0 - 2;
+            const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;   // centre row yc needs rows up to yc + 2
+            si_lo = (yc_lo + 2) / 3;
+            n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
+            if (n_srow < 0) n_srow = 0;
+            constexpr int NG = NT / (3 * NS);                                 // sample-row groups
+            if (tid < NG * 3 * NS) {
+                const int id = tid % (3 * NS), grp = tid / (3 * NS);
+                const int k = id % NS, level = 1 + id / NS;
+                const int xc = X0 + 3 * k, x = xc - X0c;
+                const bool colok = xc <= cols - 2;
+                const int cx = tcol(x), cxm = xc > 0 ? tcol(x - 1) : cx, cxp = xc + 1 < cols ? tcol(x + 1) : cx;
+                const u8 *d = tiles + DT0 + level * LS;
+                for (int sr = grp; sr < n_srow; sr += NG) {
+                    const int yc = 3 * (si_lo + sr);
+                    const int s = (sr * 3 + level - 1) * NS + k;
+                    int res = -1;
+                    if (colok) {
+                        // D tile of DoG `level` at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
+                        const int ty = yc - y0 + 4;
+                        const int cy = trow(ty), cym = yc > 0 ? trow(ty - 1) : cy, cyp = yc + 1 < rows ? trow(ty + 1) : cy;
+                        const int c = d[cx + cy];
+                        const int a0 = d[cxm + cym], a1 = d[cx + cym], a2 = d[cxm + cy];                                  // level
+                        const int b0 = d[cxm + cym - LS], b1 = d[cx + cym - LS], b2 = d[cxm + cy - LS], b3 = d[cx + cy - LS];   // level - 1
+                        const int c0 = d[cxm + cym + LS], c1 = d[cx + cym + LS], c2 = d[cxm + cy + LS], c3 = d[cx + cy + LS];   // level + 1
+                        const int mn = min(min(min(a0, a1), min(a2, c)), min(min(min(b0, b1), min(b2, b3)), min(min(c0, c1), min(c2, c3))));
+                        const int mx = max(max(max(a0, a1), max(a2, c)), max(max(max(b0, b1), max(b2, b3)), max(max(c0, c1), max(c2, c3))));
+                        if (c == mn || c == mx) {                                            // Diff_of_Gauss.cpp:287
+                            const int dx = a2 - (int)d[cxp + cy], dy = a1 - (int)d[cx + cyp], ds = b3 - c3;   // :226-228
+                            if (dx == 0 || dy == 0 || ds == 0) {
+                                // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the
+                                // host with the same float ops: a.cmin, a.val_lut)
+                                if (c >= a.cmin && edge_pass(level, xc, yc, y0)) res = a.val_lut[c];
+                            } else {
+                                s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)s;
+                            }
+                        }
+                    }
+                    s_res[s] = res;
+                }
+            }
+        }
+        // ---- 4b. next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126) = byte 0 of the words ----
+        if (own_step && a.next_base) {
+            u8 *nb = a.next_base + (size_t)frame * a.next_stride;
+            for (int i = tid; i < (FWO / 2) * (FR / 2); i += NT) {
+                const int oc = i % (FWO / 2), w = i / (FWO / 2);
+                const int ox = X0 / 2 + oc, oy = (y0 >> 1) + w;
+                if (ox < a.next_cols && oy < a.next_rows)
+                    nb[(size_t)oy * a.next_pitch + ox] = (u8)tiles32[2 * TILE_W + (oc + 1) * TRP + 2 + w];
+            }
+        }
+        // ---- 4c. the rings advance by one chunk of 8 quads ----
+        if (tid < 6) {
+            int hb = s_hb[tid] + 4;
+            if (hb >= T.lv[tid].np) hb -= T.lv[tid].np;
+            s_hb[tid] = hb;
+        }
+        p_y0 = y0; p_si_lo = si_lo; p_nsrow = n_srow;
+    }
+    // drain: the last step's queue and emission
+    __syncthreads();
+    if (p_nsrow) {
+        run_queue(p_y0, p_si_lo);
+        __syncthreads();
+        emit(p_si_lo, p_nsrow);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// host: launch
+// ---------------------------------------------------------------------------------------------------------------
+int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples) {
+    static const int mode = getenv("VSLAM_FUSED_MMA") ? atoi(getenv("VSLAM_FUSED_MMA")) : 1;
+    if (!mode || io.gauss[0]) return 1;                              // materialising launches stay on fused.cu
+    if (n_frames <= 0 || n_frames > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: %d frames per launch", n_frames);
+    if ((io.base_pitch & 15) || ((uintptr_t)io.base & 15) || (io.base_stride & 15))
+        VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: base plane must be 16-byte aligned (pitch %zu)", io.base_pitch);
+    MmaArgs a;
+    memset(&a, 0, sizeof a);
+    static_cast<OctaveIO &>(a) = io;
+    if (build_mma_taps(sigma0, scale_samples, io.octave, &a.mt)) return 1;
+    cudaFuncAttributes fa;
+    static int static_smem = -1;
+    if (static_smem < 0) {
+        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_mma_k<256>));
+        static_smem = (int)fa.sharedSizeBytes;
+        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
+        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_mma_k<128>));
+        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes));
+    }
+    const size_t sm = mma_smem_bytes(a.mt);
+    if (sm + static_smem > 227 * 1024) return 1;                     // tables too large for this octave: dp4a/dp2a kernel
+    a.n_strips = mma_strips(a.cols);
+    // vertical split only when the batch alone cannot fill the machine (every extra segment repeats the warm-up)
+    const long long want = (long long)ctx->sm_count * 4;
+    const long long have = (long long)a.n_strips * n_frames;
+    int nseg = (int)((want + have - 1) / have);
+    const int max_seg = a.rows / (4 * FR) > 0 ? a.rows / (4 * FR) : 1;
+    if (nseg > max_seg) nseg = max_seg;
+    if (nseg < 1) nseg = 1;
+    const int seg_rows = ((a.rows + nseg - 1) / nseg + FR - 1) / FR * FR;
+    a.seg_rows = seg_rows;
+    a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
+    const dim3 grid(a.n_strips, a.n_segs, n_frames);
+    KernelSpan span(ctx, VSLAM_K_FUSED);
+    static const int nt = getenv("VSLAM_MMA_NT") ? atoi(getenv("VSLAM_MMA_NT")) : 256;
+    if (nt == 128) octave_mma_k<128><<<grid, 128, sm, ctx->stream>>>(a);
+    else octave_mma_k<256><<<grid, 256, sm, ctx->stream>>>(a);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
+
+}  // namespace vslam

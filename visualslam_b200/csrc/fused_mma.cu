@@ -56,24 +56,36 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
             if (t[i] < 0 || t[i] > 255) return VSLAM_E_INVALID;
             out->taps[l][i] = (u8)t[i];
         }
-        lv.sv = (4 - (2 * lv.r) % 4) % 4;
+        if (lv.r < rmin) rmin = lv.r;
+        if (lv.r > rmax) rmax = lv.r;
+    }
+    for (int l = 0; l < 6; ++l) {
+        MmaLevel &lv = out->lv[l];
+        const int n = lv.n;
+        // every level's H chunk of a step is the same 32 image rows y0 + rmax ..., so the A fragments are shared by the
+        // levels; a level's V window for output rows y0 + 8j ... starts rmax + r + sv rows above the chunk's row 8j
+        lv.sv = (4 - (rmax + lv.r) % 4) % 4;
         lv.ksv = (n + 7 + lv.sv + 31) / 32;
-        lv.cq = (2 * lv.r + lv.sv) / 4;
-        lv.np = (lv.cq + 8 + 2) / 2;                                 // quads Q = q + cq of a step: 8i .. 8i + 7 + cq
+        lv.cq = (rmax + lv.r + lv.sv) / 4;
+        lv.np = (lv.cq + 8 + 2) / 2;                                 // aligned quads Q = q + cq of a step: 8i .. 8i + 7 + cq
         if (lv.np < 8) lv.np = 8;                                    // single-step wrap of every slot computation (needs >= 6)
         lv.plane_off = poff;
         poff += 2 * lv.np * PPW;
         lv.tab_off = toff;
-        lv.tab_cp = (kMmaPadL + 32 * lv.ksv + 48 + 3) & ~3;          // V pass reads up to idx 32 ksv + 31; H pass up to n + 37
+        lv.tab_cp = (kMmaPadL + 32 * lv.ksv + 48 + 3) & ~3;          // V pass reads up to idx 32 ksv + 31; H pass up to n + 77
         if (lv.tab_cp < ((kMmaPadL + n + kMmaPadR + 3) & ~3)) lv.tab_cp = (kMmaPadL + n + kMmaPadR + 3) & ~3;
         lv.tab_cp += 32;                                             // copies 32 bytes apart modulo 128: fewer bank conflicts
         toff += 4 * lv.tab_cp;
-        if (lv.r < rmin) rmin = lv.r;
-        if (lv.r > rmax) rmax = lv.r;
     }
     out->rmin = rmin; out->rmax = rmax;
-    out->stage_rows = FR + rmax - rmin;
+    out->stage_rows = FR;
     out->stage_pitch = (2 * rmax + 15 + FW + 127) / 128 * 128;       // left halo rmax (+ up to 15 alignment), 64 columns, right halo
+    {   // row = (q * magic) >> 16 for q < stage_rows * (pitch / 16): checked exhaustively
+        const int spq = out->stage_pitch >> 4, nq = out->stage_rows * spq;
+        out->spq_magic = ((1 << 16) + spq - 1) / spq;
+        for (int q = 0; q < nq; ++q)
+            if ((int)(((unsigned)q * (unsigned)out->spq_magic) >> 16) != q / spq) return VSLAM_E_INVALID;
+    }
     out->plane_words = poff;
     out->tab_bytes = (toff + 15) & ~15;
     return VSLAM_OK;
@@ -98,6 +110,13 @@ __device__ __forceinline__ void imma(int (&d)[4], u32 a0, u32 a1, u32 a2, u32 a3
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// same with a constant accumulator input (the compiler materialises it once; RZ for 0)
+__device__ __forceinline__ void imma_c(int (&d)[4], u32 a0, u32 a1, u32 a2, u32 a3, u32 b0, u32 b1, int c) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c));
 }
 
 // byte offset of pixel (x, ty) inside a tile: words of 2 x 2 pixels [x even/odd][row even/odd], column pairs TRP words apart
@@ -137,12 +156,12 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
     const int yv = seg > 0 ? ys - FR : 0;        // first step with a V pass (one extra step feeds the detector's history)
     const int K = (2 * T.rmax + FR - 1) / FR;    // warm-up steps: H pass only
 
-    // ---- stage base rows y0 + rmin ..., columns xs16 ..., reflect-101 resolved (16-byte cp.async inside the image) ----
+    // ---- stage base rows y0 + rmax ..., columns xs16 ..., reflect-101 resolved (16-byte cp.async inside the image) ----
     const int SPQ = SP >> 4, n_stage = T.stage_rows * SPQ;
     auto issue_stage = [&](int y0n) {
         for (int q = tid; q < n_stage; q += NT) {
-            const int row = q / SPQ, j = q - row * SPQ;
-            const int y = refl101(y0n + T.rmin + row, rows);
+            const int row = (int)(((u32)q * (u32)T.spq_magic) >> 16), j = q - row * SPQ;
+            const int y = refl101(y0n + T.rmax + row, rows);
             const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
             u32 *dst = (u32 *)(stage + row * SP) + 4 * (j ^ ((row >> 2) & 7));   // 16-byte groups XOR-swizzled by the row quad
             const int x = xs16 + 16 * j;
@@ -248,11 +267,12 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
     // H pass, A fragment through ldmatrix.x4: lane L supplies the address of row (L & 7) of matrix (L >> 3); matrices 0/1
     // are the M rows 0-7 / 8-15 of K bytes 0-15, matrices 2/3 the same rows of K bytes 16-31.  M row m <-> image row
     // 4 pi(m & 7) + (m >> 3) (+2 for the second M block), so that a thread ends up with four consecutive rows of a quad.
-    const int h_pi = ((lane & 7) >> 1) + 4 * (lane & 1);                      // quad of the chunk this lane addresses
-    const int h_row = 4 * h_pi + ((lane >> 3) & 1);                           // image row inside the chunk, M block 0
+    const int h_row = 4 * (((lane & 7) >> 1) + 4 * (lane & 1)) + ((lane >> 3) & 1);   // staged row this lane addresses, M block 0
     const int h_kh = lane >> 4;                                               // K half
-    const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the chunk this thread's D rows belong to
     const u32 stage_sa = (u32)__cvta_generic_to_shared(stage);
+    const u32 saA = stage_sa + h_row * SP, saB = saA + 2 * SP;
+    const int keyA = (h_row >> 2) & 7, keyB = ((h_row + 2) >> 2) & 7;
+    const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the chunk this thread's D rows belong to
     // Per step three barriers.  Small jobs of the PREVIOUS step ride along with the two blur passes:
     //   P1 (after B1)  H pass of step c            + queued localisations of step c-1 (its tiles are still intact)
     //   P2 (after B2)  V pass of step c -> tiles   + ordered emission of step c-1, prefetch of step c+1's base rows
@@ -262,25 +282,21 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
         const bool do_v = y0 >= yv;
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();                                                      // B1: staged rows landed; P3 of c-1 done
-        // ---- 2. H pass: rows y0 + r_l .. y0 + r_l + 31 of every level -> 8 quads of the level's ring ----
-        // unit = (level, 16 output columns); levels in descending cost so the warps' shares are similar
-        for (int u = warp; u < 24; u += NW) {
-            const int l = 5 - (u >> 2), cgp = u & 3;
-            const MmaLevel &lv = T.lv[l];
-            const int r = lv.r, n = lv.n;
-            if (y0 + FR <= yv - 2 * r) continue;                 // warm-up: this level's rows are not needed yet
-            const int cb0 = cboff + 16 * cgp;                    // staged column of the unit's first output column
-            const int c_lo = (cb0 - r) >> 5, c_hi = (cb0 + 15 + r) >> 5;
-            const int rowA = r - T.rmin + h_row, rowB = rowA + 2;
-            const u32 saA = stage_sa + rowA * SP, saB = stage_sa + rowB * SP;
-            const int keyA = (rowA >> 2) & 7, keyB = (rowB >> 2) & 7;
-            // B fragment of (chunk c, block bb): b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 ..,
-            // idx0 = r + 32 c - (cb0 + 8 bb) + 4 t - g
-            const int p0 = r - cb0 + 4 * t - g + kMmaPadL;
-            const u8 *tb = tab + lv.tab_off + (p0 & 3) * lv.tab_cp + (p0 - (p0 & 3));   // two's complement: fine for p0 < 0
-            int acc[2][2][4];
+        // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
+        // warp = 8 output columns; the image fragments of a 32-byte chunk serve every level whose band touches it
+        for (int b = warp; b < 8; b += NW) {
+            const int cb = cboff + 8 * b;                        // staged column of the block's first output column
+            const int c_lo = (cb - T.rmax) >> 5, c_hi = (cb + 7 + T.rmax) >> 5;
+            // B fragment of (level, chunk c): b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 .., idx0 = r + 32 c - cb + 4 t - g
+            const u8 *tb[6];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) (&acc[0][0][0])[i] = 0;
+            for (int l = 0; l < 6; ++l) {
+                const int p0 = T.lv[l].r - cb + 4 * t - g + kMmaPadL;
+                tb[l] = tab + T.lv[l].tab_off + (p0 & 3) * T.lv[l].tab_cp + (p0 - (p0 & 3));   // two's complement: fine for p0 < 0
+            }
+            int acc[6][2][4];
+#pragma unroll
+            for (int i = 0; i < 48; ++i) (&acc[0][0][0])[i] = 0;
             for (int c = c_lo; c <= c_hi; ++c) {
                 u32 a0[4], a1[4];
                 const int ch = 2 * c + h_kh;
@@ -289,30 +305,29 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
                 asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                              : "=r"(a1[0]), "=r"(a1[1]), "=r"(a1[2]), "=r"(a1[3]) : "r"(saB + ((ch ^ keyB) << 4)));
 #pragma unroll
-                for (int bb = 0; bb < 2; ++bb) {
-                    const int bs = r + 32 * c - cb0 - 8 * bb;                 // tap index of (k = 0, n = 0): warp-uniform
-                    if (bs < -31 || bs > n + 6) continue;                     // the band misses this chunk
-                    const u32 b0 = *(const u32 *)(tb + 32 * c - 8 * bb), b1 = *(const u32 *)(tb + 32 * c - 8 * bb + 16);
-                    imma(acc[bb][0], a0[0], a0[1], a0[2], a0[3], b0, b1);
-                    imma(acc[bb][1], a1[0], a1[1], a1[2], a1[3], b0, b1);
+                for (int l = 0; l < 6; ++l) {
+                    const int bs = T.lv[l].r + 32 * c - cb;                   // tap index of (k = 0, n = 0): warp-uniform
+                    if (bs < -31 || bs > T.lv[l].n + 6) continue;             // the band misses this chunk
+                    const u32 b0 = *(const u32 *)(tb[l] + 32 * c), b1 = *(const u32 *)(tb[l] + 32 * c + 16);
+                    imma(acc[l][0], a0[0], a0[1], a0[2], a0[3], b0, b1);
+                    imma(acc[l][1], a1[0], a1[1], a1[2], a1[3], b0, b1);
                 }
             }
-            // thread: rows 4 d_pi .. + 3 of columns 2t, 2t + 1 of each block -> low bytes {c0, c1} and high bytes {c0, c1}
-            // of one quad, in the pair-aligned planes (aligned quad Q = q + cq, pair Q >> 1, position Q & 1)
-            const int Q = d_pi + lv.cq;
-            int slot = s_hb[l] + (Q >> 1);
-            if (slot >= lv.np) slot -= lv.np;
-            u32 *plo = planes + lv.plane_off + slot * PPW + 4 * (8 * cgp + t) + 2 * (Q & 1);
-            u32 *phi = plo + lv.np * PPW;
+            // thread: rows 4 d_pi .. + 3 of columns 2t, 2t + 1 -> low bytes {c0, c1} and high bytes {c0, c1} of one quad,
+            // in the pair-aligned planes (aligned quad Q = q + cq, pair Q >> 1, position Q & 1)
 #pragma unroll
-            for (int bb = 0; bb < 2; ++bb) {
-                const u32 e01 = __byte_perm(acc[bb][0][0], acc[bb][0][2], 0x5410), e23 = __byte_perm(acc[bb][1][0], acc[bb][1][2], 0x5410);
-                const u32 o01 = __byte_perm(acc[bb][0][1], acc[bb][0][3], 0x5410), o23 = __byte_perm(acc[bb][1][1], acc[bb][1][3], 0x5410);
+            for (int l = 0; l < 6; ++l) {
+                const int Q = d_pi + T.lv[l].cq;
+                int slot = s_hb[l] + (Q >> 1);
+                if (slot >= T.lv[l].np) slot -= T.lv[l].np;
+                u32 *plo = planes + T.lv[l].plane_off + slot * PPW + 4 * (4 * b + t) + 2 * (Q & 1);
+                const u32 e01 = __byte_perm(acc[l][0][0], acc[l][0][2], 0x5410), e23 = __byte_perm(acc[l][1][0], acc[l][1][2], 0x5410);
+                const u32 o01 = __byte_perm(acc[l][0][1], acc[l][0][3], 0x5410), o23 = __byte_perm(acc[l][1][1], acc[l][1][3], 0x5410);
                 uint2 vl, vh;
                 vl.x = __byte_perm(e01, e23, 0x6420); vh.x = __byte_perm(e01, e23, 0x7531);
                 vl.y = __byte_perm(o01, o23, 0x6420); vh.y = __byte_perm(o01, o23, 0x7531);
-                *(uint2 *)(plo + 16 * bb) = vl;
-                *(uint2 *)(phi + 16 * bb) = vh;
+                *(uint2 *)plo = vl;
+                *(uint2 *)(plo + T.lv[l].np * PPW) = vh;
             }
         }
         if (p_nsrow) run_queue(p_y0, p_si_lo);
@@ -324,41 +339,45 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
             u32 prev0[RBW], prev1[RBW];                          // previous level, columns 2g and 2g + 1, rows as 16-bit halves
 #pragma unroll
             for (int rb = 0; rb < RBW; ++rb) prev0[rb] = prev1[rb] = 0;
-#pragma unroll 1
+            const int wi0 = (8 * cb + g) * TRP + 2 + 4 * jb + t;
+#pragma unroll
             for (int l = 0; l < 6; ++l) {
-                const MmaLevel &lv = T.lv[l];
-                const u32 ring = (u32)lv.np * (PPW * 4), hi_off = ring;       // bytes of one plane
-                const int ksv = lv.ksv;
-                const u8 *plane = (const u8 *)(planes + lv.plane_off) + 16 * (8 * cb + g);
+                const u32 ring = (u32)T.lv[l].np * (PPW * 4);                 // bytes of one plane; the high-byte plane follows
+                const u8 *plane = (const u8 *)(planes + T.lv[l].plane_off) + 16 * (8 * cb + g);
                 // pair of (row block j, K step k, lane t): 4i + j + 4k + t; slot = that modulo np
                 u32 off[RBW];
                 {
                     int s0 = s_hb[l] + jb + t;
-                    if (s0 >= lv.np) s0 -= lv.np;
+                    if (s0 >= T.lv[l].np) s0 -= T.lv[l].np;
 #pragma unroll
                     for (int rb = 0; rb < RBW; ++rb) {
                         int s1 = s0 + rb;
-                        if (s1 >= lv.np) s1 -= lv.np;
+                        if (s1 >= T.lv[l].np) s1 -= T.lv[l].np;
                         off[rb] = (u32)s1 * (PPW * 4);
                     }
                 }
-                const int p0 = 8 * t - g + kMmaPadL - lv.sv;     // >= 40 - 7 - 3
-                const u8 *tb = tab + lv.tab_off + (p0 & 3) * lv.tab_cp + (p0 & ~3);
+                const int p0 = 8 * t - g + kMmaPadL - T.lv[l].sv;             // >= 40 - 7 - 3
+                const u8 *tb = tab + T.lv[l].tab_off + (p0 & 3) * T.lv[l].tab_cp + (p0 & ~3);
                 int lo[RBW][4], hi[RBW][4];
+                {   // K step 0 seeds the accumulators: 32768 (rounding) for the low bytes, 0 for the high bytes
+                    const u32 b0 = *(const u32 *)tb, b1 = *(const u32 *)(tb + 4);
 #pragma unroll
-                for (int rb = 0; rb < RBW; ++rb)
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) { lo[rb][i] = 32768; hi[rb][i] = 0; }
+                    for (int rb = 0; rb < RBW; ++rb) {
+                        const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + ring);
+                        imma_c(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1, 32768);
+                        imma_c(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1, 0);
+                    }
+                }
 #pragma unroll 1
-                for (int k = 0; k < ksv; ++k) {
+                for (int k = 1; k < T.lv[l].ksv; ++k) {
                     const u32 b0 = *(const u32 *)(tb + 32 * k), b1 = *(const u32 *)(tb + 32 * k + 4);
 #pragma unroll
                     for (int rb = 0; rb < RBW; ++rb) {
-                        const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + hi_off);
-                        imma(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1);
-                        imma(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1);
                         const u32 nx = off[rb] + 4 * (PPW * 4);
                         off[rb] = min(nx, nx - ring);            // wrap: nx - ring is huge (unsigned) unless nx >= ring
+                        const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + ring);
+                        imma(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1);
+                        imma(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1);
                     }
                 }
 #pragma unroll
@@ -367,7 +386,7 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
                     const u32 v0 = (u32)(hi[rb][0] << 8) + (u32)lo[rb][0], v1 = (u32)(hi[rb][1] << 8) + (u32)lo[rb][1];
                     const u32 v2 = (u32)(hi[rb][2] << 8) + (u32)lo[rb][2], v3 = (u32)(hi[rb][3] << 8) + (u32)lo[rb][3];
                     const u32 c0 = __byte_perm(v0, v1, 0x7632), c1 = __byte_perm(v2, v3, 0x7632);
-                    const int wi = (8 * cb + g) * TRP + 2 + 4 * (jb + rb) + t;
+                    const int wi = wi0 + 4 * rb;
                     if (jb + rb == 3 && t >= 2 && l >= 1) {      // rows y0+28 .. y0+31 of the last step become the history
                         if (l <= 3) tiles32[(l - 1) * TILE_W + wi - 16] = tiles32[(l - 1) * TILE_W + wi];
                         tiles32[(N_G + l - 1) * TILE_W + wi - 16] = tiles32[(N_G + l - 1) * TILE_W + wi];

@@ -10,9 +10,9 @@ constexpr int kMmaPadR = 40;
 // One Gaussian level of octave_mma_k.
 struct MmaLevel {
     int n, r;
-    int sv;                         // V pass: rows the window starts above (out row - r) so that it is quad aligned: (-2r) mod 4
+    int sv;                         // V pass: rows the window starts above (out row - r) so that it is quad aligned: -(rmax + r) mod 4
     int ksv;                        // V pass: 32-row K steps, ceil((n + 7 + sv) / 32)
-    int cq;                         // quads between a row block's window start and the step's H chunk: (2r + sv) / 4
+    int cq;                         // quads between a row block's window start and the step's H chunk: (rmax + r + sv) / 4
     int np;                         // ring slots of this level's h planes, in PAIRS of row quads
     int plane_off;                  // word offset of the level's low-byte plane; the high-byte plane follows it
     int tab_off;                    // byte offset of the level's four byte-shifted tap copies
@@ -23,7 +23,8 @@ struct MmaTaps {
     MmaLevel lv[6];
     u8 taps[6][248];
     int rmin, rmax;
-    int stage_rows, stage_pitch;    // staged base tile: 32 + rmax - rmin rows, pitch a multiple of 128 bytes (XOR swizzle)
+    int stage_rows, stage_pitch;    // staged base tile: 32 rows (y0 + rmax ...), pitch a multiple of 128 bytes (XOR swizzle)
+    int spq_magic;                  // ceil(2^16 / (stage_pitch / 16)): flattened index -> row without a division
     int plane_words;                // all six planes
     int tab_bytes;                  // all tap copies
 };

@@ -125,8 +125,10 @@ __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1)
 
 }  // namespace
 
-template <int NT>
-__global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaArgs a) {
+// NCH = 32-byte chunks of a staged row that the bands of one 8-column block can touch: (8 + 2 rmax + 31) / 32 + 1
+template <int NCH>
+__global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ MmaArgs a) {
+    constexpr int NT = 256;
     extern __shared__ __align__(16) u32 smem[];
     constexpr int NW = NT / 32;
     constexpr int RBW = 16 / NW;                // 8-row blocks of one 16-column block a warp owns in the V pass
@@ -140,7 +142,6 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
     __shared__ int s_res[3 * MAX_SROW * NS];                 // detector results of one step
     __shared__ unsigned short s_queue[3 * MAX_SROW * NS];     // samples that need the full localisation
     __shared__ int s_nq;
-    __shared__ int s_hb[6];                                   // ring slot of the step's first quad pair, per level
     __shared__ float s_div[511];                              // float(i - 255) / 255f, the reference's divisions
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -189,7 +190,6 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
             }
     }
     for (int i = tid; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
-    if (tid < 6) s_hb[tid] = 0;
     if (tid == 0) s_nq = 0;
 
     constexpr int DT0 = N_G * TILE_W * 4;                                     // byte offset of the first D tile
@@ -263,104 +263,115 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
         }
     };
 
-    // ---- lane constants of the two passes ----
+    // ---- lane constants of the two passes (nothing below depends on the step) ----
     // H pass, A fragment through ldmatrix.x4: lane L supplies the address of row (L & 7) of matrix (L >> 3); matrices 0/1
     // are the M rows 0-7 / 8-15 of K bytes 0-15, matrices 2/3 the same rows of K bytes 16-31.  M row m <-> image row
     // 4 pi(m & 7) + (m >> 3) (+2 for the second M block), so that a thread ends up with four consecutive rows of a quad.
     const int h_row = 4 * (((lane & 7) >> 1) + 4 * (lane & 1)) + ((lane >> 3) & 1);   // staged row this lane addresses, M block 0
-    const int h_kh = lane >> 4;                                               // K half
     const u32 stage_sa = (u32)__cvta_generic_to_shared(stage);
-    const u32 saA = stage_sa + h_row * SP, saB = saA + 2 * SP;
-    const int keyA = (h_row >> 2) & 7, keyB = ((h_row + 2) >> 2) & 7;
-    const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the chunk this thread's D rows belong to
+    const int hcb = cboff + 8 * warp;                                         // H pass: warp = 8 output columns (staged column hcb ...)
+    const int c_lo = (hcb - T.rmax) >> 5;                                     // first 32-byte chunk any level's band touches
+    u32 saA[NCH], saB[NCH];                                                   // ldmatrix addresses of the chunks (XOR swizzle resolved)
+#pragma unroll
+    for (int ci = 0; ci < NCH; ++ci) {
+        const int ch = 2 * (c_lo + ci) + (lane >> 4);
+        saA[ci] = stage_sa + h_row * SP + ((ch ^ ((h_row >> 2) & 7)) << 4);
+        saB[ci] = stage_sa + (h_row + 2) * SP + ((ch ^ (((h_row + 2) >> 2) & 7)) << 4);
+    }
+    // B fragments: b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 ..; H pass idx0 = r + 32 c - hcb + 4 t - g,
+    // V pass (K rows remapped so that a thread's 8 rows are consecutive) b1 = taps idx0 + 4 .., idx0 = 32 k + 8 t - g - sv
+    const u8 *htb[6], *vtb[6];
+    unsigned long long hmask = 0;                                             // bit 6 ci + l: level l's band touches chunk c_lo + ci
+    const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the H chunk this thread's D rows belong to
+    const int vcb = warp % 4, vjb = (warp / 4) * RBW;                         // V pass: warp = (16-column block, RBW blocks of 8 rows)
+    u32 hoff[6], voff[6];                                                     // ring byte offsets: H store slot, V window start (row block vjb)
+#pragma unroll
+    for (int l = 0; l < 6; ++l) {
+        const int p0 = T.lv[l].r - hcb + 4 * t - g + kMmaPadL + 32 * c_lo;
+        htb[l] = tab + T.lv[l].tab_off + (p0 & 3) * T.lv[l].tab_cp + (p0 - (p0 & 3));   // two's complement: fine for p0 < 0
+        const int p1 = 8 * t - g + kMmaPadL - T.lv[l].sv;                     // >= 40 - 7 - 3
+        vtb[l] = tab + T.lv[l].tab_off + (p1 & 3) * T.lv[l].tab_cp + (p1 & ~3);
+#pragma unroll
+        for (int ci = 0; ci < NCH; ++ci) {
+            const int bs = T.lv[l].r + 32 * (c_lo + ci) - hcb;                // tap index of (k = 0, n = 0)
+            if (bs >= -31 && bs <= T.lv[l].n + 6) hmask |= 1ull << (6 * ci + l);
+        }
+        hoff[l] = (u32)((d_pi + T.lv[l].cq) >> 1) * (PPW * 4);                // < np pairs
+        voff[l] = (u32)(vjb + t) * (PPW * 4);
+    }
+    const u32 hlane = 16 * (4 * warp + t), vlane = 16 * (8 * vcb + g);        // column part of the plane addresses
+    const int wi0 = (8 * vcb + g) * TRP + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
     // Per step three barriers.  Small jobs of the PREVIOUS step ride along with the two blur passes:
     //   P1 (after B1)  H pass of step c            + queued localisations of step c-1 (its tiles are still intact)
     //   P2 (after B2)  V pass of step c -> tiles   + ordered emission of step c-1, prefetch of step c+1's base rows
-    //   P3 (after B3)  detector tests of step c, decimated level 3 -> next base, ring bases advance
+    //   P3 (after B3)  detector tests of step c, decimated level 3 -> next base
     int p_y0 = 0, p_si_lo = 0, p_nsrow = 0;                                   // the previous step's detector state
     for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
         const bool do_v = y0 >= yv;
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();                                                      // B1: staged rows landed; P3 of c-1 done
         // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
-        // warp = 8 output columns; the image fragments of a 32-byte chunk serve every level whose band touches it
-        for (int b = warp; b < 8; b += NW) {
-            const int cb = cboff + 8 * b;                        // staged column of the block's first output column
-            const int c_lo = (cb - T.rmax) >> 5, c_hi = (cb + 7 + T.rmax) >> 5;
-            // B fragment of (level, chunk c): b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 .., idx0 = r + 32 c - cb + 4 t - g
-            const u8 *tb[6];
+        // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them
+        {
+            u32 fa[NCH][4], fb[NCH][4];
+#pragma unroll
+            for (int ci = 0; ci < NCH; ++ci) {
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(fa[ci][0]), "=r"(fa[ci][1]), "=r"(fa[ci][2]), "=r"(fa[ci][3]) : "r"(saA[ci]));
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(fb[ci][0]), "=r"(fb[ci][1]), "=r"(fb[ci][2]), "=r"(fb[ci][3]) : "r"(saB[ci]));
+            }
 #pragma unroll
             for (int l = 0; l < 6; ++l) {
-                const int p0 = T.lv[l].r - cb + 4 * t - g + kMmaPadL;
-                tb[l] = tab + T.lv[l].tab_off + (p0 & 3) * T.lv[l].tab_cp + (p0 - (p0 & 3));   // two's complement: fine for p0 < 0
-            }
-            int acc[6][2][4];
+                int acc[2][4];
 #pragma unroll
-            for (int i = 0; i < 48; ++i) (&acc[0][0][0])[i] = 0;
-            for (int c = c_lo; c <= c_hi; ++c) {
-                u32 a0[4], a1[4];
-                const int ch = 2 * c + h_kh;
-                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-                             : "=r"(a0[0]), "=r"(a0[1]), "=r"(a0[2]), "=r"(a0[3]) : "r"(saA + ((ch ^ keyA) << 4)));
-                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-                             : "=r"(a1[0]), "=r"(a1[1]), "=r"(a1[2]), "=r"(a1[3]) : "r"(saB + ((ch ^ keyB) << 4)));
+                for (int i = 0; i < 8; ++i) (&acc[0][0])[i] = 0;
 #pragma unroll
-                for (int l = 0; l < 6; ++l) {
-                    const int bs = T.lv[l].r + 32 * c - cb;                   // tap index of (k = 0, n = 0): warp-uniform
-                    if (bs < -31 || bs > T.lv[l].n + 6) continue;             // the band misses this chunk
-                    const u32 b0 = *(const u32 *)(tb[l] + 32 * c), b1 = *(const u32 *)(tb[l] + 32 * c + 16);
-                    imma(acc[l][0], a0[0], a0[1], a0[2], a0[3], b0, b1);
-                    imma(acc[l][1], a1[0], a1[1], a1[2], a1[3], b0, b1);
+                for (int ci = 0; ci < NCH; ++ci) {
+                    if (hmask & (1ull << (6 * ci + l))) {                       // warp-uniform
+                        const u32 b0 = *(const u32 *)(htb[l] + 32 * ci), b1 = *(const u32 *)(htb[l] + 32 * ci + 16);
+                        imma(acc[0], fa[ci][0], fa[ci][1], fa[ci][2], fa[ci][3], b0, b1);
+                        imma(acc[1], fb[ci][0], fb[ci][1], fb[ci][2], fb[ci][3], b0, b1);
+                    }
                 }
-            }
-            // thread: rows 4 d_pi .. + 3 of columns 2t, 2t + 1 -> low bytes {c0, c1} and high bytes {c0, c1} of one quad,
-            // in the pair-aligned planes (aligned quad Q = q + cq, pair Q >> 1, position Q & 1)
-#pragma unroll
-            for (int l = 0; l < 6; ++l) {
-                const int Q = d_pi + T.lv[l].cq;
-                int slot = s_hb[l] + (Q >> 1);
-                if (slot >= T.lv[l].np) slot -= T.lv[l].np;
-                u32 *plo = planes + T.lv[l].plane_off + slot * PPW + 4 * (4 * b + t) + 2 * (Q & 1);
-                const u32 e01 = __byte_perm(acc[l][0][0], acc[l][0][2], 0x5410), e23 = __byte_perm(acc[l][1][0], acc[l][1][2], 0x5410);
-                const u32 o01 = __byte_perm(acc[l][0][1], acc[l][0][3], 0x5410), o23 = __byte_perm(acc[l][1][1], acc[l][1][3], 0x5410);
+                // thread: rows 4 d_pi .. + 3 of columns 2t, 2t + 1 -> low bytes {c0, c1} and high bytes {c0, c1} of one quad,
+                // in the pair-aligned planes (aligned quad Q = q + cq, pair Q >> 1, position Q & 1)
+                const u32 ring = (u32)T.lv[l].np * (PPW * 4);
+                u8 *plo = (u8 *)(planes + T.lv[l].plane_off) + hoff[l] + hlane + 8 * ((d_pi + T.lv[l].cq) & 1);
+                const u32 e01 = __byte_perm(acc[0][0], acc[0][2], 0x5410), e23 = __byte_perm(acc[1][0], acc[1][2], 0x5410);
+                const u32 o01 = __byte_perm(acc[0][1], acc[0][3], 0x5410), o23 = __byte_perm(acc[1][1], acc[1][3], 0x5410);
                 uint2 vl, vh;
                 vl.x = __byte_perm(e01, e23, 0x6420); vh.x = __byte_perm(e01, e23, 0x7531);
                 vl.y = __byte_perm(o01, o23, 0x6420); vh.y = __byte_perm(o01, o23, 0x7531);
                 *(uint2 *)plo = vl;
-                *(uint2 *)(plo + T.lv[l].np * PPW) = vh;
+                *(uint2 *)(plo + ring) = vh;
+                const u32 nx = hoff[l] + 4 * (PPW * 4);                       // the next step's chunk is four pairs further on
+                hoff[l] = min(nx, nx - ring);
             }
         }
         if (p_nsrow) run_queue(p_y0, p_si_lo);
         __syncthreads();                                                      // B2
         if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
-        // ---- 3. V pass + rounding + DoG -> tiles.  warp = (16-column block, RBW blocks of 8 rows), levels in order ----
+        // ---- 3. V pass + rounding + DoG -> tiles, levels in order ----
         if (do_v) {
-            const int cb = warp % 4, jb = (warp / 4) * RBW;
             u32 prev0[RBW], prev1[RBW];                          // previous level, columns 2g and 2g + 1, rows as 16-bit halves
 #pragma unroll
             for (int rb = 0; rb < RBW; ++rb) prev0[rb] = prev1[rb] = 0;
-            const int wi0 = (8 * cb + g) * TRP + 2 + 4 * jb + t;
 #pragma unroll
             for (int l = 0; l < 6; ++l) {
                 const u32 ring = (u32)T.lv[l].np * (PPW * 4);                 // bytes of one plane; the high-byte plane follows
-                const u8 *plane = (const u8 *)(planes + T.lv[l].plane_off) + 16 * (8 * cb + g);
+                const u8 *plane = (const u8 *)(planes + T.lv[l].plane_off) + vlane;
                 // pair of (row block j, K step k, lane t): 4i + j + 4k + t; slot = that modulo np
                 u32 off[RBW];
-                {
-                    int s0 = s_hb[l] + jb + t;
-                    if (s0 >= T.lv[l].np) s0 -= T.lv[l].np;
+                off[0] = voff[l];
 #pragma unroll
-                    for (int rb = 0; rb < RBW; ++rb) {
-                        int s1 = s0 + rb;
-                        if (s1 >= T.lv[l].np) s1 -= T.lv[l].np;
-                        off[rb] = (u32)s1 * (PPW * 4);
-                    }
+                for (int rb = 1; rb < RBW; ++rb) {
+                    const u32 nx = off[rb - 1] + PPW * 4;
+                    off[rb] = min(nx, nx - ring);
                 }
-                const int p0 = 8 * t - g + kMmaPadL - T.lv[l].sv;             // >= 40 - 7 - 3
-                const u8 *tb = tab + T.lv[l].tab_off + (p0 & 3) * T.lv[l].tab_cp + (p0 & ~3);
                 int lo[RBW][4], hi[RBW][4];
                 {   // K step 0 seeds the accumulators: 32768 (rounding) for the low bytes, 0 for the high bytes
-                    const u32 b0 = *(const u32 *)tb, b1 = *(const u32 *)(tb + 4);
+                    const u32 b0 = *(const u32 *)vtb[l], b1 = *(const u32 *)(vtb[l] + 4);
 #pragma unroll
                     for (int rb = 0; rb < RBW; ++rb) {
                         const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + ring);
@@ -370,7 +381,7 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
                 }
 #pragma unroll 1
                 for (int k = 1; k < T.lv[l].ksv; ++k) {
-                    const u32 b0 = *(const u32 *)(tb + 32 * k), b1 = *(const u32 *)(tb + 32 * k + 4);
+                    const u32 b0 = *(const u32 *)(vtb[l] + 32 * k), b1 = *(const u32 *)(vtb[l] + 32 * k + 4);
 #pragma unroll
                     for (int rb = 0; rb < RBW; ++rb) {
                         const u32 nx = off[rb] + 4 * (PPW * 4);
@@ -387,7 +398,7 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
                     const u32 v2 = (u32)(hi[rb][2] << 8) + (u32)lo[rb][2], v3 = (u32)(hi[rb][3] << 8) + (u32)lo[rb][3];
                     const u32 c0 = __byte_perm(v0, v1, 0x7632), c1 = __byte_perm(v2, v3, 0x7632);
                     const int wi = wi0 + 4 * rb;
-                    if (jb + rb == 3 && t >= 2 && l >= 1) {      // rows y0+28 .. y0+31 of the last step become the history
+                    if (vjb + rb == 3 && t >= 2 && l >= 1) {     // rows y0+28 .. y0+31 of the last step become the history
                         if (l <= 3) tiles32[(l - 1) * TILE_W + wi - 16] = tiles32[(l - 1) * TILE_W + wi];
                         tiles32[(N_G + l - 1) * TILE_W + wi - 16] = tiles32[(N_G + l - 1) * TILE_W + wi];
                     }
@@ -399,6 +410,12 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
                     prev0[rb] = c0; prev1[rb] = c1;
                 }
             }
+        }
+        // the V windows of the next step start four pairs further on (also during the warm-up steps)
+#pragma unroll
+        for (int l = 0; l < 6; ++l) {
+            const u32 ring = (u32)T.lv[l].np * (PPW * 4), nx = voff[l] + 4 * (PPW * 4);
+            voff[l] = min(nx, nx - ring);
         }
         if (p_nsrow) emit(p_si_lo, p_nsrow);
         if (tid == 0) s_nq = 0;
@@ -461,12 +478,6 @@ __global__ void __launch_bounds__(NT) octave_mma_k(const __grid_constant__ MmaAr
                     nb[(size_t)oy * a.next_pitch + ox] = (u8)tiles32[2 * TILE_W + (oc + 1) * TRP + 2 + w];
             }
         }
-        // ---- 4c. the rings advance by one chunk of 8 quads ----
-        if (tid < 6) {
-            int hb = s_hb[tid] + 4;
-            if (hb >= T.lv[tid].np) hb -= T.lv[tid].np;
-            s_hb[tid] = hb;
-        }
         p_y0 = y0; p_si_lo = si_lo; p_nsrow = n_srow;
     }
     // drain: the last step's queue and emission
@@ -491,14 +502,16 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     memset(&a, 0, sizeof a);
     static_cast<OctaveIO &>(a) = io;
     if (build_mma_taps(sigma0, scale_samples, io.octave, &a.mt)) return 1;
-    cudaFuncAttributes fa;
+    const int nch = (8 + 2 * a.mt.rmax + 31) / 32 + 1;
+    if (nch > 6) return 1;                                           // bands wider than six chunks: dp4a/dp2a kernel
     static int static_smem = -1;
     if (static_smem < 0) {
-        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_mma_k<256>));
+        cudaFuncAttributes fa;
+        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_mma_k<3>));
         static_smem = (int)fa.sharedSizeBytes;
-        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
-        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_mma_k<128>));
-        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes));
+        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
+        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
+        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
     }
     const size_t sm = mma_smem_bytes(a.mt);
     if (sm + static_smem > 227 * 1024) return 1;                     // tables too large for this octave: dp4a/dp2a kernel
@@ -515,9 +528,9 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
     KernelSpan span(ctx, VSLAM_K_FUSED);
-    static const int nt = getenv("VSLAM_MMA_NT") ? atoi(getenv("VSLAM_MMA_NT")) : 256;
-    if (nt == 128) octave_mma_k<128><<<grid, 128, sm, ctx->stream>>>(a);
-    else octave_mma_k<256><<<grid, 256, sm, ctx->stream>>>(a);
+    if (nch <= 3) octave_mma_k<3><<<grid, 256, sm, ctx->stream>>>(a);
+    else if (nch <= 4) octave_mma_k<4><<<grid, 256, sm, ctx->stream>>>(a);
+    else octave_mma_k<6><<<grid, 256, sm, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

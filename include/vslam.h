@@ -169,6 +169,39 @@ VSLAM_API int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, 
                            uint8_t *r8, uint8_t *mask3, vslam_corner *corners, int capacity, int out_space,
                            int *counts);
 
+/* ---- per-function entry points: the reference's own function granularity, for the C++17 mirror in
+ *      visualslam_b200/host/ (HOST buffers, dense unless a pitch is given; each call synchronises).  The throughput
+ *      paths above (vslam_dog_keypoints, vslam_harris) fuse these stages; results are identical. ------------------- */
+/* GaussianBlur(img, blurred, Size(3,3), 0, 0, BORDER_DEFAULT) on 8U (Harris_corners.cpp:157-158) */
+VSLAM_API int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst,
+                                   size_t dst_pitch);
+/* Sobel(src, CV_32F, 1,0 / 0,1, ksize=1, BORDER_DEFAULT) (Harris_corners.cpp:161-164, GaussPyramid.cpp:72-75); gx or gy may be NULL */
+VSLAM_API int vslam_sobel1(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, float *gx, float *gy);
+/* HarrisCorner(Ix, Iy) incl. StructureMatrix (Harris_corners.cpp:10-68): window 3, k 0.04 in the reference */
+VSLAM_API int vslam_harris_response(vslam_ctx *ctx, const float *ix, const float *iy, int rows, int cols, int window,
+                                    float k, float *response);
+/* convertScaleAbs(src, dst) with alpha 1, beta 0 (Harris_corners.cpp:176) */
+VSLAM_API int vslam_convert_scale_abs(vslam_ctx *ctx, const float *src, int rows, int cols, uint8_t *dst);
+/* NonMaximumSuppression(response8u, 3) (Harris_corners.cpp:70-81): 255 where strictly above the 8 neighbours */
+VSLAM_API int vslam_nms3(vslam_ctx *ctx, const uint8_t *r8, int rows, int cols, uint8_t *mask);
+/* NMS2(response, window) (Harris_corners.cpp:83-129) as a proper float map: window maximum at the kept positions, else 0 */
+VSLAM_API int vslam_nms2(vslam_ctx *ctx, const float *response, int rows, int cols, int window, float *out_map);
+/* initialKeypointDetection (+ FeaturePointLocalization) of ONE octave of one frame (Diff_of_Gauss.cpp:254-297);
+ * apply_edge != 0 also applies filterKeypoints' edge threshold (:326-338).  Host list, reference order. */
+VSLAM_API int vslam_dog_detect_octave(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave,
+                                      const vslam_dog_params *params, int apply_edge, vslam_keypoint *out,
+                                      int capacity, int *count);
+/* computeEdgeResponse (Diff_of_Gauss.cpp:79-109) of n keypoints of one octave (padded coordinates as stored) */
+VSLAM_API int vslam_edge_responses(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave,
+                                   const vslam_keypoint *keypoints, int n, float *responses);
+/* FeaturePointLocalization's dog_zhat (Diff_of_Gauss.cpp:223-243) for n candidates given as int32 quadruples
+ * (d_x, d_y, d_scale, value); the caller applies `> 0.03f` and `(int)(dog_zhat * 255.0f)` (:245-246) */
+VSLAM_API int vslam_localize(vslam_ctx *ctx, const int32_t *candidates, int n, float *dog_zhat);
+/* computeEdgeResponse's arithmetic (Diff_of_Gauss.cpp:93-107) on n windows of window_len (gx, gy) pairs:
+ * responses[i] = tr^2 / det (or NULL); sums[3i..3i+2] = Ix2, Iy2, IxIy = StructureMatrix (Harris_corners.cpp:10-29) (or NULL) */
+VSLAM_API int vslam_edge_from_windows(vslam_ctx *ctx, const float *gx, const float *gy, int n, int window_len,
+                                      float *responses, float *sums);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,6 +55,9 @@ EXPORTS = [
     "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
     "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
     "vslam_profile", "vslam_profile_read",
+    # per-function entry points used by the C++17 host layer (visualslam_b200/host)
+    "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
+    "vslam_dog_detect_octave", "vslam_edge_responses", "vslam_localize", "vslam_edge_from_windows",
 ]
 
 _lib = None

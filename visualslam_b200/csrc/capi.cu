@@ -10,6 +10,7 @@
 #include "fused.cuh"
 #include "harris.cuh"
 #include "pyramid.cuh"
+#include "stages.cuh"
 
 using namespace vslam;
 
@@ -284,13 +285,16 @@ static size_t detect_segments(const Geometry &g, int window, int *seg_base /*[nu
 
 // rows G-J for one frame whose planes are in `block`; appends to d_out in emission order.
 static int detect_frame(vslam_ctx *ctx, const Geometry &g, u8 *block, const vslam_dog_params &dp, const int *seg_base,
-                        size_t n_seg, vslam_keypoint *d_out, int capacity, int frame, unsigned long long *d_stage) {
+                        size_t n_seg, vslam_keypoint *d_out, int capacity, int frame, unsigned long long *d_stage,
+                        int only_octave = -1, int apply_edge = 1) {
     int *cnt = ctx->counters.as<int>();
     VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
     for (int o = 0; o < g.num_octaves; ++o) {
+        if (only_octave >= 0 && o != only_octave) continue;
         OctavePlanes op;
         octave_planes(g, block, o, &op);
         DetectArgs a;
+        a.apply_edge = apply_edge;
         for (int l = 0; l < 5; ++l) a.dog[l] = op.dog[l];
         for (int l = 0; l < 6; ++l) a.gauss[l] = op.gauss[l];
         a.rows = op.rows; a.cols = op.cols; a.pitch = op.pitch; a.octave = o;
@@ -652,5 +656,171 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
     return emit_list(ctx, corners, out_space, d_out, sizeof(vslam_corner), total, capacity);
 }
+
+// ---- per-function entry points (host buffers; the reference's own function granularity, stages.cu) --------------------
+// Scratch: ctx->maps_dev carved into 256-byte aligned regions.
+static int stage_scratch(vslam_ctx *ctx, const size_t *bytes, int n, u8 **ptr) {
+    size_t tot = 0;
+    for (int i = 0; i < n; ++i) tot += round_up(bytes[i], 256);
+    if (ctx->maps_dev.reserve(tot)) VS_FAIL(ctx, VSLAM_E_NOMEM, "stage scratch (%zu bytes)", tot);
+    u8 *p = ctx->maps_dev.as<u8>();
+    for (int i = 0; i < n; ++i) { ptr[i] = p; p += round_up(bytes[i], 256); }
+    return VSLAM_OK;
+}
+#define H2D(dst, src, n) VS_CUDA(ctx, cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream))
+#define D2H(dst, src, n) VS_CUDA(ctx, cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, ctx->stream))
+static int stage_check(vslam_ctx *ctx, const void *a, const void *b, int rows, int cols) {
+    if (!ctx) return VSLAM_E_INVALID;
+    if (!a || !b) VS_FAIL(ctx, VSLAM_E_INVALID, "null buffer");
+    if (rows <= 0 || cols <= 0 || rows > (1 << 15) || cols > (1 << 15)) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return VSLAM_OK;
+}
+
+int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst, size_t dst_pitch) {
+    VS_TRY(stage_check(ctx, src, dst, rows, cols));
+    if (pitch < (size_t)cols || dst_pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch smaller than cols");
+    const size_t n = (size_t)rows * cols, b[2] = {n, n};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    VS_CUDA(ctx, cudaMemcpy2DAsync(d[0], cols, src, pitch, cols, rows, cudaMemcpyHostToDevice, ctx->stream));
+    VS_TRY(launch_blur3(ctx, d[0], rows, cols, cols, d[1], cols));
+    VS_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_pitch, d[1], cols, cols, rows, cudaMemcpyDeviceToHost, ctx->stream));
+    return vslam_sync(ctx);
+}
+
+int vslam_sobel1(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, float *gx, float *gy) {
+    VS_TRY(stage_check(ctx, src, gx ? (void *)gx : (void *)gy, rows, cols));
+    if (pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch smaller than cols");
+    const size_t n = (size_t)rows * cols, b[3] = {n, n * 4, n * 4};
+    u8 *d[3];
+    VS_TRY(stage_scratch(ctx, b, 3, d));
+    VS_CUDA(ctx, cudaMemcpy2DAsync(d[0], cols, src, pitch, cols, rows, cudaMemcpyHostToDevice, ctx->stream));
+    VS_TRY(launch_sobel1(ctx, d[0], rows, cols, cols, gx ? (float *)d[1] : nullptr, gy ? (float *)d[2] : nullptr));
+    if (gx) D2H(gx, d[1], n * 4);
+    if (gy) D2H(gy, d[2], n * 4);
+    return vslam_sync(ctx);
+}
+
+int vslam_harris_response(vslam_ctx *ctx, const float *ix, const float *iy, int rows, int cols, int window, float k, float *response) {
+    VS_TRY(stage_check(ctx, ix, iy, rows, cols));
+    if (!response || window < 1 || !(window & 1) || window > 31) VS_FAIL(ctx, VSLAM_E_INVALID, "window %d", window);
+    const size_t n = (size_t)rows * cols * 4, b[3] = {n, n, n};
+    u8 *d[3];
+    VS_TRY(stage_scratch(ctx, b, 3, d));
+    H2D(d[0], ix, n); H2D(d[1], iy, n);
+    VS_TRY(launch_harris_grad(ctx, (float *)d[0], (float *)d[1], rows, cols, (window - 1) / 2, k, (float *)d[2]));
+    D2H(response, d[2], n);
+    return vslam_sync(ctx);
+}
+
+int vslam_convert_scale_abs(vslam_ctx *ctx, const float *src, int rows, int cols, uint8_t *dst) {
+    VS_TRY(stage_check(ctx, src, dst, rows, cols));
+    const size_t n = (size_t)rows * cols, b[2] = {n * 4, n};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    H2D(d[0], src, n * 4);
+    VS_TRY(launch_cvtabs(ctx, (float *)d[0], n, d[1]));
+    D2H(dst, d[1], n);
+    return vslam_sync(ctx);
+}
+
+int vslam_nms3(vslam_ctx *ctx, const uint8_t *r8, int rows, int cols, uint8_t *mask) {
+    VS_TRY(stage_check(ctx, r8, mask, rows, cols));
+    const size_t n = (size_t)rows * cols, b[2] = {n, n};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    H2D(d[0], r8, n);
+    VS_TRY(launch_nms3(ctx, d[0], rows, cols, d[1]));
+    D2H(mask, d[1], n);
+    return vslam_sync(ctx);
+}
+
+int vslam_nms2(vslam_ctx *ctx, const float *response, int rows, int cols, int window, float *out_map) {
+    VS_TRY(stage_check(ctx, response, out_map, rows, cols));
+    if (window < 1 || !(window & 1) || window > 31) VS_FAIL(ctx, VSLAM_E_INVALID, "window %d", window);
+    const size_t n = (size_t)rows * cols * 4, b[2] = {n, n};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    H2D(d[0], response, n);
+    VS_TRY(launch_nms2(ctx, (float *)d[0], rows, cols, (window - 1) / 2, (float *)d[1]));
+    D2H(out_map, d[1], n);
+    return vslam_sync(ctx);
+}
+
+int vslam_dog_detect_octave(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_dog_params *params,
+                            int apply_edge, vslam_keypoint *out, int capacity, int *count) {
+    if (!ctx || !pyr || capacity < 0 || (!out && capacity > 0) || !count) return VSLAM_E_INVALID;
+    if (frame < 0 || frame >= pyr->n_frames || octave < 0 || octave >= pyr->num_octaves) VS_FAIL(ctx, VSLAM_E_INVALID, "frame %d / octave %d out of range", frame, octave);
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    vslam_dog_params dp;
+    VS_TRY(check_dog_params(ctx, params, &dp));
+    Geometry g;
+    g.num_octaves = pyr->num_octaves; g.frame_bytes = pyr->frame_bytes;
+    for (int o = 0; o < g.num_octaves; ++o) {
+        g.orows[o] = pyr->orows[o]; g.ocols[o] = pyr->ocols[o]; g.opitch[o] = pyr->opitch[o]; g.ooff[o] = pyr->ooff[o];
+        g.oplane[o] = pyr->oplane[o];
+    }
+    int seg_base[16];
+    const size_t n_seg = detect_segments(g, dp.window, seg_base);
+    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256)));
+    VS_TRY(reserve_counters(ctx, 1));
+    if (ctx->out_dev.reserve(sizeof(vslam_keypoint) * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device keypoint list");
+    vslam_keypoint *d_out = ctx->out_dev.as<vslam_keypoint>();
+    VS_TRY(detect_frame(ctx, g, pyr->maps.as<u8>() + pyr->frame_bytes * frame, dp, seg_base, n_seg, d_out, capacity, 0, nullptr, octave, apply_edge));
+    long long total = 0;
+    VS_TRY(finish_counts(ctx, 1, capacity, count, &total));
+    return emit_list(ctx, out, VSLAM_HOST, d_out, sizeof(vslam_keypoint), total, capacity);
+}
+
+int vslam_edge_responses(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *keypoints, int n,
+                         float *responses) {
+    if (!ctx || !pyr || n < 0 || (n > 0 && (!keypoints || !responses))) return VSLAM_E_INVALID;
+    if (frame < 0 || frame >= pyr->n_frames || octave < 0 || octave >= pyr->num_octaves) VS_FAIL(ctx, VSLAM_E_INVALID, "frame %d / octave %d out of range", frame, octave);
+    if (n == 0) return VSLAM_OK;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t b[3] = {sizeof(vslam_keypoint) * (size_t)n, 4 * (size_t)n, 6 * sizeof(void *)};
+    u8 *d[3];
+    VS_TRY(stage_scratch(ctx, b, 3, d));
+    const u8 *gl[6];
+    for (int l = 0; l < 6; ++l) gl[l] = pyr->plane(frame, octave, 1 + l);
+    H2D(d[0], keypoints, b[0]);
+    H2D(d[2], gl, b[2]);
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));           // gl lives on this stack frame
+    VS_TRY(launch_edge_list(ctx, (const vslam_keypoint *)d[0], n, (const u8 *const *)d[2], pyr->orows[octave], pyr->ocols[octave],
+                            pyr->opitch[octave], (float *)d[1]));
+    D2H(responses, d[1], b[1]);
+    return vslam_sync(ctx);
+}
+
+int vslam_localize(vslam_ctx *ctx, const int32_t *candidates, int n, float *dog_zhat) {
+    if (!ctx || n < 0 || (n > 0 && (!candidates || !dog_zhat))) return VSLAM_E_INVALID;
+    if (n == 0) return VSLAM_OK;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t b[2] = {16 * (size_t)n, 4 * (size_t)n};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    H2D(d[0], candidates, b[0]);
+    VS_TRY(launch_localize_list(ctx, (const int *)d[0], n, (float *)d[1]));
+    D2H(dog_zhat, d[1], b[1]);
+    return vslam_sync(ctx);
+}
+
+int vslam_edge_from_windows(vslam_ctx *ctx, const float *gx, const float *gy, int n, int window_len, float *responses, float *sums) {
+    if (!ctx || n < 0 || window_len <= 0 || (n > 0 && (!gx || !gy || (!responses && !sums)))) return VSLAM_E_INVALID;
+    if (n == 0) return VSLAM_OK;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t w = 4 * (size_t)n * window_len, b[4] = {w, w, 4 * (size_t)n, 12 * (size_t)n};
+    u8 *d[4];
+    VS_TRY(stage_scratch(ctx, b, 4, d));
+    H2D(d[0], gx, w); H2D(d[1], gy, w);
+    VS_TRY(launch_edge_windows(ctx, (const float *)d[0], (const float *)d[1], n, window_len, responses ? (float *)d[2] : nullptr,
+                               sums ? (float *)d[3] : nullptr));
+    if (responses) D2H(responses, d[2], b[2]);
+    if (sums) D2H(sums, d[3], b[3]);
+    return vslam_sync(ctx);
+}
+#undef H2D
+#undef D2H
 
 }  // extern "C"

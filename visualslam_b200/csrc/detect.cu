@@ -65,8 +65,11 @@ __global__ void __launch_bounds__(256) dog_detect_k(DetectArgs a) {
             pass_c = zhat > a.contrast_thr;
             if (pass_c) {
                 value = (int)__fmul_rn(zhat, 255.0f);                       // Diff_of_Gauss.cpp:246
-                const float resp = edge_response(a.gauss[level], rows, cols, pitch, i, j, pad);
-                pass_e = resp < a.edge_thr;                                  // :336 (NaN and +inf fail)
+                pass_e = true;
+                if (a.apply_edge) {
+                    const float resp = edge_response(a.gauss[level], rows, cols, pitch, i, j, pad);
+                    pass_e = resp < a.edge_thr;                              // :336 (NaN and +inf fail)
+                }
             }
         }
 #undef PAD_AT

@@ -12,6 +12,7 @@ struct DetectArgs {
     int octave;
     int window, pad;
     float contrast_thr, edge_thr;
+    int apply_edge;                   // 0: stop after FeaturePointLocalization (initialKeypointDetection's own output)
     int ni, nj, nchunks;              // sample rows, sample columns, 256-sample chunks per row
     int seg_base;                     // first segment index of this octave
     int *seg_off, *seg_cnt;

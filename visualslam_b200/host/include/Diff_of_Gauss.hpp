@@ -1,0 +1,35 @@
+// Diff_of_Gauss.hpp -- the DoG free functions of the reference (KeyPointDetection/Diff_of_Gauss.cpp keeps them in the
+// .cpp; promoted to a header so that other code can call them), same names, argument order and results:
+//   SLAM::point                         Diff_of_Gauss.cpp:25-35
+//   computeEdgeResponse                 :79-109
+//   FeaturePointLocalization            :223-251
+//   initialKeypointDetection            :254-297
+//   filterKeypoints                     :301-338   (up to the edge threshold; the orientation stage that follows in the
+//                                                   reference is outside the hot path)
+// All arithmetic runs on the GPU through the C ABI (include/vslam.h); these functions only move data.
+#pragma once
+#include <vector>
+
+#include "GaussPyramid.hpp"
+
+namespace SLAM {
+struct point {
+    point(int row_, int col_, int value_, int padding_, int octave_, int level_)
+        : row(row_), col(col_), value(value_), padding(padding_), octave(octave_), level(level_) {}
+    int row;
+    int col;
+    int value;
+    int padding;
+    int octave;
+    int level;
+};
+}  // namespace SLAM
+
+float computeEdgeResponse(const SLAM::point &keypoint, const Mat &grad_x, const Mat &grad_y);
+bool FeaturePointLocalization(std::vector<Mat> &dogs_padded, std::vector<SLAM::point> &keypoints, int level, SLAM::point &point);
+void initialKeypointDetection(std::vector<SLAM::point> &keypoints, GaussPyramid &pyramid, int octave, int windowSize);
+void filterKeypoints(GaussPyramid &pyramid, int octave, std::vector<SLAM::point> &keypoints, std::vector<SLAM::point> &reducedKeypoints);
+
+// The whole hot path of ./DoG for one image in one call (vslam_dog_keypoints: fused kernels, nothing but keypoints
+// leaves the GPU): every octave's keypoints after the edge threshold, in the reference's order.
+std::vector<SLAM::point> detectKeypoints(Mat &img, int numOctaves, double sigma, int windowSize = 3);

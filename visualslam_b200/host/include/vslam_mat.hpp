@@ -1,0 +1,69 @@
+// vslam_mat.hpp -- the image type of the C++17 host layer.
+//
+// The reference's surface is written against cv::Mat (GaussPyramid.hpp:2-6); OpenCV C++ does not exist on the target
+// box, so the drop-in keeps the reference's names and call shapes on this minimal ref-counted matrix: rows, cols, type
+// (CV_8U / CV_32F only), at<T>(r, c), clone(), zeros(), plus PGM (8U) / PFM (32F) file IO instead of imread/imshow.
+// No arithmetic lives here: every operator of the hot path goes through the C ABI (include/vslam.h).
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace vslam {
+
+constexpr int CV_8U = 0, CV_32F = 5;            // OpenCV's depth codes, so ported call sites read the same
+
+struct Size {
+    int width = 0, height = 0;
+};
+struct Point {
+    int x = 0, y = 0;
+    Point() = default;
+    Point(int x_, int y_) : x(x_), y(y_) {}
+};
+
+class Mat {
+  public:
+    int rows = 0, cols = 0;
+    Mat() = default;
+    Mat(int r, int c, int type) { create(r, c, type); }
+    static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }   // create() zero-fills
+    void create(int r, int c, int type) {
+        if (r < 0 || c < 0 || (type != CV_8U && type != CV_32F)) throw std::invalid_argument("vslam::Mat: bad shape or type");
+        rows = r; cols = c; type_ = type;
+        step = (size_t)c * elemSize();
+        buf_ = std::shared_ptr<uint8_t>(new uint8_t[step * (size_t)r + 1](), std::default_delete<uint8_t[]>());
+        data = buf_.get();
+    }
+    int type() const { return type_; }
+    size_t elemSize() const { return type_ == CV_32F ? 4 : 1; }
+    bool empty() const { return !data || rows == 0 || cols == 0; }
+    Size size() const { return Size{cols, rows}; }
+    size_t total() const { return (size_t)rows * cols; }
+    Mat clone() const {
+        Mat m(rows, cols, type_);
+        if (!empty()) std::memcpy(m.data, data, step * (size_t)rows);
+        return m;
+    }
+    template <class T> T &at(int r, int c) { return *reinterpret_cast<T *>(data + (size_t)r * step + (size_t)c * sizeof(T)); }
+    template <class T> const T &at(int r, int c) const { return *reinterpret_cast<const T *>(data + (size_t)r * step + (size_t)c * sizeof(T)); }
+    template <class T> T *ptr(int r = 0) { return reinterpret_cast<T *>(data + (size_t)r * step); }
+    template <class T> const T *ptr(int r = 0) const { return reinterpret_cast<const T *>(data + (size_t)r * step); }
+
+    uint8_t *data = nullptr;
+    size_t step = 0;                              // bytes between rows (dense)
+
+  private:
+    int type_ = CV_8U;
+    std::shared_ptr<uint8_t> buf_;
+};
+
+// headless IO: binary PGM (P5, 8U) and PFM (Pf, little endian, 32F; rows stored top to bottom with a negative scale)
+Mat imread_pgm(const std::string &path);                 // throws std::runtime_error
+void imwrite_pgm(const std::string &path, const Mat &m);
+void imwrite_pfm(const std::string &path, const Mat &m);
+
+}  // namespace vslam

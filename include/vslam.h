@@ -160,6 +160,15 @@ VSLAM_API int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_f
                                   const vslam_pyramid_params *pparams, const vslam_dog_params *dparams,
                                   vslam_keypoint *out, int capacity, int out_space, int *counts);
 
+/* ---- frame upload shared by several calls ------------------------------------------------------------------------ */
+/* Starts the asynchronous, chunked upload of a batch of HOST frames (pinned memory for full PCIe speed) into the
+ * context's ingest buffer and returns its device address, pitch and frame stride.  Pass those with VSLAM_DEVICE to
+ * vslam_dog_keypoints / vslam_harris / vslam_pyramid_build: each call waits per chunk, so kernels on the first frames
+ * overlap the upload of the rest, and one upload serves every call.  Valid until the next call that uploads. */
+VSLAM_API int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
+                                  size_t frame_stride, const uint8_t **d_frames, size_t *d_pitch,
+                                  size_t *d_frame_stride);
+
 /* ---- Harris: main's pre-blur + Sobel, HarrisCorner, convertScaleAbs + NonMaximumSuppression, NMS2
  *      (Harris_corners.cpp:158-164, 31-68, 176-178, 83-129) ------------------------------------------------------ */
 /* Any of response / r8 / mask3 may be NULL (not materialised).  Maps are dense n_frames x rows x cols in `space`.

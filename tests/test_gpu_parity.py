@@ -175,3 +175,19 @@ def test_full_size_properties(ctx):
     hr = ctx.harris(frames[0])
     ref = O.harris(frames[0])
     assert np.array_equal(hr["response"][0], ref["response"]) and hr["counts"] == [len(ref["corners"])]
+
+
+def test_shared_chunked_upload_gives_the_same_lists(ctx):
+    """vslam_upload_frames: one asynchronous chunked upload (several chunks at this size) serves both detectors; the
+    lists equal those of the plain host-frame calls, frame by frame, and a second upload invalidates nothing it should not."""
+    frames = np.stack([synth.frame(i % 8, 720, 1280) for i in range(160)], 0)        # 147 MB -> 3 upload chunks
+    d0 = ctx.dog_keypoints(frames, capacity=1 << 21)
+    h0 = ctx.harris(frames, want_maps=False, capacity=1 << 23)
+    up = ctx.upload(frames)
+    kp_buf = np.zeros((1 << 21, 6), np.int32)
+    d1 = ctx.dog_keypoints(up, out=kp_buf)
+    h1 = ctx.harris(up, want_maps=False, capacity=1 << 23)
+    assert d1["counts"] == d0["counts"] and np.array_equal(d1["keypoints"], d0["keypoints"])
+    assert h1["counts"] == h0["counts"] and np.array_equal(h1["corners"], h0["corners"])
+    # frames are periodic with period 8: so are the per-frame counts
+    assert d0["counts"][:8] == d0["counts"][8:16] and h0["counts"][:8] == h0["counts"][152:160]

@@ -54,7 +54,7 @@ EXPORTS = [
     "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_destroy",
     "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
     "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
-    "vslam_profile", "vslam_profile_read",
+    "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
     "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
     "vslam_dog_detect_octave", "vslam_edge_responses", "vslam_localize", "vslam_edge_from_windows",
@@ -97,6 +97,7 @@ def load():
     L.vslam_dog_keypoints.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(DogParams),
                                       vp, i, i, C.POINTER(i)]
     L.vslam_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(HarrisParams), vp, vp, vp, vp, i, i, C.POINTER(i)]
+    L.vslam_upload_frames.argtypes = [vp, vp, i, i, i, sz, sz, C.POINTER(vp), C.POINTER(sz), C.POINTER(sz)]
     _lib = L
     return L
 
@@ -118,6 +119,8 @@ def gauss_taps(sigma, ksize=None):
 
 def _frames_arg(frames):
     """numpy uint8 [n,h,w] / [h,w] (host) or a torch cuda uint8 tensor (device) -> (ptr, n, h, w, pitch, stride, space, keepalive)."""
+    if isinstance(frames, UploadedFrames):
+        return frames.ptr, frames.n, frames.h, frames.w, frames.pitch, frames.stride, DEVICE, frames
     if isinstance(frames, np.ndarray):
         a = np.ascontiguousarray(frames, np.uint8)
         if a.ndim == 2:
@@ -131,6 +134,13 @@ def _frames_arg(frames):
     t = t.contiguous()
     n, h, w = t.shape
     return t.data_ptr(), n, h, w, w, h * w, DEVICE, t
+
+
+class UploadedFrames:
+    """A batch whose upload was started by Context.upload (vslam_upload_frames): pass it wherever frames are expected."""
+
+    def __init__(self, ptr, n, h, w, pitch, stride, keep):
+        self.ptr, self.n, self.h, self.w, self.pitch, self.stride, self.keep = ptr, n, h, w, pitch, stride, keep
 
 
 class Pyramid:
@@ -222,6 +232,18 @@ class Context:
     def launches(self):
         return load().vslam_launch_count(self.h)
 
+    def upload(self, frames):
+        """Start the chunked asynchronous upload of host frames (numpy uint8 [n,h,w]; pinned memory for full PCIe speed).
+        The returned batch can be passed to dog_keypoints / harris / build_pyramid, which overlap their kernels with
+        the rest of the upload; it stays valid until the next upload on this context."""
+        a = np.ascontiguousarray(frames, np.uint8)
+        if a.ndim == 2:
+            a = a[None]
+        n, h, w = a.shape
+        dptr, dp, ds = C.c_void_p(), C.c_size_t(), C.c_size_t()
+        self._chk(load().vslam_upload_frames(self.h, a.ctypes.data, n, h, w, w, h * w, C.byref(dptr), C.byref(dp), C.byref(ds)))
+        return UploadedFrames(dptr.value, n, h, w, dp.value, ds.value, a)
+
     def build_pyramid(self, frames, num_octaves=4, sigma0=1.6, materialise=0):
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
         pp = PyramidParams(num_octaves, 3, sigma0, materialise)
@@ -251,8 +273,10 @@ class Context:
         pp = PyramidParams(num_octaves, 3, sigma0, 0)
         dp = DogParams(window, contrast_thr, edge_r)
         counts = (C.c_int * n)()
-        if out is None:
-            host = np.zeros(capacity, KEYPOINT_DTYPE)
+        if out is None or isinstance(out, np.ndarray):
+            # a caller-provided host list (e.g. a pinned buffer viewed as KEYPOINT_DTYPE) avoids a pageable copy
+            host = np.zeros(capacity, KEYPOINT_DTYPE) if out is None else out.view(KEYPOINT_DTYPE).reshape(-1)
+            capacity = host.shape[0]
             optr, ospace = host.ctypes.data, HOST
         else:
             host = None
@@ -266,7 +290,7 @@ class Context:
         return {"keypoints": host[:min(sum(cl), capacity)] if host is not None else out, "counts": cl,
                 "overflow": rc == E_CAPACITY}
 
-    def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None):
+    def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None, corners_out=None):
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
         hp = HarrisParams(k, nms2_window)
         counts = (C.c_int * n)()
@@ -281,7 +305,8 @@ class Context:
         resp = np.empty((n, h, w), np.float32) if want_maps else None
         r8 = np.empty((n, h, w), np.uint8) if want_maps else None
         m3 = np.empty((n, h, w), np.uint8) if want_maps else None
-        corners = np.zeros(capacity, CORNER_DTYPE)
+        corners = np.zeros(capacity, CORNER_DTYPE) if corners_out is None else corners_out.view(CORNER_DTYPE).reshape(-1)
+        capacity = corners.shape[0]
         p = lambda a: a.ctypes.data if a is not None else None
         rc = load().vslam_harris(self.h, ptr, n, h, w, pitch, stride, space, C.byref(hp), p(resp), p(r8), p(m3),
                                  corners.ctypes.data, capacity, HOST, counts)

@@ -93,6 +93,9 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     for (DevBuf *b : bufs) b->release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->up_ev) cudaEventDestroy(e);
+    if (ctx->up_start) cudaEventDestroy(ctx->up_start);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     free(ctx->h_taps);
     delete ctx;
@@ -217,23 +220,70 @@ static void octave_planes(const Geometry &g, u8 *frame_block, int o, OctavePlane
     }
 }
 
-// Frames that live on the host are copied into ctx->ingest (pitch = multiple of 256); device frames are used in place.
+// Frames that live on the host are copied into ctx->ingest (pitch = multiple of 256) in chunks of about 64 MB on the
+// context's copy stream; device frames are used in place.  Consumers call wait_ingest() before touching a frame range.
 static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int cols, size_t pitch, size_t frame_stride,
                          int space, const u8 **d_frames, size_t *d_pitch, size_t *d_stride) {
     if (!frames || n <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "frames null or n_frames <= 0");
     if (pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch %zu < cols %d", pitch, cols);
     if (n > 1 && frame_stride < pitch * (size_t)rows) VS_FAIL(ctx, VSLAM_E_INVALID, "frame_stride too small");
+    ctx->up_chunks = 0; ctx->up_foff = 0;
     if (space == VSLAM_DEVICE) {
         *d_frames = frames; *d_pitch = pitch; *d_stride = frame_stride;
+        // frames handed out by vslam_upload_frames: their chunks may still be in flight on the copy stream
+        const u8 *b = ctx->ingest.as<u8>();
+        if (ctx->up_total && b && frames >= b && frames < b + ctx->ingest.cap && frame_stride == ctx->up_ds) {
+            ctx->up_chunks = ctx->up_total;
+            ctx->up_foff = (int)((size_t)(frames - b) / ctx->up_ds);
+        }
         return VSLAM_OK;
     }
     const size_t dp = round_up((size_t)cols, 256), ds = dp * (size_t)rows;
     if (ctx->ingest.reserve(ds * (size_t)n)) VS_FAIL(ctx, VSLAM_E_NOMEM, "ingest buffer (%zu bytes)", ds * (size_t)n);
-    for (int f = 0; f < n; ++f)
-        VS_CUDA(ctx, cudaMemcpy2DAsync(ctx->ingest.as<u8>() + ds * f, dp, frames + frame_stride * f, pitch, (size_t)cols,
-                                       (size_t)rows, cudaMemcpyHostToDevice, ctx->stream));
+    if (!ctx->copy_stream) {
+        VS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        VS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->up_start, cudaEventDisableTiming));
+    }
+    int chunk = (int)(((size_t)64 << 20) / ds);
+    if (chunk < 1) chunk = 1;
+    if (chunk > n) chunk = n;
+    const int chunks = (n + chunk - 1) / chunk;
+    while ((int)ctx->up_ev.size() < chunks) {
+        cudaEvent_t e;
+        VS_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->up_ev.push_back(e);
+    }
+    // earlier work on the compute stream may still read the ingest buffer
+    VS_CUDA(ctx, cudaEventRecord(ctx->up_start, ctx->stream));
+    VS_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->up_start, 0));
+    for (int c = 0; c < chunks; ++c) {
+        const int f0 = c * chunk, nf = n - f0 < chunk ? n - f0 : chunk;
+        if (pitch == (size_t)cols && dp == pitch && frame_stride == ds) {
+            VS_CUDA(ctx, cudaMemcpyAsync(ctx->ingest.as<u8>() + ds * f0, frames + frame_stride * f0, ds * (size_t)nf, cudaMemcpyHostToDevice, ctx->copy_stream));
+        } else {
+            for (int f = f0; f < f0 + nf; ++f)
+                VS_CUDA(ctx, cudaMemcpy2DAsync(ctx->ingest.as<u8>() + ds * f, dp, frames + frame_stride * f, pitch, (size_t)cols,
+                                               (size_t)rows, cudaMemcpyHostToDevice, ctx->copy_stream));
+        }
+        VS_CUDA(ctx, cudaEventRecord(ctx->up_ev[c], ctx->copy_stream));
+    }
+    ctx->up_chunk = chunk; ctx->up_chunks = chunks; ctx->up_total = chunks; ctx->up_ds = ds;
     *d_frames = ctx->ingest.as<u8>(); *d_pitch = dp; *d_stride = ds;
     return VSLAM_OK;
+}
+
+// the compute stream waits for the upload of frames [f0, f0 + nf)
+static int wait_ingest(vslam_ctx *ctx, int f0, int nf) {
+    if (!ctx->up_chunks) return VSLAM_OK;
+    f0 += ctx->up_foff;
+    const int c0 = f0 / ctx->up_chunk, c1 = (f0 + nf - 1) / ctx->up_chunk;
+    for (int c = c0; c <= c1 && c < ctx->up_chunks; ++c) VS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->up_ev[c], 0));
+    return VSLAM_OK;
+}
+// frames per compute launch when the input is being uploaded: a few upload chunks, so that kernels start early
+static long long ingest_cap(const vslam_ctx *ctx, long long fb) {
+    if (ctx->up_chunks > 1 && fb > 2LL * ctx->up_chunk) fb = 2LL * ctx->up_chunk;
+    return fb;
 }
 
 // rows A-D for n_frames frames into consecutive blocks laid out by Geometry (frame f at block + f * g.frame_bytes):
@@ -241,6 +291,7 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
 static int build_frames(vslam_ctx *ctx, const Geometry &g, const u8 *frames, int n_frames, int rows, int cols, size_t pitch,
                         size_t stride, u8 *block) {
     const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
+    VS_TRY(wait_ingest(ctx, 0, n_frames));
     for (int f0 = 0; f0 < n_frames; f0 += 32768) {
         const int nf = n_frames - f0 < 32768 ? n_frames - f0 : 32768;
         u8 *blk = block + g.frame_bytes * (size_t)f0;
@@ -513,6 +564,7 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
     long long fb = (long long)(6e9 / (double)(bbytes + spf * 12));
     if (fb > (1LL << 30) / spf) fb = (1LL << 30) / spf;
     if (fb > 32768) fb = 32768;
+    fb = ingest_cap(ctx, fb);
     if (fb > n_frames) fb = n_frames;
     if (fb < 1) fb = 1;
     if (ctx->ws_maps.reserve(bbytes * (size_t)fb)) VS_FAIL(ctx, VSLAM_E_NOMEM, "octave-base workspace (%zu bytes)", bbytes * (size_t)fb);
@@ -536,6 +588,7 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
         if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, n_seg * 4, ctx->stream));
         VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
         u8 *ws = ctx->ws_maps.as<u8>();
+        VS_TRY(wait_ingest(ctx, f0, nf));
         VS_TRY(launch_upsample2x(ctx, d_frames + d_stride * f0, rows, cols, d_pitch, d_stride, ws + boff[0], g.opitch[0], bbytes, nf));
         for (int o = 0; o < g.num_octaves; ++o) {
             FusedArgs a;
@@ -587,6 +640,8 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
         int seg_base[16];
         const size_t n_seg = detect_segments(g, dp.window, seg_base);
         VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256)));
+        VS_TRY(wait_ingest(ctx, 0, n_frames));
+        ctx->up_chunks = 0;
         for (int f = 0; f < n_frames; ++f) {
             VS_TRY(build_frames(ctx, g, d_frames + d_stride * f, 1, rows, cols, d_pitch, d_stride, ctx->ws_maps.as<u8>()));
             VS_TRY(detect_frame(ctx, g, ctx->ws_maps.as<u8>(), dp, seg_base, n_seg, d_out, capacity, f, nullptr));
@@ -612,6 +667,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     const size_t spf = (size_t)rows * n_strips;                  // segments per frame: (row, strip)
     size_t fb = ((size_t)1 << 30) / spf;                         // frames per launch
     if (fb > 32768) fb = 32768;
+    fb = (size_t)ingest_cap(ctx, (long long)fb);
     if (fb > (size_t)n_frames) fb = (size_t)n_frames;
     if (fb < 1) VS_FAIL(ctx, VSLAM_E_INVALID, "image too large for the segment table");
     VS_TRY(seg_prepare(ctx, spf * fb, sizeof(vslam_corner), staging_entries(capacity, (size_t)rows * cols * fb)));
@@ -634,6 +690,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         const int nf = n_frames - f0 < (int)fb ? n_frames - f0 : (int)fb;
         if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, spf * nf * 4, ctx->stream));
         VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
+        VS_TRY(wait_ingest(ctx, f0, nf));
         HarrisArgs a;
         memset(&a, 0, sizeof a);
         a.frames = d_frames + d_stride * f0; a.pitch = d_pitch; a.frame_stride = d_stride;
@@ -655,6 +712,16 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     long long total = 0;
     VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
     return emit_list(ctx, corners, out_space, d_out, sizeof(vslam_corner), total, capacity);
+}
+
+int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride,
+                        const uint8_t **d_frames, size_t *d_pitch, size_t *d_frame_stride) {
+    if (!ctx || !d_frames || !d_pitch || !d_frame_stride) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (rows <= 0 || cols <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
+    VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, VSLAM_HOST, d_frames, d_pitch, d_frame_stride));
+    ctx->up_chunks = 0;                                          // the consumers re-arm the waits from the returned pointer
+    return VSLAM_OK;
 }
 
 // ---- per-function entry points (host buffers; the reference's own function granularity, stages.cu) --------------------

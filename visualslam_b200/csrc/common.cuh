@@ -52,6 +52,14 @@ struct vslam_ctx {
     vslam::DevBuf ws_maps;         // octave bases of a chunk of frames (or all planes of one frame)
     vslam::DevBuf out_dev;         // device output list when the caller's list is on the host
     vslam::DevBuf maps_dev;        // device response/r8/mask when the caller's maps are on the host
+    // host frames are uploaded in chunks on a second stream; compute on chunk c waits for up_ev[c] only, so the upload
+    // of later chunks overlaps the kernels of earlier ones
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t up_start = nullptr;
+    std::vector<cudaEvent_t> up_ev;
+    int up_chunk = 0, up_chunks = 0;   // frames per upload chunk, chunks in flight (0: frames were already on the device)
+    int up_total = 0, up_foff = 0;     // chunks of the last upload; first uploaded frame the current call looks at
+    size_t up_ds = 0;                  // bytes between uploaded frames
     void *pinned = nullptr;        // small pinned host scratch for counters
     size_t pinned_cap = 0;
     // cached tap tables of the fused octave kernel (passed by value as kernel parameters)

@@ -25,7 +25,8 @@ sys.path.insert(0, ROOT)
 
 WORKLOADS = {"1080p": (1080, 1920, 256), "4k": (2160, 3840, 64), "8k": (4320, 7680, 16)}
 MAC_PER_PX = 1738.0            # blur MACs per input pixel (both passes, 4 octaves x 6 levels)
-ALU_PEAK_T = 18.58             # measured IDP.4A / IDP.2A peak, T lane-instr/s (tools/alu_peak.cu, profiles/alu_peak_r1.json)
+IMMA_PEAK_TMAC = 568.9         # measured mma.sync.m16n8k32 u8 peak, TMAC/s (tools/imma_peak.cu, profiles/imma_peak_r1.json)
+IDP_PEAK_TMAC = (74.31, 37.13)  # measured dp4a / dp2a peaks, TMAC/s (tools/alu_peak.cu, profiles/alu_peak_r1.json)
 KP_CAP_PER_MPX = 40000         # output list capacity (entries per input Mpix), generous: ~1.2k/Mpx expected
 METRIC = "Mpix/s (frames/s) DoG+Harris at 1/2/4/8 B200; % HBM roofline vs host CPU"
 
@@ -55,7 +56,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([c.strip() for c in o.split(",")])
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.05)
 
     def summary(self):
         self.stop_flag = True
@@ -139,7 +140,7 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="1080p", choices=list(WORKLOADS))
     ap.add_argument("--frames", type=int, default=0, help="frames per GPU per step (default: workload's)")
@@ -172,7 +173,9 @@ def main():
     ctx = vs.Context(local, stream=stream.cuda_stream)
 
     # ---- inputs: 8 unique frames cycled; device-resident copy + pinned host copy ----
-    uniq = [synth.frame(8 * rank + i, h, w) for i in range(min(8, nf))]
+    from visualslam_b200 import shard
+    ids = shard.weak_batch(rank, world, nf)                      # this rank's frames of the global batch (contiguous block)
+    uniq = [synth.frame(ids[0] + i, h, w) for i in range(min(8, nf))]
     host = torch.empty((nf, h, w), dtype=torch.uint8, pin_memory=True)
     hnp = host.numpy()
     for i in range(nf):
@@ -271,30 +274,45 @@ def main():
         #   upsample2x_k: read 1 B, write 4 B per input pixel
         oct_px = [4.0 * h * w / 4 ** o for o in range(4)]
         fused_bytes = nf * (sum(oct_px) + sum(oct_px[1:])) / 4 + 24.0 * nk / 4
-        per_launch = {"octave_fused_k": fused_bytes, "harris_fused_k": 6.0 * h * w + 12.0 * nc / max(nf, 1),
+        per_launch = {"octave_fused_k": fused_bytes, "harris_fused_k": 6.0 * h * w * nf + 12.0 * nc,
                       "upsample2x_k": 5.0 * h * w * nf}
         alg = per_launch.get(dom, 0.0)
         ach = alg / 1e9 / (prof[dom]["ms"] / dlaunch * 1e-3) if alg else None
         fused_ms = prof["octave_fused_k"]["ms"]
-        # the Gaussian stack is integer-ALU bound: packed dot-product instructions against the measured
-        # IDP.4A / IDP.2A issue peak (tools/alu_peak.cu on this pool's B200: 18.58 T lane-instr/s)
-        idp_per_px = MAC_PER_PX / 2 / 4 + MAC_PER_PX / 2 / 2          # H pass dp4a + V pass dp2a, exact tap counts
-        idp_s = idp_per_px * px_step * args.steps / (fused_ms * 1e-3) if fused_ms else None
-        line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                            "frac": ach / hbm_peak if ach else None, "traffic": None, "peak_source": peak_src,
+        # The Gaussian stack (1738 MAC per input pixel) runs on the integer tensor pipe as banded-Toeplitz
+        # products (IMMA.16832.U8.U8); useful MAC/s against the measured IMMA issue peak, and against what the packed
+        # dot-product pipe could do at its measured peak (the bound of the dp4a/dp2a kernel this replaced)
+        tmac = MAC_PER_PX * px_step * args.steps / (fused_ms * 1e-3) / 1e12 if fused_ms else None
+        idp_bound = 2.0 / (1.0 / IDP_PEAK_TMAC[0] + 1.0 / IDP_PEAK_TMAC[1])   # half the MACs on dp4a, half on dp2a
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic_r1.json")
+        if os.path.exists(tp):
+            tj = json.load(open(tp))
+            key = f"{args.workload}x{nf}"
+            if key in tj and dom in tj[key]:
+                traffic = tj[key][dom]
+        line["roofline"] = {"bound": "hbm", "kernel": dom + (" (octave_mma_k<NCH>: tensor-pipe blur)" if dom == "octave_fused_k" else ""),
+                            "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                            "frac": ach / hbm_peak if ach else None, "traffic": traffic, "peak_source": peak_src,
                             "mode": "keypoints-only (fused): octave bases are the only maps in HBM",
-                            "note": "octave_fused_k is integer-ALU bound, not HBM bound (1738 MAC per input pixel, SURVEY.md 8(d)): "
-                                    "its meaningful fraction is alu.frac; the HBM fraction is reported because the contract asks for it",
-                            "alu": {"bound": "IDP (dp4a/dp2a) issue", "achieved": idp_s / 1e12 if idp_s else None, "peak": ALU_PEAK_T,
-                                    "unit": "T lane-instr/s", "frac": idp_s / 1e12 / ALU_PEAK_T if idp_s else None,
-                                    "peak_source": "measured with tools/alu_peak.cu on a B200 of this pool (profiles/alu_peak_r1.json)",
-                                    "idp_per_input_px": idp_per_px, "mac_per_input_px": MAC_PER_PX,
-                                    "TMAC_s": MAC_PER_PX * px_step * args.steps / (fused_ms * 1e-3) / 1e12 if fused_ms else None},
+                            "note": "the fused octave kernel is not HBM bound (11.6 algorithmic bytes against 1738 MAC per input pixel, "
+                                    "SURVEY.md 8(d)); the HBM fraction is reported because the contract asks for it, the tensor block says "
+                                    "how far the blur is from the pipe it runs on; the kernel is issue/latency bound (profiles/)",
+                            "tensor": {"pipe": "IMMA.16832.U8.U8 (mma.sync u8 x u8 -> s32), exact integer arithmetic",
+                                       "useful_TMAC_s": tmac, "peak_TMAC_s": IMMA_PEAK_TMAC,
+                                       "frac": tmac / IMMA_PEAK_TMAC if tmac else None,
+                                       "vs_idp_pipe_bound": tmac / idp_bound if tmac else None,
+                                       "idp_pipe_bound_TMAC_s": idp_bound,
+                                       "peak_source": "measured on a B200 of this pool: tools/imma_peak.cu, tools/alu_peak.cu (profiles/*_peak_r1.json)",
+                                       "mac_per_input_px": MAC_PER_PX},
+                            "other_kernels_hbm": {k: {"achieved_GBps": per_launch[k] / 1e9 / (prof[k]["ms"] / max(prof[k]["launches"], 1) * 1e-3),
+                                                      "frac": per_launch[k] / 1e9 / (prof[k]["ms"] / max(prof[k]["launches"], 1) * 1e-3) / hbm_peak}
+                                                  for k in per_launch if k != dom and prof.get(k, {}).get("launches")},
                             "kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in prof.items() if v["launches"]},
                             "kernel_launches_per_step": {k: v["launches"] / args.steps for k, v in prof.items() if v["launches"]},
                             "kernel_share": {k: v["ms"] / tot for k, v in prof.items() if v["launches"]}}
     if not args.no_cpu_baseline:
-        n_sample = 2 if h * w <= 2.1e6 else 1
+        n_sample = 8 if h * w <= 2.1e6 else (2 if h * w <= 8.3e6 else 1)     # 5-15 s of CPU work
         dt, kind, cores, _, _ = cpu_reference_frames([uniq[i] for i in range(min(n_sample, len(uniq)))])
         line["cpu_baseline"] = {"value": min(n_sample, len(uniq)) * h * w / 1e6 / dt, "unit": "Mpix/s", "cores": cores, "kind": kind,
                                 "sample": f"{min(n_sample, len(uniq))} frames of the same workload ({dt:.1f} s of CPU work)"}

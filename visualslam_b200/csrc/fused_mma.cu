@@ -140,13 +140,18 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
     const u8 *tiles = (const u8 *)tiles32;
     u8 *tab = (u8 *)(tiles32 + (N_G + N_D) * TILE_W);
     __shared__ int s_res[3 * MAX_SROW * NS];                 // detector results of one step
-    __shared__ unsigned short s_queue[3 * MAX_SROW * NS];     // samples that need the full localisation
-    __shared__ int s_nq;
+    __shared__ int s_any[2];                                  // step parity -> the step's detector left work for run_queue / emit
     __shared__ float s_div[511];                              // float(i - 255) / 255f, the reference's divisions
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // special registers are read once through volatile asm: under the 128-register cap the compiler otherwise re-reads
+    // them (S2R, long latency) inside the marching loop
+    int tid, strip, seg, frame;
+    asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));
+    asm volatile("mov.u32 %0, %%ctaid.x;" : "=r"(strip));
+    asm volatile("mov.u32 %0, %%ctaid.y;" : "=r"(seg));
+    asm volatile("mov.u32 %0, %%ctaid.z;" : "=r"(frame));
+    const int lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
-    const int strip = blockIdx.x, seg = blockIdx.y, frame = blockIdx.z;
     const int rows = a.rows, cols = a.cols;
     const int X0 = strip * FWO, X0c = X0 - 2, xs = X0c - T.rmax;
     const int xs16 = xs & ~15;                   // staged rows start on a 16-byte boundary of the plane
@@ -190,7 +195,7 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
             }
     }
     for (int i = tid; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
-    if (tid == 0) s_nq = 0;
+    if (tid < 2) s_any[tid] = 0;
 
     constexpr int DT0 = N_G * TILE_W * 4;                                     // byte offset of the first D tile
     constexpr int LS = TILE_W * 4;                                            // bytes between tiles
@@ -213,11 +218,11 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
             }
         return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // Diff_of_Gauss.cpp:336
     };
-    // queued samples of the step whose tiles start at row yb: FeaturePointLocalization's full sequence, all lanes busy
-    auto run_queue = [&](int yb, int si_lo) {
-        const int nq = s_nq;
-        for (int i = tid; i < nq; i += NT) {
-            const int s = s_queue[i];
+    // samples marked -2 by the detector (all three derivatives non-zero) of the step whose tiles start at row yb:
+    // FeaturePointLocalization's full sequence
+    auto run_queue = [&](int yb, int si_lo, int n_srow) {
+        for (int s = tid; s < 3 * n_srow * NS; s += NT) {
+            if (s_res[s] != -2) continue;
             const int k = s % NS, tt = s / NS;
             const int level = 1 + tt % 3, sr = tt / 3;
             const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
@@ -230,8 +235,10 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
             const int dx = (int)d[cxm + cy] - (int)d[cxp + cy], dy = (int)d[cx + cym] - (int)d[cx + cyp];
             const int ds = (int)d[cx + cy - LS] - (int)d[cx + cy + LS];
             const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
+            int res = -1;
             if (zhat > a.contrast_thr && edge_pass(level, xc, yc, yb))               // :245
-                s_res[s] = (int)__fmul_rn(zhat, 255.0f);                             // :246
+                res = (int)__fmul_rn(zhat, 255.0f);                                  // :246
+            s_res[s] = res;
         }
     };
     // ordered emission: one warp per segment (level, sample row, strip) of a finished step
@@ -301,15 +308,24 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
     }
     const u32 hlane = 16 * (4 * warp + t), vlane = 16 * (8 * vcb + g);        // column part of the plane addresses
     const int wi0 = (8 * vcb + g) * TRP + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
+    // detector: thread = (sample column det_k, sample row det_sr of the step)
+    const int det_k = tid % NS, det_sr = tid / NS;                            // 256 threads: rows 0 .. 12 (at most 12 are live)
+    const int det_xc = X0 + 3 * det_k;
+    const bool det_colok = det_xc <= cols - 2;
+    const int det_cx = tcol(det_xc - X0c), det_cxm = det_xc > 0 ? tcol(det_xc - X0c - 1) : det_cx;
+    const int det_cxp = det_xc + 1 < cols ? tcol(det_xc - X0c + 1) : det_cx;
     // Per step three barriers.  Small jobs of the PREVIOUS step ride along with the two blur passes:
     //   P1 (after B1)  H pass of step c            + queued localisations of step c-1 (its tiles are still intact)
     //   P2 (after B2)  V pass of step c -> tiles   + ordered emission of step c-1, prefetch of step c+1's base rows
     //   P3 (after B3)  detector tests of step c, decimated level 3 -> next base
     int p_y0 = 0, p_si_lo = 0, p_nsrow = 0;                                   // the previous step's detector state
-    for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
+    int par = 0;                                                              // step parity
+    for (int y0 = yv - K * FR; y0 < ye; y0 += FR, par ^= 1) {
         const bool do_v = y0 >= yv;
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();                                                      // B1: staged rows landed; P3 of c-1 done
+        const bool p_work = p_nsrow && s_any[par ^ 1];                        // the previous step found candidates worth a second look
+        if (tid == 0) s_any[par] = 0;                                         // this step's flag (set in P3, two barriers from here)
         // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
         // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them
         {
@@ -349,7 +365,7 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
                 hoff[l] = min(nx, nx - ring);
             }
         }
-        if (p_nsrow) run_queue(p_y0, p_si_lo);
+        if (p_work) run_queue(p_y0, p_si_lo, p_nsrow);
         __syncthreads();                                                      // B2
         if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
         // ---- 3. V pass + rounding + DoG -> tiles, levels in order ----
@@ -417,12 +433,12 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
             const u32 ring = (u32)T.lv[l].np * (PPW * 4), nx = voff[l] + 4 * (PPW * 4);
             voff[l] = min(nx, nx - ring);
         }
-        if (p_nsrow) emit(p_si_lo, p_nsrow);
-        if (tid == 0) s_nq = 0;
+        if (p_work) emit(p_si_lo, p_nsrow);
         __syncthreads();                                                      // B3
-        // ---- 4a. detector, test.  Thread = (sample column, level), marching over the step's sample rows.  Result per
-        // sample in s_res: the keypoint's value, or -1; samples whose three derivatives are all non-zero need the full
-        // 3x3 inverse (rare) and are queued for P1 of the next step.
+        // ---- 4a. detector, test.  Thread = one grid position (sample column, sample row) for the three levels: the five
+        // DoG levels' 2 x 2 windows are read once, their minima / maxima shared by the levels.  Result per sample in s_res:
+        // the keypoint's value, -1, or -2 for samples whose three derivatives are all non-zero: those need the full 3x3
+        // inverse (rare) and are finished by run_queue in P1 of the next step.
         const bool own_step = do_v && y0 >= ys;
         int si_lo = 0, n_srow = 0;
         if (own_step && a.detect) {
@@ -431,59 +447,66 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
             si_lo = (yc_lo + 2) / 3;
             n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
             if (n_srow < 0) n_srow = 0;
-            constexpr int NG = NT / (3 * NS);                                 // sample-row groups
-            if (tid < NG * 3 * NS) {
-                const int id = tid % (3 * NS), grp = tid / (3 * NS);
-                const int k = id % NS, level = 1 + id / NS;
-                const int xc = X0 + 3 * k, x = xc - X0c;
-                const bool colok = xc <= cols - 2;
-                const int cx = tcol(x), cxm = xc > 0 ? tcol(x - 1) : cx, cxp = xc + 1 < cols ? tcol(x + 1) : cx;
-                const u8 *d = tiles + DT0 + level * LS;
-                for (int sr = grp; sr < n_srow; sr += NG) {
-                    const int yc = 3 * (si_lo + sr);
-                    const int s = (sr * 3 + level - 1) * NS + k;
-                    int res = -1;
-                    if (colok) {
-                        // D tile of DoG `level` at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
-                        const int ty = yc - y0 + 4;
-                        const int cy = trow(ty), cym = yc > 0 ? trow(ty - 1) : cy, cyp = yc + 1 < rows ? trow(ty + 1) : cy;
-                        const int c = d[cx + cy];
-                        const int a0 = d[cxm + cym], a1 = d[cx + cym], a2 = d[cxm + cy];                                  // level
-                        const int b0 = d[cxm + cym - LS], b1 = d[cx + cym - LS], b2 = d[cxm + cy - LS], b3 = d[cx + cy - LS];   // level - 1
-                        const int c0 = d[cxm + cym + LS], c1 = d[cx + cym + LS], c2 = d[cxm + cy + LS], c3 = d[cx + cy + LS];   // level + 1
-                        const int mn = min(min(min(a0, a1), min(a2, c)), min(min(min(b0, b1), min(b2, b3)), min(min(c0, c1), min(c2, c3))));
-                        const int mx = max(max(max(a0, a1), max(a2, c)), max(max(max(b0, b1), max(b2, b3)), max(max(c0, c1), max(c2, c3))));
-                        if (c == mn || c == mx) {                                            // Diff_of_Gauss.cpp:287
-                            const int dx = a2 - (int)d[cxp + cy], dy = a1 - (int)d[cx + cyp], ds = b3 - c3;   // :226-228
+            if (det_sr < n_srow) {
+                const int yc = 3 * (si_lo + det_sr);
+                int res[3] = {-1, -1, -1};
+                if (det_colok) {
+                    // D tiles at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
+                    const int ty = yc - y0 + 4;
+                    const int cy = trow(ty), cym = yc > 0 ? trow(ty - 1) : cy, cyp = yc + 1 < rows ? trow(ty + 1) : cy;
+                    const u8 *d = tiles + DT0;
+                    int w00[5], w01[5], w10[5], w11[5], mn[5], mx[5];
+#pragma unroll
+                    for (int l = 0; l < 5; ++l) {
+                        w00[l] = d[l * LS + det_cxm + cym]; w01[l] = d[l * LS + det_cx + cym];
+                        w10[l] = d[l * LS + det_cxm + cy]; w11[l] = d[l * LS + det_cx + cy];
+                        mn[l] = min(min(w00[l], w01[l]), min(w10[l], w11[l]));
+                        mx[l] = max(max(w00[l], w01[l]), max(w10[l], w11[l]));
+                    }
+                    bool any = false;
+#pragma unroll
+                    for (int level = 1; level <= 3; ++level) {
+                        const int c = w11[level];
+                        const int lo3 = min(min(mn[level - 1], mn[level]), mn[level + 1]);
+                        const int hi3 = max(max(mx[level - 1], mx[level]), mx[level + 1]);
+                        if (c == lo3 || c == hi3) {                                          // Diff_of_Gauss.cpp:287
+                            const int dx = w10[level] - (int)d[level * LS + det_cxp + cy];   // :226-228
+                            const int dy = w01[level] - (int)d[level * LS + det_cx + cyp];
+                            const int ds = w11[level - 1] - w11[level + 1];
                             if (dx == 0 || dy == 0 || ds == 0) {
                                 // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the
                                 // host with the same float ops: a.cmin, a.val_lut)
-                                if (c >= a.cmin && edge_pass(level, xc, yc, y0)) res = a.val_lut[c];
+                                if (c >= a.cmin && edge_pass(level, det_xc, yc, y0)) { res[level - 1] = a.val_lut[c]; any = true; }
                             } else {
-                                s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)s;
+                                res[level - 1] = -2;
+                                any = true;
                             }
                         }
                     }
-                    s_res[s] = res;
+                    if (any) s_any[par] = 1;
                 }
+#pragma unroll
+                for (int level = 1; level <= 3; ++level) s_res[(det_sr * 3 + level - 1) * NS + det_k] = res[level - 1];
             }
         }
-        // ---- 4b. next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126) = byte 0 of the words ----
-        if (own_step && a.next_base) {
-            u8 *nb = a.next_base + (size_t)frame * a.next_stride;
-            for (int i = tid; i < (FWO / 2) * (FR / 2); i += NT) {
-                const int oc = i % (FWO / 2), w = i / (FWO / 2);
-                const int ox = X0 / 2 + oc, oy = (y0 >> 1) + w;
-                if (ox < a.next_cols && oy < a.next_rows)
-                    nb[(size_t)oy * a.next_pitch + ox] = (u8)tiles32[2 * TILE_W + (oc + 1) * TRP + 2 + w];
+        // ---- 4b. next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126) = byte 0 of the words;
+        // thread = (row, pair of output columns): the strip's 30 columns start on an even column of the next base ----
+        if (own_step && a.next_base && tid < (FWO / 4) * (FR / 2)) {
+            const int oc = 2 * (tid % (FWO / 4)), w = tid / (FWO / 4);
+            const int ox = X0 / 2 + oc, oy = (y0 >> 1) + w;
+            if (oy < a.next_rows && ox < a.next_cols) {
+                const u32 v0 = tiles32[2 * TILE_W + (oc + 1) * TRP + 2 + w], v1 = tiles32[2 * TILE_W + (oc + 2) * TRP + 2 + w];
+                u8 *dst = a.next_base + (size_t)frame * a.next_stride + (size_t)oy * a.next_pitch + ox;
+                if (ox + 1 < a.next_cols) *(u16 *)dst = (u16)((v0 & 0xffu) | (v1 & 0xffu) << 8);
+                else *dst = (u8)v0;
             }
         }
         p_y0 = y0; p_si_lo = si_lo; p_nsrow = n_srow;
     }
     // drain: the last step's queue and emission
     __syncthreads();
-    if (p_nsrow) {
-        run_queue(p_y0, p_si_lo);
+    if (p_nsrow && s_any[par ^ 1]) {
+        run_queue(p_y0, p_si_lo, p_nsrow);
         __syncthreads();
         emit(p_si_lo, p_nsrow);
     }

@@ -22,6 +22,9 @@ namespace vslam {
 
 constexpr int HS = kHarrisStrip, HB = kHarrisBand;
 constexpr int H_WARPS = 4;                 // warps per CTA, each an independent (strip, band)
+#ifndef HARRIS_MIN_CTAS
+#define HARRIS_MIN_CTAS 4        // <= 128 registers: 16 warps per SM (4.68 -> 4.06 ms per 1080p x 256; 5 or 6 CTAs spill and lose)
+#endif
 constexpr int H_CAP = 256;                 // staged corners per warp before a flush
 constexpr int H_ROWS = 8;                  // rows per flush
 
@@ -34,7 +37,7 @@ __device__ __forceinline__ int r8_of(float r) {
 }
 
 template <int P2>
-__global__ void __launch_bounds__(32 * H_WARPS) harris_march_k(const HarrisArgs a) {
+__global__ void __launch_bounds__(32 * H_WARPS, HARRIS_MIN_CTAS) harris_march_k(const HarrisArgs a) {
     __shared__ vslam_corner s_buf[H_WARPS][H_CAP];
     __shared__ int s_rowoff[H_WARPS][H_ROWS], s_rowcnt[H_WARPS][H_ROWS];
     const unsigned FULL = 0xffffffffu;

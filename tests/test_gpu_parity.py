@@ -97,6 +97,36 @@ def test_dog_keypoints_synthetic_vs_oracle(ctx):
         start += n
 
 
+@pytest.mark.parametrize("sigma0,octaves", [(1.2, 4), (1.9, 3), (0.9, 4)])
+def test_dog_keypoints_other_sigma_vs_oracle(ctx, sigma0, octaves):
+    """sigma0 != 1.6: the tensor-pipe kernel's run-time geometry (the default pyramid runs compile-time instantiations)."""
+    frames = np.stack([synth.frame(i, 200, 333) for i in (1, 5)], 0)
+    res = ctx.dog_keypoints(frames, num_octaves=octaves, sigma0=sigma0)
+    start = 0
+    for f in range(len(frames)):
+        kc, _, _ = O.dog_keypoints(frames[f], num_octaves=octaves, sigma0=sigma0)
+        n = res["counts"][f]
+        assert n == len(kc), f
+        assert np.array_equal(kp_array(res["keypoints"][start:start + n]), kc), f
+        start += n
+
+
+def test_dog_keypoints_kernel_variants_agree(tmp_path):
+    """VSLAM_MMA_STATIC=0 (run-time geometry) and VSLAM_FUSED_MMA=0 (dp4a/dp2a kernel) give the default kernels' lists."""
+    import subprocess, sys, os
+    code = ("import numpy as np, sys; import visualslam_b200 as vs; from visualslam_b200 import synth;"
+            "f = np.stack([synth.frame(i, 540, 960) for i in range(8)], 0); c = vs.Context(0);"
+            "r = c.dog_keypoints(f); np.save(sys.argv[1], np.asarray(r['keypoints']))")
+    outs = []
+    for i, env in enumerate(({}, {"VSLAM_MMA_STATIC": "0"}, {"VSLAM_FUSED_MMA": "0"})):
+        out = str(tmp_path / f"k{i}.npy")
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        subprocess.check_call([sys.executable, "-c", code, out], env={**os.environ, **env, "PYTHONPATH": root}, timeout=600)
+        outs.append(np.load(out))
+    assert len(outs[0]) > 1000
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
 def test_dog_capacity_overflow(ctx, images):
     img = image_for(images, "building", "cvt")
     res = ctx.dog_keypoints(img, capacity=100)

@@ -21,6 +21,8 @@
 #include <math.h>
 #include <string.h>
 
+#include <algorithm>
+
 #include "detect_math.cuh"
 #include "fused_mma.cuh"
 
@@ -28,7 +30,7 @@ namespace vslam {
 
 namespace {
 constexpr int FW = kFusedW, FWO = kFusedWO, FR = kFusedR;
-constexpr int PPW = 4 * (FW / 2) + 8;       // words per quad PAIR of an h plane: 32 column pairs x 16 bytes, + 8 (== 8 mod 32: conflict-free LDS.128)
+constexpr int PPW = kMmaPPW;                // words per quad PAIR of an h plane
 constexpr int TRP = 20;                     // words per column pair of a tile: 2 history + 16 row pairs (+2: conflict-free STS)
 constexpr int TILE_W = (FW / 2) * TRP;      // words per tile
 constexpr int N_G = 3, N_D = 5;             // G tiles: Gaussian levels 1..3; D tiles: DoG levels 0..4
@@ -43,7 +45,7 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
     memset(out, 0, sizeof *out);
     int32_t t[kMaxKsize];
     const double k = pow(2.0, 1.0 / (double)scale_samples);          // GaussPyramid.hpp:69
-    int rmin = 1 << 30, rmax = 0, poff = 0, toff = 0;
+    int rmin = 1 << 30, rmax = 0, poff = 0;
     for (int l = 0; l < 6; ++l) {
         const double sig = pow(2, octave) * sigma0 * pow(k, l);      // GaussPyramid.cpp:157
         const int n = host_gauss_ksize(sig);
@@ -71,11 +73,25 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
         if (lv.np < 8) lv.np = 8;                                    // single-step wrap of every slot computation (needs >= 6)
         lv.plane_off = poff;
         poff += 2 * lv.np * PPW;
-        lv.tab_off = toff;
-        lv.tab_cp = (kMmaPadL + 32 * lv.ksv + 48 + 3) & ~3;          // V pass reads up to idx 32 ksv + 31; H pass up to n + 77
-        if (lv.tab_cp < ((kMmaPadL + n + kMmaPadR + 3) & ~3)) lv.tab_cp = (kMmaPadL + n + kMmaPadR + 3) & ~3;
-        lv.tab_cp += 32;                                             // copies 32 bytes apart modulo 128: fewer bank conflicts
-        toff += 4 * lv.tab_cp;
+    }
+    // tap copies (fused_mma.cuh): the left pad covers the H pass's chunks in front of the band, padl + r == 0 (mod 4)
+    out->nch = (8 + 2 * rmax + 31) / 32 + 1;
+    int cp = 0;
+    for (int l = 0; l < 6; ++l) {
+        MmaLevel &lv = out->lv[l];
+        lv.padl = rmax - lv.r + 41 + (4 - (rmax + 41) % 4) % 4;
+        const int need_h = lv.padl + lv.r - rmax + 12 + 32 * (out->nch - 1) + 20;
+        const int need_v = lv.padl + 24 + 32 * (lv.ksv - 1) + 8;
+        const int need_t = lv.padl + lv.n + 3;
+        cp = std::max(cp, std::max(need_h, std::max(need_v, need_t)));
+    }
+    cp = (cp + 3) & ~3;
+    while (cp % 128 != 32) cp += 4;                                  // copies 32 bytes apart modulo 128: fewer bank conflicts
+    out->cp = cp;
+    for (int l = 0; l < 6; ++l) {
+        MmaLevel &lv = out->lv[l];
+        lv.tab_hoff = 4 * cp * l + lv.padl + lv.r;
+        lv.tab_voff = 4 * cp * l + lv.padl - lv.sv - rmax % 4;
     }
     out->rmin = rmin; out->rmax = rmax;
     out->stage_rows = FR;
@@ -87,7 +103,7 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
             if ((int)(((unsigned)q * (unsigned)out->spq_magic) >> 16) != q / spq) return VSLAM_E_INVALID;
     }
     out->plane_words = poff;
-    out->tab_bytes = (toff + 15) & ~15;
+    out->tab_bytes = (24 * cp + 15) & ~15;
     return VSLAM_OK;
 }
 
@@ -126,17 +142,19 @@ __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1)
 }  // namespace
 
 // NCH = 32-byte chunks of a staged row that the bands of one 8-column block can touch: (8 + 2 rmax + 31) / 32 + 1
-template <int NCH>
-__global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ MmaArgs a) {
+// GEO = the level geometry: MmaStaticGeom<n0..n5> (immediates) or MmaDynGeom (read from the argument)
+template <int NCH, class GEO>
+__global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __grid_constant__ MmaArgs a) {
     constexpr int NT = 256;
     extern __shared__ __align__(16) u32 smem[];
     constexpr int NW = NT / 32;
     constexpr int RBW = 16 / NW;                // 8-row blocks of one 16-column block a warp owns in the V pass
     const MmaTaps &T = a.mt;
-    u32 *planes = smem;
-    u8 *stage = (u8 *)(smem + T.plane_words);
-    const int SP = T.stage_pitch;
-    u32 *tiles32 = (u32 *)(stage + T.stage_rows * SP);
+    const GEO geo(a.mt);
+    u8 *planes = (u8 *)smem;
+    u8 *stage = (u8 *)(smem + geo.plane_words());
+    const int SP = geo.stage_pitch();
+    u32 *tiles32 = (u32 *)(stage + FR * SP);
     const u8 *tiles = (const u8 *)tiles32;
     u8 *tab = (u8 *)(tiles32 + (N_G + N_D) * TILE_W);
     __shared__ int s_res[3 * MAX_SROW * NS];                 // detector results of one step
@@ -153,21 +171,21 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
     const int lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int rows = a.rows, cols = a.cols;
-    const int X0 = strip * FWO, X0c = X0 - 2, xs = X0c - T.rmax;
+    const int X0 = strip * FWO, X0c = X0 - 2, xs = X0c - geo.rmax();
     const int xs16 = xs & ~15;                   // staged rows start on a 16-byte boundary of the plane
     const int cboff = X0c - xs16;                // staged column of the strip's first computed column
     const u8 *__restrict__ base = a.base + (size_t)frame * a.base_stride;
     const int ys = seg * a.seg_rows;
     const int ye = min(ys + a.seg_rows, rows);
     const int yv = seg > 0 ? ys - FR : 0;        // first step with a V pass (one extra step feeds the detector's history)
-    const int K = (2 * T.rmax + FR - 1) / FR;    // warm-up steps: H pass only
+    const int K = (2 * geo.rmax() + FR - 1) / FR;    // warm-up steps: H pass only
 
     // ---- stage base rows y0 + rmax ..., columns xs16 ..., reflect-101 resolved (16-byte cp.async inside the image) ----
-    const int SPQ = SP >> 4, n_stage = T.stage_rows * SPQ;
+    const int SPQ = SP >> 4, n_stage = FR * SPQ;
     auto issue_stage = [&](int y0n) {
         for (int q = tid; q < n_stage; q += NT) {
-            const int row = (int)(((u32)q * (u32)T.spq_magic) >> 16), j = q - row * SPQ;
-            const int y = refl101(y0n + T.rmax + row, rows);
+            const int row = (int)(((u32)q * (u32)geo.spq_magic()) >> 16), j = q - row * SPQ;
+            const int y = refl101(y0n + geo.rmax() + row, rows);
             const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
             u32 *dst = (u32 *)(stage + row * SP) + 4 * (j ^ ((row >> 2) & 7));   // 16-byte groups XOR-swizzled by the row quad
             const int x = xs16 + 16 * j;
@@ -187,11 +205,10 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
     issue_stage(yv - K * FR);
     // ---- tables: four byte-shifted, zero-padded copies of every level's taps; the division table; ring bases ----
     for (int l = 0; l < 6; ++l) {
-        const MmaLevel &lv = T.lv[l];
         for (int s = 0; s < 4; ++s)
-            for (int j = tid; j < lv.tab_cp; j += NT) {
-                const int idx = j + s - kMmaPadL;
-                tab[lv.tab_off + s * lv.tab_cp + j] = (idx >= 0 && idx < lv.n) ? T.taps[l][idx] : (u8)0;
+            for (int j = tid; j < geo.cp(); j += NT) {
+                const int idx = j + s - geo.padl(l);
+                tab[(4 * l + s) * geo.cp() + j] = (idx >= 0 && idx < geo.n(l)) ? T.taps[l][idx] : (u8)0;
             }
     }
     for (int i = tid; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
@@ -277,7 +294,7 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
     const int h_row = 4 * (((lane & 7) >> 1) + 4 * (lane & 1)) + ((lane >> 3) & 1);   // staged row this lane addresses, M block 0
     const u32 stage_sa = (u32)__cvta_generic_to_shared(stage);
     const int hcb = cboff + 8 * warp;                                         // H pass: warp = 8 output columns (staged column hcb ...)
-    const int c_lo = (hcb - T.rmax) >> 5;                                     // first 32-byte chunk any level's band touches
+    const int c_lo = (hcb - geo.rmax()) >> 5;                                     // first 32-byte chunk any level's band touches
     u32 saA[NCH], saB[NCH];                                                   // ldmatrix addresses of the chunks (XOR swizzle resolved)
 #pragma unroll
     for (int ci = 0; ci < NCH; ++ci) {
@@ -286,27 +303,20 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
         saB[ci] = stage_sa + (h_row + 2) * SP + ((ch ^ (((h_row + 2) >> 2) & 7)) << 4);
     }
     // B fragments: b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 ..; H pass idx0 = r + 32 c - hcb + 4 t - g,
-    // V pass (K rows remapped so that a thread's 8 rows are consecutive) b1 = taps idx0 + 4 .., idx0 = 32 k + 8 t - g - sv
-    const u8 *htb[6], *vtb[6];
-    unsigned long long hmask = 0;                                             // bit 6 ci + l: level l's band touches chunk c_lo + ci
+    // V pass (K rows remapped so that a thread's 8 rows are consecutive) b1 = taps idx0 + 4 .., idx0 = 32 k + 8 t - g - sv.
+    // One lane pointer per pass (byte-shifted copy + word offset); the level is an offset (fused_mma.cuh)
+    const int hu = 4 * t - g - hcb + 32 * c_lo, vu = 8 * t - g + geo.rmax() % 4;
+    const u8 *hbase = tab + (hu & 3) * geo.cp() + (hu - (hu & 3));             // two's complement: fine for hu < 0
+    const u8 *vbase = tab + (vu & 3) * geo.cp() + (vu - (vu & 3));
     const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the H chunk this thread's D rows belong to
     const int vcb = warp % 4, vjb = (warp / 4) * RBW;                         // V pass: warp = (16-column block, RBW blocks of 8 rows)
     u32 hoff[6], voff[6];                                                     // ring byte offsets: H store slot, V window start (row block vjb)
 #pragma unroll
     for (int l = 0; l < 6; ++l) {
-        const int p0 = T.lv[l].r - hcb + 4 * t - g + kMmaPadL + 32 * c_lo;
-        htb[l] = tab + T.lv[l].tab_off + (p0 & 3) * T.lv[l].tab_cp + (p0 - (p0 & 3));   // two's complement: fine for p0 < 0
-        const int p1 = 8 * t - g + kMmaPadL - T.lv[l].sv;                     // >= 40 - 7 - 3
-        vtb[l] = tab + T.lv[l].tab_off + (p1 & 3) * T.lv[l].tab_cp + (p1 & ~3);
-#pragma unroll
-        for (int ci = 0; ci < NCH; ++ci) {
-            const int bs = T.lv[l].r + 32 * (c_lo + ci) - hcb;                // tap index of (k = 0, n = 0)
-            if (bs >= -31 && bs <= T.lv[l].n + 6) hmask |= 1ull << (6 * ci + l);
-        }
-        hoff[l] = (u32)((d_pi + T.lv[l].cq) >> 1) * (PPW * 4);                // < np pairs
-        voff[l] = (u32)(vjb + t) * (PPW * 4);
+        // the lane's column part (< one pair row) rides in the ring offsets: the wrap test does not see it
+        hoff[l] = (u32)((d_pi + geo.cq(l)) >> 1) * (PPW * 4) + 16 * (4 * warp + t) + 8 * ((d_pi + geo.cq(l)) & 1);   // < np pairs
+        voff[l] = (u32)(vjb + t) * (PPW * 4) + 16 * (8 * vcb + g);
     }
-    const u32 hlane = 16 * (4 * warp + t), vlane = 16 * (8 * vcb + g);        // column part of the plane addresses
     const int wi0 = (8 * vcb + g) * TRP + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
     // detector: thread = (sample column det_k, sample row det_sr of the step)
     const int det_k = tid % NS, det_sr = tid / NS;                            // 256 threads: rows 0 .. 12 (at most 12 are live)
@@ -327,7 +337,11 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
         const bool p_work = p_nsrow && s_any[par ^ 1];                        // the previous step found candidates worth a second look
         if (tid == 0) s_any[par] = 0;                                         // this step's flag (set in P3, two barriers from here)
         // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
-        // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them
+        // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them.
+        // One basic block, software pipelined by hand: every chunk is multiplied (chunks outside a level's band meet the
+        // zero padding of its tap copies: no band test, no branch), level l + 1's taps are loaded before level l's MMAs
+        // and level l - 1's stores come after them (the compiler cannot hoist a shared load above a shared store it
+        // cannot disambiguate).
         {
             u32 fa[NCH][4], fb[NCH][4];
 #pragma unroll
@@ -337,25 +351,22 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
                 asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                              : "=r"(fb[ci][0]), "=r"(fb[ci][1]), "=r"(fb[ci][2]), "=r"(fb[ci][3]) : "r"(saB[ci]));
             }
-#pragma unroll
-            for (int l = 0; l < 6; ++l) {
-                int acc[2][4];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) (&acc[0][0])[i] = 0;
+            u32 tb[2][NCH][2];
+            int acc[2][2][4];
+            auto load_taps = [&](int l, int buf) {
 #pragma unroll
                 for (int ci = 0; ci < NCH; ++ci) {
-                    if (hmask & (1ull << (6 * ci + l))) {                       // warp-uniform
-                        const u32 b0 = *(const u32 *)(htb[l] + 32 * ci), b1 = *(const u32 *)(htb[l] + 32 * ci + 16);
-                        imma(acc[0], fa[ci][0], fa[ci][1], fa[ci][2], fa[ci][3], b0, b1);
-                        imma(acc[1], fb[ci][0], fb[ci][1], fb[ci][2], fb[ci][3], b0, b1);
-                    }
+                    tb[buf][ci][0] = *(const u32 *)(hbase + geo.tab_hoff(l) + 32 * ci);
+                    tb[buf][ci][1] = *(const u32 *)(hbase + geo.tab_hoff(l) + 32 * ci + 16);
                 }
-                // thread: rows 4 d_pi .. + 3 of columns 2t, 2t + 1 -> low bytes {c0, c1} and high bytes {c0, c1} of one quad,
-                // in the pair-aligned planes (aligned quad Q = q + cq, pair Q >> 1, position Q & 1)
-                const u32 ring = (u32)T.lv[l].np * (PPW * 4);
-                u8 *plo = (u8 *)(planes + T.lv[l].plane_off) + hoff[l] + hlane + 8 * ((d_pi + T.lv[l].cq) & 1);
-                const u32 e01 = __byte_perm(acc[0][0], acc[0][2], 0x5410), e23 = __byte_perm(acc[1][0], acc[1][2], 0x5410);
-                const u32 o01 = __byte_perm(acc[0][1], acc[0][3], 0x5410), o23 = __byte_perm(acc[1][1], acc[1][3], 0x5410);
+            };
+            // thread: rows 4 d_pi .. + 3 of columns 2t, 2t + 1 -> low bytes {c0, c1} and high bytes {c0, c1} of one quad,
+            // in the pair-aligned planes (aligned quad Q = q + cq, pair Q >> 1, position Q & 1)
+            auto h_store = [&](int l, const int (&ac)[2][4]) {
+                const u32 ring = (u32)geo.np(l) * (PPW * 4);
+                u8 *plo = planes + 4 * geo.plane_off(l) + hoff[l];
+                const u32 e01 = __byte_perm(ac[0][0], ac[0][2], 0x5410), e23 = __byte_perm(ac[1][0], ac[1][2], 0x5410);
+                const u32 o01 = __byte_perm(ac[0][1], ac[0][3], 0x5410), o23 = __byte_perm(ac[1][1], ac[1][3], 0x5410);
                 uint2 vl, vh;
                 vl.x = __byte_perm(e01, e23, 0x6420); vh.x = __byte_perm(e01, e23, 0x7531);
                 vl.y = __byte_perm(o01, o23, 0x6420); vh.y = __byte_perm(o01, o23, 0x7531);
@@ -363,7 +374,25 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
                 *(uint2 *)(plo + ring) = vh;
                 const u32 nx = hoff[l] + 4 * (PPW * 4);                       // the next step's chunk is four pairs further on
                 hoff[l] = min(nx, nx - ring);
+            };
+            load_taps(0, 0);
+#pragma unroll
+            for (int l = 0; l < 6; ++l) {
+                const int b = l & 1;
+                if (l < 5) load_taps(l + 1, b ^ 1);
+#pragma unroll
+                for (int ci = 0; ci < NCH; ++ci) {
+                    if (ci == 0) {
+                        imma_c(acc[b][0], fa[ci][0], fa[ci][1], fa[ci][2], fa[ci][3], tb[b][ci][0], tb[b][ci][1], 0);
+                        imma_c(acc[b][1], fb[ci][0], fb[ci][1], fb[ci][2], fb[ci][3], tb[b][ci][0], tb[b][ci][1], 0);
+                    } else {
+                        imma(acc[b][0], fa[ci][0], fa[ci][1], fa[ci][2], fa[ci][3], tb[b][ci][0], tb[b][ci][1]);
+                        imma(acc[b][1], fb[ci][0], fb[ci][1], fb[ci][2], fb[ci][3], tb[b][ci][0], tb[b][ci][1]);
+                    }
+                }
+                if (l > 0) h_store(l - 1, acc[b ^ 1]);
             }
+            h_store(5, acc[1]);
         }
         if (p_work) run_queue(p_y0, p_si_lo, p_nsrow);
         __syncthreads();                                                      // B2
@@ -373,51 +402,25 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
             u32 prev0[RBW], prev1[RBW];                          // previous level, columns 2g and 2g + 1, rows as 16-bit halves
 #pragma unroll
             for (int rb = 0; rb < RBW; ++rb) prev0[rb] = prev1[rb] = 0;
+            {   // rows y0+28 .. y0+31 of the last step become the history of the G and D tiles (before anything is overwritten)
+                const int hrb = 3 - vjb;
+                if (hrb >= 0 && hrb < RBW && t >= 2) {
+                    const int wi = wi0 + 4 * hrb;
+                    u32 hv[N_G + N_D];
 #pragma unroll
-            for (int l = 0; l < 6; ++l) {
-                const u32 ring = (u32)T.lv[l].np * (PPW * 4);                 // bytes of one plane; the high-byte plane follows
-                const u8 *plane = (const u8 *)(planes + T.lv[l].plane_off) + vlane;
-                // pair of (row block j, K step k, lane t): 4i + j + 4k + t; slot = that modulo np
-                u32 off[RBW];
-                off[0] = voff[l];
+                    for (int k2 = 0; k2 < N_G + N_D; ++k2) hv[k2] = tiles32[k2 * TILE_W + wi];
 #pragma unroll
-                for (int rb = 1; rb < RBW; ++rb) {
-                    const u32 nx = off[rb - 1] + PPW * 4;
-                    off[rb] = min(nx, nx - ring);
+                    for (int k2 = 0; k2 < N_G + N_D; ++k2) tiles32[k2 * TILE_W + wi - 16] = hv[k2];
                 }
-                int lo[RBW][4], hi[RBW][4];
-                {   // K step 0 seeds the accumulators: 32768 (rounding) for the low bytes, 0 for the high bytes
-                    const u32 b0 = *(const u32 *)vtb[l], b1 = *(const u32 *)(vtb[l] + 4);
-#pragma unroll
-                    for (int rb = 0; rb < RBW; ++rb) {
-                        const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + ring);
-                        imma_c(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1, 32768);
-                        imma_c(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1, 0);
-                    }
-                }
-#pragma unroll 1
-                for (int k = 1; k < T.lv[l].ksv; ++k) {
-                    const u32 b0 = *(const u32 *)(vtb[l] + 32 * k), b1 = *(const u32 *)(vtb[l] + 32 * k + 4);
-#pragma unroll
-                    for (int rb = 0; rb < RBW; ++rb) {
-                        const u32 nx = off[rb] + 4 * (PPW * 4);
-                        off[rb] = min(nx, nx - ring);            // wrap: nx - ring is huge (unsigned) unless nx >= ring
-                        const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + ring);
-                        imma(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1);
-                        imma(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1);
-                    }
-                }
+            }
+            // (256 hi + lo + 32768) >> 16 lands in byte 2; rows 2t, 2t+1 of a column share a register as 16-bit halves
+            auto v_out = [&](int l, const int (&lo)[RBW][4], const int (&hi)[RBW][4]) {
 #pragma unroll
                 for (int rb = 0; rb < RBW; ++rb) {
-                    // (256 hi + lo + 32768) >> 16 lands in byte 2; rows 2t, 2t+1 of a column share a register as 16-bit halves
                     const u32 v0 = (u32)(hi[rb][0] << 8) + (u32)lo[rb][0], v1 = (u32)(hi[rb][1] << 8) + (u32)lo[rb][1];
                     const u32 v2 = (u32)(hi[rb][2] << 8) + (u32)lo[rb][2], v3 = (u32)(hi[rb][3] << 8) + (u32)lo[rb][3];
                     const u32 c0 = __byte_perm(v0, v1, 0x7632), c1 = __byte_perm(v2, v3, 0x7632);
                     const int wi = wi0 + 4 * rb;
-                    if (vjb + rb == 3 && t >= 2 && l >= 1) {     // rows y0+28 .. y0+31 of the last step become the history
-                        if (l <= 3) tiles32[(l - 1) * TILE_W + wi - 16] = tiles32[(l - 1) * TILE_W + wi];
-                        tiles32[(N_G + l - 1) * TILE_W + wi - 16] = tiles32[(N_G + l - 1) * TILE_W + wi];
-                    }
                     if (l >= 1 && l <= 3) tiles32[(l - 1) * TILE_W + wi] = __byte_perm(c0, c1, 0x6420);
                     if (l >= 1) {
                         const u32 d0 = __vmaxu2(c0, prev0[rb]) - prev0[rb], d1 = __vmaxu2(c1, prev1[rb]) - prev1[rb];   // max(cur - prev, 0)
@@ -425,12 +428,100 @@ __global__ void __launch_bounds__(256, 2) octave_mma_k(const __grid_constant__ M
                     }
                     prev0[rb] = c0; prev1[rb] = c1;
                 }
+            };
+            // pair of (row block j, K step k, lane t): 4i + j + 4k + t; slot = that modulo np
+            if constexpr (GEO::is_static) {
+                // every (level, K step) is an item of one unrolled pipeline: item i + 1's fragments are loaded before item
+                // i's MMAs are issued, level l - 1's epilogue (tile stores) follows level l's first MMAs
+                constexpr int NI = GEO::items();
+                uint4 fl[2][RBW], fh[2][RBW];
+                u32 tb[2][2], off[RBW];
+                int lo[2][RBW][4], hi[2][RBW][4];
+                auto load_item = [&](int i, int buf) {
+                    const int l = GEO::item_l(i), k = GEO::item_k(i);
+                    const u32 ring = (u32)geo.np(l) * (PPW * 4);
+                    const u8 *plane = planes + 4 * geo.plane_off(l);
+                    if (k == 0) {
+                        off[0] = voff[l];
+#pragma unroll
+                        for (int rb = 1; rb < RBW; ++rb) {
+                            const u32 nx = off[rb - 1] + PPW * 4;
+                            off[rb] = min(nx, nx - ring);
+                        }
+                    } else {
+#pragma unroll
+                        for (int rb = 0; rb < RBW; ++rb) {
+                            const u32 nx = off[rb] + 4 * (PPW * 4);
+                            off[rb] = min(nx, nx - ring);        // wrap: nx - ring is huge (unsigned) unless nx >= ring
+                        }
+                    }
+                    tb[buf][0] = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k); tb[buf][1] = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k + 4);
+#pragma unroll
+                    for (int rb = 0; rb < RBW; ++rb) {
+                        fl[buf][rb] = *(const uint4 *)(plane + off[rb]);
+                        fh[buf][rb] = *(const uint4 *)(plane + off[rb] + ring);
+                    }
+                };
+                load_item(0, 0);
+#pragma unroll
+                for (int i = 0; i < NI; ++i) {
+                    const int l = GEO::item_l(i), k = GEO::item_k(i), b = i & 1, lb = l & 1;
+                    if (i + 1 < NI) load_item(i + 1, b ^ 1);
+#pragma unroll
+                    for (int rb = 0; rb < RBW; ++rb) {
+                        if (k == 0) {   // K step 0 seeds the accumulators: 32768 (rounding) for the low bytes, 0 for the high bytes
+                            imma_c(lo[lb][rb], fl[b][rb].x, fl[b][rb].y, fl[b][rb].z, fl[b][rb].w, tb[b][0], tb[b][1], 32768);
+                            imma_c(hi[lb][rb], fh[b][rb].x, fh[b][rb].y, fh[b][rb].z, fh[b][rb].w, tb[b][0], tb[b][1], 0);
+                        } else {
+                            imma(lo[lb][rb], fl[b][rb].x, fl[b][rb].y, fl[b][rb].z, fl[b][rb].w, tb[b][0], tb[b][1]);
+                            imma(hi[lb][rb], fh[b][rb].x, fh[b][rb].y, fh[b][rb].z, fh[b][rb].w, tb[b][0], tb[b][1]);
+                        }
+                    }
+                    if (k == 0 && l > 0) v_out(l - 1, lo[lb ^ 1], hi[lb ^ 1]);
+                }
+                v_out(5, lo[1], hi[1]);
+            } else {
+#pragma unroll
+                for (int l = 0; l < 6; ++l) {
+                    const u32 ring = (u32)geo.np(l) * (PPW * 4);              // bytes of one plane; the high-byte plane follows
+                    const u8 *plane = planes + 4 * geo.plane_off(l);
+                    u32 off[RBW];
+                    off[0] = voff[l];
+#pragma unroll
+                    for (int rb = 1; rb < RBW; ++rb) {
+                        const u32 nx = off[rb - 1] + PPW * 4;
+                        off[rb] = min(nx, nx - ring);
+                    }
+                    int lo[RBW][4], hi[RBW][4];
+                    {   // K step 0 seeds the accumulators: 32768 (rounding) for the low bytes, 0 for the high bytes
+                        const u32 b0 = *(const u32 *)(vbase + geo.tab_voff(l)), b1 = *(const u32 *)(vbase + geo.tab_voff(l) + 4);
+#pragma unroll
+                        for (int rb = 0; rb < RBW; ++rb) {
+                            const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + ring);
+                            imma_c(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1, 32768);
+                            imma_c(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1, 0);
+                        }
+                    }
+#pragma unroll 1
+                    for (int k = 1; k < geo.ksv(l); ++k) {
+                        const u32 b0 = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k), b1 = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k + 4);
+#pragma unroll
+                        for (int rb = 0; rb < RBW; ++rb) {
+                            const u32 nx = off[rb] + 4 * (PPW * 4);
+                            off[rb] = min(nx, nx - ring);        // wrap: nx - ring is huge (unsigned) unless nx >= ring
+                            const uint4 vl = *(const uint4 *)(plane + off[rb]), vh = *(const uint4 *)(plane + off[rb] + ring);
+                            imma(lo[rb], vl.x, vl.y, vl.z, vl.w, b0, b1);
+                            imma(hi[rb], vh.x, vh.y, vh.z, vh.w, b0, b1);
+                        }
+                    }
+                    v_out(l, lo, hi);
+                }
             }
         }
         // the V windows of the next step start four pairs further on (also during the warm-up steps)
 #pragma unroll
         for (int l = 0; l < 6; ++l) {
-            const u32 ring = (u32)T.lv[l].np * (PPW * 4), nx = voff[l] + 4 * (PPW * 4);
+            const u32 ring = (u32)geo.np(l) * (PPW * 4), nx = voff[l] + 4 * (PPW * 4);
             voff[l] = min(nx, nx - ring);
         }
         if (p_work) emit(p_si_lo, p_nsrow);
@@ -525,16 +616,27 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     memset(&a, 0, sizeof a);
     static_cast<OctaveIO &>(a) = io;
     if (build_mma_taps(sigma0, scale_samples, io.octave, &a.mt)) return 1;
-    const int nch = (8 + 2 * a.mt.rmax + 31) / 32 + 1;
+    const int nch = a.mt.nch;
     if (nch > 6) return 1;                                           // bands wider than six chunks: dp4a/dp2a kernel
+    // the default pyramid's octaves run the instantiations with compile-time geometry
+    using G0 = MmaStaticGeom<11, 13, 17, 21, 25, 31>;
+    using G1 = MmaStaticGeom<21, 25, 31, 39, 49, 63>;
+    using G2 = MmaStaticGeom<39, 49, 63, 79, 99, 123>;
+    typedef void (*kern_t)(const MmaArgs);
+    static const kern_t kerns[6] = {octave_mma_k<3, MmaDynGeom>, octave_mma_k<4, MmaDynGeom>, octave_mma_k<6, MmaDynGeom>,
+                                    octave_mma_k<3, G0>,         octave_mma_k<4, G1>,         octave_mma_k<6, G2>};
+    static const int use_static = getenv("VSLAM_MMA_STATIC") ? atoi(getenv("VSLAM_MMA_STATIC")) : 1;
     static int static_smem = -1;
     if (static_smem < 0) {
         cudaFuncAttributes fa;
-        VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_mma_k<3>));
-        static_smem = (int)fa.sharedSizeBytes;
-        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
-        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
-        VS_CUDA(ctx, cudaFuncSetAttribute(octave_mma_k<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - static_smem));
+        int mx = 0;
+        for (int i = 0; i < 6; ++i) {
+            VS_CUDA(ctx, cudaFuncGetAttributes(&fa, kerns[i]));
+            if ((int)fa.sharedSizeBytes > mx) mx = (int)fa.sharedSizeBytes;
+        }
+        for (int i = 0; i < 6; ++i)
+            VS_CUDA(ctx, cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - mx));
+        static_smem = mx;
     }
     const size_t sm = mma_smem_bytes(a.mt);
     if (sm + static_smem > 227 * 1024) return 1;                     // tables too large for this octave: dp4a/dp2a kernel
@@ -551,9 +653,9 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
     KernelSpan span(ctx, VSLAM_K_FUSED);
-    if (nch <= 3) octave_mma_k<3><<<grid, 256, sm, ctx->stream>>>(a);
-    else if (nch <= 4) octave_mma_k<4><<<grid, 256, sm, ctx->stream>>>(a);
-    else octave_mma_k<6><<<grid, 256, sm, ctx->stream>>>(a);
+    int ki = nch <= 3 ? 0 : nch <= 4 ? 1 : 2;
+    if (use_static && ((ki == 0 && G0::matches(a.mt)) || (ki == 1 && G1::matches(a.mt)) || (ki == 2 && G2::matches(a.mt)))) ki += 3;
+    kerns[ki]<<<grid, 256, sm, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

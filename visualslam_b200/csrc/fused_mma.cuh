@@ -4,8 +4,11 @@
 
 namespace vslam {
 
-constexpr int kMmaPadL = 40;        // zero bytes in front of / behind the taps in the shifted tap copies
-constexpr int kMmaPadR = 40;
+// Tap tables: per level four byte-shifted, zero-padded copies of the taps, every copy `cp` bytes (one size for all
+// levels).  Level l's taps start `padl` bytes into a copy; padl is large enough that every chunk of the H pass's K range
+// that lies outside the band reads zeros (all chunks are multiplied, no band test), and padl + r is a multiple of 4, so
+// that the byte shift and the word offset of a lane's B fragment are the same for all levels: one lane pointer per pass,
+// the levels are immediates (tab_hoff / tab_voff).
 
 // One Gaussian level of octave_mma_k.
 struct MmaLevel {
@@ -15,8 +18,8 @@ struct MmaLevel {
     int cq;                         // quads between a row block's window start and the step's H chunk: (rmax + r + sv) / 4
     int np;                         // ring slots of this level's h planes, in PAIRS of row quads
     int plane_off;                  // word offset of the level's low-byte plane; the high-byte plane follows it
-    int tab_off;                    // byte offset of the level's four byte-shifted tap copies
-    int tab_cp;                     // bytes per copy: padL + n + padR rounded up to 4
+    int padl;                       // zero bytes in front of the taps in a copy: >= rmax - r + 41, padl + r == 0 (mod 4)
+    int tab_hoff, tab_voff;         // H / V pass: byte offset of the level's B fragments from the lane pointer of the pass
 };
 
 struct MmaTaps {
@@ -26,7 +29,100 @@ struct MmaTaps {
     int stage_rows, stage_pitch;    // staged base tile: 32 rows (y0 + rmax ...), pitch a multiple of 128 bytes (XOR swizzle)
     int spq_magic;                  // ceil(2^16 / (stage_pitch / 16)): flattened index -> row without a division
     int plane_words;                // all six planes
-    int tab_bytes;                  // all tap copies
+    int nch;                        // 32-byte chunks of a staged row one 8-column block's bands can touch
+    int cp;                         // bytes per tap copy
+    int tab_bytes;                  // all tap copies (6 levels x 4 copies)
+};
+
+constexpr int kMmaPPW = 4 * (kFusedW / 2) + 8;   // words per quad PAIR of an h plane: 32 column pairs x 16 bytes, + 8 (== 8 mod 32: conflict-free LDS.128)
+
+// The same geometry as compile-time functions of the six kernel sizes: the default pyramid (sigma0 1.6, three scale
+// samples) runs instantiations whose plane / table offsets, ring sizes and trip counts are immediates.  build_mma_taps
+// stays the single source of the layout: the launcher compares every field of the two before it picks a static kernel.
+template <int N0, int N1, int N2, int N3, int N4, int N5>
+struct MmaStaticGeom {
+    static constexpr bool is_static = true;
+    __host__ __device__ constexpr MmaStaticGeom() {}
+    __host__ __device__ explicit constexpr MmaStaticGeom(const MmaTaps &) {}
+    __host__ __device__ static constexpr int n(int l) { return l == 0 ? N0 : l == 1 ? N1 : l == 2 ? N2 : l == 3 ? N3 : l == 4 ? N4 : N5; }
+    __host__ __device__ static constexpr int r(int l) { return n(l) / 2; }
+    __host__ __device__ static constexpr int rmax() {
+        int m = 0;
+        for (int l = 0; l < 6; ++l) m = r(l) > m ? r(l) : m;
+        return m;
+    }
+    __host__ __device__ static constexpr int sv(int l) { return (4 - (rmax() + r(l)) % 4) % 4; }
+    __host__ __device__ static constexpr int ksv(int l) { return (n(l) + 7 + sv(l) + 31) / 32; }
+    __host__ __device__ static constexpr int cq(int l) { return (rmax() + r(l) + sv(l)) / 4; }
+    __host__ __device__ static constexpr int np(int l) { return (cq(l) + 10) / 2 < 8 ? 8 : (cq(l) + 10) / 2; }
+    __host__ __device__ static constexpr int plane_off(int l) {
+        int s = 0;
+        for (int j = 0; j < l; ++j) s += 2 * np(j) * kMmaPPW;
+        return s;
+    }
+    __host__ __device__ static constexpr int nch() { return (8 + 2 * rmax() + 31) / 32 + 1; }
+    __host__ __device__ static constexpr int padl(int l) { return rmax() - r(l) + 41 + (4 - (rmax() + 41) % 4) % 4; }
+    __host__ __device__ static constexpr int cp_need(int l) {
+        int a = padl(l) + r(l) - rmax() + 12 + 32 * (nch() - 1) + 20;     // H pass: last word of the last chunk
+        int b = padl(l) + 24 + 32 * (ksv(l) - 1) + 8;                     // V pass: last word of the last K step
+        int c = padl(l) + n(l) + 3;                                       // the taps themselves, shifted by up to 3
+        return a > b ? (a > c ? a : c) : (b > c ? b : c);
+    }
+    __host__ __device__ static constexpr int cp() {
+        int m = 0;
+        for (int l = 0; l < 6; ++l) m = cp_need(l) > m ? cp_need(l) : m;
+        m = (m + 3) & ~3;
+        while (m % 128 != 32) m += 4;                                      // copies 32 bytes apart modulo 128: fewer bank conflicts
+        return m;
+    }
+    __host__ __device__ static constexpr int tab_hoff(int l) { return 4 * cp() * l + padl(l) + r(l); }
+    __host__ __device__ static constexpr int tab_voff(int l) { return 4 * cp() * l + padl(l) - sv(l) - rmax() % 4; }
+    __host__ __device__ static constexpr int plane_words() { return plane_off(6); }
+    // the V pass as a flat list of (level, K step) items
+    __host__ __device__ static constexpr int items() { return ksv(0) + ksv(1) + ksv(2) + ksv(3) + ksv(4) + ksv(5); }
+    __host__ __device__ static constexpr int item_l(int i) {
+        int l = 0;
+        while (l < 5 && i >= ksv(l)) { i -= ksv(l); ++l; }
+        return l;
+    }
+    __host__ __device__ static constexpr int item_k(int i) {
+        int l = 0;
+        while (l < 5 && i >= ksv(l)) { i -= ksv(l); ++l; }
+        return i;
+    }
+    __host__ __device__ static constexpr int stage_pitch() { return (2 * rmax() + 15 + kFusedW + 127) / 128 * 128; }
+    __host__ __device__ static constexpr int spq_magic() { return ((1 << 16) + (stage_pitch() >> 4) - 1) / (stage_pitch() >> 4); }
+    static bool matches(const MmaTaps &t) {
+        bool ok = t.rmax == rmax() && t.stage_pitch == stage_pitch() && t.spq_magic == spq_magic() && t.plane_words == plane_words() &&
+                  t.nch == nch() && t.cp == cp();
+        for (int l = 0; l < 6; ++l)
+            ok = ok && t.lv[l].n == n(l) && t.lv[l].r == r(l) && t.lv[l].sv == sv(l) && t.lv[l].ksv == ksv(l) && t.lv[l].cq == cq(l) &&
+                 t.lv[l].np == np(l) && t.lv[l].plane_off == plane_off(l) && t.lv[l].padl == padl(l) && t.lv[l].tab_hoff == tab_hoff(l) &&
+                 t.lv[l].tab_voff == tab_voff(l);
+        return ok;
+    }
+};
+
+// ... and read from the kernel argument (any sigma0 / scale samples)
+struct MmaDynGeom {
+    static constexpr bool is_static = false;
+    const MmaTaps &T;
+    __device__ explicit MmaDynGeom(const MmaTaps &t) : T(t) {}
+    __device__ int n(int l) const { return T.lv[l].n; }
+    __device__ int r(int l) const { return T.lv[l].r; }
+    __device__ int rmax() const { return T.rmax; }
+    __device__ int sv(int l) const { return T.lv[l].sv; }
+    __device__ int ksv(int l) const { return T.lv[l].ksv; }
+    __device__ int cq(int l) const { return T.lv[l].cq; }
+    __device__ int np(int l) const { return T.lv[l].np; }
+    __device__ int plane_off(int l) const { return T.lv[l].plane_off; }
+    __device__ int padl(int l) const { return T.lv[l].padl; }
+    __device__ int cp() const { return T.cp; }
+    __device__ int tab_hoff(int l) const { return T.lv[l].tab_hoff; }
+    __device__ int tab_voff(int l) const { return T.lv[l].tab_voff; }
+    __device__ int plane_words() const { return T.plane_words; }
+    __device__ int stage_pitch() const { return T.stage_pitch; }
+    __device__ int spq_magic() const { return T.spq_magic; }
 };
 
 int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out);

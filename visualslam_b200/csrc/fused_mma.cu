@@ -158,7 +158,9 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     const u8 *tiles = (const u8 *)tiles32;
     u8 *tab = (u8 *)(tiles32 + (N_G + N_D) * TILE_W);
     __shared__ int s_res[3 * MAX_SROW * NS];                 // detector results of one step
-    __shared__ int s_any[2];                                  // step parity -> the step's detector left work for run_queue / emit
+    __shared__ unsigned long long s_mask[2];                  // step parity -> segments (level, sample row) of the step with survivors
+    __shared__ unsigned short s_queue[3 * MAX_SROW * NS];     // samples of the step that need the full localisation
+    __shared__ int s_nq;
     __shared__ float s_div[511];                              // float(i - 255) / 255f, the reference's divisions
 
     // special registers are read once through volatile asm: under the 128-register cap the compiler otherwise re-reads
@@ -212,7 +214,8 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             }
     }
     for (int i = tid; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
-    if (tid < 2) s_any[tid] = 0;
+    if (tid < 2) s_mask[tid] = 0;
+    if (tid == 2) s_nq = 0;
 
     constexpr int DT0 = N_G * TILE_W * 4;                                     // byte offset of the first D tile
     constexpr int LS = TILE_W * 4;                                            // bytes between tiles
@@ -235,13 +238,12 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             }
         return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // Diff_of_Gauss.cpp:336
     };
-    // samples marked -2 by the detector (all three derivatives non-zero) of the step whose tiles start at row yb:
-    // FeaturePointLocalization's full sequence
-    auto run_queue = [&](int yb, int si_lo, int n_srow) {
-        for (int s = tid; s < 3 * n_srow * NS; s += NT) {
-            if (s_res[s] != -2) continue;
-            const int k = s % NS, tt = s / NS;
-            const int level = 1 + tt % 3, sr = tt / 3;
+    // samples queued by the detector (all three derivatives non-zero) of the step whose tiles start at row yb:
+    // FeaturePointLocalization's full sequence, one lane per queued sample; survivors flag their segment in s_mask[mp]
+    auto run_queue = [&](int yb, int si_lo, int nq, int mp) {
+        for (int e = tid; e < nq; e += NT) {
+            const int code = s_queue[e];                                             // k | level << 5 | sample row << 8
+            const int k = code & 31, level = (code >> 5) & 3, sr = code >> 8;
             const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
             const u8 *d = tiles + DT0 + level * LS;
             const int x = xc - X0c, ty = yc - yb + 4;
@@ -252,36 +254,38 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             const int dx = (int)d[cxm + cy] - (int)d[cxp + cy], dy = (int)d[cx + cym] - (int)d[cx + cyp];
             const int ds = (int)d[cx + cy - LS] - (int)d[cx + cy + LS];
             const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
-            int res = -1;
-            if (zhat > a.contrast_thr && edge_pass(level, xc, yc, yb))               // :245
-                res = (int)__fmul_rn(zhat, 255.0f);                                  // :246
-            s_res[s] = res;
+            if (zhat > a.contrast_thr && edge_pass(level, xc, yc, yb)) {             // :245
+                const int task = sr * 3 + level - 1;
+                s_res[task * NS + k] = (int)__fmul_rn(zhat, 255.0f);                 // :246
+                atomicOr(&s_mask[mp], 1ull << task);
+            }
         }
     };
-    // ordered emission: one warp per segment (level, sample row, strip) of a finished step
-    auto emit = [&](int si_lo, int n_srow) {
-        for (int task = warp; task < 3 * n_srow; task += NW) {
+    // ordered emission: one warp per segment (level, sample row, strip) with survivors of a finished step
+    auto emit = [&](int si_lo, unsigned long long mask) {
+        for (int i = 0; mask; ++i) {
+            const int task = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            if ((i & (NW - 1)) != warp) continue;
             const int res = lane < NS ? s_res[task * NS + lane] : -1;
             const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
-            if (bal) {
-                const int level = 1 + task % 3, si = si_lo + task / 3;
-                const int cnt = __popc(bal);
-                const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
-                int off = 0;
-                if (lane == 0) {
-                    off = atomicAdd(a.cursor, cnt);
-                    a.seg_off[sg] = off;
-                    a.seg_cnt[sg] = cnt;
-                }
-                off = __shfl_sync(0xffffffffu, off, 0);
-                if (res >= 0) {
-                    const int pos = off + __popc(bal & ((1u << lane) - 1u));
-                    if (pos < a.staging_cap) {
-                        vslam_keypoint kp;
-                        kp.row = 3 * si + 1; kp.col = X0 + 3 * lane + 1; kp.value = res; kp.padding = 1; kp.octave = a.octave;
-                        kp.level = level;
-                        a.staging[pos] = kp;
-                    }
+            const int level = 1 + task % 3, si = si_lo + task / 3;
+            const int cnt = __popc(bal);
+            const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
+            int off = 0;
+            if (lane == 0) {
+                off = atomicAdd(a.cursor, cnt);
+                a.seg_off[sg] = off;
+                a.seg_cnt[sg] = cnt;
+            }
+            off = __shfl_sync(0xffffffffu, off, 0);
+            if (res >= 0) {
+                const int pos = off + __popc(bal & ((1u << lane) - 1u));
+                if (pos < a.staging_cap) {
+                    vslam_keypoint kp;
+                    kp.row = 3 * si + 1; kp.col = X0 + 3 * lane + 1; kp.value = res; kp.padding = 1; kp.octave = a.octave;
+                    kp.level = level;
+                    a.staging[pos] = kp;
                 }
             }
         }
@@ -334,8 +338,8 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
         const bool do_v = y0 >= yv;
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();                                                      // B1: staged rows landed; P3 of c-1 done
-        const bool p_work = p_nsrow && s_any[par ^ 1];                        // the previous step found candidates worth a second look
-        if (tid == 0) s_any[par] = 0;                                         // this step's flag (set in P3, two barriers from here)
+        const int p_nq = s_nq;                                                // samples the previous step queued for the full localisation
+        if (tid == 0) s_mask[par] = 0;                                        // this step's segments (set in P3, two barriers from here)
         // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
         // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them.
         // One basic block, software pipelined by hand: every chunk is multiplied (chunks outside a level's band meet the
@@ -394,7 +398,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             }
             h_store(5, acc[1]);
         }
-        if (p_work) run_queue(p_y0, p_si_lo, p_nsrow);
+        if (p_nq) run_queue(p_y0, p_si_lo, p_nq, par ^ 1);
         __syncthreads();                                                      // B2
         if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
         // ---- 3. V pass + rounding + DoG -> tiles, levels in order ----
@@ -524,12 +528,17 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             const u32 ring = (u32)geo.np(l) * (PPW * 4), nx = voff[l] + 4 * (PPW * 4);
             voff[l] = min(nx, nx - ring);
         }
-        if (p_work) emit(p_si_lo, p_nsrow);
+        {
+            const unsigned long long p_mask = s_mask[par ^ 1];
+            if (tid == 0) s_nq = 0;
+            if (p_mask) emit(p_si_lo, p_mask);
+        }
         __syncthreads();                                                      // B3
         // ---- 4a. detector, test.  Thread = one grid position (sample column, sample row) for the three levels: the five
         // DoG levels' 2 x 2 windows are read once, their minima / maxima shared by the levels.  Result per sample in s_res:
-        // the keypoint's value, -1, or -2 for samples whose three derivatives are all non-zero: those need the full 3x3
-        // inverse (rare) and are finished by run_queue in P1 of the next step.
+        // the keypoint's value or -1.  Samples whose three derivatives are all non-zero need the full 3x3 inverse: they are
+        // queued (s_queue) and finished, one lane per sample, by run_queue in P1 of the next step.  Segments with
+        // survivors are flagged in s_mask: emit (P2 of the next step) touches nothing else.
         const bool own_step = do_v && y0 >= ys;
         int si_lo = 0, n_srow = 0;
         if (own_step && a.detect) {
@@ -554,7 +563,6 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
                         mn[l] = min(min(w00[l], w01[l]), min(w10[l], w11[l]));
                         mx[l] = max(max(w00[l], w01[l]), max(w10[l], w11[l]));
                     }
-                    bool any = false;
 #pragma unroll
                     for (int level = 1; level <= 3; ++level) {
                         const int c = w11[level];
@@ -567,14 +575,15 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
                             if (dx == 0 || dy == 0 || ds == 0) {
                                 // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the
                                 // host with the same float ops: a.cmin, a.val_lut)
-                                if (c >= a.cmin && edge_pass(level, det_xc, yc, y0)) { res[level - 1] = a.val_lut[c]; any = true; }
+                                if (c >= a.cmin && edge_pass(level, det_xc, yc, y0)) {
+                                    res[level - 1] = a.val_lut[c];
+                                    atomicOr(&s_mask[par], 1ull << (det_sr * 3 + level - 1));
+                                }
                             } else {
-                                res[level - 1] = -2;
-                                any = true;
+                                s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)(det_k | level << 5 | det_sr << 8);
                             }
                         }
                     }
-                    if (any) s_any[par] = 1;
                 }
 #pragma unroll
                 for (int level = 1; level <= 3; ++level) s_res[(det_sr * 3 + level - 1) * NS + det_k] = res[level - 1];
@@ -596,10 +605,12 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     }
     // drain: the last step's queue and emission
     __syncthreads();
-    if (p_nsrow && s_any[par ^ 1]) {
-        run_queue(p_y0, p_si_lo, p_nsrow);
+    {
+        const int p_nq = s_nq;
+        if (p_nq) run_queue(p_y0, p_si_lo, p_nq, par ^ 1);
         __syncthreads();
-        emit(p_si_lo, p_nsrow);
+        const unsigned long long p_mask = s_mask[par ^ 1];
+        if (p_mask) emit(p_si_lo, p_mask);
     }
 }
 

@@ -557,7 +557,7 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
         int nc;
         detect_grid(g.orows[o], g.ocols[o], 3, &ni[o], &nj[o], &nc);
         seg_base[o] = (int)spf;
-        spf += 3LL * ni[o] * fused_strips(g.ocols[o]);
+        spf += 3LL * ni[o] * octave_strips(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o, g.ocols[o]);
     }
     if (spf == 0) spf = 1;
     // chunk size: workspace <= 6 GB, segment arrays <= 2^30 entries

@@ -69,6 +69,8 @@ int fused_strips(int cols);
 int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames);
 // Tensor-pipe variant (fused_mma.cu): same results; used for keypoints-only launches whose tap tables fit.
 // Returns 1 when the launch was not taken (caller falls back to launch_octave_fused), 0 on success, < 0 on error.
+// strips per frame of the kernel that will run the octave on the detect path (fused_mma.cu)
+int octave_strips(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols);
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
 
 }  // namespace vslam

@@ -22,6 +22,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <type_traits>
 
 #include "detect_math.cuh"
 #include "fused_mma.cuh"
@@ -29,20 +30,21 @@
 namespace vslam {
 
 namespace {
-constexpr int FW = kFusedW, FWO = kFusedWO, FR = kFusedR;
-constexpr int PPW = kMmaPPW;                // words per quad PAIR of an h plane
+constexpr int FR = kFusedR;
 constexpr int TRP = 20;                     // words per column pair of a tile: 2 history + 16 row pairs (+2: conflict-free STS)
-constexpr int TILE_W = (FW / 2) * TRP;      // words per tile
 constexpr int N_G = 3, N_D = 5;             // G tiles: Gaussian levels 1..3; D tiles: DoG levels 0..4
-constexpr int NS = FWO / 3;                 // 20 sample columns per strip
+constexpr int MAX_NS = 20;                  // sample columns per strip at FW = 64
 constexpr int MAX_SROW = FR / 3 + 2;
+__host__ __device__ constexpr int tile_words(int fw) { return (fw / 2) * TRP; }
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------
 // host: tables
 // ---------------------------------------------------------------------------------------------------------------
-int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
+int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps *out) {
     memset(out, 0, sizeof *out);
+    out->fw = fw;
+    const int PPW = mma_ppw(fw);
     int32_t t[kMaxKsize];
     const double k = pow(2.0, 1.0 / (double)scale_samples);          // GaussPyramid.hpp:69
     int rmin = 1 << 30, rmax = 0, poff = 0;
@@ -75,7 +77,16 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
         poff += 2 * lv.np * PPW;
     }
     // tap copies (fused_mma.cuh): the left pad covers the H pass's chunks in front of the band, padl + r == 0 (mod 4)
+    // rounded up to an instantiated chunk count: every chunk is multiplied, so the zero padding must cover all of them
     out->nch = (8 + 2 * rmax + 31) / 32 + 1;
+    {
+        const int have64[] = {3, 4, 6}, have32[] = {6, 9};
+        int pick = 0;
+        for (int c : have64) if (fw == 64 && !pick && c >= out->nch) pick = c;
+        for (int c : have32) if (fw == 32 && !pick && c >= out->nch) pick = c;
+        if (!pick) return VSLAM_E_INVALID;                           // bands wider than the widest instantiation
+        out->nch = pick;
+    }
     int cp = 0;
     for (int l = 0; l < 6; ++l) {
         MmaLevel &lv = out->lv[l];
@@ -95,7 +106,7 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
     }
     out->rmin = rmin; out->rmax = rmax;
     out->stage_rows = FR;
-    out->stage_pitch = (2 * rmax + 15 + FW + 127) / 128 * 128;       // left halo rmax (+ up to 15 alignment), 64 columns, right halo
+    out->stage_pitch = (2 * rmax + 15 + fw + 127) / 128 * 128;       // left halo rmax (+ up to 15 alignment), 64 columns, right halo
     {   // row = (q * magic) >> 16 for q < stage_rows * (pitch / 16): checked exhaustively
         const int spq = out->stage_pitch >> 4, nq = out->stage_rows * spq;
         out->spq_magic = ((1 << 16) + spq - 1) / spq;
@@ -108,10 +119,10 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out) {
 }
 
 size_t mma_smem_bytes(const MmaTaps &t) {
-    return (size_t)t.plane_words * 4 + (size_t)t.stage_rows * t.stage_pitch + (size_t)(N_G + N_D) * TILE_W * 4 + (size_t)t.tab_bytes;
+    return (size_t)t.plane_words * 4 + (size_t)t.stage_rows * t.stage_pitch + (size_t)(N_G + N_D) * tile_words(t.fw) * 4 + (size_t)t.tab_bytes;
 }
 
-int mma_strips(int cols) { return (cols + FWO - 1) / FWO; }
+int mma_strips(int cols, int fw) { return (cols + mma_fwo(fw) - 1) / mma_fwo(fw); }
 
 // ---------------------------------------------------------------------------------------------------------------
 // device
@@ -143,12 +154,17 @@ __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1)
 
 // NCH = 32-byte chunks of a staged row that the bands of one 8-column block can touch: (8 + 2 rmax + 31) / 32 + 1
 // GEO = the level geometry: MmaStaticGeom<n0..n5> (immediates) or MmaDynGeom (read from the argument)
-template <int NCH, class GEO>
+// FW  = columns a CTA computes: 64, or 32 with the warps regrouped (H pass: 4 column blocks x 2 groups of three levels;
+//       V pass: 2 column blocks x 4 row blocks)
+template <int NCH, class GEO, int FW>
 __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __grid_constant__ MmaArgs a) {
     constexpr int NT = 256;
     extern __shared__ __align__(16) u32 smem[];
     constexpr int NW = NT / 32;
-    constexpr int RBW = 16 / NW;                // 8-row blocks of one 16-column block a warp owns in the V pass
+    constexpr int FWO = mma_fwo(FW), PPW = mma_ppw(FW), TILE_W = tile_words(FW), NS = FWO / 3;
+    constexpr int HCB = FW / 8, LG = NW / HCB, LPW = 6 / LG;    // H pass: 8-column blocks, level groups, levels per warp
+    constexpr int VCB = FW / 16;                // V pass: 16-column blocks
+    constexpr int RBW = 4 * VCB / NW;           // 8-row blocks of one 16-column block a warp owns in the V pass
     const MmaTaps &T = a.mt;
     const GEO geo(a.mt);
     u8 *planes = (u8 *)smem;
@@ -157,9 +173,9 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     u32 *tiles32 = (u32 *)(stage + FR * SP);
     const u8 *tiles = (const u8 *)tiles32;
     u8 *tab = (u8 *)(tiles32 + (N_G + N_D) * TILE_W);
-    __shared__ int s_res[3 * MAX_SROW * NS];                 // detector results of one step
+    __shared__ int s_res[3 * MAX_SROW * MAX_NS];             // detector results of one step
     __shared__ unsigned long long s_mask[2];                  // step parity -> segments (level, sample row) of the step with survivors
-    __shared__ unsigned short s_queue[3 * MAX_SROW * NS];     // samples of the step that need the full localisation
+    __shared__ unsigned short s_queue[3 * MAX_SROW * MAX_NS]; // samples of the step that need the full localisation
     __shared__ int s_nq;
     __shared__ float s_div[511];                              // float(i - 255) / 255f, the reference's divisions
 
@@ -297,7 +313,8 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     // 4 pi(m & 7) + (m >> 3) (+2 for the second M block), so that a thread ends up with four consecutive rows of a quad.
     const int h_row = 4 * (((lane & 7) >> 1) + 4 * (lane & 1)) + ((lane >> 3) & 1);   // staged row this lane addresses, M block 0
     const u32 stage_sa = (u32)__cvta_generic_to_shared(stage);
-    const int hcb = cboff + 8 * warp;                                         // H pass: warp = 8 output columns (staged column hcb ...)
+    const int hw = warp % HCB, hlg = warp / HCB;                              // H pass: warp = (8 output columns, group of levels)
+    const int hcb = cboff + 8 * hw;                                           // staged column of the warp's first output column
     const int c_lo = (hcb - geo.rmax()) >> 5;                                     // first 32-byte chunk any level's band touches
     u32 saA[NCH], saB[NCH];                                                   // ldmatrix addresses of the chunks (XOR swizzle resolved)
 #pragma unroll
@@ -313,12 +330,12 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     const u8 *hbase = tab + (hu & 3) * geo.cp() + (hu - (hu & 3));             // two's complement: fine for hu < 0
     const u8 *vbase = tab + (vu & 3) * geo.cp() + (vu - (vu & 3));
     const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the H chunk this thread's D rows belong to
-    const int vcb = warp % 4, vjb = (warp / 4) * RBW;                         // V pass: warp = (16-column block, RBW blocks of 8 rows)
+    const int vcb = warp % VCB, vjb = (warp / VCB) * RBW;                         // V pass: warp = (16-column block, RBW blocks of 8 rows)
     u32 hoff[6], voff[6];                                                     // ring byte offsets: H store slot, V window start (row block vjb)
 #pragma unroll
     for (int l = 0; l < 6; ++l) {
         // the lane's column part (< one pair row) rides in the ring offsets: the wrap test does not see it
-        hoff[l] = (u32)((d_pi + geo.cq(l)) >> 1) * (PPW * 4) + 16 * (4 * warp + t) + 8 * ((d_pi + geo.cq(l)) & 1);   // < np pairs
+        hoff[l] = (u32)((d_pi + geo.cq(l)) >> 1) * (PPW * 4) + 16 * (4 * hw + t) + 8 * ((d_pi + geo.cq(l)) & 1);   // < np pairs
         voff[l] = (u32)(vjb + t) * (PPW * 4) + 16 * (8 * vcb + g);
     }
     const int wi0 = (8 * vcb + g) * TRP + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
@@ -379,11 +396,13 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
                 const u32 nx = hoff[l] + 4 * (PPW * 4);                       // the next step's chunk is four pairs further on
                 hoff[l] = min(nx, nx - ring);
             };
-            load_taps(0, 0);
+            auto h_levels = [&](auto l0_) {
+            constexpr int L0 = decltype(l0_)::value;
+            load_taps(L0, 0);
 #pragma unroll
-            for (int l = 0; l < 6; ++l) {
-                const int b = l & 1;
-                if (l < 5) load_taps(l + 1, b ^ 1);
+            for (int l = L0; l < L0 + LPW; ++l) {
+                const int b = (l - L0) & 1;
+                if (l < L0 + LPW - 1) load_taps(l + 1, b ^ 1);
 #pragma unroll
                 for (int ci = 0; ci < NCH; ++ci) {
                     if (ci == 0) {
@@ -394,9 +413,12 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
                         imma(acc[b][1], fb[ci][0], fb[ci][1], fb[ci][2], fb[ci][3], tb[b][ci][0], tb[b][ci][1]);
                     }
                 }
-                if (l > 0) h_store(l - 1, acc[b ^ 1]);
+                if (l > L0) h_store(l - 1, acc[b ^ 1]);
             }
-            h_store(5, acc[1]);
+            h_store(L0 + LPW - 1, acc[(LPW - 1) & 1]);
+            };
+            if (LG == 1 || hlg == 0) h_levels(std::integral_constant<int, 0>());
+            else h_levels(std::integral_constant<int, 6 - LPW>());
         }
         if (p_nq) run_queue(p_y0, p_si_lo, p_nq, par ^ 1);
         __syncthreads();                                                      // B2
@@ -617,41 +639,76 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
 // ---------------------------------------------------------------------------------------------------------------
 // host: launch
 // ---------------------------------------------------------------------------------------------------------------
-int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples) {
+namespace {
+typedef void (*mma_kern_t)(const MmaArgs);
+struct MmaVariant { mma_kern_t k; int fw, nch; bool (*match)(const MmaTaps &); };
+
+// Which instantiation runs an octave: 64-column strips when the rings fit shared memory, else 32-column strips, else
+// none (the dp4a/dp2a kernel).  The default pyramid's octaves get the instantiations with compile-time geometry.
+const MmaVariant *mma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, MmaTaps *mt, size_t *smem) {
+    using G0 = MmaStaticGeom<64, 11, 13, 17, 21, 25, 31>;
+    using G1 = MmaStaticGeom<64, 21, 25, 31, 39, 49, 63>;
+    using G2 = MmaStaticGeom<64, 39, 49, 63, 79, 99, 123>;
+    using G3 = MmaStaticGeom<32, 79, 99, 123, 155, 195, 245>;
+    static const MmaVariant variants[] = {
+        {octave_mma_k<3, G0, 64>, 64, 3, G0::matches}, {octave_mma_k<4, G1, 64>, 64, 4, G1::matches},
+        {octave_mma_k<6, G2, 64>, 64, 6, G2::matches}, {octave_mma_k<9, G3, 32>, 32, 9, G3::matches},
+        {octave_mma_k<3, MmaDynGeom, 64>, 64, 3, nullptr}, {octave_mma_k<4, MmaDynGeom, 64>, 64, 4, nullptr},
+        {octave_mma_k<6, MmaDynGeom, 64>, 64, 6, nullptr}, {octave_mma_k<6, MmaDynGeom, 32>, 32, 6, nullptr},
+        {octave_mma_k<9, MmaDynGeom, 32>, 32, 9, nullptr}};
+    constexpr int NV = sizeof variants / sizeof variants[0];
     static const int mode = getenv("VSLAM_FUSED_MMA") ? atoi(getenv("VSLAM_FUSED_MMA")) : 1;
-    if (!mode || io.gauss[0]) return 1;                              // materialising launches stay on fused.cu
+    static const int use_static = getenv("VSLAM_MMA_STATIC") ? atoi(getenv("VSLAM_MMA_STATIC")) : 1;
+    static const int force_fw = getenv("VSLAM_MMA_FW") ? atoi(getenv("VSLAM_MMA_FW")) : 0;
+    if (!mode) return nullptr;
+    static int static_smem = -1;
+    if (static_smem < 0) {
+        cudaFuncAttributes fa;
+        int mx = 0;
+        for (int i = 0; i < NV; ++i) {
+            if (cudaFuncGetAttributes(&fa, variants[i].k) != cudaSuccess) return nullptr;
+            if ((int)fa.sharedSizeBytes > mx) mx = (int)fa.sharedSizeBytes;
+        }
+        for (int i = 0; i < NV; ++i)
+            if (cudaFuncSetAttribute(variants[i].k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - mx) != cudaSuccess) return nullptr;
+        static_smem = mx;
+    }
+    (void)ctx;
+    for (int fw = (force_fw == 32 ? 32 : 64); fw >= 32; fw -= 32) {
+        if (build_mma_taps(sigma0, scale_samples, octave, fw, mt)) continue;
+        *smem = mma_smem_bytes(*mt);
+        if (*smem + static_smem > 227 * 1024) continue;
+        for (int pass = use_static ? 0 : 1; pass < 2; ++pass)
+            for (int i = 0; i < NV; ++i) {
+                const MmaVariant &c = variants[i];
+                if (c.fw != fw || (pass == 0) != (c.match != nullptr)) continue;
+                if (c.nch == mt->nch && (pass == 1 || c.match(*mt))) return &c;
+            }
+    }
+    return nullptr;
+}
+}  // namespace
+
+// strips per frame of the kernel that will run the octave (the caller sizes the segment arrays with it)
+int octave_strips(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols) {
+    MmaTaps mt;
+    size_t sm;
+    const MmaVariant *v = mma_plan(ctx, sigma0, scale_samples, octave, &mt, &sm);
+    return v ? mma_strips(cols, mt.fw) : fused_strips(cols);
+}
+
+int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples) {
+    if (io.gauss[0]) return 1;                                       // materialising launches stay on fused.cu
     if (n_frames <= 0 || n_frames > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: %d frames per launch", n_frames);
     if ((io.base_pitch & 15) || ((uintptr_t)io.base & 15) || (io.base_stride & 15))
         VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: base plane must be 16-byte aligned (pitch %zu)", io.base_pitch);
     MmaArgs a;
     memset(&a, 0, sizeof a);
+    size_t sm = 0;
+    const MmaVariant *v = mma_plan(ctx, sigma0, scale_samples, io.octave, &a.mt, &sm);
+    if (!v) return 1;
     static_cast<OctaveIO &>(a) = io;
-    if (build_mma_taps(sigma0, scale_samples, io.octave, &a.mt)) return 1;
-    const int nch = a.mt.nch;
-    if (nch > 6) return 1;                                           // bands wider than six chunks: dp4a/dp2a kernel
-    // the default pyramid's octaves run the instantiations with compile-time geometry
-    using G0 = MmaStaticGeom<11, 13, 17, 21, 25, 31>;
-    using G1 = MmaStaticGeom<21, 25, 31, 39, 49, 63>;
-    using G2 = MmaStaticGeom<39, 49, 63, 79, 99, 123>;
-    typedef void (*kern_t)(const MmaArgs);
-    static const kern_t kerns[6] = {octave_mma_k<3, MmaDynGeom>, octave_mma_k<4, MmaDynGeom>, octave_mma_k<6, MmaDynGeom>,
-                                    octave_mma_k<3, G0>,         octave_mma_k<4, G1>,         octave_mma_k<6, G2>};
-    static const int use_static = getenv("VSLAM_MMA_STATIC") ? atoi(getenv("VSLAM_MMA_STATIC")) : 1;
-    static int static_smem = -1;
-    if (static_smem < 0) {
-        cudaFuncAttributes fa;
-        int mx = 0;
-        for (int i = 0; i < 6; ++i) {
-            VS_CUDA(ctx, cudaFuncGetAttributes(&fa, kerns[i]));
-            if ((int)fa.sharedSizeBytes > mx) mx = (int)fa.sharedSizeBytes;
-        }
-        for (int i = 0; i < 6; ++i)
-            VS_CUDA(ctx, cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - mx));
-        static_smem = mx;
-    }
-    const size_t sm = mma_smem_bytes(a.mt);
-    if (sm + static_smem > 227 * 1024) return 1;                     // tables too large for this octave: dp4a/dp2a kernel
-    a.n_strips = mma_strips(a.cols);
+    a.n_strips = mma_strips(a.cols, a.mt.fw);
     // vertical split only when the batch alone cannot fill the machine (every extra segment repeats the warm-up)
     const long long want = (long long)ctx->sm_count * 4;
     const long long have = (long long)a.n_strips * n_frames;
@@ -664,9 +721,7 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
     KernelSpan span(ctx, VSLAM_K_FUSED);
-    int ki = nch <= 3 ? 0 : nch <= 4 ? 1 : 2;
-    if (use_static && ((ki == 0 && G0::matches(a.mt)) || (ki == 1 && G1::matches(a.mt)) || (ki == 2 && G2::matches(a.mt)))) ki += 3;
-    kerns[ki]<<<grid, 256, sm, ctx->stream>>>(a);
+    v->k<<<grid, 256, sm, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

@@ -29,17 +29,23 @@ struct MmaTaps {
     int stage_rows, stage_pitch;    // staged base tile: 32 rows (y0 + rmax ...), pitch a multiple of 128 bytes (XOR swizzle)
     int spq_magic;                  // ceil(2^16 / (stage_pitch / 16)): flattened index -> row without a division
     int plane_words;                // all six planes
+    int fw;                         // columns a CTA computes (64 or 32)
     int nch;                        // 32-byte chunks of a staged row one 8-column block's bands can touch
     int cp;                         // bytes per tap copy
     int tab_bytes;                  // all tap copies (6 levels x 4 copies)
 };
 
-constexpr int kMmaPPW = 4 * (kFusedW / 2) + 8;   // words per quad PAIR of an h plane: 32 column pairs x 16 bytes, + 8 (== 8 mod 32: conflict-free LDS.128)
+// Strip widths: a CTA computes FW columns and owns FWO of them (2 halo columns each side; FWO a multiple of 6: sample
+// columns of stride 3, even start on the next octave's base).  64 / 60 by default; 32 / 24 for octaves whose rings do
+// not fit shared memory at 64 columns.
+__host__ __device__ constexpr int mma_fwo(int fw) { return fw == 64 ? 60 : 24; }
+// words per quad PAIR of an h plane: FW / 2 column pairs x 16 bytes, + 8 (== 8 mod 32: conflict-free LDS.128)
+__host__ __device__ constexpr int mma_ppw(int fw) { return 4 * (fw / 2) + 8; }
 
 // The same geometry as compile-time functions of the six kernel sizes: the default pyramid (sigma0 1.6, three scale
 // samples) runs instantiations whose plane / table offsets, ring sizes and trip counts are immediates.  build_mma_taps
 // stays the single source of the layout: the launcher compares every field of the two before it picks a static kernel.
-template <int N0, int N1, int N2, int N3, int N4, int N5>
+template <int FW_, int N0, int N1, int N2, int N3, int N4, int N5>
 struct MmaStaticGeom {
     static constexpr bool is_static = true;
     __host__ __device__ constexpr MmaStaticGeom() {}
@@ -57,10 +63,13 @@ struct MmaStaticGeom {
     __host__ __device__ static constexpr int np(int l) { return (cq(l) + 10) / 2 < 8 ? 8 : (cq(l) + 10) / 2; }
     __host__ __device__ static constexpr int plane_off(int l) {
         int s = 0;
-        for (int j = 0; j < l; ++j) s += 2 * np(j) * kMmaPPW;
+        for (int j = 0; j < l; ++j) s += 2 * np(j) * mma_ppw(FW_);
         return s;
     }
-    __host__ __device__ static constexpr int nch() { return (8 + 2 * rmax() + 31) / 32 + 1; }
+    __host__ __device__ static constexpr int nch() {                       // rounded up to an instantiated chunk count
+        const int c = (8 + 2 * rmax() + 31) / 32 + 1;
+        return FW_ == 64 ? (c <= 3 ? 3 : c <= 4 ? 4 : 6) : (c <= 6 ? 6 : 9);
+    }
     __host__ __device__ static constexpr int padl(int l) { return rmax() - r(l) + 41 + (4 - (rmax() + 41) % 4) % 4; }
     __host__ __device__ static constexpr int cp_need(int l) {
         int a = padl(l) + r(l) - rmax() + 12 + 32 * (nch() - 1) + 20;     // H pass: last word of the last chunk
@@ -90,10 +99,10 @@ struct MmaStaticGeom {
         while (l < 5 && i >= ksv(l)) { i -= ksv(l); ++l; }
         return i;
     }
-    __host__ __device__ static constexpr int stage_pitch() { return (2 * rmax() + 15 + kFusedW + 127) / 128 * 128; }
+    __host__ __device__ static constexpr int stage_pitch() { return (2 * rmax() + 15 + FW_ + 127) / 128 * 128; }
     __host__ __device__ static constexpr int spq_magic() { return ((1 << 16) + (stage_pitch() >> 4) - 1) / (stage_pitch() >> 4); }
     static bool matches(const MmaTaps &t) {
-        bool ok = t.rmax == rmax() && t.stage_pitch == stage_pitch() && t.spq_magic == spq_magic() && t.plane_words == plane_words() &&
+        bool ok = t.fw == FW_ && t.rmax == rmax() && t.stage_pitch == stage_pitch() && t.spq_magic == spq_magic() && t.plane_words == plane_words() &&
                   t.nch == nch() && t.cp == cp();
         for (int l = 0; l < 6; ++l)
             ok = ok && t.lv[l].n == n(l) && t.lv[l].r == r(l) && t.lv[l].sv == sv(l) && t.lv[l].ksv == ksv(l) && t.lv[l].cq == cq(l) &&
@@ -125,7 +134,7 @@ struct MmaDynGeom {
     __device__ int spq_magic() const { return T.spq_magic; }
 };
 
-int build_mma_taps(double sigma0, int scale_samples, int octave, MmaTaps *out);
+int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps *out);
 size_t mma_smem_bytes(const MmaTaps &t);
 
 }  // namespace vslam

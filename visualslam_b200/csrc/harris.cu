@@ -23,7 +23,7 @@ namespace vslam {
 constexpr int HS = kHarrisStrip, HB = kHarrisBand;
 constexpr int H_WARPS = 4;                 // warps per CTA, each an independent (strip, band)
 #ifndef HARRIS_MIN_CTAS
-#define HARRIS_MIN_CTAS 4        // <= 128 registers: 16 warps per SM (4.68 -> 4.06 ms per 1080p x 256; 5 or 6 CTAs spill and lose)
+#define HARRIS_MIN_CTAS 3        // <= 128 registers: 16 warps per SM (4.68 -> 4.06 ms per 1080p x 256; 5 or 6 CTAs spill and lose)
 #endif
 constexpr int H_CAP = 256;                 // staged corners per warp before a flush
 constexpr int H_ROWS = 8;                  // rows per flush
@@ -96,19 +96,29 @@ __global__ void __launch_bounds__(32 * H_WARPS, HARRIS_MIN_CTAS) harris_march_k(
         cur = 0; ri = 0;
     };
 
+    // raw row yr, reflect-101
+    auto load_row = [&](int yr) -> u32 {
+        const u8 *__restrict__ src = img + (size_t)refl101(yr, rows) * a.pitch;
+        if (fast_ld) return *(const u32 *)(src + c);
+        return (u32)src[refl101(c, cols)] | (u32)src[refl101(c + 1, cols)] << 8 |
+               (u32)src[refl101(c + 2, cols)] << 16 | (u32)src[refl101(c + 3, cols)] << 24;
+    };
     const int yr_begin = (Y0 - 5) & ~3;                         // ring slots are compile-time: start on a multiple of 4
+    u32 wn[4];                                                  // the four raw rows of the NEXT group: loads stay one group ahead
+#pragma unroll
+    for (int ph = 0; ph < 4; ++ph) wn[ph] = load_row(yr_begin + ph);
     for (int yr4 = yr_begin; yr4 <= Y1 + 3; yr4 += 4) {
+        u32 wc[4];
+#pragma unroll
+        for (int ph = 0; ph < 4; ++ph) wc[ph] = wn[ph];
+        if (yr4 + 4 <= Y1 + 3) {
+#pragma unroll
+            for (int ph = 0; ph < 4; ++ph) wn[ph] = load_row(yr4 + 4 + ph);
+        }
 #pragma unroll
         for (int ph = 0; ph < 4; ++ph) {
             const int yr = yr4 + ph;                            // (yr & 3) == ph
-            // ---- raw row yr, reflect-101 --------------------------------------------------------------------
-            u32 w;
-            {
-                const u8 *__restrict__ src = img + (size_t)refl101(yr, rows) * a.pitch;
-                if (fast_ld) w = *(const u32 *)(src + c);
-                else w = (u32)src[refl101(c, cols)] | (u32)src[refl101(c + 1, cols)] << 8 |
-                         (u32)src[refl101(c + 2, cols)] << 16 | (u32)src[refl101(c + 3, cols)] << 24;
-            }
+            const u32 w = wc[ph];
             const u32 n0 = pk(w, 0, 0x4140), n1 = pk(w, 0, 0x4342);
             // ---- row K: blurred row yr-1 = (121 x 121 + 8) >> 4 -----------------------------------------------
             const u32 V0 = ra0 + 2 * rb0 + n0, V1 = ra1 + 2 * rb1 + n1;

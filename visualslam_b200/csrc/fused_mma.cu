@@ -146,6 +146,18 @@ __device__ __forceinline__ void imma_c(int (&d)[4], u32 a0, u32 a1, u32 a2, u32 
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c));
 }
 
+// split barrier (arrive early, wait late) on an mbarrier in shared memory
+__device__ __forceinline__ void mbar_init(u32 sa, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(sa), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(u32 sa) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(sa) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u32 sa, u32 parity) {
+    asm volatile("{\n\t.reg .pred p;\n\tMB_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra MB_DONE;\n\t"
+                 "bra MB_WAIT;\n\tMB_DONE:\n\t}" ::"r"(sa), "r"(parity) : "memory");
+}
+
 // byte offset of pixel (x, ty) inside a tile: words of 2 x 2 pixels [x even/odd][row even/odd], column pairs TRP words apart
 __device__ __forceinline__ int tcol(int x) { return (x >> 1) * (TRP * 4) + ((x & 1) << 1); }
 __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1); }
@@ -177,6 +189,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     __shared__ unsigned long long s_mask[2];                  // step parity -> segments (level, sample row) of the step with survivors
     __shared__ unsigned short s_queue[3 * MAX_SROW * MAX_NS]; // samples of the step that need the full localisation
     __shared__ int s_nq;
+    __shared__ __align__(8) unsigned long long s_mbar;        // split barrier between the detector and the queue
     __shared__ float s_div[511];                              // float(i - 255) / 255f, the reference's divisions
 
     // special registers are read once through volatile asm: under the 128-register cap the compiler otherwise re-reads
@@ -232,6 +245,8 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     for (int i = tid; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
     if (tid < 2) s_mask[tid] = 0;
     if (tid == 2) s_nq = 0;
+    const u32 mb_sa = (u32)__cvta_generic_to_shared(&s_mbar);
+    if (tid == 3) mbar_init(mb_sa, NT);
 
     constexpr int DT0 = N_G * TILE_W * 4;                                     // byte offset of the first D tile
     constexpr int LS = TILE_W * 4;                                            // bytes between tiles
@@ -345,18 +360,92 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     const bool det_colok = det_xc <= cols - 2;
     const int det_cx = tcol(det_xc - X0c), det_cxm = det_xc > 0 ? tcol(det_xc - X0c - 1) : det_cx;
     const int det_cxp = det_xc + 1 < cols ? tcol(det_xc - X0c + 1) : det_cx;
-    // Per step three barriers.  Small jobs of the PREVIOUS step ride along with the two blur passes:
-    //   P1 (after B1)  H pass of step c            + queued localisations of step c-1 (its tiles are still intact)
-    //   P2 (after B2)  V pass of step c -> tiles   + ordered emission of step c-1, prefetch of step c+1's base rows
-    //   P3 (after B3)  detector tests of step c, decimated level 3 -> next base
-    int p_y0 = 0, p_si_lo = 0, p_nsrow = 0;                                   // the previous step's detector state
-    int par = 0;                                                              // step parity
-    for (int y0 = yv - K * FR; y0 < ye; y0 += FR, par ^= 1) {
+    // ---- 4. detector of a finished step (its tiles start at row y0), decimation of its level 3 ----
+    auto detect_step = [&](int y0, bool own_step, int par) -> int {
+        // ---- 4a. detector, test.  Thread = one grid position (sample column, sample row) for the three levels: the five
+        // DoG levels' 2 x 2 windows are read once, their minima / maxima shared by the levels.  Result per sample in s_res:
+        // the keypoint's value or -1.  Samples whose three derivatives are all non-zero need the full 3x3 inverse: they are
+        // queued (s_queue) and finished, one lane per sample, by run_queue behind the split barrier.  Segments with
+        // survivors are flagged in s_mask: emit (next phase) touches nothing else.
+        int si_lo = 0, n_srow = 0;
+        if (own_step && a.detect) {
+            const int yc_lo = y0 == 0 ? 0 : y0 - 2;
+            const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;   // centre row yc needs rows up to yc + 2
+            si_lo = (yc_lo + 2) / 3;
+            n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
+            if (n_srow < 0) n_srow = 0;
+            if (det_sr < n_srow) {
+                const int yc = 3 * (si_lo + det_sr);
+                int res[3] = {-1, -1, -1};
+                if (det_colok) {
+                    // D tiles at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
+                    const int ty = yc - y0 + 4;
+                    const int cy = trow(ty), cym = yc > 0 ? trow(ty - 1) : cy, cyp = yc + 1 < rows ? trow(ty + 1) : cy;
+                    const u8 *d = tiles + DT0;
+                    int w00[5], w01[5], w10[5], w11[5], mn[5], mx[5];
+#pragma unroll
+                    for (int l = 0; l < 5; ++l) {
+                        w00[l] = d[l * LS + det_cxm + cym]; w01[l] = d[l * LS + det_cx + cym];
+                        w10[l] = d[l * LS + det_cxm + cy]; w11[l] = d[l * LS + det_cx + cy];
+                        mn[l] = min(min(w00[l], w01[l]), min(w10[l], w11[l]));
+                        mx[l] = max(max(w00[l], w01[l]), max(w10[l], w11[l]));
+                    }
+#pragma unroll
+                    for (int level = 1; level <= 3; ++level) {
+                        const int c = w11[level];
+                        const int lo3 = min(min(mn[level - 1], mn[level]), mn[level + 1]);
+                        const int hi3 = max(max(mx[level - 1], mx[level]), mx[level + 1]);
+                        if (c == lo3 || c == hi3) {                                          // Diff_of_Gauss.cpp:287
+                            const int dx = w10[level] - (int)d[level * LS + det_cxp + cy];   // :226-228
+                            const int dy = w01[level] - (int)d[level * LS + det_cx + cyp];
+                            const int ds = w11[level - 1] - w11[level + 1];
+                            if (dx == 0 || dy == 0 || ds == 0) {
+                                // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the
+                                // host with the same float ops: a.cmin, a.val_lut)
+                                if (c >= a.cmin && edge_pass(level, det_xc, yc, y0)) {
+                                    res[level - 1] = a.val_lut[c];
+                                    atomicOr(&s_mask[par], 1ull << (det_sr * 3 + level - 1));
+                                }
+                            } else {
+                                s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)(det_k | level << 5 | det_sr << 8);
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int level = 1; level <= 3; ++level) s_res[(det_sr * 3 + level - 1) * NS + det_k] = res[level - 1];
+            }
+        }
+        // ---- 4b. next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126) = byte 0 of the words;
+        // thread = (row, pair of output columns): the strip's 30 columns start on an even column of the next base ----
+        if (own_step && a.next_base && tid < (FWO / 4) * (FR / 2)) {
+            const int oc = 2 * (tid % (FWO / 4)), w = tid / (FWO / 4);
+            const int ox = X0 / 2 + oc, oy = (y0 >> 1) + w;
+            if (oy < a.next_rows && ox < a.next_cols) {
+                const u32 v0 = tiles32[2 * TILE_W + (oc + 1) * TRP + 2 + w], v1 = tiles32[2 * TILE_W + (oc + 2) * TRP + 2 + w];
+                u8 *dst = a.next_base + (size_t)frame * a.next_stride + (size_t)oy * a.next_pitch + ox;
+                if (ox + 1 < a.next_cols) *(u16 *)dst = (u16)((v0 & 0xffu) | (v1 & 0xffu) << 8);
+                else *dst = (u8)v0;
+            }
+        }
+        return si_lo;
+    };
+    // Per step two barriers and a split one.  The detector of the PREVIOUS step shares a phase with this step's H pass
+    // (they touch different buffers); its queue is finished behind an mbarrier every thread arrived at before its H
+    // pass, so nobody waits there:
+    //   X (after Bx)  detector tests + decimation of step c-1 | arrive | H pass of step c | wait | queued localisations of c-1
+    //   Y (after By)  prefetch of step c+1's base rows, V pass of step c -> tiles, ordered emission of step c-1
+    int p_y0 = 0;                                                             // the previous step (tiles hold it)
+    bool p_own = false;
+    int par = 0;                                                              // parity of the step the detector works on
+    u32 mb_phase = 0;
+    int si_lo = 0;
+    for (int y0 = yv - K * FR; y0 < ye; y0 += FR) {
         const bool do_v = y0 >= yv;
         asm volatile("cp.async.wait_all;" ::: "memory");
-        __syncthreads();                                                      // B1: staged rows landed; P3 of c-1 done
-        const int p_nq = s_nq;                                                // samples the previous step queued for the full localisation
-        if (tid == 0) s_mask[par] = 0;                                        // this step's segments (set in P3, two barriers from here)
+        __syncthreads();                                                      // Bx: staged rows landed; V pass / emission of c-1 done
+        si_lo = detect_step(p_y0, p_own, par);
+        mbar_arrive(mb_sa);
         // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
         // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them.
         // One basic block, software pipelined by hand: every chunk is multiplied (chunks outside a level's band meet the
@@ -420,8 +509,13 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             if (LG == 1 || hlg == 0) h_levels(std::integral_constant<int, 0>());
             else h_levels(std::integral_constant<int, 6 - LPW>());
         }
-        if (p_nq) run_queue(p_y0, p_si_lo, p_nq, par ^ 1);
-        __syncthreads();                                                      // B2
+        mbar_wait(mb_sa, mb_phase);                                           // every thread's detector results are visible
+        mb_phase ^= 1;
+        {
+            const int nq = s_nq;
+            if (nq) run_queue(p_y0, si_lo, nq, par);
+        }
+        __syncthreads();                                                      // By
         if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
         // ---- 3. V pass + rounding + DoG -> tiles, levels in order ----
         if (do_v) {
@@ -551,88 +645,24 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             voff[l] = min(nx, nx - ring);
         }
         {
-            const unsigned long long p_mask = s_mask[par ^ 1];
-            if (tid == 0) s_nq = 0;
-            if (p_mask) emit(p_si_lo, p_mask);
+            const unsigned long long p_mask = s_mask[par];
+            if (tid == 0) { s_nq = 0; s_mask[par ^ 1] = 0; }                  // the next step's queue and segment flags
+            if (p_mask) emit(si_lo, p_mask);
         }
-        __syncthreads();                                                      // B3
-        // ---- 4a. detector, test.  Thread = one grid position (sample column, sample row) for the three levels: the five
-        // DoG levels' 2 x 2 windows are read once, their minima / maxima shared by the levels.  Result per sample in s_res:
-        // the keypoint's value or -1.  Samples whose three derivatives are all non-zero need the full 3x3 inverse: they are
-        // queued (s_queue) and finished, one lane per sample, by run_queue in P1 of the next step.  Segments with
-        // survivors are flagged in s_mask: emit (P2 of the next step) touches nothing else.
-        const bool own_step = do_v && y0 >= ys;
-        int si_lo = 0, n_srow = 0;
-        if (own_step && a.detect) {
-            const int yc_lo = y0 == 0 ? 0 : y0 - 2;
-            const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;   // centre row yc needs rows up to yc + 2
-            si_lo = (yc_lo + 2) / 3;
-            n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
-            if (n_srow < 0) n_srow = 0;
-            if (det_sr < n_srow) {
-                const int yc = 3 * (si_lo + det_sr);
-                int res[3] = {-1, -1, -1};
-                if (det_colok) {
-                    // D tiles at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
-                    const int ty = yc - y0 + 4;
-                    const int cy = trow(ty), cym = yc > 0 ? trow(ty - 1) : cy, cyp = yc + 1 < rows ? trow(ty + 1) : cy;
-                    const u8 *d = tiles + DT0;
-                    int w00[5], w01[5], w10[5], w11[5], mn[5], mx[5];
-#pragma unroll
-                    for (int l = 0; l < 5; ++l) {
-                        w00[l] = d[l * LS + det_cxm + cym]; w01[l] = d[l * LS + det_cx + cym];
-                        w10[l] = d[l * LS + det_cxm + cy]; w11[l] = d[l * LS + det_cx + cy];
-                        mn[l] = min(min(w00[l], w01[l]), min(w10[l], w11[l]));
-                        mx[l] = max(max(w00[l], w01[l]), max(w10[l], w11[l]));
-                    }
-#pragma unroll
-                    for (int level = 1; level <= 3; ++level) {
-                        const int c = w11[level];
-                        const int lo3 = min(min(mn[level - 1], mn[level]), mn[level + 1]);
-                        const int hi3 = max(max(mx[level - 1], mx[level]), mx[level + 1]);
-                        if (c == lo3 || c == hi3) {                                          // Diff_of_Gauss.cpp:287
-                            const int dx = w10[level] - (int)d[level * LS + det_cxp + cy];   // :226-228
-                            const int dy = w01[level] - (int)d[level * LS + det_cx + cyp];
-                            const int ds = w11[level - 1] - w11[level + 1];
-                            if (dx == 0 || dy == 0 || ds == 0) {
-                                // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (tables built on the
-                                // host with the same float ops: a.cmin, a.val_lut)
-                                if (c >= a.cmin && edge_pass(level, det_xc, yc, y0)) {
-                                    res[level - 1] = a.val_lut[c];
-                                    atomicOr(&s_mask[par], 1ull << (det_sr * 3 + level - 1));
-                                }
-                            } else {
-                                s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)(det_k | level << 5 | det_sr << 8);
-                            }
-                        }
-                    }
-                }
-#pragma unroll
-                for (int level = 1; level <= 3; ++level) s_res[(det_sr * 3 + level - 1) * NS + det_k] = res[level - 1];
-            }
-        }
-        // ---- 4b. next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126) = byte 0 of the words;
-        // thread = (row, pair of output columns): the strip's 30 columns start on an even column of the next base ----
-        if (own_step && a.next_base && tid < (FWO / 4) * (FR / 2)) {
-            const int oc = 2 * (tid % (FWO / 4)), w = tid / (FWO / 4);
-            const int ox = X0 / 2 + oc, oy = (y0 >> 1) + w;
-            if (oy < a.next_rows && ox < a.next_cols) {
-                const u32 v0 = tiles32[2 * TILE_W + (oc + 1) * TRP + 2 + w], v1 = tiles32[2 * TILE_W + (oc + 2) * TRP + 2 + w];
-                u8 *dst = a.next_base + (size_t)frame * a.next_stride + (size_t)oy * a.next_pitch + ox;
-                if (ox + 1 < a.next_cols) *(u16 *)dst = (u16)((v0 & 0xffu) | (v1 & 0xffu) << 8);
-                else *dst = (u8)v0;
-            }
-        }
-        p_y0 = y0; p_si_lo = si_lo; p_nsrow = n_srow;
+        p_y0 = y0; p_own = do_v && y0 >= ys; par ^= 1;
     }
-    // drain: the last step's queue and emission
+    // drain: the last step's detector, queue and emission
+    __syncthreads();
+    si_lo = detect_step(p_y0, p_own, par);
     __syncthreads();
     {
-        const int p_nq = s_nq;
-        if (p_nq) run_queue(p_y0, p_si_lo, p_nq, par ^ 1);
-        __syncthreads();
-        const unsigned long long p_mask = s_mask[par ^ 1];
-        if (p_mask) emit(p_si_lo, p_mask);
+        const int nq = s_nq;
+        if (nq) run_queue(p_y0, si_lo, nq, par);
+    }
+    __syncthreads();
+    {
+        const unsigned long long p_mask = s_mask[par];
+        if (p_mask) emit(si_lo, p_mask);
     }
 }
 

@@ -547,9 +547,15 @@ int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_p
 static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_frames, int n_frames, int rows, int cols,
                                size_t d_pitch, size_t d_stride, const vslam_dog_params &dp, vslam_keypoint *d_out, int capacity) {
     const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
-    // bases-only workspace layout of one frame
-    size_t boff[16], bbytes = 0;
-    for (int o = 0; o < g.num_octaves; ++o) { boff[o] = bbytes; bbytes += g.oplane[o]; }
+    // bases-only workspace layout of one frame; every row carries the reflect-101 margins its octave's kernel stages from
+    size_t boff[16], bpitch[16], bbytes = 0;
+    int bpad[16];
+    for (int o = 0; o < g.num_octaves; ++o) {
+        bpad[o] = octave_base_pad(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o);
+        bpitch[o] = bpad[o] ? round_up((size_t)g.ocols[o] + 2 * (size_t)bpad[o] + 4, 16) : g.opitch[o];   // + 4: the right margin is written in words
+        boff[o] = bbytes + bpad[o];
+        bbytes += round_up(bpitch[o] * (size_t)g.orows[o] + 256, 256);     // + slack: staging may read past the last row's margin
+    }
     // segments of one frame: (octave, level 1..3, sample row, strip)
     int seg_base[16], ni[16], nj[16];
     long long spf = 0;
@@ -589,15 +595,16 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
         VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
         u8 *ws = ctx->ws_maps.as<u8>();
         VS_TRY(wait_ingest(ctx, f0, nf));
-        VS_TRY(launch_upsample2x(ctx, d_frames + d_stride * f0, rows, cols, d_pitch, d_stride, ws + boff[0], g.opitch[0], bbytes, nf));
+        VS_TRY(launch_upsample2x(ctx, d_frames + d_stride * f0, rows, cols, d_pitch, d_stride, ws + boff[0], bpitch[0], bbytes, nf));
         for (int o = 0; o < g.num_octaves; ++o) {
             FusedArgs a;
             memset(&a, 0, sizeof a);
             a.taps = h[o];
-            a.base = ws + boff[o]; a.base_pitch = g.opitch[o]; a.base_stride = bbytes;
+            a.base = ws + boff[o]; a.base_pitch = bpitch[o]; a.base_stride = bbytes; a.base_pad = bpad[o];
+            VS_TRY(launch_reflect_pad(ctx, ws + boff[o], g.orows[o], g.ocols[o], bpitch[o], bbytes, bpad[o], nf));
             a.rows = g.orows[o]; a.cols = g.ocols[o]; a.octave = o;
             if (o + 1 < g.num_octaves) {
-                a.next_base = ws + boff[o + 1]; a.next_pitch = g.opitch[o + 1]; a.next_stride = bbytes;
+                a.next_base = ws + boff[o + 1]; a.next_pitch = bpitch[o + 1]; a.next_stride = bbytes;
                 a.next_rows = g.orows[o + 1]; a.next_cols = g.ocols[o + 1];
             }
             a.detect = 1; a.cmin = cmin; memcpy(a.val_lut, val_lut, 256); a.contrast_thr = dp.contrast_thr; a.edge_thr = (rp1 * rp1) / dp.edge_r;   // Diff_of_Gauss.cpp:332-333

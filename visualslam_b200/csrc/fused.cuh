@@ -30,6 +30,7 @@ struct FusedTaps {
 struct OctaveIO {
     const u8 *base;                 // octave input
     size_t base_pitch, base_stride;
+    int base_pad;                   // columns left and right of every base row that hold its reflect-101 continuation (0: none)
     int rows, cols, octave;
     int n_strips, n_segs, seg_rows; // grid = (strips, vertical segments, frames); seg_rows is a multiple of R
     // next octave's base: level 3 decimated by two (GaussPyramid.cpp:123-126), or nullptr
@@ -71,6 +72,10 @@ int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames);
 // Returns 1 when the launch was not taken (caller falls back to launch_octave_fused), 0 on success, < 0 on error.
 // strips per frame of the kernel that will run the octave on the detect path (fused_mma.cu)
 int octave_strips(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols);
+// reflect-101 columns the kernel of that octave wants next to every base row (a multiple of 16; 0 for the dp4a/dp2a kernel)
+int octave_base_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);
+// fills them: base[y][-pad .. -1] and base[y][cols .. cols + pad - 1] of every frame
+int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int n_frames);
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
 
 }  // namespace vslam

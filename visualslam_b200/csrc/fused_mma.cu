@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
             u32 *dst = (u32 *)(stage + row * SP) + 4 * (j ^ ((row >> 2) & 7));   // 16-byte groups XOR-swizzled by the row quad
             const int x = xs16 + 16 * j;
-            if (x >= 0 && x + 15 < cols) {
+            if (x >= -a.base_pad && x + 15 < cols + a.base_pad) {            // inside the image or its reflected margins
                 const u32 sa = (u32)__cvta_generic_to_shared(dst);
                 asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src + x) : "memory");
             } else {
@@ -725,6 +725,42 @@ int octave_strips(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, 
     size_t sm;
     const MmaVariant *v = mma_plan(ctx, sigma0, scale_samples, octave, &mt, &sm);
     return v ? mma_strips(cols, mt.fw) : fused_strips(cols);
+}
+
+int octave_base_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave) {
+    MmaTaps mt;
+    size_t sm;
+    if (!mma_plan(ctx, sigma0, scale_samples, octave, &mt, &sm)) return 0;
+    // staged columns: ((X0 - 2 - rmax) & ~15) + [0, stage_pitch), X0 < cols
+    return (mt.stage_pitch - mt.rmax + 30) & ~15;
+}
+
+// thread = one aligned word of a margin; the right margin starts at the last aligned word that still holds image
+// columns (those bytes are rewritten with their own values)
+__global__ void reflect_pad_k(u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad) {
+    const int wl = pad >> 2, x_r = cols & ~3, wr = (cols + pad - x_r + 3) >> 2, wpr = wl + wr;
+    u8 *plane = base + (size_t)blockIdx.y * stride;
+    const int n = rows * wpr;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int y = i / wpr, w = i - y * wpr;
+        const int x = w < wl ? 4 * w - pad : x_r + 4 * (w - wl);
+        u8 *row = plane + (size_t)y * pitch;
+        const u32 v = (u32)row[refl101(x, cols)] | (u32)row[refl101(x + 1, cols)] << 8 | (u32)row[refl101(x + 2, cols)] << 16 |
+                      (u32)row[refl101(x + 3, cols)] << 24;
+        *(u32 *)(row + x) = v;
+    }
+}
+
+int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int n_frames) {
+    if (pad <= 0) return VSLAM_OK;
+    const int wpr = (pad >> 2) + ((cols + pad - (cols & ~3) + 3) >> 2);
+    int bx = (rows * wpr + 255) / 256;
+    if (bx > 64) bx = 64;
+    const dim3 grid(bx, n_frames);
+    KernelSpan span(ctx, VSLAM_K_UPSAMPLE);
+    reflect_pad_k<<<grid, 256, 0, ctx->stream>>>(base, rows, cols, pitch, stride, pad);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
 }
 
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples) {

@@ -96,6 +96,8 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     for (cudaEvent_t e : ctx->up_ev) cudaEventDestroy(e);
     if (ctx->up_start) cudaEventDestroy(ctx->up_start);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    for (cudaEvent_t e : ctx->down_ev) cudaEventDestroy(e);
+    if (ctx->down_stream) cudaStreamDestroy(ctx->down_stream);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     free(ctx->h_taps);
     delete ctx;
@@ -244,7 +246,7 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
         VS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
         VS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->up_start, cudaEventDisableTiming));
     }
-    int chunk = (int)(((size_t)64 << 20) / ds);
+    int chunk = (int)(((size_t)16 << 20) / ds);                 // small chunks: the first kernels start after ~0.3 ms of upload
     if (chunk < 1) chunk = 1;
     if (chunk > n) chunk = n;
     const int chunks = (n + chunk - 1) / chunk;
@@ -280,10 +282,14 @@ static int wait_ingest(vslam_ctx *ctx, int f0, int nf) {
     for (int c = c0; c <= c1 && c < ctx->up_chunks; ++c) VS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->up_ev[c], 0));
     return VSLAM_OK;
 }
-// frames per compute launch when the input is being uploaded: a few upload chunks, so that kernels start early
+// frames per compute launch when the input is being uploaded: ~128 MB of frames, and a short first launch so that the
+// kernels start early (ingest_first)
 static long long ingest_cap(const vslam_ctx *ctx, long long fb) {
-    if (ctx->up_chunks > 1 && fb > 2LL * ctx->up_chunk) fb = 2LL * ctx->up_chunk;
+    if (ctx->up_chunks > 1 && fb > 8LL * ctx->up_chunk) fb = 8LL * ctx->up_chunk;
     return fb;
+}
+static int ingest_first(const vslam_ctx *ctx, long long fb) {
+    return (int)(ctx->up_chunks > 1 && fb > 2LL * ctx->up_chunk ? 2LL * ctx->up_chunk : fb);
 }
 
 // rows A-D for n_frames frames into consecutive blocks laid out by Geometry (frame f at block + f * g.frame_bytes):
@@ -496,8 +502,61 @@ static int check_dog_params(vslam_ctx *ctx, const vslam_dog_params *in, vslam_do
     return VSLAM_OK;
 }
 
-static int emit_list(vslam_ctx *ctx, void *out, int out_space, const void *d_list, size_t entry, long long total, int capacity) {
-    if (out_space != VSLAM_DEVICE && out) {
+// A device list that grows chunk by chunk (seg_finalise appends at the running total) streams to the caller's host
+// buffer while later chunks compute: after every chunk the running total is snapshot into pinned memory behind an event;
+// once the NEXT chunk has been queued, the host waits for that event and queues the chunk's slice on a third stream.
+struct ListDrain {
+    u8 *host = nullptr;
+    const u8 *dev = nullptr;
+    size_t entry = 0;
+    long long cap = 0, copied = 0;
+    int n = 0;
+    bool on = false;
+};
+static const int kDrainMax = 1024;
+
+static int drain_begin(vslam_ctx *ctx, ListDrain &d, void *out, int out_space, const void *d_list, size_t entry, int capacity, long long chunks) {
+    d = ListDrain();
+    if (out_space == VSLAM_DEVICE || !out || chunks < 2 || chunks > kDrainMax || !ctx->pinned || ctx->pinned_cap < kDrainMax * sizeof(int)) return VSLAM_OK;
+    if (!ctx->down_stream) VS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking));
+    while ((long long)ctx->down_ev.size() < chunks) {
+        cudaEvent_t e;
+        VS_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->down_ev.push_back(e);
+    }
+    d.host = (u8 *)out; d.dev = (const u8 *)d_list; d.entry = entry; d.cap = capacity; d.on = true;
+    return VSLAM_OK;
+}
+static int drain_settle(vslam_ctx *ctx, ListDrain &d, int j) {
+    VS_CUDA(ctx, cudaEventSynchronize(ctx->down_ev[j]));
+    long long t = ((const int *)ctx->pinned)[j];
+    if (t > d.cap) t = d.cap;
+    if (t > d.copied) {
+        VS_CUDA(ctx, cudaMemcpyAsync(d.host + d.copied * d.entry, d.dev + d.copied * d.entry, (size_t)(t - d.copied) * d.entry,
+                                     cudaMemcpyDeviceToHost, ctx->down_stream));
+        d.copied = t;
+    }
+    return VSLAM_OK;
+}
+// after a chunk's seg_finalise
+static int drain_chunk(vslam_ctx *ctx, ListDrain &d, const int *d_total) {
+    if (!d.on) return VSLAM_OK;
+    VS_CUDA(ctx, cudaMemcpyAsync((int *)ctx->pinned + d.n, d_total, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaEventRecord(ctx->down_ev[d.n], ctx->stream));
+    if (d.n > 0) VS_TRY(drain_settle(ctx, d, d.n - 1));
+    ++d.n;
+    return VSLAM_OK;
+}
+static int drain_end(vslam_ctx *ctx, ListDrain &d) {
+    if (!d.on) return VSLAM_OK;
+    if (d.n > 0) VS_TRY(drain_settle(ctx, d, d.n - 1));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->down_stream));
+    return VSLAM_OK;
+}
+
+static int emit_list(vslam_ctx *ctx, void *out, int out_space, const void *d_list, size_t entry, long long total, int capacity,
+                     bool drained = false) {
+    if (out_space != VSLAM_DEVICE && out && !drained) {
         const size_t n = (size_t)(total < capacity ? total : capacity);
         if (n) VS_CUDA(ctx, cudaMemcpyAsync(out, d_list, n * entry, cudaMemcpyDeviceToHost, ctx->stream));
         VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -545,7 +604,8 @@ int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_p
 // Throughput path: batched fused pipeline.  Per chunk of frames: one upsample launch, one fused launch per octave
 // (blur + DoG + detector; only the octave bases live in HBM), then the segment scan / ordered gather.
 static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_frames, int n_frames, int rows, int cols,
-                               size_t d_pitch, size_t d_stride, const vslam_dog_params &dp, vslam_keypoint *d_out, int capacity) {
+                               size_t d_pitch, size_t d_stride, const vslam_dog_params &dp, vslam_keypoint *d_out, int capacity,
+                               ListDrain *drain, void *out, int out_space) {
     const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
     // bases-only workspace layout of one frame; every row carries the reflect-101 margins its octave's kernel stages from
     size_t boff[16], bpitch[16], bbytes = 0;
@@ -588,8 +648,10 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
         val_lut[c] = (u8)(int)w;
         if (v > dp.contrast_thr) cmin = c;
     }
-    for (int f0 = 0; f0 < n_frames; f0 += (int)fb) {
-        const int nf = n_frames - f0 < fb ? n_frames - f0 : (int)fb;
+    VS_TRY(drain_begin(ctx, *drain, out, out_space, d_out, sizeof(vslam_keypoint), capacity, (n_frames + fb - 1) / fb + 1));
+    const int first = ingest_first(ctx, fb);
+    for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)fb) {
+        const int nf = n_frames - f0 < step ? n_frames - f0 : step;
         const size_t n_seg = (size_t)spf * nf;
         if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, n_seg * 4, ctx->stream));
         VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
@@ -616,6 +678,7 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
             if (rc == 1) VS_TRY(launch_octave_fused(ctx, a, nf));                                         // dp4a/dp2a blur
         }
         VS_TRY(seg_finalise(ctx, n_seg, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf));
+        VS_TRY(drain_chunk(ctx, *drain, cnt + 2));
     }
     return VSLAM_OK;
 }
@@ -639,8 +702,9 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
         if (ctx->out_dev.reserve(sizeof(vslam_keypoint) * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device keypoint list");
         d_out = ctx->out_dev.as<vslam_keypoint>();
     }
+    ListDrain drain;
     if (dp.window == 3) {
-        VS_TRY(dog_keypoints_fused(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, dp, d_out, capacity));
+        VS_TRY(dog_keypoints_fused(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, dp, d_out, capacity, &drain, out, out_space));
     } else {
         // other grid strides: materialise one frame at a time and run the stand-alone detector (detect.cu)
         if (ctx->ws_maps.reserve(g.frame_bytes)) VS_FAIL(ctx, VSLAM_E_NOMEM, "frame workspace (%zu bytes)", g.frame_bytes);
@@ -656,7 +720,8 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
     }
     long long total = 0;
     VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
-    return emit_list(ctx, out, out_space, d_out, sizeof(vslam_keypoint), total, capacity);
+    VS_TRY(drain_end(ctx, drain));
+    return emit_list(ctx, out, out_space, d_out, sizeof(vslam_keypoint), total, capacity, drain.on);
 }
 
 int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
@@ -693,8 +758,11 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         d_m3 = mask3 ? ctx->maps_dev.as<u8>() + px * 5 * n_frames : nullptr;
     }
     int *cnt = ctx->counters.as<int>();
-    for (int f0 = 0; f0 < n_frames; f0 += (int)fb) {
-        const int nf = n_frames - f0 < (int)fb ? n_frames - f0 : (int)fb;
+    ListDrain drain;
+    VS_TRY(drain_begin(ctx, drain, corners, out_space, d_out, sizeof(vslam_corner), capacity, ((long long)n_frames + (long long)fb - 1) / (long long)fb + 1));
+    const int first = ingest_first(ctx, (long long)fb);
+    for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)fb) {
+        const int nf = n_frames - f0 < step ? n_frames - f0 : step;
         if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, spf * nf * 4, ctx->stream));
         VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
         VS_TRY(wait_ingest(ctx, f0, nf));
@@ -710,6 +778,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         a.want_corners = 1;
         VS_TRY(launch_harris(ctx, a, nf));
         VS_TRY(seg_finalise(ctx, spf * nf, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf));
+        VS_TRY(drain_chunk(ctx, drain, cnt + 2));
     }
     if (out_space != VSLAM_DEVICE) {
         if (response) VS_CUDA(ctx, cudaMemcpyAsync(response, d_resp, px * 4 * n_frames, cudaMemcpyDeviceToHost, ctx->stream));
@@ -718,7 +787,8 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     }
     long long total = 0;
     VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
-    return emit_list(ctx, corners, out_space, d_out, sizeof(vslam_corner), total, capacity);
+    VS_TRY(drain_end(ctx, drain));
+    return emit_list(ctx, corners, out_space, d_out, sizeof(vslam_corner), total, capacity, drain.on);
 }
 
 int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride,

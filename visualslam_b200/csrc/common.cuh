@@ -60,6 +60,9 @@ struct vslam_ctx {
     int up_chunk = 0, up_chunks = 0;   // frames per upload chunk, chunks in flight (0: frames were already on the device)
     int up_total = 0, up_foff = 0;     // chunks of the last upload; first uploaded frame the current call looks at
     size_t up_ds = 0;                  // bytes between uploaded frames
+    // host result lists leave chunk by chunk on a third stream while later chunks compute (capi.cu: ListDrain)
+    cudaStream_t down_stream = nullptr;
+    std::vector<cudaEvent_t> down_ev;
     void *pinned = nullptr;        // small pinned host scratch for counters
     size_t pinned_cap = 0;
     // cached tap tables of the fused octave kernel (passed by value as kernel parameters)

@@ -31,6 +31,7 @@ namespace vslam {
 
 namespace {
 constexpr int FR = kFusedR;
+constexpr int kMmaThreads = 288;            // eight compute warps and a service warp (queued localisations, emission)
 constexpr int TRP = 20;                     // words per column pair of a tile: 2 history + 16 row pairs (+2: conflict-free STS)
 constexpr int N_G = 3, N_D = 5;             // G tiles: Gaussian levels 1..3; D tiles: DoG levels 0..4
 constexpr int MAX_NS = 20;                  // sample columns per strip at FW = 64
@@ -169,7 +170,7 @@ __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1)
 // FW  = columns a CTA computes: 64, or 32 with the warps regrouped (H pass: 4 column blocks x 2 groups of three levels;
 //       V pass: 2 column blocks x 4 row blocks)
 template <int NCH, class GEO, int FW>
-__global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __grid_constant__ MmaArgs a) {
+__global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(const __grid_constant__ MmaArgs a) {
     constexpr int NT = 256;
     extern __shared__ __align__(16) u32 smem[];
     constexpr int NW = NT / 32;
@@ -200,6 +201,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     asm volatile("mov.u32 %0, %%ctaid.y;" : "=r"(seg));
     asm volatile("mov.u32 %0, %%ctaid.z;" : "=r"(frame));
     const int lane = tid & 31, warp = tid >> 5;
+    const bool svc = tid >= NT;                  // service warp: no blur passes, no detector
     const int g = lane >> 2, t = lane & 3;
     const int rows = a.rows, cols = a.cols;
     const int X0 = strip * FWO, X0c = X0 - 2, xs = X0c - geo.rmax();
@@ -214,7 +216,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     // ---- stage base rows y0 + rmax ..., columns xs16 ..., reflect-101 resolved (16-byte cp.async inside the image) ----
     const int SPQ = SP >> 4, n_stage = FR * SPQ;
     auto issue_stage = [&](int y0n) {
-        for (int q = tid; q < n_stage; q += NT) {
+        for (int q = svc ? n_stage : tid; q < n_stage; q += NT) {
             const int row = (int)(((u32)q * (u32)geo.spq_magic()) >> 16), j = q - row * SPQ;
             const int y = refl101(y0n + geo.rmax() + row, rows);
             const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
@@ -271,8 +273,10 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     };
     // samples queued by the detector (all three derivatives non-zero) of the step whose tiles start at row yb:
     // FeaturePointLocalization's full sequence, one lane per queued sample; survivors flag their segment in s_mask[mp]
+    // The service warp takes the first 32 samples while the compute warps are still in their H pass; the compute warps
+    // take what is left after it.
     auto run_queue = [&](int yb, int si_lo, int nq, int mp) {
-        for (int e = tid; e < nq; e += NT) {
+        for (int e = svc ? lane : 32 + tid; e < nq; e += NT + 32) {
             const int code = s_queue[e];                                             // k | level << 5 | sample row << 8
             const int k = code & 31, level = (code >> 5) & 3, sr = code >> 8;
             const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
@@ -292,24 +296,29 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
             }
         }
     };
-    // ordered emission: one warp per segment (level, sample row, strip) with survivors of a finished step
+    // ordered emission (service warp): the flagged segments (level, sample row, strip) of a finished step get consecutive
+    // staging ranges behind ONE atomic
     auto emit = [&](int si_lo, unsigned long long mask) {
-        for (int i = 0; mask; ++i) {
-            const int task = __ffsll((long long)mask) - 1;
-            mask &= mask - 1;
-            if ((i & (NW - 1)) != warp) continue;
+        int total = 0;
+        for (unsigned long long m = mask; m; m &= m - 1) {
+            const int task = __ffsll((long long)m) - 1;
+            const int res = lane < NS ? s_res[task * NS + lane] : -1;
+            total += __popc(__ballot_sync(0xffffffffu, res >= 0));
+        }
+        int off = 0;
+        if (lane == 0) off = atomicAdd(a.cursor, total);
+        off = __shfl_sync(0xffffffffu, off, 0);
+        for (unsigned long long m = mask; m; m &= m - 1) {
+            const int task = __ffsll((long long)m) - 1;
             const int res = lane < NS ? s_res[task * NS + lane] : -1;
             const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
             const int level = 1 + task % 3, si = si_lo + task / 3;
             const int cnt = __popc(bal);
-            const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
-            int off = 0;
             if (lane == 0) {
-                off = atomicAdd(a.cursor, cnt);
+                const int sg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.n_strips + strip;
                 a.seg_off[sg] = off;
                 a.seg_cnt[sg] = cnt;
             }
-            off = __shfl_sync(0xffffffffu, off, 0);
             if (res >= 0) {
                 const int pos = off + __popc(bal & ((1u << lane) - 1u));
                 if (pos < a.staging_cap) {
@@ -319,6 +328,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
                     a.staging[pos] = kp;
                 }
             }
+            off += cnt;
         }
     };
 
@@ -435,6 +445,8 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     // pass, so nobody waits there:
     //   X (after Bx)  detector tests + decimation of step c-1 | arrive | H pass of step c | wait | queued localisations of c-1
     //   Y (after By)  prefetch of step c+1's base rows, V pass of step c -> tiles, ordered emission of step c-1
+    // A ninth (service) warp skips the passes: it waits for the detector, runs the first 32 queued localisations while
+    // the compute warps are in their H pass, and emits the survivors (one global atomic per step) during the V pass.
     int p_y0 = 0;                                                             // the previous step (tiles hold it)
     bool p_own = false;
     int par = 0;                                                              // parity of the step the detector works on
@@ -445,14 +457,14 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();                                                      // Bx: staged rows landed; V pass / emission of c-1 done
         si_lo = detect_step(p_y0, p_own, par);
-        mbar_arrive(mb_sa);
+        if (!svc) mbar_arrive(mb_sa);                                         // the service warp goes straight to the wait
         // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
         // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them.
         // One basic block, software pipelined by hand: every chunk is multiplied (chunks outside a level's band meet the
         // zero padding of its tap copies: no band test, no branch), level l + 1's taps are loaded before level l's MMAs
         // and level l - 1's stores come after them (the compiler cannot hoist a shared load above a shared store it
         // cannot disambiguate).
-        {
+        if (!svc) {
             u32 fa[NCH][4], fb[NCH][4];
 #pragma unroll
             for (int ci = 0; ci < NCH; ++ci) {
@@ -518,7 +530,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
         __syncthreads();                                                      // By
         if (y0 + FR < ye) issue_stage(y0 + FR);                  // the H pass is done with the staging buffer
         // ---- 3. V pass + rounding + DoG -> tiles, levels in order ----
-        if (do_v) {
+        if (do_v && !svc) {
             u32 prev0[RBW], prev1[RBW];                          // previous level, columns 2g and 2g + 1, rows as 16-bit halves
 #pragma unroll
             for (int rb = 0; rb < RBW; ++rb) prev0[rb] = prev1[rb] = 0;
@@ -647,7 +659,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
         {
             const unsigned long long p_mask = s_mask[par];
             if (tid == 0) { s_nq = 0; s_mask[par ^ 1] = 0; }                  // the next step's queue and segment flags
-            if (p_mask) emit(si_lo, p_mask);
+            if (svc && p_mask) emit(si_lo, p_mask);
         }
         p_y0 = y0; p_own = do_v && y0 >= ys; par ^= 1;
     }
@@ -662,7 +674,7 @@ __global__ void __launch_bounds__(256, NCH <= 4 ? 2 : 1) octave_mma_k(const __gr
     __syncthreads();
     {
         const unsigned long long p_mask = s_mask[par];
-        if (p_mask) emit(si_lo, p_mask);
+        if (svc && p_mask) emit(si_lo, p_mask);
     }
 }
 
@@ -787,7 +799,7 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
     KernelSpan span(ctx, VSLAM_K_FUSED);
-    v->k<<<grid, 256, sm, ctx->stream>>>(a);
+    v->k<<<grid, kMmaThreads, sm, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

@@ -22,6 +22,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
+#include <vector>
 #include <type_traits>
 
 #include "detect_math.cuh"
@@ -130,6 +132,7 @@ int mma_strips(int cols, int fw) { return (cols + mma_fwo(fw) - 1) / mma_fwo(fw)
 // ---------------------------------------------------------------------------------------------------------------
 struct MmaArgs : OctaveIO {
     MmaTaps mt;
+    const uint4 *tab_image;         // mt.tab_bytes of shifted tap copies, built on the host once per (device, pyramid, octave, width)
 };
 
 namespace {
@@ -236,14 +239,8 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
         }
     };
     issue_stage(yv - K * FR);
-    // ---- tables: four byte-shifted, zero-padded copies of every level's taps; the division table; ring bases ----
-    for (int l = 0; l < 6; ++l) {
-        for (int s = 0; s < 4; ++s)
-            for (int j = tid; j < geo.cp(); j += NT) {
-                const int idx = j + s - geo.padl(l);
-                tab[(4 * l + s) * geo.cp() + j] = (idx >= 0 && idx < geo.n(l)) ? T.taps[l][idx] : (u8)0;
-            }
-    }
+    // ---- tables: four byte-shifted, zero-padded copies of every level's taps (host-built image); the division table ----
+    for (int i = tid; i < (T.tab_bytes >> 4); i += NT) ((uint4 *)tab)[i] = a.tab_image[i];
     for (int i = tid; i < 511; i += NT) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
     if (tid < 2) s_mask[tid] = 0;
     if (tid == 2) s_nq = 0;
@@ -731,6 +728,28 @@ const MmaVariant *mma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int
 }
 }  // namespace
 
+// device image of an octave's shifted tap copies: tab[(4 l + s) cp + j] = tap_l[j + s - padl_l] or 0
+const uint4 *mma_tab_image(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, const MmaTaps &mt) {
+    struct Entry { int dev; double sigma0; int ss, octave, fw; void *d; };
+    static std::vector<Entry> cache;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    for (const Entry &e : cache)
+        if (e.dev == ctx->device && e.sigma0 == sigma0 && e.ss == scale_samples && e.octave == octave && e.fw == mt.fw) return (const uint4 *)e.d;
+    std::vector<u8> img((size_t)mt.tab_bytes, 0);
+    for (int l = 0; l < 6; ++l)
+        for (int sft = 0; sft < 4; ++sft)
+            for (int j = 0; j < mt.cp; ++j) {
+                const int idx = j + sft - mt.lv[l].padl;
+                img[(size_t)(4 * l + sft) * mt.cp + j] = (idx >= 0 && idx < mt.lv[l].n) ? mt.taps[l][idx] : (u8)0;
+            }
+    void *d = nullptr;
+    if (cudaMalloc(&d, img.size()) != cudaSuccess) return nullptr;
+    if (cudaMemcpy(d, img.data(), img.size(), cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(d); return nullptr; }
+    cache.push_back({ctx->device, sigma0, scale_samples, octave, mt.fw, d});
+    return (const uint4 *)d;
+}
+
 // strips per frame of the kernel that will run the octave (the caller sizes the segment arrays with it)
 int octave_strips(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols) {
     MmaTaps mt;
@@ -786,6 +805,8 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     const MmaVariant *v = mma_plan(ctx, sigma0, scale_samples, io.octave, &a.mt, &sm);
     if (!v) return 1;
     static_cast<OctaveIO &>(a) = io;
+    a.tab_image = mma_tab_image(ctx, sigma0, scale_samples, io.octave, a.mt);
+    if (!a.tab_image) VS_FAIL(ctx, VSLAM_E_NOMEM, "tap table image of octave %d", io.octave);
     a.n_strips = mma_strips(a.cols, a.mt.fw);
     // vertical split only when the batch alone cannot fill the machine (every extra segment repeats the warm-up)
     const long long want = (long long)ctx->sm_count * 4;

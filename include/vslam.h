@@ -108,7 +108,7 @@ VSLAM_API long long vslam_launch_count(const vslam_ctx *ctx);
  * vslam_profile(ctx, 1) clears the accumulators and starts bracketing every launch; vslam_profile_read syncs the
  * stream and returns the summed duration and launch count of one kernel class. */
 typedef enum vslam_kernel_id {
-    VSLAM_K_UPSAMPLE = 0, VSLAM_K_HBLUR = 1, VSLAM_K_VBLUR = 2, VSLAM_K_DETECT = 3, VSLAM_K_COMPACT = 4,
+    VSLAM_K_UPSAMPLE = 0, VSLAM_K_PAD = 1 /* reflect-101 margins of the octave bases */, VSLAM_K_VBLUR = 2, VSLAM_K_DETECT = 3, VSLAM_K_COMPACT = 4,
     VSLAM_K_HARRIS = 5, VSLAM_K_GRAD = 6, VSLAM_K_FUSED = 7, VSLAM_KERNEL_COUNT = 8
 } vslam_kernel_id;
 VSLAM_API int vslam_profile(vslam_ctx *ctx, int enable);

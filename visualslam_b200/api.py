@@ -215,7 +215,7 @@ class Context:
     def sync(self):
         self._chk(load().vslam_sync(self.h))
 
-    KERNELS = ["upsample2x_k", "(unused)", "(unused2)", "dog_detect_k", "segment scan+gather", "harris_fused_k", "grad_k", "octave_fused_k"]
+    KERNELS = ["upsample2x_k", "reflect_pad_k", "(unused2)", "dog_detect_k", "segment scan+gather", "harris_fused_k", "grad_k", "octave_fused_k"]
 
     def profile(self, enable=True):
         self._chk(load().vslam_profile(self.h, 1 if enable else 0))

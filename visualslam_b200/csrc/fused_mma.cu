@@ -788,7 +788,7 @@ int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitc
     int bx = (rows * wpr + 255) / 256;
     if (bx > 64) bx = 64;
     const dim3 grid(bx, n_frames);
-    KernelSpan span(ctx, VSLAM_K_UPSAMPLE);
+    KernelSpan span(ctx, VSLAM_K_PAD);
     reflect_pad_k<<<grid, 256, 0, ctx->stream>>>(base, rows, cols, pitch, stride, pad);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;

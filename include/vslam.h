@@ -34,7 +34,9 @@ typedef enum vslam_status {
     VSLAM_OK = 0,
     VSLAM_E_INVALID = -1,  /* bad argument (null pointer, non-positive size, unsupported kernel width ...) */
     VSLAM_E_CUDA = -2,     /* a CUDA call failed; see vslam_last_error */
-    VSLAM_E_CAPACITY = -3, /* output list too small; counts[] hold the true sizes, lists hold the first `capacity` */
+    VSLAM_E_CAPACITY = -3, /* output list too small; counts[] hold the true sizes; the list holds the first `capacity`
+                            * entries as long as one launch batch emits at most max(capacity, 2^20) entries (the staging
+                            * list's size), otherwise the first `capacity` of an unspecified, ordered subset */
     VSLAM_E_NOMEM = -4     /* device or host allocation failed */
 } vslam_status;
 

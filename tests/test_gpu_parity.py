@@ -210,6 +210,38 @@ def test_full_size_properties(ctx):
     assert np.array_equal(hr["response"][0], ref["response"]) and hr["counts"] == [len(ref["corners"])]
 
 
+def test_4k_frame_vs_oracle(ctx):
+    """BASELINE.json's 4K size: one natural-tile frame, DoG keypoints and the Harris response / corners against the C oracle."""
+    f = synth.frame(2, 2160, 3840)
+    res = ctx.dog_keypoints(f)
+    kc, _, _ = O.dog_keypoints(f)
+    assert res["counts"] == [len(kc)] and np.array_equal(kp_array(res["keypoints"]), kc)
+    hr = ctx.harris(f)
+    ref = O.harris(f)
+    assert np.array_equal(hr["response"][0], ref["response"])
+    c = hr["corners"]
+    assert hr["counts"] == [len(ref["corners"])] and np.array_equal(np.stack([c["row"], c["col"]], 1), ref["corners"])
+
+
+def test_8k_properties(ctx):
+    """BASELINE.json's 8K size (the oracle would take minutes): batch independence, agreement of the two octave kernels'
+    strip decompositions on the top-left 4K crop's interior, constant frames."""
+    f = np.stack([synth.frame(i, 4320, 7680) for i in (1, 6)], 0)
+    both = ctx.dog_keypoints(f)
+    one = ctx.dog_keypoints(f[1])
+    n0, n1 = both["counts"]
+    assert n0 > 1000 and one["counts"] == [n1]
+    assert np.array_equal(one["keypoints"], both["keypoints"][n0:n0 + n1])
+    up = ctx.upload(f)                                            # chunked upload path at this size
+    again = ctx.dog_keypoints(up)
+    assert again["counts"] == [n0, n1] and np.array_equal(again["keypoints"], both["keypoints"])
+    h2 = ctx.harris(f, want_maps=False, capacity=1 << 22)
+    h1 = ctx.harris(f[0], want_maps=False, capacity=1 << 22)
+    assert not h2["overflow"] and h1["counts"] == [h2["counts"][0]] and np.array_equal(h1["corners"], h2["corners"][:h2["counts"][0]])
+    flat = np.full((4320, 7680), 200, np.uint8)
+    assert ctx.dog_keypoints(flat)["counts"] == [0] and ctx.harris(flat, want_maps=False)["counts"] == [0]
+
+
 def test_shared_chunked_upload_gives_the_same_lists(ctx):
     """vslam_upload_frames: one asynchronous chunked upload (several chunks at this size) serves both detectors; the
     lists equal those of the plain host-frame calls, frame by frame, and a second upload invalidates nothing it should not."""

@@ -242,6 +242,21 @@ def test_8k_properties(ctx):
     assert ctx.dog_keypoints(flat)["counts"] == [0] and ctx.harris(flat, want_maps=False)["counts"] == [0]
 
 
+def test_two_devices_in_one_process(ctx):
+    """Contexts on two devices of one process (function attributes and table images are per device)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU")
+    import visualslam_b200 as vs
+    f = np.stack([synth.frame(i, 300, 500) for i in (0, 7)], 0)
+    a = ctx.dog_keypoints(f)
+    c1 = vs.Context(1)
+    b = c1.dog_keypoints(f)
+    assert a["counts"] == b["counts"] and np.array_equal(a["keypoints"], b["keypoints"])
+    ha, hb = ctx.harris(f), c1.harris(f)
+    assert np.array_equal(ha["response"], hb["response"]) and np.array_equal(ha["corners"], hb["corners"])
+
+
 def test_shared_chunked_upload_gives_the_same_lists(ctx):
     """vslam_upload_frames: one asynchronous chunked upload (several chunks at this size) serves both detectors; the
     lists equal those of the plain host-frame calls, frame by frame, and a second upload invalidates nothing it should not."""

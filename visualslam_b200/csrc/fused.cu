@@ -507,7 +507,8 @@ int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames) {
     a.seg_rows = seg_rows;
     a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
-    static bool attr_done = false;
+    static bool attr_done_dev[64] = {false};                         // function attributes belong to a device
+    bool &attr_done = attr_done_dev[ctx->device >= 0 && ctx->device < 64 ? ctx->device : 0];
     if (!attr_done) {
         cudaFuncAttributes fa;
         VS_CUDA(ctx, cudaFuncGetAttributes(&fa, octave_fused_k<128>));

@@ -700,19 +700,28 @@ const MmaVariant *mma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int
     static const int use_static = getenv("VSLAM_MMA_STATIC") ? atoi(getenv("VSLAM_MMA_STATIC")) : 1;
     static const int force_fw = getenv("VSLAM_MMA_FW") ? atoi(getenv("VSLAM_MMA_FW")) : 0;
     if (!mode) return nullptr;
-    static int static_smem = -1;
-    if (static_smem < 0) {
-        cudaFuncAttributes fa;
-        int mx = 0;
-        for (int i = 0; i < NV; ++i) {
-            if (cudaFuncGetAttributes(&fa, variants[i].k) != cudaSuccess) return nullptr;
-            if ((int)fa.sharedSizeBytes > mx) mx = (int)fa.sharedSizeBytes;
+    // function attributes belong to a device: set them once per device this process launches on
+    static int static_smem_dev[64];
+    static bool dev_init = false;
+    static std::mutex mu;
+    int static_smem;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!dev_init) { for (int &v : static_smem_dev) v = -1; dev_init = true; }
+        const int di = ctx->device >= 0 && ctx->device < 64 ? ctx->device : 0;
+        if (static_smem_dev[di] < 0) {
+            cudaFuncAttributes fa;
+            int mx = 0;
+            for (int i = 0; i < NV; ++i) {
+                if (cudaFuncGetAttributes(&fa, variants[i].k) != cudaSuccess) return nullptr;
+                if ((int)fa.sharedSizeBytes > mx) mx = (int)fa.sharedSizeBytes;
+            }
+            for (int i = 0; i < NV; ++i)
+                if (cudaFuncSetAttribute(variants[i].k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - mx) != cudaSuccess) return nullptr;
+            static_smem_dev[di] = mx;
         }
-        for (int i = 0; i < NV; ++i)
-            if (cudaFuncSetAttribute(variants[i].k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - mx) != cudaSuccess) return nullptr;
-        static_smem = mx;
+        static_smem = static_smem_dev[di];
     }
-    (void)ctx;
     for (int fw = (force_fw == 32 ? 32 : 64); fw >= 32; fw -= 32) {
         if (build_mma_taps(sigma0, scale_samples, octave, fw, mt)) continue;
         *smem = mma_smem_bytes(*mt);

@@ -31,6 +31,24 @@ KP_CAP_PER_MPX = 40000         # output list capacity (entries per input Mpix), 
 METRIC = "Mpix/s (frames/s) DoG+Harris at 1/2/4/8 B200; % HBM roofline vs host CPU"
 
 
+def bind_near_gpu(index):
+    """One process per GPU: run (and first-touch the pinned host buffers) on the CPUs NVML reports as local to the GPU, so
+    that eight ranks' uploads do not all cross the socket interconnect.  Returns the CPU count bound to, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -162,6 +180,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
+    numa = bind_near_gpu(local) if world > 1 else None           # pinned buffers are first-touched on the GPU's own NUMA node
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -260,7 +279,8 @@ def main():
             "config": {"workload": f"synthetic {w}x{h} grayscale batch of {nf} frames per GPU, DoG (4 octaves x 6 levels, sigma 1.6) "
                                    f"+ Harris pipeline mode, {world} B200", "frames_per_gpu": nf, "rows": h, "cols": w,
                        "l2": f"inputs larger than L2 ({px_step / 1e6:.0f} MB batch per step, 8 unique frames cycled)",
-                       "parallelism": f"frame-batch dp{world}, no data-path collective"},
+                       "parallelism": f"frame-batch dp{world}, no data-path collective",
+                       "host_cpus_bound": numa},
             "keypoints_per_step": int(nk), "corners_per_step": int(nc), "clocks": clocks, "gpu_launches": int(launches),
             "e2e": e2e}
     if prof:

@@ -183,6 +183,11 @@ VSLAM_API int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, 
 /* ---- per-function entry points: the reference's own function granularity, for the C++17 mirror in
  *      visualslam_b200/host/ (HOST buffers, dense unless a pitch is given; each call synchronises).  The throughput
  *      paths above (vslam_dog_keypoints, vslam_harris) fuse these stages; results are identical. ------------------- */
+/* cvtColor(img_color, img, COLOR_BGR2GRAY) on 8-bit BGR frames (Diff_of_Gauss.cpp:739, tests/GaussPyramid_Test.cpp:81):
+ * gray = (3735 B + 19235 G + 9798 R + 2^14) >> 15.  bgr: n_frames x rows x cols x 3 bytes (pitch in bytes per row),
+ * gray: n_frames x rows x cols. */
+VSLAM_API int vslam_bgr_to_gray(vslam_ctx *ctx, const uint8_t *bgr, int n_frames, int rows, int cols, size_t pitch,
+                                size_t frame_stride, uint8_t *gray, size_t gray_pitch, size_t gray_stride);
 /* GaussianBlur(img, blurred, Size(3,3), 0, 0, BORDER_DEFAULT) on 8U (Harris_corners.cpp:157-158) */
 VSLAM_API int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst,
                                    size_t dst_pitch);

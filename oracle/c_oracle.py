@@ -40,6 +40,7 @@ def lib():
         L.vo_upsample2x.restype = None
         L.vo_blur_8u.argtypes = [u8p, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, u8p]
         L.vo_gaussian_blur_8u.argtypes = [u8p, C.c_int, C.c_int, C.c_double, u8p]
+        L.vo_bgr_to_gray.argtypes = [u8p, C.c_int, C.c_int, u8p]
         L.vo_dog.argtypes = [u8p, u8p, C.c_size_t, u8p]
         L.vo_dog.restype = None
         L.vo_half_size.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -101,6 +102,14 @@ def upsample2x(img: np.ndarray) -> np.ndarray:
     h, w = img.shape
     out = np.empty((2 * h, 2 * w), np.uint8)
     lib().vo_upsample2x(_u8(img), h, w, _u8(out))
+    return out
+
+
+def bgr_to_gray(bgr: np.ndarray) -> np.ndarray:
+    bgr = np.ascontiguousarray(bgr, np.uint8)
+    h, w, _ = bgr.shape
+    out = np.empty((h, w), np.uint8)
+    assert lib().vo_bgr_to_gray(_u8(bgr), h, w, _u8(out)) == 0
     return out
 
 

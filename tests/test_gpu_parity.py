@@ -242,6 +242,21 @@ def test_8k_properties(ctx):
     assert ctx.dog_keypoints(flat)["counts"] == [0] and ctx.harris(flat, want_maps=False)["counts"] == [0]
 
 
+def test_bgr_to_gray(ctx, images):
+    """vslam_bgr_to_gray (the ingest step in front of the pyramid, Diff_of_Gauss.cpp:739) against the golden grey image and
+    the oracle on awkward shapes (odd widths: the byte path; batches)."""
+    import os
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "home_bgr.npz")) as z:
+        bgr = z["home_bgr"]
+    assert np.array_equal(ctx.bgr_to_gray(bgr), images["home_cvt"])
+    rng = np.random.default_rng(5)
+    for shape in [(1, 1, 1), (2, 3, 5), (3, 17, 33), (1, 64, 128), (4, 31, 250)]:
+        x = rng.integers(0, 256, shape + (3,), dtype=np.uint8)
+        got = ctx.bgr_to_gray(x)
+        for f in range(shape[0]):
+            assert np.array_equal(got[f], O.bgr_to_gray(x[f])), shape
+
+
 def test_two_devices_in_one_process(ctx):
     """Contexts on two devices of one process (function attributes and table images are per device)."""
     import torch

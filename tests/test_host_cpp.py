@@ -82,6 +82,22 @@ def test_dog_executable_matches_golden(tmp_path, images, golden_lists, stem):
 
 
 @pytest.mark.gpu
+def test_dog_executable_on_colour_input(tmp_path, golden_lists):
+    """./DoG on a colour PPM: imread(IMREAD_COLOR) + cvtColor on the GPU (Diff_of_Gauss.cpp:730-739), then the golden keypoints."""
+    _build()
+    with np.load(os.path.join(ROOT, "tests", "golden", "home_bgr.npz")) as z:
+        bgr = z["home_bgr"]
+    p = str(tmp_path / "home.ppm")
+    with open(p, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (bgr.shape[1], bgr.shape[0]))
+        f.write(np.ascontiguousarray(bgr[..., ::-1]).tobytes())          # PPM is RGB
+    out = str(tmp_path / "kp.txt")
+    r = _run("DoG", p, "--out", out, "--fused")
+    assert r.returncode == 0, r.stderr
+    assert np.array_equal(np.loadtxt(out, dtype=np.int64).reshape(-1, 6), golden_lists["dog_home"])
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("stem", ["blox", "chessboard", "building"])
 def test_harris_executable_matches_golden(tmp_path, images, golden_lists, stem):
     from conftest import image_for

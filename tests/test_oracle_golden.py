@@ -24,6 +24,16 @@ def test_reference_pins_pyramid_test(golden):
     assert golden["pyramid"]["building"]["sizes"] == [[1200, 1736], [600, 868], [300, 434], [150, 217]]
 
 
+def test_bgr_to_gray_matches_golden(images):
+    """Diff_of_Gauss.cpp:730,739: the colour decode of home.jpg (fixture) through the oracle's cvtColor is the golden grey image."""
+    import os
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "home_bgr.npz")) as z:
+        bgr = z["home_bgr"]
+    assert np.array_equal(O.bgr_to_gray(bgr), images["home_cvt"])
+    v = np.arange(256, dtype=np.uint8)
+    assert np.array_equal(O.bgr_to_gray(np.stack([v, v, v], -1)[None])[0], v)       # grey in, grey out
+
+
 def test_taps_match_cv2_impulse_tables(golden):
     for key, e in golden["taps"].items():
         t = O.gauss_taps(e["sigma"])

@@ -56,7 +56,7 @@ EXPORTS = [
     "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
     "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
-    "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
+    "vslam_bgr_to_gray", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
     "vslam_dog_detect_octave", "vslam_edge_responses", "vslam_localize", "vslam_edge_from_windows",
 ]
 
@@ -85,6 +85,7 @@ def load():
     L.vslam_calculate_num_octaves.argtypes = [i, i]
     L.vslam_gauss_ksize.argtypes = [C.c_double]
     L.vslam_gauss_taps.argtypes = [C.c_double, i, C.POINTER(C.c_int32)]
+    L.vslam_bgr_to_gray.argtypes = [vp, vp, i, i, i, sz, sz, vp, sz, sz]
     L.vslam_pyramid_build.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(vp)]
     L.vslam_pyramid_destroy.argtypes = [vp]; L.vslam_pyramid_destroy.restype = None
     L.vslam_pyramid_num_octaves.argtypes = [vp]
@@ -289,6 +290,19 @@ class Context:
         cl = list(counts)
         return {"keypoints": host[:min(sum(cl), capacity)] if host is not None else out, "counts": cl,
                 "overflow": rc == E_CAPACITY}
+
+    def bgr_to_gray(self, bgr):
+        """cvtColor(COLOR_BGR2GRAY) of (rows, cols, 3) or (n, rows, cols, 3) uint8 frames -> uint8 gray frames."""
+        a = np.ascontiguousarray(bgr, np.uint8)
+        single = a.ndim == 3
+        if single:
+            a = a[None]
+        if a.ndim != 4 or a.shape[3] != 3:
+            raise ValueError("bgr frames must be (rows, cols, 3) or (n, rows, cols, 3)")
+        n, r, c, _ = a.shape
+        out = np.empty((n, r, c), np.uint8)
+        self._chk(load().vslam_bgr_to_gray(self.h, a.ctypes.data, n, r, c, 3 * c, 3 * c * r, out.ctypes.data, c, c * r))
+        return out[0] if single else out
 
     def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None, corners_out=None):
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)

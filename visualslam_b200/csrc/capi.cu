@@ -821,6 +821,25 @@ static int stage_check(vslam_ctx *ctx, const void *a, const void *b, int rows, i
     return VSLAM_OK;
 }
 
+int vslam_bgr_to_gray(vslam_ctx *ctx, const uint8_t *bgr, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride,
+                      uint8_t *gray, size_t gray_pitch, size_t gray_stride) {
+    if (!ctx || !bgr || !gray || n_frames <= 0 || rows <= 0 || cols <= 0) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (n_frames > 65535 || rows > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "bgr_to_gray: %d frames of %d rows per call", n_frames, rows);
+    if (pitch < 3 * (size_t)cols || gray_pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch smaller than a row");
+    if (n_frames > 1 && (frame_stride < pitch * (size_t)rows || gray_stride < gray_pitch * (size_t)rows)) VS_FAIL(ctx, VSLAM_E_INVALID, "frame stride too small");
+    const size_t sp = round_up(3 * (size_t)cols, 4), ss = sp * rows, dp = round_up((size_t)cols, 4), ds = dp * rows;
+    const size_t b[2] = {ss * n_frames, ds * n_frames};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    for (int f = 0; f < n_frames; ++f)
+        VS_CUDA(ctx, cudaMemcpy2DAsync(d[0] + ss * f, sp, bgr + frame_stride * f, pitch, 3 * (size_t)cols, rows, cudaMemcpyHostToDevice, ctx->stream));
+    VS_TRY(launch_bgr2gray(ctx, d[0], rows, cols, sp, ss, d[1], dp, ds, n_frames));
+    for (int f = 0; f < n_frames; ++f)
+        VS_CUDA(ctx, cudaMemcpy2DAsync(gray + gray_stride * f, gray_pitch, d[1] + ds * f, dp, cols, rows, cudaMemcpyDeviceToHost, ctx->stream));
+    return vslam_sync(ctx);
+}
+
 int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst, size_t dst_pitch) {
     VS_TRY(stage_check(ctx, src, dst, rows, cols));
     if (pitch < (size_t)cols || dst_pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch smaller than cols");

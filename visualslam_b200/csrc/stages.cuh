@@ -3,6 +3,8 @@
 #include "common.cuh"
 
 namespace vslam {
+int launch_bgr2gray(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, size_t stride, u8 *dst, size_t dpitch,
+                    size_t dstride, int n_frames);
 int launch_blur3(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, u8 *dst, size_t dpitch);
 int launch_sobel1(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, float *gx, float *gy);
 int launch_harris_grad(vslam_ctx *ctx, const float *ix, const float *iy, int rows, int cols, int pad, float k, float *out);

@@ -2,7 +2,7 @@
 // pyramid (4 octaves, sigma 1.6), per octave initialKeypointDetection + filterKeypoints' edge threshold, with the
 // reference's stdout lines (:784, :786).  Orientation / SIFT descriptors / drawing follow the hot path in the reference
 // and are out of scope; HighGUI is unavailable on this box, so keypoints go to a text file instead.
-//   usage: DoG [image.pgm] [--fused] [--out keypoints.txt]      (default image: ../images/home.pgm, like the reference's
+//   usage: DoG [image.pgm|image.ppm] [--fused] [--out keypoints.txt]      (default image: ../images/home.pgm, like the reference's
 //   ../images/home.jpg; JPEG decoding is not part of the path -- convert once with any tool)
 #include <cstdio>
 #include <cstring>
@@ -19,11 +19,14 @@ int main(int argc, char **argv) {
     for (int i = 1; i < argc; ++i) {
         if (!strcmp(argv[i], "--fused")) fused = true;
         else if (!strcmp(argv[i], "--out") && i + 1 < argc) out_path = argv[++i];
-        else if (!strcmp(argv[i], "--help")) { printf("usage: DoG [image.pgm] [--fused] [--out keypoints.txt]\n"); return 0; }
+        else if (!strcmp(argv[i], "--help")) { printf("usage: DoG [image.pgm|image.ppm] [--fused] [--out keypoints.txt]\n"); return 0; }
         else path = argv[i];
     }
     try {
-        Mat img = vslam::imread_pgm(path);
+        // Diff_of_Gauss.cpp:730-739: imread(IMREAD_COLOR) + cvtColor(COLOR_BGR2GRAY); a grey PGM is taken as it is
+        Mat img_color = vslam::imread(path, vslam::IMREAD_COLOR);
+        Mat img;
+        vslam::cvtColor(img_color, img, vslam::COLOR_BGR2GRAY);
         int numOctaves = 4;          // Diff_of_Gauss.cpp:742
         double pyr_sigma = 1.6;      // :743
         int windowSize = 3;          // :772

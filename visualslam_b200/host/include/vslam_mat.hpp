@@ -14,7 +14,8 @@
 
 namespace vslam {
 
-constexpr int CV_8U = 0, CV_32F = 5;            // OpenCV's depth codes, so ported call sites read the same
+constexpr int CV_8U = 0, CV_32F = 5, CV_8UC3 = 16;   // OpenCV's type codes, so ported call sites read the same
+constexpr int IMREAD_GRAYSCALE = 0, IMREAD_COLOR = 1, COLOR_BGR2GRAY = 6;
 
 struct Size {
     int width = 0, height = 0;
@@ -32,14 +33,15 @@ class Mat {
     Mat(int r, int c, int type) { create(r, c, type); }
     static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }   // create() zero-fills
     void create(int r, int c, int type) {
-        if (r < 0 || c < 0 || (type != CV_8U && type != CV_32F)) throw std::invalid_argument("vslam::Mat: bad shape or type");
+        if (r < 0 || c < 0 || (type != CV_8U && type != CV_32F && type != CV_8UC3)) throw std::invalid_argument("vslam::Mat: bad shape or type");
         rows = r; cols = c; type_ = type;
         step = (size_t)c * elemSize();
         buf_ = std::shared_ptr<uint8_t>(new uint8_t[step * (size_t)r + 1](), std::default_delete<uint8_t[]>());
         data = buf_.get();
     }
     int type() const { return type_; }
-    size_t elemSize() const { return type_ == CV_32F ? 4 : 1; }
+    size_t elemSize() const { return type_ == CV_32F ? 4 : type_ == CV_8UC3 ? 3 : 1; }
+    int channels() const { return type_ == CV_8UC3 ? 3 : 1; }
     bool empty() const { return !data || rows == 0 || cols == 0; }
     Size size() const { return Size{cols, rows}; }
     size_t total() const { return (size_t)rows * cols; }
@@ -63,6 +65,11 @@ class Mat {
 
 // headless IO: binary PGM (P5, 8U) and PFM (Pf, little endian, 32F; rows stored top to bottom with a negative scale)
 Mat imread_pgm(const std::string &path);                 // throws std::runtime_error
+// imread(path, IMREAD_COLOR / IMREAD_GRAYSCALE) for binary PNM files: P6 -> CV_8UC3 in BGR order (what cv::imread hands to
+// cvtColor at Diff_of_Gauss.cpp:730-739), P5 -> CV_8U (IMREAD_COLOR replicates it into three channels, as cv::imread does)
+Mat imread(const std::string &path, int flags = IMREAD_COLOR);
+// cvtColor(src, dst, COLOR_BGR2GRAY) on the GPU (vslam_bgr_to_gray); the only conversion the reference uses
+void cvtColor(const Mat &src, Mat &dst, int code);
 void imwrite_pgm(const std::string &path, const Mat &m);
 void imwrite_pfm(const std::string &path, const Mat &m);
 

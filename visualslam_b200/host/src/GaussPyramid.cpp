@@ -25,6 +25,16 @@ vslam_ctx *host_context() {
     return ctx;
 }
 
+// cvtColor(img_color, img, COLOR_BGR2GRAY): Diff_of_Gauss.cpp:739, tests/GaussPyramid_Test.cpp:81
+void cvtColor(const Mat &src, Mat &dst, int code) {
+    if (code != COLOR_BGR2GRAY || src.type() != CV_8UC3) throw std::invalid_argument("cvtColor: COLOR_BGR2GRAY of a CV_8UC3 image only");
+    Mat out(src.rows, src.cols, CV_8U);
+    if (!src.empty())
+        throw_on(vslam_bgr_to_gray(host_context(), src.data, 1, src.rows, src.cols, src.step, src.step * (size_t)src.rows, out.data, out.step,
+                                   out.step * (size_t)out.rows), "vslam_bgr_to_gray");
+    dst = out;
+}
+
 }  // namespace vslam
 
 using namespace vslam;

@@ -32,6 +32,32 @@ Mat imread_pgm(const std::string &path) {
     return m;
 }
 
+Mat imread(const std::string &path, int flags) {
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) throw std::runtime_error("cannot open " + path);
+    char magic[3] = {0, 0, 0};
+    if (fread(magic, 1, 2, f) != 2 || magic[0] != 'P' || (magic[1] != '5' && magic[1] != '6')) { fclose(f); throw std::runtime_error(path + ": not a binary PNM (P5 / P6)"); }
+    const int ch = magic[1] == '6' ? 3 : 1;
+    const int w = pnm_int(f), h = pnm_int(f), mx = pnm_int(f);
+    if (w <= 0 || h <= 0 || mx <= 0 || mx > 255) { fclose(f); throw std::runtime_error(path + ": unsupported PNM header"); }
+    std::vector<uint8_t> raw((size_t)w * h * ch);
+    const size_t got = fread(raw.data(), 1, raw.size(), f);
+    fclose(f);
+    if (got != raw.size()) throw std::runtime_error(path + ": truncated PNM");
+    if (flags == IMREAD_GRAYSCALE) {
+        if (ch != 1) throw std::runtime_error(path + ": IMREAD_GRAYSCALE of a colour PNM is the decoder's own conversion; read it IMREAD_COLOR and cvtColor");
+        Mat m(h, w, CV_8U);
+        std::memcpy(m.data, raw.data(), raw.size());
+        return m;
+    }
+    Mat m(h, w, CV_8UC3);
+    for (size_t i = 0; i < (size_t)w * h; ++i) {
+        const uint8_t r = raw[ch * i], g = raw[ch * i + (ch == 3 ? 1 : 0)], b = raw[ch * i + (ch == 3 ? 2 : 0)];
+        m.data[3 * i] = b; m.data[3 * i + 1] = g; m.data[3 * i + 2] = r;
+    }
+    return m;
+}
+
 void imwrite_pgm(const std::string &path, const Mat &m) {
     if (m.type() != CV_8U) throw std::invalid_argument("imwrite_pgm: CV_8U only");
     FILE *f = fopen(path.c_str(), "wb");

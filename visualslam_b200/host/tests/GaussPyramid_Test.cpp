@@ -15,7 +15,9 @@ int main(int argc, char **argv) {
     const std::string path = argc > 1 ? argv[1] : "../images/building.pgm";
     try {
         cout << "vslam version : " << vslam_version() << endl;
-        Mat img = vslam::imread_pgm(path);
+        Mat img_color = vslam::imread(path, vslam::IMREAD_COLOR);      // tests/GaussPyramid_Test.cpp:78-81
+        Mat img;
+        vslam::cvtColor(img_color, img, vslam::COLOR_BGR2GRAY);
         int numOctaves = 4;
         double sigma = 1.6;
         GaussPyramid pyramid{img, numOctaves, sigma};

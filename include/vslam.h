@@ -188,6 +188,16 @@ VSLAM_API int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, 
  * gray: n_frames x rows x cols. */
 VSLAM_API int vslam_bgr_to_gray(vslam_ctx *ctx, const uint8_t *bgr, int n_frames, int rows, int cols, size_t pitch,
                                 size_t frame_stride, uint8_t *gray, size_t gray_pitch, size_t gray_stride);
+/* SLAM::Rotation::rotate_mat_CCW(I, center, angles) (include/src/Rotation/rotation.cpp:66-84) on an 8U image: every
+ * output pixel gathers I at rotate_pt_CW(pixel) (:19-28, int offsets x float cos/sin, truncated) when the rotated point
+ * has 0 < x < cols and 0 < y < rows, else 0.  (cos_a, sin_a) = Rotation::cos_sin_of_angle(theta), computed by the caller. */
+VSLAM_API int vslam_rotate_mat_ccw(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, int center_x,
+                                   int center_y, float cos_a, float sin_a, uint8_t *dst, size_t dst_pitch);
+/* SLAM::Rotation::getRotatedWindow(I, center, windowSize, theta) (rotation.cpp:87-108): dst[i][j] = I at
+ * rotate_pt_CW(center - windowSize/2 + (j, i)), window x window (the reference's loops run one row / column further
+ * and write past its ROI; its reads outside the image are undefined: 0 here). */
+VSLAM_API int vslam_rotated_window(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, int center_x,
+                                   int center_y, int window, float cos_a, float sin_a, uint8_t *dst, size_t dst_pitch);
 /* GaussianBlur(img, blurred, Size(3,3), 0, 0, BORDER_DEFAULT) on 8U (Harris_corners.cpp:157-158) */
 VSLAM_API int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst,
                                    size_t dst_pitch);

@@ -41,6 +41,9 @@ def lib():
         L.vo_blur_8u.argtypes = [u8p, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, u8p]
         L.vo_gaussian_blur_8u.argtypes = [u8p, C.c_int, C.c_int, C.c_double, u8p]
         L.vo_bgr_to_gray.argtypes = [u8p, C.c_int, C.c_int, u8p]
+        L.vo_cos_sin_of_angle.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]; L.vo_cos_sin_of_angle.restype = None
+        L.vo_rotate_mat_ccw.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, u8p]; L.vo_rotate_mat_ccw.restype = None
+        L.vo_rotated_window.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, u8p]; L.vo_rotated_window.restype = None
         L.vo_dog.argtypes = [u8p, u8p, C.c_size_t, u8p]
         L.vo_dog.restype = None
         L.vo_half_size.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -102,6 +105,26 @@ def upsample2x(img: np.ndarray) -> np.ndarray:
     h, w = img.shape
     out = np.empty((2 * h, 2 * w), np.uint8)
     lib().vo_upsample2x(_u8(img), h, w, _u8(out))
+    return out
+
+
+def cos_sin_of_angle(theta_deg: float):
+    c, s = C.c_float(), C.c_float()
+    lib().vo_cos_sin_of_angle(theta_deg, C.byref(c), C.byref(s))
+    return c.value, s.value
+
+
+def rotate_mat_ccw(img: np.ndarray, center, cos_sin) -> np.ndarray:
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty_like(img)
+    lib().vo_rotate_mat_ccw(_u8(img), img.shape[0], img.shape[1], int(center[0]), int(center[1]), cos_sin[0], cos_sin[1], _u8(out))
+    return out
+
+
+def rotated_window(img: np.ndarray, center, window: int, cos_sin) -> np.ndarray:
+    img = np.ascontiguousarray(img, np.uint8)
+    out = np.empty((window, window), np.uint8)
+    lib().vo_rotated_window(_u8(img), img.shape[0], img.shape[1], int(center[0]), int(center[1]), window, cos_sin[0], cos_sin[1], _u8(out))
     return out
 
 

@@ -257,6 +257,19 @@ def test_bgr_to_gray(ctx, images):
             assert np.array_equal(got[f], O.bgr_to_gray(x[f])), shape
 
 
+@pytest.mark.parametrize("theta", [0.0, 33.0, 45.0, 90.0, 180.0, 271.5])
+def test_rotation_gathers_vs_oracle(ctx, images, theta):
+    """vslam_rotate_mat_ccw / vslam_rotated_window (SLAM::Rotation, rotation.cpp:66-108) against the oracle's literal arithmetic."""
+    img = images["blox"]
+    cs = O.cos_sin_of_angle(theta)
+    center = (img.shape[1] // 2, img.shape[0] // 2)
+    assert np.array_equal(ctx.rotate_mat_ccw(img, center, cs), O.rotate_mat_ccw(img, center, cs))
+    for window, c in ((16, center), (100, center), (16, (3, 250))):          # the last one reads outside the image
+        assert np.array_equal(ctx.rotated_window(img, c, window, cs), O.rotated_window(img, c, window, cs))
+    odd = synth.frame(3, 37, 91)
+    assert np.array_equal(ctx.rotate_mat_ccw(odd, (10, 30), cs), O.rotate_mat_ccw(odd, (10, 30), cs))
+
+
 def test_two_devices_in_one_process(ctx):
     """Contexts on two devices of one process (function attributes and table images are per device)."""
     import torch

@@ -33,7 +33,7 @@ def _run(exe, *args):
 
 def test_host_layer_builds_and_prints_usage():
     _build()
-    for exe in ("DoG", "Harris", os.path.join("tests", "Pyramid_Test"), "libvslam_host.a"):
+    for exe in ("DoG", "Harris", os.path.join("tests", "Pyramid_Test"), os.path.join("tests", "RotateImgTest"), "libvslam_host.a"):
         assert os.path.exists(os.path.join(BIN, exe)), exe
     for exe in ("DoG", "Harris"):
         r = _run(exe, "--help")
@@ -118,6 +118,29 @@ def test_harris_executable_matches_golden(tmp_path, images, golden_lists, stem):
         resp = resp.reshape(img.shape)
         assert np.array_equal(resp[want[:, 0], want[:, 1]], vals)
     assert outs[0] == outs[1]       # function-by-function and fused pipelines print the same numbers
+
+
+@pytest.mark.gpu
+def test_rotate_img_test_executable(tmp_path, images):
+    """tests/RotateImgTest (rotate_image_test.cpp:55-84): the timing line, and the dumped gathers equal the oracle's."""
+    from oracle import c_oracle as O
+    _build()
+    img = images["blox"]
+    p = str(tmp_path / "blox.pgm")
+    _pgm(p, img)
+    r = _run(os.path.join("tests", "RotateImgTest"), p, "--dump", str(tmp_path / "r"))
+    assert r.returncode == 0, r.stderr
+    assert "Time rotating 16x16 ROI (averaged for 100 runs):" in r.stdout
+    cs = O.cos_sin_of_angle(45.0)
+    center = (img.shape[1] // 2, img.shape[0] // 2)
+
+    def pgm(path):
+        raw = open(path, "rb").read()
+        parts = raw.split(b"\n", 3)
+        w, h = map(int, parts[1].split())
+        return np.frombuffer(parts[3], np.uint8).reshape(h, w)
+    assert np.array_equal(pgm(str(tmp_path / "r_rotated.pgm")), O.rotate_mat_ccw(img, center, cs))
+    assert np.array_equal(pgm(str(tmp_path / "r_roi.pgm")), O.rotated_window(img, center, 100, cs))
 
 
 @pytest.mark.gpu

@@ -34,6 +34,29 @@ def test_bgr_to_gray_matches_golden(images):
     assert np.array_equal(O.bgr_to_gray(np.stack([v, v, v], -1)[None])[0], v)       # grey in, grey out
 
 
+def test_rotation_known_answers():
+    """SLAM::Rotation (rotation.cpp:9-28, 66-108), parity unpinned (no reference vectors): known answers of the literal
+    float arithmetic.  0 degrees is the identity except row 0 / column 0 (the strict '> 0' tests of rotate_mat_CCW)."""
+    c0 = O.cos_sin_of_angle(0.0)
+    assert c0 == (1.0, 0.0)
+    c, s = O.cos_sin_of_angle(90.0)
+    assert s == 1.0 and c == np.float32(np.cos(np.float64(np.float32(90.0 * (np.pi / np.float64(np.float32(180.0)))))))
+    img = np.arange(1, 8 * 9 + 1, dtype=np.uint8).reshape(8, 9)
+    want = img.copy(); want[0, :] = 0; want[:, 0] = 0
+    assert np.array_equal(O.rotate_mat_ccw(img, (4, 4), c0), want)
+    assert np.array_equal(O.rotated_window(img, (4, 4), 4, c0), img[2:6, 2:6])
+    # literal numpy-float32 transcription of rotate_pt_CW for an arbitrary angle
+    cs = O.cos_sin_of_angle(33.0)
+    got = O.rotate_mat_ccw(img, (3, 5), cs)
+    cf, sf = np.float32(cs[0]), np.float32(cs[1])
+    for y in range(8):
+        for x in range(9):
+            rx, ry = np.float32(x - 3), np.float32(y - 5)
+            xr = int(np.float32(rx * cf) - np.float32(ry * sf)) + 3
+            yr = int(np.float32(rx * sf) + np.float32(ry * cf)) + 5
+            assert got[y, x] == (img[yr, xr] if 0 < xr < 9 and 0 < yr < 8 else 0)
+
+
 def test_taps_match_cv2_impulse_tables(golden):
     for key, e in golden["taps"].items():
         t = O.gauss_taps(e["sigma"])

@@ -56,7 +56,7 @@ EXPORTS = [
     "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
     "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
-    "vslam_bgr_to_gray", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
+    "vslam_bgr_to_gray", "vslam_rotate_mat_ccw", "vslam_rotated_window", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
     "vslam_dog_detect_octave", "vslam_edge_responses", "vslam_localize", "vslam_edge_from_windows",
 ]
 
@@ -86,6 +86,8 @@ def load():
     L.vslam_gauss_ksize.argtypes = [C.c_double]
     L.vslam_gauss_taps.argtypes = [C.c_double, i, C.POINTER(C.c_int32)]
     L.vslam_bgr_to_gray.argtypes = [vp, vp, i, i, i, sz, sz, vp, sz, sz]
+    L.vslam_rotate_mat_ccw.argtypes = [vp, vp, i, i, sz, i, i, C.c_float, C.c_float, vp, sz]
+    L.vslam_rotated_window.argtypes = [vp, vp, i, i, sz, i, i, i, C.c_float, C.c_float, vp, sz]
     L.vslam_pyramid_build.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(vp)]
     L.vslam_pyramid_destroy.argtypes = [vp]; L.vslam_pyramid_destroy.restype = None
     L.vslam_pyramid_num_octaves.argtypes = [vp]
@@ -303,6 +305,22 @@ class Context:
         out = np.empty((n, r, c), np.uint8)
         self._chk(load().vslam_bgr_to_gray(self.h, a.ctypes.data, n, r, c, 3 * c, 3 * c * r, out.ctypes.data, c, c * r))
         return out[0] if single else out
+
+    def rotate_mat_ccw(self, img, center, cos_sin):
+        """Rotation::rotate_mat_CCW(I, center=(x, y), angles=(cos, sin))."""
+        a = np.ascontiguousarray(img, np.uint8)
+        out = np.empty_like(a)
+        self._chk(load().vslam_rotate_mat_ccw(self.h, a.ctypes.data, a.shape[0], a.shape[1], a.shape[1], int(center[0]), int(center[1]),
+                                              float(cos_sin[0]), float(cos_sin[1]), out.ctypes.data, a.shape[1]))
+        return out
+
+    def rotated_window(self, img, center, window, cos_sin):
+        """Rotation::getRotatedWindow(I, center=(x, y), windowSize, theta) with (cos, sin) of theta."""
+        a = np.ascontiguousarray(img, np.uint8)
+        out = np.empty((window, window), np.uint8)
+        self._chk(load().vslam_rotated_window(self.h, a.ctypes.data, a.shape[0], a.shape[1], a.shape[1], int(center[0]), int(center[1]),
+                                              int(window), float(cos_sin[0]), float(cos_sin[1]), out.ctypes.data, window))
+        return out
 
     def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None, corners_out=None):
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)

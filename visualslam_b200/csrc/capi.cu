@@ -840,6 +840,32 @@ int vslam_bgr_to_gray(vslam_ctx *ctx, const uint8_t *bgr, int n_frames, int rows
     return vslam_sync(ctx);
 }
 
+static int rotate_common(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, int cx, int cy, float c, float s, int x0,
+                         int y0, int ow, int oh, uint8_t *dst, size_t dst_pitch, int mode) {
+    VS_TRY(stage_check(ctx, src, dst, rows, cols));
+    if (pitch < (size_t)cols || dst_pitch < (size_t)ow || ow <= 0 || oh <= 0 || oh > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "rotate: bad pitch or window");
+    const size_t b[2] = {(size_t)rows * cols, (size_t)ow * oh};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    VS_CUDA(ctx, cudaMemcpy2DAsync(d[0], cols, src, pitch, cols, rows, cudaMemcpyHostToDevice, ctx->stream));
+    VS_TRY(launch_rotate_gather(ctx, d[0], rows, cols, cols, cx, cy, c, s, x0, y0, ow, oh, d[1], ow, mode));
+    VS_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_pitch, d[1], ow, ow, oh, cudaMemcpyDeviceToHost, ctx->stream));
+    return vslam_sync(ctx);
+}
+
+int vslam_rotate_mat_ccw(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, int center_x, int center_y, float cos_a,
+                         float sin_a, uint8_t *dst, size_t dst_pitch) {
+    return rotate_common(ctx, src, rows, cols, pitch, center_x, center_y, cos_a, sin_a, 0, 0, cols, rows, dst, dst_pitch, 0);
+}
+
+int vslam_rotated_window(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, int center_x, int center_y, int window,
+                         float cos_a, float sin_a, uint8_t *dst, size_t dst_pitch) {
+    if (window <= 0) return VSLAM_E_INVALID;
+    const int pad = window / 2;
+    return rotate_common(ctx, src, rows, cols, pitch, center_x, center_y, cos_a, sin_a, center_x - pad, center_y - pad, window, window, dst,
+                         dst_pitch, 1);
+}
+
 int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst, size_t dst_pitch) {
     VS_TRY(stage_check(ctx, src, dst, rows, cols));
     if (pitch < (size_t)cols || dst_pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch smaller than cols");

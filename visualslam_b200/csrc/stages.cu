@@ -158,6 +158,27 @@ __global__ void bgr2gray_k(const u8 *__restrict__ src, int rows, int cols, size_
     }
 }
 
+// Rotation::rotate_pt_CW (rotation.cpp:19-28): float products of the int offsets, one float subtraction / addition,
+// truncation toward zero -- no FMA contraction (the reference is x86-64 code built without -mfma)
+__device__ __forceinline__ void rot_pt_cw(int x, int y, int cx, int cy, float c, float s, int &xr, int &yr) {
+    const float rx = (float)(x - cx), ry = (float)(y - cy);
+    xr = (int)__fsub_rn(__fmul_rn(rx, c), __fmul_rn(ry, s)) + cx;
+    yr = (int)__fadd_rn(__fmul_rn(rx, s), __fmul_rn(ry, c)) + cy;
+}
+// mode 0: Rotation::rotate_mat_CCW (rotation.cpp:66-84): output pixel (x, y) = I[rot] when 0 < rot.x < cols and
+//         0 < rot.y < rows (both strict, as written), else 0.
+// mode 1: Rotation::getRotatedWindow (rotation.cpp:87-108): output (i, j) = I[rot(x0 + j, y0 + i)]; the reference does
+//         not test the rotated point, reads outside the image give 0 here.
+__global__ void rotate_gather_k(const u8 *__restrict__ src, int rows, int cols, size_t pitch, int cx, int cy, float c, float s,
+                                int x0, int y0, int ow, int oh, u8 *__restrict__ dst, size_t dpitch, int mode) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= ow || i >= oh) return;
+    int xr, yr;
+    rot_pt_cw(x0 + j, y0 + i, cx, cy, c, s, xr, yr);
+    const bool in = mode == 0 ? (xr < cols && xr > 0 && yr < rows && yr > 0) : (xr < cols && xr >= 0 && yr < rows && yr >= 0);
+    dst[(size_t)i * dpitch + j] = in ? src[(size_t)yr * pitch + xr] : (u8)0;
+}
+
 #define GRID2D(cols, rows) dim3(((cols) + 127) / 128, (rows)), 128, 0, ctx->stream
 
 int launch_blur3(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, u8 *dst, size_t dpitch) {
@@ -172,6 +193,13 @@ int launch_bgr2gray(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pi
     const dim3 grid(((cols + 3) / 4 + 127) / 128, rows, n_frames);
     KernelSpan span(ctx, VSLAM_K_UPSAMPLE);
     bgr2gray_k<<<grid, 128, 0, ctx->stream>>>(src, rows, cols, pitch, stride, dst, dpitch, dstride, vec);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
+int launch_rotate_gather(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, int cx, int cy, float c, float s, int x0,
+                         int y0, int ow, int oh, u8 *dst, size_t dpitch, int mode) {
+    KernelSpan span(ctx, VSLAM_K_UPSAMPLE);
+    rotate_gather_k<<<GRID2D(ow, oh)>>>(src, rows, cols, pitch, cx, cy, c, s, x0, y0, ow, oh, dst, dpitch, mode);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

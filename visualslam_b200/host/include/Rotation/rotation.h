@@ -1,0 +1,38 @@
+// rotation.h -- SLAM::Rotation of the reference (KeyPointDetection/include/src/Rotation/rotation.h:11-26), same static
+// methods, on vslam::Mat.  The point helpers are host geometry exactly as written in rotation.cpp:5-62 (float products of
+// int offsets, truncation); the two image gathers run on the GPU through the C ABI (vslam_rotate_mat_ccw,
+// vslam_rotated_window).  Not mirrored: drawRotated / doubleCrop (rotation.cpp:132-202) -- cv::warpAffine and drawing
+// have no counterpart on this box; doubleCrop throws.
+#pragma once
+#include <vector>
+
+#include "../GaussPyramid.hpp"
+
+struct Point2i {
+    int x = 0, y = 0;
+    Point2i() = default;
+    Point2i(int x_, int y_) : x(x_), y(y_) {}
+};
+struct Point2f {
+    float x = 0, y = 0;
+    Point2f() = default;
+    Point2f(float x_, float y_) : x(x_), y(y_) {}
+};
+
+namespace SLAM {
+class Transform {};
+
+class Rotation : public Transform {
+  public:
+    static float convertToRadians(float theta);
+    static const Point2f cos_sin_of_angle(float theta, bool degrees = true);
+    static Point2i rotate_pt_CW(const Point2i &pt, const Point2i &center, const Point2f &angles);
+    static Point2i rotate_pt_CCW(const Point2i &pt, const Point2i &center, const Point2f &angles);
+    static Point2i rotate_pt_CCW(const Point2i &pt, const Point2i &center, float theta, bool degrees = true);
+    static Point2i rotate_pt_CW(const Point2i &pt, const Point2i &center, float theta, bool degrees = true);
+    static Mat rotate_mat_CCW(Mat &I, const Point2i &center, const Point2f &angles);
+    static Mat getRotatedWindow(Mat &I, const Point2i &center, int windowSize, float theta, bool degrees = true);
+    static std::vector<Point2i> getRotatedWindowPoints(Mat &I, const Point2i &center, int windowSize, float theta, bool degrees = true);
+    static Mat doubleCrop(Mat &src, const Point2i &center, int windowSize, double angle);   // throws: needs cv::warpAffine
+};
+}  // namespace SLAM

@@ -630,7 +630,10 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
     long long fb = (long long)(6e9 / (double)(bbytes + spf * 12));
     if (fb > (1LL << 30) / spf) fb = (1LL << 30) / spf;
     if (fb > 32768) fb = 32768;
-    fb = ingest_cap(ctx, fb);
+    // frames still being uploaded: launches double in size (16, 32, 64, ... frames at 1080p) -- every launch's frames have
+    // landed by the time the previous launch ends (the upload is ~2.5x faster than these kernels), the first kernels
+    // start after two upload chunks, and most frames run in large launches.  The lists are small: no need for many chunks.
+    const bool doubling = ctx->up_chunks > 1;
     if (fb > n_frames) fb = n_frames;
     if (fb < 1) fb = 1;
     if (ctx->ws_maps.reserve(bbytes * (size_t)fb)) VS_FAIL(ctx, VSLAM_E_NOMEM, "octave-base workspace (%zu bytes)", bbytes * (size_t)fb);
@@ -648,9 +651,9 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
         val_lut[c] = (u8)(int)w;
         if (v > dp.contrast_thr) cmin = c;
     }
-    VS_TRY(drain_begin(ctx, *drain, out, out_space, d_out, sizeof(vslam_keypoint), capacity, (n_frames + fb - 1) / fb + 1));
-    const int first = ingest_first(ctx, fb);
-    for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)fb) {
+    VS_TRY(drain_begin(ctx, *drain, out, out_space, d_out, sizeof(vslam_keypoint), capacity, (n_frames + fb - 1) / fb + 32));
+    const int first = doubling ? ingest_first(ctx, fb) : (int)fb;
+    for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)(doubling && 2LL * step < fb ? 2LL * step : fb)) {
         const int nf = n_frames - f0 < step ? n_frames - f0 : step;
         const size_t n_seg = (size_t)spf * nf;
         if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, n_seg * 4, ctx->stream));

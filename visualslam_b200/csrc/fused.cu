@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(NT) octave_fused_k(const __grid_constant__ Fus
     const FusedTaps &T = a.taps;
     u32 *hbuf = smem;
     u8 *stage = (u8 *)(smem + T.hbuf_words);
-    const int SP = T.stage_pitch, SPW = SP >> 2;   // SP is a multiple of 16
+    const int SP = T.stage_pitch;                  // a multiple of 16
     u8 *tiles = stage + T.stage_rows * SP;
     u32 *tiles32 = (u32 *)tiles;
     u8 *gt = tiles, *dt = tiles + F_NG * FW * FTR;

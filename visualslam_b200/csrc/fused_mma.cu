@@ -338,6 +338,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
     const int hw = warp % HCB, hlg = warp / HCB;                              // H pass: warp = (8 output columns, group of levels)
     const int hcb = cboff + 8 * hw;                                           // staged column of the warp's first output column
     const int c_lo = (hcb - geo.rmax()) >> 5;                                     // first 32-byte chunk any level's band touches
+    const bool h_short = hcb - 32 * c_lo + 7 + geo.rmax() < 32 * (NCH - 1);         // (warp-uniform) the widest band ends before the last chunk
     u32 saA[NCH], saB[NCH];                                                   // ldmatrix addresses of the chunks (XOR swizzle resolved)
 #pragma unroll
     for (int ci = 0; ci < NCH; ++ci) {
@@ -461,20 +462,21 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
         // zero padding of its tap copies: no band test, no branch), level l + 1's taps are loaded before level l's MMAs
         // and level l - 1's stores come after them (the compiler cannot hoist a shared load above a shared store it
         // cannot disambiguate).
-        if (!svc) {
-            u32 fa[NCH][4], fb[NCH][4];
+        auto h_pass = [&](auto nc_) {
+            constexpr int NC = decltype(nc_)::value;           // chunks this warp multiplies: NCH, or NCH - 1 when no band reaches the last
+            u32 fa[NC][4], fb[NC][4];
 #pragma unroll
-            for (int ci = 0; ci < NCH; ++ci) {
+            for (int ci = 0; ci < NC; ++ci) {
                 asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                              : "=r"(fa[ci][0]), "=r"(fa[ci][1]), "=r"(fa[ci][2]), "=r"(fa[ci][3]) : "r"(saA[ci]));
                 asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                              : "=r"(fb[ci][0]), "=r"(fb[ci][1]), "=r"(fb[ci][2]), "=r"(fb[ci][3]) : "r"(saB[ci]));
             }
-            u32 tb[2][NCH][2];
+            u32 tb[2][NC][2];
             int acc[2][2][4];
             auto load_taps = [&](int l, int buf) {
 #pragma unroll
-                for (int ci = 0; ci < NCH; ++ci) {
+                for (int ci = 0; ci < NC; ++ci) {
                     tb[buf][ci][0] = *(const u32 *)(hbase + geo.tab_hoff(l) + 32 * ci);
                     tb[buf][ci][1] = *(const u32 *)(hbase + geo.tab_hoff(l) + 32 * ci + 16);
                 }
@@ -502,7 +504,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
                 const int b = (l - L0) & 1;
                 if (l < L0 + LPW - 1) load_taps(l + 1, b ^ 1);
 #pragma unroll
-                for (int ci = 0; ci < NCH; ++ci) {
+                for (int ci = 0; ci < NC; ++ci) {
                     if (ci == 0) {
                         imma_c(acc[b][0], fa[ci][0], fa[ci][1], fa[ci][2], fa[ci][3], tb[b][ci][0], tb[b][ci][1], 0);
                         imma_c(acc[b][1], fb[ci][0], fb[ci][1], fb[ci][2], fb[ci][3], tb[b][ci][0], tb[b][ci][1], 0);
@@ -517,6 +519,10 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
             };
             if (LG == 1 || hlg == 0) h_levels(std::integral_constant<int, 0>());
             else h_levels(std::integral_constant<int, 6 - LPW>());
+        };
+        if (!svc) {
+            if (h_short) h_pass(std::integral_constant<int, NCH - 1>());
+            else h_pass(std::integral_constant<int, NCH>());
         }
         mbar_wait(mb_sa, mb_phase);                                           // every thread's detector results are visible
         mb_phase ^= 1;

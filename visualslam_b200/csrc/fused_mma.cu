@@ -66,14 +66,22 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps
         if (lv.r < rmin) rmin = lv.r;
         if (lv.r > rmax) rmax = lv.r;
     }
+    // rows between a step's first output row and its H chunk: rmax, or up to 3 more when that saves V-pass K steps
+    auto v_ksteps = [&](int v) {
+        int s = 0;
+        for (int l = 0; l < 6; ++l) s += (out->lv[l].n + 7 + (4 - (v + out->lv[l].r) % 4) % 4 + 31) / 32;
+        return s;
+    };
+    int rv = rmax;
+    for (int v = rmax + 1; v < rmax + 4; ++v) if (v_ksteps(v) < v_ksteps(rv)) rv = v;
     for (int l = 0; l < 6; ++l) {
         MmaLevel &lv = out->lv[l];
         const int n = lv.n;
-        // every level's H chunk of a step is the same 32 image rows y0 + rmax ..., so the A fragments are shared by the
-        // levels; a level's V window for output rows y0 + 8j ... starts rmax + r + sv rows above the chunk's row 8j
-        lv.sv = (4 - (rmax + lv.r) % 4) % 4;
+        // every level's H chunk of a step is the same 32 image rows y0 + rv ..., so the A fragments are shared by the
+        // levels; a level's V window for output rows y0 + 8j ... starts rv + r + sv rows above the chunk's row 8j
+        lv.sv = (4 - (rv + lv.r) % 4) % 4;
         lv.ksv = (n + 7 + lv.sv + 31) / 32;
-        lv.cq = (rmax + lv.r + lv.sv) / 4;
+        lv.cq = (rv + lv.r + lv.sv) / 4;
         lv.np = (lv.cq + 8 + 2) / 2;                                 // aligned quads Q = q + cq of a step: 8i .. 8i + 7 + cq
         if (lv.np < 8) lv.np = 8;                                    // single-step wrap of every slot computation (needs >= 6)
         lv.plane_off = poff;
@@ -105,9 +113,9 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps
     for (int l = 0; l < 6; ++l) {
         MmaLevel &lv = out->lv[l];
         lv.tab_hoff = 4 * cp * l + lv.padl + lv.r;
-        lv.tab_voff = 4 * cp * l + lv.padl - lv.sv - rmax % 4;
+        lv.tab_voff = 4 * cp * l + lv.padl - lv.sv - rv % 4;
     }
-    out->rmin = rmin; out->rmax = rmax;
+    out->rmin = rmin; out->rmax = rmax; out->rv = rv;
     out->stage_rows = FR;
     out->stage_pitch = (2 * rmax + 15 + fw + 127) / 128 * 128;       // left halo rmax (+ up to 15 alignment), 64 columns, right halo
     {   // row = (q * magic) >> 16 for q < stage_rows * (pitch / 16): checked exhaustively
@@ -214,14 +222,14 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
     const int ys = seg * a.seg_rows;
     const int ye = min(ys + a.seg_rows, rows);
     const int yv = seg > 0 ? ys - FR : 0;        // first step with a V pass (one extra step feeds the detector's history)
-    const int K = (2 * geo.rmax() + FR - 1) / FR;    // warm-up steps: H pass only
+    const int K = (geo.rmax() + geo.rv() + FR - 1) / FR;    // warm-up steps: H pass only
 
-    // ---- stage base rows y0 + rmax ..., columns xs16 ..., reflect-101 resolved (16-byte cp.async inside the image) ----
+    // ---- stage base rows y0 + rv ..., columns xs16 ..., reflect-101 resolved (16-byte cp.async inside the image) ----
     const int SPQ = SP >> 4, n_stage = FR * SPQ;
     auto issue_stage = [&](int y0n) {
         for (int q = svc ? n_stage : tid; q < n_stage; q += NT) {
             const int row = (int)(((u32)q * (u32)geo.spq_magic()) >> 16), j = q - row * SPQ;
-            const int y = refl101(y0n + geo.rmax() + row, rows);
+            const int y = refl101(y0n + geo.rv() + row, rows);
             const u8 *__restrict__ src = base + (size_t)y * a.base_pitch;
             u32 *dst = (u32 *)(stage + row * SP) + 4 * (j ^ ((row >> 2) & 7));   // 16-byte groups XOR-swizzled by the row quad
             const int x = xs16 + 16 * j;
@@ -349,7 +357,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
     // B fragments: b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 ..; H pass idx0 = r + 32 c - hcb + 4 t - g,
     // V pass (K rows remapped so that a thread's 8 rows are consecutive) b1 = taps idx0 + 4 .., idx0 = 32 k + 8 t - g - sv.
     // One lane pointer per pass (byte-shifted copy + word offset); the level is an offset (fused_mma.cuh)
-    const int hu = 4 * t - g - hcb + 32 * c_lo, vu = 8 * t - g + geo.rmax() % 4;
+    const int hu = 4 * t - g - hcb + 32 * c_lo, vu = 8 * t - g + geo.rv() % 4;
     const u8 *hbase = tab + (hu & 3) * geo.cp() + (hu - (hu & 3));             // two's complement: fine for hu < 0
     const u8 *vbase = tab + (vu & 3) * geo.cp() + (vu - (vu & 3));
     const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the H chunk this thread's D rows belong to
@@ -456,7 +464,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
         __syncthreads();                                                      // Bx: staged rows landed; V pass / emission of c-1 done
         si_lo = detect_step(p_y0, p_own, par);
         if (!svc) mbar_arrive(mb_sa);                                         // the service warp goes straight to the wait
-        // ---- 2. H pass: image rows y0 + rmax .. + 31 for all six levels -> 8 quads of every level's ring ----
+        // ---- 2. H pass: image rows y0 + rv .. + 31 for all six levels -> 8 quads of every level's ring ----
         // the image fragments of the warp's chunks are loaded once and serve every level whose band touches them.
         // One basic block, software pipelined by hand: every chunk is multiplied (chunks outside a level's band meet the
         // zero padding of its tap copies: no band test, no branch), level l + 1's taps are loaded before level l's MMAs

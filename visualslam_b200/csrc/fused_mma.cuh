@@ -26,6 +26,8 @@ struct MmaTaps {
     MmaLevel lv[6];
     u8 taps[6][248];
     int rmin, rmax;
+    int rv;                         // rows between a step's first output row and its H chunk: rmax + 0..3, the offset that
+                                    // quad-aligns the V windows with the fewest K steps
     int stage_rows, stage_pitch;    // staged base tile: 32 rows (y0 + rmax ...), pitch a multiple of 128 bytes (XOR swizzle)
     int spq_magic;                  // ceil(2^16 / (stage_pitch / 16)): flattened index -> row without a division
     int plane_words;                // all six planes
@@ -57,9 +59,20 @@ struct MmaStaticGeom {
         for (int l = 0; l < 6; ++l) m = r(l) > m ? r(l) : m;
         return m;
     }
-    __host__ __device__ static constexpr int sv(int l) { return (4 - (rmax() + r(l)) % 4) % 4; }
+    __host__ __device__ static constexpr int sv_at(int l, int v) { return (4 - (v + r(l)) % 4) % 4; }
+    __host__ __device__ static constexpr int ksteps_at(int v) {
+        int s = 0;
+        for (int l = 0; l < 6; ++l) s += (n(l) + 7 + sv_at(l, v) + 31) / 32;
+        return s;
+    }
+    __host__ __device__ static constexpr int rv() {
+        int best = rmax();
+        for (int v = rmax() + 1; v < rmax() + 4; ++v) best = ksteps_at(v) < ksteps_at(best) ? v : best;
+        return best;
+    }
+    __host__ __device__ static constexpr int sv(int l) { return sv_at(l, rv()); }
     __host__ __device__ static constexpr int ksv(int l) { return (n(l) + 7 + sv(l) + 31) / 32; }
-    __host__ __device__ static constexpr int cq(int l) { return (rmax() + r(l) + sv(l)) / 4; }
+    __host__ __device__ static constexpr int cq(int l) { return (rv() + r(l) + sv(l)) / 4; }
     __host__ __device__ static constexpr int np(int l) { return (cq(l) + 10) / 2 < 8 ? 8 : (cq(l) + 10) / 2; }
     __host__ __device__ static constexpr int plane_off(int l) {
         int s = 0;
@@ -85,7 +98,7 @@ struct MmaStaticGeom {
         return m;
     }
     __host__ __device__ static constexpr int tab_hoff(int l) { return 4 * cp() * l + padl(l) + r(l); }
-    __host__ __device__ static constexpr int tab_voff(int l) { return 4 * cp() * l + padl(l) - sv(l) - rmax() % 4; }
+    __host__ __device__ static constexpr int tab_voff(int l) { return 4 * cp() * l + padl(l) - sv(l) - rv() % 4; }
     __host__ __device__ static constexpr int plane_words() { return plane_off(6); }
     // the V pass as a flat list of (level, K step) items
     __host__ __device__ static constexpr int items() { return ksv(0) + ksv(1) + ksv(2) + ksv(3) + ksv(4) + ksv(5); }
@@ -102,7 +115,7 @@ struct MmaStaticGeom {
     __host__ __device__ static constexpr int stage_pitch() { return (2 * rmax() + 15 + FW_ + 127) / 128 * 128; }
     __host__ __device__ static constexpr int spq_magic() { return ((1 << 16) + (stage_pitch() >> 4) - 1) / (stage_pitch() >> 4); }
     static bool matches(const MmaTaps &t) {
-        bool ok = t.fw == FW_ && t.rmax == rmax() && t.stage_pitch == stage_pitch() && t.spq_magic == spq_magic() && t.plane_words == plane_words() &&
+        bool ok = t.fw == FW_ && t.rmax == rmax() && t.rv == rv() && t.stage_pitch == stage_pitch() && t.spq_magic == spq_magic() && t.plane_words == plane_words() &&
                   t.nch == nch() && t.cp == cp();
         for (int l = 0; l < 6; ++l)
             ok = ok && t.lv[l].n == n(l) && t.lv[l].r == r(l) && t.lv[l].sv == sv(l) && t.lv[l].ksv == ksv(l) && t.lv[l].cq == cq(l) &&
@@ -120,6 +133,7 @@ struct MmaDynGeom {
     __device__ int n(int l) const { return T.lv[l].n; }
     __device__ int r(int l) const { return T.lv[l].r; }
     __device__ int rmax() const { return T.rmax; }
+    __device__ int rv() const { return T.rv; }
     __device__ int sv(int l) const { return T.lv[l].sv; }
     __device__ int ksv(int l) const { return T.lv[l].ksv; }
     __device__ int cq(int l) const { return T.lv[l].cq; }

@@ -111,7 +111,7 @@ VSLAM_API long long vslam_launch_count(const vslam_ctx *ctx);
  * stream and returns the summed duration and launch count of one kernel class. */
 typedef enum vslam_kernel_id {
     VSLAM_K_UPSAMPLE = 0, VSLAM_K_PAD = 1 /* reflect-101 margins of the octave bases */, VSLAM_K_VBLUR = 2, VSLAM_K_DETECT = 3, VSLAM_K_COMPACT = 4,
-    VSLAM_K_HARRIS = 5, VSLAM_K_GRAD = 6, VSLAM_K_FUSED = 7, VSLAM_KERNEL_COUNT = 8
+    VSLAM_K_HARRIS = 5, VSLAM_K_GRAD = 6, VSLAM_K_FUSED = 7, VSLAM_K_DESCRIPTOR = 8 /* orientation + SIFT */, VSLAM_KERNEL_COUNT = 9
 } vslam_kernel_id;
 VSLAM_API int vslam_profile(vslam_ctx *ctx, int enable);
 VSLAM_API int vslam_profile_read(vslam_ctx *ctx, int kernel_id, double *total_ms, long long *launches);
@@ -227,6 +227,28 @@ VSLAM_API int vslam_localize(vslam_ctx *ctx, const int32_t *candidates, int n, f
  * responses[i] = tr^2 / det (or NULL); sums[3i..3i+2] = Ix2, Iy2, IxIy = StructureMatrix (Harris_corners.cpp:10-29) (or NULL) */
 VSLAM_API int vslam_edge_from_windows(vslam_ctx *ctx, const float *gx, const float *gy, int n, int window_len,
                                       float *responses, float *sums);
+
+/* ---- the stage after the hot path in ./DoG ------------------------------------------
+ * fp32 Gaussian kernel of cv::GaussianBlur on a CV_32F image: size cvRound(sigma*4*2+1)|1, taps = the normalised double
+ * Gaussian rounded to float (getGaussianKernel(n, sigma, CV_32F)). */
+VSLAM_API int vslam_gauss_ksize_f32(double sigma);
+VSLAM_API int vslam_gauss_taps_f32(double sigma, int ksize, float *taps);
+/* filterKeypoints' orientation stage (Diff_of_Gauss.cpp:340-369, orientationHistogram :112-133) for n keypoints of ONE
+ * octave of one frame that passed the edge test: 16x16 window of the level's magnitude map blurred with sigma =
+ * 1.5 * getSigmaAt(octave, level), 36-bin histogram, one output point {row, col, angle = bin * 10, 0, octave, level}
+ * per bin above 0.8 of the peak, in the reference's order.  *count = number found (may exceed capacity; only the first
+ * `capacity` are stored).  histograms: optional n x 36 floats. */
+VSLAM_API int vslam_assign_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave,
+                                        const vslam_keypoint *keypoints, int n, vslam_keypoint *out, int capacity,
+                                        int *count, float *histograms);
+/* SIFT (Diff_of_Gauss.cpp:561-693, rotateImageSection :528-559) for n oriented keypoints of one octave: descriptors =
+ * n x 128 floats.  valid[i] = 0 where the reference's swapped (x, y) indexing leaves the padded map (it then reads
+ * memory outside the image: undefined there; here such samples come from the nearest end of the map). */
+VSLAM_API int vslam_sift_descriptors(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave,
+                                     const vslam_keypoint *oriented, int n, float *descriptors, uint8_t *valid);
+/* featureDescriptors.dat as ./DoG writes it (Diff_of_Gauss.cpp:837-863): int32 count, int32 128, int32
+ * sizeof(std::vector<float>) (24 on LP64), then count x 128 float32.  Host only. */
+VSLAM_API int vslam_write_descriptor_file(const char *path, const float *descriptors, int n);
 
 #ifdef __cplusplus
 }

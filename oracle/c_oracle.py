@@ -73,6 +73,12 @@ def lib():
         L.vo_harris_nms3.restype = None
         L.vo_harris_nms2.argtypes = [f32p, C.c_int, C.c_int, C.c_int, i32p, f32p, C.c_long, f32p]
         L.vo_harris_nms2.restype = C.c_long
+        L.vo_gauss_ksize_32f.argtypes = [C.c_double]
+        L.vo_gauss_taps_32f.argtypes = [C.c_double, C.c_int, f32p]
+        L.vo_orientation_histogram.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, f32p]
+        L.vo_assign_orientations.argtypes = [C.POINTER(u8p), C.c_int, C.c_int, C.POINTER(C.c_double), i32p, C.c_long, i32p, C.c_long]
+        L.vo_assign_orientations.restype = C.c_long
+        L.vo_sift.argtypes = [C.POINTER(u8p), C.c_int, C.c_int, C.POINTER(C.c_double), i32p, C.c_long, f32p, u8p]
         _lib = L
     return _lib
 
@@ -218,3 +224,53 @@ def harris(img: np.ndarray, k: float = 0.04, nms_window: int = 5) -> dict:
     n = L.vo_harris_nms2(_f32(resp), h, w, nms_window, corners.ctypes.data_as(i32p), _f32(vals), cap, C.byref(tmax))
     return {"blurred": blurred, "response": resp, "r8": r8, "mask3": mask, "corners": corners[:n].copy(),
             "corner_values": vals[:n].copy(), "true_max": float(tmax.value)}
+
+
+# ---- "next" rows: orientation assignment and SIFT descriptors (Diff_of_Gauss.cpp:340-369, 561-693) ----------------
+def gauss_taps_32f(sigma: float, n: int | None = None) -> np.ndarray:
+    n = lib().vo_gauss_ksize_32f(sigma) if n is None else n
+    t = np.empty(n, np.float32)
+    assert lib().vo_gauss_taps_32f(sigma, n, _f32(t)) == 0
+    return t
+
+
+def orientation_histogram(g: np.ndarray, y: int, x: int, sigma: float) -> np.ndarray:
+    h = np.empty(36, np.float32)
+    assert lib().vo_orientation_histogram(_u8(g), g.shape[0], g.shape[1], y, x, sigma, _f32(h)) == 0
+    return h
+
+
+def assign_orientations(gauss, sigmas, kps: np.ndarray) -> np.ndarray:
+    """filterKeypoints' second half over one octave's keypoints (n x 6 int32) -> oriented keypoints (m x 6)."""
+    kps = np.ascontiguousarray(kps, np.int32).reshape(-1, 6)
+    rows, cols = gauss[0].shape
+    out = np.zeros((36 * max(len(kps), 1), 6), np.int32)
+    sg = (C.c_double * 6)(*[float(v) for v in sigmas])
+    m = lib().vo_assign_orientations(_ptr_array(gauss), rows, cols, sg, kps.ctypes.data_as(i32p), len(kps),
+                                     out.ctypes.data_as(i32p), len(out))
+    assert m >= 0
+    return out[:m].copy()
+
+
+def sift(gauss, sigmas, oriented: np.ndarray):
+    """SIFT() over one octave's oriented keypoints -> (m x 128 float32 descriptors, m uint8 valid flags)."""
+    oriented = np.ascontiguousarray(oriented, np.int32).reshape(-1, 6)
+    rows, cols = gauss[0].shape
+    desc = np.zeros((len(oriented), 128), np.float32)
+    valid = np.zeros(len(oriented), np.uint8)
+    sg = (C.c_double * 6)(*[float(v) for v in sigmas])
+    rc = lib().vo_sift(_ptr_array(gauss), rows, cols, sg, oriented.ctypes.data_as(i32p), len(oriented), _f32(desc), _u8(valid))
+    assert rc == 0, rc
+    return desc, valid
+
+
+def dog_features(img: np.ndarray, num_octaves: int = 4, sigma0: float = 1.6, window: int = 3):
+    """./DoG's per-octave loop (Diff_of_Gauss.cpp:781-790): keypoints -> oriented keypoints -> descriptors."""
+    pyr = build_pyramid(img, num_octaves, sigma0)
+    ori, des, val = [], [], []
+    for o in range(num_octaves):
+        k, _ = detect_octave(pyr["dog"][o], pyr["gauss"][o], o, window)
+        r = assign_orientations(pyr["gauss"][o], pyr["sigma"][o], k)
+        d, v = sift(pyr["gauss"][o], pyr["sigma"][o], r)
+        ori.append(r); des.append(d); val.append(v)
+    return np.concatenate(ori, 0), np.concatenate(des, 0), np.concatenate(val, 0), pyr

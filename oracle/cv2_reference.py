@@ -337,3 +337,68 @@ def gaussian_taps_by_impulse(sigma: float, n: int | None = None) -> np.ndarray:
         m = np.nonzero(lut == y)[0]
         out[i] = m[0] if len(m) == 1 else -1
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# "next" rows: orientation assignment (Diff_of_Gauss.cpp:340-369) and SIFT (:561-693) through cv2
+# ----------------------------------------------------------------------------------------------
+def orientation_histograms(mag: np.ndarray, orient: np.ndarray, kps, sigma: float) -> np.ndarray:
+    """36-bin histograms of the keypoints (rows of (row, col, ...)) of ONE level.  A cv::Mat ROI keeps its parent, so
+    GaussianBlur(windowMag, ...) (:348) filters with the padded map's pixels around the window; cv2 cannot express a
+    parented ROI, but filtering the whole padded map and cropping is the same arithmetic per output pixel."""
+    cv = require_cv2()
+    pm = pad_octave(8, [mag])[0]
+    po = pad_octave(8, [orient])[0]
+    blurred = cv.GaussianBlur(pm, (0, 0), sigma, sigmaY=0, borderType=cv.BORDER_DEFAULT)
+    coeff = np.float32(36) / np.float32(360.0)
+    out = np.zeros((len(kps), 36), np.float32)
+    for n, k in enumerate(kps):
+        y, x = int(k[0]), int(k[1])
+        w = blurred[y:y + 16, x:x + 16]
+        idx = (po[y:y + 16, x:x + 16] * coeff).astype(np.int32)
+        for i in range(16):
+            for j in range(16):
+                out[n, idx[i, j]] += w[i, j]
+    return out
+
+
+def sift_descriptor(mag: np.ndarray, orient: np.ndarray, y: int, x: int, angle: int, sigma: float):
+    """SIFT() for one oriented keypoint of a level; returns (descriptor[128], in_bounds)."""
+    cv = require_cv2()
+    f = np.float32
+    pm = pad_octave(20, [mag])[0]
+    po = pad_octave(20, [orient])[0]
+    cx, cy = x + 20, y + 20
+    ang = f(np.float64(f(angle)) * (np.pi / np.float64(f(180.0))))
+    c, s = f(np.cos(np.float64(ang))), f(np.sin(np.float64(ang)))
+    pts = []
+    for i in range(cy - 8, cy + 9):                     # rotation.cpp:122-127 ('<=': 17 x 17 points)
+        for j in range(cx - 8, cx + 9):
+            rx, ry = f(j - cx), f(i - cy)
+            pts.append((int(f(rx * c) - f(ry * s)) + cx, int(f(rx * s) + f(ry * c)) + cy))
+    m = np.zeros((16, 16), np.float32)
+    o = np.zeros((16, 16), np.float32)
+    ok = True
+    fm, fo = pm.reshape(-1), po.reshape(-1)
+    for i in range(16):
+        for j in range(16):
+            px, py = pts[i * 16 + j]                    # :545
+            lin = px * pm.shape[1] + py                 # :549-554 at<>(x, y)
+            if not (0 <= lin < fm.size):
+                ok = False
+                lin = min(max(lin, 0), fm.size - 1)
+            m[i, j] = fm[lin]; o[i, j] = fo[lin]
+    w = cv.GaussianBlur(m, (0, 0), sigma, sigmaY=0, borderType=cv.BORDER_DEFAULT)    # :611
+    coeff = np.float32(8) / np.float32(360.0)
+    d = np.zeros(128, np.float32)
+    idx = (o * coeff).astype(np.int32)
+    for cell in range(16):
+        r0, c0 = 4 * (cell // 4), 4 * (cell % 4)
+        for i in range(r0, r0 + 4):
+            for j in range(c0, c0 + 4):
+                d[8 * cell + idx[i, j]] += w[i, j]
+    with np.errstate(all="ignore"):
+        d = d / d.max()
+        d = np.where(f(0.2) < d, f(0.2), d)
+        d = d / d.max()
+    return d.astype(np.float32), ok

@@ -299,3 +299,99 @@ def test_shared_chunked_upload_gives_the_same_lists(ctx):
     assert h1["counts"] == h0["counts"] and np.array_equal(h1["corners"], h0["corners"])
     # frames are periodic with period 8: so are the per-frame counts
     assert d0["counts"][:8] == d0["counts"][8:16] and h0["counts"][:8] == h0["counts"][152:160]
+
+
+# ---- the stage after the hot path: orientation assignment + SIFT descriptors (descriptor.cu) -----------------------------
+FP32_TOL = 1e-4          # BASELINE.json north_star tolerance; against the C oracle the kernels are bit-exact
+
+
+def same_floats(a, b):
+    """Bit-identical apart from the payload of NaNs (0 / 0 yields a different quiet NaN on the two machines)."""
+    na, nb = np.isnan(a), np.isnan(b)
+    return np.array_equal(na, nb) and np.array_equal(a[~na].view(np.uint32), b[~nb].view(np.uint32))
+
+
+def _features_gpu(ctx, img, kp6, num_octaves=4):
+    """./DoG's per-octave loop (Diff_of_Gauss.cpp:781-790) after the hot path, through the C ABI."""
+    pyr = ctx.build_pyramid(img, num_octaves, 1.6)
+    hist, ori, desc, valid = [], [], [], []
+    for o in range(num_octaves):
+        k = np.ascontiguousarray(kp6[kp6[:, 4] == o], np.int32)
+        r, h = ctx.assign_orientations(pyr, o, k, histograms=True)
+        d, v = ctx.sift_descriptors(pyr, o, r)
+        hist.append(h); ori.append(kp_array(r).reshape(-1, 6)); desc.append(d); valid.append(v)
+    pyr.close()
+    return np.concatenate(hist, 0), np.concatenate(ori, 0), np.concatenate(desc, 0), np.concatenate(valid, 0)
+
+
+@pytest.mark.parametrize("stem", ["home", "building"])
+def test_orientations_and_descriptors_golden(ctx, stem, images, golden_lists):
+    import os
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "descriptors.npz")) as z:
+        gd = {k: z[k] for k in z.files}
+    img = image_for(images, stem, "cvt")
+    kp = golden_lists[f"dog_{stem}"]
+    hist, ori, desc, valid = _features_gpu(ctx, img, kp)
+    # bit-exact against the C oracle
+    opyr = O.build_pyramid(img)
+    want_h = np.stack([O.orientation_histogram(opyr["gauss"][k[4]][k[5]], int(k[0]), int(k[1]), 1.5 * opyr["sigma"][k[4]][k[5]])
+                       for k in kp], 0)
+    assert np.array_equal(hist.view(np.uint32), want_h.view(np.uint32))
+    want_ori = np.concatenate([O.assign_orientations(opyr["gauss"][o], opyr["sigma"][o], kp[kp[:, 4] == o]) for o in range(4)], 0)
+    assert np.array_equal(ori, want_ori)
+    wd, wv = zip(*[O.sift(opyr["gauss"][o], opyr["sigma"][o], want_ori[want_ori[:, 4] == o]) for o in range(4)])
+    wd, wv = np.concatenate(wd, 0), np.concatenate(wv, 0)
+    assert np.array_equal(valid, wv)
+    assert same_floats(desc, wd)       # incl. the flagged ones: same stand-in samples
+    # within the fp32 tolerance of the cv2 fixtures (the reference's own OpenCV calls)
+    assert np.abs(hist - gd[f"{stem}_hist"]).max() / gd[f"{stem}_hist"].max() <= FP32_TOL
+    assert np.array_equal(ori, gd[f"{stem}_oriented"])
+    assert np.array_equal(valid, gd[f"{stem}_valid"])
+    ok = valid.astype(bool)
+    assert np.nanmax(np.abs(desc[ok] - gd[f"{stem}_desc"][ok])) <= FP32_TOL
+
+
+def test_descriptors_synthetic_all_octaves_vs_oracle(ctx):
+    """A synthetic frame large enough to have keypoints in the coarse octaves (blur radii up to 154 at octave 3 level 3)."""
+    img = synth.frame(3, 540, 720)
+    ori_o, desc_o, valid_o, _ = O.dog_features(img)
+    kc, _, _ = O.dog_keypoints(img)
+    assert len(kc[kc[:, 4] >= 2]) > 0
+    hist, ori, desc, valid = _features_gpu(ctx, img, kc)
+    assert np.array_equal(ori, ori_o)
+    assert np.array_equal(valid, valid_o)
+    assert same_floats(desc, desc_o)
+
+
+def test_descriptor_edge_cases(ctx, tmp_path):
+    img = synth.frame(1, 96, 128)
+    pyr = ctx.build_pyramid(img, 3, 1.6)
+    opyr = O.build_pyramid(img, 3, 1.6)
+    # empty lists
+    assert len(ctx.assign_orientations(pyr, 0, np.zeros((0, 6), np.int32))) == 0
+    d, v = ctx.sift_descriptors(pyr, 0, np.zeros((0, 6), np.int32))
+    assert d.shape == (0, 128) and v.shape == (0,)
+    # keypoints in the corners / on the borders, every level (incl. the widest kernel of the octave, wider than the map)
+    rows, cols = pyr.octave_size(2)
+    pts = [(0, 0), (0, cols - 1), (rows - 1, 0), (rows - 1, cols - 1), (rows // 2, cols // 2), (1, cols - 2)]
+    kp = np.array([[y, x, 5, 1, 2, l] for l in range(6) for (y, x) in pts], np.int32)
+    r, h = ctx.assign_orientations(pyr, 2, kp, histograms=True)
+    want = O.assign_orientations(opyr["gauss"][2], opyr["sigma"][2], kp)
+    assert np.array_equal(kp_array(r).reshape(-1, 6), want)
+    d, v = ctx.sift_descriptors(pyr, 2, want)
+    wd, wv = O.sift(opyr["gauss"][2], opyr["sigma"][2], want)
+    assert np.array_equal(v, wv) and same_floats(d, wd)
+    # a point outside the map is refused quietly: no orientation, NaN descriptor flagged invalid
+    bad = np.array([[rows, 0, 0, 0, 2, 1]], np.int32)
+    assert len(ctx.assign_orientations(pyr, 2, bad)) == 0
+    d, v = ctx.sift_descriptors(pyr, 2, bad)
+    assert np.isnan(d).all() and v[0] == 0
+    with pytest.raises(vs.VslamError):
+        ctx.assign_orientations(pyr, 7, kp)
+    # featureDescriptors.dat (Diff_of_Gauss.cpp:837-863)
+    path = tmp_path / "featureDescriptors.dat"
+    vs.api.write_descriptor_file(str(path), wd)
+    raw = path.read_bytes()
+    assert np.frombuffer(raw[:12], "<i4").tolist() == [len(wd), 128, 24]
+    assert np.array_equal(np.frombuffer(raw[12:], "<f4").reshape(-1, 128).view(np.uint32), wd.view(np.uint32))
+    pyr.close()

@@ -1,6 +1,7 @@
 """CPU tests: the plain-C oracle (oracle/vslam_oracle.c) against the fixtures generated from the reference's own
 OpenCV calls (tools/make_golden.py -> tests/golden/), and against cv2 live where it is importable."""
 import hashlib
+import os
 
 import numpy as np
 import pytest
@@ -156,3 +157,70 @@ def test_localize_numpy_vs_literal_cv2():
         vec = np.float32(R.localize_numpy(dx, dy, ds, val))
         c = np.float32(L.vo_localize(dx, dy, ds, val))
         assert (lit == vec == c) or (np.isnan(lit) and np.isnan(vec) and np.isnan(c)), (dx, dy, ds, val)
+
+
+# ---- the stage after the hot path: orientation assignment and SIFT descriptors (tests/golden/descriptors.npz, generated
+# ---- by tools/make_golden_descriptors.py through cv2) -------------------------------------------------------------------
+FP32_TOL = 1e-4          # BASELINE.json north_star: max abs err <= 1e-4 on [0, 1]-normalised values
+
+
+@pytest.fixture(scope="module")
+def golden_desc():
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "descriptors.npz")) as z:
+        return {k: z[k] for k in z.files}
+
+
+def test_fp32_gauss_taps_match_cv2():
+    cv2 = pytest.importorskip("cv2")
+    for o in range(4):
+        for l in range(6):
+            s = 1.5 * O.lib().vo_calculate_sigma(o, l, 1.6, 3)
+            n = O.lib().vo_gauss_ksize_32f(s)
+            assert np.array_equal(O.gauss_taps_32f(s), cv2.getGaussianKernel(n, s, cv2.CV_32F).ravel()), (o, l)
+    assert O.lib().vo_gauss_ksize_32f(1.5 * 1.6 * 8 * 2 ** (5 / 3)) == 489
+
+
+@pytest.mark.parametrize("stem", ["home", "building"])
+def test_oracle_orientations_and_descriptors_match_cv2_golden(stem, images, golden_lists, golden_desc):
+    img = image_for(images, stem, "cvt")
+    kp = golden_lists[f"dog_{stem}"]
+    pyr = O.build_pyramid(img)
+    hist = np.stack([O.orientation_histogram(pyr["gauss"][k[4]][k[5]], int(k[0]), int(k[1]), 1.5 * pyr["sigma"][k[4]][k[5]])
+                     for k in kp], 0)
+    want = golden_desc[f"{stem}_hist"]
+    peak = want.max(1, keepdims=True)
+    assert np.abs(hist - want).max() <= FP32_TOL * max(1.0, float(peak.max()))
+    assert (np.abs(hist - want) / peak).max() <= FP32_TOL          # peak-normalised, like the 0.8 * peak decision
+    ori = np.concatenate([O.assign_orientations(pyr["gauss"][o], pyr["sigma"][o], kp[kp[:, 4] == o]) for o in range(4)], 0)
+    assert np.array_equal(ori, golden_desc[f"{stem}_oriented"])    # no bin of these images sits within tolerance of 0.8 * peak
+    desc, valid = [], []
+    for o in range(4):
+        d, v = O.sift(pyr["gauss"][o], pyr["sigma"][o], ori[ori[:, 4] == o])
+        desc.append(d); valid.append(v)
+    desc, valid = np.concatenate(desc, 0), np.concatenate(valid, 0)
+    assert np.array_equal(valid, golden_desc[f"{stem}_valid"])
+    ok = valid.astype(bool)
+    assert ok.sum() > 50
+    a, b = desc[ok], golden_desc[f"{stem}_desc"][ok]
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    assert np.nanmax(np.abs(a - b)) <= FP32_TOL
+    assert np.nanmax(a) == 1.0 and np.nanmin(a) >= 0.0
+
+
+def test_oracle_descriptor_known_answers():
+    """A flat image has zero gradients: every histogram is empty, no orientation is assigned, and SIFT divides 0 by 0."""
+    g = [np.full((64, 80), 77, np.uint8)] * 6
+    sig = [1.6 * 2 ** (l / 3) for l in range(6)]
+    kp = np.array([[30, 40, 9, 1, 0, 2]], np.int32)
+    assert np.array_equal(O.orientation_histogram(g[2], 30, 40, 1.5 * sig[2]), np.zeros(36, np.float32))
+    assert len(O.assign_orientations(g, sig, kp)) == 0
+    d, v = O.sift(g, sig, np.array([[30, 40, 90, 0, 0, 2]], np.int32))
+    assert np.isnan(d).all() and v[0] == 1
+    # a horizontal ramp has gx = 2, gy = 0 away from the border: orientation 0 degrees, everything lands in bin 0
+    ramp = np.tile((np.arange(80) * 2).astype(np.uint8), (64, 1))
+    h = O.orientation_histogram(ramp, 30, 40, 1.5 * sig[1])
+    assert h[0] > 0 and not h[1:].any()
+    ori = O.assign_orientations([ramp] * 6, sig, np.array([[30, 40, 9, 1, 0, 1]], np.int32))
+    assert ori.tolist() == [[30, 40, 0, 0, 0, 1]]
+    d, v = O.sift([ramp] * 6, sig, ori)
+    assert v[0] == 1 and set(np.nonzero(d[0])[0]) == set(range(0, 128, 8)) and d[0].max() == 1.0

@@ -58,6 +58,9 @@ EXPORTS = [
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
     "vslam_bgr_to_gray", "vslam_rotate_mat_ccw", "vslam_rotated_window", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
     "vslam_dog_detect_octave", "vslam_edge_responses", "vslam_localize", "vslam_edge_from_windows",
+    # the stage after the hot path: orientation assignment, SIFT descriptors, featureDescriptors.dat
+    "vslam_gauss_ksize_f32", "vslam_gauss_taps_f32", "vslam_assign_orientations", "vslam_sift_descriptors",
+    "vslam_write_descriptor_file",
 ]
 
 _lib = None
@@ -101,12 +104,35 @@ def load():
                                       vp, i, i, C.POINTER(i)]
     L.vslam_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(HarrisParams), vp, vp, vp, vp, i, i, C.POINTER(i)]
     L.vslam_upload_frames.argtypes = [vp, vp, i, i, i, sz, sz, C.POINTER(vp), C.POINTER(sz), C.POINTER(sz)]
+    L.vslam_gauss_ksize_f32.argtypes = [C.c_double]
+    L.vslam_gauss_taps_f32.argtypes = [C.c_double, i, C.POINTER(C.c_float)]
+    L.vslam_assign_orientations.argtypes = [vp, vp, i, i, vp, i, vp, i, C.POINTER(i), vp]
+    L.vslam_sift_descriptors.argtypes = [vp, vp, i, i, vp, i, vp, vp]
+    L.vslam_write_descriptor_file.argtypes = [C.c_char_p, vp, i]
     _lib = L
     return L
 
 
 def calculate_sigma(octave, level, sigma0=1.6, scale_samples=3):
     return load().vslam_calculate_sigma(octave, level, sigma0, scale_samples)
+
+
+def gauss_taps_f32(sigma, ksize=None):
+    L = load()
+    if ksize is None:
+        ksize = L.vslam_gauss_ksize_f32(sigma)
+    t = np.zeros(ksize, np.float32)
+    rc = L.vslam_gauss_taps_f32(sigma, ksize, t.ctypes.data_as(C.POINTER(C.c_float)))
+    if rc:
+        raise VslamError(rc, "vslam_gauss_taps_f32")
+    return t
+
+
+def write_descriptor_file(path, descriptors):
+    d = np.ascontiguousarray(descriptors, np.float32).reshape(-1, 128)
+    rc = load().vslam_write_descriptor_file(os.fsencode(path), d.ctypes.data, d.shape[0])
+    if rc:
+        raise VslamError(rc, "vslam_write_descriptor_file")
 
 
 def gauss_taps(sigma, ksize=None):
@@ -292,6 +318,26 @@ class Context:
         cl = list(counts)
         return {"keypoints": host[:min(sum(cl), capacity)] if host is not None else out, "counts": cl,
                 "overflow": rc == E_CAPACITY}
+
+    def assign_orientations(self, pyr, octave, keypoints, frame=0, histograms=False):
+        """filterKeypoints' orientation stage (Diff_of_Gauss.cpp:340-369) for one octave's keypoints."""
+        kp = np.ascontiguousarray(keypoints).view(KEYPOINT_DTYPE).reshape(-1)
+        n = kp.shape[0]
+        out = np.zeros(36 * max(n, 1), KEYPOINT_DTYPE)
+        hist = np.zeros((n, 36), np.float32) if histograms else None
+        cnt = C.c_int(0)
+        self._chk(load().vslam_assign_orientations(self.h, pyr.h, frame, octave, kp.ctypes.data, n, out.ctypes.data, out.shape[0],
+                                                   C.byref(cnt), hist.ctypes.data if histograms else None))
+        return (out[:cnt.value], hist) if histograms else out[:cnt.value]
+
+    def sift_descriptors(self, pyr, octave, oriented, frame=0):
+        """SIFT() (Diff_of_Gauss.cpp:561-693) for one octave's oriented keypoints -> (n x 128 float32, n uint8 valid)."""
+        kp = np.ascontiguousarray(oriented).view(KEYPOINT_DTYPE).reshape(-1)
+        n = kp.shape[0]
+        desc = np.zeros((n, 128), np.float32)
+        valid = np.zeros(n, np.uint8)
+        self._chk(load().vslam_sift_descriptors(self.h, pyr.h, frame, octave, kp.ctypes.data, n, desc.ctypes.data, valid.ctypes.data))
+        return desc, valid
 
     def bgr_to_gray(self, bgr):
         """cvtColor(COLOR_BGR2GRAY) of (rows, cols, 3) or (n, rows, cols, 3) uint8 frames -> uint8 gray frames."""

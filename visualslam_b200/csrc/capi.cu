@@ -6,6 +6,7 @@
 
 #include <mutex>
 
+#include "descriptor.cuh"
 #include "detect.cuh"
 #include "fused.cuh"
 #include "harris.cuh"
@@ -983,6 +984,124 @@ int vslam_edge_responses(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, in
                             pyr->opitch[octave], (float *)d[1]));
     D2H(responses, d[1], b[1]);
     return vslam_sync(ctx);
+}
+
+int vslam_gauss_ksize_f32(double sigma) { return sigma > 0 ? ((int)nearbyint(sigma * 4 * 2 + 1) | 1) : -1; }
+
+int vslam_gauss_taps_f32(double sigma, int ksize, float *taps) {
+    if (!taps || ksize <= 0 || !(ksize & 1) || !(sigma > 0)) return VSLAM_E_INVALID;
+    std::vector<double> t((size_t)ksize);
+    const double scale2x = -0.5 / (sigma * sigma);
+    double sum = 0;
+    for (int i = 0; i < ksize; ++i) {
+        const double x = i - (ksize - 1) * 0.5;
+        t[i] = exp(scale2x * x * x);
+        sum += t[i];
+    }
+    sum = 1. / sum;
+    for (int i = 0; i < ksize; ++i) taps[i] = (float)(t[i] * sum);
+    return VSLAM_OK;
+}
+
+// tap tables of sigma = 1.5 * getSigmaAt(octave, l) for the levels the list uses, uploaded behind the other scratch regions
+static int desc_levels(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *kp, int n, std::vector<float> &h_taps,
+                       DescLevels &lv, int &max_r) {
+    bool used[6] = {false, false, false, false, false, false};
+    for (int i = 0; i < n; ++i)
+        if (kp[i].level >= 0 && kp[i].level < 6) used[kp[i].level] = true;
+    max_r = 0;
+    h_taps.clear();
+    for (int l = 0; l < 6; ++l) {
+        lv.gauss[l] = pyr->plane(frame, octave, 1 + l);
+        lv.tap_off[l] = (int)h_taps.size();
+        lv.ksize[l] = 1;
+        if (!used[l]) continue;
+        const double sigma = 1.5 * pyr->sigma[octave][l];                  // Diff_of_Gauss.cpp:346, :610
+        const int ks = vslam_gauss_ksize_f32(sigma);
+        if (ks <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "sigma of octave %d level %d is not positive", octave, l);
+        lv.ksize[l] = ks;
+        h_taps.resize(h_taps.size() + ks);
+        vslam_gauss_taps_f32(sigma, ks, h_taps.data() + lv.tap_off[l]);
+        max_r = ks / 2 > max_r ? ks / 2 : max_r;
+    }
+    if (h_taps.empty()) h_taps.push_back(1.f);
+    return VSLAM_OK;
+}
+
+int vslam_assign_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *keypoints, int n,
+                              vslam_keypoint *out, int capacity, int *count, float *histograms) {
+    if (!ctx || !pyr || !count || n < 0 || capacity < 0 || (n > 0 && !keypoints) || (capacity > 0 && !out)) return VSLAM_E_INVALID;
+    if (frame < 0 || frame >= pyr->n_frames || octave < 0 || octave >= pyr->num_octaves) VS_FAIL(ctx, VSLAM_E_INVALID, "frame %d / octave %d out of range", frame, octave);
+    *count = 0;
+    if (n == 0) return VSLAM_OK;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::vector<float> h_taps;
+    DescLevels lv;
+    int max_r = 0;
+    VS_TRY(desc_levels(ctx, pyr, frame, octave, keypoints, n, h_taps, lv, max_r));
+    const size_t b[4] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, histograms ? 144 * (size_t)n : 0, 4 * h_taps.size()};
+    u8 *d[4];
+    VS_TRY(stage_scratch(ctx, b, 4, d));
+    H2D(d[0], keypoints, b[0]);
+    H2D(d[3], h_taps.data(), b[3]);
+    lv.taps = (const float *)d[3];
+    VS_TRY(launch_orient_hist(ctx, (const vslam_keypoint *)d[0], n, lv, max_r, pyr->orows[octave], pyr->ocols[octave], pyr->opitch[octave],
+                              (unsigned long long *)d[1], histograms ? (float *)d[2] : nullptr));
+    std::vector<unsigned long long> masks((size_t)n);
+    D2H(masks.data(), d[1], b[1]);
+    if (histograms) D2H(histograms, d[2], b[2]);
+    VS_TRY(vslam_sync(ctx));
+    long long m = 0;
+    for (int i = 0; i < n; ++i)                                            // :362-368: bins in ascending order per keypoint
+        for (int bin = 0; bin < 36; ++bin)
+            if (masks[i] >> bin & 1) {
+                if (m < capacity) out[m] = vslam_keypoint{keypoints[i].row, keypoints[i].col, bin * 10, 0, keypoints[i].octave, keypoints[i].level};
+                ++m;
+            }
+    if (m > 0x7fffffff) VS_FAIL(ctx, VSLAM_E_INVALID, "oriented keypoint count overflows int");
+    *count = (int)m;
+    return VSLAM_OK;
+}
+
+int vslam_sift_descriptors(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *oriented, int n,
+                           float *descriptors, uint8_t *valid) {
+    if (!ctx || !pyr || n < 0 || (n > 0 && (!oriented || !descriptors || !valid))) return VSLAM_E_INVALID;
+    if (frame < 0 || frame >= pyr->n_frames || octave < 0 || octave >= pyr->num_octaves) VS_FAIL(ctx, VSLAM_E_INVALID, "frame %d / octave %d out of range", frame, octave);
+    if (n == 0) return VSLAM_OK;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::vector<float> h_taps;
+    DescLevels lv;
+    int max_r = 0;
+    VS_TRY(desc_levels(ctx, pyr, frame, octave, oriented, n, h_taps, lv, max_r));
+    std::vector<float2> cs((size_t)n);
+    for (int i = 0; i < n; ++i) {                                          // Rotation::cos_sin_of_angle (rotation.cpp:9-17)
+        const float angle = (float)((double)(float)oriented[i].value * (3.1415926535897932384626433832795 / (double)180.0f));
+        cs[i] = make_float2((float)cos((double)angle), (float)sin((double)angle));
+    }
+    const size_t b[5] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, 512 * (size_t)n, (size_t)n, 4 * h_taps.size()};
+    u8 *d[5];
+    VS_TRY(stage_scratch(ctx, b, 5, d));
+    H2D(d[0], oriented, b[0]);
+    H2D(d[1], cs.data(), b[1]);
+    H2D(d[4], h_taps.data(), b[4]);
+    lv.taps = (const float *)d[4];
+    VS_TRY(launch_sift(ctx, (const vslam_keypoint *)d[0], (const float2 *)d[1], n, lv, max_r, pyr->orows[octave], pyr->ocols[octave],
+                       pyr->opitch[octave], (float *)d[2], d[3]));
+    D2H(descriptors, d[2], b[2]);
+    D2H(valid, d[3], b[3]);
+    return vslam_sync(ctx);                                                // the host vectors above outlive the copies
+}
+
+int vslam_write_descriptor_file(const char *path, const float *descriptors, int n) {
+    if (!path || n < 0 || (n > 0 && !descriptors)) return VSLAM_E_INVALID;
+    FILE *f = fopen(path, "wb");
+    if (!f) VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_INVALID, "cannot write %s", path);
+    const int32_t head[3] = {n, 128, 24};                                  // :842-848: frontSize = sizeof(std::vector<float>)
+    bool ok = fwrite(head, 4, 3, f) == 3;
+    if (n > 0) ok = ok && fwrite(descriptors, 512, (size_t)n, f) == (size_t)n;
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_INVALID, "short write to %s", path);
+    return VSLAM_OK;
 }
 
 int vslam_localize(vslam_ctx *ctx, const int32_t *candidates, int n, float *dog_zhat) {

@@ -1,0 +1,206 @@
+// descriptor.cu -- the stage that follows the hot path in ./DoG, one CTA per keypoint:
+//   orient_hist_k   filterKeypoints' second half   Diff_of_Gauss.cpp:340-369 + orientationHistogram :112-133
+//   sift_k          SIFT + rotateImageSection      Diff_of_Gauss.cpp:561-693, :528-559
+// Both blur a 16x16 magnitude window with OpenCV's fp32 GaussianBlur (kernel size cvRound(sigma*8+1)|1, up to 489 taps):
+// every output is one sequential chain of fused multiply-adds in the order OpenCV's RowFilter (taps left to right) and
+// SymmColumnFilter (centre tap, then symmetric pairs) use, so the result does not depend on how the work is split over threads.
+// Magnitude and orientation are formed from the level's u8 Gaussian on the fly (grad_math.cuh): the fp32 maps of
+// GaussPyramid::processGradients never exist in HBM.
+#include "descriptor.cuh"
+#include "grad_math.cuh"
+
+namespace vslam {
+
+static const int W = 16;                                           // windowSize (Diff_of_Gauss.cpp:305, :565)
+
+__host__ __device__ __forceinline__ int stage_stride(int r) {     // floats per staged row: >= 16 + 2r, == 16 (mod 32)
+    const int need = W + 2 * r;
+    return ((need + 15) / 32) * 32 + 16;
+}
+
+size_t orient_smem_bytes(int r) {
+    const int n = 2 * r + 1, span = W + 2 * r;
+    return sizeof(float) * ((size_t)n + (size_t)W * stage_stride(r) + (size_t)span * W + 256 + 36) + sizeof(int) * ((size_t)span + 256);
+}
+
+// The window is Rect(x, y, 16, 16) of the level's maps replicate-padded by 8 (:318-320, :341-343).  The blur of that ROI
+// reads the padded parent around it and reflects (101) at the parent's edges, so source row q of the (16 + 2r)^2
+// neighbourhood is padded row refl101(y + q - r, rows + 16), i.e. map row clamp(. - 8).
+__global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__restrict__ kp, int n_kp, DescLevels lv, int rows, int cols,
+                                                     size_t pitch, unsigned long long *__restrict__ masks, float *__restrict__ histos) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int t = threadIdx.x;
+    const vslam_keypoint k = kp[blockIdx.x];
+    if (k.level < 0 || k.level >= 6 || k.row < 0 || k.row >= rows || k.col < 0 || k.col >= cols) {
+        if (t == 0) masks[blockIdx.x] = 0;
+        if (histos && t < 36) histos[(size_t)blockIdx.x * 36 + t] = 0.f;
+        return;
+    }
+    const int n = lv.ksize[k.level], r = n / 2, span = W + 2 * r, SP = stage_stride(r), pad = 8;
+    const u8 *__restrict__ g = lv.gauss[k.level];
+    float *taps = (float *)smem_raw;                               // n
+    float *S = taps + n;                                           // 16 x SP staged magnitudes
+    float *H = S + W * SP;                                         // span x 16 row-filtered
+    float *wv = H + span * W;                                      // 256 weighted magnitudes
+    float *hs = wv + 256;                                          // 36 bins
+    int *cidx = (int *)(hs + 36);                                  // span source columns
+    int *wb = cidx + span;                                         // 256 bin indices
+    for (int i = t; i < n; i += 256) taps[i] = lv.taps[lv.tap_off[k.level] + i];
+    for (int c = t; c < span; c += 256) cidx[c] = clampi(refl101(k.col + c - r, cols + 2 * pad) - pad, 0, cols - 1);
+    __syncthreads();
+    const int q = t >> 4, j = t & 15;
+    for (int q0 = 0; q0 < span; q0 += W) {
+        for (int idx = t; idx < W * span; idx += 256) {
+            const int qq = idx / span, c = idx - qq * span;
+            if (q0 + qq < span) {
+                const int sy = clampi(refl101(k.row + q0 + qq - r, rows + 2 * pad) - pad, 0, rows - 1);
+                S[qq * SP + c] = mag_at(g, rows, cols, pitch, sy, cidx[c]);
+            }
+        }
+        __syncthreads();
+        if (q0 + q < span) {
+            const float *s = S + q * SP + j;
+            float a = __fmul_rn(taps[0], s[0]);
+            for (int u = 1; u < n; ++u) a = __fmaf_rn(taps[u], s[u], a);
+            H[(q0 + q) * W + j] = a;
+        }
+        __syncthreads();
+    }
+    {   // column pass for window sample (i, j) = (q, j)
+        const float *h = H + (q + r) * W + j;
+        float a = __fmul_rn(taps[r], h[0]);
+        for (int v = 1; v <= r; ++v) a = __fmaf_rn(taps[r + v], __fadd_rn(h[v * W], h[-v * W]), a);
+        float dx, dy;
+        grad_at(g, rows, cols, pitch, clampi(k.row + q - pad, 0, rows - 1), clampi(k.col + j - pad, 0, cols - 1), dx, dy);
+        const float coeff = 36.f / 360.0f;                         // :114
+        wv[t] = a;
+        wb[t] = (int)__fmul_rn(fast_atan2_deg(dy, dx), coeff);     // :125
+    }
+    __syncthreads();
+    if (t < 36) {                                                  // :128 in the reference's order (rows, then columns)
+        float a = 0.f;
+        for (int i = 0; i < 256; ++i)
+            if (wb[i] == t) a = __fadd_rn(a, wv[i]);
+        hs[t] = a;
+        if (histos) histos[(size_t)blockIdx.x * 36 + t] = a;
+    }
+    __syncthreads();
+    if (t == 0) {
+        float peak = hs[0];
+        for (int b = 1; b < 36; ++b) peak = hs[b] > peak ? hs[b] : peak;
+        const float thr = __fmul_rn(peak, 0.8f);                   // :359
+        unsigned long long m = 0;
+        for (int b = 0; b < 36; ++b)
+            if (hs[b] > thr) m |= 1ull << b;
+        masks[blockIdx.x] = m;
+    }
+}
+
+size_t sift_smem_bytes(int r) { return sizeof(float) * (size_t)(2 * r + 1) + sizeof(int) * (size_t)(2 * r + W); }
+
+// One oriented keypoint: the 16x16 rotated section of the maps replicate-padded by 20 (:578-580), read the way
+// rotateImageSection does -- list index i * 16 + j into the 17-wide point list (:545) and at<>(point.x, point.y), x as
+// the row (:549-554).  A sample whose linear address leaves the padded map is undefined in the reference; it is taken
+// from the nearest end of the buffer and the descriptor is flagged invalid.
+__global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__ kp, const float2 *__restrict__ cs, int n_kp, DescLevels lv,
+                                              int rows, int cols, size_t pitch, float *__restrict__ desc, u8 *__restrict__ valid) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ float M[256], Hh[256], Wt[256], D[128], red[4];
+    __shared__ int B[256], bad;
+    const int t = threadIdx.x, i = t >> 4, j = t & 15;
+    const vslam_keypoint k = kp[blockIdx.x];
+    float *out = desc + (size_t)blockIdx.x * 128;
+    if (k.level < 0 || k.level >= 6 || k.row < 0 || k.row >= rows || k.col < 0 || k.col >= cols) {
+        if (t < 128) out[t] = __int_as_float(0x7fc00000);
+        if (t == 0) valid[blockIdx.x] = 0;
+        return;
+    }
+    const int n = lv.ksize[k.level], r = n / 2, pad = 20;
+    const u8 *__restrict__ g = lv.gauss[k.level];
+    float *taps = (float *)smem_raw;
+    int *ridx = (int *)(taps + n);                                 // ridx[c] = refl101(c - r, 16), c in [0, 2r + 16)
+    for (int c = t; c < n; c += 256) taps[c] = lv.taps[lv.tap_off[k.level] + c];
+    for (int c = t; c < 2 * r + W; c += 256) ridx[c] = refl101(c - r, W);
+    if (t == 0) bad = 0;
+    __syncthreads();
+    {
+        const int PR = rows + 2 * pad, PC = cols + 2 * pad, cx = k.col + pad, cy = k.row + pad;
+        const int p = i * W + j, pi = p / (W + 1), pj = p - pi * (W + 1);
+        const float c = cs[blockIdx.x].x, s = cs[blockIdx.x].y;
+        const int rx = pj - 8, ry = pi - 8;                        // rotate_pt_CW (rotation.cpp:19-28)
+        const int xr = (int)__fsub_rn(__fmul_rn((float)rx, c), __fmul_rn((float)ry, s)) + cx;
+        const int yr = (int)__fadd_rn(__fmul_rn((float)rx, s), __fmul_rn((float)ry, c)) + cy;
+        long long lin = (long long)xr * PC + yr;
+        const long long total = (long long)PR * PC;
+        if (lin < 0 || lin >= total) { bad = 1; lin = lin < 0 ? 0 : total - 1; }
+        const int sy = clampi((int)(lin / PC) - pad, 0, rows - 1), sx = clampi((int)(lin % PC) - pad, 0, cols - 1);
+        float dx, dy;
+        grad_at(g, rows, cols, pitch, sy, sx, dx, dy);
+        M[t] = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+        B[t] = (int)__fmul_rn(fast_atan2_deg(dy, dx), 8.f / 360.0f);
+    }
+    __syncthreads();
+    {   // GaussianBlur of the stand-alone 16x16 Mat (:611): reflect-101 on the window itself
+        const float *m = M + i * W;
+        float a = __fmul_rn(taps[0], m[ridx[j]]);
+        for (int u = 1; u < n; ++u) a = __fmaf_rn(taps[u], m[ridx[j + u]], a);
+        Hh[t] = a;
+    }
+    __syncthreads();
+    {
+        float a = __fmul_rn(taps[r], Hh[t]);
+        for (int v = 1; v <= r; ++v) a = __fmaf_rn(taps[r + v], __fadd_rn(Hh[ridx[i + v + r] * W + j], Hh[ridx[i - v + r] * W + j]), a);
+        Wt[t] = a;
+    }
+    __syncthreads();
+    if (t < 128) {                                                 // :630-646: cell t / 8 (columns first), bin t % 8
+        const int cell = t >> 3, b = t & 7, r0 = 4 * (cell >> 2), c0 = 4 * (cell & 3);
+        float a = 0.f;
+        for (int y = r0; y < r0 + 4; ++y)
+            for (int x = c0; x < c0 + 4; ++x)
+                if (B[y * W + x] == b) a = __fadd_rn(a, Wt[y * W + x]);
+        D[t] = a;
+    }
+    for (int pass = 0; pass < 2; ++pass) {                         // :652-669: / max, min(., 0.2), / max
+        __syncthreads();
+        if (t < 128) {                                             // max_element: NaN never replaces the running maximum
+            float v = D[t];
+            for (int o = 16; o; o >>= 1) { const float w = __shfl_xor_sync(0xffffffffu, v, o); v = w > v ? w : v; }
+            if ((t & 31) == 0) red[t >> 5] = v;
+        }
+        __syncthreads();
+        if (t < 128) {
+            float peak = red[0];
+            for (int w = 1; w < 4; ++w) peak = red[w] > peak ? red[w] : peak;
+            float v = __fdiv_rn(D[t], peak);
+            if (pass == 0) v = 0.2f < v ? 0.2f : v;
+            D[t] = v;
+        }
+    }
+    if (t < 128) out[t] = D[t];
+    if (t == 0) valid[blockIdx.x] = bad ? 0 : 1;
+}
+
+int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, int n, const DescLevels &lv, int max_r, int rows, int cols, size_t pitch,
+                       unsigned long long *masks, float *histos) {
+    const size_t smem = orient_smem_bytes(max_r);
+    if (smem > 227 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "orientation window blur needs %zu bytes of shared memory (sigma too large)", smem);
+    VS_CUDA(ctx, cudaFuncSetAttribute(orient_hist_k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KernelSpan span(ctx, VSLAM_K_DESCRIPTOR);
+    orient_hist_k<<<n, 256, smem, ctx->stream>>>(kp, n, lv, rows, cols, pitch, masks, histos);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
+
+int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const float2 *cs, int n, const DescLevels &lv, int max_r, int rows, int cols,
+                size_t pitch, float *desc, u8 *valid) {
+    const size_t smem = sift_smem_bytes(max_r);
+    if (smem > 200 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "descriptor window blur needs %zu bytes of shared memory (sigma too large)", smem);
+    VS_CUDA(ctx, cudaFuncSetAttribute(sift_k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KernelSpan span(ctx, VSLAM_K_DESCRIPTOR);
+    sift_k<<<n, 256, smem, ctx->stream>>>(kp, cs, n, lv, rows, cols, pitch, desc, valid);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
+
+}  // namespace vslam

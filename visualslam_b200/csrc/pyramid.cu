@@ -5,6 +5,7 @@
 //
 // The Gaussian stack itself (rows B, C, D) lives in fused.cu.
 #include "pyramid.cuh"
+#include "grad_math.cuh"
 
 namespace vslam {
 
@@ -119,27 +120,6 @@ int launch_upsample2x(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t 
 // row E: Sobel(CV_32F, ksize=1) = central differences with reflect-101 borders (zero on the first/last
 // column / row), cv::magnitude, cv::phase(degrees) (OpenCV's fastAtan polynomial, evaluated without FMA).
 // ------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
-    const float scale = (float)(180.0 / 3.14159265358979323846);
-    const float p1 = 0.9997878412794807f * scale, p3 = -0.3258083974640975f * scale,
-                p5 = 0.1555786518463281f * scale, p7 = -0.04432655554792128f * scale;
-    const float ax = fabsf(x), ay = fabsf(y);
-    const float eps = (float)2.2204460492503131e-16;
-    float a, c, c2;
-    if (ax >= ay) {
-        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
-        c2 = __fmul_rn(c, c);
-        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
-    } else {
-        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
-        c2 = __fmul_rn(c, c);
-        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
-    }
-    if (x < 0) a = __fsub_rn(180.f, a);
-    if (y < 0) a = __fsub_rn(360.f, a);
-    return a;
-}
-
 __global__ void __launch_bounds__(256) grad_k(const u8 *__restrict__ g, int rows, int cols, size_t pitch,
                                               float *__restrict__ gx, float *__restrict__ gy,
                                               float *__restrict__ mag, float *__restrict__ orient, size_t op) {

@@ -246,6 +246,13 @@ VSLAM_API int vslam_assign_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr
  * memory outside the image: undefined there; here such samples come from the nearest end of the map). */
 VSLAM_API int vslam_sift_descriptors(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave,
                                      const vslam_keypoint *oriented, int n, float *descriptors, uint8_t *valid);
+/* Both stages for every frame of a pyramid in two launches (one CTA per keypoint, all frames and octaves together):
+ * keypoints = the hot path's lists of frames 0..n_frames-1 back to back (counts[f] each, every point read in its own
+ * .octave); oriented / descriptors / valid receive up to `capacity` points in the same frame order and
+ * oriented_counts[f] their number per frame (the totals are reported even when VSLAM_E_CAPACITY is returned). */
+VSLAM_API int vslam_describe_keypoints(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_keypoint *keypoints,
+                                       const int *counts, vslam_keypoint *oriented, int capacity, int *oriented_counts,
+                                       float *descriptors, uint8_t *valid);
 /* featureDescriptors.dat as ./DoG writes it (Diff_of_Gauss.cpp:837-863): int32 count, int32 128, int32
  * sizeof(std::vector<float>) (24 on LP64), then count x 128 float32.  Host only. */
 VSLAM_API int vslam_write_descriptor_file(const char *path, const float *descriptors, int n);

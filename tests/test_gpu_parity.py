@@ -395,3 +395,28 @@ def test_descriptor_edge_cases(ctx, tmp_path):
     assert np.frombuffer(raw[:12], "<i4").tolist() == [len(wd), 128, 24]
     assert np.array_equal(np.frombuffer(raw[12:], "<f4").reshape(-1, 128).view(np.uint32), wd.view(np.uint32))
     pyr.close()
+
+
+def test_describe_keypoints_batch_vs_oracle(ctx):
+    """All frames and octaves of a batch in two launches: per frame the oracle's oriented list and descriptors."""
+    frames = np.stack([synth.frame(i, 270, 480) for i in (2, 5, 6)], 0)
+    pyr = ctx.build_pyramid(frames, 4, 1.6)
+    det = ctx.dog_detect(pyr, stage_counts=False)
+    res = ctx.describe_keypoints(pyr, det["keypoints"], det["counts"])
+    start = 0
+    for f in range(len(frames)):
+        ori_o, desc_o, valid_o, _ = O.dog_features(frames[f])
+        n = res["counts"][f]
+        assert n == len(ori_o), f
+        assert np.array_equal(kp_array(res["oriented"][start:start + n]).reshape(-1, 6), ori_o), f
+        assert np.array_equal(res["valid"][start:start + n], valid_o), f
+        assert same_floats(res["descriptors"][start:start + n], desc_o), f
+        start += n
+    # a list that does not fit: totals are still reported, the stored prefix is right
+    small = ctx.describe_keypoints(pyr, det["keypoints"], det["counts"], capacity=10)
+    assert small["overflow"] and small["counts"] == res["counts"]
+    assert np.array_equal(small["oriented"], res["oriented"][:10]) and same_floats(small["descriptors"], res["descriptors"][:10])
+    # no keypoints at all
+    none = ctx.describe_keypoints(pyr, np.zeros((0, 6), np.int32), [0, 0, 0])
+    assert none["counts"] == [0, 0, 0] and len(none["oriented"]) == 0
+    pyr.close()

@@ -82,6 +82,31 @@ def test_dog_executable_matches_golden(tmp_path, images, golden_lists, stem):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("flags", [[], ["--fused"]])
+def test_dog_executable_writes_the_descriptor_file(tmp_path, images, flags):
+    """./DoG after the hot path: oriented keypoints and featureDescriptors.dat (Diff_of_Gauss.cpp:787-791, 815, 834, 837-863)
+    against the cv2 fixtures of tools/make_golden_descriptors.py."""
+    from conftest import image_for
+    _build()
+    with np.load(os.path.join(ROOT, "tests", "golden", "descriptors.npz")) as z:
+        gd = {k: z[k] for k in z.files}
+    p = str(tmp_path / "home.pgm")
+    _pgm(p, image_for(images, "home", "cvt"))
+    ori, dat = str(tmp_path / "oriented.txt"), str(tmp_path / "featureDescriptors.dat")
+    r = _run("DoG", p, "--oriented", ori, "--desc", dat, *flags)
+    assert r.returncode == 0, r.stderr
+    want = gd["home_oriented"]
+    assert _last_int(r.stdout, "Number of features found in image:") == len(want)
+    assert _last_int(r.stdout, "Number of keypoints after edge orientation:") == len(want)
+    assert np.array_equal(np.loadtxt(ori, dtype=np.int64).reshape(-1, 6), want)
+    raw = open(dat, "rb").read()
+    assert np.frombuffer(raw[:12], "<i4").tolist() == [len(want), 128, 24]
+    desc = np.frombuffer(raw[12:], "<f4").reshape(-1, 128)
+    ok = gd["home_valid"].astype(bool)
+    assert np.nanmax(np.abs(desc[ok] - gd["home_desc"][ok])) <= 1e-4
+
+
+@pytest.mark.gpu
 def test_dog_executable_on_colour_input(tmp_path, golden_lists):
     """./DoG on a colour PPM: imread(IMREAD_COLOR) + cvtColor on the GPU (Diff_of_Gauss.cpp:730-739), then the golden keypoints."""
     _build()

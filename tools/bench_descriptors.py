@@ -1,0 +1,100 @@
+#!/usr/bin/env python
+"""Timing of the stage after the hot path (orientation assignment + SIFT descriptors) on synthetic 1080p frames:
+device time of orient_hist_k + sift_k (CUDA events on the context's stream, vslam_profile) and the time of the C-ABI
+calls with host lists in and out, beside the plain-C oracle on the host (1 thread) for a bounded sample.
+
+    python tools/bench_descriptors.py [--frames 8] [--rows 1080 --cols 1920] [--cpu-frames 1] > profiles/descriptors_rXX.json
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import visualslam_b200 as vs  # noqa: E402
+from visualslam_b200 import synth  # noqa: E402
+
+
+def kp6(k):
+    return np.stack([k[n] for n in ("row", "col", "value", "padding", "octave", "level")], 1).astype(np.int32)
+
+
+def fma_count(pyr, kps6):
+    """Chain steps the two kernels execute per keypoint: row pass (16 + 2r) x 16 x n, column pass 256 x (r + 1)."""
+    tot = 0
+    for o, l in {(int(a), int(b)) for a, b in kps6[:, 4:6]}:
+        n = vs.load().vslam_gauss_ksize_f32(1.5 * pyr.sigma_at(o, l))
+        r = n // 2
+        cnt = int(((kps6[:, 4] == o) & (kps6[:, 5] == l)).sum())
+        tot += cnt * ((16 + 2 * r) * 16 * n + 256 * (r + 1))
+    return tot
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=8)
+    ap.add_argument("--rows", type=int, default=1080)
+    ap.add_argument("--cols", type=int, default=1920)
+    ap.add_argument("--cpu-frames", type=int, default=1)
+    a = ap.parse_args()
+    ctx = vs.Context(0)
+    frames = [synth.frame(i, a.rows, a.cols) for i in range(a.frames)]
+    stats = {"keypoints": 0, "oriented": 0, "valid": 0, "orient_fma": 0, "sift_fma": 0}
+    wall = {}
+    dev_ms = 0.0
+    launches = 0
+    batch = np.stack(frames, 0)
+    pyr = ctx.build_pyramid(batch, 4, 1.6)                  # the whole batch materialised: 12 u8 planes x 5.3 px per input px
+    det = ctx.dog_detect(pyr, stage_counts=False, capacity=1 << 22)
+    k = kp6(det["keypoints"])
+    for it in range(3):                                    # first pass warms up
+        ctx.profile(True)
+        t0 = time.perf_counter()
+        res = ctx.describe_keypoints(pyr, det["keypoints"], det["counts"])
+        t1 = time.perf_counter()
+        p = ctx.profile_read()["orient_hist_k + sift_k"]
+        ctx.profile(False)
+        if it:
+            wall["describe_keypoints"] = wall.get("describe_keypoints", 0.0) + (t1 - t0) / 2
+            dev_ms += p["ms"] / 2; launches = p["launches"]
+    o6 = kp6(res["oriented"])
+    stats["keypoints"] = len(k); stats["oriented"] = len(o6); stats["valid"] = int(res["valid"].sum())
+    stats["orient_fma"] = fma_count(pyr, k)
+    for oo, l in {(int(x), int(y)) for x, y in o6[:, 4:6]}:
+        n = vs.load().vslam_gauss_ksize_f32(1.5 * pyr.sigma_at(oo, l))
+        stats["sift_fma"] += int(((o6[:, 4] == oo) & (o6[:, 5] == l)).sum()) * (256 * n + 256 * (n // 2 + 1))
+    pyr.close()
+    px = a.frames * a.rows * a.cols
+    out = {"workload": f"{a.frames} synthetic {a.cols}x{a.rows} frames, 4 octaves, sigma 1.6: orientation assignment + SIFT of every hot-path keypoint",
+           **stats, "kernel_launches": launches, "device_ms": dev_ms,
+           "device_keypoints_per_s": stats["keypoints"] / (dev_ms * 1e-3), "device_Mpix_per_s": px / 1e6 / (dev_ms * 1e-3),
+           "device_GFMA_per_s": (stats["orient_fma"] + stats["sift_fma"]) / 1e9 / (dev_ms * 1e-3),
+           "fp32_peak_GFMA_per_s": 148 * 128 * 1.965, "peak_source": "148 SMs x 128 FMA lanes x 1.965 GHz (MEASURED_PEAKS.json sm_max_mhz)",
+           "abi_ms": {k: v * 1e3 for k, v in wall.items()},
+           "abi_Mpix_per_s": px / 1e6 / sum(wall.values()),
+           "api": "vslam_describe_keypoints: host keypoint lists in, host oriented lists + descriptors out, two launches for the batch"}
+    if a.cpu_frames > 0:
+        from oracle import c_oracle as O
+        t = 0.0
+        nk = 0
+        for img in frames[:a.cpu_frames]:
+            pyr = O.build_pyramid(img)
+            ks = [O.detect_octave(pyr["dog"][o], pyr["gauss"][o], o)[0] for o in range(4)]
+            t0 = time.perf_counter()
+            for o in range(4):
+                r = O.assign_orientations(pyr["gauss"][o], pyr["sigma"][o], ks[o])
+                O.sift(pyr["gauss"][o], pyr["sigma"][o], r)
+                nk += len(ks[o])
+            t += time.perf_counter() - t0
+        out["cpu_baseline"] = {"kind": "port", "cores": 1, "sample": f"{a.cpu_frames} frame(s)", "seconds": t,
+                               "keypoints_per_s": nk / t, "Mpix_per_s": a.cpu_frames * a.rows * a.cols / 1e6 / t}
+    print(json.dumps(out))
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

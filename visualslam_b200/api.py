@@ -60,7 +60,7 @@ EXPORTS = [
     "vslam_dog_detect_octave", "vslam_edge_responses", "vslam_localize", "vslam_edge_from_windows",
     # the stage after the hot path: orientation assignment, SIFT descriptors, featureDescriptors.dat
     "vslam_gauss_ksize_f32", "vslam_gauss_taps_f32", "vslam_assign_orientations", "vslam_sift_descriptors",
-    "vslam_write_descriptor_file",
+    "vslam_write_descriptor_file", "vslam_describe_keypoints",
 ]
 
 _lib = None
@@ -109,6 +109,7 @@ def load():
     L.vslam_assign_orientations.argtypes = [vp, vp, i, i, vp, i, vp, i, C.POINTER(i), vp]
     L.vslam_sift_descriptors.argtypes = [vp, vp, i, i, vp, i, vp, vp]
     L.vslam_write_descriptor_file.argtypes = [C.c_char_p, vp, i]
+    L.vslam_describe_keypoints.argtypes = [vp, vp, vp, C.POINTER(i), vp, i, C.POINTER(i), vp, vp]
     _lib = L
     return L
 
@@ -244,7 +245,7 @@ class Context:
     def sync(self):
         self._chk(load().vslam_sync(self.h))
 
-    KERNELS = ["upsample2x_k", "reflect_pad_k", "(unused2)", "dog_detect_k", "segment scan+gather", "harris_fused_k", "grad_k", "octave_fused_k"]
+    KERNELS = ["upsample2x_k", "reflect_pad_k", "(unused2)", "dog_detect_k", "segment scan+gather", "harris_fused_k", "grad_k", "octave_fused_k", "orient_hist_k + sift_k"]
 
     def profile(self, enable=True):
         self._chk(load().vslam_profile(self.h, 1 if enable else 0))
@@ -338,6 +339,23 @@ class Context:
         valid = np.zeros(n, np.uint8)
         self._chk(load().vslam_sift_descriptors(self.h, pyr.h, frame, octave, kp.ctypes.data, n, desc.ctypes.data, valid.ctypes.data))
         return desc, valid
+
+    def describe_keypoints(self, pyr, keypoints, counts, capacity=None):
+        """Orientation assignment + SIFT for every frame of a pyramid in two launches (vslam_describe_keypoints)."""
+        kp = np.ascontiguousarray(keypoints).view(KEYPOINT_DTYPE).reshape(-1)
+        assert len(counts) == pyr.n_frames and sum(counts) == kp.shape[0]
+        capacity = 36 * max(kp.shape[0], 1) if capacity is None else capacity
+        out = np.zeros(capacity, KEYPOINT_DTYPE)
+        desc = np.zeros((capacity, 128), np.float32)
+        valid = np.zeros(capacity, np.uint8)
+        cin = (C.c_int * pyr.n_frames)(*[int(c) for c in counts])
+        cout = (C.c_int * pyr.n_frames)()
+        rc = load().vslam_describe_keypoints(self.h, pyr.h, kp.ctypes.data, cin, out.ctypes.data, capacity, cout, desc.ctypes.data,
+                                             valid.ctypes.data)
+        if rc and rc != E_CAPACITY:
+            self._chk(rc)
+        m = min(sum(cout), capacity)
+        return {"oriented": out[:m], "descriptors": desc[:m], "valid": valid[:m], "counts": list(cout), "overflow": rc == E_CAPACITY}
 
     def bgr_to_gray(self, bgr):
         """cvtColor(COLOR_BGR2GRAY) of (rows, cols, 3) or (n, rows, cols, 3) uint8 frames -> uint8 gray frames."""

@@ -1003,29 +1003,95 @@ int vslam_gauss_taps_f32(double sigma, int ksize, float *taps) {
     return VSLAM_OK;
 }
 
-// tap tables of sigma = 1.5 * getSigmaAt(octave, l) for the levels the list uses, uploaded behind the other scratch regions
-static int desc_levels(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *kp, int n, std::vector<float> &h_taps,
-                       DescLevels &lv, int &max_r) {
-    bool used[6] = {false, false, false, false, false, false};
-    for (int i = 0; i < n; ++i)
-        if (kp[i].level >= 0 && kp[i].level < 6) used[kp[i].level] = true;
+// Kernel-side description of the pyramid + the tap tables of sigma = 1.5 * getSigmaAt(o, l) (Diff_of_Gauss.cpp:346, :610) for the
+// (octave, level) pairs the list uses; octave >= 0 reads every keypoint in that octave.
+static int desc_pyr(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *kp, long long n, std::vector<float> &h_taps,
+                    DescPyr &P, int &max_r) {
+    if (pyr->num_octaves > kDescMaxOctaves) VS_FAIL(ctx, VSLAM_E_INVALID, "descriptor stage supports up to %d octaves", kDescMaxOctaves);
+    bool used[kDescMaxOctaves][6] = {};
+    for (long long i = 0; i < n; ++i) {
+        const int o = octave >= 0 ? octave : kp[i].octave;
+        if (o >= 0 && o < pyr->num_octaves && kp[i].level >= 0 && kp[i].level < 6) used[o][kp[i].level] = true;
+    }
+    memset(&P, 0, sizeof P);
+    P.maps = pyr->maps.as<u8>(); P.frame_bytes = pyr->frame_bytes; P.num_octaves = pyr->num_octaves; P.octave = octave; P.frame0 = frame;
     max_r = 0;
     h_taps.clear();
-    for (int l = 0; l < 6; ++l) {
-        lv.gauss[l] = pyr->plane(frame, octave, 1 + l);
-        lv.tap_off[l] = (int)h_taps.size();
-        lv.ksize[l] = 1;
-        if (!used[l]) continue;
-        const double sigma = 1.5 * pyr->sigma[octave][l];                  // Diff_of_Gauss.cpp:346, :610
-        const int ks = vslam_gauss_ksize_f32(sigma);
-        if (ks <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "sigma of octave %d level %d is not positive", octave, l);
-        lv.ksize[l] = ks;
-        h_taps.resize(h_taps.size() + ks);
-        vslam_gauss_taps_f32(sigma, ks, h_taps.data() + lv.tap_off[l]);
-        max_r = ks / 2 > max_r ? ks / 2 : max_r;
+    for (int o = 0; o < pyr->num_octaves; ++o) {
+        P.ooff[o] = pyr->ooff[o]; P.oplane[o] = pyr->oplane[o]; P.opitch[o] = pyr->opitch[o]; P.orows[o] = pyr->orows[o]; P.ocols[o] = pyr->ocols[o];
+        for (int l = 0; l < 6; ++l) {
+            if (!used[o][l]) continue;
+            const double sigma = 1.5 * pyr->sigma[o][l];
+            const int ks = vslam_gauss_ksize_f32(sigma);
+            if (ks <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "sigma of octave %d level %d is not positive", o, l);
+            P.tap_off[o][l] = (int)h_taps.size();
+            P.ksize[o][l] = ks;
+            h_taps.resize(h_taps.size() + ks);
+            vslam_gauss_taps_f32(sigma, ks, h_taps.data() + P.tap_off[o][l]);
+            max_r = ks / 2 > max_r ? ks / 2 : max_r;
+        }
     }
     if (h_taps.empty()) h_taps.push_back(1.f);
     return VSLAM_OK;
+}
+
+// orientation stage of n keypoints (frame_of: host list of their frames or nullptr); masks[i] bit b = bin b is above 0.8 of the peak
+static int run_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *kp, const int *frame_of, int n,
+                            std::vector<unsigned long long> &masks, float *histograms) {
+    std::vector<float> h_taps;
+    DescPyr P;
+    int max_r = 0;
+    VS_TRY(desc_pyr(ctx, pyr, frame, octave, kp, n, h_taps, P, max_r));
+    const size_t b[5] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, histograms ? 144 * (size_t)n : 0, 4 * h_taps.size(), frame_of ? 4 * (size_t)n : 0};
+    u8 *d[5];
+    VS_TRY(stage_scratch(ctx, b, 5, d));
+    H2D(d[0], kp, b[0]);
+    H2D(d[3], h_taps.data(), b[3]);
+    if (frame_of) H2D(d[4], frame_of, b[4]);
+    P.taps = (const float *)d[3];
+    VS_TRY(launch_orient_hist(ctx, (const vslam_keypoint *)d[0], frame_of ? (const int *)d[4] : nullptr, n, P, max_r, (unsigned long long *)d[1],
+                              histograms ? (float *)d[2] : nullptr));
+    masks.resize((size_t)n);
+    D2H(masks.data(), d[1], b[1]);
+    if (histograms) D2H(histograms, d[2], b[2]);
+    return vslam_sync(ctx);                                                // h_taps outlives the copies
+}
+
+static int run_sift(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *kp, const int *frame_of, int n,
+                    float *descriptors, uint8_t *valid) {
+    std::vector<float> h_taps;
+    DescPyr P;
+    int max_r = 0;
+    VS_TRY(desc_pyr(ctx, pyr, frame, octave, kp, n, h_taps, P, max_r));
+    std::vector<float2> cs((size_t)n);
+    for (int i = 0; i < n; ++i) {                                          // Rotation::cos_sin_of_angle (rotation.cpp:9-17)
+        const float angle = (float)((double)(float)kp[i].value * (3.1415926535897932384626433832795 / (double)180.0f));
+        cs[i] = make_float2((float)cos((double)angle), (float)sin((double)angle));
+    }
+    const size_t b[6] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, 512 * (size_t)n, (size_t)n, 4 * h_taps.size(), frame_of ? 4 * (size_t)n : 0};
+    u8 *d[6];
+    VS_TRY(stage_scratch(ctx, b, 6, d));
+    H2D(d[0], kp, b[0]);
+    H2D(d[1], cs.data(), b[1]);
+    H2D(d[4], h_taps.data(), b[4]);
+    if (frame_of) H2D(d[5], frame_of, b[5]);
+    P.taps = (const float *)d[4];
+    VS_TRY(launch_sift(ctx, (const vslam_keypoint *)d[0], frame_of ? (const int *)d[5] : nullptr, (const float2 *)d[1], n, P, max_r, (float *)d[2], d[3]));
+    D2H(descriptors, d[2], b[2]);
+    D2H(valid, d[3], b[3]);
+    return vslam_sync(ctx);                                                // the host vectors above outlive the copies
+}
+
+// :362-368: bins in ascending order per keypoint; returns the number of points (only the first `capacity` are stored)
+static long long expand_orientations(const vslam_keypoint *kp, const unsigned long long *masks, long long n, vslam_keypoint *out, long long capacity) {
+    long long m = 0;
+    for (long long i = 0; i < n; ++i)
+        for (int bin = 0; bin < 36; ++bin)
+            if (masks[i] >> bin & 1) {
+                if (m < capacity) out[m] = vslam_keypoint{kp[i].row, kp[i].col, bin * 10, 0, kp[i].octave, kp[i].level};
+                ++m;
+            }
+    return m;
 }
 
 int vslam_assign_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave, const vslam_keypoint *keypoints, int n,
@@ -1035,29 +1101,9 @@ int vslam_assign_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int fram
     *count = 0;
     if (n == 0) return VSLAM_OK;
     VS_CUDA(ctx, cudaSetDevice(ctx->device));
-    std::vector<float> h_taps;
-    DescLevels lv;
-    int max_r = 0;
-    VS_TRY(desc_levels(ctx, pyr, frame, octave, keypoints, n, h_taps, lv, max_r));
-    const size_t b[4] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, histograms ? 144 * (size_t)n : 0, 4 * h_taps.size()};
-    u8 *d[4];
-    VS_TRY(stage_scratch(ctx, b, 4, d));
-    H2D(d[0], keypoints, b[0]);
-    H2D(d[3], h_taps.data(), b[3]);
-    lv.taps = (const float *)d[3];
-    VS_TRY(launch_orient_hist(ctx, (const vslam_keypoint *)d[0], n, lv, max_r, pyr->orows[octave], pyr->ocols[octave], pyr->opitch[octave],
-                              (unsigned long long *)d[1], histograms ? (float *)d[2] : nullptr));
-    std::vector<unsigned long long> masks((size_t)n);
-    D2H(masks.data(), d[1], b[1]);
-    if (histograms) D2H(histograms, d[2], b[2]);
-    VS_TRY(vslam_sync(ctx));
-    long long m = 0;
-    for (int i = 0; i < n; ++i)                                            // :362-368: bins in ascending order per keypoint
-        for (int bin = 0; bin < 36; ++bin)
-            if (masks[i] >> bin & 1) {
-                if (m < capacity) out[m] = vslam_keypoint{keypoints[i].row, keypoints[i].col, bin * 10, 0, keypoints[i].octave, keypoints[i].level};
-                ++m;
-            }
+    std::vector<unsigned long long> masks;
+    VS_TRY(run_orientations(ctx, pyr, frame, octave, keypoints, nullptr, n, masks, histograms));
+    const long long m = expand_orientations(keypoints, masks.data(), n, out, capacity);
     if (m > 0x7fffffff) VS_FAIL(ctx, VSLAM_E_INVALID, "oriented keypoint count overflows int");
     *count = (int)m;
     return VSLAM_OK;
@@ -1069,27 +1115,49 @@ int vslam_sift_descriptors(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, 
     if (frame < 0 || frame >= pyr->n_frames || octave < 0 || octave >= pyr->num_octaves) VS_FAIL(ctx, VSLAM_E_INVALID, "frame %d / octave %d out of range", frame, octave);
     if (n == 0) return VSLAM_OK;
     VS_CUDA(ctx, cudaSetDevice(ctx->device));
-    std::vector<float> h_taps;
-    DescLevels lv;
-    int max_r = 0;
-    VS_TRY(desc_levels(ctx, pyr, frame, octave, oriented, n, h_taps, lv, max_r));
-    std::vector<float2> cs((size_t)n);
-    for (int i = 0; i < n; ++i) {                                          // Rotation::cos_sin_of_angle (rotation.cpp:9-17)
-        const float angle = (float)((double)(float)oriented[i].value * (3.1415926535897932384626433832795 / (double)180.0f));
-        cs[i] = make_float2((float)cos((double)angle), (float)sin((double)angle));
+    return run_sift(ctx, pyr, frame, octave, oriented, nullptr, n, descriptors, valid);
+}
+
+int vslam_describe_keypoints(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_keypoint *keypoints, const int *counts, vslam_keypoint *oriented,
+                             int capacity, int *oriented_counts, float *descriptors, uint8_t *valid) {
+    if (!ctx || !pyr || !counts || !oriented_counts || capacity < 0 || (capacity > 0 && (!oriented || !descriptors || !valid))) return VSLAM_E_INVALID;
+    long long n = 0;
+    for (int f = 0; f < pyr->n_frames; ++f) {
+        if (counts[f] < 0) VS_FAIL(ctx, VSLAM_E_INVALID, "negative count for frame %d", f);
+        n += counts[f];
+        oriented_counts[f] = 0;
     }
-    const size_t b[5] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, 512 * (size_t)n, (size_t)n, 4 * h_taps.size()};
-    u8 *d[5];
-    VS_TRY(stage_scratch(ctx, b, 5, d));
-    H2D(d[0], oriented, b[0]);
-    H2D(d[1], cs.data(), b[1]);
-    H2D(d[4], h_taps.data(), b[4]);
-    lv.taps = (const float *)d[4];
-    VS_TRY(launch_sift(ctx, (const vslam_keypoint *)d[0], (const float2 *)d[1], n, lv, max_r, pyr->orows[octave], pyr->ocols[octave],
-                       pyr->opitch[octave], (float *)d[2], d[3]));
-    D2H(descriptors, d[2], b[2]);
-    D2H(valid, d[3], b[3]);
-    return vslam_sync(ctx);                                                // the host vectors above outlive the copies
+    if (n > 0x7fffffff / 36) VS_FAIL(ctx, VSLAM_E_INVALID, "too many keypoints for one call (%lld)", n);
+    if (n == 0) return VSLAM_OK;
+    if (!keypoints) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::vector<int> frame_of((size_t)n);
+    {
+        long long i = 0;
+        for (int f = 0; f < pyr->n_frames; ++f)
+            for (int c = 0; c < counts[f]; ++c) frame_of[(size_t)i++] = f;
+    }
+    std::vector<unsigned long long> masks;
+    VS_TRY(run_orientations(ctx, pyr, 0, -1, keypoints, frame_of.data(), (int)n, masks, nullptr));
+    // expansion frame by frame: the reference's order inside a frame, frames back to back
+    std::vector<int> oframe;
+    long long m = 0, i0 = 0;
+    for (int f = 0; f < pyr->n_frames; ++f) {
+        const long long got = expand_orientations(keypoints + i0, masks.data() + i0, counts[f], oriented ? oriented + (m < capacity ? m : capacity) : nullptr,
+                                                  m < capacity ? capacity - m : 0);
+        oriented_counts[f] = (int)got;
+        i0 += counts[f];
+        m += got;
+    }
+    const long long stored = m < capacity ? m : capacity;
+    if (stored > 0) {
+        oframe.resize((size_t)stored);
+        long long j = 0;
+        for (int f = 0; f < pyr->n_frames && j < stored; ++f)
+            for (int c = 0; c < oriented_counts[f] && j < stored; ++c) oframe[(size_t)j++] = f;
+        VS_TRY(run_sift(ctx, pyr, 0, -1, oriented, oframe.data(), (int)stored, descriptors, valid));
+    }
+    return m > capacity ? VSLAM_E_CAPACITY : VSLAM_OK;
 }
 
 int vslam_write_descriptor_file(const char *path, const float *descriptors, int n) {

@@ -26,18 +26,35 @@ size_t orient_smem_bytes(int r) {
 // The window is Rect(x, y, 16, 16) of the level's maps replicate-padded by 8 (:318-320, :341-343).  The blur of that ROI
 // reads the padded parent around it and reflects (101) at the parent's edges, so source row q of the (16 + 2r)^2
 // neighbourhood is padded row refl101(y + q - r, rows + 16), i.e. map row clamp(. - 8).
-__global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__restrict__ kp, int n_kp, DescLevels lv, int rows, int cols,
-                                                     size_t pitch, unsigned long long *__restrict__ masks, float *__restrict__ histos) {
+// Resolves a keypoint to its level's Gaussian, map size and tap table; false for points outside the pyramid.
+struct DescSite { const u8 *g; const float *taps; int rows, cols, n; size_t pitch; };
+__device__ __forceinline__ bool desc_site(const DescPyr &P, const vslam_keypoint &k, int frame, DescSite &s) {
+    const int o = P.octave >= 0 ? P.octave : k.octave;
+    if (o < 0 || o >= P.num_octaves || k.level < 0 || k.level >= 6) return false;
+    s.rows = P.orows[o]; s.cols = P.ocols[o]; s.pitch = P.opitch[o];
+    s.n = P.ksize[o][k.level];
+    if (s.n <= 0 || k.row < 0 || k.row >= s.rows || k.col < 0 || k.col >= s.cols) return false;
+    s.g = P.maps + (size_t)frame * P.frame_bytes + P.ooff[o] + P.oplane[o] * (size_t)(1 + k.level);
+    s.taps = P.taps + P.tap_off[o][k.level];
+    return true;
+}
+
+__global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__restrict__ kp, const int *__restrict__ frame_of, int n_kp,
+                                                     const __grid_constant__ DescPyr P, unsigned long long *__restrict__ masks,
+                                                     float *__restrict__ histos) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int t = threadIdx.x;
     const vslam_keypoint k = kp[blockIdx.x];
-    if (k.level < 0 || k.level >= 6 || k.row < 0 || k.row >= rows || k.col < 0 || k.col >= cols) {
+    DescSite site;
+    if (!desc_site(P, k, frame_of ? frame_of[blockIdx.x] : P.frame0, site)) {
         if (t == 0) masks[blockIdx.x] = 0;
         if (histos && t < 36) histos[(size_t)blockIdx.x * 36 + t] = 0.f;
         return;
     }
-    const int n = lv.ksize[k.level], r = n / 2, span = W + 2 * r, SP = stage_stride(r), pad = 8;
-    const u8 *__restrict__ g = lv.gauss[k.level];
+    const int rows = site.rows, cols = site.cols;
+    const size_t pitch = site.pitch;
+    const int n = site.n, r = n / 2, span = W + 2 * r, SP = stage_stride(r), pad = 8;
+    const u8 *__restrict__ g = site.g;
     float *taps = (float *)smem_raw;                               // n
     float *S = taps + n;                                           // 16 x SP staged magnitudes
     float *H = S + W * SP;                                         // span x 16 row-filtered
@@ -45,16 +62,32 @@ __global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__res
     float *hs = wv + 256;                                          // 36 bins
     int *cidx = (int *)(hs + 36);                                  // span source columns
     int *wb = cidx + span;                                         // 256 bin indices
-    for (int i = t; i < n; i += 256) taps[i] = lv.taps[lv.tap_off[k.level] + i];
+    for (int i = t; i < n; i += 256) taps[i] = site.taps[i];
     for (int c = t; c < span; c += 256) cidx[c] = clampi(refl101(k.col + c - r, cols + 2 * pad) - pad, 0, cols - 1);
     __syncthreads();
     const int q = t >> 4, j = t & 15;
     for (int q0 = 0; q0 < span; q0 += W) {
-        for (int idx = t; idx < W * span; idx += 256) {
-            const int qq = idx / span, c = idx - qq * span;
-            if (q0 + qq < span) {
-                const int sy = clampi(refl101(k.row + q0 + qq - r, rows + 2 * pad) - pad, 0, rows - 1);
-                S[qq * SP + c] = mag_at(g, rows, cols, pitch, sy, cidx[c]);
+        // stage 16 source rows of magnitudes: thread (q, j) walks row q in steps of 16 columns, four samples in flight
+        if (q0 + q < span) {
+            const int sy = clampi(refl101(k.row + q0 + q - r, rows + 2 * pad) - pad, 0, rows - 1);
+            const u8 *__restrict__ r0 = g + (size_t)sy * pitch;
+            const u8 *__restrict__ rm = g + (size_t)refl101(sy - 1, rows) * pitch;
+            const u8 *__restrict__ rp = g + (size_t)refl101(sy + 1, rows) * pitch;
+            for (int c0 = j; c0 < span; c0 += 64) {
+                int a[4], b[4], u[4], d[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int c = c0 + 16 * e;
+                    const int sx = cidx[c < span ? c : span - 1];
+                    a[e] = r0[refl101(sx + 1, cols)]; b[e] = r0[refl101(sx - 1, cols)];
+                    d[e] = rp[sx]; u[e] = rm[sx];
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int c = c0 + 16 * e;
+                    const float dx = (float)(a[e] - b[e]), dy = (float)(d[e] - u[e]);
+                    if (c < span) S[q * SP + c] = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+                }
             }
         }
         __syncthreads();
@@ -102,24 +135,27 @@ size_t sift_smem_bytes(int r) { return sizeof(float) * (size_t)(2 * r + 1) + siz
 // rotateImageSection does -- list index i * 16 + j into the 17-wide point list (:545) and at<>(point.x, point.y), x as
 // the row (:549-554).  A sample whose linear address leaves the padded map is undefined in the reference; it is taken
 // from the nearest end of the buffer and the descriptor is flagged invalid.
-__global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__ kp, const float2 *__restrict__ cs, int n_kp, DescLevels lv,
-                                              int rows, int cols, size_t pitch, float *__restrict__ desc, u8 *__restrict__ valid) {
+__global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__ kp, const int *__restrict__ frame_of, const float2 *__restrict__ cs,
+                                              int n_kp, const __grid_constant__ DescPyr P, float *__restrict__ desc, u8 *__restrict__ valid) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ float M[256], Hh[256], Wt[256], D[128], red[4];
     __shared__ int B[256], bad;
     const int t = threadIdx.x, i = t >> 4, j = t & 15;
     const vslam_keypoint k = kp[blockIdx.x];
     float *out = desc + (size_t)blockIdx.x * 128;
-    if (k.level < 0 || k.level >= 6 || k.row < 0 || k.row >= rows || k.col < 0 || k.col >= cols) {
+    DescSite site;
+    if (!desc_site(P, k, frame_of ? frame_of[blockIdx.x] : P.frame0, site)) {
         if (t < 128) out[t] = __int_as_float(0x7fc00000);
         if (t == 0) valid[blockIdx.x] = 0;
         return;
     }
-    const int n = lv.ksize[k.level], r = n / 2, pad = 20;
-    const u8 *__restrict__ g = lv.gauss[k.level];
+    const int rows = site.rows, cols = site.cols;
+    const size_t pitch = site.pitch;
+    const int n = site.n, r = n / 2, pad = 20;
+    const u8 *__restrict__ g = site.g;
     float *taps = (float *)smem_raw;
     int *ridx = (int *)(taps + n);                                 // ridx[c] = refl101(c - r, 16), c in [0, 2r + 16)
-    for (int c = t; c < n; c += 256) taps[c] = lv.taps[lv.tap_off[k.level] + c];
+    for (int c = t; c < n; c += 256) taps[c] = site.taps[c];
     for (int c = t; c < 2 * r + W; c += 256) ridx[c] = refl101(c - r, W);
     if (t == 0) bad = 0;
     __syncthreads();
@@ -181,24 +217,24 @@ __global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__
     if (t == 0) valid[blockIdx.x] = bad ? 0 : 1;
 }
 
-int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, int n, const DescLevels &lv, int max_r, int rows, int cols, size_t pitch,
+int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, int n, const DescPyr &P, int max_r,
                        unsigned long long *masks, float *histos) {
     const size_t smem = orient_smem_bytes(max_r);
     if (smem > 227 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "orientation window blur needs %zu bytes of shared memory (sigma too large)", smem);
     VS_CUDA(ctx, cudaFuncSetAttribute(orient_hist_k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     KernelSpan span(ctx, VSLAM_K_DESCRIPTOR);
-    orient_hist_k<<<n, 256, smem, ctx->stream>>>(kp, n, lv, rows, cols, pitch, masks, histos);
+    orient_hist_k<<<n, 256, smem, ctx->stream>>>(kp, frame_of, n, P, masks, histos);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }
 
-int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const float2 *cs, int n, const DescLevels &lv, int max_r, int rows, int cols,
-                size_t pitch, float *desc, u8 *valid) {
+int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const float2 *cs, int n, const DescPyr &P, int max_r, float *desc,
+                u8 *valid) {
     const size_t smem = sift_smem_bytes(max_r);
     if (smem > 200 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "descriptor window blur needs %zu bytes of shared memory (sigma too large)", smem);
     VS_CUDA(ctx, cudaFuncSetAttribute(sift_k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     KernelSpan span(ctx, VSLAM_K_DESCRIPTOR);
-    sift_k<<<n, 256, smem, ctx->stream>>>(kp, cs, n, lv, rows, cols, pitch, desc, valid);
+    sift_k<<<n, 256, smem, ctx->stream>>>(kp, frame_of, cs, n, P, desc, valid);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

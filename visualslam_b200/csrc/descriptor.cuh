@@ -3,17 +3,26 @@
 #include "common.cuh"
 
 namespace vslam {
-// the six levels of one octave of one frame: u8 Gaussians, and the fp32 blur taps of sigma = 1.5 * getSigmaAt(octave, level)
-struct DescLevels {
-    const u8 *gauss[6];
-    const float *taps;     // the six tap tables back to back
-    int tap_off[6];        // first tap of level l
-    int ksize[6];          // cvRound(sigma * 4 * 2 + 1) | 1
+// Where the kernels find a (frame, octave, level) Gaussian of a device pyramid and the fp32 blur taps of
+// sigma = 1.5 * getSigmaAt(octave, level); passed by value.
+static const int kDescMaxOctaves = 8;
+struct DescPyr {
+    const u8 *maps;                       // vslam_pyramid::maps
+    size_t frame_bytes;
+    size_t ooff[kDescMaxOctaves], oplane[kDescMaxOctaves], opitch[kDescMaxOctaves];
+    int orows[kDescMaxOctaves], ocols[kDescMaxOctaves];
+    int num_octaves;
+    int octave;                           // >= 0: every keypoint is read in this octave (per-octave entry points); -1: its own
+    int frame0;                           // frame of every keypoint when no per-keypoint frame list is given
+    const float *taps;                    // the tap tables back to back
+    int tap_off[kDescMaxOctaves][6];      // first tap of (octave, level)
+    int ksize[kDescMaxOctaves][6];        // cvRound(sigma * 4 * 2 + 1) | 1; 0 = level not prepared
 };
 size_t orient_smem_bytes(int r);
 size_t sift_smem_bytes(int r);
-int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, int n, const DescLevels &lv, int max_r, int rows, int cols, size_t pitch,
+// frame_of: device list of the frame of every keypoint, or nullptr (all in P.frame0)
+int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, int n, const DescPyr &P, int max_r,
                        unsigned long long *masks, float *histos);
-int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const float2 *cs, int n, const DescLevels &lv, int max_r, int rows, int cols,
-                size_t pitch, float *desc, u8 *valid);
+int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const float2 *cs, int n, const DescPyr &P, int max_r, float *desc,
+                u8 *valid);
 }  // namespace vslam

@@ -1,10 +1,12 @@
-// DoG -- the reference's ./DoG executable (KeyPointDetection/Diff_of_Gauss.cpp:725-870) up to the end of the hot path:
-// pyramid (4 octaves, sigma 1.6), per octave initialKeypointDetection + filterKeypoints' edge threshold, with the
-// reference's stdout lines (:784, :786).  Orientation / SIFT descriptors / drawing follow the hot path in the reference
-// and are out of scope; HighGUI is unavailable on this box, so keypoints go to a text file instead.
-//   usage: DoG [image.pgm|image.ppm] [--fused] [--out keypoints.txt]      (default image: ../images/home.pgm, like the reference's
+// DoG -- the reference's ./DoG executable (KeyPointDetection/Diff_of_Gauss.cpp:725-870) without its windows:
+// pyramid (4 octaves, sigma 1.6), per octave initialKeypointDetection + filterKeypoints (edge threshold, orientation
+// assignment) + SIFT, the reference's stdout lines (:784, :786, :815, :834) and featureDescriptors.dat (:837-863).
+// Drawing / HighGUI are unavailable on this box; the keypoint lists go to text files instead.
+//   usage: DoG [image.pgm|image.ppm] [--fused] [--out keypoints.txt] [--oriented oriented.txt] [--desc featureDescriptors.dat]
+//          [--no-descriptors]                                             (default image: ../images/home.pgm, like the reference's
 //   ../images/home.jpg; JPEG decoding is not part of the path -- convert once with any tool)
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <iostream>
 
@@ -14,12 +16,18 @@ using std::cout;
 using std::endl;
 
 int main(int argc, char **argv) {
-    std::string path = "../images/home.pgm", out_path;
-    bool fused = false;
+    std::string path = "../images/home.pgm", out_path, oriented_path, desc_path = "featureDescriptors.dat";
+    bool fused = false, descriptors = true;
     for (int i = 1; i < argc; ++i) {
         if (!strcmp(argv[i], "--fused")) fused = true;
         else if (!strcmp(argv[i], "--out") && i + 1 < argc) out_path = argv[++i];
-        else if (!strcmp(argv[i], "--help")) { printf("usage: DoG [image.pgm|image.ppm] [--fused] [--out keypoints.txt]\n"); return 0; }
+        else if (!strcmp(argv[i], "--oriented") && i + 1 < argc) oriented_path = argv[++i];
+        else if (!strcmp(argv[i], "--desc") && i + 1 < argc) desc_path = argv[++i];
+        else if (!strcmp(argv[i], "--no-descriptors")) descriptors = false;
+        else if (!strcmp(argv[i], "--help")) {
+            printf("usage: DoG [image.pgm|image.ppm] [--fused] [--out keypoints.txt] [--oriented oriented.txt] [--desc featureDescriptors.dat] [--no-descriptors]\n");
+            return 0;
+        }
         else path = argv[i];
     }
     try {
@@ -30,30 +38,57 @@ int main(int argc, char **argv) {
         int numOctaves = 4;          // Diff_of_Gauss.cpp:742
         double pyr_sigma = 1.6;      // :743
         int windowSize = 3;          // :772
-        std::vector<SLAM::point> reducedKeypoints_AllScales;
+        std::vector<SLAM::point> edgeKeypoints_AllScales;        // the hot path's list (after the edge threshold)
+        std::vector<SLAM::point> reducedKeypoints_AllScales;     // :777, after orientation assignment
+        std::vector<std::vector<float>> featureDescriptors_vec;  // :779
         if (fused) {
             // one call, fused kernels: same keypoints, nothing but the list leaves the GPU
-            reducedKeypoints_AllScales = detectKeypoints(img, numOctaves, pyr_sigma, windowSize);
+            edgeKeypoints_AllScales = detectKeypoints(img, numOctaves, pyr_sigma, windowSize);
+            if (descriptors) {
+                GaussPyramid pyramid{img, numOctaves, pyr_sigma};
+                for (int octave = 0; octave < numOctaves; ++octave) {
+                    std::vector<SLAM::point> edgeKeypoints, reducedKeypoints;
+                    for (const auto &k : edgeKeypoints_AllScales)
+                        if (k.octave == octave) edgeKeypoints.emplace_back(k);
+                    assignOrientations(pyramid, octave, edgeKeypoints, reducedKeypoints);
+                    SIFT(reducedKeypoints, featureDescriptors_vec, pyramid, octave);
+                    for (auto &point : reducedKeypoints) reducedKeypoints_AllScales.emplace_back(point);
+                }
+            }
         } else {
             GaussPyramid pyramid{img, numOctaves, pyr_sigma};
             for (const auto &kv : pyramid.pyramidGauss()) {
                 std::vector<SLAM::point> keypoints;
+                std::vector<SLAM::point> edgeKeypoints;
                 std::vector<SLAM::point> reducedKeypoints;
                 int octave = kv.first;
                 cout << "Pyramid octave: " << kv.first << endl;
                 initialKeypointDetection(keypoints, pyramid, octave, windowSize);
                 cout << "image size: width.height (" << kv.second.at(0).cols << ", " << kv.second.at(0).rows << ")" << endl;
-                filterKeypoints(pyramid, octave, keypoints, reducedKeypoints);
-                cout << "keypoints after contrast test: " << keypoints.size() << ", after edge test: " << reducedKeypoints.size() << endl;
-                for (auto &point : reducedKeypoints) reducedKeypoints_AllScales.emplace_back(point);
+                filterKeypointsEdge(pyramid, octave, keypoints, edgeKeypoints);          // filterKeypoints (:787) in its two halves
+                cout << "keypoints after contrast test: " << keypoints.size() << ", after edge test: " << edgeKeypoints.size() << endl;
+                for (auto &point : edgeKeypoints) edgeKeypoints_AllScales.emplace_back(point);
+                if (descriptors) {
+                    assignOrientations(pyramid, octave, edgeKeypoints, reducedKeypoints);
+                    SIFT(reducedKeypoints, featureDescriptors_vec, pyramid, octave);      // :791
+                    for (auto &point : reducedKeypoints) reducedKeypoints_AllScales.emplace_back(point);
+                }
             }
         }
-        cout << "Number of keypoints after edge response: " << reducedKeypoints_AllScales.size() << endl;
-        if (!out_path.empty()) {
-            FILE *f = fopen(out_path.c_str(), "w");
-            if (!f) { fprintf(stderr, "cannot write %s\n", out_path.c_str()); return 1; }
-            for (const auto &k : reducedKeypoints_AllScales) fprintf(f, "%d %d %d %d %d %d\n", k.row, k.col, k.value, k.padding, k.octave, k.level);
+        cout << "Number of keypoints after edge response: " << edgeKeypoints_AllScales.size() << endl;
+        auto dump = [](const std::string &p, const std::vector<SLAM::point> &list) {
+            FILE *f = fopen(p.c_str(), "w");
+            if (!f) { fprintf(stderr, "cannot write %s\n", p.c_str()); return false; }
+            for (const auto &k : list) fprintf(f, "%d %d %d %d %d %d\n", k.row, k.col, k.value, k.padding, k.octave, k.level);
             fclose(f);
+            return true;
+        };
+        if (!out_path.empty() && !dump(out_path, edgeKeypoints_AllScales)) return 1;
+        if (descriptors) {
+            cout << "Number of features found in image: " << featureDescriptors_vec.size() << endl;                         // :815
+            std::cout << "Number of keypoints after edge orientation: " << reducedKeypoints_AllScales.size() << std::endl;   // :834
+            if (!oriented_path.empty() && !dump(oriented_path, reducedKeypoints_AllScales)) return 1;
+            if (!writeFeatureDescriptors(desc_path, featureDescriptors_vec)) return EXIT_FAILURE;                           // :837-863
         }
     } catch (const std::exception &e) {
         fprintf(stderr, "DoG: %s\n", e.what());

@@ -62,8 +62,8 @@ void initialKeypointDetection(std::vector<SLAM::point> &keypoints, GaussPyramid 
         keypoints.emplace_back(buf[i].row, buf[i].col, buf[i].value, buf[i].padding, buf[i].octave, buf[i].level);
 }
 
-// Diff_of_Gauss.cpp:301-338: computeEdgeResponse on the level's gradients, keep response < (r + 1)^2 / r, r = 10
-void filterKeypoints(GaussPyramid &pyramid, int octave, std::vector<SLAM::point> &keypoints, std::vector<SLAM::point> &reducedKeypoints) {
+// Diff_of_Gauss.cpp:326-338: computeEdgeResponse on the level's gradients, keep response < (r + 1)^2 / r, r = 10 (end of the hot path)
+void filterKeypointsEdge(GaussPyramid &pyramid, int octave, std::vector<SLAM::point> &keypoints, std::vector<SLAM::point> &edgeKeypoints) {
     if (keypoints.empty()) return;
     std::vector<float> resp(keypoints.size());
     throw_on(vslam_edge_responses(host_context(), pyramid.devicePyramid(), 0, octave, reinterpret_cast<const vslam_keypoint *>(keypoints.data()),
@@ -72,7 +72,53 @@ void filterKeypoints(GaussPyramid &pyramid, int octave, std::vector<SLAM::point>
     const float r = 10.0f;
     const float threshold = ((r + 1.0f) * (r + 1.0f)) / r;
     for (size_t i = 0; i < keypoints.size(); ++i)
-        if (resp[i] < threshold) reducedKeypoints.emplace_back(keypoints[i]);
+        if (resp[i] < threshold) edgeKeypoints.emplace_back(keypoints[i]);
+}
+
+// Diff_of_Gauss.cpp:340-369: 16x16 window, Gaussian-weighted magnitudes, 36-bin histogram, one point per bin above 0.8 of the peak
+void assignOrientations(GaussPyramid &pyramid, int octave, const std::vector<SLAM::point> &edgeKeypoints, std::vector<SLAM::point> &reducedKeypoints) {
+    if (edgeKeypoints.empty()) return;
+    std::vector<vslam_keypoint> buf(edgeKeypoints.size() * 36);
+    int count = 0;
+    throw_on(vslam_assign_orientations(host_context(), pyramid.devicePyramid(), 0, octave, reinterpret_cast<const vslam_keypoint *>(edgeKeypoints.data()),
+                                       (int)edgeKeypoints.size(), buf.data(), (int)buf.size(), &count, nullptr),
+             "vslam_assign_orientations");
+    reducedKeypoints.reserve(reducedKeypoints.size() + (size_t)count);
+    for (int i = 0; i < count; ++i)
+        reducedKeypoints.emplace_back(buf[i].row, buf[i].col, buf[i].value, buf[i].padding, buf[i].octave, buf[i].level);
+}
+
+// Diff_of_Gauss.cpp:301-369, the whole function: edge threshold, then orientation assignment
+void filterKeypoints(GaussPyramid &pyramid, int octave, std::vector<SLAM::point> &keypoints, std::vector<SLAM::point> &reducedKeypoints) {
+    std::vector<SLAM::point> edgeKeypoints;
+    filterKeypointsEdge(pyramid, octave, keypoints, edgeKeypoints);
+    assignOrientations(pyramid, octave, edgeKeypoints, reducedKeypoints);
+}
+
+// Diff_of_Gauss.cpp:561-693: one 128-vector per oriented keypoint, appended to featureDescriptors_vec
+void SIFT(std::vector<SLAM::point> &reducedKeypoints, std::vector<std::vector<float>> &featureDescriptors_vec, GaussPyramid &pyramid, int octave,
+          std::vector<uint8_t> *valid) {
+    if (reducedKeypoints.empty()) return;
+    const size_t n = reducedKeypoints.size();
+    std::vector<float> desc(n * 128);
+    std::vector<uint8_t> ok(n);
+    throw_on(vslam_sift_descriptors(host_context(), pyramid.devicePyramid(), 0, octave, reinterpret_cast<const vslam_keypoint *>(reducedKeypoints.data()),
+                                    (int)n, desc.data(), ok.data()),
+             "vslam_sift_descriptors");
+    featureDescriptors_vec.reserve(featureDescriptors_vec.size() + n);
+    for (size_t i = 0; i < n; ++i) featureDescriptors_vec.emplace_back(desc.begin() + i * 128, desc.begin() + (i + 1) * 128);
+    if (valid) valid->insert(valid->end(), ok.begin(), ok.end());
+}
+
+// Diff_of_Gauss.cpp:837-863
+bool writeFeatureDescriptors(const std::string &file_name, const std::vector<std::vector<float>> &featureDescriptors_vec) {
+    std::vector<float> flat;
+    flat.reserve(featureDescriptors_vec.size() * 128);
+    for (const auto &d : featureDescriptors_vec) {
+        if (d.size() != 128) throw std::invalid_argument("writeFeatureDescriptors: 128 values per descriptor");
+        flat.insert(flat.end(), d.begin(), d.end());
+    }
+    return vslam_write_descriptor_file(file_name.c_str(), flat.data(), (int)featureDescriptors_vec.size()) == VSLAM_OK;
 }
 
 std::vector<SLAM::point> detectKeypoints(Mat &img, int numOctaves, double sigma, int windowSize) {

@@ -4,6 +4,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 
 #include "descriptor.cuh"
@@ -1042,14 +1043,31 @@ static int run_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame,
     DescPyr P;
     int max_r = 0;
     VS_TRY(desc_pyr(ctx, pyr, frame, octave, kp, n, h_taps, P, max_r));
-    const size_t b[5] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, histograms ? 144 * (size_t)n : 0, 4 * h_taps.size(), frame_of ? 4 * (size_t)n : 0};
-    u8 *d[5];
-    VS_TRY(stage_scratch(ctx, b, 5, d));
+    // CTAs run widest kernel first (coarse octaves: up to 309 taps at octave 3 of the default pyramid), so that the long ones
+    // do not form the tail of the launch; the narrow ones follow in list order
+    std::vector<std::pair<int, int>> heavy;                                // (-r, index)
+    std::vector<int> order, light;
+    order.reserve((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        const int o = octave >= 0 ? octave : kp[i].octave;
+        const int ks = (o >= 0 && o < pyr->num_octaves && kp[i].level >= 0 && kp[i].level < 6) ? P.ksize[o][kp[i].level] : 1;
+        if (ks / 2 > 40) heavy.emplace_back(-(ks / 2), i);
+        else light.push_back(i);
+    }
+    std::sort(heavy.begin(), heavy.end());
+    for (const auto &h : heavy) order.push_back(h.second);
+    order.insert(order.end(), light.begin(), light.end());
+    const size_t b[6] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, histograms ? 144 * (size_t)n : 0, 4 * h_taps.size(), frame_of ? 4 * (size_t)n : 0,
+                         4 * (size_t)n};
+    u8 *d[6];
+    VS_TRY(stage_scratch(ctx, b, 6, d));
     H2D(d[0], kp, b[0]);
     H2D(d[3], h_taps.data(), b[3]);
     if (frame_of) H2D(d[4], frame_of, b[4]);
+    H2D(d[5], order.data(), b[5]);
     P.taps = (const float *)d[3];
-    VS_TRY(launch_orient_hist(ctx, (const vslam_keypoint *)d[0], frame_of ? (const int *)d[4] : nullptr, n, P, max_r, (unsigned long long *)d[1],
+    const int *d_frame = frame_of ? (const int *)d[4] : nullptr;
+    VS_TRY(launch_orient_hist(ctx, (const vslam_keypoint *)d[0], d_frame, (const int *)d[5], n, P, max_r, (unsigned long long *)d[1],
                               histograms ? (float *)d[2] : nullptr));
     masks.resize((size_t)n);
     D2H(masks.data(), d[1], b[1]);

@@ -18,9 +18,32 @@ __host__ __device__ __forceinline__ int stage_stride(int r) {     // floats per 
     return ((need + 15) / 32) * 32 + 16;
 }
 
+// One output of OpenCV's RowFilter: taps left to right over n consecutive samples, one fused multiply-add each.  The tap
+// table starts 16-byte aligned, so four taps arrive per shared-memory load.
+__device__ __forceinline__ float row_chain(const float *__restrict__ taps, const float *__restrict__ s, int n) {
+    float a = __fmul_rn(taps[0], s[0]);
+    int u = 1;
+    for (; u < 4 && u < n; ++u) a = __fmaf_rn(taps[u], s[u], a);
+    for (; u + 3 < n; u += 4) {
+        const float4 t = *reinterpret_cast<const float4 *>(taps + u);
+        a = __fmaf_rn(t.x, s[u], a);
+        a = __fmaf_rn(t.y, s[u + 1], a);
+        a = __fmaf_rn(t.z, s[u + 2], a);
+        a = __fmaf_rn(t.w, s[u + 3], a);
+    }
+    for (; u < n; ++u) a = __fmaf_rn(taps[u], s[u], a);
+    return a;
+}
+// One output of SymmColumnFilter: centre tap, then the symmetric pairs; h points at the centre row, rows are `stride` apart.
+__device__ __forceinline__ float col_chain(const float *__restrict__ taps, const float *__restrict__ h, int r, int stride) {
+    float a = __fmul_rn(taps[r], h[0]);
+    for (int v = 1; v <= r; ++v) a = __fmaf_rn(taps[r + v], __fadd_rn(h[v * stride], h[-v * stride]), a);
+    return a;
+}
+
 size_t orient_smem_bytes(int r) {
     const int n = 2 * r + 1, span = W + 2 * r;
-    return sizeof(float) * ((size_t)n + (size_t)W * stage_stride(r) + (size_t)span * W + 256 + 36) + sizeof(int) * ((size_t)span + 256);
+    return sizeof(float) * ((size_t)((n + 3) & ~3) + (size_t)W * stage_stride(r) + (size_t)span * W + 256 + 36) + sizeof(int) * (3 * (size_t)span + 256);
 }
 
 // The window is Rect(x, y, 16, 16) of the level's maps replicate-padded by 8 (:318-320, :341-343).  The blur of that ROI
@@ -39,16 +62,18 @@ __device__ __forceinline__ bool desc_site(const DescPyr &P, const vslam_keypoint
     return true;
 }
 
-__global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__restrict__ kp, const int *__restrict__ frame_of, int n_kp,
-                                                     const __grid_constant__ DescPyr P, unsigned long long *__restrict__ masks,
-                                                     float *__restrict__ histos) {
+// order: the keypoints this launch works on (widest kernels first), or nullptr for all of them in list order.
+__global__ void __launch_bounds__(256, 4) orient_hist_k(const vslam_keypoint *__restrict__ kp, const int *__restrict__ frame_of,
+                                                        const int *__restrict__ order, int n_kp, const __grid_constant__ DescPyr P,
+                                                        unsigned long long *__restrict__ masks, float *__restrict__ histos) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int t = threadIdx.x;
-    const vslam_keypoint k = kp[blockIdx.x];
+    const int kid = order ? order[blockIdx.x] : (int)blockIdx.x;
+    const vslam_keypoint k = kp[kid];
     DescSite site;
-    if (!desc_site(P, k, frame_of ? frame_of[blockIdx.x] : P.frame0, site)) {
-        if (t == 0) masks[blockIdx.x] = 0;
-        if (histos && t < 36) histos[(size_t)blockIdx.x * 36 + t] = 0.f;
+    if (!desc_site(P, k, frame_of ? frame_of[kid] : P.frame0, site)) {
+        if (t == 0) masks[kid] = 0;
+        if (histos && t < 36) histos[(size_t)kid * 36 + t] = 0.f;
         return;
     }
     const int rows = site.rows, cols = site.cols;
@@ -56,14 +81,18 @@ __global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__res
     const int n = site.n, r = n / 2, span = W + 2 * r, SP = stage_stride(r), pad = 8;
     const u8 *__restrict__ g = site.g;
     float *taps = (float *)smem_raw;                               // n
-    float *S = taps + n;                                           // 16 x SP staged magnitudes
+    float *S = taps + ((n + 3) & ~3);                              // 16 x SP staged magnitudes
     float *H = S + W * SP;                                         // span x 16 row-filtered
     float *wv = H + span * W;                                      // 256 weighted magnitudes
     float *hs = wv + 256;                                          // 36 bins
     int *cidx = (int *)(hs + 36);                                  // span source columns
-    int *wb = cidx + span;                                         // 256 bin indices
+    int *cpl = cidx + span, *cmi = cpl + span;                     // their reflect-101 neighbours (Sobel ksize 1)
+    int *wb = cmi + span;                                          // 256 bin indices
     for (int i = t; i < n; i += 256) taps[i] = site.taps[i];
-    for (int c = t; c < span; c += 256) cidx[c] = clampi(refl101(k.col + c - r, cols + 2 * pad) - pad, 0, cols - 1);
+    for (int c = t; c < span; c += 256) {
+        const int sx = clampi(refl101(k.col + c - r, cols + 2 * pad) - pad, 0, cols - 1);
+        cidx[c] = sx; cpl[c] = refl101(sx + 1, cols); cmi[c] = refl101(sx - 1, cols);
+    }
     __syncthreads();
     const int q = t >> 4, j = t & 15;
     for (int q0 = 0; q0 < span; q0 += W) {
@@ -78,8 +107,8 @@ __global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__res
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const int c = c0 + 16 * e;
-                    const int sx = cidx[c < span ? c : span - 1];
-                    a[e] = r0[refl101(sx + 1, cols)]; b[e] = r0[refl101(sx - 1, cols)];
+                    const int cc = c < span ? c : span - 1, sx = cidx[cc];
+                    a[e] = r0[cpl[cc]]; b[e] = r0[cmi[cc]];
                     d[e] = rp[sx]; u[e] = rm[sx];
                 }
 #pragma unroll
@@ -92,17 +121,12 @@ __global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__res
         }
         __syncthreads();
         if (q0 + q < span) {
-            const float *s = S + q * SP + j;
-            float a = __fmul_rn(taps[0], s[0]);
-            for (int u = 1; u < n; ++u) a = __fmaf_rn(taps[u], s[u], a);
-            H[(q0 + q) * W + j] = a;
+            H[(q0 + q) * W + j] = row_chain(taps, S + q * SP + j, n);
         }
         __syncthreads();
     }
     {   // column pass for window sample (i, j) = (q, j)
-        const float *h = H + (q + r) * W + j;
-        float a = __fmul_rn(taps[r], h[0]);
-        for (int v = 1; v <= r; ++v) a = __fmaf_rn(taps[r + v], __fadd_rn(h[v * W], h[-v * W]), a);
+        const float a = col_chain(taps, H + (q + r) * W + j, r, W);
         float dx, dy;
         grad_at(g, rows, cols, pitch, clampi(k.row + q - pad, 0, rows - 1), clampi(k.col + j - pad, 0, cols - 1), dx, dy);
         const float coeff = 36.f / 360.0f;                         // :114
@@ -110,12 +134,21 @@ __global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__res
         wb[t] = (int)__fmul_rn(fast_atan2_deg(dy, dx), coeff);     // :125
     }
     __syncthreads();
-    if (t < 36) {                                                  // :128 in the reference's order (rows, then columns)
+    // :128 in the reference's order (rows, then columns): a warp takes bins w, w + 8, ...; a ballot per 32 samples finds
+    // the members of the bin, which are then added one after the other
+    for (int b = t >> 5; b < 36; b += 8) {
         float a = 0.f;
-        for (int i = 0; i < 256; ++i)
-            if (wb[i] == t) a = __fadd_rn(a, wv[i]);
-        hs[t] = a;
-        if (histos) histos[(size_t)blockIdx.x * 36 + t] = a;
+        for (int c = 0; c < 256; c += 32) {
+            unsigned m = __ballot_sync(0xffffffffu, wb[c + (t & 31)] == b);
+            while (m) {
+                a = __fadd_rn(a, wv[c + __ffs(m) - 1]);
+                m &= m - 1;
+            }
+        }
+        if ((t & 31) == 0) {
+            hs[b] = a;
+            if (histos) histos[(size_t)kid * 36 + b] = a;
+        }
     }
     __syncthreads();
     if (t == 0) {
@@ -125,11 +158,11 @@ __global__ void __launch_bounds__(256) orient_hist_k(const vslam_keypoint *__res
         unsigned long long m = 0;
         for (int b = 0; b < 36; ++b)
             if (hs[b] > thr) m |= 1ull << b;
-        masks[blockIdx.x] = m;
+        masks[kid] = m;
     }
 }
 
-size_t sift_smem_bytes(int r) { return sizeof(float) * (size_t)(2 * r + 1) + sizeof(int) * (size_t)(2 * r + W); }
+size_t sift_smem_bytes(int r) { return sizeof(float) * ((size_t)((2 * r + 4) & ~3) + (size_t)W * stage_stride(r)); }
 
 // One oriented keypoint: the 16x16 rotated section of the maps replicate-padded by 20 (:578-580), read the way
 // rotateImageSection does -- list index i * 16 + j into the 17-wide point list (:545) and at<>(point.x, point.y), x as
@@ -153,10 +186,10 @@ __global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__
     const size_t pitch = site.pitch;
     const int n = site.n, r = n / 2, pad = 20;
     const u8 *__restrict__ g = site.g;
+    const int span = W + 2 * r, SP = stage_stride(r);
     float *taps = (float *)smem_raw;
-    int *ridx = (int *)(taps + n);                                 // ridx[c] = refl101(c - r, 16), c in [0, 2r + 16)
+    float *E = taps + ((n + 3) & ~3);                              // the window extended by reflection: 16 x SP, rows then columns
     for (int c = t; c < n; c += 256) taps[c] = site.taps[c];
-    for (int c = t; c < 2 * r + W; c += 256) ridx[c] = refl101(c - r, W);
     if (t == 0) bad = 0;
     __syncthreads();
     {
@@ -176,18 +209,20 @@ __global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__
         B[t] = (int)__fmul_rn(fast_atan2_deg(dy, dx), 8.f / 360.0f);
     }
     __syncthreads();
-    {   // GaussianBlur of the stand-alone 16x16 Mat (:611): reflect-101 on the window itself
-        const float *m = M + i * W;
-        float a = __fmul_rn(taps[0], m[ridx[j]]);
-        for (int u = 1; u < n; ++u) a = __fmaf_rn(taps[u], m[ridx[j + u]], a);
-        Hh[t] = a;
+    // GaussianBlur of the stand-alone 16x16 Mat (:611): reflect-101 on the window itself.  E[i][c] = M[i][refl101(c - r)]
+    for (int idx = t; idx < W * span; idx += 256) {
+        const int y = idx / span, c = idx - y * span;
+        E[y * SP + c] = M[y * W + refl101(c - r, W)];
     }
     __syncthreads();
-    {
-        float a = __fmul_rn(taps[r], Hh[t]);
-        for (int v = 1; v <= r; ++v) a = __fmaf_rn(taps[r + v], __fadd_rn(Hh[ridx[i + v + r] * W + j], Hh[ridx[i - v + r] * W + j]), a);
-        Wt[t] = a;
+    Hh[t] = row_chain(taps, E + i * SP + j, n);
+    __syncthreads();
+    for (int idx = t; idx < W * span; idx += 256) {               // E[j][c] = Hh[refl101(c - r)][j]: columns laid out as rows
+        const int x = idx / span, c = idx - x * span;
+        E[x * SP + c] = Hh[refl101(c - r, W) * W + x];
     }
+    __syncthreads();
+    Wt[j * W + i] = col_chain(taps, E + i * SP + j + r, r, 1);   // this thread: window row j, column i (lanes walk a column)
     __syncthreads();
     if (t < 128) {                                                 // :630-646: cell t / 8 (columns first), bin t % 8
         const int cell = t >> 3, b = t & 7, r0 = 4 * (cell >> 2), c0 = 4 * (cell & 3);
@@ -217,13 +252,13 @@ __global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__
     if (t == 0) valid[blockIdx.x] = bad ? 0 : 1;
 }
 
-int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, int n, const DescPyr &P, int max_r,
+int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const int *order, int n, const DescPyr &P, int max_r,
                        unsigned long long *masks, float *histos) {
     const size_t smem = orient_smem_bytes(max_r);
     if (smem > 227 * 1024) VS_FAIL(ctx, VSLAM_E_INVALID, "orientation window blur needs %zu bytes of shared memory (sigma too large)", smem);
     VS_CUDA(ctx, cudaFuncSetAttribute(orient_hist_k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     KernelSpan span(ctx, VSLAM_K_DESCRIPTOR);
-    orient_hist_k<<<n, 256, smem, ctx->stream>>>(kp, frame_of, n, P, masks, histos);
+    orient_hist_k<<<n, 256, smem, ctx->stream>>>(kp, frame_of, order, n, P, masks, histos);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

@@ -21,7 +21,8 @@ struct DescPyr {
 size_t orient_smem_bytes(int r);
 size_t sift_smem_bytes(int r);
 // frame_of: device list of the frame of every keypoint, or nullptr (all in P.frame0)
-int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, int n, const DescPyr &P, int max_r,
+// order: device list of the n keypoint indices this launch covers (nullptr: keypoints 0..n-1); max_r sizes the shared memory
+int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const int *order, int n, const DescPyr &P, int max_r,
                        unsigned long long *masks, float *histos);
 int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const float2 *cs, int n, const DescPyr &P, int max_r, float *desc,
                 u8 *valid);

@@ -420,3 +420,36 @@ def test_describe_keypoints_batch_vs_oracle(ctx):
     none = ctx.describe_keypoints(pyr, np.zeros((0, 6), np.int32), [0, 0, 0])
     assert none["counts"] == [0, 0, 0] and len(none["oriented"]) == 0
     pyr.close()
+
+
+def test_describe_keypoints_1080p_frame_vs_oracle(ctx):
+    """BASELINE.json's frame size: every keypoint of one 1080p frame (blur radii 12 ... 154) against the oracle, bit for bit."""
+    img = synth.frame(11, 1080, 1920)
+    pyr = ctx.build_pyramid(img, 4, 1.6)
+    det = ctx.dog_detect(pyr, stage_counts=False)
+    res = ctx.describe_keypoints(pyr, det["keypoints"], det["counts"])
+    pyr.close()
+    ori_o, desc_o, valid_o, _ = O.dog_features(img)
+    assert len(ori_o) > 2000 and set(ori_o[:, 4]) == {0, 1, 2, 3}
+    assert np.array_equal(kp_array(res["oriented"]).reshape(-1, 6), ori_o)
+    assert np.array_equal(res["valid"], valid_o)
+    assert same_floats(res["descriptors"], desc_o)
+    d = res["descriptors"][res["valid"].astype(bool)]
+    d = d[~np.isnan(d).any(1)]
+    assert d.min() >= 0.0 and np.all(d.max(1) == 1.0)            # size-independent: renormalised to a unit peak
+
+
+def test_descriptors_five_octaves_other_sigma(ctx):
+    """A deeper pyramid with another sigma: up to 489-tap fp32 kernels at octave 4, several times wider than the 68 x 90 map they blur."""
+    img = synth.frame(9, 540, 720)
+    pyr = ctx.build_pyramid(img, 5, 0.8)
+    opyr = O.build_pyramid(img, 5, 0.8)
+    rows, cols = pyr.octave_size(4)
+    kp = np.array([[y, x, 3, 1, 4, l] for l in (1, 2, 3, 5) for (y, x) in ((0, 0), (rows // 2, cols // 2), (rows - 1, cols - 2))], np.int32)
+    r, h = ctx.assign_orientations(pyr, 4, kp, histograms=True)
+    want = O.assign_orientations(opyr["gauss"][4], opyr["sigma"][4], kp)
+    assert np.array_equal(kp_array(r).reshape(-1, 6), want) and len(want) > 0
+    d, v = ctx.sift_descriptors(pyr, 4, want)
+    wd, wv = O.sift(opyr["gauss"][4], opyr["sigma"][4], want)
+    assert np.array_equal(v, wv) and same_floats(d, wd)
+    pyr.close()

@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256, 4) orient_hist_k(const vslam_keypoint *__
     }
 }
 
-size_t sift_smem_bytes(int r) { return sizeof(float) * ((size_t)((2 * r + 4) & ~3) + (size_t)W * stage_stride(r)); }
+size_t sift_smem_bytes(int r) { return sizeof(float) * ((size_t)((2 * r + 4) & ~3) + (size_t)W * stage_stride(r)) + sizeof(int) * (size_t)(W + 2 * r); }
 
 // One oriented keypoint: the 16x16 rotated section of the maps replicate-padded by 20 (:578-580), read the way
 // rotateImageSection does -- list index i * 16 + j into the 17-wide point list (:545) and at<>(point.x, point.y), x as
@@ -189,7 +189,9 @@ __global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__
     const int span = W + 2 * r, SP = stage_stride(r);
     float *taps = (float *)smem_raw;
     float *E = taps + ((n + 3) & ~3);                              // the window extended by reflection: 16 x SP, rows then columns
+    int *ridx = (int *)(E + W * SP);                               // ridx[c] = refl101(c - r, 16), c in [0, span)
     for (int c = t; c < n; c += 256) taps[c] = site.taps[c];
+    for (int c = t; c < span; c += 256) ridx[c] = refl101(c - r, W);
     if (t == 0) bad = 0;
     __syncthreads();
     {
@@ -210,17 +212,11 @@ __global__ void __launch_bounds__(256) sift_k(const vslam_keypoint *__restrict__
     }
     __syncthreads();
     // GaussianBlur of the stand-alone 16x16 Mat (:611): reflect-101 on the window itself.  E[i][c] = M[i][refl101(c - r)]
-    for (int idx = t; idx < W * span; idx += 256) {
-        const int y = idx / span, c = idx - y * span;
-        E[y * SP + c] = M[y * W + refl101(c - r, W)];
-    }
+    for (int c = j; c < span; c += W) E[i * SP + c] = M[i * W + ridx[c]];
     __syncthreads();
     Hh[t] = row_chain(taps, E + i * SP + j, n);
     __syncthreads();
-    for (int idx = t; idx < W * span; idx += 256) {               // E[j][c] = Hh[refl101(c - r)][j]: columns laid out as rows
-        const int x = idx / span, c = idx - x * span;
-        E[x * SP + c] = Hh[refl101(c - r, W) * W + x];
-    }
+    for (int c = j; c < span; c += W) E[i * SP + c] = Hh[ridx[c] * W + i];   // E[x][c] = Hh[refl101(c - r)][x]: columns laid out as rows
     __syncthreads();
     Wt[j * W + i] = col_chain(taps, E + i * SP + j + r, r, 1);   // this thread: window row j, column i (lanes walk a column)
     __syncthreads();

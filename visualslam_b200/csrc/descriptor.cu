@@ -131,26 +131,32 @@ __global__ void __launch_bounds__(256, 4) orient_hist_k(const vslam_keypoint *__
         grad_at(g, rows, cols, pitch, clampi(k.row + q - pad, 0, rows - 1), clampi(k.col + j - pad, 0, cols - 1), dx, dy);
         const float coeff = 36.f / 360.0f;                         // :114
         wv[t] = a;
-        wb[t] = (int)__fmul_rn(fast_atan2_deg(dy, dx), coeff);     // :125
+        wb[t] = clampi((int)__fmul_rn(fast_atan2_deg(dy, dx), coeff), 0, 35);     // :125 (orientations are < 359.8: always inside)
     }
     __syncthreads();
-    // :128 in the reference's order (rows, then columns): a warp takes bins w, w + 8, ...; a ballot per 32 samples finds
-    // the members of the bin, which are then added one after the other
-    for (int b = t >> 5; b < 36; b += 8) {
-        float a = 0.f;
+    // :128 in the reference's order (rows, then columns): warp 0 walks the eight chunks of 32 samples in order; one match finds
+    // the lanes of a chunk that share a bin, and the lowest lane of each group adds the group's values to the bin one by one
+    if (t < 32) {
+        if (t < 4) hs[32 + t] = 0.f;
+        hs[t] = 0.f;
+        __syncwarp();
         for (int c = 0; c < 256; c += 32) {
-            unsigned m = __ballot_sync(0xffffffffu, wb[c + (t & 31)] == b);
-            while (m) {
-                a = __fadd_rn(a, wv[c + __ffs(m) - 1]);
-                m &= m - 1;
+            const int b = wb[c + t];
+            const float v = wv[c + t];
+            const unsigned grp = __match_any_sync(0xffffffffu, b);
+            const bool leader = (__ffs(grp) - 1) == t;
+            float a = leader ? hs[b] : 0.f;
+            unsigned m = leader ? grp : 0u;
+            while (__any_sync(0xffffffffu, m != 0)) {
+                const float x = __shfl_sync(0xffffffffu, v, m ? __ffs(m) - 1 : t);
+                if (m) { a = __fadd_rn(a, x); m &= m - 1; }
             }
-        }
-        if ((t & 31) == 0) {
-            hs[b] = a;
-            if (histos) histos[(size_t)kid * 36 + b] = a;
+            if (leader) hs[b] = a;
+            __syncwarp();
         }
     }
     __syncthreads();
+    if (histos && t < 36) histos[(size_t)kid * 36 + t] = hs[t];
     if (t == 0) {
         float peak = hs[0];
         for (int b = 1; b < 36; ++b) peak = hs[b] > peak ? hs[b] : peak;

@@ -78,3 +78,31 @@ def test_synthetic_frames_are_deterministic():
     a, b = synth.frame(1, 96, 128), synth.frame(1, 96, 128)
     assert np.array_equal(a, b) and a.dtype == np.uint8 and a.shape == (96, 128)
     assert synth.batch(10, 32, 48).shape == (10, 32, 48)
+
+
+def test_fp32_tap_generator_and_descriptor_file_need_no_gpu(lib, tmp_path):
+    """Host-only entry points of the descriptor stage: the fp32 Gaussian taps (cv::getGaussianKernel(n, sigma, CV_32F)) and
+    the featureDescriptors.dat writer (Diff_of_Gauss.cpp:837-863)."""
+    from oracle import c_oracle as O
+    for o in range(4):
+        for l in range(6):
+            s = 1.5 * api.calculate_sigma(o, l)
+            n = lib.vslam_gauss_ksize_f32(s)
+            assert n == O.lib().vo_gauss_ksize_32f(s) and n % 2 == 1
+            t = api.gauss_taps_f32(s)
+            assert np.array_equal(t, O.gauss_taps_32f(s)) and abs(float(t.astype(np.float64).sum()) - 1.0) < 1e-5
+            assert np.array_equal(t, t[::-1])
+    assert lib.vslam_gauss_ksize_f32(1.5 * api.calculate_sigma(3, 3)) == 309
+    assert lib.vslam_gauss_ksize_f32(0.0) < 0
+    with pytest.raises(api.VslamError):
+        api.gauss_taps_f32(2.0, 8)                                  # even kernel size
+    d = np.arange(3 * 128, dtype=np.float32).reshape(3, 128) / 7
+    p = tmp_path / "featureDescriptors.dat"
+    api.write_descriptor_file(str(p), d)
+    raw = p.read_bytes()
+    assert len(raw) == 12 + 3 * 512 and np.frombuffer(raw[:12], "<i4").tolist() == [3, 128, 24]
+    assert np.array_equal(np.frombuffer(raw[12:], "<f4").reshape(3, 128), d)
+    api.write_descriptor_file(str(p), np.zeros((0, 128), np.float32))
+    assert np.frombuffer(p.read_bytes(), "<i4").tolist() == [0, 128, 24]
+    with pytest.raises(api.VslamError):
+        api.write_descriptor_file(str(tmp_path / "no_such_dir" / "x.dat"), d)

@@ -246,7 +246,7 @@ VSLAM_API int vslam_assign_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr
  * memory outside the image: undefined there; here such samples come from the nearest end of the map). */
 VSLAM_API int vslam_sift_descriptors(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int octave,
                                      const vslam_keypoint *oriented, int n, float *descriptors, uint8_t *valid);
-/* Both stages for every frame of a pyramid in two launches (one CTA per keypoint, all frames and octaves together):
+/* Both stages for every frame of a pyramid in a handful of launches (one CTA per keypoint, all frames and octaves together):
  * keypoints = the hot path's lists of frames 0..n_frames-1 back to back (counts[f] each, every point read in its own
  * .octave); oriented / descriptors / valid receive up to `capacity` points in the same frame order and
  * oriented_counts[f] their number per frame (the totals are reported even when VSLAM_E_CAPACITY is returned). */

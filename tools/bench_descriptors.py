@@ -76,7 +76,7 @@ def main():
            "fp32_peak_GFMA_per_s": 148 * 128 * 1.965, "peak_source": "148 SMs x 128 FMA lanes x 1.965 GHz (MEASURED_PEAKS.json sm_max_mhz)",
            "abi_ms": {k: v * 1e3 for k, v in wall.items()},
            "abi_Mpix_per_s": px / 1e6 / sum(wall.values()),
-           "api": "vslam_describe_keypoints: host keypoint lists in, host oriented lists + descriptors out, two launches for the batch"}
+           "api": "vslam_describe_keypoints: host keypoint lists in, host oriented lists + descriptors out, five launches for the batch"}
     if a.cpu_frames > 0:
         from oracle import c_oracle as O
         t = 0.0

@@ -341,7 +341,7 @@ class Context:
         return desc, valid
 
     def describe_keypoints(self, pyr, keypoints, counts, capacity=None):
-        """Orientation assignment + SIFT for every frame of a pyramid in two launches (vslam_describe_keypoints)."""
+        """Orientation assignment + SIFT for every frame of a pyramid in five launches (vslam_describe_keypoints)."""
         kp = np.ascontiguousarray(keypoints).view(KEYPOINT_DTYPE).reshape(-1)
         assert len(counts) == pyr.n_frames and sum(counts) == kp.shape[0]
         capacity = 36 * max(kp.shape[0], 1) if capacity is None else capacity

@@ -1043,20 +1043,18 @@ static int run_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame,
     DescPyr P;
     int max_r = 0;
     VS_TRY(desc_pyr(ctx, pyr, frame, octave, kp, n, h_taps, P, max_r));
-    // CTAs run widest kernel first (coarse octaves: up to 309 taps at octave 3 of the default pyramid), so that the long ones
-    // do not form the tail of the launch; the narrow ones follow in list order
-    std::vector<std::pair<int, int>> heavy;                                // (-r, index)
-    std::vector<int> order, light;
-    order.reserve((size_t)n);
+    // Keypoints are ordered widest kernel first (up to 309 taps at octave 3 of the default pyramid, 25 at octave 0) and
+    // launched in width classes, each with the shared memory its widest member needs: the narrow classes, which hold most of
+    // the keypoints, then fit many more CTAs per SM than a launch sized for the widest kernel would allow
+    std::vector<std::pair<int, int>> by_r((size_t)n);                      // (-r, index): stable order inside one width
     for (int i = 0; i < n; ++i) {
         const int o = octave >= 0 ? octave : kp[i].octave;
         const int ks = (o >= 0 && o < pyr->num_octaves && kp[i].level >= 0 && kp[i].level < 6) ? P.ksize[o][kp[i].level] : 1;
-        if (ks / 2 > 40) heavy.emplace_back(-(ks / 2), i);
-        else light.push_back(i);
+        by_r[(size_t)i] = {-(ks / 2), i};
     }
-    std::sort(heavy.begin(), heavy.end());
-    for (const auto &h : heavy) order.push_back(h.second);
-    order.insert(order.end(), light.begin(), light.end());
+    std::sort(by_r.begin(), by_r.end());
+    std::vector<int> order((size_t)n);
+    for (int i = 0; i < n; ++i) order[(size_t)i] = by_r[(size_t)i].second;
     const size_t b[6] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, histograms ? 144 * (size_t)n : 0, 4 * h_taps.size(), frame_of ? 4 * (size_t)n : 0,
                          4 * (size_t)n};
     u8 *d[6];
@@ -1067,8 +1065,17 @@ static int run_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame,
     H2D(d[5], order.data(), b[5]);
     P.taps = (const float *)d[3];
     const int *d_frame = frame_of ? (const int *)d[4] : nullptr;
-    VS_TRY(launch_orient_hist(ctx, (const vslam_keypoint *)d[0], d_frame, (const int *)d[5], n, P, max_r, (unsigned long long *)d[1],
-                              histograms ? (float *)d[2] : nullptr));
+    static const int kClassR[] = {80, 40, 20, 0};                          // class c holds the radii above kClassR[c]
+    for (int c = 0, i0 = 0; c < 4 && i0 < n; ++c) {
+        int i1 = i0;
+        while (i1 < n && -by_r[(size_t)i1].first > kClassR[c]) ++i1;
+        if (c == 3) i1 = n;
+        if (i1 > i0)
+            VS_TRY(launch_orient_hist(ctx, (const vslam_keypoint *)d[0], d_frame, (const int *)d[5] + i0, i1 - i0, P, -by_r[(size_t)i0].first,
+                                      (unsigned long long *)d[1], histograms ? (float *)d[2] : nullptr));
+        i0 = i1;
+    }
+    (void)max_r;
     masks.resize((size_t)n);
     D2H(masks.data(), d[1], b[1]);
     if (histograms) D2H(histograms, d[2], b[2]);

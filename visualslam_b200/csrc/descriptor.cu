@@ -63,7 +63,7 @@ __device__ __forceinline__ bool desc_site(const DescPyr &P, const vslam_keypoint
 }
 
 // order: the keypoints this launch works on (widest kernels first), or nullptr for all of them in list order.
-__global__ void __launch_bounds__(256, 4) orient_hist_k(const vslam_keypoint *__restrict__ kp, const int *__restrict__ frame_of,
+__global__ void __launch_bounds__(256, 6) orient_hist_k(const vslam_keypoint *__restrict__ kp, const int *__restrict__ frame_of,
                                                         const int *__restrict__ order, int n_kp, const __grid_constant__ DescPyr P,
                                                         unsigned long long *__restrict__ masks, float *__restrict__ histos) {
     extern __shared__ __align__(16) unsigned char smem_raw[];

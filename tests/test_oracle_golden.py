@@ -224,3 +224,32 @@ def test_oracle_descriptor_known_answers():
     assert ori.tolist() == [[30, 40, 0, 0, 0, 1]]
     d, v = O.sift([ramp] * 6, sig, ori)
     assert v[0] == 1 and set(np.nonzero(d[0])[0]) == set(range(0, 128, 8)) and d[0].max() == 1.0
+
+
+def test_oracle_descriptor_stage_vs_cv2_live_on_a_tiny_pyramid():
+    """Kernels several times wider than the map (octave 2 of a 48 x 64 frame is 24 x 32; up to 155 taps): OpenCV's repeated
+    reflect-101 bouncing, live through cv2 (oracle/cv2_reference.py), against the C restatement."""
+    pytest.importorskip("cv2")
+    from oracle import cv2_reference as R
+    from visualslam_b200 import synth
+    img = synth.frame(5, 48, 64)
+    pyr = O.build_pyramid(img, 3, 1.6)
+    ref = R.build_pyramid(img, 3, 1.6)
+    for o in range(3):
+        rows, cols = pyr["gauss"][o][0].shape
+        pts = [(0, 0), (rows - 1, cols - 1), (rows // 2, cols // 3), (1, cols - 2), (rows - 2, 3)]
+        for l in (1, 2, 3):
+            sig = 1.5 * pyr["sigma"][o][l]
+            kp = np.array([[y, x, 0, 1, o, l] for (y, x) in pts], np.int32)
+            want = R.orientation_histograms(ref["mag"][o][l], ref["orient"][o][l], kp, sig)
+            got = np.stack([O.orientation_histogram(pyr["gauss"][o][l], y, x, sig) for (y, x) in pts], 0)
+            assert np.abs(got - want).max() <= FP32_TOL * max(1.0, float(want.max())), (o, l)
+            ori = O.assign_orientations(pyr["gauss"][o], pyr["sigma"][o], kp)
+            desc, valid = O.sift(pyr["gauss"][o], pyr["sigma"][o], ori)
+            for n, k in enumerate(ori):
+                d, ok = R.sift_descriptor(ref["mag"][o][l], ref["orient"][o][l], int(k[0]), int(k[1]), int(k[2]), sig)
+                assert ok == bool(valid[n]), (o, l, n)
+                if ok:
+                    assert np.array_equal(np.isnan(d), np.isnan(desc[n]))
+                    if not np.isnan(d).any():
+                        assert np.abs(d - desc[n]).max() <= FP32_TOL, (o, l, n)

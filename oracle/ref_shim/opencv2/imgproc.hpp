@@ -1,0 +1,3 @@
+// TEST INFRASTRUCTURE ONLY -- see shim.hpp
+#pragma once
+#include <opencv2/shim.hpp>

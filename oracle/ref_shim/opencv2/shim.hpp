@@ -62,7 +62,11 @@ template <class T> struct Point_ {
     Point_() : x(0), y(0) {}
     Point_(T x_, T y_) : x(x_), y(y_) {}
     template <class U> Point_(const Point_<U> &p) : x((T)p.x), y((T)p.y) {}
+    Point_ &operator-=(const Point_ &o) { x -= o.x; y -= o.y; return *this; }
+    Point_ &operator+=(const Point_ &o) { x += o.x; y += o.y; return *this; }
 };
+template <class T> Point_<T> operator-(const Point_<T> &a, const Point_<T> &b) { return Point_<T>(a.x - b.x, a.y - b.y); }
+template <class T> Point_<T> operator+(const Point_<T> &a, const Point_<T> &b) { return Point_<T>(a.x + b.x, a.y + b.y); }
 typedef Point_<int> Point2i;
 typedef Point_<float> Point2f;
 typedef Point_<double> Point2d;

@@ -112,15 +112,15 @@ def test_dog_keypoints_other_sigma_vs_oracle(ctx, sigma0, octaves):
 
 
 def test_dog_keypoints_kernel_variants_agree(tmp_path):
-    """VSLAM_MMA_STATIC=0 (run-time geometry), VSLAM_MMA_FW=32 (32-column strips for every octave) and VSLAM_FUSED_MMA=0
-    (dp4a/dp2a kernel) give the default kernels' lists."""
+    """VSLAM_UMMA=0 (mma.sync kernel for octaves 0 and 1 instead of the tcgen05 one), VSLAM_MMA_STATIC=0 (run-time geometry),
+    VSLAM_MMA_FW=32 (32-column strips for every octave) and VSLAM_FUSED_MMA=0 (dp4a/dp2a kernel) give the default kernels' lists."""
     import subprocess, sys, os
     code = ("import numpy as np, sys; import visualslam_b200 as vs; from visualslam_b200 import synth;"
             "f = np.stack([synth.frame(i, 540, 960) for i in range(8)], 0); c = vs.Context(0);"
             "r = c.dog_keypoints(f); np.save(sys.argv[1], np.asarray(r['keypoints']))")
     outs = []
-    for i, env in enumerate(({}, {"VSLAM_MMA_STATIC": "0"}, {"VSLAM_FUSED_MMA": "0"}, {"VSLAM_MMA_FW": "32"},
-                             {"VSLAM_MMA_FW": "32", "VSLAM_MMA_STATIC": "0"})):
+    for i, env in enumerate(({}, {"VSLAM_UMMA": "0"}, {"VSLAM_UMMA": "0", "VSLAM_MMA_STATIC": "0"}, {"VSLAM_UMMA": "0", "VSLAM_FUSED_MMA": "0"},
+                             {"VSLAM_UMMA": "0", "VSLAM_MMA_FW": "32"}, {"VSLAM_UMMA": "0", "VSLAM_MMA_FW": "32", "VSLAM_MMA_STATIC": "0"})):
         out = str(tmp_path / f"k{i}.npy")
         root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
         subprocess.check_call([sys.executable, "-c", code, out], env={**os.environ, **env, "PYTHONPATH": root}, timeout=600)

@@ -611,12 +611,13 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
     const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
     // bases-only workspace layout of one frame; every row carries the reflect-101 margins its octave's kernel stages from
     size_t boff[16], bpitch[16], bbytes = 0;
-    int bpad[16];
+    int bpad[16], brp[16];
     for (int o = 0; o < g.num_octaves; ++o) {
         bpad[o] = octave_base_pad(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o);
+        brp[o] = octave_base_row_pad(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o);     // tcgen05 kernel: margins above / below too
         bpitch[o] = bpad[o] ? round_up((size_t)g.ocols[o] + 2 * (size_t)bpad[o] + 4, 16) : g.opitch[o];   // + 4: the right margin is written in words
-        boff[o] = bbytes + bpad[o];
-        bbytes += round_up(bpitch[o] * (size_t)g.orows[o] + 256, 256);     // + slack: staging may read past the last row's margin
+        boff[o] = bbytes + (size_t)brp[o] * bpitch[o] + bpad[o];
+        bbytes += round_up(bpitch[o] * (size_t)(g.orows[o] + 2 * brp[o]) + 256, 256);     // + slack: staging may read past the last row's margin
     }
     // segments of one frame: (octave, level 1..3, sample row, strip)
     int seg_base[16], ni[16], nj[16];
@@ -667,8 +668,8 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
             FusedArgs a;
             memset(&a, 0, sizeof a);
             a.taps = h[o];
-            a.base = ws + boff[o]; a.base_pitch = bpitch[o]; a.base_stride = bbytes; a.base_pad = bpad[o];
-            VS_TRY(launch_reflect_pad(ctx, ws + boff[o], g.orows[o], g.ocols[o], bpitch[o], bbytes, bpad[o], nf));
+            a.base = ws + boff[o]; a.base_pitch = bpitch[o]; a.base_stride = bbytes; a.base_pad = bpad[o]; a.base_row_pad = brp[o];
+            VS_TRY(launch_reflect_pad(ctx, ws + boff[o], g.orows[o], g.ocols[o], bpitch[o], bbytes, bpad[o], brp[o], nf));
             a.rows = g.orows[o]; a.cols = g.ocols[o]; a.octave = o;
             if (o + 1 < g.num_octaves) {
                 a.next_base = ws + boff[o + 1]; a.next_pitch = bpitch[o + 1]; a.next_stride = bbytes;
@@ -678,7 +679,8 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
             a.ni = ni[o]; a.nj = nj[o]; a.seg_base = seg_base[o]; a.segs_per_frame = (int)spf;
             a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
             a.cursor = cnt; a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = ctx->staging_entries;
-            const int rc = launch_octave_mma(ctx, a, nf, ctx->taps_sigma0, ctx->taps_scale_samples);   // tensor-pipe blur
+            int rc = launch_octave_umma(ctx, a, nf, ctx->taps_sigma0, ctx->taps_scale_samples);         // tcgen05 + TMA (octaves 0, 1)
+            if (rc == 1) rc = launch_octave_mma(ctx, a, nf, ctx->taps_sigma0, ctx->taps_scale_samples);  // mma.sync blur
             if (rc < 0) return rc;
             if (rc == 1) VS_TRY(launch_octave_fused(ctx, a, nf));                                         // dp4a/dp2a blur
         }

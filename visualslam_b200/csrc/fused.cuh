@@ -31,6 +31,7 @@ struct OctaveIO {
     const u8 *base;                 // octave input
     size_t base_pitch, base_stride;
     int base_pad;                   // columns left and right of every base row that hold its reflect-101 continuation (0: none)
+    int base_row_pad;               // rows above and below the plane that hold its reflect-101 continuation (0: none)
     int rows, cols, octave;
     int n_strips, n_segs, seg_rows; // grid = (strips, vertical segments, frames); seg_rows is a multiple of R
     // next octave's base: level 3 decimated by two (GaussPyramid.cpp:123-126), or nullptr
@@ -74,8 +75,15 @@ int launch_octave_fused(vslam_ctx *ctx, FusedArgs &a, int n_frames);
 int octave_strips(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols);
 // reflect-101 columns the kernel of that octave wants next to every base row (a multiple of 16; 0 for the dp4a/dp2a kernel)
 int octave_base_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);
-// fills them: base[y][-pad .. -1] and base[y][cols .. cols + pad - 1] of every frame
-int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int n_frames);
+// rows above / below the plane the kernel of that octave wants (0 for all but the tcgen05 kernel)
+int octave_base_row_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);
+// fills them: base[y][-pad .. -1] and base[y][cols .. cols + pad - 1] of every frame, then rows -row_pad .. -1 and
+// rows .. rows + row_pad - 1 (whole padded rows, so the corners are reflections in both axes)
+int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames);
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
+// tcgen05 / TMA variant (fused_umma.cu): same contract as launch_octave_mma; takes the octaves whose kernels have at most 63 taps
+int launch_octave_umma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
+bool octave_uses_umma(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);
+int umma_base_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);
 
 }  // namespace vslam

@@ -775,13 +775,19 @@ const uint4 *mma_tab_image(vslam_ctx *ctx, double sigma0, int scale_samples, int
 
 // strips per frame of the kernel that will run the octave (the caller sizes the segment arrays with it)
 int octave_strips(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols) {
+    if (octave_uses_umma(ctx, sigma0, scale_samples, octave)) return (cols + 47) / 48;   // fused_umma.cuh: kUmmaFWO
     MmaTaps mt;
     size_t sm;
     const MmaVariant *v = mma_plan(ctx, sigma0, scale_samples, octave, &mt, &sm);
     return v ? mma_strips(cols, mt.fw) : fused_strips(cols);
 }
 
+int octave_base_row_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave) {
+    return umma_base_pad(ctx, sigma0, scale_samples, octave);
+}
+
 int octave_base_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave) {
+    if (const int up = umma_base_pad(ctx, sigma0, scale_samples, octave)) return up;
     MmaTaps mt;
     size_t sm;
     if (!mma_plan(ctx, sigma0, scale_samples, octave, &mt, &sm)) return 0;
@@ -805,7 +811,21 @@ __global__ void reflect_pad_k(u8 *base, int rows, int cols, size_t pitch, size_t
     }
 }
 
-int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int n_frames) {
+// thread = one 16-byte word of a margin row: row -k copies row refl101(-k), row rows - 1 + k copies row refl101(rows - 1 + k)
+// (whole padded rows; runs after reflect_pad_k)
+__global__ void reflect_pad_rows_k(u8 *base, int rows, size_t pitch, size_t stride, int pad, int row_pad) {
+    u8 *plane = base + (size_t)blockIdx.y * stride;
+    const int wpr = (int)(pitch >> 4), n = 2 * row_pad * wpr;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int j = i / wpr, w = i - j * wpr;
+        const int y = j < row_pad ? j - row_pad : rows + (j - row_pad);
+        const uint4 *src = (const uint4 *)(plane + (ptrdiff_t)refl101(y, rows) * (ptrdiff_t)pitch - pad);
+        uint4 *dst = (uint4 *)(plane + (ptrdiff_t)y * (ptrdiff_t)pitch - pad);
+        dst[w] = src[w];
+    }
+}
+
+int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames) {
     if (pad <= 0) return VSLAM_OK;
     const int wpr = (pad >> 2) + ((cols + pad - (cols & ~3) + 3) >> 2);
     int bx = (rows * wpr + 255) / 256;
@@ -814,6 +834,12 @@ int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitc
     KernelSpan span(ctx, VSLAM_K_PAD);
     reflect_pad_k<<<grid, 256, 0, ctx->stream>>>(base, rows, cols, pitch, stride, pad);
     VS_LAUNCH_CHECK(ctx);
+    if (row_pad > 0) {
+        int by = (int)((2 * row_pad * (pitch >> 4) + 255) / 256);
+        if (by > 64) by = 64;
+        reflect_pad_rows_k<<<dim3(by, n_frames), 256, 0, ctx->stream>>>(base, rows, pitch, stride, pad, row_pad);
+        VS_LAUNCH_CHECK(ctx);
+    }
     return VSLAM_OK;
 }
 

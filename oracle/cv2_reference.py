@@ -167,7 +167,9 @@ def edge_response_numpy(gx: np.ndarray, gy: np.ndarray, rows: np.ndarray, cols: 
     ix2 = np.zeros(rows.shape, f32); iy2 = np.zeros(rows.shape, f32); ixy = np.zeros(rows.shape, f32)
     for du in range(-padding, padding):
         for dv in range(-padding, padding):
-            a = gx[rows + du, cols + dv]; b = gy[rows + du, cols + dv]
+            # padding 1 stays inside the maps; wider windows leave them in the reference (undefined): repeat the border sample
+            uu = np.clip(rows + du, 0, gx.shape[0] - 1); vv = np.clip(cols + dv, 0, gx.shape[1] - 1)
+            a = gx[uu, vv]; b = gy[uu, vv]
             ix2 = (ix2 + (a * a).astype(f32)).astype(f32)
             iy2 = (iy2 + (b * b).astype(f32)).astype(f32)
             ixy = (ixy + (a * b).astype(f32)).astype(f32)

@@ -15,8 +15,11 @@ namespace vslam {
 // computeEdgeResponse on the gradients of Gaussian level g (Sobel ksize=1 of row E formed on the fly)
 __device__ float edge_response(const u8 *__restrict__ g, int rows, int cols, size_t pitch, int y, int x, int pad) {
     float ix2 = 0.f, iy2 = 0.f, ixy = 0.f;
-    for (int u = y - pad; u < y + pad; ++u)
-        for (int v = x - pad; v < x + pad; ++v) {
+    // window 3 never leaves the map; wider windows do in the reference (padded coordinates on an unpadded Mat: undefined
+    // behaviour) -- the defined semantics here: samples outside the map repeat the border sample
+    for (int uu = y - pad; uu < y + pad; ++uu)
+        for (int vv = x - pad; vv < x + pad; ++vv) {
+            const int u = clampi(uu, 0, rows - 1), v = clampi(vv, 0, cols - 1);
             const u8 *row = g + (size_t)u * pitch;
             const float a = (float)((int)row[refl101(v + 1, cols)] - (int)row[refl101(v - 1, cols)]);
             const float b = (float)((int)g[(size_t)refl101(u + 1, rows) * pitch + v] - (int)g[(size_t)refl101(u - 1, rows) * pitch + v]);

@@ -19,10 +19,12 @@
 //            tap[8 j + row + byte - shift], and the no-swizzle K-major descriptor (SBO 128, LBO 256) walks OVERLAPPING core
 //            matrices -- 4.4 KB per level instead of 20 KB.  Reversed rows only permute TMEM lanes / columns.
 //
-// One CTA per SM: a control warp (TMA producer + the single MMA-issuing thread) and eight epilogue warps (TMEM lane
-// quadrant = warp % 4, column half = warp / 4); D_v and D_h are double buffered in TMEM (512 columns), so the tensor pipe
-// works on level l + 1 while the warps drain level l.  The detector, localisation, edge test, ordered emission and
-// decimation are those of fused_mma.cu on a row-major byte tile.
+// One CTA per SM, seventeen warps: a control warp (TMA producer + the single MMA-issuing thread), eight warps that turn D_v
+// into the byte planes X (warps 8..15) and eight that turn D_lo / D_hi into Gaussian / DoG tile rows (warps 0..7); TMEM lane
+// quadrant = warp % 4, column half = (warp / 4) % 2.  D_v, D_h (and X where shared memory allows) are double buffered, so the
+// tensor pipe, the X warps and the tile warps work on three different levels at once; the X warps run two levels ahead
+// across the step boundary.  All sixteen warps share the detector of a finished step.  The detector, localisation, edge
+// test, ordered emission and decimation are those of fused_mma.cu on a row-major byte tile.
 #include <math.h>
 #include <string.h>
 
@@ -40,8 +42,8 @@ using namespace umma;
 
 namespace {
 constexpr int FR = kUmmaRows, FWO = kUmmaFWO, NS = FWO / 3;
-constexpr int kThreads = 288;                   // eight epilogue warps + the control warp
-constexpr int NE = 256;                         // epilogue threads
+constexpr int kThreads = 576;                   // eight tile warps, eight X warps, the control warp, the service warp
+constexpr int NE = 512;                         // threads of the sixteen epilogue warps
 constexpr int TROWS = FR + 4;                   // tile rows: 4 rows of history + the step
 constexpr int TILE_B = TROWS * 64;              // bytes per tile: 64 columns (49 used), 16-byte chunks XOR-swizzled by the row pair
 constexpr int N_G = 3, N_D = 5;                 // G tiles: Gaussian levels 1..3; D tiles: DoG levels 0..4
@@ -80,6 +82,7 @@ int umma_geometry(double sigma0, int scale_samples, int octave, UmmaGeom *g) {
 struct UmmaArgs : OctaveIO {
     const uint4 *tab_image;         // compact Toeplitz tables of the six levels: V tables, then H tables
     int plane_x0, plane_y0;         // coordinates of image pixel (0, 0) inside the TMA tensor (the padded plane)
+    long long *dbg;                 // VSLAM_UMMA_DBG=1: cycle counters of CTA (0, 0, 0) per role (diagnosis only)
 };
 
 namespace {
@@ -93,6 +96,30 @@ __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&v)[4]) {
 // byte offset of pixel (tile row tr, column n) inside a tile
 __device__ __forceinline__ int toff(int tr, int n) { return tr * 64 + ((((n >> 4) ^ (tr >> 1)) & 3) << 4) + (n & 15); }
 
+// computeEdgeResponse + threshold (Diff_of_Gauss.cpp:79-109, :336) on the G tile `gt` of a level around sample (xc, yc).
+// rb = ring row of row y0 - 4 (the tiles are rings of TROWS rows); tile column of image column x is x - X0 + 1.
+// One copy in the kernel (instruction cache): the detector calls it from a single site per level.
+__device__ __noinline__ bool edge_pass_tile(const u8 *gt, int xc, int yc, int y0, int rb, int X0, int rows, int cols, float edge_thr) {
+    int ix2 = 0, iy2 = 0, ixy = 0;
+#pragma unroll
+    for (int u = 0; u <= 1; ++u) {
+        const int yy = yc + u;
+        const int yd = (yy + 1 < rows ? yy + 1 : max(rows - 2, 0)), yu = (yy > 0 ? yy - 1 : min(1, rows - 1));   // reflect-101, single bounce
+        int ty = rb + yy - y0 + 4, tyd = rb + yd - y0 + 4, tyu = rb + yu - y0 + 4;
+        ty -= ty >= TROWS ? TROWS : 0; tyd -= tyd >= TROWS ? TROWS : 0; tyu -= tyu >= TROWS ? TROWS : 0;
+#pragma unroll
+        for (int v = 0; v <= 1; ++v) {
+            const int xx = xc + v;
+            const int xr = (xx + 1 < cols ? xx + 1 : max(cols - 2, 0)), xl = (xx > 0 ? xx - 1 : min(1, cols - 1));
+            const int tx = xx - X0 + 1;
+            const int gxv = (int)gt[toff(ty, xr - X0 + 1)] - (int)gt[toff(ty, xl - X0 + 1)];
+            const int gyv = (int)gt[toff(tyd, tx)] - (int)gt[toff(tyu, tx)];
+            ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
+        }
+    }
+    return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < edge_thr;
+}
+
 }  // namespace
 
 // KV row chunks / KH column chunks / NV staged columns: (5, 3, 80) for kernels up to 31 taps, (6, 4, 112) up to 63 taps
@@ -104,18 +131,21 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
     constexpr int RC = KV + 4;                      // ring chunks: one step's window + the next step's four new chunks
     constexpr int XPB = 2 * KH * 2048;              // bytes of one byte plane: 2 KH K-units of [16 row groups][8 rows][16 bytes]
     constexpr int NP = NV / 16, PMID = (NP + 1) / 2;   // 16-column pieces of D_v: the first PMID go to column half 0
+    constexpr int NFLAG = (3 * MAX_SROW + 31) / 32, NRES = 3 * MAX_SROW * NS;
+    constexpr int QS = 64;                          // queued samples of a step the service warp finishes; the detector threads take the rest
     extern __shared__ __align__(1024) u8 smem_raw[];
     u8 *smem = (u8 *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     u8 *ring = smem;
     u8 *xbuf = ring + RC * 4096;
     u8 *tab = xbuf + XBUF * 2 * XPB;
     u8 *tiles = tab + 6 * (TVB + THB);
-    __shared__ __align__(8) unsigned long long s_bar[12];
+    __shared__ __align__(8) unsigned long long s_bar[17];
     __shared__ uint32_t s_tmem;
-    __shared__ int s_res[3 * MAX_SROW * NS];                  // detector results of one step
-    __shared__ unsigned short s_queue[3 * MAX_SROW * NS];     // samples that need the full localisation
-    __shared__ unsigned int s_flag[(3 * MAX_SROW + 31) / 32]; // segments (sample row, level) of the step with survivors
-    __shared__ int s_nq;
+    // detector results of a step, double buffered: the service warp finishes and emits step s while the others are in s + 1
+    __shared__ short s_res[2][NRES];                          // keypoint value per (sample row, level, sample column), or -1
+    __shared__ uint2 s_queue[NRES];                           // samples that need the full localisation, with their derivatives and edge test
+    __shared__ unsigned int s_flag[2][NFLAG];                 // segments (sample row, level) of the step with survivors
+    __shared__ int s_nq[2];                                   // queue lengths: front (full localisation), back (zero derivative)
     __shared__ float s_div[511];                              // float(i - 255) / 255f, the reference's divisions
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -125,32 +155,47 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
     const int ys = blockIdx.y * a.seg_rows, ye = min(ys + a.seg_rows, rows);
     const int n_steps = (ye - ys + FR - 1) / FR;
 
-    // barriers: [0,1] ring full, [2,3] D_v full, [4,5] D_v free, [6,7] X full, [8,9] D_h full, [10,11] D_h free
-    uint32_t bar[12];
-#pragma unroll
-    for (int i = 0; i < 12; ++i) bar[i] = smem_u32(&s_bar[i]);
+    // barriers: 0,1 ring full; 2,3 D_v full; 4,5 D_v free; 6,7 X full; 8,9 D_h full; 10,11 D_h free; 12,13 detector results
+    // full; 14,15 detector results free; 16 queue free
+    const uint32_t bar0 = smem_u32(&s_bar[0]);
+    auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
     if (tid == 0) {
-        mbar_init(bar[0], 1); mbar_init(bar[1], 1);
-        mbar_init(bar[2], 1); mbar_init(bar[3], 1);
-        mbar_init(bar[4], 8); mbar_init(bar[5], 8);
-        mbar_init(bar[6], 8); mbar_init(bar[7], 8);
-        mbar_init(bar[8], 1); mbar_init(bar[9], 1);
-        mbar_init(bar[10], 8); mbar_init(bar[11], 8);
+        mbar_init(bar(0), 1); mbar_init(bar(1), 1);
+        mbar_init(bar(2), 1); mbar_init(bar(3), 1);
+        mbar_init(bar(4), 8); mbar_init(bar(5), 8);
+        mbar_init(bar(6), 8); mbar_init(bar(7), 8);
+        mbar_init(bar(8), 1); mbar_init(bar(9), 1);
+        mbar_init(bar(10), 8); mbar_init(bar(11), 8);
+        mbar_init(bar(12), 16); mbar_init(bar(13), 16);
+        mbar_init(bar(14), 1); mbar_init(bar(15), 1); mbar_init(bar(16), 1);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(smem_u32(&s_tmem), kTmemCols);
     for (int i = tid; i < 6 * (TVB + THB) / 16; i += kThreads) ((uint4 *)tab)[i] = a.tab_image[i];
     for (int i = tid; i < 511; i += kThreads) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
-    if (tid < (3 * MAX_SROW + 31) / 32) s_flag[tid] = 0;
-    if (tid == 0) s_nq = 0;
+    if (tid < 2 * NFLAG) (&s_flag[0][0])[tid] = 0;
+    if (tid < 2) s_nq[tid] = 0;
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tm = s_tmem;
     // TMEM columns: D_v buffers at 0 / 128, D_h buffers at 256 / 384 (low-byte plane, +64 high-byte plane)
+    // completion count of a per-level barrier pair (index l & 1) at level l of step s: 3 s + (l >> 1)
+#ifdef VSLAM_UMMA_DBG_BUILD                                     // cycle counters of CTA (0, 0, 0): they spill, so a separate build only
+    long long c_wait = 0, c_work = 0, c_det = 0, c_e0 = clock64(), c_d1 = 0, c_d2 = 0, c_d3 = 0, c_d4 = 0;
+#define DBG_T(acc) do { const long long t_ = clock64(); acc += t_ - c_e0; c_e0 = t_; } while (0)
+#define DBG_T2(acc, acc2) do { const long long t_ = clock64(); acc += t_ - c_e0; acc2 += t_ - c_e0; c_e0 = t_; } while (0)
+#define DBG_WAIT(acc, stmt) do { const long long t_ = clock64(); stmt; acc += clock64() - t_; } while (0)
+#define DBG_ONLY(stmt) stmt
+#else
+#define DBG_T(acc) do { } while (0)
+#define DBG_T2(acc, acc2) do { } while (0)
+#define DBG_WAIT(acc, stmt) do { stmt; } while (0)
+#define DBG_ONLY(stmt)
+#endif
 
-    if (warp == 8) {
+    if (warp == 16) {
         // =============================== control: TMA producer + MMA issuer (one thread) ===============================
         if (lane == 0) {
             const int tx = X0 - P + a.plane_x0;                       // first staged column inside the padded plane: multiple of 16
@@ -160,37 +205,38 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             // descriptor halves that never change
             constexpr uint64_t tv_d = smem_desc(0, 256, 128, kLayoutNone), img_d = smem_desc(0, 4096, 1024, kLayoutSw128),
                                x_d = smem_desc(0, 2048, 128, kLayoutNone);
-            mbar_expect_tx(bar[0], KV * 4096);
-            for (int k = 0; k < KV; ++k) tma_load_3d(ring_sa + 4096 * k, &tmap, bar[0], tx, ty + 32 * k, frame);
+            mbar_expect_tx(bar(0), KV * 4096);
+            for (int k = 0; k < KV; ++k) tma_load_3d(ring_sa + 4096 * k, &tmap, bar(0), tx, ty + 32 * k, frame);
+            DBG_ONLY(long long c_xfull = 0; long long c_free = 0;)
             for (int s = 0; s < n_steps; ++s) {
                 if (s + 1 < n_steps) {
                     // the next step's four new chunks replace the four oldest of step s - 1: its last V pass must have completed
-                    if (s > 0) mbar_wait(bar[3], (3 * (s - 1) + 2) & 1);
-                    const uint32_t b = bar[(s + 1) & 1];
+                    if (s > 0) mbar_wait(bar(3), (3 * (s - 1) + 2) & 1);
+                    const uint32_t b = bar((s + 1) & 1);
                     mbar_expect_tx(b, 4 * 4096);
                     for (int j = 0; j < 4; ++j) {
                         const int c = KV + 4 * s + j;
                         tma_load_3d(ring_sa + 4096 * (c % RC), &tmap, b, tx, ty + 32 * c, frame);
                     }
                 }
-                mbar_wait(bar[s & 1], (s >> 1) & 1);
+                mbar_wait(bar(s & 1), (s >> 1) & 1);
                 auto v_pass = [&](int l) {
                     const int n = 3 * s + (l >> 1);                   // use count of this D_v buffer
-                    if (n > 0) mbar_wait(bar[4 + (l & 1)], (n - 1) & 1);
+                    DBG_WAIT(c_free, if (n > 0) mbar_wait(bar(4 + (l & 1)), (n - 1) & 1));
                     tc_fence_after();
 #pragma unroll
                     for (int k = 0; k < KV; ++k) {
                         const uint32_t slot = (uint32_t)((4 * s + k) % RC);
                         mma_i8_ss(tm + 128 * (l & 1), tv_d + ((tab_sa + l * TVB + 512 * k) >> 4), img_d + ((ring_sa + 4096 * slot) >> 4), iv, k > 0);
                     }
-                    mma_commit(bar[2 + (l & 1)]);
+                    mma_commit(bar(2 + (l & 1)));
                 };
                 auto h_pass = [&](int l) {
                     const int xb = XBUF == 2 ? (l & 1) : 0;
                     const int nx = XBUF == 2 ? 3 * s + (l >> 1) : 6 * s + l;
-                    mbar_wait(bar[6 + xb], nx & 1);
+                    DBG_WAIT(c_xfull, mbar_wait(bar(6 + xb), nx & 1));
                     const int n = 3 * s + (l >> 1);
-                    if (n > 0) mbar_wait(bar[10 + (l & 1)], (n - 1) & 1);
+                    DBG_WAIT(c_free, if (n > 0) mbar_wait(bar(10 + (l & 1)), (n - 1) & 1));
                     tc_fence_after();
                     const uint32_t xl = x_sa + xb * 2 * XPB, th = tab_sa + 6 * TVB + l * THB, d = tm + 256 + 128 * (l & 1);
 #pragma unroll
@@ -199,231 +245,63 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
                         mma_i8_ss(d, x_d + ((xl + 4096 * k) >> 4), bd, ih, k > 0);
                         mma_i8_ss(d + 64, x_d + ((xl + XPB + 4096 * k) >> 4), bd, ih, k > 0);
                     }
-                    mma_commit(bar[8 + (l & 1)]);
+                    mma_commit(bar(8 + (l & 1)));
                 };
-                v_pass(0); v_pass(1); h_pass(0); v_pass(2); h_pass(1); v_pass(3); h_pass(2); v_pass(4); h_pass(3); v_pass(5); h_pass(4); h_pass(5);
+                // V0 V1 H0 V2 H1 V3 H2 V4 H3 V5 H4 H5: the V pass stays two levels ahead of the H pass
+#pragma unroll 1
+                for (int i = 0; i < 12; ++i) {
+                    const bool is_v = i < 2 || (i < 10 && (i & 1));
+                    const int l = i < 2 ? i : (i >= 10 ? i - 6 : (is_v ? (i + 1) / 2 : (i - 2) / 2));
+                    if (is_v) v_pass(l);
+                    else h_pass(l);
+                }
             }
+            DBG_ONLY(if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0) { a.dbg[0] = clock64() - c_e0; a.dbg[1] = c_xfull; a.dbg[2] = c_free; a.dbg[5] = n_steps; })
         }
-    } else {
-        // =============================== epilogue warps ===============================
-        const int q = warp & 3, h = warp >> 2;
-        const int mp = 32 * q + lane;                                 // TMEM lane = reversed row of the step
-        const int m = 127 - mp;
-        const uint32_t lane_off = (uint32_t)(32 * q) << 16;
-        const int xoff = mp * 16;                                     // (mp >> 3) * 128 + (mp & 7) * 16
-        const int tr_own = m + 4;                                     // tile row of this thread's output row
-        const int tswz = (tr_own >> 1) & 3;
-        constexpr int DT0 = N_G * TILE_B;                             // byte offset of the first D tile
-        uint32_t prev[18];                                            // previous level, 16-bit halves: 2 pixels per register
-
-        // ---- computeEdgeResponse + threshold on the G tile of `level` around sample (xc, yc); y0 = first row of the step ----
-        auto edge_pass = [&](int level, int xc, int yc, int y0) -> bool {
-            const u8 *gt = tiles + (level - 1) * TILE_B;
-            int ix2 = 0, iy2 = 0, ixy = 0;
-#pragma unroll
-            for (int u = 0; u <= 1; ++u)
-#pragma unroll
-                for (int v = 0; v <= 1; ++v) {
-                    // reflect-101 of an index at most one outside [0, len): a single bounce (len == 1 -> 0)
-                    const int xx = xc + v, yy = yc + u;
-                    const int xr = (xx + 1 < cols ? xx + 1 : max(cols - 2, 0)), xl = (xx > 0 ? xx - 1 : min(1, cols - 1));
-                    const int yd = (yy + 1 < rows ? yy + 1 : max(rows - 2, 0)), yu = (yy > 0 ? yy - 1 : min(1, rows - 1));
-                    const int ty = yy - y0 + 4, tx = xx - X0 + 1;
-                    const int gxv = (int)gt[toff(ty, xr - X0 + 1)] - (int)gt[toff(ty, xl - X0 + 1)];
-                    const int gyv = (int)gt[toff(yd - y0 + 4, tx)] - (int)gt[toff(yu - y0 + 4, tx)];
-                    ix2 += gxv * gxv; iy2 += gyv * gyv; ixy += gxv * gyv;
-                }
-            return edge_from_sums((float)ix2, (float)iy2, (float)ixy) < a.edge_thr;   // Diff_of_Gauss.cpp:336
-        };
-
+    } else if (warp == 17) {
+        // =============================== service warp: queued localisations + ordered emission of a finished step ===============================
+        DBG_ONLY(long long c_q = 0;)
         for (int s = 0; s < n_steps; ++s) {
+            const int b = s & 1;
             const int y0 = ys + FR * s;
-            // ---- EV(l): D_v -> byte planes X (+ the rounding bias of the H pass) ----
-            auto ev = [&](int l) {
-                if (XBUF == 1 && l > 0) mbar_wait(bar[8 + ((l - 1) & 1)], (3 * s + ((l - 1) >> 1)) & 1);   // H(l-1) has read X
-                mbar_wait(bar[2 + (l & 1)], (3 * s + (l >> 1)) & 1);
-                tc_fence_after();
-                const uint32_t tb = tm + 128 * (l & 1) + lane_off;
-                u8 *xl = xbuf + (XBUF == 2 ? (l & 1) : 0) * 2 * XPB + xoff;
-                constexpr int NPH = PMID;                             // pieces of the larger half
-                uint32_t v[NPH][16];
-                const int p0 = h ? PMID : 0, np = h ? NP - PMID : PMID;
-#pragma unroll
-                for (int p = 0; p < NPH; ++p)
-                    if (p < np) tmem_ld16(tb + 16 * (p0 + p), v[p]);
-                tmem_ld_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar[4 + (l & 1)]);         // D_v buffer is free again
-#pragma unroll
-                for (int p = 0; p < NPH; ++p)
-                    if (p < np) {
-                        uint32_t lo[4], hi[4];
-#pragma unroll
-                        for (int w = 0; w < 4; ++w) {
-                            const uint32_t t0 = __byte_perm(v[p][4 * w], v[p][4 * w + 1], 0x5410) + 0x00800080u;
-                            const uint32_t t1 = __byte_perm(v[p][4 * w + 2], v[p][4 * w + 3], 0x5410) + 0x00800080u;
-                            lo[w] = __byte_perm(t0, t1, 0x6420);
-                            hi[w] = __byte_perm(t0, t1, 0x7531);
-                        }
-                        *(uint4 *)(xl + (p0 + p) * 2048) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                        *(uint4 *)(xl + XPB + (p0 + p) * 2048) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                    }
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar[6 + (XBUF == 2 ? (l & 1) : 0)]);
-            };
-            // ---- EH(l): D_lo, D_hi -> Gaussian level l, DoG level l - 1 -> tiles ----
-            // 16 columns n' = c0 .. c0 + 15 of the (column-reversed) accumulators = image columns n = 48 - c0 .. 63 - c0;
-            // pi = index of the piece's first register pair in prev[]
-            auto eh_piece16 = [&](int l, uint32_t dlo, int c0, int pi) {
-                uint32_t lo[16], hi[16];
-                tmem_ld16(dlo + c0, lo);
-                tmem_ld16(dlo + 64 + c0, hi);
-                tmem_ld_wait();
-                uint32_t g2[8], d2[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const uint32_t va = (hi[15 - 2 * j] << 8) + lo[15 - 2 * j], vb = (hi[14 - 2 * j] << 8) + lo[14 - 2 * j];
-                    g2[j] = __byte_perm(va, vb, 0x7632);              // byte 2 of each sum: (256 hi + lo) >> 16, bias included
-                    d2[j] = __vmaxu2(g2[j], prev[pi + j]) - prev[pi + j];   // max(cur - prev, 0), GaussPyramid.cpp:197
-                    prev[pi + j] = g2[j];
+            const int si_lo = ((y0 == 0 ? 0 : y0 - 2) + 2) / 3;
+            mbar_wait(bar(12 + b), (s >> 1) & 1);
+            DBG_T(c_wait);
+            // FeaturePointLocalization's full sequence for the samples whose three derivatives are all non-zero, one lane per
+            // sample; their derivatives and edge tests were taken from the tiles by the detector threads
+            // (the first QS entries; the detector threads took the rest themselves)
+            const int nq_all = s_nq[0], nq = min(nq_all, QS);
+            DBG_ONLY(c_q += nq_all;)
+            for (int e = lane; e < nq; e += 32) {
+                const uint2 qe = s_queue[e];
+                if (!((qe.x >> 16) & 1)) continue;                                           // fails the edge test (:336)
+                const int k = qe.x & 31, level = (qe.x >> 5) & 3, sr = (qe.x >> 8) & 255, c = (qe.x >> 17) & 255;
+                const int dx = (int)(qe.y & 511) - 255, dy = (int)((qe.y >> 9) & 511) - 255, ds = (int)((qe.y >> 18) & 511) - 255;
+                const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
+                if (zhat > a.contrast_thr) {                                                 // Diff_of_Gauss.cpp:245
+                    const int task = sr * 3 + level - 1;
+                    s_res[b][task * NS + k] = (short)(int)__fmul_rn(zhat, 255.0f);           // :246
+                    atomicOr(&s_flag[b][task >> 5], 1u << (task & 31));
                 }
-                const int ch = ((48 - c0) >> 4) ^ tswz;
-                if (l >= 1 && l <= 3)
-                    *(uint4 *)(tiles + (l - 1) * TILE_B + tr_own * 64 + ch * 16) =
-                        make_uint4(__byte_perm(g2[0], g2[1], 0x6420), __byte_perm(g2[2], g2[3], 0x6420), __byte_perm(g2[4], g2[5], 0x6420), __byte_perm(g2[6], g2[7], 0x6420));
-                if (l >= 1)
-                    *(uint4 *)(tiles + DT0 + (l - 1) * TILE_B + tr_own * 64 + ch * 16) =
-                        make_uint4(__byte_perm(d2[0], d2[1], 0x6420), __byte_perm(d2[2], d2[3], 0x6420), __byte_perm(d2[4], d2[5], 0x6420), __byte_perm(d2[6], d2[7], 0x6420));
-            };
-            auto eh = [&](int l) {
-                mbar_wait(bar[8 + (l & 1)], (3 * s + (l >> 1)) & 1);
-                tc_fence_after();
-                const uint32_t dlo = tm + 256 + 128 * (l & 1) + lane_off;
-                if (h) {                                              // columns n = 0 .. 31
-                    eh_piece16(l, dlo, 48, 0);
-                    eh_piece16(l, dlo, 32, 8);
-                } else {                                              // columns n = 32 .. 51 (49 .. 51 are never read)
-                    eh_piece16(l, dlo, 16, 0);
-                    uint32_t lo[4], hi[4];
-                    tmem_ld4(dlo + 12, lo);
-                    tmem_ld4(dlo + 64 + 12, hi);
-                    tmem_ld_wait();
-                    uint32_t g2[2], d2[2];
-#pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        const uint32_t va = (hi[3 - 2 * j] << 8) + lo[3 - 2 * j], vb = (hi[2 - 2 * j] << 8) + lo[2 - 2 * j];
-                        g2[j] = __byte_perm(va, vb, 0x7632);
-                        d2[j] = __vmaxu2(g2[j], prev[8 + j]) - prev[8 + j];
-                        prev[8 + j] = g2[j];
-                    }
-                    const int ch = 3 ^ tswz;
-                    if (l >= 1 && l <= 3) *(uint32_t *)(tiles + (l - 1) * TILE_B + tr_own * 64 + ch * 16) = __byte_perm(g2[0], g2[1], 0x6420);
-                    if (l >= 1) *(uint32_t *)(tiles + DT0 + (l - 1) * TILE_B + tr_own * 64 + ch * 16) = __byte_perm(d2[0], d2[1], 0x6420);
-                }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar[10 + (l & 1)]);        // D_h buffer is free again
-            };
-            ev(0); ev(1); eh(0); ev(2); eh(1); ev(3); eh(2); ev(4); eh(3); ev(5); eh(4); eh(5);
-
-            // ================= detector of the step (rows G, H, I, J), next octave's base, tile history =================
-            named_bar(1, NE);                                         // every warp's tile rows are in place
-            int si_lo = 0, n_srow = 0;
+            }
+            __syncwarp();
+            if (lane == 0) { s_nq[0] = 0; s_nq[1] = 0; mbar_arrive(bar(16)); }   // the queue may be refilled
+            // ordered emission: flagged segments (level, sample row, strip) get consecutive staging ranges behind ONE atomic per step
             if (a.detect) {
-                const int yc_lo = y0 == 0 ? 0 : y0 - 2;
-                const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;     // centre row yc needs rows up to yc + 2
-                si_lo = (yc_lo + 2) / 3;
-                n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
-                if (n_srow < 0) n_srow = 0;
-                // ---- 4a. thread = one grid position (sample column k, sample row sr) for the three levels ----
-                for (int e = tid; e < n_srow * NS; e += NE) {
-                    const int k = e % NS, sr = e / NS;
-                    const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
-                    int res[3] = {-1, -1, -1};
-                    if (xc <= cols - 2) {
-                        // D tiles at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
-                        const int ty = yc - y0 + 4, tx = 3 * k + 1;
-                        const int tym = yc > 0 ? ty - 1 : ty, typ = yc + 1 < rows ? ty + 1 : ty;
-                        const int txm = xc > 0 ? tx - 1 : tx, txp = xc + 1 < cols ? tx + 1 : tx;
-                        const int o00 = toff(tym, txm), o01 = toff(tym, tx), o10 = toff(ty, txm), o11 = toff(ty, tx);
-                        const u8 *d = tiles + DT0;
-                        int w01[5], w10[5], w11[5], mn[5], mx[5];
-#pragma unroll
-                        for (int l = 0; l < 5; ++l) {
-                            const int w00 = d[l * TILE_B + o00];
-                            w01[l] = d[l * TILE_B + o01]; w10[l] = d[l * TILE_B + o10]; w11[l] = d[l * TILE_B + o11];
-                            mn[l] = min(min(w00, w01[l]), min(w10[l], w11[l]));
-                            mx[l] = max(max(w00, w01[l]), max(w10[l], w11[l]));
-                        }
-#pragma unroll
-                        for (int level = 1; level <= 3; ++level) {
-                            const int c = w11[level];
-                            const int lo3 = min(min(mn[level - 1], mn[level]), mn[level + 1]);
-                            const int hi3 = max(max(mx[level - 1], mx[level]), mx[level + 1]);
-                            if (c == lo3 || c == hi3) {                                          // Diff_of_Gauss.cpp:287
-                                const int dx = w10[level] - (int)d[level * TILE_B + toff(ty, txp)];   // :226-228
-                                const int dy = w01[level] - (int)d[level * TILE_B + toff(typ, tx)];
-                                const int ds = w11[level - 1] - w11[level + 1];
-                                if (dx == 0 || dy == 0 || ds == 0) {
-                                    // cv::invert of the singular A*A^T gives zeros: dog_zhat = value/255 (a.cmin, a.val_lut: the
-                                    // same float ops, tabulated on the host)
-                                    if (c >= a.cmin && edge_pass(level, xc, yc, y0)) {
-                                        res[level - 1] = a.val_lut[c];
-                                        atomicOr(&s_flag[(sr * 3 + level - 1) >> 5], 1u << ((sr * 3 + level - 1) & 31));
-                                    }
-                                } else {
-                                    s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)(k | level << 5 | sr << 8);
-                                }
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int level = 1; level <= 3; ++level) s_res[(sr * 3 + level - 1) * NS + k] = res[level - 1];
-                }
-            }
-            named_bar(1, NE);
-            // ---- queued samples: FeaturePointLocalization's full sequence, one thread per sample ----
-            {
-                const int nq = s_nq;
-                for (int e = tid; e < nq; e += NE) {
-                    const int code = s_queue[e];                                             // k | level << 5 | sample row << 8
-                    const int k = code & 31, level = (code >> 5) & 3, sr = code >> 8;
-                    const int yc = 3 * (si_lo + sr), xc = X0 + 3 * k;
-                    const u8 *d = tiles + DT0 + level * TILE_B;
-                    const int ty = yc - y0 + 4, tx = 3 * k + 1;
-                    const int tym = yc > 0 ? ty - 1 : ty, typ = yc + 1 < rows ? ty + 1 : ty;
-                    const int txm = xc > 0 ? tx - 1 : tx, txp = xc + 1 < cols ? tx + 1 : tx;
-                    const int c = d[toff(ty, tx)];
-                    const int dx = (int)d[toff(ty, txm)] - (int)d[toff(ty, txp)], dy = (int)d[toff(tym, tx)] - (int)d[toff(typ, tx)];
-                    const int ds = (int)d[toff(ty, tx) - TILE_B] - (int)d[toff(ty, tx) + TILE_B];
-                    const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
-                    if (zhat > a.contrast_thr && edge_pass(level, xc, yc, y0)) {             // :245
-                        const int task = sr * 3 + level - 1;
-                        s_res[task * NS + k] = (int)__fmul_rn(zhat, 255.0f);                 // :246
-                        atomicOr(&s_flag[task >> 5], 1u << (task & 31));
-                    }
-                }
-            }
-            named_bar(1, NE);
-            // ---- ordered emission (warp 0): flagged segments (level, sample row, strip) get consecutive staging ranges
-            // behind ONE atomic per step ----
-            if (warp == 0 && a.detect) {
                 int total = 0;
-                for (int wd = 0; wd < (3 * MAX_SROW + 31) / 32; ++wd)
-                    for (unsigned mk = s_flag[wd]; mk; mk &= mk - 1) {
+                for (int wd = 0; wd < NFLAG; ++wd)
+                    for (unsigned mk = s_flag[b][wd]; mk; mk &= mk - 1) {
                         const int task = 32 * wd + __ffs((int)mk) - 1;
-                        const int res = lane < NS ? s_res[task * NS + lane] : -1;
+                        const int res = lane < NS ? s_res[b][task * NS + lane] : -1;
                         total += __popc(__ballot_sync(0xffffffffu, res >= 0));
                     }
                 int off = 0;
                 if (lane == 0 && total) off = atomicAdd(a.cursor, total);
                 off = __shfl_sync(0xffffffffu, off, 0);
-                for (int wd = 0; wd < (3 * MAX_SROW + 31) / 32; ++wd)
-                    for (unsigned mk = s_flag[wd]; mk; mk &= mk - 1) {
+                for (int wd = 0; wd < NFLAG; ++wd)
+                    for (unsigned mk = s_flag[b][wd]; mk; mk &= mk - 1) {
                         const int task = 32 * wd + __ffs((int)mk) - 1;
-                        const int res = lane < NS ? s_res[task * NS + lane] : -1;
+                        const int res = lane < NS ? s_res[b][task * NS + lane] : -1;
                         const unsigned bal = __ballot_sync(0xffffffffu, res >= 0);
                         const int level = 1 + task % 3, si = si_lo + task / 3;
                         const int cnt = __popc(bal);
@@ -444,34 +322,278 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
                         off += cnt;
                     }
             }
-            // ---- next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126); thread = (row, four output columns) ----
-            if (a.next_base) {
-                for (int e = tid; e < (FR / 2) * (FWO / 8); e += NE) {
-                    const int g = e % (FWO / 8), w = e / (FWO / 8);
-                    const int oy = (y0 >> 1) + w, ox = X0 / 2 + 4 * g;
-                    if (oy < a.next_rows && ox < a.next_cols && y0 + 2 * w < ye) {
-                        const u8 *t3 = tiles + 2 * TILE_B;
-                        const int tr = 2 * w + 4;
-                        u8 b[4];
+            __syncwarp();
+            if (lane < NFLAG) s_flag[b][lane] = 0;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(14 + b));
+            DBG_T(c_work);
+        }
+        DBG_ONLY(if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0 && lane == 0) { a.dbg[6] = c_q; a.dbg[7] = c_work; })
+    } else {
+        // =============================== epilogue warps ===============================
+        const int q = warp & 3, h = (warp >> 2) & 1;
+        const bool xgroup = warp >= 8;                                // X warps (D_v -> byte planes) or tile warps (D_h -> tiles)
+        const int mp = 32 * q + lane;                                 // TMEM lane = reversed row of the step
+        const int m = 127 - mp;
+        const uint32_t lane_off = (uint32_t)(32 * q) << 16;
+        constexpr int DT0 = N_G * TILE_B;                             // byte offset of the first D tile
+
+        // ---- EV(s, l): D_v -> byte planes X (+ the rounding bias of the H pass) ----
+        auto ev = [&](int s, int l) {
+            const int n = 3 * s + (l >> 1);
+            if (XBUF == 2) {
+                if (n > 0) mbar_wait(bar(8 + (l & 1)), (n - 1) & 1);  // H(l - 2) has read this X buffer
+            } else if (6 * s + l > 0) {
+                const int lp = l == 0 ? 5 : l - 1, sp = l == 0 ? s - 1 : s;
+                mbar_wait(bar(8 + (lp & 1)), (3 * sp + (lp >> 1)) & 1);   // H(l - 1) has read X
+            }
+            mbar_wait(bar(2 + (l & 1)), n & 1);
+            DBG_T(c_wait);
+            tc_fence_after();
+            const uint32_t tb = tm + 128 * (l & 1) + lane_off;
+            u8 *xl = xbuf + (XBUF == 2 ? (l & 1) : 0) * 2 * XPB + mp * 16;   // (mp >> 3) * 128 + (mp & 7) * 16
+            const int p0 = h ? PMID : 0, np = h ? NP - PMID : PMID;
+            // two 16-column pieces in flight (18 warps leave 96 registers per thread)
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) b[i] = t3[toff(tr, 8 * g + 2 * i + 1)];
-                        u8 *dst = a.next_base + (size_t)frame * a.next_stride + (size_t)oy * a.next_pitch + ox;
-                        if (ox + 3 < a.next_cols) *(uint32_t *)dst = (uint32_t)b[0] | (uint32_t)b[1] << 8 | (uint32_t)b[2] << 16 | (uint32_t)b[3] << 24;
-                        else for (int i = 0; i < 4 && ox + i < a.next_cols; ++i) dst[i] = b[i];
+            for (int pp = 0; pp < PMID; pp += 2) {
+                uint32_t v[2][16];
+#pragma unroll
+                for (int p = 0; p < 2; ++p)
+                    if (pp + p < np) tmem_ld16(tb + 16 * (p0 + pp + p), v[p]);
+                tmem_ld_wait();
+                if (pp + 2 >= PMID) {                                 // last loads of the level: the D_v buffer is free again
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar(4 + (l & 1)));
+                }
+#pragma unroll
+                for (int p = 0; p < 2; ++p)
+                    if (pp + p < np) {
+                        uint32_t lo[4], hi[4];
+#pragma unroll
+                        for (int w = 0; w < 4; ++w) {
+                            const uint32_t t0 = __byte_perm(v[p][4 * w], v[p][4 * w + 1], 0x5410) + 0x00800080u;
+                            const uint32_t t1 = __byte_perm(v[p][4 * w + 2], v[p][4 * w + 3], 0x5410) + 0x00800080u;
+                            lo[w] = __byte_perm(t0, t1, 0x6420);
+                            hi[w] = __byte_perm(t0, t1, 0x7531);
+                        }
+                        *(uint4 *)(xl + (p0 + pp + p) * 2048) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                        *(uint4 *)(xl + XPB + (p0 + pp + p) * 2048) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                     }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(6 + (XBUF == 2 ? (l & 1) : 0)));
+            DBG_T(c_work);
+        };
+
+        // ---- EH(s, l): D_lo, D_hi -> Gaussian level l, DoG level l - 1 -> tiles ----
+        // The tiles are rings of TROWS = 132 rows: row y of step s sits at ring row (128 s + (y - y0) + 4) mod 132, so the
+        // last four rows of step s - 1 are the four rows in front of step s without a copy
+        u8 *trow = tiles;
+        int tswz = 0;
+        uint32_t prev[18];                                            // previous level, 16-bit halves: 2 pixels per register
+        // 16 columns n' = c0 .. c0 + 15 of the (column-reversed) accumulators = image columns n = 48 - c0 .. 63 - c0;
+        // pi = index of the piece's first register pair in prev[]
+        auto eh_piece16 = [&](int l, uint32_t dlo, int c0, int pi) {
+            uint32_t lo[16], hi[16];
+            tmem_ld16(dlo + c0, lo);
+            tmem_ld16(dlo + 64 + c0, hi);
+            tmem_ld_wait();
+            uint32_t g2[8], d2[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t va = (hi[15 - 2 * j] << 8) + lo[15 - 2 * j], vb = (hi[14 - 2 * j] << 8) + lo[14 - 2 * j];
+                g2[j] = __byte_perm(va, vb, 0x7632);                  // byte 2 of each sum: (256 hi + lo) >> 16, bias included
+                d2[j] = __vmaxu2(g2[j], prev[pi + j]) - prev[pi + j];   // max(cur - prev, 0), GaussPyramid.cpp:197
+                prev[pi + j] = g2[j];
+            }
+            const int ch = (((48 - c0) >> 4) ^ tswz) * 16;
+            if (l >= 1 && l <= 3)
+                *(uint4 *)(trow + (l - 1) * TILE_B + ch) =
+                    make_uint4(__byte_perm(g2[0], g2[1], 0x6420), __byte_perm(g2[2], g2[3], 0x6420), __byte_perm(g2[4], g2[5], 0x6420), __byte_perm(g2[6], g2[7], 0x6420));
+            if (l >= 1)
+                *(uint4 *)(trow + DT0 + (l - 1) * TILE_B + ch) =
+                    make_uint4(__byte_perm(d2[0], d2[1], 0x6420), __byte_perm(d2[2], d2[3], 0x6420), __byte_perm(d2[4], d2[5], 0x6420), __byte_perm(d2[6], d2[7], 0x6420));
+        };
+        auto eh = [&](int s, int l) {
+            mbar_wait(bar(8 + (l & 1)), (3 * s + (l >> 1)) & 1);
+            DBG_T(c_wait);
+            tc_fence_after();
+            const uint32_t dlo = tm + 256 + 128 * (l & 1) + lane_off;
+            if (h) {                                                  // columns n = 0 .. 31
+                eh_piece16(l, dlo, 48, 0);
+                eh_piece16(l, dlo, 32, 8);
+            } else {                                                  // columns n = 32 .. 51 (49 .. 51 are never read)
+                eh_piece16(l, dlo, 16, 0);
+                uint32_t lo[4], hi[4];
+                tmem_ld4(dlo + 12, lo);
+                tmem_ld4(dlo + 64 + 12, hi);
+                tmem_ld_wait();
+                uint32_t g2[2], d2[2];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const uint32_t va = (hi[3 - 2 * j] << 8) + lo[3 - 2 * j], vb = (hi[2 - 2 * j] << 8) + lo[2 - 2 * j];
+                    g2[j] = __byte_perm(va, vb, 0x7632);
+                    d2[j] = __vmaxu2(g2[j], prev[8 + j]) - prev[8 + j];
+                    prev[8 + j] = g2[j];
+                }
+                const int ch = (3 ^ tswz) * 16;
+                if (l >= 1 && l <= 3) *(uint32_t *)(trow + (l - 1) * TILE_B + ch) = __byte_perm(g2[0], g2[1], 0x6420);
+                if (l >= 1) *(uint32_t *)(trow + DT0 + (l - 1) * TILE_B + ch) = __byte_perm(d2[0], d2[1], 0x6420);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(10 + (l & 1)));            // D_h buffer is free again
+            DBG_T(c_work);
+        };
+
+        // ================= detector tests of a finished step (rows G, H, I), next octave's base: all 16 warps =================
+        // Thread = one grid position (sample column k, sample row sr) for the three levels.  Result per sample in s_res (value
+        // or -1); samples whose three derivatives are all non-zero need the full 3x3 inverse in double: they are queued with
+        // their derivatives and edge test for the service warp, which also emits the step's survivors.
+        auto det_phase = [&](int s) {
+            const int y0 = ys + FR * s, b = s & 1;
+            const int rb = (128 * s) % TROWS;                         // ring row of row y0 - 4
+            auto rr = [&](int ty) { const int r = rb + ty; return r >= TROWS ? r - TROWS : r; };   // ring row of tile row ty = y - y0 + 4
+            if (s >= 2) mbar_wait(bar(14 + b), ((s >> 1) - 1) & 1);   // the service warp is done with this result buffer
+            if (s >= 1) mbar_wait(bar(16), (s - 1) & 1);              // ... and with the queue
+            named_bar(2, NE);                                         // every tile warp's rows of the step are in place
+            DBG_T(c_wait);
+            const int yc_lo = y0 == 0 ? 0 : y0 - 2;
+            const int yc_hi = (y0 + FR >= rows) ? rows - 2 : y0 + FR - 3;         // centre row yc needs rows up to yc + 2
+            const int si_lo = (yc_lo + 2) / 3;
+            if (a.detect) {
+                int n_srow = yc_hi >= 0 ? yc_hi / 3 - si_lo + 1 : 0;
+                if (n_srow < 0) n_srow = 0;
+                const int k = tid & (NS - 1), xc = X0 + 3 * k, tx = 3 * k + 1;
+                const int txm = xc > 0 ? tx - 1 : tx, txp = xc + 1 < cols ? tx + 1 : tx;
+                // column parts of the tile offsets: 16-byte chunk (XOR-swizzled by the row pair) and byte inside it
+                const int gm = txm >> 4, bm = txm & 15, g0 = tx >> 4, b0 = tx & 15, gp = txp >> 4, bp = txp & 15;
+                const u8 *d = tiles + DT0;
+                for (int sr = tid >> 4; sr < n_srow; sr += NE / NS) {
+                    const int yc = 3 * (si_lo + sr);
+                    if (xc <= cols - 2) {
+                        // D tiles at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
+                        const int t0 = yc - y0 + 4;
+                        const int ty = rr(t0), tym = yc > 0 ? rr(t0 - 1) : ty, typ = yc + 1 < rows ? rr(t0 + 1) : ty;
+                        const int sw = (ty >> 1) & 3, swm = (tym >> 1) & 3, swp = (typ >> 1) & 3;
+                        const int o00 = tym * 64 + ((gm ^ swm) << 4) + bm, o01 = tym * 64 + ((g0 ^ swm) << 4) + b0;
+                        const int o10 = ty * 64 + ((gm ^ sw) << 4) + bm, o11 = ty * 64 + ((g0 ^ sw) << 4) + b0;
+                        int w01[5], w10[5], w11[5], mn[5], mx[5];
+#pragma unroll
+                        for (int l = 0; l < 5; ++l) {
+                            const int w00 = d[l * TILE_B + o00];
+                            w01[l] = d[l * TILE_B + o01]; w10[l] = d[l * TILE_B + o10]; w11[l] = d[l * TILE_B + o11];
+                            mn[l] = min(min(w00, w01[l]), min(w10[l], w11[l]));
+                            mx[l] = max(max(w00, w01[l]), max(w10[l], w11[l]));
+                        }
+#pragma unroll
+                        for (int level = 1; level <= 3; ++level) {
+                            const int c = w11[level];
+                            const int lo3 = min(min(mn[level - 1], mn[level]), mn[level + 1]);
+                            const int hi3 = max(max(mx[level - 1], mx[level]), mx[level + 1]);
+                            if (c == lo3 || c == hi3) {                                          // Diff_of_Gauss.cpp:287
+                                const int dx = w10[level] - (int)d[level * TILE_B + ty * 64 + ((gp ^ sw) << 4) + bp];    // :226-228
+                                const int dy = w01[level] - (int)d[level * TILE_B + typ * 64 + ((g0 ^ swp) << 4) + b0];
+                                const int ds = w11[level - 1] - w11[level + 1];
+                                const unsigned code = (unsigned)(k | level << 5 | sr << 8) | (unsigned)c << 17;
+                                // all three derivatives non-zero: the full localisation (front of the queue); a zero derivative:
+                                // cv::invert of the singular A*A^T gives zeros, dog_zhat = value/255 > 0.03 <=> c >= cmin (back of the queue)
+                                if (dx != 0 && dy != 0 && ds != 0)
+                                    s_queue[atomicAdd(&s_nq[0], 1)] = make_uint2(code, (unsigned)(dx + 255) | (unsigned)(dy + 255) << 9 | (unsigned)(ds + 255) << 18);
+                                else if (c >= a.cmin)
+                                    s_queue[NRES - 1 - atomicAdd(&s_nq[1], 1)].x = code;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int level = 1; level <= 3; ++level) s_res[b][(sr * 3 + level - 1) * NS + k] = (short)-1;
                 }
             }
-            named_bar(1, NE);                                         // emission and decimation have read s_res / the tiles
-            // ---- rows y0 + 124 .. y0 + 127 become the history of the next step (same swizzle: 128 + i and i share (tr >> 1) & 3) ----
-            if (tid < (N_G + N_D) * 16) {
-                const int t = tid >> 4, i = tid & 15;                 // 4 rows x 4 chunks
-                uint4 *tp = (uint4 *)(tiles + t * TILE_B);
-                tp[i] = tp[FR * 4 + i];
+            DBG_T2(c_d1, c_det);
+            // ---- next octave's base: level 3 at even rows and columns (GaussPyramid.cpp:123-126); thread = (row, four output columns) ----
+            if (a.next_base && tid < (FR / 2) * (FWO / 8)) {
+                const int g = tid % (FWO / 8), w = tid / (FWO / 8);
+                const int oy = (y0 >> 1) + w, ox = X0 / 2 + 4 * g;
+                if (oy < a.next_rows && ox < a.next_cols) {
+                    const u8 *t3 = tiles + 2 * TILE_B;
+                    const int tr = rr(2 * w + 4);
+                    u8 bb[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) bb[i] = t3[toff(tr, 8 * g + 2 * i + 1)];
+                    u8 *dst = a.next_base + (size_t)frame * a.next_stride + (size_t)oy * a.next_pitch + ox;
+                    if (ox + 3 < a.next_cols) *(uint32_t *)dst = (uint32_t)bb[0] | (uint32_t)bb[1] << 8 | (uint32_t)bb[2] << 16 | (uint32_t)bb[3] << 24;
+                    else for (int i = 0; i < 4 && ox + i < a.next_cols; ++i) dst[i] = bb[i];
+                }
             }
-            if (tid < (3 * MAX_SROW + 31) / 32) s_flag[tid] = 0;
-            if (tid == 0) s_nq = 0;
-            named_bar(1, NE);
+            DBG_T2(c_d2, c_det);
+            named_bar(3, NE);                                         // the queue is complete
+            // ---- the edge test of the queued samples, one thread per sample (a dense pass: the survivors of the extrema test
+            // are few, a per-sample branch would run the test in nearly every warp) ----
+            const int nqb = s_nq[0], nqa = s_nq[1];
+            for (int e = tid; e < nqb + nqa; e += NE) {
+                const int qi = e < nqb ? e : NRES - 1 - (e - nqb);
+                const unsigned code = s_queue[qi].x;
+                const int k = code & 31, level = (code >> 5) & 3, sr = (code >> 8) & 255;
+                const bool ok = edge_pass_tile(tiles + (level - 1) * TILE_B, X0 + 3 * k, 3 * (si_lo + sr), y0, rb, X0, rows, cols, a.edge_thr);
+                if (e < nqb) {
+                    if (ok) s_queue[qi].x = code | 1u << 16;
+                } else if (ok) {
+                    const int task = sr * 3 + level - 1;
+                    s_res[b][task * NS + k] = (short)a.val_lut[(code >> 17) & 255];
+                    atomicOr(&s_flag[b][task >> 5], 1u << (task & 31));
+                }
+            }
+            DBG_T2(c_d3, c_det);
+            named_bar(1, NE);                                         // the tiles may be overwritten
+            // a long queue (textured frames): everything beyond the service warp's share is finished here, one thread per sample
+            for (int e = QS + tid; e < nqb; e += NE) {
+                const uint2 qe = s_queue[e];
+                if (!((qe.x >> 16) & 1)) continue;                                           // fails the edge test (:336)
+                const int k = qe.x & 31, level = (qe.x >> 5) & 3, sr = (qe.x >> 8) & 255, c = (qe.x >> 17) & 255;
+                const int dx = (int)(qe.y & 511) - 255, dy = (int)((qe.y >> 9) & 511) - 255, ds = (int)((qe.y >> 18) & 511) - 255;
+                const float zhat = localize_f(s_div[dx + 255], s_div[dy + 255], s_div[ds + 255], s_div[c + 255]);
+                if (zhat > a.contrast_thr) {                                                 // Diff_of_Gauss.cpp:245
+                    const int task = sr * 3 + level - 1;
+                    s_res[b][task * NS + k] = (short)(int)__fmul_rn(zhat, 255.0f);           // :246
+                    atomicOr(&s_flag[b][task >> 5], 1u << (task & 31));
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(12 + b));                  // this warp's results are complete
+            DBG_ONLY(c_d4 += clock64() - c_e0;)
+            DBG_T(c_det);
+        };
+
+        // One loop over (step, level) for both groups (one copy of every stage in the instruction stream).  The X warps run two
+        // levels ahead of the step boundary: levels 0 and 1 of step s + 1 come before the detector of step s.
+        const int n_lv = 6 * n_steps;
+#pragma unroll 1
+        for (int gl = 0; gl <= n_lv; ++gl) {
+            const int s = gl / 6, l = gl - 6 * s;
+            int sdet = -1;
+            if (xgroup) {
+                if (gl < n_lv) { ev(s, l); if (l == 1 && s > 0) sdet = s - 1; }
+                else sdet = n_steps - 1;
+            } else if (gl < n_lv) {
+                if (l == 0) {
+                    const int tr_own = (128 * s + m + 4) % TROWS;     // ring row of this thread's output row
+                    trow = tiles + tr_own * 64;
+                    tswz = (tr_own >> 1) & 3;
+                }
+                eh(s, l);
+                if (l == 5) sdet = s;
+            }
+            if (sdet >= 0) det_phase(sdet);
         }
+#ifdef VSLAM_UMMA_DBG_BUILD
+        if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0 && lane == 0 && (warp == 0 || warp == 8)) {
+            long long *o = a.dbg + (warp == 0 ? 8 : 12);
+            o[0] = c_wait; o[1] = c_work; o[2] = c_det;
+            if (warp == 0) { a.dbg[16] = c_d1; a.dbg[17] = c_d2; a.dbg[18] = c_d3; a.dbg[19] = c_d4; }
+        }
+#endif
     }
     tc_fence_before();
     __syncthreads();
@@ -590,9 +712,22 @@ int launch_octave_umma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double 
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) VS_FAIL(ctx, VSLAM_E_CUDA, "cuTensorMapEncodeTiled -> %d (octave %d)", (int)cr, io.octave);
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
-    KernelSpan span(ctx, VSLAM_K_FUSED);
-    p.k<<<grid, kThreads, p.smem, ctx->stream>>>(tmap, a);
+    static const bool dbg = getenv("VSLAM_UMMA_DBG") && atoi(getenv("VSLAM_UMMA_DBG"));
+    static long long *d_dbg = nullptr;
+    if (dbg && !d_dbg) cudaMalloc(&d_dbg, 24 * sizeof(long long));
+    a.dbg = dbg ? d_dbg : nullptr;
+    {
+        KernelSpan span(ctx, VSLAM_K_FUSED);
+        p.k<<<grid, kThreads, p.smem, ctx->stream>>>(tmap, a);
+    }
     VS_LAUNCH_CHECK(ctx);
+    if (dbg) {
+        long long h[24];
+        cudaStreamSynchronize(ctx->stream);
+        cudaMemcpy(h, d_dbg, sizeof h, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "umma dbg octave %d: steps %lld  control total %lld (x_full wait %lld, free wait %lld) | tile warp: wait %lld work %lld det %lld | "
+                        "X warp: wait %lld work %lld det %lld | service: queued %lld work %lld | det parts: tests %lld decim %lld bar %lld help %lld\n", io.octave, h[5], h[0], h[1], h[2], h[8], h[9], h[10], h[12], h[13], h[14], h[6], h[7], h[16], h[17], h[18], h[19]);
+    }
     return VSLAM_OK;
 }
 

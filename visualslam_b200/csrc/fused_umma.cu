@@ -10,8 +10,8 @@
 //            128B-swizzled.  That layout is at once the MN-major operand of the V pass (K = rows) -- no transposition, no
 //            staging code, no border path.
 //   V pass   D_v[128 out rows x NV cols] = T_v[128 x 32 KV] * ring chunks; all six levels read the same ring.
-//   X        warps read D_v from TMEM (thread = row), add the rounding bias of the second pass (128 per 8.8 sum: the taps
-//            sum to 256), split the 16-bit sums into two byte planes and store them K-major for the H pass.
+//   X        warps read D_v from TMEM (thread = row), split the 16-bit sums into two byte planes and store them K-major for
+//            the H pass (the rounding bias of that pass is one more tcgen05.mma into the low-byte accumulator).
 //   H pass   D_lo / D_hi[128 rows x 64 out cols] = X_lo / X_hi[128 x 32 KH] * T_h[64 x 32 KH]^T.
 //   epilogue out = (256 D_hi + D_lo) >> 16, saturating DoG against the previous level (registers), byte tiles in shared
 //            memory for the detector.
@@ -93,6 +93,12 @@ __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&v)[4]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr));
 }
 
+// 16 consecutive columns as 8 registers: the low 16 bits of two adjacent columns per register (the 8.8 sums fit 16 bits)
+__device__ __forceinline__ void tmem_ld16_pack(uint32_t taddr, uint32_t (&v)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr));
+}
+
 // byte offset of pixel (tile row tr, column n) inside a tile
 __device__ __forceinline__ int toff(int tr, int n) { return tr * 64 + ((((n >> 4) ^ (tr >> 1)) & 3) << 4) + (n & 15); }
 
@@ -139,6 +145,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
     u8 *xbuf = ring + RC * 4096;
     u8 *tab = xbuf + XBUF * 2 * XPB;
     u8 *tiles = tab + 6 * (TVB + THB);
+    u8 *biasop = tiles + (N_G + N_D) * TILE_B;     // operands of the rounding-bias MMA: 512 bytes of 0x80, then 8 x [row pattern | zeros]
     __shared__ __align__(8) unsigned long long s_bar[17];
     __shared__ uint32_t s_tmem;
     // detector results of a step, double buffered: the service warp finishes and emits step s while the others are in s + 1
@@ -165,7 +172,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
         mbar_init(bar(4), 8); mbar_init(bar(5), 8);
         mbar_init(bar(6), 8); mbar_init(bar(7), 8);
         mbar_init(bar(8), 1); mbar_init(bar(9), 1);
-        mbar_init(bar(10), 8); mbar_init(bar(11), 8);
+        mbar_init(bar(10), 12); mbar_init(bar(11), 12);
         mbar_init(bar(12), 16); mbar_init(bar(13), 16);
         mbar_init(bar(14), 1); mbar_init(bar(15), 1); mbar_init(bar(16), 1);
         fence_barrier_init();
@@ -173,6 +180,13 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
     if (warp == 0) tmem_alloc(smem_u32(&s_tmem), kTmemCols);
     for (int i = tid; i < 6 * (TVB + THB) / 16; i += kThreads) ((uint4 *)tab)[i] = a.tab_image[i];
     for (int i = tid; i < 511; i += kThreads) s_div[i] = __fdiv_rn((float)(i - 255), 255.0f);
+    // rounding bias of the second pass, (sum + 32768) >> 16, as one more tcgen05.mma per level into the low-byte accumulator:
+    // A = 128 x 32 bytes of 0x80 (every core matrix aliases the same 512-byte block), B[n][0] = B[n][1] = 0x80, else 0:
+    // D_lo += 2 * 128 * 128.  Costs ~50 tensor-pipe cycles per level and removes an add per 8.8 sum from the X warps.
+    for (int i = tid; i < (512 + 8 * 256) / 4; i += kThreads) {
+        const int o = 4 * i;
+        ((uint32_t *)biasop)[i] = o < 512 ? 0x80808080u : ((((o - 512) & 255) < 128 && ((o - 512) & 15) == 0) ? 0x00008080u : 0u);
+    }
     if (tid < 2 * NFLAG) (&s_flag[0][0])[tid] = 0;
     if (tid < 2) s_nq[tid] = 0;
     fence_proxy_async();
@@ -205,6 +219,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             // descriptor halves that never change
             constexpr uint64_t tv_d = smem_desc(0, 256, 128, kLayoutNone), img_d = smem_desc(0, 4096, 1024, kLayoutSw128),
                                x_d = smem_desc(0, 2048, 128, kLayoutNone);
+            const uint64_t ba_d = smem_desc(smem_u32(biasop), 16, 16, kLayoutNone), bb_d = smem_desc(smem_u32(biasop) + 512, 128, 256, kLayoutNone);
             mbar_expect_tx(bar(0), KV * 4096);
             for (int k = 0; k < KV; ++k) tma_load_3d(ring_sa + 4096 * k, &tmap, bar(0), tx, ty + 32 * k, frame);
             DBG_ONLY(long long c_xfull = 0; long long c_free = 0;)
@@ -245,6 +260,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
                         mma_i8_ss(d, x_d + ((xl + 4096 * k) >> 4), bd, ih, k > 0);
                         mma_i8_ss(d + 64, x_d + ((xl + XPB + 4096 * k) >> 4), bd, ih, k > 0);
                     }
+                    mma_i8_ss(d, ba_d, bb_d, ih, 1);                 // + 32768
                     mma_commit(bar(8 + (l & 1)));
                 };
                 // V0 V1 H0 V2 H1 V3 H2 V4 H3 V5 H4 H5: the V pass stays two levels ahead of the H pass
@@ -331,8 +347,10 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
         DBG_ONLY(if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0 && lane == 0) { a.dbg[6] = c_q; a.dbg[7] = c_work; })
     } else {
         // =============================== epilogue warps ===============================
-        const int q = warp & 3, h = (warp >> 2) & 1;
-        const bool xgroup = warp >= 8;                                // X warps (D_v -> byte planes) or tile warps (D_h -> tiles)
+        // role r = warp / 4 of the four warps of a TMEM lane quadrant (the tile epilogue costs ~3x the X epilogue per column):
+        //   0: tile columns 0..15   1: tile columns 16..31 and 48..51   2: tile columns 32..47 + X piece 0   3: X pieces 1 .. NP - 1
+        const int q = warp & 3, r = warp >> 2;
+        const bool has_ev = r >= 2, has_eh = r <= 2;
         const int mp = 32 * q + lane;                                 // TMEM lane = reversed row of the step
         const int m = 127 - mp;
         const uint32_t lane_off = (uint32_t)(32 * q) << 16;
@@ -352,35 +370,23 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             tc_fence_after();
             const uint32_t tb = tm + 128 * (l & 1) + lane_off;
             u8 *xl = xbuf + (XBUF == 2 ? (l & 1) : 0) * 2 * XPB + mp * 16;   // (mp >> 3) * 128 + (mp & 7) * 16
-            const int p0 = h ? PMID : 0, np = h ? NP - PMID : PMID;
-            // two 16-column pieces in flight (18 warps leave 96 registers per thread)
+            const int p0 = r == 2 ? 0 : 1, np = r == 2 ? 1 : NP - 1;
+            uint32_t v[NP - 1][8];                                    // 16 columns per piece, two 16-bit sums per register
 #pragma unroll
-            for (int pp = 0; pp < PMID; pp += 2) {
-                uint32_t v[2][16];
+            for (int p = 0; p < NP - 1; ++p)
+                if (p < np) tmem_ld16_pack(tb + 16 * (p0 + p), v[p]);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(4 + (l & 1)));             // D_v buffer is free again
 #pragma unroll
-                for (int p = 0; p < 2; ++p)
-                    if (pp + p < np) tmem_ld16(tb + 16 * (p0 + pp + p), v[p]);
-                tmem_ld_wait();
-                if (pp + 2 >= PMID) {                                 // last loads of the level: the D_v buffer is free again
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bar(4 + (l & 1)));
+            for (int p = 0; p < NP - 1; ++p)
+                if (p < np) {
+                    *(uint4 *)(xl + (p0 + p) * 2048) = make_uint4(__byte_perm(v[p][0], v[p][1], 0x6420), __byte_perm(v[p][2], v[p][3], 0x6420),
+                                                                   __byte_perm(v[p][4], v[p][5], 0x6420), __byte_perm(v[p][6], v[p][7], 0x6420));
+                    *(uint4 *)(xl + XPB + (p0 + p) * 2048) = make_uint4(__byte_perm(v[p][0], v[p][1], 0x7531), __byte_perm(v[p][2], v[p][3], 0x7531),
+                                                                         __byte_perm(v[p][4], v[p][5], 0x7531), __byte_perm(v[p][6], v[p][7], 0x7531));
                 }
-#pragma unroll
-                for (int p = 0; p < 2; ++p)
-                    if (pp + p < np) {
-                        uint32_t lo[4], hi[4];
-#pragma unroll
-                        for (int w = 0; w < 4; ++w) {
-                            const uint32_t t0 = __byte_perm(v[p][4 * w], v[p][4 * w + 1], 0x5410) + 0x00800080u;
-                            const uint32_t t1 = __byte_perm(v[p][4 * w + 2], v[p][4 * w + 3], 0x5410) + 0x00800080u;
-                            lo[w] = __byte_perm(t0, t1, 0x6420);
-                            hi[w] = __byte_perm(t0, t1, 0x7531);
-                        }
-                        *(uint4 *)(xl + (p0 + pp + p) * 2048) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                        *(uint4 *)(xl + XPB + (p0 + pp + p) * 2048) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                    }
-            }
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(6 + (XBUF == 2 ? (l & 1) : 0)));
@@ -392,7 +398,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
         // last four rows of step s - 1 are the four rows in front of step s without a copy
         u8 *trow = tiles;
         int tswz = 0;
-        uint32_t prev[18];                                            // previous level, 16-bit halves: 2 pixels per register
+        uint32_t prev[10];                                            // previous level, 16-bit halves: 2 pixels per register
         // 16 columns n' = c0 .. c0 + 15 of the (column-reversed) accumulators = image columns n = 48 - c0 .. 63 - c0;
         // pi = index of the piece's first register pair in prev[]
         auto eh_piece16 = [&](int l, uint32_t dlo, int c0, int pi) {
@@ -421,11 +427,8 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             DBG_T(c_wait);
             tc_fence_after();
             const uint32_t dlo = tm + 256 + 128 * (l & 1) + lane_off;
-            if (h) {                                                  // columns n = 0 .. 31
-                eh_piece16(l, dlo, 48, 0);
-                eh_piece16(l, dlo, 32, 8);
-            } else {                                                  // columns n = 32 .. 51 (49 .. 51 are never read)
-                eh_piece16(l, dlo, 16, 0);
+            eh_piece16(l, dlo, 48 - 16 * r, 0);                       // columns n = 16 r .. 16 r + 15
+            if (r == 1) {                                             // columns n = 48 .. 51 (49 .. 51 are never read)
                 uint32_t lo[4], hi[4];
                 tmem_ld4(dlo + 12, lo);
                 tmem_ld4(dlo + 64 + 12, hi);
@@ -566,29 +569,29 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             DBG_T(c_det);
         };
 
-        // One loop over (step, level) for both groups (one copy of every stage in the instruction stream).  The X warps run two
-        // levels ahead of the step boundary: levels 0 and 1 of step s + 1 come before the detector of step s.
+        // One loop over (step, level) for all sixteen warps (one copy of every stage in the instruction stream).  The X stage
+        // runs two levels ahead of the tile stage, across the step boundary: levels 0 and 1 of step s + 1 come before the
+        // detector of step s.
         const int n_lv = 6 * n_steps;
+        if (has_ev) { ev(0, 0); ev(0, 1); }
+        int s = 0, l = 0, s2 = 0, l2 = 2;                             // (s, l): tile stage; (s2, l2): X stage
 #pragma unroll 1
-        for (int gl = 0; gl <= n_lv; ++gl) {
-            const int s = gl / 6, l = gl - 6 * s;
-            int sdet = -1;
-            if (xgroup) {
-                if (gl < n_lv) { ev(s, l); if (l == 1 && s > 0) sdet = s - 1; }
-                else sdet = n_steps - 1;
-            } else if (gl < n_lv) {
+        for (int gl = 0; gl < n_lv; ++gl) {
+            if (has_eh) {
                 if (l == 0) {
                     const int tr_own = (128 * s + m + 4) % TROWS;     // ring row of this thread's output row
                     trow = tiles + tr_own * 64;
                     tswz = (tr_own >> 1) & 3;
                 }
                 eh(s, l);
-                if (l == 5) sdet = s;
             }
-            if (sdet >= 0) det_phase(sdet);
+            if (has_ev && gl + 2 < n_lv) ev(s2, l2);
+            if (l == 5) det_phase(s);
+            s += l == 5; l = l == 5 ? 0 : l + 1;
+            s2 += l2 == 5; l2 = l2 == 5 ? 0 : l2 + 1;
         }
 #ifdef VSLAM_UMMA_DBG_BUILD
-        if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0 && lane == 0 && (warp == 0 || warp == 8)) {
+        if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0 && lane == 0 && (warp == 0 || warp == 12)) {
             long long *o = a.dbg + (warp == 0 ? 8 : 12);
             o[0] = c_wait; o[1] = c_work; o[2] = c_det;
             if (warp == 0) { a.dbg[16] = c_d1; a.dbg[17] = c_d2; a.dbg[18] = c_d3; a.dbg[19] = c_d4; }
@@ -611,7 +614,7 @@ typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, vo
 struct UmmaPlan { umma_kern_t k; size_t smem; UmmaGeom g; };
 
 template <int KV, int KH, int NV, int XBUF> constexpr size_t umma_smem() {
-    return 1024 + (size_t)(KV + 4) * 4096 + (size_t)XBUF * 2 * (2 * KH * 2048) + 6 * (size_t)((14 + 4 * KV) + (6 + 4 * KH)) * 128 + (size_t)(N_G + N_D) * TILE_B;
+    return 1024 + (size_t)(KV + 4) * 4096 + (size_t)XBUF * 2 * (2 * KH * 2048) + 6 * (size_t)((14 + 4 * KV) + (6 + 4 * KH)) * 128 + (size_t)(N_G + N_D) * TILE_B + 512 + 8 * 256;
 }
 
 bool umma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, UmmaPlan *p) {

@@ -112,15 +112,15 @@ def test_dog_keypoints_other_sigma_vs_oracle(ctx, sigma0, octaves):
 
 
 def test_dog_keypoints_kernel_variants_agree(tmp_path):
-    """VSLAM_UMMA=0 (mma.sync kernel for octaves 0 and 1 instead of the tcgen05 one), VSLAM_MMA_STATIC=0 (run-time geometry),
+    """VSLAM_UMMA=1 (tcgen05 + TMA kernel for octaves 0 and 1 instead of the mma.sync one), VSLAM_MMA_STATIC=0 (run-time geometry),
     VSLAM_MMA_FW=32 (32-column strips for every octave) and VSLAM_FUSED_MMA=0 (dp4a/dp2a kernel) give the default kernels' lists."""
     import subprocess, sys, os
     code = ("import numpy as np, sys; import visualslam_b200 as vs; from visualslam_b200 import synth;"
             "f = np.stack([synth.frame(i, 540, 960) for i in range(8)], 0); c = vs.Context(0);"
             "r = c.dog_keypoints(f); np.save(sys.argv[1], np.asarray(r['keypoints']))")
     outs = []
-    for i, env in enumerate(({}, {"VSLAM_UMMA": "0"}, {"VSLAM_UMMA": "0", "VSLAM_MMA_STATIC": "0"}, {"VSLAM_UMMA": "0", "VSLAM_FUSED_MMA": "0"},
-                             {"VSLAM_UMMA": "0", "VSLAM_MMA_FW": "32"}, {"VSLAM_UMMA": "0", "VSLAM_MMA_FW": "32", "VSLAM_MMA_STATIC": "0"})):
+    for i, env in enumerate(({}, {"VSLAM_UMMA": "1"}, {"VSLAM_MMA_STATIC": "0"}, {"VSLAM_FUSED_MMA": "0"}, {"VSLAM_MMA_FW": "32"},
+                             {"VSLAM_MMA_FW": "32", "VSLAM_MMA_STATIC": "0"})):
         out = str(tmp_path / f"k{i}.npy")
         root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
         subprocess.check_call([sys.executable, "-c", code, out], env={**os.environ, **env, "PYTHONPATH": root}, timeout=600)
@@ -128,6 +128,24 @@ def test_dog_keypoints_kernel_variants_agree(tmp_path):
     assert len(outs[0]) > 1000
     for o in outs[1:]:
         assert np.array_equal(outs[0], o)
+
+
+def test_tcgen05_kernel_matches_oracle(tmp_path):
+    """The tcgen05 / TMA octave kernel (fused_umma.cu, VSLAM_UMMA=1) against the plain-C oracle on awkward sizes: strips that
+    end inside the image, a last step of one row, an octave smaller than one step, sizes smaller than the kernel radius."""
+    import subprocess, sys, os
+    code = ("import numpy as np, sys; import visualslam_b200 as vs; from visualslam_b200 import synth; from oracle import c_oracle as O;"
+            "c = vs.Context(0)\n"
+            "for (h, w) in ((192, 256), (300, 217), (65, 1), (1, 65), (64, 49), (129, 97), (5, 7), (257, 96)):\n"
+            "    img = synth.frame(h + w, h, w); r = c.dog_keypoints(img); k = r['keypoints']\n"
+            "    got = np.stack([k[n] for n in ('row', 'col', 'value', 'padding', 'octave', 'level')], 1)\n"
+            "    want = O.dog_keypoints(img)[0]\n"
+            "    assert np.array_equal(got, want), (h, w, len(got), len(want))\n"
+            "print('ok')")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], env={**os.environ, "VSLAM_UMMA": "1", "PYTHONPATH": root}, timeout=900,
+                         capture_output=True, text=True)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
 
 
 def test_dog_capacity_overflow(ctx, images):

@@ -42,8 +42,9 @@ using namespace umma;
 
 namespace {
 constexpr int FR = kUmmaRows, FWO = kUmmaFWO, NS = FWO / 3;
-constexpr int kThreads = 576;                   // eight tile warps, eight X warps, the control warp, the service warp
-constexpr int NE = 512;                         // threads of the sixteen epilogue warps
+constexpr int kThreads = 960;                   // 28 epilogue warps (7 per TMEM lane quadrant), the control warp, the service warp
+constexpr int NE = 896;                         // threads of the epilogue warps
+constexpr int W_CTL = 28, W_SVC = 29;
 constexpr int TROWS = FR + 4;                   // tile rows: 4 rows of history + the step
 constexpr int TILE_B = TROWS * 64;              // bytes per tile: 64 columns (49 used), 16-byte chunks XOR-swizzled by the row pair
 constexpr int N_G = 3, N_D = 5;                 // G tiles: Gaussian levels 1..3; D tiles: DoG levels 0..4
@@ -89,6 +90,10 @@ namespace {
 
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&v)[4]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr));
 }
@@ -169,11 +174,11 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
     if (tid == 0) {
         mbar_init(bar(0), 1); mbar_init(bar(1), 1);
         mbar_init(bar(2), 1); mbar_init(bar(3), 1);
-        mbar_init(bar(4), 8); mbar_init(bar(5), 8);
-        mbar_init(bar(6), 8); mbar_init(bar(7), 8);
+        mbar_init(bar(4), 4); mbar_init(bar(5), 4);
+        mbar_init(bar(6), 4); mbar_init(bar(7), 4);
         mbar_init(bar(8), 1); mbar_init(bar(9), 1);
-        mbar_init(bar(10), 12); mbar_init(bar(11), 12);
-        mbar_init(bar(12), 16); mbar_init(bar(13), 16);
+        mbar_init(bar(10), 24); mbar_init(bar(11), 24);
+        mbar_init(bar(12), 28); mbar_init(bar(13), 28);
         mbar_init(bar(14), 1); mbar_init(bar(15), 1); mbar_init(bar(16), 1);
         fence_barrier_init();
     }
@@ -196,11 +201,23 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
     const uint32_t tm = s_tmem;
     // TMEM columns: D_v buffers at 0 / 128, D_h buffers at 256 / 384 (low-byte plane, +64 high-byte plane)
     // completion count of a per-level barrier pair (index l & 1) at level l of step s: 3 s + (l >> 1)
-#ifdef VSLAM_UMMA_DBG_BUILD                                     // cycle counters of CTA (0, 0, 0): they spill, so a separate build only
-    long long c_wait = 0, c_work = 0, c_det = 0, c_e0 = clock64(), c_d1 = 0, c_d2 = 0, c_d3 = 0, c_d4 = 0;
-#define DBG_T(acc) do { const long long t_ = clock64(); acc += t_ - c_e0; c_e0 = t_; } while (0)
-#define DBG_T2(acc, acc2) do { const long long t_ = clock64(); acc += t_ - c_e0; acc2 += t_ - c_e0; c_e0 = t_; } while (0)
-#define DBG_WAIT(acc, stmt) do { const long long t_ = clock64(); stmt; acc += clock64() - t_; } while (0)
+#ifdef VSLAM_UMMA_DBG_BUILD                                     // cycle counters per warp in shared memory (lane 0 only): a separate build
+    __shared__ long long s_dbg[32][8];                          // slots: 0 wait, 1 work, 2 det, 3 tests, 4 decim, 5 edge, 6 tail, 7 last stamp
+    if (tid < 256) (&s_dbg[0][0])[tid] = 0;
+    __syncthreads();
+    if (lane == 0) s_dbg[warp][7] = clock64();
+#define c_wait 0
+#define c_work 1
+#define c_det 2
+#define c_d1 3
+#define c_d2 4
+#define c_d3 5
+#define c_d4 6
+#define c_xfull 0
+#define c_free 1
+#define DBG_T(slot) do { if (lane == 0) { const long long t_ = clock64(); s_dbg[warp][slot] += t_ - s_dbg[warp][7]; s_dbg[warp][7] = t_; } } while (0)
+#define DBG_T2(slot, slot2) do { if (lane == 0) { const long long t_ = clock64(); s_dbg[warp][slot] += t_ - s_dbg[warp][7]; s_dbg[warp][slot2] += t_ - s_dbg[warp][7]; s_dbg[warp][7] = t_; } } while (0)
+#define DBG_WAIT(slot, stmt) do { const long long t_ = clock64(); stmt; s_dbg[warp][slot] += clock64() - t_; } while (0)
 #define DBG_ONLY(stmt) stmt
 #else
 #define DBG_T(acc) do { } while (0)
@@ -209,7 +226,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
 #define DBG_ONLY(stmt)
 #endif
 
-    if (warp == 16) {
+    if (warp == W_CTL) {
         // =============================== control: TMA producer + MMA issuer (one thread) ===============================
         if (lane == 0) {
             const int tx = X0 - P + a.plane_x0;                       // first staged column inside the padded plane: multiple of 16
@@ -222,61 +239,80 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             const uint64_t ba_d = smem_desc(smem_u32(biasop), 16, 16, kLayoutNone), bb_d = smem_desc(smem_u32(biasop) + 512, 128, 256, kLayoutNone);
             mbar_expect_tx(bar(0), KV * 4096);
             for (int k = 0; k < KV; ++k) tma_load_3d(ring_sa + 4096 * k, &tmap, bar(0), tx, ty + 32 * k, frame);
-            DBG_ONLY(long long c_xfull = 0; long long c_free = 0;)
+            // The issuing thread is the pacemaker of the CTA: every instruction it spends between two tcgen05.mma delays all
+            // 29 other warps.  Levels are compile-time here (descriptor offsets are immediates), the ring slots of a step are
+            // computed once, barrier parities come from the step's parity.
+            const uint32_t tab_lo = tab_sa >> 4, x_lo = x_sa >> 4, ring_lo = ring_sa >> 4;
+            constexpr uint32_t tv_hi = (uint32_t)(tv_d >> 32), img_hi = (uint32_t)(img_d >> 32), x_hi = (uint32_t)(x_d >> 32);
+            constexpr uint32_t tv_l = (uint32_t)tv_d, img_l = (uint32_t)img_d, x_l = (uint32_t)x_d;
+            const uint32_t ba_lo = (uint32_t)ba_d, ba_hi = (uint32_t)(ba_d >> 32), bb_lo = (uint32_t)bb_d, bb_hi = (uint32_t)(bb_d >> 32);
+            auto mma2 = [&](uint32_t d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc, uint32_t acc) {
+                asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\tsetp.ne.b32 p, %6, 0;\n\t"
+                             "tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %5, {%7, %7, %7, %7}, p;\n\t}"
+                             ::"r"(d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(acc), "r"(0u) : "memory");
+            };
+            int slot0 = 0;                                            // ring slot of the step's first chunk: (4 s) % RC
             for (int s = 0; s < n_steps; ++s) {
+                const uint32_t sp = (uint32_t)s & 1u;
                 if (s + 1 < n_steps) {
                     // the next step's four new chunks replace the four oldest of step s - 1: its last V pass must have completed
-                    if (s > 0) mbar_wait(bar(3), (3 * (s - 1) + 2) & 1);
+                    if (s > 0) mbar_wait(bar(3), sp ^ 1u);            // completion 3 (s - 1) + 2 of D_v-full[1]
                     const uint32_t b = bar((s + 1) & 1);
                     mbar_expect_tx(b, 4 * 4096);
+#pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        const int c = KV + 4 * s + j;
-                        tma_load_3d(ring_sa + 4096 * (c % RC), &tmap, b, tx, ty + 32 * c, frame);
+                        int sl = slot0 + KV + j;
+                        sl -= sl >= RC ? RC : 0; sl -= sl >= RC ? RC : 0;
+                        tma_load_3d(ring_sa + 4096 * sl, &tmap, b, tx, ty + 32 * (KV + 4 * s + j), frame);
                     }
+                }
+                uint32_t rs[KV];                                      // descriptor address fields of the step's ring chunks
+#pragma unroll
+                for (int k = 0; k < KV; ++k) {
+                    int sl = slot0 + k;
+                    sl -= sl >= RC ? RC : 0;
+                    rs[k] = img_l + ring_lo + 256u * (uint32_t)sl;
                 }
                 mbar_wait(bar(s & 1), (s >> 1) & 1);
-                auto v_pass = [&](int l) {
-                    const int n = 3 * s + (l >> 1);                   // use count of this D_v buffer
-                    DBG_WAIT(c_free, if (n > 0) mbar_wait(bar(4 + (l & 1)), (n - 1) & 1));
+                auto v_pass = [&](auto l_) {
+                    constexpr int l = decltype(l_)::value;
+                    constexpr uint32_t lp = (l >> 1) & 1;             // completion 3 s + (l >> 1) has parity sp ^ lp
+                    if (s > 0 || l >= 2) DBG_WAIT(c_free, mbar_wait(bar(4 + (l & 1)), sp ^ lp ^ 1u));
                     tc_fence_after();
 #pragma unroll
-                    for (int k = 0; k < KV; ++k) {
-                        const uint32_t slot = (uint32_t)((4 * s + k) % RC);
-                        mma_i8_ss(tm + 128 * (l & 1), tv_d + ((tab_sa + l * TVB + 512 * k) >> 4), img_d + ((ring_sa + 4096 * slot) >> 4), iv, k > 0);
-                    }
+                    for (int k = 0; k < KV; ++k)
+                        mma2(tm + 128 * (l & 1), tv_l + tab_lo + (uint32_t)((l * TVB + 512 * k) >> 4), tv_hi, rs[k], img_hi, iv, k > 0);
                     mma_commit(bar(2 + (l & 1)));
                 };
-                auto h_pass = [&](int l) {
-                    const int xb = XBUF == 2 ? (l & 1) : 0;
-                    const int nx = XBUF == 2 ? 3 * s + (l >> 1) : 6 * s + l;
-                    DBG_WAIT(c_xfull, mbar_wait(bar(6 + xb), nx & 1));
-                    const int n = 3 * s + (l >> 1);
-                    DBG_WAIT(c_free, if (n > 0) mbar_wait(bar(10 + (l & 1)), (n - 1) & 1));
+                auto h_pass = [&](auto l_) {
+                    constexpr int l = decltype(l_)::value;
+                    constexpr uint32_t lp = (l >> 1) & 1;
+                    constexpr int xb = XBUF == 2 ? (l & 1) : 0;
+                    DBG_WAIT(c_xfull, mbar_wait(bar(6 + xb), XBUF == 2 ? (sp ^ lp) : (uint32_t)(l & 1)));
+                    if (s > 0 || l >= 2) DBG_WAIT(c_free, mbar_wait(bar(10 + (l & 1)), sp ^ lp ^ 1u));
                     tc_fence_after();
-                    const uint32_t xl = x_sa + xb * 2 * XPB, th = tab_sa + 6 * TVB + l * THB, d = tm + 256 + 128 * (l & 1);
+                    const uint32_t d = tm + 256 + 128 * (l & 1);
 #pragma unroll
                     for (int k = 0; k < KH; ++k) {
-                        const uint64_t bd = tv_d + ((th + 512 * k) >> 4);
-                        mma_i8_ss(d, x_d + ((xl + 4096 * k) >> 4), bd, ih, k > 0);
-                        mma_i8_ss(d + 64, x_d + ((xl + XPB + 4096 * k) >> 4), bd, ih, k > 0);
+                        const uint32_t blo = tv_l + tab_lo + (uint32_t)((6 * TVB + l * THB + 512 * k) >> 4);
+                        mma2(d, x_l + x_lo + (uint32_t)((xb * 2 * XPB + 4096 * k) >> 4), x_hi, blo, tv_hi, ih, k > 0);
+                        mma2(d + 64, x_l + x_lo + (uint32_t)((xb * 2 * XPB + XPB + 4096 * k) >> 4), x_hi, blo, tv_hi, ih, k > 0);
                     }
-                    mma_i8_ss(d, ba_d, bb_d, ih, 1);                 // + 32768
+                    mma2(d, ba_lo, ba_hi, bb_lo, bb_hi, ih, 1);      // + 32768
                     mma_commit(bar(8 + (l & 1)));
                 };
-                // V0 V1 H0 V2 H1 V3 H2 V4 H3 V5 H4 H5: the V pass stays two levels ahead of the H pass
-#pragma unroll 1
-                for (int i = 0; i < 12; ++i) {
-                    const bool is_v = i < 2 || (i < 10 && (i & 1));
-                    const int l = i < 2 ? i : (i >= 10 ? i - 6 : (is_v ? (i + 1) / 2 : (i - 2) / 2));
-                    if (is_v) v_pass(l);
-                    else h_pass(l);
-                }
+                using std::integral_constant;
+                // the V pass stays two levels ahead of the H pass
+                v_pass(integral_constant<int, 0>()); v_pass(integral_constant<int, 1>()); h_pass(integral_constant<int, 0>());
+                v_pass(integral_constant<int, 2>()); h_pass(integral_constant<int, 1>()); v_pass(integral_constant<int, 3>());
+                h_pass(integral_constant<int, 2>()); v_pass(integral_constant<int, 4>()); h_pass(integral_constant<int, 3>());
+                v_pass(integral_constant<int, 5>()); h_pass(integral_constant<int, 4>()); h_pass(integral_constant<int, 5>());
+                slot0 += 4;
+                slot0 -= slot0 >= RC ? RC : 0;
             }
-            DBG_ONLY(if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0) { a.dbg[0] = clock64() - c_e0; a.dbg[1] = c_xfull; a.dbg[2] = c_free; a.dbg[5] = n_steps; })
         }
-    } else if (warp == 17) {
+    } else if (warp == W_SVC) {
         // =============================== service warp: queued localisations + ordered emission of a finished step ===============================
-        DBG_ONLY(long long c_q = 0;)
         for (int s = 0; s < n_steps; ++s) {
             const int b = s & 1;
             const int y0 = ys + FR * s;
@@ -287,7 +323,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             // sample; their derivatives and edge tests were taken from the tiles by the detector threads
             // (the first QS entries; the detector threads took the rest themselves)
             const int nq_all = s_nq[0], nq = min(nq_all, QS);
-            DBG_ONLY(c_q += nq_all;)
+            DBG_ONLY(if (lane == 0) s_dbg[warp][3] += nq_all;)
             for (int e = lane; e < nq; e += 32) {
                 const uint2 qe = s_queue[e];
                 if (!((qe.x >> 16) & 1)) continue;                                           // fails the edge test (:336)
@@ -344,13 +380,14 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             if (lane == 0) mbar_arrive(bar(14 + b));
             DBG_T(c_work);
         }
-        DBG_ONLY(if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0 && lane == 0) { a.dbg[6] = c_q; a.dbg[7] = c_work; })
     } else {
         // =============================== epilogue warps ===============================
-        // role r = warp / 4 of the four warps of a TMEM lane quadrant (the tile epilogue costs ~3x the X epilogue per column):
-        //   0: tile columns 0..15   1: tile columns 16..31 and 48..51   2: tile columns 32..47 + X piece 0   3: X pieces 1 .. NP - 1
+        // Seven warps per TMEM lane quadrant (q = warp % 4), role r = warp / 4: r < 6 turns the 8 tile columns 8 r .. 8 r + 7 of
+        // D_lo / D_hi into Gaussian / DoG tile bytes (r == 5 also columns 48..51), r == 6 turns D_v into the byte planes X.
+        // Many light warps instead of a few heavy ones: every stage is a dependent chain (TMEM load -> wait -> pack -> store),
+        // so the issue slots are filled by warp count, not by instruction-level parallelism.
         const int q = warp & 3, r = warp >> 2;
-        const bool has_ev = r >= 2, has_eh = r <= 2;
+        const bool has_ev = r == 6, has_eh = r < 6;
         const int mp = 32 * q + lane;                                 // TMEM lane = reversed row of the step
         const int m = 127 - mp;
         const uint32_t lane_off = (uint32_t)(32 * q) << 16;
@@ -370,23 +407,28 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             tc_fence_after();
             const uint32_t tb = tm + 128 * (l & 1) + lane_off;
             u8 *xl = xbuf + (XBUF == 2 ? (l & 1) : 0) * 2 * XPB + mp * 16;   // (mp >> 3) * 128 + (mp & 7) * 16
-            const int p0 = r == 2 ? 0 : 1, np = r == 2 ? 1 : NP - 1;
-            uint32_t v[NP - 1][8];                                    // 16 columns per piece, two 16-bit sums per register
+            // up to four 16-column pieces in flight (two 16-bit sums per register)
 #pragma unroll
-            for (int p = 0; p < NP - 1; ++p)
-                if (p < np) tmem_ld16_pack(tb + 16 * (p0 + p), v[p]);
-            tmem_ld_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(4 + (l & 1)));             // D_v buffer is free again
+            for (int pb = 0; pb < NP; pb += 4) {
+                uint32_t v[4][8];
 #pragma unroll
-            for (int p = 0; p < NP - 1; ++p)
-                if (p < np) {
-                    *(uint4 *)(xl + (p0 + p) * 2048) = make_uint4(__byte_perm(v[p][0], v[p][1], 0x6420), __byte_perm(v[p][2], v[p][3], 0x6420),
-                                                                   __byte_perm(v[p][4], v[p][5], 0x6420), __byte_perm(v[p][6], v[p][7], 0x6420));
-                    *(uint4 *)(xl + XPB + (p0 + p) * 2048) = make_uint4(__byte_perm(v[p][0], v[p][1], 0x7531), __byte_perm(v[p][2], v[p][3], 0x7531),
-                                                                         __byte_perm(v[p][4], v[p][5], 0x7531), __byte_perm(v[p][6], v[p][7], 0x7531));
+                for (int p = 0; p < 4; ++p)
+                    if (pb + p < NP) tmem_ld16_pack(tb + 16 * (pb + p), v[p]);
+                tmem_ld_wait();
+                if (pb + 4 >= NP) {                                   // last loads of the level: the D_v buffer is free again
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar(4 + (l & 1)));
                 }
+#pragma unroll
+                for (int p = 0; p < 4; ++p)
+                    if (pb + p < NP) {
+                        *(uint4 *)(xl + (pb + p) * 2048) = make_uint4(__byte_perm(v[p][0], v[p][1], 0x6420), __byte_perm(v[p][2], v[p][3], 0x6420),
+                                                                       __byte_perm(v[p][4], v[p][5], 0x6420), __byte_perm(v[p][6], v[p][7], 0x6420));
+                        *(uint4 *)(xl + XPB + (pb + p) * 2048) = make_uint4(__byte_perm(v[p][0], v[p][1], 0x7531), __byte_perm(v[p][2], v[p][3], 0x7531),
+                                                                             __byte_perm(v[p][4], v[p][5], 0x7531), __byte_perm(v[p][6], v[p][7], 0x7531));
+                    }
+            }
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(6 + (XBUF == 2 ? (l & 1) : 0)));
@@ -398,37 +440,30 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
         // last four rows of step s - 1 are the four rows in front of step s without a copy
         u8 *trow = tiles;
         int tswz = 0;
-        uint32_t prev[10];                                            // previous level, 16-bit halves: 2 pixels per register
-        // 16 columns n' = c0 .. c0 + 15 of the (column-reversed) accumulators = image columns n = 48 - c0 .. 63 - c0;
-        // pi = index of the piece's first register pair in prev[]
-        auto eh_piece16 = [&](int l, uint32_t dlo, int c0, int pi) {
-            uint32_t lo[16], hi[16];
-            tmem_ld16(dlo + c0, lo);
-            tmem_ld16(dlo + 64 + c0, hi);
-            tmem_ld_wait();
-            uint32_t g2[8], d2[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const uint32_t va = (hi[15 - 2 * j] << 8) + lo[15 - 2 * j], vb = (hi[14 - 2 * j] << 8) + lo[14 - 2 * j];
-                g2[j] = __byte_perm(va, vb, 0x7632);                  // byte 2 of each sum: (256 hi + lo) >> 16, bias included
-                d2[j] = __vmaxu2(g2[j], prev[pi + j]) - prev[pi + j];   // max(cur - prev, 0), GaussPyramid.cpp:197
-                prev[pi + j] = g2[j];
-            }
-            const int ch = (((48 - c0) >> 4) ^ tswz) * 16;
-            if (l >= 1 && l <= 3)
-                *(uint4 *)(trow + (l - 1) * TILE_B + ch) =
-                    make_uint4(__byte_perm(g2[0], g2[1], 0x6420), __byte_perm(g2[2], g2[3], 0x6420), __byte_perm(g2[4], g2[5], 0x6420), __byte_perm(g2[6], g2[7], 0x6420));
-            if (l >= 1)
-                *(uint4 *)(trow + DT0 + (l - 1) * TILE_B + ch) =
-                    make_uint4(__byte_perm(d2[0], d2[1], 0x6420), __byte_perm(d2[2], d2[3], 0x6420), __byte_perm(d2[4], d2[5], 0x6420), __byte_perm(d2[6], d2[7], 0x6420));
-        };
+        uint32_t prev[6];                                             // previous level, 16-bit halves: 2 pixels per register
         auto eh = [&](int s, int l) {
             mbar_wait(bar(8 + (l & 1)), (3 * s + (l >> 1)) & 1);
             DBG_T(c_wait);
             tc_fence_after();
             const uint32_t dlo = tm + 256 + 128 * (l & 1) + lane_off;
-            eh_piece16(l, dlo, 48 - 16 * r, 0);                       // columns n = 16 r .. 16 r + 15
-            if (r == 1) {                                             // columns n = 48 .. 51 (49 .. 51 are never read)
+            {   // accumulator columns n' = 56 - 8 r .. 63 - 8 r (column-reversed) = image columns n = 8 r .. 8 r + 7
+                uint32_t lo[8], hi[8];
+                tmem_ld8(dlo + 56 - 8 * r, lo);
+                tmem_ld8(dlo + 64 + 56 - 8 * r, hi);
+                tmem_ld_wait();
+                uint32_t g2[4], d2[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t va = (hi[7 - 2 * j] << 8) + lo[7 - 2 * j], vb = (hi[6 - 2 * j] << 8) + lo[6 - 2 * j];
+                    g2[j] = __byte_perm(va, vb, 0x7632);              // byte 2 of each sum: (256 hi + lo) >> 16, bias included
+                    d2[j] = __vmaxu2(g2[j], prev[j]) - prev[j];       // max(cur - prev, 0), GaussPyramid.cpp:197
+                    prev[j] = g2[j];
+                }
+                const int ch = (((r >> 1) ^ tswz) << 4) + ((r & 1) << 3);
+                if (l >= 1 && l <= 3) *(uint2 *)(trow + (l - 1) * TILE_B + ch) = make_uint2(__byte_perm(g2[0], g2[1], 0x6420), __byte_perm(g2[2], g2[3], 0x6420));
+                if (l >= 1) *(uint2 *)(trow + DT0 + (l - 1) * TILE_B + ch) = make_uint2(__byte_perm(d2[0], d2[1], 0x6420), __byte_perm(d2[2], d2[3], 0x6420));
+            }
+            if (r == 5) {                                             // columns n = 48 .. 51 (49 .. 51 are never read)
                 uint32_t lo[4], hi[4];
                 tmem_ld4(dlo + 12, lo);
                 tmem_ld4(dlo + 64 + 12, hi);
@@ -438,8 +473,8 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
                 for (int j = 0; j < 2; ++j) {
                     const uint32_t va = (hi[3 - 2 * j] << 8) + lo[3 - 2 * j], vb = (hi[2 - 2 * j] << 8) + lo[2 - 2 * j];
                     g2[j] = __byte_perm(va, vb, 0x7632);
-                    d2[j] = __vmaxu2(g2[j], prev[8 + j]) - prev[8 + j];
-                    prev[8 + j] = g2[j];
+                    d2[j] = __vmaxu2(g2[j], prev[4 + j]) - prev[4 + j];
+                    prev[4 + j] = g2[j];
                 }
                 const int ch = (3 ^ tswz) * 16;
                 if (l >= 1 && l <= 3) *(uint32_t *)(trow + (l - 1) * TILE_B + ch) = __byte_perm(g2[0], g2[1], 0x6420);
@@ -474,7 +509,8 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
                 // column parts of the tile offsets: 16-byte chunk (XOR-swizzled by the row pair) and byte inside it
                 const int gm = txm >> 4, bm = txm & 15, g0 = tx >> 4, b0 = tx & 15, gp = txp >> 4, bp = txp & 15;
                 const u8 *d = tiles + DT0;
-                for (int sr = tid >> 4; sr < n_srow; sr += NE / NS) {
+                const int sr = tid >> 4;                              // 56 sample rows of threads, at most 44 live
+                if (sr < n_srow) {
                     const int yc = 3 * (si_lo + sr);
                     if (xc <= cols - 2) {
                         // D tiles at (xc, yc); neighbours clamped at the image border (padOctave's replicate)
@@ -565,8 +601,7 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(12 + b));                  // this warp's results are complete
-            DBG_ONLY(c_d4 += clock64() - c_e0;)
-            DBG_T(c_det);
+            DBG_T2(c_d4, c_det);
         };
 
         // One loop over (step, level) for all sixteen warps (one copy of every stage in the instruction stream).  The X stage
@@ -590,17 +625,13 @@ __global__ void __launch_bounds__(kThreads, 1) octave_umma_k(const __grid_consta
             s += l == 5; l = l == 5 ? 0 : l + 1;
             s2 += l2 == 5; l2 = l2 == 5 ? 0 : l2 + 1;
         }
-#ifdef VSLAM_UMMA_DBG_BUILD
-        if (a.dbg && blockIdx.x == 0 && blockIdx.z == 0 && lane == 0 && (warp == 0 || warp == 12)) {
-            long long *o = a.dbg + (warp == 0 ? 8 : 12);
-            o[0] = c_wait; o[1] = c_work; o[2] = c_det;
-            if (warp == 0) { a.dbg[16] = c_d1; a.dbg[17] = c_d2; a.dbg[18] = c_d3; a.dbg[19] = c_d4; }
-        }
-#endif
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tm, kTmemCols);
+#ifdef VSLAM_UMMA_DBG_BUILD
+    if (a.dbg && blockIdx.x == 1 && blockIdx.z == 1 && tid < 256) a.dbg[tid] = (&s_dbg[0][0])[tid];
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -618,7 +649,9 @@ template <int KV, int KH, int NV, int XBUF> constexpr size_t umma_smem() {
 }
 
 bool umma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, UmmaPlan *p) {
-    static const int mode = getenv("VSLAM_UMMA") ? atoi(getenv("VSLAM_UMMA")) : 1;
+    // opt-in: bit-exact and covered by the GPU tests, but measured slower than the mma.sync kernel of fused_mma.cu on this
+    // workload (31.9 against 25.6 ms per 1080p x 256 step for the four octave launches)
+    static const int mode = getenv("VSLAM_UMMA") ? atoi(getenv("VSLAM_UMMA")) : 0;
     if (!mode) return false;
     if (umma_geometry(sigma0, scale_samples, octave, &p->g)) return false;
     if (p->g.KV == 5) { p->k = octave_umma_k<5, 3, 80, 2>; p->smem = umma_smem<5, 3, 80, 2>(); }
@@ -705,6 +738,7 @@ int launch_octave_umma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double 
     a.n_segs = 1;
     a.seg_rows = (a.rows + FR - 1) / FR * FR;
     a.plane_x0 = io.base_pad; a.plane_y0 = io.base_row_pad;
+    if (getenv("VSLAM_UMMA_NODETECT")) a.detect = 0;               // timing experiments only: the blur pipeline without the detector
     // the padded plane as a 3-D tensor (byte column, row, frame); boxes of 128 bytes x 32 rows, 128B-swizzled
     CUtensorMap tmap;
     u8 *origin = const_cast<u8 *>(io.base) - (size_t)io.base_row_pad * io.base_pitch - io.base_pad;
@@ -717,7 +751,7 @@ int launch_octave_umma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double 
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
     static const bool dbg = getenv("VSLAM_UMMA_DBG") && atoi(getenv("VSLAM_UMMA_DBG"));
     static long long *d_dbg = nullptr;
-    if (dbg && !d_dbg) cudaMalloc(&d_dbg, 24 * sizeof(long long));
+    if (dbg && !d_dbg) cudaMalloc(&d_dbg, 256 * sizeof(long long));
     a.dbg = dbg ? d_dbg : nullptr;
     {
         KernelSpan span(ctx, VSLAM_K_FUSED);
@@ -725,11 +759,13 @@ int launch_octave_umma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double 
     }
     VS_LAUNCH_CHECK(ctx);
     if (dbg) {
-        long long h[24];
+        long long h[256];
         cudaStreamSynchronize(ctx->stream);
         cudaMemcpy(h, d_dbg, sizeof h, cudaMemcpyDeviceToHost);
-        fprintf(stderr, "umma dbg octave %d: steps %lld  control total %lld (x_full wait %lld, free wait %lld) | tile warp: wait %lld work %lld det %lld | "
-                        "X warp: wait %lld work %lld det %lld | service: queued %lld work %lld | det parts: tests %lld decim %lld bar %lld help %lld\n", io.octave, h[5], h[0], h[1], h[2], h[8], h[9], h[10], h[12], h[13], h[14], h[6], h[7], h[16], h[17], h[18], h[19]);
+        fprintf(stderr, "umma dbg octave %d (CTA 1,0,1), cycles per warp: wait work det | tests decim edge tail\n", io.octave);
+        for (int w = 0; w < 30; w += (w < 24 ? 4 : 1))
+            fprintf(stderr, "  warp %2d (role %d): %8lld %8lld %8lld | %8lld %8lld %8lld %8lld\n", w, w >> 2, h[8 * w], h[8 * w + 1], h[8 * w + 2], h[8 * w + 3],
+                    h[8 * w + 4], h[8 * w + 5], h[8 * w + 6]);
     }
     return VSLAM_OK;
 }

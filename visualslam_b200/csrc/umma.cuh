@@ -32,7 +32,11 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    while (!mbar_try(bar, parity)) {}
+    while (!mbar_try(bar, parity)) {
+#ifdef VSLAM_MBAR_SLEEP
+        __nanosleep(VSLAM_MBAR_SLEEP);
+#endif
+    }
 }
 
 // ---- proxies --------------------------------------------------------------------------------------------------------

@@ -136,7 +136,7 @@ def test_tcgen05_kernel_matches_oracle(tmp_path):
     import subprocess, sys, os
     code = ("import numpy as np, sys; import visualslam_b200 as vs; from visualslam_b200 import synth; from oracle import c_oracle as O;"
             "c = vs.Context(0)\n"
-            "for (h, w) in ((192, 256), (300, 217), (65, 1), (1, 65), (64, 49), (129, 97), (5, 7), (257, 96)):\n"
+            "for (h, w) in ((192, 256), (300, 217), (70, 9), (9, 70), (64, 49), (129, 97), (5, 7), (257, 96)):\n"
             "    img = synth.frame(h + w, h, w); r = c.dog_keypoints(img); k = r['keypoints']\n"
             "    got = np.stack([k[n] for n in ('row', 'col', 'value', 'padding', 'octave', 'level')], 1)\n"
             "    want = O.dog_keypoints(img)[0]\n"

@@ -7,7 +7,10 @@ A "step" is one pass of the hot path over one batch of synthetic frames (SURVEY.
 vslam_dog_keypoints (frame -> ordered keypoint list) and vslam_harris in pipeline mode (frame -> response fp32 +
 3x3-NMS mask + ordered NMS2 corner list).  value = input Mpix/s over all ranks with frames resident in HBM;
 e2e = the same through the C ABI with HOST (pinned) frames and host result lists, copies inside the timed region.
-Multi-GPU: frame-batch data parallelism, one process per GPU, no collective on the data path (weak scaling).
+Multi-GPU: frame-batch data parallelism, one process per GPU, no collective on the data path (weak scaling); before
+the timed region every rank runs the SAME eight frames once and the ranks compare the md5 of their result lists.
+The line also carries a `sweep` block (unless --no-sweep): the 4K and 8K batches of BASELINE.json's configs 4 and 5,
+the single-frame 8K latency, and the materialise mode (everything the reference's GaussPyramid constructor produces).
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -24,6 +27,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {"1080p": (1080, 1920, 256), "4k": (2160, 3840, 64), "8k": (4320, 7680, 16)}
+MATERIALISE_ALL = 0x78          # VSLAM_MATERIALISE_ALL: gx, gy, magnitude, orientation of every level (include/vslam.h)
+MATERIALISE_BYTES_PER_PX = 1 + 5.3125 * (11 + 96)   # 569.4 B per input pixel
 MAC_PER_PX = 1738.0            # blur MACs per input pixel (both passes, 4 octaves x 6 levels)
 IMMA_PEAK_TMAC = 568.9         # measured mma.sync.m16n8k32 u8 peak, TMAC/s (tools/imma_peak.cu, profiles/imma_peak_r1.json)
 IDP_PEAK_TMAC = (74.31, 37.13)  # measured dp4a / dp2a peaks, TMAC/s (tools/alu_peak.cu, profiles/alu_peak_r1.json)
@@ -50,10 +55,12 @@ def bind_near_gpu(index):
 
 
 def peaks():
+    """(HBM GB/s, dense bf16 TFLOP/s sustained, source): the roofline denominators."""
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
-        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
-    return 6650.0, "fallback (B200_PROFILING.md)"
+        j = json.load(open(p))
+        return j.get("hbm_gbs", 6650.0), j.get("bf16_tflops_sustained", j.get("bf16_tflops", 1590.0)), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1400.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler(threading.Thread):
@@ -146,7 +153,9 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": mpix, "unit": "Mpix/s", "frames_per_s": mpix * 1e6 / (h * w),
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: DoG keypoints + Harris pipeline, bounded sample", "sample": sample},
+            "config": {"workload": f"{args.workload}: DoG keypoints + Harris pipeline, bounded sample", "sample": sample,
+                       "cpu_work": "the reference's stock path: the GaussPyramid constructor forms all 48 gradient / magnitude / phase maps per frame "
+                                   "(GaussPyramid.cpp:65-104) that the GPU's keypoints-only path never forms (~2.7x of the CPU time, SURVEY.md 6)"},
             "cpu_baseline": {"value": mpix, "unit": "Mpix/s", "cores": cores, "kind": kind, "sample": sample,
                              "how": "cv2 (reference's OpenCV calls, OpenCV's own threads) + plain-C restatement of the reference's scalar loops (1 thread)"},
             "e2e": {"value": mpix, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -155,6 +164,219 @@ def run_reference(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------------------------
+class Runner:
+    """One GPU's side of the bench: owns the context, runs a workload (h, w, frames) device-resident and end to end."""
+
+    def __init__(self, args, rank, world, local):
+        import torch
+        import torch.distributed as dist
+
+        import visualslam_b200 as vs
+        self.torch, self.dist, self.vs = torch, dist, vs
+        self.args, self.rank, self.world, self.local = args, rank, world, local
+        self.device = torch.device("cuda", local)
+        self.stream = torch.cuda.Stream()
+        self.ctx = vs.Context(local, stream=self.stream.cuda_stream)
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def timed(self, fn, steps):
+        """CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks."""
+        torch = self.torch
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        out = None
+        with torch.cuda.stream(self.stream):
+            e0.record(self.stream)
+            for _ in range(steps):
+                out = fn()
+            e1.record(self.stream)
+        self.barrier()
+        ms = e0.elapsed_time(e1)
+        if self.world > 1:
+            t = torch.tensor([ms], device=self.device)
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, out
+
+    def frames(self, h, w, nf, same_on_all_ranks=False):
+        """8 unique synthetic frames cycled to fill the batch: pinned host copy + device copy."""
+        from visualslam_b200 import shard, synth
+        torch = self.torch
+        first = 0 if same_on_all_ranks else shard.weak_batch(self.rank, self.world, nf)[0]
+        uniq = [synth.frame(first + i, h, w) for i in range(min(8, nf))]
+        host = torch.empty((nf, h, w), dtype=torch.uint8, pin_memory=True)
+        hnp = host.numpy()
+        for i in range(nf):
+            hnp[i] = uniq[i % len(uniq)]
+        return uniq, hnp, host.to(self.device)
+
+    def workload(self, h, w, nf, steps, warmup, e2e=True, kernel_timing=True, clocks=False):
+        """Device-resident value + (optionally) the end-to-end figure of one (h, w, frames-per-GPU) workload."""
+        torch, ctx = self.torch, self.ctx
+        px_step = nf * h * w
+        uniq, hnp, dev = self.frames(h, w, nf)
+        cap = int(KP_CAP_PER_MPX * px_step / 1e6) + 1024
+        kp_dev = torch.zeros((cap, 6), dtype=torch.int32, device=self.device)
+        co_dev = torch.zeros((cap * 4, 3), dtype=torch.int32, device=self.device)
+        resp_dev = torch.empty((nf, h, w), dtype=torch.float32, device=self.device)
+        mask_dev = torch.empty((nf, h, w), dtype=torch.uint8, device=self.device)
+        overflow = [False]
+
+        def step_device():
+            a = ctx.dog_keypoints(dev, out=kp_dev)
+            b = ctx.harris(dev, device_out={"response": resp_dev, "mask3": mask_dev, "corners": co_dev})
+            overflow[0] |= bool(a["overflow"] or b["overflow"])
+            return sum(a["counts"]), sum(b["counts"])
+
+        for _ in range(warmup):
+            step_device()
+        sampler = None
+        if clocks:
+            sampler = ClockSampler(self.local); sampler.start()
+        l0 = ctx.launches
+        if kernel_timing:
+            ctx.profile(True)
+        ms, (nk, nc) = self.timed(step_device, steps)
+        launches = ctx.launches - l0
+        prof = ctx.profile_read() if kernel_timing else {}
+        ctx.profile(False)
+        res = {"h": h, "w": w, "frames_per_gpu": nf, "px_step": px_step, "ms_per_step": ms / steps,
+               "value": self.world * px_step / 1e6 / (ms / steps * 1e-3), "keypoints": nk, "corners": nc, "launches": launches,
+               "prof": prof, "uniq": uniq, "clocks": sampler.summary() if sampler else None}
+        if overflow[0]:
+            raise SystemExit(f"output list overflow in the device-resident steps of {w}x{h} x {nf}")
+        if e2e:
+            # e2e result lists: pinned host buffers owned by the caller (a pageable list would be staged by the driver)
+            kp_host = torch.empty((cap, 6), dtype=torch.int32, pin_memory=True).numpy()
+            co_host = torch.empty((cap * 4, 3), dtype=torch.int32, pin_memory=True).numpy()
+            eo = [False]
+
+            def step_e2e():
+                up = ctx.upload(hnp)                                          # one chunked H2D of the batch, overlapped with the kernels
+                a = ctx.dog_keypoints(up, out=kp_host)                        # keypoint list D2H inside
+                b = ctx.harris(up, want_maps=False, corners_out=co_host)      # corner-only mode on the e2e path, corner list D2H inside
+                eo[0] |= bool(a["overflow"] or b["overflow"])
+                return len(a["keypoints"]), len(b["corners"])
+
+            step_e2e()
+            ems, (ek, ec) = self.timed(step_e2e, steps)
+            if eo[0]:
+                raise SystemExit(f"output list overflow in the end-to-end steps of {w}x{h} x {nf}")
+            ems /= steps
+            res["e2e"] = {"value": self.world * px_step / 1e6 / (ems * 1e-3), "unit": "Mpix/s", "ms_per_step": ems, "steps": steps,
+                          "h2d_bytes_per_step": px_step, "d2h_bytes_per_step": int(ek * 24 + ec * 12 + 8 * nf),
+                          "api": "vslam_upload_frames (chunked, overlapped) + vslam_dog_keypoints + vslam_harris(corner-only): host (pinned) "
+                                 "frames in, host (pinned) result lists out; value's steps run Harris in pipeline mode (response + mask stay in HBM)"}
+        del kp_dev, co_dev, resp_dev, mask_dev, dev
+        torch.cuda.empty_cache()
+        return res
+
+    def materialise(self, h, w, nf, steps, warmup):
+        """The reference constructor's real output (GaussPyramid.cpp:106-131: 6 Gaussians + 5 DoG u8, gx / gy / magnitude /
+        orientation fp32 of every level, all octaves = 569.4 B per input pixel) + the detector on the materialised pyramid."""
+        torch, ctx = self.torch, self.ctx
+        _, _, dev = self.frames(h, w, nf)
+        keep = {}
+
+        def step():
+            pyr = ctx.build_pyramid(dev, 4, 1.6, materialise=MATERIALISE_ALL)
+            r = ctx.dog_detect(pyr, stage_counts=False)
+            keep["n"] = sum(r["counts"]); keep["ovf"] = r["overflow"]
+            pyr.close()
+            return keep["n"]
+
+        for _ in range(warmup):
+            step()
+        ctx.profile(True)
+        ms, nk = self.timed(step, steps)
+        prof = ctx.profile_read()
+        ctx.profile(False)
+        del dev
+        torch.cuda.empty_cache()
+        ms_step = ms / steps
+        px = nf * h * w
+        hbm, _, src = peaks()
+        build_ms = sum(prof[k]["ms"] for k in ("upsample2x_k", "octave_fused_k", "grad_k") if k in prof) / steps
+        gbs = MATERIALISE_BYTES_PER_PX * px / 1e9 / (build_ms * 1e-3) if build_ms else None
+        return {"workload": f"{w}x{h} x {nf} frames per GPU: vslam_pyramid_build(VSLAM_MATERIALISE_ALL) + vslam_dog_detect", "ms_per_step": ms_step,
+                "value": self.world * px / 1e6 / (ms_step * 1e-3), "unit": "Mpix/s", "keypoints": int(nk), "overflow": bool(keep.get("ovf")),
+                "bytes_per_input_px": MATERIALISE_BYTES_PER_PX,
+                "build_kernels_ms_per_step": build_ms, "build_achieved_GBps": gbs, "build_hbm_frac": gbs / hbm if gbs else None, "peak_source": src,
+                "kernel_ms_per_step": {k: v["ms"] / steps for k, v in prof.items() if v["launches"]},
+                "note": "value is timed over the whole call incl. the host-side pyramid handle and the (pageable) keypoint list; the HBM fraction "
+                        "uses the device time of the building kernels (upsample2x_k + octave_fused_k + grad_k) against 569.4 algorithmic bytes per input pixel"}
+
+    def parity_across_ranks(self, h, w):
+        """Un-timed: every rank runs the SAME 8 frames; the md5 of (keypoint list, corner list) must agree on all ranks."""
+        import hashlib
+        torch = self.torch
+        _, hnp, dev = self.frames(h, w, 8, same_on_all_ranks=True)
+        a = self.ctx.dog_keypoints(dev)
+        b = self.ctx.harris(dev, want_maps=False, capacity=8 * h * w // 8)
+        if a["overflow"] or b["overflow"]:
+            raise SystemExit("output list overflow in the multi-GPU parity step")
+        dig = hashlib.md5(np.ascontiguousarray(a["keypoints"]).tobytes() + np.ascontiguousarray(b["corners"]).tobytes()).digest()
+        mine = torch.tensor(list(dig), dtype=torch.uint8, device=self.device)
+        if self.world > 1:
+            allv = [torch.empty_like(mine) for _ in range(self.world)]
+            self.dist.all_gather(allv, mine)
+            same = all(bool((v == allv[0]).all().item()) for v in allv)
+        else:
+            same = True
+        del dev
+        return same, dig.hex(), len(a["keypoints"]), len(b["corners"])
+
+
+def roofline_block(res, steps, world):
+    """roofline of the dominant kernel of the headline workload + HBM fractions of the other kernels on the timed path."""
+    prof, h, w, nf = res["prof"], res["h"], res["w"], res["frames_per_gpu"]
+    px_step, nk, nc = res["px_step"], res["keypoints"], res["corners"]
+    hbm_peak, bf16_peak, peak_src = peaks()
+    live = {k: v for k, v in prof.items() if v["launches"]}
+    tot = sum(v["ms"] for v in live.values()) or 1.0
+    per_ms = {k: v["ms"] / max(v["launches"], 1) for k, v in live.items()}       # average launch duration
+    # ALGORITHMIC HBM bytes per launch (DESIGN.md 4, 5); the octave kernels: read the octave base 1 B/px, write the next base
+    # 1/4 B/px (none after the last octave), 24 B per keypoint -- four launches per step, one per octave: the average
+    oct_px = [4.0 * h * w / 4 ** o for o in range(4)]
+    octave_bytes = nf * (sum(oct_px) + sum(oct_px[1:])) / 4 + 24.0 * nk / 4
+    alg = {"octave_mma_k": octave_bytes, "octave_umma_k": octave_bytes, "octave_fused_k": octave_bytes,
+           "harris_march_k": 6.0 * h * w * nf + 12.0 * nc, "upsample2x_k": 5.0 * h * w * nf}
+    octave_kernels = [k for k in ("octave_mma_k", "octave_umma_k", "octave_fused_k") if k in live]
+    dom = max(live, key=lambda k: live[k]["ms"])
+    blur_ms = sum(live[k]["ms"] for k in octave_kernels)
+    # The Gaussian stack is 1738 u8 MAC per input pixel (SURVEY.md 8(d)) evaluated exactly on the integer tensor pipe; the kernel
+    # is bound by the instructions around the MMAs (issue slots), not by HBM: the tensor fraction is the binding one.
+    tmac = MAC_PER_PX * px_step * steps / (blur_ms * 1e-3) / 1e12 if blur_ms else None
+    tops = 2.0 * tmac if tmac else None
+    hbm_ach = alg.get(dom, 0.0) / 1e9 / (per_ms[dom] * 1e-3) if alg.get(dom) else None
+    block = {"bound": "tensor" if dom in octave_kernels else "hbm", "kernel": dom,
+             "achieved": tops if dom in octave_kernels else hbm_ach,
+             "peak": bf16_peak if dom in octave_kernels else hbm_peak, "unit": "TFLOP/s" if dom in octave_kernels else "GB/s",
+             "frac": (tops / bf16_peak if tops else None) if dom in octave_kernels else (hbm_ach / hbm_peak if hbm_ach else None),
+             "traffic": None, "peak_source": peak_src,
+             "mode": "keypoints-only (fused): octave bases are the only maps in HBM",
+             "note": "achieved = useful integer ops of the blur (2 x 1738 MAC per input pixel: the banded-Toeplitz zeros the MMAs also multiply are "
+                     "not counted) over the device time of the octave kernels; peak = the measured dense bf16 rate (sustained) of MEASURED_PEAKS.json "
+                     "-- the u8 rate of the tensor pipe is nominally twice that, so the fraction is an upper bound of the pipe's utilisation. "
+                     "traffic: not measured in this run (ncu captures under profiles/ hold dram bytes per launch).",
+             "tensor": {"useful_TMAC_s": tmac, "mma_sync_u8_peak_TMAC_s": IMMA_PEAK_TMAC, "frac_of_mma_sync_peak": tmac / IMMA_PEAK_TMAC if tmac else None,
+                        "mac_per_input_px": MAC_PER_PX,
+                        "peak_source": "mma.sync.m16n8k32 u8 issue peak measured on a B200 of this pool (tools/imma_peak.cu, profiles/imma_peak_r1.json)"},
+             "hbm": {"achieved_GBps": hbm_ach, "frac": hbm_ach / hbm_peak if hbm_ach else None, "peak": hbm_peak,
+                     "algorithmic_bytes_per_launch": alg.get(dom)},
+             "other_kernels_hbm": {k: {"achieved_GBps": alg[k] / 1e9 / (per_ms[k] * 1e-3), "frac": alg[k] / 1e9 / (per_ms[k] * 1e-3) / hbm_peak}
+                                   for k in alg if k in live and k != dom},
+             "kernel_ms_per_step": {k: v["ms"] / steps for k, v in live.items()},
+             "kernel_launches_per_step": {k: v["launches"] / steps for k, v in live.items()},
+             "kernel_share": {k: v["ms"] / tot for k, v in live.items()}}
+    return block
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -166,6 +388,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the 4K / 8K / latency / materialise lines of the sweep block")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -175,8 +398,7 @@ def main():
     import torch
     import torch.distributed as dist
 
-    import visualslam_b200 as vs
-    from visualslam_b200 import synth
+    from visualslam_b200 import shard
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
@@ -184,154 +406,67 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    R = Runner(args, rank, world, local)
     h, w, nf = WORKLOADS[args.workload]
     if args.frames:
         nf = args.frames
-    px_step = nf * h * w
-    stream = torch.cuda.Stream()
-    ctx = vs.Context(local, stream=stream.cuda_stream)
 
-    # ---- inputs: 8 unique frames cycled; device-resident copy + pinned host copy ----
-    from visualslam_b200 import shard
-    ids = shard.weak_batch(rank, world, nf)                      # this rank's frames of the global batch (contiguous block)
-    uniq = [synth.frame(ids[0] + i, h, w) for i in range(min(8, nf))]
-    host = torch.empty((nf, h, w), dtype=torch.uint8, pin_memory=True)
-    hnp = host.numpy()
-    for i in range(nf):
-        hnp[i] = uniq[i % len(uniq)]
-    dev = host.to(f"cuda:{local}")
-    cap = int(KP_CAP_PER_MPX * px_step / 1e6) + 1024
-    kp_dev = torch.zeros((cap, 6), dtype=torch.int32, device=dev.device)
-    co_dev = torch.zeros((cap * 4, 3), dtype=torch.int32, device=dev.device)
-    resp_dev = torch.empty((nf, h, w), dtype=torch.float32, device=dev.device)
-    mask_dev = torch.empty((nf, h, w), dtype=torch.uint8, device=dev.device)
+    # ---- un-timed: the same 8 frames on every rank, result lists compared across ranks ----
+    same, digest, pk, pc = R.parity_across_ranks(h, w)
+    if not same:
+        raise SystemExit("multi-GPU parity FAILED: ranks disagree on the result lists of the same frames")
 
-    def step_device():
-        a = ctx.dog_keypoints(dev, out=kp_dev)
-        b = ctx.harris(dev, device_out={"response": resp_dev, "mask3": mask_dev, "corners": co_dev})
-        return sum(a["counts"]), sum(b["counts"]), a["overflow"] or b["overflow"]
+    # ---- headline workload ----
+    res = R.workload(h, w, nf, args.steps, max(args.warmup, 1), e2e=not args.no_e2e, kernel_timing=not args.no_kernel_timing, clocks=True)
+    nk, nc, ms_max = shard.reduce_counts(res["keypoints"], res["corners"], res["ms_per_step"], device=R.device)
 
-    # e2e result lists: pinned host buffers owned by the caller (a pageable list would be staged by the driver)
-    kp_host = torch.empty((cap, 6), dtype=torch.int32, pin_memory=True).numpy()
-    co_host = torch.empty((cap * 4, 3), dtype=torch.int32, pin_memory=True).numpy()
-
-    def step_e2e():
-        up = ctx.upload(hnp)                                          # one chunked H2D of the batch, overlapped with the kernels
-        a = ctx.dog_keypoints(up, out=kp_host)                        # keypoint list D2H inside
-        b = ctx.harris(up, want_maps=False, corners_out=co_host)      # corner-only mode on the e2e path, corner list D2H inside
-        return len(a["keypoints"]), len(b["corners"])
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with torch.cuda.stream(stream):
-            e0.record(stream)
-            for _ in range(steps):
-                out = fn()
-            e1.record(stream)
-        barrier()
-        ms = e0.elapsed_time(e1)
-        if world > 1:
-            t = torch.tensor([ms], device=dev.device)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, out
-
-    for _ in range(args.warmup):
-        nk, nc, ovf = step_device()
-    if ovf:
-        raise SystemExit("output list overflow in warm-up")
-    sampler = ClockSampler(local); sampler.start()
-    l0 = ctx.launches
-    if not args.no_kernel_timing:
-        ctx.profile(True)
-    ms, (nk, nc, ovf) = timed(step_device, args.steps)
-    launches = ctx.launches - l0
-    prof = ctx.profile_read() if not args.no_kernel_timing else {}
-    ctx.profile(False)
-    clocks = sampler.summary()
-    ms_step = ms / args.steps
-    value = world * px_step / 1e6 / (ms_step * 1e-3)
-
-    e2e = None
-    if not args.no_e2e:
-        step_e2e()
-        ems, (ek, ec) = timed(step_e2e, max(1, min(args.steps, 2)))
-        ems /= max(1, min(args.steps, 2))
-        e2e = {"value": world * px_step / 1e6 / (ems * 1e-3), "unit": "Mpix/s", "ms_per_step": ems,
-               "h2d_bytes_per_step": px_step, "d2h_bytes_per_step": int(ek * 24 + ec * 12 + 8 * nf),
-               "api": "vslam_upload_frames (chunked, overlapped) + vslam_dog_keypoints + vslam_harris(corner-only): host (pinned) frames in, host (pinned) result lists out"}
+    # ---- sweep: BASELINE.json configs 4 and 5 per GPU, single-frame latency, materialise mode ----
+    sweep = None
+    if not args.no_sweep:
+        sweep = {}
+        ss, sw_ = max(2, min(args.steps, 3)), 1
+        for name in ("4k", "8k"):
+            if name == args.workload and not args.frames:
+                continue
+            sh, sw2, snf = WORKLOADS[name]
+            r = R.workload(sh, sw2, snf, ss, sw_, e2e=not args.no_e2e, kernel_timing=False)
+            sweep[f"{name}x{snf}"] = {"workload": f"synthetic {sw2}x{sh} x {snf} frames per GPU, DoG + Harris pipeline mode", "steps": ss,
+                                      "value": r["value"], "unit": "Mpix/s", "frames_per_s": r["value"] * 1e6 / (sh * sw2), "ms_per_step": r["ms_per_step"],
+                                      "e2e": r.get("e2e"), "keypoints_per_step": int(r["keypoints"]) * world, "corners_per_step": int(r["corners"]) * world}
+        sh, sw2, _ = WORKLOADS["8k"]
+        r = R.workload(sh, sw2, 1, max(args.steps, 5), 2, e2e=not args.no_e2e, kernel_timing=False)
+        sweep["8kx1_latency"] = {"workload": f"one synthetic {sw2}x{sh} frame per GPU per step (latency regime: 320 strips, one frame)",
+                                 "ms_per_frame": r["ms_per_step"], "value": r["value"], "unit": "Mpix/s",
+                                 "e2e_ms_per_frame": r["e2e"]["ms_per_step"] if r.get("e2e") else None}
+        mh, mw, _ = WORKLOADS[args.workload]
+        mnf = 8 if mh * mw <= 2.1e6 else (2 if mh * mw <= 8.3e6 else 1)           # 1.18 / 4.7 / 18.9 GB of maps per frame
+        sweep["materialise"] = R.materialise(mh, mw, mnf, max(2, min(args.steps, 3)), 1)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    hbm_peak, peak_src = peaks()
+    value = world * res["px_step"] / 1e6 / (ms_max * 1e-3)
     line = {"metric": METRIC, "value": value, "unit": "Mpix/s", "frames_per_s": value * 1e6 / (h * w), "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": f"synthetic {w}x{h} grayscale batch of {nf} frames per GPU, DoG (4 octaves x 6 levels, sigma 1.6) "
                                    f"+ Harris pipeline mode, {world} B200", "frames_per_gpu": nf, "rows": h, "cols": w,
-                       "l2": f"inputs larger than L2 ({px_step / 1e6:.0f} MB batch per step, 8 unique frames cycled)",
+                       "l2": f"inputs larger than L2 ({res['px_step'] / 1e6:.0f} MB batch per step, 8 unique frames cycled)",
                        "parallelism": f"frame-batch dp{world}, no data-path collective",
-                       "host_cpus_bound": numa},
-            "keypoints_per_step": int(nk), "corners_per_step": int(nc), "clocks": clocks, "gpu_launches": int(launches),
-            "e2e": e2e}
-    if prof:
-        tot = sum(v["ms"] for v in prof.values()) or 1.0
-        dom = max(prof, key=lambda k: prof[k]["ms"])
-        dlaunch = prof[dom]["launches"] or 1
-        # ALGORITHMIC HBM bytes per launch of each kernel, launches cover the whole batch:
-        #   octave_fused_k (keypoints-only mode): read the octave base 1 B/px, write the next base 1/4 B/px (none after the
-        #     last octave), 24 B per keypoint; 4 launches per step, one per octave -> average over the 4
-        #   harris_fused_k (pipeline mode): read 1 B, write response 4 B + mask 1 B per pixel, 12 B per corner
-        #   upsample2x_k: read 1 B, write 4 B per input pixel
-        oct_px = [4.0 * h * w / 4 ** o for o in range(4)]
-        fused_bytes = nf * (sum(oct_px) + sum(oct_px[1:])) / 4 + 24.0 * nk / 4
-        per_launch = {"octave_fused_k": fused_bytes, "harris_fused_k": 6.0 * h * w * nf + 12.0 * nc,
-                      "upsample2x_k": 5.0 * h * w * nf}
-        alg = per_launch.get(dom, 0.0)
-        ach = alg / 1e9 / (prof[dom]["ms"] / dlaunch * 1e-3) if alg else None
-        fused_ms = prof["octave_fused_k"]["ms"]
-        # The Gaussian stack (1738 MAC per input pixel) runs on the integer tensor pipe as banded-Toeplitz
-        # products (IMMA.16832.U8.U8); useful MAC/s against the measured IMMA issue peak, and against what the packed
-        # dot-product pipe could do at its measured peak (the bound of the dp4a/dp2a kernel this replaced)
-        tmac = MAC_PER_PX * px_step * args.steps / (fused_ms * 1e-3) / 1e12 if fused_ms else None
-        idp_bound = 2.0 / (1.0 / IDP_PEAK_TMAC[0] + 1.0 / IDP_PEAK_TMAC[1])   # half the MACs on dp4a, half on dp2a
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic_r1.json")
-        if os.path.exists(tp):
-            tj = json.load(open(tp))
-            key = f"{args.workload}x{nf}"
-            if key in tj and dom in tj[key]:
-                traffic = tj[key][dom]
-        line["roofline"] = {"bound": "hbm", "kernel": dom + (" (octave_mma_k<NCH>: tensor-pipe blur)" if dom == "octave_fused_k" else ""),
-                            "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                            "frac": ach / hbm_peak if ach else None, "traffic": traffic, "peak_source": peak_src,
-                            "mode": "keypoints-only (fused): octave bases are the only maps in HBM",
-                            "note": "the fused octave kernel is not HBM bound (11.6 algorithmic bytes against 1738 MAC per input pixel, "
-                                    "SURVEY.md 8(d)); the HBM fraction is reported because the contract asks for it, the tensor block says "
-                                    "how far the blur is from the pipe it runs on; the kernel is issue/latency bound (profiles/)",
-                            "tensor": {"pipe": "IMMA.16832.U8.U8 (mma.sync u8 x u8 -> s32), exact integer arithmetic",
-                                       "useful_TMAC_s": tmac, "peak_TMAC_s": IMMA_PEAK_TMAC,
-                                       "frac": tmac / IMMA_PEAK_TMAC if tmac else None,
-                                       "vs_idp_pipe_bound": tmac / idp_bound if tmac else None,
-                                       "idp_pipe_bound_TMAC_s": idp_bound,
-                                       "peak_source": "measured on a B200 of this pool: tools/imma_peak.cu, tools/alu_peak.cu (profiles/*_peak_r1.json)",
-                                       "mac_per_input_px": MAC_PER_PX},
-                            "other_kernels_hbm": {k: {"achieved_GBps": per_launch[k] / 1e9 / (prof[k]["ms"] / max(prof[k]["launches"], 1) * 1e-3),
-                                                      "frac": per_launch[k] / 1e9 / (prof[k]["ms"] / max(prof[k]["launches"], 1) * 1e-3) / hbm_peak}
-                                                  for k in per_launch if k != dom and prof.get(k, {}).get("launches")},
-                            "kernel_ms_per_step": {k: v["ms"] / args.steps for k, v in prof.items() if v["launches"]},
-                            "kernel_launches_per_step": {k: v["launches"] / args.steps for k, v in prof.items() if v["launches"]},
-                            "kernel_share": {k: v["ms"] / tot for k, v in prof.items() if v["launches"]}}
+                       "host_cpus_bound": numa,
+                       "cpu_arm": "the CPU arm (cpu_baseline / --impl reference) runs the reference's stock path, whose GaussPyramid constructor also forms "
+                                  "the 48 gradient / magnitude / phase maps per frame (GaussPyramid.cpp:65-104); the GPU's keypoints-only path does not "
+                                  "form them (~2.7x of the CPU time, SURVEY.md 6) -- sweep.materialise is the GPU mode that does"},
+            "keypoints_per_step": int(nk), "corners_per_step": int(nc), "clocks": res["clocks"], "gpu_launches": int(res["launches"]),
+            "multi_gpu_parity": bool(same), "parity_step": {"frames": 8, "md5": digest, "keypoints": pk, "corners": pc, "ranks_compared": world},
+            "e2e": res.get("e2e")}
+    if res["prof"]:
+        line["roofline"] = roofline_block(res, args.steps, world)
+    if sweep is not None:
+        line["sweep"] = sweep
     if not args.no_cpu_baseline:
+        uniq = res["uniq"]
         n_sample = 8 if h * w <= 2.1e6 else (2 if h * w <= 8.3e6 else 1)     # 5-15 s of CPU work
         dt, kind, cores, _, _ = cpu_reference_frames([uniq[i] for i in range(min(n_sample, len(uniq)))])
         line["cpu_baseline"] = {"value": min(n_sample, len(uniq)) * h * w / 1e6 / dt, "unit": "Mpix/s", "cores": cores, "kind": kind,

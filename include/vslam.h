@@ -111,7 +111,9 @@ VSLAM_API long long vslam_launch_count(const vslam_ctx *ctx);
  * stream and returns the summed duration and launch count of one kernel class. */
 typedef enum vslam_kernel_id {
     VSLAM_K_UPSAMPLE = 0, VSLAM_K_PAD = 1 /* reflect-101 margins of the octave bases */, VSLAM_K_VBLUR = 2, VSLAM_K_DETECT = 3, VSLAM_K_COMPACT = 4,
-    VSLAM_K_HARRIS = 5, VSLAM_K_GRAD = 6, VSLAM_K_FUSED = 7, VSLAM_K_DESCRIPTOR = 8 /* orientation + SIFT */, VSLAM_KERNEL_COUNT = 9
+    VSLAM_K_HARRIS = 5, VSLAM_K_GRAD = 6, VSLAM_K_FUSED = 7 /* octave_fused_k: dp4a / dp2a, materialising launches */,
+    VSLAM_K_DESCRIPTOR = 8 /* orientation + SIFT */, VSLAM_K_OCTAVE_MMA = 9 /* octave_mma_k: mma.sync */, VSLAM_K_OCTAVE_UMMA = 10 /* octave_umma_k: tcgen05 + TMA */,
+    VSLAM_KERNEL_COUNT = 11
 } vslam_kernel_id;
 VSLAM_API int vslam_profile(vslam_ctx *ctx, int enable);
 VSLAM_API int vslam_profile_read(vslam_ctx *ctx, int kernel_id, double *total_ms, long long *launches);

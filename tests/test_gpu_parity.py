@@ -59,6 +59,27 @@ def test_mag_orient_tolerance(ctx, images, golden_lists):
     assert np.abs(ori - golden_lists["orient_o3l1_home"]).max() < 1e-3                 # degrees
 
 
+@pytest.mark.parametrize("shape", [(48, 64), (37, 51), (3, 5)])
+def test_materialised_gradient_maps(ctx, shape):
+    """vslam_pyramid_build with VSLAM_MATERIALISE_ALL keeps the four fp32 maps of processGradients (GaussPyramid.cpp:65-104)
+    resident for every level and frame (grad_all_k); they equal the maps formed on demand (grad_k) bit for bit, and gx / gy
+    equal the oracle's Sobel(ksize=1)."""
+    rng = np.random.default_rng(shape[0] + shape[1])
+    frames = rng.integers(0, 256, (3,) + shape, dtype=np.uint8)
+    no = 2 if min(shape) >= 8 else 1
+    lazy = ctx.build_pyramid(frames, no, 1.6)
+    res = ctx.build_pyramid(frames, no, 1.6, materialise=0x78)
+    ref = O.build_pyramid(frames[2], no, 1.6, gradients=True)
+    for o in range(no):
+        for l in range(6):
+            for kind in (vs.MAP_GRADX, vs.MAP_GRADY, vs.MAP_MAG, vs.MAP_ORIENT):
+                for f in (0, 2):
+                    assert np.array_equal(res.get(kind, o, l, f), lazy.get(kind, o, l, f)), (o, l, kind, f)
+            assert np.array_equal(res.get(vs.MAP_GRADX, o, l, 2), ref["gx"][o][l])
+            assert np.array_equal(res.get(vs.MAP_GRADY, o, l, 2), ref["gy"][o][l])
+    lazy.close(); res.close()
+
+
 @pytest.mark.parametrize("shape", [(1, 37), (37, 1), (2, 2), (5, 7), (33, 64), (48, 31), (97, 131), (130, 258)])
 def test_pyramid_awkward_sizes(ctx, shape):
     rng = np.random.default_rng(shape[0] * 1000 + shape[1])

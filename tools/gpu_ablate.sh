@@ -15,6 +15,6 @@ ctx.profile(True)
 for _ in range(3):
     r = ctx.dog_keypoints(d)
 p = ctx.profile_read()
-print("octave kernels ms per 64 frames:", p["octave_fused_k"]["ms"] / 3, "keypoints", sum(r["counts"]))
+print("octave kernels ms per 64 frames:", sum(p[k]["ms"] for k in ("octave_fused_k","octave_mma_k","octave_umma_k")) / 3, "keypoints", sum(r["counts"]))
 PY
 done

@@ -35,6 +35,9 @@ struct vslam_pyramid {
     size_t frame_bytes = 0;
     double sigma[16][6];
     DevBuf maps;                                // n_frames x [octave][base, gauss0..5, dog0..4]
+    DevBuf grads;                               // materialise != 0: n_frames x [octave][level][gx, gy, mag, orient] dense fp32 planes
+    size_t goff[16], grad_frame_floats = 0;     // float offset of an octave inside a frame's gradient block
+    float *grad_plane(int f, int o, int l, int k) const { return grads.as<float>() + (size_t)f * grad_frame_floats + goff[o] + ((size_t)l * 4 + k) * (size_t)orows[o] * ocols[o]; }
     u8 *plane(int f, int o, int idx) const { return maps.as<u8>() + (size_t)f * frame_bytes + ooff[o] + oplane[o] * idx; }
 };
 
@@ -419,6 +422,22 @@ int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
         const int rc = build_frames(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, p->maps.as<u8>());
         if (rc) { cudaStreamSynchronize(ctx->stream); p->maps.release(); delete p; return rc; }
     }
+    // the maps processGradients leaves behind (GaussPyramid.cpp:65-104), when the caller wants them resident
+    const unsigned gmask = (p->materialise >> VSLAM_MAP_GRADX) & 15u;
+    if (gmask) {
+        size_t fl = 0;
+        for (int o = 0; o < no; ++o) { p->goff[o] = fl; fl += (size_t)24 * g.orows[o] * g.ocols[o]; }
+        p->grad_frame_floats = fl;
+        if (p->grads.reserve(fl * 4 * (size_t)n_frames)) {
+            cudaStreamSynchronize(ctx->stream); p->maps.release(); delete p;
+            VS_FAIL(ctx, VSLAM_E_NOMEM, "gradient maps of %d frames need %zu bytes", n_frames, fl * 4 * (size_t)n_frames);
+        }
+        for (int o = 0; o < no; ++o) {
+            const int rc = launch_gradients_all(ctx, p->plane(0, o, 1), g.orows[o], g.ocols[o], g.opitch[o], g.oplane[o], g.frame_bytes,
+                                                p->grads.as<float>() + p->goff[o], (size_t)g.orows[o] * g.ocols[o], fl, gmask, n_frames);
+            if (rc) { cudaStreamSynchronize(ctx->stream); p->maps.release(); p->grads.release(); delete p; return rc; }
+        }
+    }
     *out = p;
     return VSLAM_OK;
 }
@@ -428,6 +447,7 @@ void vslam_pyramid_destroy(vslam_pyramid *pyr) {
     cudaSetDevice(pyr->device);
     cudaDeviceSynchronize();
     pyr->maps.release();
+    pyr->grads.release();
     delete pyr;
 }
 int vslam_pyramid_num_octaves(const vslam_pyramid *pyr) { return pyr ? pyr->num_octaves : VSLAM_E_INVALID; }
@@ -475,7 +495,12 @@ int vslam_pyramid_get(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int k
     } else if (kind <= VSLAM_MAP_ORIENT) {
         if (level < 0 || level >= 6) VS_FAIL(ctx, VSLAM_E_INVALID, "level %d", level);
         if (dst_pitch < (size_t)c * 4) VS_FAIL(ctx, VSLAM_E_INVALID, "dst_pitch %zu < %d floats", dst_pitch, c);
-        // gradient maps are formed from the resident Gaussian level (row E); one dense fp32 scratch plane
+        if (pyr->materialise >> kind & 1u) {      // resident since vslam_pyramid_build
+            VS_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_pitch, pyr->grad_plane(frame, octave, level, kind - VSLAM_MAP_GRADX), (size_t)c * 4, (size_t)c * 4, (size_t)r, mk, ctx->stream));
+            if (space != VSLAM_DEVICE) VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            return VSLAM_OK;
+        }
+        // otherwise gradient maps are formed from the resident Gaussian level (row E); one dense fp32 scratch plane
         float *tmp = (float *)dst;
         size_t tp = dst_pitch / 4;
         if (space != VSLAM_DEVICE || (dst_pitch & 3)) {

@@ -868,7 +868,7 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     a.seg_rows = seg_rows;
     a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
-    KernelSpan span(ctx, VSLAM_K_FUSED);
+    KernelSpan span(ctx, VSLAM_K_OCTAVE_MMA);
     v->k<<<grid, kMmaThreads, sm, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;

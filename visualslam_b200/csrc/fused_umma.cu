@@ -754,7 +754,7 @@ int launch_octave_umma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double 
     if (dbg && !d_dbg) cudaMalloc(&d_dbg, 256 * sizeof(long long));
     a.dbg = dbg ? d_dbg : nullptr;
     {
-        KernelSpan span(ctx, VSLAM_K_FUSED);
+        KernelSpan span(ctx, VSLAM_K_OCTAVE_UMMA);
         p.k<<<grid, kThreads, p.smem, ctx->stream>>>(tmap, a);
     }
     VS_LAUNCH_CHECK(ctx);

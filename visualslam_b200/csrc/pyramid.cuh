@@ -32,4 +32,9 @@ int launch_upsample2x(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t 
 int launch_gradients(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pitch, float *gx, float *gy, float *mag,
                      float *orient, size_t out_pitch_elems);
 
+// row E for every level of one octave of a batch into resident planes: per frame and level four dense fp32 planes
+// [gx, gy, magnitude, orientation] of `oplane` floats; mask bit k selects plane k
+int launch_gradients_all(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pitch, size_t gplane, size_t gstride, float *out,
+                         size_t oplane, size_t ostride, unsigned mask, int n_frames);
+
 }  // namespace vslam

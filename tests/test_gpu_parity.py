@@ -265,6 +265,41 @@ def test_4k_frame_vs_oracle(ctx):
     assert hr["counts"] == [len(ref["corners"])] and np.array_equal(np.stack([c["row"], c["col"]], 1), ref["corners"])
 
 
+def test_1080p_all_unique_frames_vs_oracle(ctx):
+    """parity on all 8 unique frames of the 1080p workload -- natural-tile, procedural and uniform-noise frames
+    drive the queue / compaction tail differently.  One batched GPU call; DoG lists and Harris corner lists per frame."""
+    frames = np.stack([synth.frame(i, 1080, 1920) for i in range(8)], 0)
+    res = ctx.dog_keypoints(frames, capacity=1 << 21)
+    hr = ctx.harris(frames, want_maps=False, capacity=1 << 23)
+    assert not res["overflow"] and not hr["overflow"]
+    k0 = c0 = 0
+    for f in range(8):
+        kc, _, _ = O.dog_keypoints(frames[f])
+        n = res["counts"][f]
+        assert n == len(kc) and np.array_equal(kp_array(res["keypoints"][k0:k0 + n]), kc), f
+        k0 += n
+        ref = O.harris(frames[f])
+        m = hr["counts"][f]
+        c = hr["corners"][c0:c0 + m]
+        assert m == len(ref["corners"]) and np.array_equal(np.stack([c["row"], c["col"]], 1), ref["corners"]), f
+        assert np.array_equal(c["value"], ref["corner_values"]), f
+        c0 += m
+
+
+def test_8k_frame_vs_oracle(ctx):
+    """BASELINE.json's 8K size against the C oracle itself: one natural-tile frame, DoG keypoints and Harris corners
+    (tens of seconds of single-threaded CPU work)."""
+    f = synth.frame(3, 4320, 7680)
+    res = ctx.dog_keypoints(f, capacity=1 << 21)
+    kc, _, _ = O.dog_keypoints(f)
+    assert not res["overflow"] and res["counts"] == [len(kc)] and np.array_equal(kp_array(res["keypoints"]), kc)
+    hr = ctx.harris(f, want_maps=False, capacity=1 << 23)
+    ref = O.harris(f)
+    c = hr["corners"]
+    assert not hr["overflow"] and hr["counts"] == [len(ref["corners"])]
+    assert np.array_equal(np.stack([c["row"], c["col"]], 1), ref["corners"]) and np.array_equal(c["value"], ref["corner_values"])
+
+
 def test_8k_properties(ctx):
     """BASELINE.json's 8K size (the oracle would take minutes): batch independence, agreement of the two octave kernels'
     strip decompositions on the top-left 4K crop's interior, constant frames."""

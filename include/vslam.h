@@ -34,9 +34,10 @@ typedef enum vslam_status {
     VSLAM_OK = 0,
     VSLAM_E_INVALID = -1,  /* bad argument (null pointer, non-positive size, unsupported kernel width ...) */
     VSLAM_E_CUDA = -2,     /* a CUDA call failed; see vslam_last_error */
-    VSLAM_E_CAPACITY = -3, /* output list too small; counts[] hold the true sizes; the list holds the first `capacity`
-                            * entries as long as one launch batch emits at most max(capacity, 2^20) entries (the staging
-                            * list's size), otherwise the first `capacity` of an unspecified, ordered subset */
+    VSLAM_E_CAPACITY = -3, /* output list too small; counts[] hold the true sizes and the list holds the first `capacity`
+                            * entries of the ordered result.  One launch batch stages at most max(capacity, 2^20) entries:
+                            * if it emits more, the positions are still those of the full ordered result, but entries that
+                            * found no staging slot are returned as markers with row = -1 (never silently as garbage) */
     VSLAM_E_NOMEM = -4     /* device or host allocation failed */
 } vslam_status;
 
@@ -96,6 +97,15 @@ typedef enum vslam_map_kind {
 #define VSLAM_DEVICE 1
 
 /* ---- context ------------------------------------------------------------------------------------------------ */
+/* Stream contract.  Every call enqueues its work on the context's stream and returns; host-space outputs are complete on
+ * return, device-space outputs when the stream reaches that point (vslam_sync, or later work on the same stream).
+ * vslam_ctx_create makes a private NON-BLOCKING stream: device buffers produced or consumed by the caller's other streams
+ * are NOT ordered with it -- finish that work before the call and vslam_sync before reading device outputs, or create the
+ * context on the caller's stream with vslam_ctx_create_on_stream, which orders everything with the caller's own work.
+ * The GaussPyramid materialise mask (vslam_pyramid_params.materialise, VSLAM_MATERIALISE_*) makes the chosen fp32 gradient
+ * maps of every level resident at build time; maps outside the mask are formed on demand by vslam_pyramid_get.
+ * Kernel widths: the 8U Gaussian kernels of an octave must not exceed 247 taps (sigma <= ~41): with sigma0 = 1.6 that is
+ * four octaves; a fifth octave (vslam_calculate_num_octaves on images whose short side is >= 512) returns VSLAM_E_INVALID. */
 VSLAM_API int vslam_ctx_create(int device, vslam_ctx **out);
 /* Same, but work is enqueued on a caller-owned CUDA stream (cudaStream_t / CUstream passed as void*). */
 VSLAM_API int vslam_ctx_create_on_stream(int device, void *cuda_stream, vslam_ctx **out);

@@ -177,6 +177,20 @@ def test_dog_capacity_overflow(ctx, images):
     assert np.array_equal(res["keypoints"], full["keypoints"][:100])
 
 
+def test_harris_staging_overflow_is_marked(ctx):
+    """A batch that emits more corners than the staging list holds (max(capacity, 2^20) entries) with a small capacity:
+    VSLAM_E_CAPACITY, true counts, and every returned entry is either the entry of the full ordered list at that position
+    or a row = -1 marker (include/vslam.h) -- never uninitialised memory."""
+    frames = np.stack([synth.frame(i % 8, 1080, 1920) for i in range(24)], 0)
+    full = ctx.harris(frames, want_maps=False, capacity=1 << 22)
+    assert not full["overflow"] and sum(full["counts"]) > (1 << 20)
+    small = ctx.harris(frames, want_maps=False, capacity=5000)
+    assert small["overflow"] and small["counts"] == full["counts"] and len(small["corners"]) == 5000
+    got, want = small["corners"], full["corners"][:5000]
+    ok = (got["row"] == -1) | ((got["row"] == want["row"]) & (got["col"] == want["col"]) & (got["value"] == want["value"]))
+    assert ok.all()
+
+
 @pytest.mark.parametrize("shape", [(96, 160), (49, 84)])
 def test_dog_window_sizes(ctx, shape):
     """Other grid strides.  (49, 84): at window 5 the last sample row / column of octave 0 (98 x 168) and octave 1 sits on

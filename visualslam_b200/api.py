@@ -230,6 +230,25 @@ class Context:
             raise VslamError(rc, L.vslam_last_error(None).decode())
         self.h = h
         self.device = device
+        self._own_stream = not stream      # the library's own non-blocking stream: torch's streams are not ordered with it
+
+    def _torch_in(self, *objs):
+        """Stream contract (include/vslam.h): work is enqueued on the context's stream.  A context created on the caller's
+        stream is ordered with the caller's work; one with its own stream is not, so torch tensors handed to it are made
+        ready first (host wait on the tensor's current stream) and device results are complete on return (_torch_out)."""
+        if not self._own_stream:
+            return False
+        dev = False
+        for o in objs:
+            if o is not None and not isinstance(o, (np.ndarray, UploadedFrames)) and hasattr(o, "data_ptr"):
+                import torch
+                torch.cuda.current_stream(o.device).synchronize()
+                dev = True
+        return dev
+
+    def _torch_out(self, dev):
+        if dev:
+            self.sync()
 
     def close(self):
         if getattr(self, "h", None):
@@ -277,6 +296,7 @@ class Context:
         return UploadedFrames(dptr.value, n, h, w, dp.value, ds.value, a)
 
     def build_pyramid(self, frames, num_octaves=4, sigma0=1.6, materialise=0):
+        self._torch_in(frames)
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
         pp = PyramidParams(num_octaves, 3, sigma0, materialise)
         ph = C.c_void_p()
@@ -301,6 +321,7 @@ class Context:
     def dog_keypoints(self, frames, num_octaves=4, sigma0=1.6, window=3, contrast_thr=0.03, edge_r=10.0,
                       capacity=1 << 20, out=None):
         """Throughput path. `out` may be a torch cuda tensor viewed as int32 [capacity,6] to keep results on device."""
+        dev = self._torch_in(frames, out)
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
         pp = PyramidParams(num_octaves, 3, sigma0, 0)
         dp = DogParams(window, contrast_thr, edge_r)
@@ -318,6 +339,7 @@ class Context:
                                         capacity, ospace, counts)
         if rc and rc != E_CAPACITY:
             self._chk(rc)
+        self._torch_out(dev)
         cl = list(counts)
         return {"keypoints": host[:min(sum(cl), capacity)] if host is not None else out, "counts": cl,
                 "overflow": rc == E_CAPACITY}
@@ -389,6 +411,7 @@ class Context:
         return out
 
     def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None, corners_out=None):
+        dev = self._torch_in(frames, *(device_out.values() if device_out else ()))
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
         hp = HarrisParams(k, nms2_window)
         counts = (C.c_int * n)()
@@ -399,6 +422,7 @@ class Context:
                                      g("mask3"), g("corners"), capacity, DEVICE, counts)
             if rc and rc != E_CAPACITY:
                 self._chk(rc)
+            self._torch_out(dev)
             return {"counts": list(counts), "overflow": rc == E_CAPACITY}
         resp = np.empty((n, h, w), np.float32) if want_maps else None
         r8 = np.empty((n, h, w), np.uint8) if want_maps else None

@@ -125,9 +125,14 @@ __global__ void __launch_bounds__(256) seg_gather_k(const int *__restrict__ off,
     if (!c) return;
     const int o = off[i], d = dst[i];
     for (int e = 0; e < c; ++e) {
-        if (o + e >= staging_cap || d + e >= capacity) break;
-        const u32 *s = staging + (size_t)(o + e) * words;
+        if (d + e >= capacity) break;
         u32 *t = out + (size_t)(d + e) * words;
+        if (o + e >= staging_cap) {                      // the producer had no staging slot left for this entry: mark it (row = -1)
+            t[0] = 0xffffffffu;
+            for (int w = 1; w < words; ++w) t[w] = 0;
+            continue;
+        }
+        const u32 *s = staging + (size_t)(o + e) * words;
         for (int w = 0; w < words; ++w) t[w] = s[w];
     }
 }

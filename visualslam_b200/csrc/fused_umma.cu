@@ -19,12 +19,12 @@
 //            tap[8 j + row + byte - shift], and the no-swizzle K-major descriptor (SBO 128, LBO 256) walks OVERLAPPING core
 //            matrices -- 4.4 KB per level instead of 20 KB.  Reversed rows only permute TMEM lanes / columns.
 //
-// One CTA per SM, seventeen warps: a control warp (TMA producer + the single MMA-issuing thread), eight warps that turn D_v
-// into the byte planes X (warps 8..15) and eight that turn D_lo / D_hi into Gaussian / DoG tile rows (warps 0..7); TMEM lane
-// quadrant = warp % 4, column half = (warp / 4) % 2.  D_v, D_h (and X where shared memory allows) are double buffered, so the
-// tensor pipe, the X warps and the tile warps work on three different levels at once; the X warps run two levels ahead
-// across the step boundary.  All sixteen warps share the detector of a finished step.  The detector, localisation, edge
-// test, ordered emission and decimation are those of fused_mma.cu on a row-major byte tile.
+// One CTA per SM, thirty warps (960 threads, 64 registers): 24 tile warps that turn D_lo / D_hi into Gaussian / DoG tile rows
+// and then run the detector (8 columns each), 4 X warps that turn D_v into the byte planes, a control warp (TMA producer +
+// the single MMA-issuing thread) and a service warp (queued localisations, ordered emission); TMEM lane quadrant =
+// warp % 4.  D_v and D_h are double buffered in TMEM, so the tensor pipe, the X warps and the tile warps work on three
+// different levels at once.  The detector, localisation, edge test, ordered emission and decimation are those of
+// fused_mma.cu on a row-major byte tile.  Measured against fused_mma.cu in DESIGN.md 4.1b (slower: opt-in, VSLAM_UMMA=1).
 #include <math.h>
 #include <string.h>
 

@@ -218,6 +218,19 @@ VSLAM_API int vslam_sobel1(vslam_ctx *ctx, const uint8_t *src, int rows, int col
 /* HarrisCorner(Ix, Iy) incl. StructureMatrix (Harris_corners.cpp:10-68): window 3, k 0.04 in the reference */
 VSLAM_API int vslam_harris_response(vslam_ctx *ctx, const float *ix, const float *iy, int rows, int cols, int window,
                                     float k, float *response);
+/* No counterpart in the reference: added for callers that cannot allocate (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The same map as vslam_harris's
+ * `response` (= vslam_gaussian_blur3 -> vslam_sobel1 -> vslam_harris_response) of ONE image, but with DEVICE pointers for
+ * the image (pitch in bytes) and the dense rows x cols float response, and with the intermediates (blurred image, Ix, Iy,
+ * one counter) in a file-scope static __device__ array instead of cudaMalloc'd context buffers: the call allocates
+ * nothing, enqueues its work on the context's stream and returns without synchronising.  d_positive: optional DEVICE int
+ * that receives the number of responses > 0.  Limits: rows * cols <= VSLAM_STATIC_MAX_PIXELS (larger images return
+ * VSLAM_E_INVALID with a message; use vslam_harris); the array (256 + 9 bytes per pixel of the maximum = 18 MiB) is held by
+ * every GPU that loads the library until the process exits.  Every call on a device shares it: calls that overlap on the
+ * GPU (different streams or contexts) race; calls on one stream are ordered and safe. */
+#define VSLAM_STATIC_MAX_PIXELS 2097152 /* 2 Mi pixels: covers 1920 x 1080 */
+VSLAM_API int vslam_harris_response_static(vslam_ctx *ctx, const uint8_t *d_image, int rows, int cols, size_t pitch,
+                                           int window, float k, float *d_response, int *d_positive);
 /* convertScaleAbs(src, dst) with alpha 1, beta 0 (Harris_corners.cpp:176) */
 VSLAM_API int vslam_convert_scale_abs(vslam_ctx *ctx, const float *src, int rows, int cols, uint8_t *dst);
 /* NonMaximumSuppression(response8u, 3) (Harris_corners.cpp:70-81): 255 where strictly above the 8 neighbours */

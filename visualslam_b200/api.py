@@ -61,6 +61,8 @@ EXPORTS = [
     # the stage after the hot path: orientation assignment, SIFT descriptors, featureDescriptors.dat
     "vslam_gauss_ksize_f32", "vslam_gauss_taps_f32", "vslam_assign_orientations", "vslam_sift_descriptors",
     "vslam_write_descriptor_file", "vslam_describe_keypoints",
+    # allocation-free variant (static device scratch); no counterpart in the reference
+    "vslam_harris_response_static",
 ]
 
 _lib = None
@@ -110,6 +112,7 @@ def load():
     L.vslam_sift_descriptors.argtypes = [vp, vp, i, i, vp, i, vp, vp]
     L.vslam_write_descriptor_file.argtypes = [C.c_char_p, vp, i]
     L.vslam_describe_keypoints.argtypes = [vp, vp, vp, C.POINTER(i), vp, i, C.POINTER(i), vp, vp]
+    L.vslam_harris_response_static.argtypes = [vp, vp, i, i, sz, i, C.c_float, vp, vp]
     _lib = L
     return L
 

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libvslam_b200.so")
-SOURCES = ["capi.cu", "taps.cu", "pyramid.cu", "fused.cu", "fused_mma.cu", "fused_umma.cu", "detect.cu", "harris.cu", "compaction.cu", "stages.cu", "descriptor.cu"]
+SOURCES = ["capi.cu", "taps.cu", "pyramid.cu", "fused.cu", "fused_mma.cu", "fused_umma.cu", "detect.cu", "harris.cu", "compaction.cu", "stages.cu", "descriptor.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",
          "-Xcompiler", "-fPIC,-fvisibility=hidden,-O2", "-cudart", "static", "-Xptxas", "-v"] + os.environ.get("VSLAM_NVCC_EXTRA", "").split()

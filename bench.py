@@ -345,7 +345,7 @@ def roofline_block(res, steps, world):
     oct_px = [4.0 * h * w / 4 ** o for o in range(4)]
     octave_bytes = nf * (sum(oct_px) + sum(oct_px[1:])) / 4 + 24.0 * nk / 4
     alg = {"octave_mma_k": octave_bytes, "octave_umma_k": octave_bytes, "octave_fused_k": octave_bytes,
-           "harris_march_k": 6.0 * h * w * nf + 12.0 * nc, "upsample2x_k": 5.0 * h * w * nf}
+           "harris_fast_k": 6.0 * h * w * nf + 12.0 * nc, "upsample2x_k": 5.0 * h * w * nf}
     octave_kernels = [k for k in ("octave_mma_k", "octave_umma_k", "octave_fused_k") if k in live]
     dom = max(live, key=lambda k: live[k]["ms"])
     blur_ms = sum(live[k]["ms"] for k in octave_kernels)

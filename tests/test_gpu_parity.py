@@ -151,6 +151,26 @@ def test_dog_keypoints_kernel_variants_agree(tmp_path):
         assert np.array_equal(outs[0], o)
 
 
+def test_harris_kernel_variants_agree(tmp_path):
+    """harris_fast_k (4-pixel-word shapes, the default) and harris_march_k (VSLAM_HARRIS_FAST=0) give identical maps and corner
+    lists: strips on both image borders, a single strip, cols % 4 == 0 shapes smaller than a strip, both NMS2 windows."""
+    import subprocess, sys, os
+    code = ("import numpy as np, sys, hashlib; import visualslam_b200 as vs; from visualslam_b200 import synth;"
+            "c = vs.Context(0); out = []\n"
+            "for (n, h, w, win) in ((8, 540, 960, 5), (2, 270, 480, 3), (1, 33, 240, 5), (1, 1, 124, 5), (1, 2, 8, 3), (3, 131, 116, 5), (1, 400, 1124, 5)):\n"
+            "    f = np.stack([synth.frame(i + h, h, w) for i in range(n)], 0); r = c.harris(f, nms2_window=win)\n"
+            "    out += [np.frombuffer(hashlib.md5(r[k].tobytes()).digest(), np.uint8) for k in ('response', 'r8', 'mask3')]\n"
+            "    out += [np.frombuffer(hashlib.md5(np.asarray(r['corners']).tobytes()).digest(), np.uint8), np.asarray(r['counts'], np.int64).view(np.uint8)]\n"
+            "np.save(sys.argv[1], np.concatenate(out))")
+    outs = []
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for i, env in enumerate(({}, {"VSLAM_HARRIS_FAST": "0"})):
+        out = str(tmp_path / f"h{i}.npy")
+        subprocess.check_call([sys.executable, "-c", code, out], env={**os.environ, **env, "PYTHONPATH": root}, timeout=600)
+        outs.append(np.load(out))
+    assert len(outs[0]) > 100 and np.array_equal(outs[0], outs[1])
+
+
 def test_tcgen05_kernel_matches_oracle(tmp_path):
     """The tcgen05 / TMA octave kernel (fused_umma.cu, VSLAM_UMMA=1) against the plain-C oracle on awkward sizes: strips that
     end inside the image, a last step of one row, an octave smaller than one step, sizes smaller than the kernel radius."""

@@ -5,5 +5,5 @@ set -x
 CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
 $CMD > gpurun_out/plain.log 2>&1 || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:'octave_mma_k|octave_fused_k|harris_march_k|upsample2x_k|reflect_pad_k' -s 10 -c 10 -f -o gpurun_out/prof_all $CMD > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'octave_mma_k|octave_fused_k|harris_fast_k|harris_march_k|upsample2x_k|reflect_pad_k' -s 10 -c 10 -f -o gpurun_out/prof_all $CMD > gpurun_out/ncu_full.log 2>&1
 tail -2 gpurun_out/ncu_full.log

@@ -268,7 +268,7 @@ class Context:
         self._chk(load().vslam_sync(self.h))
 
     # names of the kernels behind vslam_kernel_id (include/vslam.h), as they appear in an ncu launch list
-    KERNELS = ["upsample2x_k", "reflect_pad_k", "(unused2)", "dog_detect_k", "seg_reduce_k + seg_spine_k + seg_apply_k + seg_gather_k", "harris_march_k", "grad_k",
+    KERNELS = ["upsample2x_k", "reflect_pad_k", "(unused2)", "dog_detect_k", "seg_reduce_k + seg_spine_k + seg_apply_k + seg_gather_k", "harris_fast_k", "grad_k",
                "octave_fused_k", "orient_hist_k + sift_k", "octave_mma_k", "octave_umma_k"]
 
     def profile(self, enable=True):

@@ -34,11 +34,13 @@ namespace vslam {
 namespace {
 constexpr int FR = kFusedR;
 constexpr int kMmaThreads = 288;            // eight compute warps and a service warp (queued localisations, emission)
-constexpr int TRP = 20;                     // words per column pair of a tile: 2 history + 16 row pairs (+2: conflict-free STS)
+constexpr int TRP = 20;                     // words per column pair of a tile: 2 history + 16 row pairs (+2: conflict-free STS);
+                                            // every block of 8 column pairs is skewed by one more word (tcol): 20 m mod 32 repeats with
+                                            // period 8, and the detector / decimation read column pairs 8, 16, 24 apart in one warp
 constexpr int N_G = 3, N_D = 5;             // G tiles: Gaussian levels 1..3; D tiles: DoG levels 0..4
 constexpr int MAX_NS = 20;                  // sample columns per strip at FW = 64
 constexpr int MAX_SROW = FR / 3 + 2;
-__host__ __device__ constexpr int tile_words(int fw) { return (fw / 2) * TRP; }
+__host__ __device__ constexpr int tile_words(int fw) { return (fw / 2) * TRP + 4; }
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -107,8 +109,11 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps
         const int need_t = lv.padl + lv.n + 3;
         cp = std::max(cp, std::max(need_h, std::max(need_v, need_t)));
     }
-    cp = (cp + 3) & ~3;
-    while (cp % 128 != 32) cp += 4;                                  // copies 32 bytes apart modulo 128: fewer bank conflicts
+    cp = (cp + 4 + 3) & ~3;                                          // 4 spare bytes: copies s > rv % 4 start one word later (below)
+    // Copies 32 bytes apart modulo 128.  A V-pass fragment load touches 8 consecutive words of every copy: words -1 .. 6 of the
+    // copies s <= rv % 4, words -2 .. 5 of the others; moving those one word up tiles the 32 banks exactly (round 2: the load ran
+    // at two wavefronts per request, 22 M excess wavefronts per 32 frames at octaves 0 and 1).  The H pass touches 5 words per copy.
+    while (cp % 128 != 32) cp += 4;
     out->cp = cp;
     for (int l = 0; l < 6; ++l) {
         MmaLevel &lv = out->lv[l];
@@ -125,7 +130,7 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps
             if ((int)(((unsigned)q * (unsigned)out->spq_magic) >> 16) != q / spq) return VSLAM_E_INVALID;
     }
     out->plane_words = poff;
-    out->tab_bytes = (24 * cp + 15) & ~15;
+    out->tab_bytes = (24 * cp + 4 + 15) & ~15;
     return VSLAM_OK;
 }
 
@@ -171,7 +176,7 @@ __device__ __forceinline__ void mbar_wait(u32 sa, u32 parity) {
 }
 
 // byte offset of pixel (x, ty) inside a tile: words of 2 x 2 pixels [x even/odd][row even/odd], column pairs TRP words apart
-__device__ __forceinline__ int tcol(int x) { return (x >> 1) * (TRP * 4) + ((x & 1) << 1); }
+__device__ __forceinline__ int tcol(int x) { return (x >> 1) * (TRP * 4) + ((x >> 4) << 2) + ((x & 1) << 1); }
 __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1); }
 
 }  // namespace
@@ -358,8 +363,8 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
     // V pass (K rows remapped so that a thread's 8 rows are consecutive) b1 = taps idx0 + 4 .., idx0 = 32 k + 8 t - g - sv.
     // One lane pointer per pass (byte-shifted copy + word offset); the level is an offset (fused_mma.cuh)
     const int hu = 4 * t - g - hcb + 32 * c_lo, vu = 8 * t - g + geo.rv() % 4;
-    const u8 *hbase = tab + (hu & 3) * geo.cp() + (hu - (hu & 3));             // two's complement: fine for hu < 0
-    const u8 *vbase = tab + (vu & 3) * geo.cp() + (vu - (vu & 3));
+    const u8 *hbase = tab + (hu & 3) * geo.cp() + ((hu & 3) > geo.rv() % 4 ? 4 : 0) + (hu - (hu & 3));   // two's complement: fine for hu < 0
+    const u8 *vbase = tab + (vu & 3) * geo.cp() + ((vu & 3) > geo.rv() % 4 ? 4 : 0) + (vu - (vu & 3));
     const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the H chunk this thread's D rows belong to
     const int vcb = warp % VCB, vjb = (warp / VCB) * RBW;                         // V pass: warp = (16-column block, RBW blocks of 8 rows)
     u32 hoff[6], voff[6];                                                     // ring byte offsets: H store slot, V window start (row block vjb)
@@ -369,7 +374,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
         hoff[l] = (u32)((d_pi + geo.cq(l)) >> 1) * (PPW * 4) + 16 * (4 * hw + t) + 8 * ((d_pi + geo.cq(l)) & 1);   // < np pairs
         voff[l] = (u32)(vjb + t) * (PPW * 4) + 16 * (8 * vcb + g);
     }
-    const int wi0 = (8 * vcb + g) * TRP + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
+    const int wi0 = (8 * vcb + g) * TRP + vcb + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
     // detector: thread = (sample column det_k, sample row det_sr of the step)
     const int det_k = tid % NS, det_sr = tid / NS;                            // 256 threads: rows 0 .. 12 (at most 12 are live)
     const int det_xc = X0 + 3 * det_k;
@@ -438,7 +443,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
             const int oc = 2 * (tid % (FWO / 4)), w = tid / (FWO / 4);
             const int ox = X0 / 2 + oc, oy = (y0 >> 1) + w;
             if (oy < a.next_rows && ox < a.next_cols) {
-                const u32 v0 = tiles32[2 * TILE_W + (oc + 1) * TRP + 2 + w], v1 = tiles32[2 * TILE_W + (oc + 2) * TRP + 2 + w];
+                const u32 v0 = tiles32[2 * TILE_W + (oc + 1) * TRP + ((oc + 1) >> 3) + 2 + w], v1 = tiles32[2 * TILE_W + (oc + 2) * TRP + ((oc + 2) >> 3) + 2 + w];
                 u8 *dst = a.next_base + (size_t)frame * a.next_stride + (size_t)oy * a.next_pitch + ox;
                 if (ox + 1 < a.next_cols) *(u16 *)dst = (u16)((v0 & 0xffu) | (v1 & 0xffu) << 8);
                 else *dst = (u8)v0;
@@ -764,7 +769,7 @@ const uint4 *mma_tab_image(vslam_ctx *ctx, double sigma0, int scale_samples, int
         for (int sft = 0; sft < 4; ++sft)
             for (int j = 0; j < mt.cp; ++j) {
                 const int idx = j + sft - mt.lv[l].padl;
-                img[(size_t)(4 * l + sft) * mt.cp + j] = (idx >= 0 && idx < mt.lv[l].n) ? mt.taps[l][idx] : (u8)0;
+                img[(size_t)(4 * l + sft) * mt.cp + (sft > mt.rv % 4 ? 4 : 0) + j] = (idx >= 0 && idx < mt.lv[l].n) ? mt.taps[l][idx] : (u8)0;
             }
     void *d = nullptr;
     if (cudaMalloc(&d, img.size()) != cudaSuccess) return nullptr;

@@ -93,8 +93,8 @@ struct MmaStaticGeom {
     __host__ __device__ static constexpr int cp() {
         int m = 0;
         for (int l = 0; l < 6; ++l) m = cp_need(l) > m ? cp_need(l) : m;
-        m = (m + 3) & ~3;
-        while (m % 128 != 32) m += 4;                                      // copies 32 bytes apart modulo 128: fewer bank conflicts
+        m = (m + 4 + 3) & ~3;                                              // 4 spare bytes: copies s > rv % 4 start one word later
+        while (m % 128 != 32) m += 4;                                      // copies 32 bytes apart modulo 128 (build_mma_taps: bank tiling)
         return m;
     }
     __host__ __device__ static constexpr int tab_hoff(int l) { return 4 * cp() * l + padl(l) + r(l); }

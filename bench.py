@@ -253,13 +253,13 @@ class Runner:
         if e2e:
             # e2e result lists: pinned host buffers owned by the caller (a pageable list would be staged by the driver)
             kp_host = torch.empty((cap, 6), dtype=torch.int32, pin_memory=True).numpy()
-            co_host = torch.empty((cap * 4, 3), dtype=torch.int32, pin_memory=True).numpy()
+            co_host = torch.empty((cap * 4, 2), dtype=torch.int32, pin_memory=True).numpy()    # vslam_corner8 entries (VSLAM_COMPACT)
             eo = [False]
 
             def step_e2e():
                 up = ctx.upload(hnp)                                          # one chunked H2D of the batch, overlapped with the kernels
                 a = ctx.dog_keypoints(up, out=kp_host)                        # keypoint list D2H inside
-                b = ctx.harris(up, want_maps=False, corners_out=co_host)      # corner-only mode on the e2e path, corner list D2H inside
+                b = ctx.harris(up, want_maps=False, corners_out=co_host, compact=True)   # corner-only mode, 8-byte corner list D2H inside
                 eo[0] |= bool(a["overflow"] or b["overflow"])
                 return len(a["keypoints"]), len(b["corners"])
 
@@ -269,9 +269,9 @@ class Runner:
                 raise SystemExit(f"output list overflow in the end-to-end steps of {w}x{h} x {nf}")
             ems /= steps
             res["e2e"] = {"value": self.world * px_step / 1e6 / (ems * 1e-3), "unit": "Mpix/s", "ms_per_step": ems, "steps": steps,
-                          "h2d_bytes_per_step": px_step, "d2h_bytes_per_step": int(ek * 24 + ec * 12 + 8 * nf),
-                          "api": "vslam_upload_frames (chunked, overlapped) + vslam_dog_keypoints + vslam_harris(corner-only): host (pinned) "
-                                 "frames in, host (pinned) result lists out; value's steps run Harris in pipeline mode (response + mask stay in HBM)"}
+                          "h2d_bytes_per_step": px_step, "d2h_bytes_per_step": int(ek * 24 + ec * 8 + 8 * nf),
+                          "api": "vslam_upload_frames (chunked, overlapped) + vslam_dog_keypoints + vslam_harris(corner-only, VSLAM_COMPACT: "
+                                 "8-byte vslam_corner8 list, lossless): host (pinned) frames in, host (pinned) result lists out; value's steps run Harris in pipeline mode (response + mask stay in HBM)"}
         del kp_dev, co_dev, resp_dev, mask_dev, dev
         torch.cuda.empty_cache()
         return res

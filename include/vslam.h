@@ -55,6 +55,13 @@ typedef struct vslam_corner {
     int32_t row, col;
     float value;
 } vslam_corner;
+/* The same corner in 8 bytes, for callers that move large lists across PCIe (no counterpart in the reference; lossless for
+ * images below 65536 rows / columns): OR VSLAM_COMPACT into vslam_harris's out_space and pass a vslam_corner8 buffer.
+ * An entry the staging buffer had no room for is marked row = col = 0xffff (the 12-byte list marks it row = -1). */
+typedef struct vslam_corner8 {
+    uint16_t row, col;
+    float value;
+} vslam_corner8;
 
 /* GaussPyramid ctor arguments + constants (GaussPyramid.hpp:17-21,65-69). */
 typedef struct vslam_pyramid_params {
@@ -95,6 +102,7 @@ typedef enum vslam_map_kind {
 /* memory space of a caller buffer */
 #define VSLAM_HOST 0
 #define VSLAM_DEVICE 1
+#define VSLAM_COMPACT 0x100 /* vslam_harris only: `corners` receives vslam_corner8 entries (8 bytes) instead of vslam_corner */
 
 /* ---- context ------------------------------------------------------------------------------------------------ */
 /* Stream contract.  Every call enqueues its work on the context's stream and returns; host-space outputs are complete on
@@ -186,7 +194,9 @@ VSLAM_API int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_f
 /* ---- Harris: main's pre-blur + Sobel, HarrisCorner, convertScaleAbs + NonMaximumSuppression, NMS2
  *      (Harris_corners.cpp:158-164, 31-68, 176-178, 83-129) ------------------------------------------------------ */
 /* Any of response / r8 / mask3 may be NULL (not materialised).  Maps are dense n_frames x rows x cols in `space`.
- * corners: capacity entries in row-major order per frame, frames concatenated; counts: n_frames ints (host). */
+ * corners: capacity entries in row-major order per frame, frames concatenated; counts: n_frames ints (host).
+ * out_space: VSLAM_HOST or VSLAM_DEVICE, optionally | VSLAM_COMPACT (corners is then a vslam_corner8 buffer: a third fewer
+ * bytes to bring back, the dominant device-to-host transfer of the end-to-end path). */
 VSLAM_API int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
                            size_t frame_stride, int space, const vslam_harris_params *params, float *response,
                            uint8_t *r8, uint8_t *mask3, vslam_corner *corners, int capacity, int out_space,

@@ -211,6 +211,29 @@ def test_harris_staging_overflow_is_marked(ctx):
     assert ok.all()
 
 
+def test_harris_compact_corner_list(ctx):
+    """VSLAM_COMPACT (vslam_corner8: u16 row, u16 col, f32 value) carries the same ordered list in two thirds of the bytes: host
+    and device output, several launch chunks, the overflow markers."""
+    import torch
+    frames = np.stack([synth.frame(i % 8, 540, 960) for i in range(12)], 0)
+    full = ctx.harris(frames, want_maps=False, capacity=1 << 21)
+    c8 = ctx.harris(frames, want_maps=False, capacity=1 << 21, compact=True)
+    assert c8["counts"] == full["counts"] and c8["corners"].dtype.itemsize == 8
+    assert np.array_equal(vs.expand_corners(c8["corners"]), full["corners"])
+    dev = torch.zeros((len(full["corners"]) + 7, 2), dtype=torch.int32, device="cuda")
+    r = ctx.harris(torch.from_numpy(frames).cuda(), device_out={"corners": dev}, compact=True)
+    assert r["counts"] == full["counts"]
+    assert np.array_equal(vs.expand_corners(dev.cpu().numpy()[:len(full["corners"])].view(vs.CORNER8_DTYPE)), full["corners"])
+    # staging overflow: positions of the full list or 0xffff markers (-> row = -1)
+    big = np.stack([synth.frame(i % 8, 1080, 1920) for i in range(24)], 0)
+    want = ctx.harris(big, want_maps=False, capacity=1 << 22)
+    small = ctx.harris(big, want_maps=False, capacity=5000, compact=True)
+    assert small["overflow"] and small["counts"] == want["counts"]
+    got, w5 = vs.expand_corners(small["corners"]), want["corners"][:5000]
+    ok = (got["row"] == -1) | ((got["row"] == w5["row"]) & (got["col"] == w5["col"]) & (got["value"] == w5["value"]))
+    assert ok.all()
+
+
 @pytest.mark.parametrize("shape", [(96, 160), (49, 84)])
 def test_dog_window_sizes(ctx, shape):
     """Other grid strides.  (49, 84): at window 5 the last sample row / column of octave 0 (98 x 168) and octave 1 sits on

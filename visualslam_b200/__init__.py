@@ -3,9 +3,9 @@
 Product code: CUDA kernels + C ABI in csrc/ (libvslam_b200.so), C++17 host mirror of the reference surface in
 host/, and this ctypes binding.  Nothing here imports oracle/.
 """
-from .api import (CORNER_DTYPE, DEVICE, HOST, KEYPOINT_DTYPE, MAP_BASE, MAP_DOG, MAP_GAUSS, MAP_GRADX, MAP_GRADY,
-                  MAP_MAG, MAP_ORIENT, Context, Pyramid, VslamError, calculate_sigma, gauss_taps, load)
+from .api import (COMPACT, CORNER8_DTYPE, CORNER_DTYPE, DEVICE, HOST, KEYPOINT_DTYPE, MAP_BASE, MAP_DOG, MAP_GAUSS, MAP_GRADX, MAP_GRADY,
+                  MAP_MAG, MAP_ORIENT, Context, Pyramid, VslamError, calculate_sigma, expand_corners, gauss_taps, load)
 
 __all__ = ["Context", "Pyramid", "VslamError", "load", "calculate_sigma", "gauss_taps", "KEYPOINT_DTYPE",
-           "CORNER_DTYPE", "HOST", "DEVICE", "MAP_BASE", "MAP_GAUSS", "MAP_DOG", "MAP_GRADX", "MAP_GRADY", "MAP_MAG",
+           "CORNER_DTYPE", "CORNER8_DTYPE", "COMPACT", "expand_corners", "HOST", "DEVICE", "MAP_BASE", "MAP_GAUSS", "MAP_DOG", "MAP_GRADX", "MAP_GRADY", "MAP_MAG",
            "MAP_ORIENT"]

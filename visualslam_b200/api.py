@@ -26,6 +26,8 @@ LIB_PATH = os.path.join(_HERE, "libvslam_b200.so")
 KEYPOINT_DTYPE = np.dtype([("row", "<i4"), ("col", "<i4"), ("value", "<i4"), ("padding", "<i4"),
                            ("octave", "<i4"), ("level", "<i4")])
 CORNER_DTYPE = np.dtype([("row", "<i4"), ("col", "<i4"), ("value", "<f4")])
+CORNER8_DTYPE = np.dtype([("row", "<u2"), ("col", "<u2"), ("value", "<f4")])      # vslam_corner8 (VSLAM_COMPACT)
+COMPACT = 0x100
 
 
 class PyramidParams(C.Structure):
@@ -115,6 +117,16 @@ def load():
     L.vslam_harris_response_static.argtypes = [vp, vp, i, i, sz, i, C.c_float, vp, vp]
     _lib = L
     return L
+
+
+def expand_corners(c8):
+    """vslam_corner8 list (CORNER8_DTYPE) -> vslam_corner list (CORNER_DTYPE); the 0xffff overflow marker becomes row = -1."""
+    c8 = np.asarray(c8).view(CORNER8_DTYPE).reshape(-1)
+    out = np.zeros(len(c8), CORNER_DTYPE)
+    out["row"] = c8["row"]; out["col"] = c8["col"]; out["value"] = c8["value"]
+    lost = (c8["row"] == 0xffff) & (c8["col"] == 0xffff)
+    out["row"][lost] = -1; out["col"][lost] = 0; out["value"][lost] = 0
+    return out
 
 
 def calculate_sigma(octave, level, sigma0=1.6, scale_samples=3):
@@ -413,16 +425,20 @@ class Context:
                                               int(window), float(cos_sin[0]), float(cos_sin[1]), out.ctypes.data, window))
         return out
 
-    def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None, corners_out=None):
+    def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None, corners_out=None, compact=False):
+        """compact=True: the corner list comes back as vslam_corner8 (CORNER8_DTYPE, 8 bytes per corner; expand_corners() gives
+        the 12-byte layout); device_out["corners"] / corners_out must then hold 8 bytes per entry."""
         dev = self._torch_in(frames, *(device_out.values() if device_out else ()))
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
         hp = HarrisParams(k, nms2_window)
         counts = (C.c_int * n)()
+        flag = COMPACT if compact else 0
+        dt = CORNER8_DTYPE if compact else CORNER_DTYPE
         if device_out is not None:      # dict of torch cuda tensors: response/r8/mask3 (optional), corners (required)
             g = lambda name: device_out[name].data_ptr() if device_out.get(name) is not None else None
             capacity = device_out["corners"].shape[0]
             rc = load().vslam_harris(self.h, ptr, n, h, w, pitch, stride, space, C.byref(hp), g("response"), g("r8"),
-                                     g("mask3"), g("corners"), capacity, DEVICE, counts)
+                                     g("mask3"), g("corners"), capacity, DEVICE | flag, counts)
             if rc and rc != E_CAPACITY:
                 self._chk(rc)
             self._torch_out(dev)
@@ -430,11 +446,11 @@ class Context:
         resp = np.empty((n, h, w), np.float32) if want_maps else None
         r8 = np.empty((n, h, w), np.uint8) if want_maps else None
         m3 = np.empty((n, h, w), np.uint8) if want_maps else None
-        corners = np.zeros(capacity, CORNER_DTYPE) if corners_out is None else corners_out.view(CORNER_DTYPE).reshape(-1)
+        corners = np.zeros(capacity, dt) if corners_out is None else corners_out.view(dt).reshape(-1)
         capacity = corners.shape[0]
         p = lambda a: a.ctypes.data if a is not None else None
         rc = load().vslam_harris(self.h, ptr, n, h, w, pitch, stride, space, C.byref(hp), p(resp), p(r8), p(m3),
-                                 corners.ctypes.data, capacity, HOST, counts)
+                                 corners.ctypes.data, capacity, HOST | flag, counts)
         if rc and rc != E_CAPACITY:
             self._chk(rc)
         cl = list(counts)

@@ -56,6 +56,16 @@ const char *vslam_last_error(const vslam_ctx *ctx) {
     return copy.c_str();
 }
 
+// live contexts per device
+static int ctx_live(int device, int delta) {
+    static std::mutex mu;
+    static int live[64] = {0};
+    std::lock_guard<std::mutex> lock(mu);
+    if (device < 0 || device >= 64) return 1;
+    live[device] += delta;
+    return live[device];
+}
+
 int vslam_ctx_create_on_stream(int device, void *cuda_stream, vslam_ctx **out) {
     if (!out) VS_FAIL((vslam_ctx *)nullptr, VSLAM_E_INVALID, "vslam_ctx_create: out is null");
     *out = nullptr;
@@ -83,6 +93,7 @@ int vslam_ctx_create_on_stream(int device, void *cuda_stream, vslam_ctx **out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     ctx->pinned_cap = 1 << 20;
     if (cudaMallocHost(&ctx->pinned, ctx->pinned_cap) != cudaSuccess) { ctx->pinned = nullptr; ctx->pinned_cap = 0; cudaGetLastError(); }
+    ctx_live(device, +1);
     *out = ctx;
     return VSLAM_OK;
 }
@@ -105,6 +116,8 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     if (ctx->down_stream) cudaStreamDestroy(ctx->down_stream);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     free(ctx->h_taps);
+    // device-wide caches (tap-table images of the octave kernels) go with the last context of the device
+    if (ctx_live(ctx->device, -1) == 0) { mma_tab_release(ctx->device); umma_tab_release(ctx->device); }
     delete ctx;
 }
 
@@ -762,6 +775,10 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     if (!ctx || capacity < 0 || (!corners && capacity > 0)) return VSLAM_E_INVALID;
     VS_CUDA(ctx, cudaSetDevice(ctx->device));
     if (rows <= 0 || cols <= 0 || rows > (1 << 15) || cols > (1 << 15)) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
+    const int compact = (out_space & VSLAM_COMPACT) ? 1 : 0;          // `corners` is a vslam_corner8 buffer
+    out_space &= ~VSLAM_COMPACT;
+    if (out_space != VSLAM_HOST && out_space != VSLAM_DEVICE) VS_FAIL(ctx, VSLAM_E_INVALID, "out_space %d", out_space);
+    const size_t centry = compact ? sizeof(vslam_corner8) : sizeof(vslam_corner);
     const float k = params ? params->k : 0.04f;
     const int w2 = params ? params->nms2_window : 5;
     if (w2 != 3 && w2 != 5) VS_FAIL(ctx, VSLAM_E_INVALID, "nms2_window must be 3 or 5 (got %d)", w2);
@@ -776,10 +793,10 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     if (fb < 1) VS_FAIL(ctx, VSLAM_E_INVALID, "image too large for the segment table");
     VS_TRY(seg_prepare(ctx, spf * fb, sizeof(vslam_corner), staging_entries(capacity, (size_t)rows * cols * fb)));
     VS_TRY(reserve_counters(ctx, n_frames));
-    vslam_corner *d_out = corners;
+    void *d_out = corners;
     if (out_space != VSLAM_DEVICE) {
-        if (ctx->out_dev.reserve(sizeof(vslam_corner) * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device corner list");
-        d_out = ctx->out_dev.as<vslam_corner>();
+        if (ctx->out_dev.reserve(centry * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device corner list");
+        d_out = ctx->out_dev.p;
     }
     const size_t px = (size_t)rows * cols;
     float *d_resp = response; u8 *d_r8 = r8, *d_m3 = mask3;
@@ -791,7 +808,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     }
     int *cnt = ctx->counters.as<int>();
     ListDrain drain;
-    VS_TRY(drain_begin(ctx, drain, corners, out_space, d_out, sizeof(vslam_corner), capacity, ((long long)n_frames + (long long)fb - 1) / (long long)fb + 1));
+    VS_TRY(drain_begin(ctx, drain, corners, out_space, d_out, centry, capacity, ((long long)n_frames + (long long)fb - 1) / (long long)fb + 1));
     const int first = ingest_first(ctx, (long long)fb);
     for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)fb) {
         const int nf = n_frames - f0 < step ? n_frames - f0 : step;
@@ -809,7 +826,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = ctx->staging_entries;
         a.want_corners = 1;
         VS_TRY(launch_harris(ctx, a, nf));
-        VS_TRY(seg_finalise(ctx, spf * nf, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf));
+        VS_TRY(seg_finalise(ctx, spf * nf, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf, compact));
         VS_TRY(drain_chunk(ctx, drain, cnt + 2));
     }
     if (out_space != VSLAM_DEVICE) {
@@ -820,7 +837,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
     long long total = 0;
     VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
     VS_TRY(drain_end(ctx, drain));
-    return emit_list(ctx, corners, out_space, d_out, sizeof(vslam_corner), total, capacity, drain.on);
+    return emit_list(ctx, corners, out_space, d_out, centry, total, capacity, drain.on);
 }
 
 int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride,

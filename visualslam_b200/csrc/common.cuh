@@ -152,7 +152,8 @@ int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t entry_bytes, size_t en
 // after the producer kernel: order the staged entries of n_segments segments into dst[dst_base ...];
 // d_total[0] accumulates the number written so far (device counter); entry_bytes 12 or 24.
 // n_segments = n_frames * segments per frame; d_frame_count (n_frames ints) receives the per-frame counts.
+// compact != 0 (corners only): dst receives 8-byte vslam_corner8 entries
 int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, int capacity, int *d_total,
-                 int *d_frame_count, int n_frames);
+                 int *d_frame_count, int n_frames, int compact = 0);
 
 }  // namespace vslam

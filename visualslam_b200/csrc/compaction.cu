@@ -118,12 +118,24 @@ __global__ void frame_counts_k(const int *__restrict__ dst, long long segs_per_f
 __global__ void __launch_bounds__(256) seg_gather_k(const int *__restrict__ off, const int *__restrict__ cnt,
                                                     const int *__restrict__ dst, long long n, int words,
                                                     const u32 *__restrict__ staging, int staging_cap,
-                                                    u32 *__restrict__ out, int capacity) {
+                                                    u32 *__restrict__ out, int capacity, int compact) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int c = cnt[i];
     if (!c) return;
     const int o = off[i], d = dst[i];
+    if (compact) {                                       // vslam_corner {row, col, value} -> vslam_corner8 {u16 row, u16 col, value}
+        for (int e = 0; e < c; ++e) {
+            if (d + e >= capacity) break;
+            uint2 t = make_uint2(0xffffffffu, 0u);       // no staging slot: row = col = 0xffff
+            if (o + e < staging_cap) {
+                const u32 *s = staging + (size_t)(o + e) * 3;
+                t = make_uint2((s[0] & 0xffffu) | s[1] << 16, s[2]);
+            }
+            *(uint2 *)(out + (size_t)(d + e) * 2) = t;
+        }
+        return;
+    }
     for (int e = 0; e < c; ++e) {
         if (d + e >= capacity) break;
         u32 *t = out + (size_t)(d + e) * words;
@@ -149,7 +161,8 @@ int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t entry_bytes, size_t en
 }
 
 int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, int capacity, int *d_total,
-                 int *d_frame_count, int n_frames) {
+                 int *d_frame_count, int n_frames, int compact) {
+    if (compact && entry_bytes != (int)sizeof(vslam_corner)) VS_FAIL(ctx, VSLAM_E_INVALID, "compact lists exist for corners only");
     const long long n = (long long)n_segments;
     const int nb = (int)((n + SCAN_ITEMS - 1) / SCAN_ITEMS);
     if (ctx->seg_partial.reserve((size_t)nb * 4 + 16)) VS_FAIL(ctx, VSLAM_E_NOMEM, "scan partials");
@@ -169,7 +182,7 @@ int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, 
     seg_gather_k<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->seg_off.as<int>(), ctx->seg_cnt.as<int>(),
                                                                         ctx->seg_dst.as<int>(), n, entry_bytes / 4,
                                                                         ctx->staging.as<u32>(), ctx->staging_entries, (u32 *)dst,
-                                                                        capacity);
+                                                                        capacity, compact);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

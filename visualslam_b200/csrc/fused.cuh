@@ -81,6 +81,9 @@ int octave_base_row_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int oc
 // rows .. rows + row_pad - 1 (whole padded rows, so the corners are reflections in both axes)
 int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames);
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
+// tap-table images cached per device: freed when the last context of the device goes (vslam_ctx_destroy)
+void mma_tab_release(int device);
+void umma_tab_release(int device);
 // tcgen05 / TMA variant (fused_umma.cu): same contract as launch_octave_mma; takes the octaves whose kernels have at most 63 taps
 int launch_octave_umma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
 bool octave_uses_umma(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);

@@ -757,11 +757,24 @@ const MmaVariant *mma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int
 }  // namespace
 
 // device image of an octave's shifted tap copies: tab[(4 l + s) cp + j] = tap_l[j + s - padl_l] or 0
+namespace {
+struct MmaTabEntry { int dev; double sigma0; int ss, octave, fw; void *d; };
+std::vector<MmaTabEntry> g_mma_tabs;                  // device images of the tap copies, one per (device, pyramid, octave, width)
+std::mutex g_mma_tabs_mu;
+}  // namespace
+
+// called when the last context of `device` is destroyed (capi.cu): the images live as long as some context can launch with them
+void mma_tab_release(int device) {
+    std::lock_guard<std::mutex> lock(g_mma_tabs_mu);
+    for (size_t i = 0; i < g_mma_tabs.size();)
+        if (g_mma_tabs[i].dev == device) { cudaFree(g_mma_tabs[i].d); g_mma_tabs.erase(g_mma_tabs.begin() + i); }
+        else ++i;
+}
+
 const uint4 *mma_tab_image(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, const MmaTaps &mt) {
-    struct Entry { int dev; double sigma0; int ss, octave, fw; void *d; };
-    static std::vector<Entry> cache;
-    static std::mutex mu;
-    std::lock_guard<std::mutex> lock(mu);
+    typedef MmaTabEntry Entry;
+    std::vector<Entry> &cache = g_mma_tabs;
+    std::lock_guard<std::mutex> lock(g_mma_tabs_mu);
     for (const Entry &e : cache)
         if (e.dev == ctx->device && e.sigma0 == sigma0 && e.ss == scale_samples && e.octave == octave && e.fw == mt.fw) return (const uint4 *)e.d;
     std::vector<u8> img((size_t)mt.tab_bytes, 0);

@@ -674,11 +674,16 @@ bool umma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, Umm
 // device image of an octave's compact Toeplitz tables: V tables [level][core matrix j][row i][byte kk] = tap[8 j + i + kk -
 // 127 + r - P] (rows of the 128-row output block reversed), H tables likewise with 63 + (P - 1): the staged window starts P
 // columns left of the strip and output column n is image column X0 - 1 + n
+namespace {
+struct UmmaTabEntry { int dev; double sigma0; int ss, octave; void *d; };
+std::vector<UmmaTabEntry> g_umma_tabs;
+std::mutex g_umma_tabs_mu;
+}  // namespace
+
 const uint4 *umma_tab_image(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, const UmmaGeom &g) {
-    struct Entry { int dev; double sigma0; int ss, octave; void *d; };
-    static std::vector<Entry> cache;
-    static std::mutex mu;
-    std::lock_guard<std::mutex> lock(mu);
+    typedef UmmaTabEntry Entry;
+    std::vector<Entry> &cache = g_umma_tabs;
+    std::lock_guard<std::mutex> lock(g_umma_tabs_mu);
     for (const Entry &e : cache)
         if (e.dev == ctx->device && e.sigma0 == sigma0 && e.ss == scale_samples && e.octave == octave) return (const uint4 *)e.d;
     std::vector<u8> img((size_t)g.tab_bytes, 0);
@@ -699,6 +704,15 @@ const uint4 *umma_tab_image(vslam_ctx *ctx, double sigma0, int scale_samples, in
     return (const uint4 *)d;
 }
 }  // namespace
+
+// called when the last context of `device` is destroyed (capi.cu)
+void umma_tab_release(int device) {
+    std::lock_guard<std::mutex> lock(g_umma_tabs_mu);
+    for (size_t i = 0; i < g_umma_tabs.size();)
+        if (g_umma_tabs[i].dev == device) { cudaFree(g_umma_tabs[i].d); g_umma_tabs.erase(g_umma_tabs.begin() + i); }
+        else ++i;
+}
+
 
 bool octave_uses_umma(vslam_ctx *ctx, double sigma0, int scale_samples, int octave) {
     UmmaPlan p;

@@ -1,7 +1,8 @@
 """Synthetic frame batches for the bench and the large-size parity tests.
 
 8 unique frames per resolution, cycled to fill a batch, seeded with default_rng(1234 + frame_id):
-  ids 0-3  natural-tile: the bundled building image (grey, from tests/golden/images.npz) mirror-tiled 2x2, cropped,
+  ids 0-3  natural-tile: a 600 x 868 grey photograph (visualslam_b200/data/synth_tile.npz; the package's own copy, so that the
+           bench does not reach into tests/) mirror-tiled 2x2, cropped,
            circularly shifted by a seeded offset (realistic DoG sparsity / keypoint density)
   ids 4-6  procedural: random filled rectangles and discs over a linear ramp + N(0,2) noise
   id  7    uniform noise U{0..255}
@@ -12,13 +13,13 @@ import os
 
 import numpy as np
 
-_GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "images.npz")
+_TILE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "synth_tile.npz")
 _tile_cache = {}
 
 
 def _natural_tile():
     if "t" not in _tile_cache:
-        with np.load(_GOLDEN) as z:
+        with np.load(_TILE) as z:
             b = z["building_cvt"]
         top = np.concatenate([b, b[:, ::-1]], 1)
         _tile_cache["t"] = np.concatenate([top, top[::-1]], 0)

@@ -44,6 +44,11 @@ def lib():
         L.vo_cos_sin_of_angle.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]; L.vo_cos_sin_of_angle.restype = None
         L.vo_rotate_mat_ccw.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, u8p]; L.vo_rotate_mat_ccw.restype = None
         L.vo_rotated_window.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, u8p]; L.vo_rotated_window.restype = None
+        f64p = C.POINTER(C.c_double); i32p_ = C.POINTER(C.c_int)
+        L.vo_get_rotation_matrix_2d.argtypes = [C.c_float, C.c_float, C.c_double, C.c_double, f64p]; L.vo_get_rotation_matrix_2d.restype = None
+        L.vo_warp_affine_u8.argtypes = [u8p, C.c_int, C.c_int, C.c_size_t, f64p, u8p, C.c_int, C.c_int]
+        L.vo_affine_point.argtypes = [f64p, C.c_int, C.c_int, i32p_, i32p_]; L.vo_affine_point.restype = None
+        L.vo_double_crop.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, u8p, C.c_int, i32p_, i32p_, i32p_]
         L.vo_dog.argtypes = [u8p, u8p, C.c_size_t, u8p]
         L.vo_dog.restype = None
         L.vo_half_size.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -132,6 +137,46 @@ def rotated_window(img: np.ndarray, center, window: int, cos_sin) -> np.ndarray:
     out = np.empty((window, window), np.uint8)
     lib().vo_rotated_window(_u8(img), img.shape[0], img.shape[1], int(center[0]), int(center[1]), window, cos_sin[0], cos_sin[1], _u8(out))
     return out
+
+
+def get_rotation_matrix_2d(center, angle_deg: float, scale: float = 1.0) -> np.ndarray:
+    """cv::getRotationMatrix2D(Point2f(center), angle, scale) -> 2 x 3 float64"""
+    m = np.zeros(6, np.float64)
+    lib().vo_get_rotation_matrix_2d(float(center[0]), float(center[1]), float(angle_deg), float(scale), m.ctypes.data_as(C.POINTER(C.c_double)))
+    return m.reshape(2, 3)
+
+
+def warp_affine(img: np.ndarray, m: np.ndarray, dsize) -> np.ndarray:
+    """cv::warpAffine(img, M, dsize = (width, height)): INTER_LINEAR, BORDER_CONSTANT 0, 8UC1"""
+    img = np.ascontiguousarray(img, np.uint8)
+    m = np.ascontiguousarray(m, np.float64).reshape(6)
+    out = np.empty((int(dsize[1]), int(dsize[0])), np.uint8)
+    rc = lib().vo_warp_affine_u8(_u8(img), img.shape[0], img.shape[1], img.shape[1], m.ctypes.data_as(C.POINTER(C.c_double)), _u8(out), out.shape[0], out.shape[1])
+    if rc:
+        raise ValueError(f"vo_warp_affine_u8 -> {rc}")
+    return out
+
+
+def affine_point(m: np.ndarray, x: int, y: int):
+    """Rotation::drawRotated's arithmetic: (int) of M * [x y 1]^T"""
+    m = np.ascontiguousarray(m, np.float64).reshape(6)
+    xr, yr = C.c_int(), C.c_int()
+    lib().vo_affine_point(m.ctypes.data_as(C.POINTER(C.c_double)), int(x), int(y), C.byref(xr), C.byref(yr))
+    return xr.value, yr.value
+
+
+def double_crop(img: np.ndarray, center, window: int, angle: float):
+    """Rotation::doubleCrop (rotation.cpp:147-205) -> (cropped image, first ROI (x, y, w, h)); raises where OpenCV would"""
+    img = np.ascontiguousarray(img, np.uint8)
+    cap = 16 * (window + 4) * (window + 4)
+    out = np.empty(cap, np.uint8)
+    oh, ow = C.c_int(), C.c_int()
+    roi = (C.c_int * 4)()
+    rc = lib().vo_double_crop(_u8(img), img.shape[0], img.shape[1], int(center[0]), int(center[1]), int(window), float(angle), _u8(out), cap,
+                              C.byref(oh), C.byref(ow), roi)
+    if rc:
+        raise ValueError(f"vo_double_crop -> {rc} (roi {list(roi)})")
+    return out[:oh.value * ow.value].reshape(oh.value, ow.value).copy(), tuple(roi)
 
 
 def bgr_to_gray(bgr: np.ndarray) -> np.ndarray:

@@ -43,6 +43,7 @@ def _lib(which: str):
             L.ref_rotate_mat_ccw.restype = None
             L.ref_rotated_window.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, u8p]
             L.ref_rotated_window.restype = C.c_long
+            L.ref_double_crop.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, u8p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
             L.ref_rotate_pt.argtypes = [C.c_int] * 4 + [C.c_float, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
             L.ref_rotate_pt.restype = None
         _libs[which] = L
@@ -126,6 +127,19 @@ def rotate_mat_ccw(img: np.ndarray, center, theta_deg: float) -> np.ndarray:
     out = np.empty_like(img)
     _lib("dog").ref_rotate_mat_ccw(_u8(img), img.shape[0], img.shape[1], int(center[0]), int(center[1]), theta_deg, _u8(out))
     return out
+
+
+def double_crop(img: np.ndarray, center, window: int, angle: float):
+    """SLAM::Rotation::doubleCrop (rotation.cpp:147-205) as compiled from the reference; None where it throws"""
+    img = np.ascontiguousarray(img, np.uint8)
+    cap = 16 * (window + 4) * (window + 4)
+    out = np.empty(cap, np.uint8)
+    oh, ow = C.c_int(), C.c_int()
+    rc = _lib("dog").ref_double_crop(_u8(img), img.shape[0], img.shape[1], int(center[0]), int(center[1]), int(window), float(angle), _u8(out), cap,
+                                     C.byref(oh), C.byref(ow))
+    if rc:
+        return None
+    return out[:oh.value * ow.value].reshape(oh.value, ow.value).copy()
 
 
 def rotated_window(img: np.ndarray, center, window: int, theta_deg: float):

@@ -228,4 +228,18 @@ REF_API void ref_rotate_pt(int x, int y, int cx, int cy, float theta_deg, int cc
                           : SLAM::Rotation::rotate_pt_CW(Point2i(x, y), Point2i(cx, cy), theta_deg, true);
     *xr = p.x; *yr = p.y;
 }
+// SLAM::Rotation::doubleCrop (rotation.cpp:147-205) as written; returns 0, or -3 where the stand-in's Mat(src, Rect) / warpAffine
+// reject what OpenCV would reject (a Rect outside its Mat), -4 when out is too small
+REF_API int ref_double_crop(const uint8_t *img, int h, int w, int cx, int cy, int window, double angle, uint8_t *out, int out_cap, int *oh, int *ow) {
+    try {
+        Mat I = wrap_u8(img, h, w);
+        Mat r = SLAM::Rotation::doubleCrop(I, Point2i(cx, cy), window, angle);
+        *oh = r.rows; *ow = r.cols;
+        if ((long long)r.rows * r.cols > out_cap) return -4;
+        for (int i = 0; i < r.rows; ++i) std::memcpy(out + (size_t)i * r.cols, r.data + (size_t)i * r.step, (size_t)r.cols);
+        return 0;
+    } catch (const std::exception &e) {
+        return -3;
+    }
+}
 #endif  // REF_DOG

@@ -16,6 +16,7 @@ void vo_mag_orient(const float *gx, const float *gy, size_t n, float *mag, float
 int vo_gauss_ksize_32f(double sigma);
 int vo_gauss_taps_32f(double sigma, int n, float *taps);
 int vo_refl101(int p, int len);
+int vo_warp_affine_u8(const uint8_t *src, int h, int w, size_t pitch, const double m[6], uint8_t *dst, int dh, int dw);
 }
 
 namespace cv {
@@ -312,6 +313,19 @@ Mat getRotationMatrix2D(Point2f center, double angle, double scale) {
     return M;
 }
 
-void warpAffine(const Mat &, Mat &, const Mat &, Size) { need(false, "warpAffine (Rotation::doubleCrop is not on the driver's path)"); }
+// cv::warpAffine with the defaults the reference uses (INTER_LINEAR, BORDER_CONSTANT 0) on 8UC1: the oracle's restatement,
+// pinned to cv2 by tests/test_oracle_golden.py.  A ROI view is warped as an image of its own (OpenCV does not look outside it).
+void warpAffine(const Mat &src, Mat &dst, const Mat &M, Size dsize) {
+    need(src.type() == CV_8U && M.type() == CV_64F && M.rows == 2 && M.cols == 3 && src.rows > 0 && src.cols > 0 && dsize.width > 0 && dsize.height > 0,
+         "warpAffine operands");
+    double m[6];
+    for (int i = 0; i < 2; ++i)
+        for (int j = 0; j < 3; ++j) m[3 * i + j] = M.at<double>(i, j);
+    Mat d(dsize.height, dsize.width, CV_8U);
+    std::vector<uchar> out((size_t)dsize.height * dsize.width);
+    need(vo_warp_affine_u8(src.data, src.rows, src.cols, src.step, m, out.data(), dsize.height, dsize.width) == 0, "warpAffine size");
+    undense(out, d);
+    dst = std::move(d);
+}
 
 }  // namespace cv

@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import image_for
+from conftest import GOLDEN, image_for
 from oracle import c_oracle as O
 
 
@@ -253,3 +253,23 @@ def test_oracle_descriptor_stage_vs_cv2_live_on_a_tiny_pyramid():
                     assert np.array_equal(np.isnan(d), np.isnan(desc[n]))
                     if not np.isnan(d).any():
                         assert np.abs(d - desc[n]).max() <= FP32_TOL, (o, l, n)
+
+
+def test_rotation_matrix_warp_affine_and_double_crop_match_cv2():
+    """Rotation::doubleCrop's OpenCV calls (rotation.cpp:152,185,198) and the whole function (:147-205) against cv2 4.13 vectors
+    (tools/make_golden_rotation.py): matrices bit for bit, warped images bit for bit, crops and ROIs identical."""
+    with np.load(os.path.join(GOLDEN, "warp_affine.npz")) as z:
+        g = {k: z[k] for k in z.files}
+    for i, (h, w, ang, cx, cy, dh, dw, scale, seed) in enumerate(g["warp_cases"]):
+        img = np.random.default_rng(int(seed)).integers(0, 256, (int(h), int(w)), dtype=np.uint8)
+        m = O.get_rotation_matrix_2d((cx, cy), ang, scale)
+        assert m.tobytes() == g[f"warp_m_{i}"].tobytes(), (i, m, g[f"warp_m_{i}"])
+        assert np.array_equal(O.warp_affine(img, m, (int(dw), int(dh))), g[f"warp_out_{i}"]), i
+    with np.load(os.path.join(GOLDEN, "images.npz")) as z:
+        blox = z["blox"]
+    for k, (cx, cy, window, ang, x0, y0, rw, rh) in enumerate(g["dcrop_cases"]):
+        crop, roi = O.double_crop(blox, (int(cx), int(cy)), int(window), float(ang))
+        assert roi == (int(x0), int(y0), int(rw), int(rh)), (k, roi)
+        assert crop.shape == g[f"dcrop_{k}"].shape and np.array_equal(crop, g[f"dcrop_{k}"]), (k, crop.shape)
+    with pytest.raises(ValueError):
+        O.double_crop(blox, (10, 10), 100, 45.0)          # the first crop leaves the image: cv::Mat(src, Rect) throws

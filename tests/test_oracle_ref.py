@@ -96,6 +96,15 @@ def test_rotation_matches_reference_code(images, refg):
         assert np.array_equal(O.rotated_window(images["blox"], (100, 120), 16, cs), refg[f"rot_win_{th}"])
 
 
+def test_double_crop_matches_reference_code(images, refg):
+    """SLAM::Rotation::doubleCrop (rotation.cpp:147-205) compiled from the reference: crops identical, and it throws where the
+    first crop leaves the image."""
+    assert bool(refg["dcrop_throws"][0])
+    for k, (cx, cy, win, ang) in enumerate(refg["dcrop_cases"]):
+        crop, _ = O.double_crop(images["blox"], (int(cx), int(cy)), int(win), float(ang))
+        assert crop.shape == refg[f"dcrop_{k}"].shape and np.array_equal(crop, refg[f"dcrop_{k}"]), k
+
+
 @pytest.mark.skipif(not R.available(), reason="oracle/_ref is built only where /root/reference exists")
 def test_live_reference_code_on_seeded_inputs():
     """oracle/_ref executed here: seeded square noise + structure (not a bundled image), Harris and DoG."""

@@ -63,6 +63,13 @@ def main():
     for th in (0, 30, 45, 90, 200, 333):
         out[f"rot_ccw_{th}_md5"] = np.array([md5(R.rotate_mat_ccw(z["blox"], (128, 128), float(th)))])
         out[f"rot_win_{th}"] = R.rotated_window(z["blox"], (100, 120), 16, float(th))[0]
+    # SLAM::Rotation::doubleCrop (rotation.cpp:147-205; warpAffine / getRotationMatrix2D through the stand-in)
+    DC = ((128, 128, 100, 45.0), (100, 120, 64, 30.0), (128, 128, 100, 0.0), (90, 150, 41, -17.5), (128, 128, 50, 90.0), (140, 100, 80, 200.0),
+          (128, 128, 16, 333.0), (60, 200, 33, 12.25))
+    out["dcrop_cases"] = np.array(DC, np.float64)
+    for k, (cx, cy, win, ang) in enumerate(DC):
+        out[f"dcrop_{k}"] = R.double_crop(z["blox"], (cx, cy), win, ang)
+    out["dcrop_throws"] = np.array([R.double_crop(z["blox"], (10, 10), 100, 45.0) is None])
     path = os.path.join(ROOT, "tests", "golden", "ref_golden.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes;", {k: (v.shape if hasattr(v, "shape") else v) for k, v in list(out.items())[:6]})

@@ -220,6 +220,15 @@ VSLAM_API int vslam_rotate_mat_ccw(vslam_ctx *ctx, const uint8_t *src, int rows,
  * and write past its ROI; its reads outside the image are undefined: 0 here). */
 VSLAM_API int vslam_rotated_window(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, int center_x,
                                    int center_y, int window, float cos_a, float sin_a, uint8_t *dst, size_t dst_pitch);
+/* SLAM::Rotation::doubleCrop's two OpenCV calls (include/src/Rotation/rotation.cpp:152,185 and :198); the function itself is
+ * host geometry in visualslam_b200/host/src/rotation.cpp.
+ * cv::getRotationMatrix2D(Point2f(center_x, center_y), angle, scale): m = 6 doubles, row-major 2 x 3.  Host arithmetic only. */
+VSLAM_API int vslam_get_rotation_matrix_2d(float center_x, float center_y, double angle_deg, double scale, double *m);
+/* cv::warpAffine(src, dst, M, Size(dst_cols, dst_rows)) with the defaults the reference uses: INTER_LINEAR, BORDER_CONSTANT 0,
+ * 8UC1, M the forward 2 x 3 matrix (inverted inside, as OpenCV does).  Bit-exact with OpenCV's fixed-point path (10-bit
+ * coordinates, 5 fractional bits, 15-bit weights). */
+VSLAM_API int vslam_warp_affine(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, const double *m,
+                                uint8_t *dst, int dst_rows, int dst_cols, size_t dst_pitch);
 /* GaussianBlur(img, blurred, Size(3,3), 0, 0, BORDER_DEFAULT) on 8U (Harris_corners.cpp:157-158) */
 VSLAM_API int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst,
                                    size_t dst_pitch);

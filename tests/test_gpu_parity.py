@@ -587,3 +587,23 @@ def test_descriptors_five_octaves_other_sigma(ctx):
     wd, wv = O.sift(opyr["gauss"][4], opyr["sigma"][4], want)
     assert np.array_equal(v, wv) and same_floats(d, wd)
     pyr.close()
+
+
+def test_warp_affine_and_rotation_matrix_vs_cv2_and_oracle(ctx):
+    """vslam_get_rotation_matrix_2d / vslam_warp_affine (Rotation::doubleCrop's OpenCV calls, rotation.cpp:152,185,198): the cv2
+    4.13 vectors bit for bit (matrices and images), and the oracle on sizes the vectors do not hold (1-pixel images, large shifts)."""
+    import os
+    from conftest import GOLDEN
+    with np.load(os.path.join(GOLDEN, "warp_affine.npz")) as z:
+        g = {k: z[k] for k in z.files}
+    for i, (h, w, ang, cx, cy, dh, dw, scale, seed) in enumerate(g["warp_cases"]):
+        img = np.random.default_rng(int(seed)).integers(0, 256, (int(h), int(w)), dtype=np.uint8)
+        m = vs.api.get_rotation_matrix_2d((cx, cy), ang, scale)
+        assert m.tobytes() == g[f"warp_m_{i}"].tobytes(), i
+        assert np.array_equal(ctx.warp_affine(img, m, (int(dw), int(dh))), g[f"warp_out_{i}"]), i
+    rng = np.random.default_rng(5)
+    for (h, w, dh, dw) in ((1, 1, 5, 7), (1, 37, 9, 40), (37, 1, 40, 9), (300, 217, 64, 500), (64, 64, 1, 1)):
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        m = O.get_rotation_matrix_2d((w / 2.0, h / 2.0), float(rng.uniform(-180, 180)), float(rng.uniform(0.3, 3.0)))
+        m[:, 2] += rng.uniform(-40, 40, 2)
+        assert np.array_equal(ctx.warp_affine(img, m, (dw, dh)), O.warp_affine(img, m, (dw, dh))), (h, w, dh, dw)

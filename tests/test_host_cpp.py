@@ -166,6 +166,10 @@ def test_rotate_img_test_executable(tmp_path, images):
         return np.frombuffer(parts[3], np.uint8).reshape(h, w)
     assert np.array_equal(pgm(str(tmp_path / "r_rotated.pgm")), O.rotate_mat_ccw(img, center, cs))
     assert np.array_equal(pgm(str(tmp_path / "r_roi.pgm")), O.rotated_window(img, center, 100, cs))
+    # the double-crop comparison (rotate_image_test.cpp:85-94): its timing line, and the crop equals the oracle's (= cv2's, = the
+    # reference's own compiled doubleCrop: tests/test_oracle_ref.py)
+    assert "Time rotating 16x16 ROI with the double crop method (averaged for 100 runs):" in r.stdout
+    assert np.array_equal(pgm(str(tmp_path / "r_roi2.pgm")), O.double_crop(img, center, 100, 45.0)[0])
 
 
 @pytest.mark.gpu

@@ -58,7 +58,7 @@ EXPORTS = [
     "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
     "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
-    "vslam_bgr_to_gray", "vslam_rotate_mat_ccw", "vslam_rotated_window", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
+    "vslam_bgr_to_gray", "vslam_rotate_mat_ccw", "vslam_rotated_window", "vslam_get_rotation_matrix_2d", "vslam_warp_affine", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
     "vslam_dog_detect_octave", "vslam_edge_responses", "vslam_localize", "vslam_edge_from_windows",
     # the stage after the hot path: orientation assignment, SIFT descriptors, featureDescriptors.dat
     "vslam_gauss_ksize_f32", "vslam_gauss_taps_f32", "vslam_assign_orientations", "vslam_sift_descriptors",
@@ -95,6 +95,8 @@ def load():
     L.vslam_bgr_to_gray.argtypes = [vp, vp, i, i, i, sz, sz, vp, sz, sz]
     L.vslam_rotate_mat_ccw.argtypes = [vp, vp, i, i, sz, i, i, C.c_float, C.c_float, vp, sz]
     L.vslam_rotated_window.argtypes = [vp, vp, i, i, sz, i, i, i, C.c_float, C.c_float, vp, sz]
+    L.vslam_get_rotation_matrix_2d.argtypes = [C.c_float, C.c_float, C.c_double, C.c_double, C.POINTER(C.c_double)]
+    L.vslam_warp_affine.argtypes = [vp, vp, i, i, sz, C.POINTER(C.c_double), vp, i, i, sz]
     L.vslam_pyramid_build.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(vp)]
     L.vslam_pyramid_destroy.argtypes = [vp]; L.vslam_pyramid_destroy.restype = None
     L.vslam_pyramid_num_octaves.argtypes = [vp]
@@ -117,6 +119,13 @@ def load():
     L.vslam_harris_response_static.argtypes = [vp, vp, i, i, sz, i, C.c_float, vp, vp]
     _lib = L
     return L
+
+
+def get_rotation_matrix_2d(center, angle_deg, scale=1.0):
+    """cv::getRotationMatrix2D(Point2f(center), angle, scale) -> 2 x 3 float64 (host arithmetic of the library)"""
+    m = np.zeros(6, np.float64)
+    load().vslam_get_rotation_matrix_2d(float(center[0]), float(center[1]), float(angle_deg), float(scale), m.ctypes.data_as(C.POINTER(C.c_double)))
+    return m.reshape(2, 3)
 
 
 def expand_corners(c8):
@@ -423,6 +432,15 @@ class Context:
         out = np.empty((window, window), np.uint8)
         self._chk(load().vslam_rotated_window(self.h, a.ctypes.data, a.shape[0], a.shape[1], a.shape[1], int(center[0]), int(center[1]),
                                               int(window), float(cos_sin[0]), float(cos_sin[1]), out.ctypes.data, window))
+        return out
+
+    def warp_affine(self, img, m, dsize):
+        """cv::warpAffine(img, M, dsize = (width, height)): INTER_LINEAR, BORDER_CONSTANT 0, 8UC1 (rotation.cpp:198)"""
+        a = np.ascontiguousarray(img, np.uint8)
+        mm = np.ascontiguousarray(m, np.float64).reshape(6)
+        out = np.empty((int(dsize[1]), int(dsize[0])), np.uint8)
+        self._chk(load().vslam_warp_affine(self.h, a.ctypes.data, a.shape[0], a.shape[1], a.shape[1], mm.ctypes.data_as(C.POINTER(C.c_double)),
+                                           out.ctypes.data, out.shape[0], out.shape[1], out.shape[1]))
         return out
 
     def harris(self, frames, k=0.04, nms2_window=5, want_maps=True, capacity=1 << 20, device_out=None, corners_out=None, compact=False):

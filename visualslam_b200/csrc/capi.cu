@@ -915,6 +915,39 @@ int vslam_rotated_window(vslam_ctx *ctx, const uint8_t *src, int rows, int cols,
                          dst_pitch, 1);
 }
 
+int vslam_get_rotation_matrix_2d(float center_x, float center_y, double angle_deg, double scale, double *m) {
+    if (!m) return VSLAM_E_INVALID;
+    double angle = angle_deg;
+    angle *= 3.1415926535897932384626433832795 / 180;                        // CV_PI / 180
+    const double alpha = cos(angle) * scale, beta = sin(angle) * scale;
+    m[0] = alpha; m[1] = beta; m[2] = (1 - alpha) * center_x - beta * center_y;
+    m[3] = -beta; m[4] = alpha; m[5] = beta * center_x + (1 - alpha) * center_y;
+    return VSLAM_OK;
+}
+
+int vslam_warp_affine(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, const double *m, uint8_t *dst, int dst_rows,
+                      int dst_cols, size_t dst_pitch) {
+    VS_TRY(stage_check(ctx, src, dst, rows, cols));
+    if (!m || dst_rows <= 0 || dst_cols <= 0 || dst_rows > 65535 || dst_cols > (1 << 15)) VS_FAIL(ctx, VSLAM_E_INVALID, "warp_affine: destination %dx%d", dst_rows, dst_cols);
+    if (pitch < (size_t)cols || dst_pitch < (size_t)dst_cols) VS_FAIL(ctx, VSLAM_E_INVALID, "warp_affine: pitch smaller than a row");
+    // imgwarp.cpp: without WARP_INVERSE_MAP the matrix is inverted first (doubles, each operation on its own)
+    double M[6];
+    for (int i = 0; i < 6; ++i) M[i] = m[i];
+    double D = M[0] * M[4] - M[1] * M[3];
+    D = D != 0 ? 1. / D : 0;
+    const double A11 = M[4] * D, A22 = M[0] * D;
+    M[0] = A11; M[1] *= -D; M[3] *= -D; M[4] = A22;
+    const double b1 = -M[0] * M[2] - M[1] * M[5], b2 = -M[3] * M[2] - M[4] * M[5];
+    M[2] = b1; M[5] = b2;
+    const size_t b[2] = {(size_t)rows * cols, (size_t)dst_rows * dst_cols};
+    u8 *d[2];
+    VS_TRY(stage_scratch(ctx, b, 2, d));
+    VS_CUDA(ctx, cudaMemcpy2DAsync(d[0], cols, src, pitch, cols, rows, cudaMemcpyHostToDevice, ctx->stream));
+    VS_TRY(launch_warp_affine(ctx, d[0], rows, cols, cols, M, d[1], dst_rows, dst_cols, dst_cols));
+    VS_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_pitch, d[1], dst_cols, dst_cols, dst_rows, cudaMemcpyDeviceToHost, ctx->stream));
+    return vslam_sync(ctx);
+}
+
 int vslam_gaussian_blur3(vslam_ctx *ctx, const uint8_t *src, int rows, int cols, size_t pitch, uint8_t *dst, size_t dst_pitch) {
     VS_TRY(stage_check(ctx, src, dst, rows, cols));
     if (pitch < (size_t)cols || dst_pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch smaller than cols");

@@ -179,7 +179,44 @@ __global__ void rotate_gather_k(const u8 *__restrict__ src, int rows, int cols, 
     dst[(size_t)i * dpitch + j] = in ? src[(size_t)yr * pitch + xr] : (u8)0;
 }
 
+// cv::warpAffine(src, dst, M, dsize) with the defaults Rotation::doubleCrop uses (rotation.cpp:198): INTER_LINEAR,
+// BORDER_CONSTANT 0, 8UC1.  mi = the INVERTED matrix (the host inverts like imgwarp.cpp does).  OpenCV walks the destination
+// in 10-bit fixed point: X0 = cvRound((mi1 y + mi2) 1024) + 16 per row, adelta = cvRound(mi0 x 1024) per column (doubles, each
+// operation rounded on its own), keeps 5 fractional bits and blends four taps with the 15-bit weights of BilinearTab_i --
+// (32 - fx)(32 - fy) 32 ..., except the (0, 0) entry, which is {32767, 0, 0, 1} (saturate_cast<short>(32768) + the sum fix-up).
+struct WarpM { double m[6]; };
+__global__ void warp_affine_k(const u8 *__restrict__ src, int rows, int cols, size_t pitch, const WarpM mi, u8 *__restrict__ dst, int drows,
+                              int dcols, size_t dpitch) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= dcols || y >= drows) return;
+    const int X0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(mi.m[1], (double)y), mi.m[2]), 1024.0)) + 16;
+    const int Y0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(mi.m[4], (double)y), mi.m[5]), 1024.0)) + 16;
+    const int X = (X0 + __double2int_rn(__dmul_rn(__dmul_rn(mi.m[0], (double)x), 1024.0))) >> 5;
+    const int Y = (Y0 + __double2int_rn(__dmul_rn(__dmul_rn(mi.m[3], (double)x), 1024.0))) >> 5;
+    const int sx = clampi(X >> 5, -32768, 32767), sy = clampi(Y >> 5, -32768, 32767);        // saturate_cast<short>
+    const int fx = X & 31, fy = Y & 31;
+    int w00 = (32 - fx) * (32 - fy) * 32, w01 = fx * (32 - fy) * 32, w10 = (32 - fx) * fy * 32, w11 = fx * fy * 32;
+    if (!(fx | fy)) { w00 = 32767; w11 = 1; }
+    const bool x0in = (unsigned)sx < (unsigned)cols, x1in = (unsigned)(sx + 1) < (unsigned)cols;
+    const bool y0in = (unsigned)sy < (unsigned)rows, y1in = (unsigned)(sy + 1) < (unsigned)rows;
+    const u8 *r0 = src + (size_t)(y0in ? sy : 0) * pitch, *r1 = src + (size_t)(y1in ? sy + 1 : 0) * pitch;
+    const int v00 = x0in && y0in ? r0[sx] : 0, v01 = x1in && y0in ? r0[sx + 1] : 0;
+    const int v10 = x0in && y1in ? r1[sx] : 0, v11 = x1in && y1in ? r1[sx + 1] : 0;
+    const int acc = (v00 * w00 + v01 * w01 + v10 * w10 + v11 * w11 + (1 << 14)) >> 15;
+    dst[(size_t)y * dpitch + x] = (u8)min(acc, 255);
+}
+
 #define GRID2D(cols, rows) dim3(((cols) + 127) / 128, (rows)), 128, 0, ctx->stream
+
+int launch_warp_affine(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, const double *minv, u8 *dst, int drows, int dcols,
+                       size_t dpitch) {
+    WarpM m;
+    for (int i = 0; i < 6; ++i) m.m[i] = minv[i];
+    KernelSpan span(ctx, VSLAM_K_UPSAMPLE);
+    warp_affine_k<<<GRID2D(dcols, drows)>>>(src, rows, cols, pitch, m, dst, drows, dcols, dpitch);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
 
 int launch_blur3(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, u8 *dst, size_t dpitch) {
     KernelSpan span(ctx, VSLAM_K_HARRIS);

@@ -7,6 +7,8 @@ int launch_bgr2gray(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pi
                     size_t dstride, int n_frames);
 int launch_rotate_gather(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, int cx, int cy, float c, float s, int x0,
                          int y0, int ow, int oh, u8 *dst, size_t dpitch, int mode);
+int launch_warp_affine(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, const double *minv, u8 *dst, int drows, int dcols,
+                       size_t dpitch);
 int launch_blur3(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, u8 *dst, size_t dpitch);
 int launch_sobel1(vslam_ctx *ctx, const u8 *src, int rows, int cols, size_t pitch, float *gx, float *gy);
 int launch_harris_grad(vslam_ctx *ctx, const float *ix, const float *iy, int rows, int cols, int pad, float k, float *out);

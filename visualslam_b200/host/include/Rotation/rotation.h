@@ -1,8 +1,9 @@
 // rotation.h -- SLAM::Rotation of the reference (KeyPointDetection/include/src/Rotation/rotation.h:11-26), same static
 // methods, on vslam::Mat.  The point helpers are host geometry exactly as written in rotation.cpp:5-62 (float products of
 // int offsets, truncation); the two image gathers run on the GPU through the C ABI (vslam_rotate_mat_ccw,
-// vslam_rotated_window).  Not mirrored: drawRotated / doubleCrop (rotation.cpp:132-202) -- cv::warpAffine and drawing
-// have no counterpart on this box; doubleCrop throws.
+// vslam_rotated_window).  drawRotated / doubleCrop (rotation.cpp:132-205): the point arithmetic is host code as written
+// (M * [x y 1]^T in double, truncation), cv::warpAffine runs on the GPU (vslam_warp_affine); drawRotated's circles are not
+// drawn (no HighGUI on this box).
 #pragma once
 #include <vector>
 
@@ -33,6 +34,7 @@ class Rotation : public Transform {
     static Mat rotate_mat_CCW(Mat &I, const Point2i &center, const Point2f &angles);
     static Mat getRotatedWindow(Mat &I, const Point2i &center, int windowSize, float theta, bool degrees = true);
     static std::vector<Point2i> getRotatedWindowPoints(Mat &I, const Point2i &center, int windowSize, float theta, bool degrees = true);
-    static Mat doubleCrop(Mat &src, const Point2i &center, int windowSize, double angle);   // throws: needs cv::warpAffine
+    static vslam::Point drawRotated(vslam::Point &pt, Mat &src, Mat &roi_rotation_mat, bool draw = true);
+    static Mat doubleCrop(Mat &src, const Point2i &center, int windowSize, double angle);
 };
 }  // namespace SLAM

@@ -2,7 +2,7 @@
 //
 // The reference's surface is written against cv::Mat (GaussPyramid.hpp:2-6); OpenCV C++ does not exist on the target
 // box, so the drop-in keeps the reference's names and call shapes on this minimal ref-counted matrix: rows, cols, type
-// (CV_8U / CV_32F only), at<T>(r, c), clone(), zeros(), plus PGM (8U) / PFM (32F) file IO instead of imread/imshow.
+// (CV_8U / CV_32F; CV_64F for the 2 x 3 matrices of SLAM::Rotation), at<T>(r, c), clone(), zeros(), plus PGM (8U) / PFM (32F) file IO instead of imread/imshow.
 // No arithmetic lives here: every operator of the hot path goes through the C ABI (include/vslam.h).
 #pragma once
 #include <cstdint>
@@ -14,7 +14,7 @@
 
 namespace vslam {
 
-constexpr int CV_8U = 0, CV_32F = 5, CV_8UC3 = 16;   // OpenCV's type codes, so ported call sites read the same
+constexpr int CV_8U = 0, CV_32F = 5, CV_64F = 6, CV_8UC3 = 16;   // OpenCV's type codes, so ported call sites read the same
 constexpr int IMREAD_GRAYSCALE = 0, IMREAD_COLOR = 1, COLOR_BGR2GRAY = 6;
 
 struct Size {
@@ -33,14 +33,14 @@ class Mat {
     Mat(int r, int c, int type) { create(r, c, type); }
     static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }   // create() zero-fills
     void create(int r, int c, int type) {
-        if (r < 0 || c < 0 || (type != CV_8U && type != CV_32F && type != CV_8UC3)) throw std::invalid_argument("vslam::Mat: bad shape or type");
+        if (r < 0 || c < 0 || (type != CV_8U && type != CV_32F && type != CV_64F && type != CV_8UC3)) throw std::invalid_argument("vslam::Mat: bad shape or type");
         rows = r; cols = c; type_ = type;
         step = (size_t)c * elemSize();
         buf_ = std::shared_ptr<uint8_t>(new uint8_t[step * (size_t)r + 1](), std::default_delete<uint8_t[]>());
         data = buf_.get();
     }
     int type() const { return type_; }
-    size_t elemSize() const { return type_ == CV_32F ? 4 : type_ == CV_8UC3 ? 3 : 1; }
+    size_t elemSize() const { return type_ == CV_32F ? 4 : type_ == CV_64F ? 8 : type_ == CV_8UC3 ? 3 : 1; }
     int channels() const { return type_ == CV_8UC3 ? 3 : 1; }
     bool empty() const { return !data || rows == 0 || cols == 0; }
     Size size() const { return Size{cols, rows}; }
@@ -70,6 +70,10 @@ Mat imread_pgm(const std::string &path);                 // throws std::runtime_
 Mat imread(const std::string &path, int flags = IMREAD_COLOR);
 // cvtColor(src, dst, COLOR_BGR2GRAY) on the GPU (vslam_bgr_to_gray); the only conversion the reference uses
 void cvtColor(const Mat &src, Mat &dst, int code);
+// cv::getRotationMatrix2D / cv::warpAffine as SLAM::Rotation::doubleCrop calls them (rotation.cpp:152,185,198): a 2 x 3 CV_64F
+// matrix (host arithmetic behind vslam_get_rotation_matrix_2d) and the bilinear warp of an 8U image on the GPU (vslam_warp_affine)
+Mat getRotationMatrix2D(float center_x, float center_y, double angle, double scale);
+void warpAffine(const Mat &src, Mat &dst, const Mat &M, Size dsize);
 void imwrite_pgm(const std::string &path, const Mat &m);
 void imwrite_pfm(const std::string &path, const Mat &m);
 

@@ -35,6 +35,23 @@ void cvtColor(const Mat &src, Mat &dst, int code) {
     dst = out;
 }
 
+// cv::getRotationMatrix2D(Point2f center, angle, scale): rotation.cpp:152,185
+Mat getRotationMatrix2D(float center_x, float center_y, double angle, double scale) {
+    Mat m(2, 3, CV_64F);
+    throw_on(vslam_get_rotation_matrix_2d(center_x, center_y, angle, scale, m.ptr<double>()), "vslam_get_rotation_matrix_2d");
+    return m;
+}
+
+// cv::warpAffine(src, dst, M, dsize) with the defaults (INTER_LINEAR, BORDER_CONSTANT 0): rotation.cpp:198
+void warpAffine(const Mat &src, Mat &dst, const Mat &M, Size dsize) {
+    if (src.type() != CV_8U || src.empty() || M.type() != CV_64F || M.rows != 2 || M.cols != 3 || dsize.width <= 0 || dsize.height <= 0)
+        throw std::invalid_argument("warpAffine: non-empty CV_8U image, 2 x 3 CV_64F matrix, positive size");
+    Mat out(dsize.height, dsize.width, CV_8U);
+    throw_on(vslam_warp_affine(host_context(), src.data, src.rows, src.cols, src.step, M.ptr<double>(), out.data, out.rows, out.cols, out.step),
+             "vslam_warp_affine");
+    dst = out;
+}
+
 }  // namespace vslam
 
 using namespace vslam;

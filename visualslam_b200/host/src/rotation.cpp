@@ -1,7 +1,9 @@
 // rotation.cpp -- host side of SLAM::Rotation (reference: include/src/Rotation/rotation.cpp).
 #include "Rotation/rotation.h"
 
+#include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <stdexcept>
 
 namespace SLAM {
@@ -62,8 +64,47 @@ std::vector<Point2i> Rotation::getRotatedWindowPoints(Mat &, const Point2i &cent
     return rotatedPoints;
 }
 
-Mat Rotation::doubleCrop(Mat &, const Point2i &, int, double) {
-    throw std::runtime_error("Rotation::doubleCrop needs cv::getRotationMatrix2D / cv::warpAffine: not part of this build");
+// drawRotated (:133-145): roi_rotation_mat (2 x 3, CV_64F) * [x y 1]^T -- cv::gemm sums the three products left to right in
+// double -- and (int) truncation.  The circles of draw = true are not drawn (no HighGUI here).
+vslam::Point Rotation::drawRotated(vslam::Point &pt, Mat &, Mat &m, bool) {
+    if (m.type() != vslam::CV_64F || m.rows != 2 || m.cols != 3) throw std::invalid_argument("drawRotated: 2 x 3 CV_64F matrix expected");
+    volatile double s0 = 0, s1 = 0;
+    s0 = s0 + m.at<double>(0, 0) * (double)pt.x; s0 = s0 + m.at<double>(0, 1) * (double)pt.y; s0 = s0 + m.at<double>(0, 2) * 1.0;
+    s1 = s1 + m.at<double>(1, 0) * (double)pt.x; s1 = s1 + m.at<double>(1, 1) * (double)pt.y; s1 = s1 + m.at<double>(1, 2) * 1.0;
+    return vslam::Point((int)s0, (int)s1);
+}
+
+// a Rect of a Mat as a Mat of its own (cv::Mat(src, Rect) is a view; warpAffine never looks outside it, so a copy is equivalent);
+// throws where OpenCV's constructor asserts
+static Mat crop_of(const Mat &src, int x, int y, int w, int h) {
+    if (x < 0 || y < 0 || w < 0 || h < 0 || x + w > src.cols || y + h > src.rows) throw std::out_of_range("Rotation: Rect outside the matrix");
+    Mat r(h, w, vslam::CV_8U);
+    for (int i = 0; i < h; ++i) std::memcpy(r.data + (size_t)i * r.step, src.data + (size_t)(y + i) * src.step + x, (size_t)w);
+    return r;
+}
+
+Mat Rotation::doubleCrop(Mat &src, const Point2i &center, int windowSize, double angle) {               // :147-205
+    if (src.type() != vslam::CV_8U) throw std::invalid_argument("doubleCrop: CV_8U only");
+    const int padding = windowSize / 2;
+    const double scale = 1.0;
+    Mat rotation_mat = vslam::getRotationMatrix2D((float)center.x, (float)center.y, angle, scale);       // :152
+    vslam::Point pos1(center.x - padding, center.y - padding), pos2(center.x + padding, center.y - padding);   // :156-166
+    vslam::Point pos3(center.x - padding, center.y + padding), pos4(center.x + padding, center.y + padding);
+    const vslam::Point r[4] = {drawRotated(pos1, src, rotation_mat, false), drawRotated(pos2, src, rotation_mat, false),
+                               drawRotated(pos3, src, rotation_mat, false), drawRotated(pos4, src, rotation_mat, false)};
+    int min_x = r[0].x, max_x = r[0].x, min_y = r[0].y, max_y = r[0].y;                                  // :169-175
+    for (int i = 1; i < 4; ++i) {
+        min_x = std::min(min_x, r[i].x); max_x = std::max(max_x, r[i].x);
+        min_y = std::min(min_y, r[i].y); max_y = std::max(max_y, r[i].y);
+    }
+    Mat ROI = crop_of(src, min_x, min_y, max_x - min_x, max_y - min_y);                                  // :181
+    Mat roi_rotation_mat = vslam::getRotationMatrix2D((float)(ROI.cols / 2), (float)(ROI.rows / 2), angle, scale);   // :184-185
+    vslam::Point roi_pos1(ROI.cols / 2, 0), roi_pos4(ROI.cols / 2, ROI.rows);                            // :187, :190
+    const vslam::Point p1 = drawRotated(roi_pos1, ROI, roi_rotation_mat, false), p4 = drawRotated(roi_pos4, ROI, roi_rotation_mat, false);
+    Mat rotate_dst;
+    vslam::warpAffine(ROI, rotate_dst, roi_rotation_mat, ROI.size());                                    // :198
+    const int x0 = std::min(p1.x, p4.x), y0 = std::min(p1.y, p4.y);                                      // :201 Rect(p1, p4)
+    return crop_of(rotate_dst, x0, y0, std::max(p1.x, p4.x) - x0, std::max(p1.y, p4.y) - y0);
 }
 
 }  // namespace SLAM

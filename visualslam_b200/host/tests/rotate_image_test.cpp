@@ -1,6 +1,6 @@
 // RotateImgTest -- the reference's tests/rotate_image_test.cpp:55-84 on the GPU-backed SLAM::Rotation, headless: the
 // timing line of the rotated 16x16 window (the only numbers the reference's test prints), plus the rotated image and
-// window written as PGM files instead of imshow / trackbars.  The double-crop comparison (:87-97) needs cv::warpAffine.
+// window written as PGM files instead of imshow / trackbars, and the double-crop comparison (:85-97) with its own timing line.
 //   usage: RotateImgTest [image.pgm] [--angle deg] [--dump prefix]          (default image: ../images/blox.pgm)
 #include <chrono>
 #include <cstring>
@@ -28,13 +28,18 @@ int main(int argc, char **argv) {
         for (int i = 0; i < times; i++) SLAM::Rotation::getRotatedWindow(img, center, windowSize, angle);   // :75-78
         double t = chrono::duration<double, milli>(chrono::steady_clock::now() - t0).count() / times;
         cout << "Time rotating 16x16 ROI (averaged for " << times << " runs): " << t << " milliseconds." << endl;      // :81
-        cout << "Time rotating 16x16 ROI with the double crop method: unavailable (cv::warpAffine is not part of this build)" << endl;
+        Mat ROI2 = SLAM::Rotation::doubleCrop(img, center, 100, (double)angle);                 // :86
+        t0 = chrono::steady_clock::now();
+        for (int i = 0; i < times; i++) SLAM::Rotation::doubleCrop(img, center, windowSize, (double)angle);   // :88-91
+        t = chrono::duration<double, milli>(chrono::steady_clock::now() - t0).count() / times;
+        cout << "Time rotating 16x16 ROI with the double crop method (averaged for " << times << " runs): " << t << " milliseconds." << endl;   // :94
         Mat rotated = SLAM::Rotation::rotate_mat_CCW(img, center, SLAM::Rotation::cos_sin_of_angle(angle));   // Rotation_Demo :44-48
         const Point2i rot = SLAM::Rotation::rotate_pt_CCW(Point2i(img.cols / 2, 0), center, angle);           // Rotation_Point_Demo :51-56
         cout << "Rotated point: (" << rot.x << ", " << rot.y << ")" << endl;
         if (!dump.empty()) {
             vslam::imwrite_pgm(dump + "_rotated.pgm", rotated);
             vslam::imwrite_pgm(dump + "_roi.pgm", ROI);
+            if (!ROI2.empty()) vslam::imwrite_pgm(dump + "_roi2.pgm", ROI2);
         }
     } catch (const std::exception &e) {
         fprintf(stderr, "RotateImgTest: %s\n", e.what());

@@ -388,22 +388,30 @@ class Context:
         self._chk(load().vslam_sift_descriptors(self.h, pyr.h, frame, octave, kp.ctypes.data, n, desc.ctypes.data, valid.ctypes.data))
         return desc, valid
 
-    def describe_keypoints(self, pyr, keypoints, counts, capacity=None):
-        """Orientation assignment + SIFT for every frame of a pyramid in five launches (vslam_describe_keypoints)."""
+    def describe_keypoints(self, pyr, keypoints, counts, capacity=None, out=None):
+        """Orientation assignment + SIFT for every frame of a pyramid in five launches (vslam_describe_keypoints).
+        out = (oriented [cap] KEYPOINT_DTYPE or int32 [cap, 6], descriptors float32 [cap, 128], valid uint8 [cap]): caller-owned
+        result buffers, e.g. views of pinned memory (a 100 MB descriptor block lands in pageable memory at a fraction of the PCIe rate)."""
         kp = np.ascontiguousarray(keypoints).view(KEYPOINT_DTYPE).reshape(-1)
         assert len(counts) == pyr.n_frames and sum(counts) == kp.shape[0]
-        capacity = 36 * max(kp.shape[0], 1) if capacity is None else capacity
-        out = np.zeros(capacity, KEYPOINT_DTYPE)
-        desc = np.zeros((capacity, 128), np.float32)
-        valid = np.zeros(capacity, np.uint8)
+        if out is not None:
+            o, desc, valid = out
+            o = o.view(KEYPOINT_DTYPE).reshape(-1)
+            capacity = min(o.shape[0], desc.shape[0], valid.shape[0])
+            assert desc.dtype == np.float32 and desc.shape[1] == 128 and valid.dtype == np.uint8 and desc.flags.c_contiguous
+        else:
+            capacity = 36 * max(kp.shape[0], 1) if capacity is None else capacity
+            o = np.zeros(capacity, KEYPOINT_DTYPE)
+            desc = np.zeros((capacity, 128), np.float32)
+            valid = np.zeros(capacity, np.uint8)
         cin = (C.c_int * pyr.n_frames)(*[int(c) for c in counts])
         cout = (C.c_int * pyr.n_frames)()
-        rc = load().vslam_describe_keypoints(self.h, pyr.h, kp.ctypes.data, cin, out.ctypes.data, capacity, cout, desc.ctypes.data,
+        rc = load().vslam_describe_keypoints(self.h, pyr.h, kp.ctypes.data, cin, o.ctypes.data, capacity, cout, desc.ctypes.data,
                                              valid.ctypes.data)
         if rc and rc != E_CAPACITY:
             self._chk(rc)
         m = min(sum(cout), capacity)
-        return {"oriented": out[:m], "descriptors": desc[:m], "valid": valid[:m], "counts": list(cout), "overflow": rc == E_CAPACITY}
+        return {"oriented": o[:m], "descriptors": desc[:m], "valid": valid[:m], "counts": list(cout), "overflow": rc == E_CAPACITY}
 
     def bgr_to_gray(self, bgr):
         """cvtColor(COLOR_BGR2GRAY) of (rows, cols, 3) or (n, rows, cols, 3) uint8 frames -> uint8 gray frames."""

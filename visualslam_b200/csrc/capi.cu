@@ -1124,14 +1124,25 @@ static int run_orientations(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame,
     // launched in width classes, each with the shared memory its widest member needs: the narrow classes, which hold most of
     // the keypoints, then fit many more CTAs per SM than a launch sized for the widest kernel would allow
     std::vector<std::pair<int, int>> by_r((size_t)n);                      // (-r, index): stable order inside one width
-    for (int i = 0; i < n; ++i) {
-        const int o = octave >= 0 ? octave : kp[i].octave;
-        const int ks = (o >= 0 && o < pyr->num_octaves && kp[i].level >= 0 && kp[i].level < 6) ? P.ksize[o][kp[i].level] : 1;
-        by_r[(size_t)i] = {-(ks / 2), i};
-    }
-    std::sort(by_r.begin(), by_r.end());
     std::vector<int> order((size_t)n);
-    for (int i = 0; i < n; ++i) order[(size_t)i] = by_r[(size_t)i].second;
+    {   // counting sort on the radius (a dozen distinct values): the list order is kept inside one width
+        std::vector<int> rad((size_t)n);
+        int rmax = 0;
+        for (int i = 0; i < n; ++i) {
+            const int o = octave >= 0 ? octave : kp[i].octave;
+            const int ks = (o >= 0 && o < pyr->num_octaves && kp[i].level >= 0 && kp[i].level < 6) ? P.ksize[o][kp[i].level] : 1;
+            rad[(size_t)i] = ks / 2;
+            rmax = ks / 2 > rmax ? ks / 2 : rmax;
+        }
+        std::vector<int> start((size_t)rmax + 2, 0);
+        for (int i = 0; i < n; ++i) ++start[(size_t)(rmax - rad[(size_t)i]) + 1];          // bucket = rmax - r: widest first
+        for (int b2 = 0; b2 <= rmax; ++b2) start[(size_t)b2 + 1] += start[(size_t)b2];
+        for (int i = 0; i < n; ++i) {
+            const int pos = start[(size_t)(rmax - rad[(size_t)i])]++;
+            by_r[(size_t)pos] = {-rad[(size_t)i], i};
+            order[(size_t)pos] = i;
+        }
+    }
     const size_t b[6] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, histograms ? 144 * (size_t)n : 0, 4 * h_taps.size(), frame_of ? 4 * (size_t)n : 0,
                          4 * (size_t)n};
     u8 *d[6];
@@ -1166,9 +1177,17 @@ static int run_sift(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int oct
     int max_r = 0;
     VS_TRY(desc_pyr(ctx, pyr, frame, octave, kp, n, h_taps, P, max_r));
     std::vector<float2> cs((size_t)n);
-    for (int i = 0; i < n; ++i) {                                          // Rotation::cos_sin_of_angle (rotation.cpp:9-17)
-        const float angle = (float)((double)(float)kp[i].value * (3.1415926535897932384626433832795 / (double)180.0f));
-        cs[i] = make_float2((float)cos((double)angle), (float)sin((double)angle));
+    {   // Rotation::cos_sin_of_angle (rotation.cpp:9-17); the orientation stage only emits bin * 10 degrees: 36 distinct angles
+        auto cos_sin = [](int value) {
+            const float angle = (float)((double)(float)value * (3.1415926535897932384626433832795 / (double)180.0f));
+            return make_float2((float)cos((double)angle), (float)sin((double)angle));
+        };
+        float2 lut[36];
+        for (int b2 = 0; b2 < 36; ++b2) lut[b2] = cos_sin(10 * b2);
+        for (int i = 0; i < n; ++i) {
+            const int v = kp[i].value;
+            cs[(size_t)i] = (v >= 0 && v < 360 && v % 10 == 0) ? lut[v / 10] : cos_sin(v);
+        }
     }
     const size_t b[6] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, 512 * (size_t)n, (size_t)n, 4 * h_taps.size(), frame_of ? 4 * (size_t)n : 0};
     u8 *d[6];
@@ -1188,11 +1207,11 @@ static int run_sift(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, int oct
 static long long expand_orientations(const vslam_keypoint *kp, const unsigned long long *masks, long long n, vslam_keypoint *out, long long capacity) {
     long long m = 0;
     for (long long i = 0; i < n; ++i)
-        for (int bin = 0; bin < 36; ++bin)
-            if (masks[i] >> bin & 1) {
-                if (m < capacity) out[m] = vslam_keypoint{kp[i].row, kp[i].col, bin * 10, 0, kp[i].octave, kp[i].level};
-                ++m;
-            }
+        for (unsigned long long bits = masks[i] & ((1ull << 36) - 1); bits; bits &= bits - 1) {      // set bits in ascending order
+            const int bin = __builtin_ctzll(bits);
+            if (m < capacity) out[m] = vslam_keypoint{kp[i].row, kp[i].col, bin * 10, 0, kp[i].octave, kp[i].level};
+            ++m;
+        }
     return m;
 }
 

@@ -256,12 +256,16 @@ class Runner:
             co_host = torch.empty((cap * 4, 2), dtype=torch.int32, pin_memory=True).numpy()    # vslam_corner8 entries (VSLAM_COMPACT)
             eo = [False]
 
+            pend = [ctx.upload(hnp)]                                          # batch 0 on its way (outside the timed region, like the last
+                                                                              # step's look-ahead upload is inside it: K uploads per K steps)
             def step_e2e():
-                up = ctx.upload(hnp)                                          # one chunked H2D of the batch, overlapped with the kernels
-                a = ctx.dog_keypoints(up, out=kp_host)                        # keypoint list D2H inside
-                b = ctx.harris(up, want_maps=False, corners_out=co_host, compact=True)   # corner-only mode, 8-byte corner list D2H inside
-                eo[0] |= bool(a["overflow"] or b["overflow"])
-                return len(a["keypoints"]), len(b["corners"])
+                up = pend[0]
+                pend[0] = ctx.upload(hnp)                                     # the NEXT step's batch: chunked H2D under this step's kernels
+                # both detectors per chunk of frames (corner-only Harris in front of the chunk's DoG launches): the keypoint list and
+                # the 8-byte corner list leave chunk by chunk under the kernels of later chunks
+                r = ctx.dog_harris(up, kp_out=kp_host, co_out=co_host, compact=True)
+                eo[0] |= bool(r["overflow"])
+                return len(r["keypoints"]), len(r["corners"])
 
             step_e2e()
             ems, (ek, ec) = self.timed(step_e2e, steps)
@@ -270,8 +274,9 @@ class Runner:
             ems /= steps
             res["e2e"] = {"value": self.world * px_step / 1e6 / (ems * 1e-3), "unit": "Mpix/s", "ms_per_step": ems, "steps": steps,
                           "h2d_bytes_per_step": px_step, "d2h_bytes_per_step": int(ek * 24 + ec * 8 + 8 * nf),
-                          "api": "vslam_upload_frames (chunked, overlapped) + vslam_dog_keypoints + vslam_harris(corner-only, VSLAM_COMPACT: "
-                                 "8-byte vslam_corner8 list, lossless): host (pinned) frames in, host (pinned) result lists out; value's steps run Harris in pipeline mode (response + mask stay in HBM)"}
+                          "api": "vslam_upload_frames (chunked; the next step's batch is uploaded under this step's kernels: two ingest buffers) + vslam_dog_harris (= vslam_dog_keypoints + corner-only vslam_harris "
+                                 "interleaved per chunk of frames; VSLAM_COMPACT: 8-byte vslam_corner8 list, lossless): host (pinned) frames in, "
+                                 "host (pinned) result lists out; value's steps run Harris in pipeline mode (response + mask stay in HBM)"}
         del kp_dev, co_dev, resp_dev, mask_dev, dev
         torch.cuda.empty_cache()
         return res

@@ -186,7 +186,11 @@ VSLAM_API int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_f
 /* Starts the asynchronous, chunked upload of a batch of HOST frames (pinned memory for full PCIe speed) into the
  * context's ingest buffer and returns its device address, pitch and frame stride.  Pass those with VSLAM_DEVICE to
  * vslam_dog_keypoints / vslam_harris / vslam_pyramid_build: each call waits per chunk, so kernels on the first frames
- * overlap the upload of the rest, and one upload serves every call.  Valid until the next call that uploads. */
+ * overlap the upload of the rest, and one upload serves every call.  The context holds TWO ingest buffers and alternates between
+ * them: the returned frames stay valid until the SECOND next call that uploads (vslam_upload_frames, or any call given HOST
+ * frames), so a caller can start the upload of batch i+1 before it calls the detectors on batch i -- the copy then runs under
+ * batch i's kernels, and a batch that has already landed runs in full-size launches.  An upload into a buffer first waits for
+ * the compute-stream work enqueued so far (the consumers of the batch the buffer held). */
 VSLAM_API int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
                                   size_t frame_stride, const uint8_t **d_frames, size_t *d_pitch,
                                   size_t *d_frame_stride);
@@ -201,6 +205,17 @@ VSLAM_API int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, 
                            size_t frame_stride, int space, const vslam_harris_params *params, float *response,
                            uint8_t *r8, uint8_t *mask3, vslam_corner *corners, int capacity, int out_space,
                            int *counts);
+
+/* Both detectors over the same batch in one call: what a caller who wants ./DoG's keypoints and ./Harris's corners of every frame
+ * does (vslam_dog_keypoints + vslam_harris with response / r8 / mask3 = NULL), with the Harris launch of every chunk of frames
+ * issued in front of the chunk's DoG launches, so that the (much larger) corner list leaves the GPU chunk by chunk under the DoG
+ * kernels instead of after them.  Lists, order and counts are exactly those of the two separate calls.  out_space: VSLAM_HOST or
+ * VSLAM_DEVICE for both lists, | VSLAM_COMPACT for the corner list.  Returns VSLAM_E_CAPACITY if either list overflowed. */
+VSLAM_API int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
+                               size_t frame_stride, int space, const vslam_pyramid_params *pparams,
+                               const vslam_dog_params *dparams, const vslam_harris_params *hparams,
+                               vslam_keypoint *keypoints, int kp_capacity, int *kp_counts, vslam_corner *corners,
+                               int co_capacity, int *co_counts, int out_space);
 
 /* ---- per-function entry points: the reference's own function granularity, for the C++17 mirror in
  *      visualslam_b200/host/ (HOST buffers, dense unless a pitch is given; each call synchronises).  The throughput

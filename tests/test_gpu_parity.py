@@ -607,3 +607,53 @@ def test_warp_affine_and_rotation_matrix_vs_cv2_and_oracle(ctx):
         m = O.get_rotation_matrix_2d((w / 2.0, h / 2.0), float(rng.uniform(-180, 180)), float(rng.uniform(0.3, 3.0)))
         m[:, 2] += rng.uniform(-40, 40, 2)
         assert np.array_equal(ctx.warp_affine(img, m, (dw, dh)), O.warp_affine(img, m, (dw, dh))), (h, w, dh, dw)
+
+
+def test_dog_harris_combined_call_matches_the_two_calls(ctx):
+    """vslam_dog_harris (Harris launch in front of every chunk's DoG launches, both lists draining chunk by chunk) returns exactly
+    the lists, order and counts of vslam_dog_keypoints + vslam_harris: host lists from an uploaded batch (several chunks), device
+    lists, the compact corner list, a capacity overflow on either list."""
+    import torch
+    frames = np.stack([synth.frame(i % 8, 540, 960) for i in range(40)], 0)
+    kp = ctx.dog_keypoints(frames, capacity=1 << 20)
+    co = ctx.harris(frames, want_maps=False, capacity=1 << 22)
+    pinned = torch.from_numpy(frames).pin_memory().numpy()
+    both = ctx.dog_harris(ctx.upload(pinned), kp_capacity=1 << 20, co_capacity=1 << 22)
+    assert both["kp_counts"] == kp["counts"] and both["co_counts"] == co["counts"] and not both["overflow"]
+    assert np.array_equal(both["keypoints"], kp["keypoints"]) and np.array_equal(both["corners"], co["corners"])
+    c8 = ctx.dog_harris(frames, kp_capacity=1 << 20, co_capacity=1 << 22, compact=True)
+    assert np.array_equal(c8["keypoints"], kp["keypoints"]) and np.array_equal(vs.expand_corners(c8["corners"]), co["corners"])
+    kd = torch.zeros((len(kp["keypoints"]) + 3, 6), dtype=torch.int32, device="cuda")
+    cd = torch.zeros((len(co["corners"]) + 3, 3), dtype=torch.int32, device="cuda")
+    r = ctx.dog_harris(torch.from_numpy(frames).cuda(), kp_out=kd, co_out=cd)
+    assert r["kp_counts"] == kp["counts"] and r["co_counts"] == co["counts"]
+    assert np.array_equal(kd.cpu().numpy()[:len(kp["keypoints"])].view(vs.KEYPOINT_DTYPE).reshape(-1), kp["keypoints"])
+    assert np.array_equal(cd.cpu().numpy()[:len(co["corners"])].view(vs.CORNER_DTYPE).reshape(-1), co["corners"])
+    small = ctx.dog_harris(frames, kp_capacity=100, co_capacity=1 << 22)
+    assert small["overflow"] and small["kp_counts"] == kp["counts"] and np.array_equal(small["keypoints"], kp["keypoints"][:100])
+    assert np.array_equal(small["corners"], co["corners"])
+    small = ctx.dog_harris(frames, kp_capacity=1 << 20, co_capacity=1000)
+    assert small["overflow"] and small["co_counts"] == co["counts"] and np.array_equal(small["keypoints"], kp["keypoints"])
+    # and the separate calls still work after the combined one (the two list workspaces are back in place)
+    assert np.array_equal(ctx.harris(frames[:3], want_maps=False)["corners"], co["corners"][:sum(co["counts"][:3])])
+
+
+def test_pipelined_uploads_two_ingest_buffers(ctx):
+    """vslam_upload_frames alternates between two ingest buffers: batch i+1 may be uploaded before the detectors run on batch i
+    (include/vslam.h); lists equal those of the direct calls, in either order of use, several rounds."""
+    import torch
+    A = np.stack([synth.frame(i % 8, 270, 480) for i in range(24)], 0)
+    B = np.stack([synth.frame((i + 3) % 8, 270, 480)[::-1].copy() for i in range(24)], 0)
+    want = {}
+    for name, f in (("A", A), ("B", B)):
+        want[name] = (ctx.dog_keypoints(f)["keypoints"].copy(), ctx.harris(f, want_maps=False)["corners"].copy())
+    pa, pb = torch.from_numpy(A).pin_memory().numpy(), torch.from_numpy(B).pin_memory().numpy()
+    up = ctx.upload(pa)
+    for rnd in range(4):
+        name, nxt = ("A", pb) if rnd % 2 == 0 else ("B", pa)
+        up_next = ctx.upload(nxt)                      # next batch on its way before this one is processed
+        r = ctx.dog_harris(up)
+        assert np.array_equal(r["keypoints"], want[name][0]) and np.array_equal(r["corners"], want[name][1]), rnd
+        if rnd == 1:                                   # separate calls on an uploaded batch too
+            assert np.array_equal(ctx.harris(up, want_maps=False)["corners"], want[name][1])
+        up = up_next

@@ -55,7 +55,7 @@ EXPORTS = [
     "vslam_version", "vslam_launch_count", "vslam_calculate_sigma", "vslam_calculate_num_octaves",
     "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_destroy",
     "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
-    "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris",
+    "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris", "vslam_dog_harris",
     "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
     "vslam_bgr_to_gray", "vslam_rotate_mat_ccw", "vslam_rotated_window", "vslam_get_rotation_matrix_2d", "vslam_warp_affine", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
@@ -109,6 +109,8 @@ def load():
     L.vslam_dog_keypoints.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(DogParams),
                                       vp, i, i, C.POINTER(i)]
     L.vslam_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(HarrisParams), vp, vp, vp, vp, i, i, C.POINTER(i)]
+    L.vslam_dog_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(DogParams), C.POINTER(HarrisParams),
+                                   vp, i, C.POINTER(i), vp, i, C.POINTER(i), i]
     L.vslam_upload_frames.argtypes = [vp, vp, i, i, i, sz, sz, C.POINTER(vp), C.POINTER(sz), C.POINTER(sz)]
     L.vslam_gauss_ksize_f32.argtypes = [C.c_double]
     L.vslam_gauss_taps_f32.argtypes = [C.c_double, i, C.POINTER(C.c_float)]
@@ -367,6 +369,34 @@ class Context:
         cl = list(counts)
         return {"keypoints": host[:min(sum(cl), capacity)] if host is not None else out, "counts": cl,
                 "overflow": rc == E_CAPACITY}
+
+    def dog_harris(self, frames, num_octaves=4, sigma0=1.6, contrast_thr=0.03, edge_r=10.0, k=0.04, nms2_window=5, kp_capacity=1 << 20,
+                   co_capacity=1 << 22, kp_out=None, co_out=None, compact=False):
+        """Both detectors over one batch (vslam_dog_harris): the lists of dog_keypoints and harris(want_maps=False), with the corner
+        list draining under the DoG kernels.  kp_out / co_out: caller-owned host buffers (numpy, e.g. pinned) or torch cuda tensors
+        (both on the device then); compact: the corner list as vslam_corner8."""
+        dev = self._torch_in(frames, kp_out, co_out)
+        ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
+        pp = PyramidParams(num_octaves, 3, sigma0, 0); dp = DogParams(3, contrast_thr, edge_r); hp = HarrisParams(k, nms2_window)
+        kc, cc = (C.c_int * n)(), (C.c_int * n)()
+        cdt = CORNER8_DTYPE if compact else CORNER_DTYPE
+        on_dev = kp_out is not None and not isinstance(kp_out, np.ndarray)
+        if on_dev:
+            assert co_out is not None and not isinstance(co_out, np.ndarray)
+            kptr, cptr, kcap, ccap, ospace = kp_out.data_ptr(), co_out.data_ptr(), kp_out.shape[0], co_out.shape[0], DEVICE
+            kh = ch = None
+        else:
+            kh = np.zeros(kp_capacity, KEYPOINT_DTYPE) if kp_out is None else kp_out.view(KEYPOINT_DTYPE).reshape(-1)
+            ch = np.zeros(co_capacity, cdt) if co_out is None else co_out.view(cdt).reshape(-1)
+            kptr, cptr, kcap, ccap, ospace = kh.ctypes.data, ch.ctypes.data, kh.shape[0], ch.shape[0], HOST
+        rc = load().vslam_dog_harris(self.h, ptr, n, h, w, pitch, stride, space, C.byref(pp), C.byref(dp), C.byref(hp), kptr, kcap, kc, cptr, ccap,
+                                     cc, ospace | (COMPACT if compact else 0))
+        if rc and rc != E_CAPACITY:
+            self._chk(rc)
+        self._torch_out(dev)
+        kl, cl = list(kc), list(cc)
+        return {"keypoints": kh[:min(sum(kl), kcap)] if kh is not None else kp_out, "corners": ch[:min(sum(cl), ccap)] if ch is not None else co_out,
+                "kp_counts": kl, "co_counts": cl, "overflow": rc == E_CAPACITY}
 
     def assign_orientations(self, pyr, octave, keypoints, frame=0, histograms=False):
         """filterKeypoints' orientation stage (Diff_of_Gauss.cpp:340-369) for one octave's keypoints."""

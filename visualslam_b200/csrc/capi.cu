@@ -5,6 +5,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <mutex>
 
 #include "descriptor.cuh"
@@ -105,11 +106,13 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf *bufs[] = {&ctx->seg_off, &ctx->seg_cnt, &ctx->seg_dst, &ctx->seg_partial, &ctx->staging, &ctx->counters, &ctx->stage_counts,
-                      &ctx->ingest, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev};
+                      &ctx->ingest, &ctx->ingest2, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev, &ctx->alt_seg_off, &ctx->alt_seg_cnt, &ctx->alt_seg_dst,
+                      &ctx->alt_seg_partial, &ctx->alt_staging, &ctx->alt_counters, &ctx->alt_out_dev};
     for (DevBuf *b : bufs) b->release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->up_ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->up_ev2) cudaEventDestroy(e);
     if (ctx->up_start) cudaEventDestroy(ctx->up_start);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (cudaEvent_t e : ctx->down_ev) cudaEventDestroy(e);
@@ -251,15 +254,25 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
     if (space == VSLAM_DEVICE) {
         *d_frames = frames; *d_pitch = pitch; *d_stride = frame_stride;
         // frames handed out by vslam_upload_frames: their chunks may still be in flight on the copy stream
-        const u8 *b = ctx->ingest.as<u8>();
-        if (ctx->up_total && b && frames >= b && frames < b + ctx->ingest.cap && frame_stride == ctx->up_ds) {
-            ctx->up_chunks = ctx->up_total;
+        for (int sl = 0; sl < 2; ++sl) {
+            const DevBuf &buf = sl ? ctx->ingest2 : ctx->ingest;
+            const std::vector<cudaEvent_t> &ev = sl ? ctx->up_ev2 : ctx->up_ev;
+            const u8 *b = buf.as<u8>();
+            if (!ctx->slot_total[sl] || !b || frames < b || frames >= b + buf.cap || frame_stride != ctx->slot_ds[sl]) continue;
+            ctx->up_slot = sl; ctx->up_chunk = ctx->slot_chunk[sl]; ctx->up_total = ctx->slot_total[sl]; ctx->up_ds = ctx->slot_ds[sl];
             ctx->up_foff = (int)((size_t)(frames - b) / ctx->up_ds);
+            // an upload that has already landed (started under the previous batch's kernels) needs no waits and no short first launches
+            if (cudaEventQuery(ev[(size_t)ctx->up_total - 1]) != cudaSuccess) { cudaGetLastError(); ctx->up_chunks = ctx->up_total; }
+            break;
         }
         return VSLAM_OK;
     }
     const size_t dp = round_up((size_t)cols, 256), ds = dp * (size_t)rows;
-    if (ctx->ingest.reserve(ds * (size_t)n)) VS_FAIL(ctx, VSLAM_E_NOMEM, "ingest buffer (%zu bytes)", ds * (size_t)n);
+    const int sl = ctx->ingest_next;
+    ctx->ingest_next ^= 1;
+    DevBuf &ibuf = sl ? ctx->ingest2 : ctx->ingest;
+    std::vector<cudaEvent_t> &iev = sl ? ctx->up_ev2 : ctx->up_ev;
+    if (ibuf.reserve(ds * (size_t)n)) VS_FAIL(ctx, VSLAM_E_NOMEM, "ingest buffer (%zu bytes)", ds * (size_t)n);
     if (!ctx->copy_stream) {
         VS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
         VS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->up_start, cudaEventDisableTiming));
@@ -268,10 +281,10 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
     if (chunk < 1) chunk = 1;
     if (chunk > n) chunk = n;
     const int chunks = (n + chunk - 1) / chunk;
-    while ((int)ctx->up_ev.size() < chunks) {
+    while ((int)iev.size() < chunks) {
         cudaEvent_t e;
         VS_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        ctx->up_ev.push_back(e);
+        iev.push_back(e);
     }
     // earlier work on the compute stream may still read the ingest buffer
     VS_CUDA(ctx, cudaEventRecord(ctx->up_start, ctx->stream));
@@ -279,16 +292,17 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
     for (int c = 0; c < chunks; ++c) {
         const int f0 = c * chunk, nf = n - f0 < chunk ? n - f0 : chunk;
         if (pitch == (size_t)cols && dp == pitch && frame_stride == ds) {
-            VS_CUDA(ctx, cudaMemcpyAsync(ctx->ingest.as<u8>() + ds * f0, frames + frame_stride * f0, ds * (size_t)nf, cudaMemcpyHostToDevice, ctx->copy_stream));
+            VS_CUDA(ctx, cudaMemcpyAsync(ibuf.as<u8>() + ds * f0, frames + frame_stride * f0, ds * (size_t)nf, cudaMemcpyHostToDevice, ctx->copy_stream));
         } else {
             for (int f = f0; f < f0 + nf; ++f)
-                VS_CUDA(ctx, cudaMemcpy2DAsync(ctx->ingest.as<u8>() + ds * f, dp, frames + frame_stride * f, pitch, (size_t)cols,
+                VS_CUDA(ctx, cudaMemcpy2DAsync(ibuf.as<u8>() + ds * f, dp, frames + frame_stride * f, pitch, (size_t)cols,
                                                (size_t)rows, cudaMemcpyHostToDevice, ctx->copy_stream));
         }
-        VS_CUDA(ctx, cudaEventRecord(ctx->up_ev[c], ctx->copy_stream));
+        VS_CUDA(ctx, cudaEventRecord(iev[c], ctx->copy_stream));
     }
-    ctx->up_chunk = chunk; ctx->up_chunks = chunks; ctx->up_total = chunks; ctx->up_ds = ds;
-    *d_frames = ctx->ingest.as<u8>(); *d_pitch = dp; *d_stride = ds;
+    ctx->slot_chunk[sl] = chunk; ctx->slot_total[sl] = chunks; ctx->slot_ds[sl] = ds;
+    ctx->up_slot = sl; ctx->up_chunk = chunk; ctx->up_chunks = chunks; ctx->up_total = chunks; ctx->up_ds = ds;
+    *d_frames = ibuf.as<u8>(); *d_pitch = dp; *d_stride = ds;
     return VSLAM_OK;
 }
 
@@ -297,7 +311,8 @@ static int wait_ingest(vslam_ctx *ctx, int f0, int nf) {
     if (!ctx->up_chunks) return VSLAM_OK;
     f0 += ctx->up_foff;
     const int c0 = f0 / ctx->up_chunk, c1 = (f0 + nf - 1) / ctx->up_chunk;
-    for (int c = c0; c <= c1 && c < ctx->up_chunks; ++c) VS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->up_ev[c], 0));
+    const std::vector<cudaEvent_t> &ev = ctx->up_slot ? ctx->up_ev2 : ctx->up_ev;
+    for (int c = c0; c <= c1 && c < ctx->up_chunks; ++c) VS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ev[c], 0));
     return VSLAM_OK;
 }
 // frames per compute launch when the input is being uploaded: ~128 MB of frames, and a short first launch so that the
@@ -550,16 +565,18 @@ struct ListDrain {
     const u8 *dev = nullptr;
     size_t entry = 0;
     long long cap = 0, copied = 0;
-    int n = 0;
+    int n = 0, slot0 = 0;          // chunks so far; first pinned slot / event of this drain (two drains may be open at once)
     bool on = false;
 };
 static const int kDrainMax = 1024;
 
-static int drain_begin(vslam_ctx *ctx, ListDrain &d, void *out, int out_space, const void *d_list, size_t entry, int capacity, long long chunks) {
+static int drain_begin(vslam_ctx *ctx, ListDrain &d, void *out, int out_space, const void *d_list, size_t entry, int capacity, long long chunks,
+                       int slot0 = 0) {
     d = ListDrain();
-    if (out_space == VSLAM_DEVICE || !out || chunks < 2 || chunks > kDrainMax || !ctx->pinned || ctx->pinned_cap < kDrainMax * sizeof(int)) return VSLAM_OK;
+    if (out_space == VSLAM_DEVICE || !out || chunks < 2 || chunks > kDrainMax || !ctx->pinned || ctx->pinned_cap < 2 * kDrainMax * sizeof(int)) return VSLAM_OK;
     if (!ctx->down_stream) VS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking));
-    while ((long long)ctx->down_ev.size() < chunks) {
+    d.slot0 = slot0;
+    while ((long long)ctx->down_ev.size() < slot0 + chunks) {
         cudaEvent_t e;
         VS_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         ctx->down_ev.push_back(e);
@@ -568,8 +585,8 @@ static int drain_begin(vslam_ctx *ctx, ListDrain &d, void *out, int out_space, c
     return VSLAM_OK;
 }
 static int drain_settle(vslam_ctx *ctx, ListDrain &d, int j) {
-    VS_CUDA(ctx, cudaEventSynchronize(ctx->down_ev[j]));
-    long long t = ((const int *)ctx->pinned)[j];
+    VS_CUDA(ctx, cudaEventSynchronize(ctx->down_ev[d.slot0 + j]));
+    long long t = ((const int *)ctx->pinned)[d.slot0 + j];
     if (t > d.cap) t = d.cap;
     if (t > d.copied) {
         VS_CUDA(ctx, cudaMemcpyAsync(d.host + d.copied * d.entry, d.dev + d.copied * d.entry, (size_t)(t - d.copied) * d.entry,
@@ -581,8 +598,8 @@ static int drain_settle(vslam_ctx *ctx, ListDrain &d, int j) {
 // after a chunk's seg_finalise
 static int drain_chunk(vslam_ctx *ctx, ListDrain &d, const int *d_total) {
     if (!d.on) return VSLAM_OK;
-    VS_CUDA(ctx, cudaMemcpyAsync((int *)ctx->pinned + d.n, d_total, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    VS_CUDA(ctx, cudaEventRecord(ctx->down_ev[d.n], ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync((int *)ctx->pinned + d.slot0 + d.n, d_total, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaEventRecord(ctx->down_ev[d.slot0 + d.n], ctx->stream));
     if (d.n > 0) VS_TRY(drain_settle(ctx, d, d.n - 1));
     ++d.n;
     return VSLAM_OK;
@@ -645,7 +662,7 @@ int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_p
 // (blur + DoG + detector; only the octave bases live in HBM), then the segment scan / ordered gather.
 static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_frames, int n_frames, int rows, int cols,
                                size_t d_pitch, size_t d_stride, const vslam_dog_params &dp, vslam_keypoint *d_out, int capacity,
-                               ListDrain *drain, void *out, int out_space) {
+                               ListDrain *drain, void *out, int out_space, const std::function<int(int, int)> *per_chunk = nullptr) {
     const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
     // bases-only workspace layout of one frame; every row carries the reflect-101 margins its octave's kernel stages from
     size_t boff[16], bpitch[16], bbytes = 0;
@@ -676,6 +693,13 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
     // start after two upload chunks, and most frames run in large launches.  The lists are small: no need for many chunks.
     const bool doubling = ctx->up_chunks > 1;
     if (fb > n_frames) fb = n_frames;
+    // host lists and a batch that is already resident: four launches instead of one, so that three quarters of the lists leave under
+    // later launches (136 MB per 1080p x 256 step would otherwise follow the last kernel: 2.6 ms at PCIe speed alone, 3-4x that with 8
+    // GPUs on one host).  More launches cost kernel time (wave quantisation of long-running CTAs): measured 1 / 2 / 4 / 6 / 12 launches =
+    // 31.7 / 31.2 / 31.5 / 32.5 / 36.4 ms per step at one GPU (VSLAM_HOST_CHUNKS overrides)
+    static const int host_chunks = [] { const char *e = getenv("VSLAM_HOST_CHUNKS"); return e && atoi(e) > 0 ? atoi(e) : 4; }();
+    if (!doubling && out && out_space != VSLAM_DEVICE && n_frames >= 48 && fb > (n_frames + host_chunks - 1) / host_chunks)
+        fb = (n_frames + host_chunks - 1) / host_chunks;
     if (fb < 1) fb = 1;
     if (ctx->ws_maps.reserve(bbytes * (size_t)fb)) VS_FAIL(ctx, VSLAM_E_NOMEM, "octave-base workspace (%zu bytes)", bbytes * (size_t)fb);
     const size_t bound = (size_t)spf * (FWO_SAMPLES) * (size_t)fb;
@@ -695,12 +719,15 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
     VS_TRY(drain_begin(ctx, *drain, out, out_space, d_out, sizeof(vslam_keypoint), capacity, (n_frames + fb - 1) / fb + 32));
     const int first = doubling ? ingest_first(ctx, fb) : (int)fb;
     for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)(doubling && 2LL * step < fb ? 2LL * step : fb)) {
+        // host lists leave chunk by chunk: a short LAST chunk keeps the part of the lists that can only leave after the last kernel small
+        if (drain->on && doubling && step >= n_frames - f0 && n_frames - f0 > 2 * first) step = n_frames - f0 - first;
         const int nf = n_frames - f0 < step ? n_frames - f0 : step;
         const size_t n_seg = (size_t)spf * nf;
         if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, n_seg * 4, ctx->stream));
         VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
         u8 *ws = ctx->ws_maps.as<u8>();
         VS_TRY(wait_ingest(ctx, f0, nf));
+        if (per_chunk) VS_TRY((*per_chunk)(f0, nf));             // vslam_dog_harris: the Harris launch of the same frames goes first
         VS_TRY(launch_upsample2x(ctx, d_frames + d_stride * f0, rows, cols, d_pitch, d_stride, ws + boff[0], bpitch[0], bbytes, nf));
         for (int o = 0; o < g.num_octaves; ++o) {
             FusedArgs a;
@@ -769,75 +796,185 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
     return emit_list(ctx, out, out_space, d_out, sizeof(vslam_keypoint), total, capacity, drain.on);
 }
 
+// vslam_harris in three pieces, so that vslam_dog_harris can run one Harris launch per chunk of the DoG loop
+struct HarrisJob {
+    const u8 *d_frames; size_t d_pitch, d_stride;
+    int n_frames, rows, cols, capacity, out_space, compact, w2;
+    float k;
+    size_t centry, spf, fb, px;
+    void *corners, *d_out;
+    float *response, *d_resp; u8 *r8, *mask3, *d_r8, *d_m3;
+    ListDrain drain;
+};
+
+// arguments, workspaces of the CURRENT list set (ctx->seg_*, staging, counters, out_dev) and the list drain.  max_chunk: the
+// largest number of frames one harris_chunk call will be given (0: this function picks the launch size, job.fb)
+static int harris_begin(vslam_ctx *ctx, HarrisJob &j, const u8 *d_frames, size_t d_pitch, size_t d_stride, int n_frames, int rows, int cols,
+                        const vslam_harris_params *params, float *response, uint8_t *r8, uint8_t *mask3, void *corners, int capacity,
+                        int out_space, int max_chunk, int drain_slot0) {
+    if (rows <= 0 || cols <= 0 || rows > (1 << 15) || cols > (1 << 15)) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
+    j = HarrisJob();
+    j.compact = (out_space & VSLAM_COMPACT) ? 1 : 0;             // `corners` is a vslam_corner8 buffer
+    out_space &= ~VSLAM_COMPACT;
+    if (out_space != VSLAM_HOST && out_space != VSLAM_DEVICE) VS_FAIL(ctx, VSLAM_E_INVALID, "out_space %d", out_space);
+    j.out_space = out_space;
+    j.centry = j.compact ? sizeof(vslam_corner8) : sizeof(vslam_corner);
+    j.k = params ? params->k : 0.04f;
+    j.w2 = params ? params->nms2_window : 5;
+    if (j.w2 != 3 && j.w2 != 5) VS_FAIL(ctx, VSLAM_E_INVALID, "nms2_window must be 3 or 5 (got %d)", j.w2);
+    j.d_frames = d_frames; j.d_pitch = d_pitch; j.d_stride = d_stride; j.n_frames = n_frames; j.rows = rows; j.cols = cols;
+    j.capacity = capacity; j.corners = corners; j.response = response; j.r8 = r8; j.mask3 = mask3;
+    j.spf = (size_t)rows * harris_strips(cols);                  // segments per frame: (row, strip)
+    size_t fb = ((size_t)1 << 30) / j.spf;                       // frames per launch
+    if (fb > 32768) fb = 32768;
+    if (max_chunk > 0) {
+        if (fb < (size_t)max_chunk) VS_FAIL(ctx, VSLAM_E_INVALID, "image too large for %d frames per Harris launch", max_chunk);
+        fb = (size_t)max_chunk;
+    } else {
+        fb = (size_t)ingest_cap(ctx, (long long)fb);
+    }
+    if (fb > (size_t)n_frames) fb = (size_t)n_frames;
+    if (fb < 1) VS_FAIL(ctx, VSLAM_E_INVALID, "image too large for the segment table");
+    j.fb = fb;
+    VS_TRY(seg_prepare(ctx, j.spf * fb, sizeof(vslam_corner), staging_entries(capacity, (size_t)rows * cols * fb)));
+    VS_TRY(reserve_counters(ctx, n_frames));
+    j.d_out = corners;
+    if (out_space != VSLAM_DEVICE) {
+        if (ctx->out_dev.reserve(j.centry * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device corner list");
+        j.d_out = ctx->out_dev.p;
+    }
+    j.px = (size_t)rows * cols;
+    j.d_resp = response; j.d_r8 = r8; j.d_m3 = mask3;
+    if (out_space != VSLAM_DEVICE && (response || r8 || mask3)) {
+        if (ctx->maps_dev.reserve(j.px * 6 * (size_t)n_frames)) VS_FAIL(ctx, VSLAM_E_NOMEM, "device maps (%zu bytes)", j.px * 6 * (size_t)n_frames);
+        j.d_resp = response ? ctx->maps_dev.as<float>() : nullptr;
+        j.d_r8 = r8 ? ctx->maps_dev.as<u8>() + j.px * 4 * n_frames : nullptr;
+        j.d_m3 = mask3 ? ctx->maps_dev.as<u8>() + j.px * 5 * n_frames : nullptr;
+    }
+    const long long chunks = max_chunk > 0 ? kDrainMax / 2 : ((long long)n_frames + (long long)fb - 1) / (long long)fb + 1;
+    VS_TRY(drain_begin(ctx, j.drain, corners, out_space, j.d_out, j.centry, capacity, chunks, drain_slot0));
+    return VSLAM_OK;
+}
+
+// frames [f0, f0 + nf) (nf <= job.fb): one launch, the ordered gather behind it, the chunk's slice of the list on its way out
+static int harris_chunk(vslam_ctx *ctx, HarrisJob &j, int f0, int nf) {
+    int *cnt = ctx->counters.as<int>();
+    if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, j.spf * nf * 4, ctx->stream));
+    VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
+    HarrisArgs a;
+    memset(&a, 0, sizeof a);
+    a.frames = j.d_frames + j.d_stride * f0; a.pitch = j.d_pitch; a.frame_stride = j.d_stride;
+    a.rows = j.rows; a.cols = j.cols; a.k = j.k; a.nms2_pad = (j.w2 - 1) / 2;
+    a.response = j.d_resp ? j.d_resp + j.px * f0 : nullptr;
+    a.r8 = j.d_r8 ? j.d_r8 + j.px * f0 : nullptr;
+    a.mask3 = j.d_m3 ? j.d_m3 + j.px * f0 : nullptr;
+    a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
+    a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = ctx->staging_entries;
+    a.want_corners = 1;
+    VS_TRY(launch_harris(ctx, a, nf));
+    VS_TRY(seg_finalise(ctx, j.spf * nf, (int)sizeof(vslam_corner), j.d_out, j.capacity, cnt + 2, cnt + kCounterBase + f0, nf, j.compact));
+    VS_TRY(drain_chunk(ctx, j.drain, cnt + 2));
+    return VSLAM_OK;
+}
+
+static int harris_end(vslam_ctx *ctx, HarrisJob &j, int *counts) {
+    if (j.out_space != VSLAM_DEVICE) {
+        if (j.response) VS_CUDA(ctx, cudaMemcpyAsync(j.response, j.d_resp, j.px * 4 * j.n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+        if (j.r8) VS_CUDA(ctx, cudaMemcpyAsync(j.r8, j.d_r8, j.px * j.n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+        if (j.mask3) VS_CUDA(ctx, cudaMemcpyAsync(j.mask3, j.d_m3, j.px * j.n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    long long total = 0;
+    VS_TRY(finish_counts(ctx, j.n_frames, j.capacity, counts, &total));
+    VS_TRY(drain_end(ctx, j.drain));
+    return emit_list(ctx, j.corners, j.out_space, j.d_out, j.centry, total, j.capacity, j.drain.on);
+}
+
 int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
                  size_t frame_stride, int space, const vslam_harris_params *params, float *response, uint8_t *r8,
                  uint8_t *mask3, vslam_corner *corners, int capacity, int out_space, int *counts) {
     if (!ctx || capacity < 0 || (!corners && capacity > 0)) return VSLAM_E_INVALID;
     VS_CUDA(ctx, cudaSetDevice(ctx->device));
     if (rows <= 0 || cols <= 0 || rows > (1 << 15) || cols > (1 << 15)) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
-    const int compact = (out_space & VSLAM_COMPACT) ? 1 : 0;          // `corners` is a vslam_corner8 buffer
-    out_space &= ~VSLAM_COMPACT;
-    if (out_space != VSLAM_HOST && out_space != VSLAM_DEVICE) VS_FAIL(ctx, VSLAM_E_INVALID, "out_space %d", out_space);
-    const size_t centry = compact ? sizeof(vslam_corner8) : sizeof(vslam_corner);
-    const float k = params ? params->k : 0.04f;
-    const int w2 = params ? params->nms2_window : 5;
-    if (w2 != 3 && w2 != 5) VS_FAIL(ctx, VSLAM_E_INVALID, "nms2_window must be 3 or 5 (got %d)", w2);
     const u8 *d_frames; size_t d_pitch, d_stride;
     VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
-    const int n_strips = harris_strips(cols);
-    const size_t spf = (size_t)rows * n_strips;                  // segments per frame: (row, strip)
-    size_t fb = ((size_t)1 << 30) / spf;                         // frames per launch
-    if (fb > 32768) fb = 32768;
-    fb = (size_t)ingest_cap(ctx, (long long)fb);
-    if (fb > (size_t)n_frames) fb = (size_t)n_frames;
-    if (fb < 1) VS_FAIL(ctx, VSLAM_E_INVALID, "image too large for the segment table");
-    VS_TRY(seg_prepare(ctx, spf * fb, sizeof(vslam_corner), staging_entries(capacity, (size_t)rows * cols * fb)));
-    VS_TRY(reserve_counters(ctx, n_frames));
-    void *d_out = corners;
-    if (out_space != VSLAM_DEVICE) {
-        if (ctx->out_dev.reserve(centry * (size_t)(capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device corner list");
-        d_out = ctx->out_dev.p;
-    }
-    const size_t px = (size_t)rows * cols;
-    float *d_resp = response; u8 *d_r8 = r8, *d_m3 = mask3;
-    if (out_space != VSLAM_DEVICE && (response || r8 || mask3)) {
-        if (ctx->maps_dev.reserve(px * 6 * (size_t)n_frames)) VS_FAIL(ctx, VSLAM_E_NOMEM, "device maps (%zu bytes)", px * 6 * (size_t)n_frames);
-        d_resp = response ? ctx->maps_dev.as<float>() : nullptr;
-        d_r8 = r8 ? ctx->maps_dev.as<u8>() + px * 4 * n_frames : nullptr;
-        d_m3 = mask3 ? ctx->maps_dev.as<u8>() + px * 5 * n_frames : nullptr;
-    }
-    int *cnt = ctx->counters.as<int>();
-    ListDrain drain;
-    VS_TRY(drain_begin(ctx, drain, corners, out_space, d_out, centry, capacity, ((long long)n_frames + (long long)fb - 1) / (long long)fb + 1));
-    const int first = ingest_first(ctx, (long long)fb);
-    for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)fb) {
+    HarrisJob j;
+    VS_TRY(harris_begin(ctx, j, d_frames, d_pitch, d_stride, n_frames, rows, cols, params, response, r8, mask3, corners, capacity, out_space, 0, 0));
+    const int first = ingest_first(ctx, (long long)j.fb);
+    for (int f0 = 0, step = first; f0 < n_frames; f0 += step, step = (int)j.fb) {
         const int nf = n_frames - f0 < step ? n_frames - f0 : step;
-        if (f0) VS_CUDA(ctx, cudaMemsetAsync(ctx->seg_cnt.p, 0, spf * nf * 4, ctx->stream));
-        VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
         VS_TRY(wait_ingest(ctx, f0, nf));
-        HarrisArgs a;
-        memset(&a, 0, sizeof a);
-        a.frames = d_frames + d_stride * f0; a.pitch = d_pitch; a.frame_stride = d_stride;
-        a.rows = rows; a.cols = cols; a.k = k; a.nms2_pad = (w2 - 1) / 2;
-        a.response = d_resp ? d_resp + px * f0 : nullptr;
-        a.r8 = d_r8 ? d_r8 + px * f0 : nullptr;
-        a.mask3 = d_m3 ? d_m3 + px * f0 : nullptr;
-        a.seg_off = ctx->seg_off.as<int>(); a.seg_cnt = ctx->seg_cnt.as<int>();
-        a.cursor = cnt; a.staging = ctx->staging.as<vslam_corner>(); a.staging_cap = ctx->staging_entries;
-        a.want_corners = 1;
-        VS_TRY(launch_harris(ctx, a, nf));
-        VS_TRY(seg_finalise(ctx, spf * nf, (int)sizeof(vslam_corner), d_out, capacity, cnt + 2, cnt + kCounterBase + f0, nf, compact));
-        VS_TRY(drain_chunk(ctx, drain, cnt + 2));
+        VS_TRY(harris_chunk(ctx, j, f0, nf));
     }
-    if (out_space != VSLAM_DEVICE) {
-        if (response) VS_CUDA(ctx, cudaMemcpyAsync(response, d_resp, px * 4 * n_frames, cudaMemcpyDeviceToHost, ctx->stream));
-        if (r8) VS_CUDA(ctx, cudaMemcpyAsync(r8, d_r8, px * n_frames, cudaMemcpyDeviceToHost, ctx->stream));
-        if (mask3) VS_CUDA(ctx, cudaMemcpyAsync(mask3, d_m3, px * n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+    return harris_end(ctx, j, counts);
+}
+
+// the two list workspaces of a context trade places: code written against ctx->seg_* / staging / counters / out_dev then works on
+// the other list.  RAII: the sets are swapped back on every exit path.
+struct ListSetSwap {
+    vslam_ctx *c;
+    explicit ListSetSwap(vslam_ctx *ctx) : c(ctx) { flip(); }
+    ~ListSetSwap() { flip(); }
+    void flip() {
+        std::swap(c->seg_off, c->alt_seg_off); std::swap(c->seg_cnt, c->alt_seg_cnt); std::swap(c->seg_dst, c->alt_seg_dst);
+        std::swap(c->seg_partial, c->alt_seg_partial); std::swap(c->staging, c->alt_staging); std::swap(c->counters, c->alt_counters);
+        std::swap(c->out_dev, c->alt_out_dev); std::swap(c->staging_entries, c->alt_staging_entries);
     }
+};
+
+int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride, int space,
+                     const vslam_pyramid_params *pparams, const vslam_dog_params *dparams, const vslam_harris_params *hparams,
+                     vslam_keypoint *keypoints, int kp_capacity, int *kp_counts, vslam_corner *corners, int co_capacity, int *co_counts,
+                     int out_space) {
+    if (!ctx || kp_capacity < 0 || co_capacity < 0 || (!keypoints && kp_capacity > 0) || (!corners && co_capacity > 0)) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    vslam_dog_params dp;
+    VS_TRY(check_dog_params(ctx, dparams, &dp));
+    const int kp_space = out_space & ~VSLAM_COMPACT;
+    const size_t h_spf = (size_t)(rows > 0 ? rows : 1) * harris_strips(cols > 0 ? cols : 1);
+    if (dp.window != 3 || (size_t)n_frames > ((size_t)1 << 30) / h_spf || n_frames > 32768) {
+        // shapes the interleaved loop does not take: the two calls one after the other (same results)
+        const int rk = vslam_dog_keypoints(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, pparams, dparams, keypoints, kp_capacity,
+                                           kp_space, kp_counts);
+        if (rk != VSLAM_OK && rk != VSLAM_E_CAPACITY) return rk;
+        const int rc = vslam_harris(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, hparams, nullptr, nullptr, nullptr, corners,
+                                    co_capacity, out_space, co_counts);
+        return rk != VSLAM_OK ? rk : rc;
+    }
+    Geometry g;
+    int no; double s0;
+    VS_TRY(make_geometry(ctx, rows, cols, pparams, &g, &no, &s0));
+    VS_TRY(ensure_taps(ctx, no, s0, 3));
+    const u8 *d_frames; size_t d_pitch, d_stride;
+    VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
+    VS_TRY(reserve_counters(ctx, n_frames));
+    vslam_keypoint *d_kp = keypoints;
+    if (kp_space != VSLAM_DEVICE) {
+        if (ctx->out_dev.reserve(sizeof(vslam_keypoint) * (size_t)(kp_capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device keypoint list");
+        d_kp = ctx->out_dev.as<vslam_keypoint>();
+    }
+    HarrisJob hj;
+    {
+        ListSetSwap sw(ctx);
+        VS_TRY(harris_begin(ctx, hj, d_frames, d_pitch, d_stride, n_frames, rows, cols, hparams, nullptr, nullptr, nullptr, corners, co_capacity,
+                            out_space, n_frames, kDrainMax));
+    }
+    const std::function<int(int, int)> hook = [&](int f0, int nf) -> int {
+        ListSetSwap sw(ctx);
+        return harris_chunk(ctx, hj, f0, nf);
+    };
+    ListDrain kdrain;
+    VS_TRY(dog_keypoints_fused(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, dp, d_kp, kp_capacity, &kdrain, keypoints, kp_space, &hook));
     long long total = 0;
-    VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
-    VS_TRY(drain_end(ctx, drain));
-    return emit_list(ctx, corners, out_space, d_out, centry, total, capacity, drain.on);
+    VS_TRY(finish_counts(ctx, n_frames, kp_capacity, kp_counts, &total));
+    VS_TRY(drain_end(ctx, kdrain));
+    const int rk = emit_list(ctx, keypoints, kp_space, d_kp, sizeof(vslam_keypoint), total, kp_capacity, kdrain.on);
+    if (rk != VSLAM_OK && rk != VSLAM_E_CAPACITY) return rk;
+    int rc;
+    {
+        ListSetSwap sw(ctx);
+        rc = harris_end(ctx, hj, co_counts);
+    }
+    return rk != VSLAM_OK ? rk : rc;
 }
 
 int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride,

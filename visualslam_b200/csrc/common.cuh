@@ -47,6 +47,9 @@ struct vslam_ctx {
     // segment-ordered compaction workspace (detect + harris corners)
     vslam::DevBuf seg_off, seg_cnt, seg_dst, seg_partial, staging, counters, stage_counts;
     int staging_entries = 0;       // capacity of `staging` in entries (per frame)
+    // second set of the list workspace: vslam_dog_harris keeps two ordered lists growing at once (swap_list_sets, capi.cu)
+    vslam::DevBuf alt_seg_off, alt_seg_cnt, alt_seg_dst, alt_seg_partial, alt_staging, alt_counters, alt_out_dev;
+    int alt_staging_entries = 0;
     // throughput-path workspace: one frame's pyramid, reused
     vslam::DevBuf ingest;          // aligned copy of the input frame(s)
     vslam::DevBuf ws_maps;         // octave bases of a chunk of frames (or all planes of one frame)
@@ -56,10 +59,19 @@ struct vslam_ctx {
     // of later chunks overlaps the kernels of earlier ones
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t up_start = nullptr;
-    std::vector<cudaEvent_t> up_ev;
-    int up_chunk = 0, up_chunks = 0;   // frames per upload chunk, chunks in flight (0: frames were already on the device)
-    int up_total = 0, up_foff = 0;     // chunks of the last upload; first uploaded frame the current call looks at
-    size_t up_ds = 0;                  // bytes between uploaded frames
+    std::vector<cudaEvent_t> up_ev;    // chunk events of ingest buffer 0 (`ingest`)
+    int up_chunk = 0, up_chunks = 0;   // the batch the CURRENT call consumes: frames per upload chunk, chunks that may still be in flight
+    int up_total = 0, up_foff = 0;     //   (0: frames were already on the device); chunks of that upload; first frame the call looks at
+    size_t up_ds = 0;                  //   bytes between uploaded frames
+    int up_slot = 0;                   //   ingest buffer of that batch
+    // Two ingest buffers, used alternately: a caller may start the upload of batch i+1 (vslam_upload_frames) before it calls the
+    // detectors on batch i, so the copy runs under batch i's kernels.  An upload into a buffer waits for the compute-stream work
+    // enqueued so far (the consumers of the batch that buffer held).
+    vslam::DevBuf ingest2;
+    std::vector<cudaEvent_t> up_ev2;
+    int slot_chunk[2] = {0, 0}, slot_total[2] = {0, 0};
+    size_t slot_ds[2] = {0, 0};
+    int ingest_next = 0;
     // host result lists leave chunk by chunk on a third stream while later chunks compute (capi.cu: ListDrain)
     cudaStream_t down_stream = nullptr;
     std::vector<cudaEvent_t> down_ev;

@@ -177,6 +177,8 @@ class Runner:
         self.device = torch.device("cuda", local)
         self.stream = torch.cuda.Stream()
         self.ctx = vs.Context(local, stream=self.stream.cuda_stream)
+        m = getattr(args, "e2e_mode", "auto")
+        self.e2e_mode = m if m != "auto" else ("stream" if world <= 4 else "sync")
 
     def barrier(self):
         self.torch.cuda.synchronize()
@@ -215,7 +217,7 @@ class Runner:
             hnp[i] = uniq[i % len(uniq)]
         return uniq, hnp, host.to(self.device)
 
-    def workload(self, h, w, nf, steps, warmup, e2e=True, kernel_timing=True, clocks=False):
+    def workload(self, h, w, nf, steps, warmup, e2e=True, kernel_timing=True, clocks=False, e2e_sync=False):
         """Device-resident value + (optionally) the end-to-end figure of one (h, w, frames-per-GPU) workload."""
         torch, ctx = self.torch, self.ctx
         px_step = nf * h * w
@@ -251,32 +253,62 @@ class Runner:
         if overflow[0]:
             raise SystemExit(f"output list overflow in the device-resident steps of {w}x{h} x {nf}")
         if e2e:
-            # e2e result lists: pinned host buffers owned by the caller (a pageable list would be staged by the driver)
-            kp_host = torch.empty((cap, 6), dtype=torch.int32, pin_memory=True).numpy()
-            co_host = torch.empty((cap * 4, 2), dtype=torch.int32, pin_memory=True).numpy()    # vslam_corner8 entries (VSLAM_COMPACT)
+            # e2e result lists: pinned host buffers owned by the caller (a pageable list would be staged by the driver); two sets, because
+            # a step's lists are completed (vslam_finish) after the next step has been enqueued
+            kp_host = [torch.empty((cap, 6), dtype=torch.int32, pin_memory=True).numpy() for _ in range(2)]
+            co_host = [torch.empty((cap * 4, 2), dtype=torch.int32, pin_memory=True).numpy() for _ in range(2)]   # vslam_corner8 entries (VSLAM_COMPACT)
             eo = [False]
+            it = [0]
+            pend = [ctx.upload(hnp)]                                          # batch 0 on its way; every step uploads the NEXT step's batch
+            last = [(0, 0)]
 
-            pend = [ctx.upload(hnp)]                                          # batch 0 on its way (outside the timed region, like the last
-                                                                              # step's look-ahead upload is inside it: K uploads per K steps)
             def step_e2e():
-                up = pend[0]
-                pend[0] = ctx.upload(hnp)                                     # the NEXT step's batch: chunked H2D under this step's kernels
-                # both detectors per chunk of frames (corner-only Harris in front of the chunk's DoG launches): the keypoint list and
-                # the 8-byte corner list leave chunk by chunk under the kernels of later chunks
-                r = ctx.dog_harris(up, kp_out=kp_host, co_out=co_host, compact=True)
+                # the stream-of-batches loop of INTEGRATION.md: enqueue both detectors on batch i (deferred), complete batch i-1 -- its
+                # keypoint list and 8-byte corner list leave under batch i's kernels -- then start the upload of batch i+1.  Every step = one upload, one
+                # detector call, one completed pair of host lists.
+                i = it[0]; it[0] += 1
+                ctx.dog_harris(pend[0], kp_out=kp_host[i & 1], co_out=co_host[i & 1], compact=True, defer=True)
+                if i:
+                    r = ctx.finish()                                          # batch i-1's lists: device-to-host first ...
+                    eo[0] |= bool(r["overflow"])
+                    last[0] = (len(r["keypoints"]), len(r["corners"]))
+                pend[0] = ctx.upload(hnp)                                     # ... then batch i+1's upload, both under batch i's kernels (an
+                return last[0]                                                # upload waits only for the readers of the buffer it overwrites)
+
+            def step_e2e_sync():
+                # latency regime: upload, both detectors, lists complete on return -- nothing overlaps across steps
+                r = ctx.dog_harris(ctx.upload(hnp), kp_out=kp_host[0], co_out=co_host[0], compact=True)
                 eo[0] |= bool(r["overflow"])
                 return len(r["keypoints"]), len(r["corners"])
 
+            def step_e2e_lookahead_sync():
+                # many GPUs on one host: the synchronous call (lists drain chunk by chunk inside it) with the next batch's upload
+                # started first spreads the copies over the step; measured better than the deferred loop at 8 GPUs
+                up = pend[0]
+                pend[0] = ctx.upload(hnp)
+                r = ctx.dog_harris(up, kp_out=kp_host[0], co_out=co_host[0], compact=True)
+                eo[0] |= bool(r["overflow"])
+                return len(r["keypoints"]), len(r["corners"])
+
+            mode = "latency" if e2e_sync else self.e2e_mode
+            if e2e_sync:
+                step_e2e = step_e2e_sync
+            elif mode == "sync":
+                step_e2e = step_e2e_lookahead_sync
+            step_e2e()
             step_e2e()
             ems, (ek, ec) = self.timed(step_e2e, steps)
+            r = ctx.finish()                                                  # the last step's lists (the step before the timed region was
+            eo[0] |= bool(r and r["overflow"])                                # completed inside it: one completion per timed step)
             if eo[0]:
                 raise SystemExit(f"output list overflow in the end-to-end steps of {w}x{h} x {nf}")
             ems /= steps
-            res["e2e"] = {"value": self.world * px_step / 1e6 / (ems * 1e-3), "unit": "Mpix/s", "ms_per_step": ems, "steps": steps,
+            res["e2e"] = {"value": self.world * px_step / 1e6 / (ems * 1e-3), "unit": "Mpix/s", "ms_per_step": ems, "steps": steps, "mode": mode,
                           "h2d_bytes_per_step": px_step, "d2h_bytes_per_step": int(ek * 24 + ec * 8 + 8 * nf),
-                          "api": "vslam_upload_frames (chunked; the next step's batch is uploaded under this step's kernels: two ingest buffers) + vslam_dog_harris (= vslam_dog_keypoints + corner-only vslam_harris "
-                                 "interleaved per chunk of frames; VSLAM_COMPACT: 8-byte vslam_corner8 list, lossless): host (pinned) frames in, "
-                                 "host (pinned) result lists out; value's steps run Harris in pipeline mode (response + mask stay in HBM)"}
+                          "api": "vslam_upload_frames (chunked; the next step's batch is uploaded under this step's kernels: two ingest buffers) + vslam_dog_harris | VSLAM_DEFER + vslam_finish (= vslam_dog_keypoints + corner-only vslam_harris "
+                                 "in one call; a step's lists are completed after the next step has been enqueued and leave under its kernels; VSLAM_COMPACT: 8-byte vslam_corner8 list, lossless): host (pinned) frames in, "
+                                 "host (pinned) result lists out.  value's steps run Harris in pipeline mode (response + mask written to HBM, 6 B per pixel) and "
+                                 "e2e's corner-only (nothing but the lists leaves the GPU), so e2e can exceed value by the 0.3 ms that costs"}
         del kp_dev, co_dev, resp_dev, mask_dev, dev
         torch.cuda.empty_cache()
         return res
@@ -393,6 +425,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--e2e-mode", default="auto", choices=["auto", "stream", "sync"],
+                    help="end-to-end loop: stream = deferred calls (vslam_dog_harris | VSLAM_DEFER + vslam_finish, look-ahead uploads), "
+                         "sync = one synchronous vslam_dog_harris per step with a look-ahead upload; auto = stream up to 4 GPUs per host, sync beyond")
     ap.add_argument("--no-sweep", action="store_true", help="skip the 4K / 8K / latency / materialise lines of the sweep block")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -439,10 +474,11 @@ def main():
                                       "value": r["value"], "unit": "Mpix/s", "frames_per_s": r["value"] * 1e6 / (sh * sw2), "ms_per_step": r["ms_per_step"],
                                       "e2e": r.get("e2e"), "keypoints_per_step": int(r["keypoints"]) * world, "corners_per_step": int(r["corners"]) * world}
         sh, sw2, _ = WORKLOADS["8k"]
-        r = R.workload(sh, sw2, 1, max(args.steps, 5), 2, e2e=not args.no_e2e, kernel_timing=False)
+        r = R.workload(sh, sw2, 1, max(args.steps, 5), 2, e2e=not args.no_e2e, kernel_timing=False, e2e_sync=True)
         sweep["8kx1_latency"] = {"workload": f"one synthetic {sw2}x{sh} frame per GPU per step (latency regime: 320 strips, one frame)",
                                  "ms_per_frame": r["ms_per_step"], "value": r["value"], "unit": "Mpix/s",
-                                 "e2e_ms_per_frame": r["e2e"]["ms_per_step"] if r.get("e2e") else None}
+                                 "e2e_ms_per_frame": r["e2e"]["ms_per_step"] if r.get("e2e") else None,
+                                 "e2e_mode": "synchronous call (upload + vslam_dog_harris, lists complete on return): a latency, not the stream-of-batches rate"}
         mh, mw, _ = WORKLOADS[args.workload]
         mnf = 8 if mh * mw <= 2.1e6 else (2 if mh * mw <= 8.3e6 else 1)           # 1.18 / 4.7 / 18.9 GB of maps per frame
         sweep["materialise"] = R.materialise(mh, mw, mnf, max(2, min(args.steps, 3)), 1)

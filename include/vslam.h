@@ -102,7 +102,8 @@ typedef enum vslam_map_kind {
 /* memory space of a caller buffer */
 #define VSLAM_HOST 0
 #define VSLAM_DEVICE 1
-#define VSLAM_COMPACT 0x100 /* vslam_harris only: `corners` receives vslam_corner8 entries (8 bytes) instead of vslam_corner */
+#define VSLAM_COMPACT 0x100 /* vslam_harris / vslam_dog_harris: `corners` receives vslam_corner8 entries (8 bytes) instead of vslam_corner */
+#define VSLAM_DEFER 0x200   /* vslam_dog_harris with host lists: return once the work is enqueued; vslam_finish completes it */
 
 /* ---- context ------------------------------------------------------------------------------------------------ */
 /* Stream contract.  Every call enqueues its work on the context's stream and returns; host-space outputs are complete on
@@ -216,6 +217,16 @@ VSLAM_API int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_fram
                                const vslam_dog_params *dparams, const vslam_harris_params *hparams,
                                vslam_keypoint *keypoints, int kp_capacity, int *kp_counts, vslam_corner *corners,
                                int co_capacity, int *co_counts, int out_space);
+
+/* Deferred completion, for callers that process a stream of batches (no counterpart in the reference): with VSLAM_HOST |
+ * VSLAM_DEFER vslam_dog_harris returns as soon as its work is enqueued -- nothing in the host lists or the count arrays is valid
+ * yet.  vslam_finish waits for the OLDEST pending call, fills its count arrays, copies its lists into the host buffers given to
+ * that call and returns its status (VSLAM_OK, VSLAM_E_CAPACITY ...).  At most two calls may be pending, so the usual loop is
+ *   vslam_dog_harris(batch i, buffers[i & 1], ... | VSLAM_DEFER); if (i) vslam_finish(ctx); upload(i+1);      (vslam_finish completes batch i-1)
+ * and the lists of batch i-1, then the frames of batch i+1, cross PCIe under the kernels of batch i (one direction at a time: a
+ * host shared by several GPUs moves far fewer bytes when both directions are busy at once).  Buffers and count arrays of a pending call must stay
+ * alive and untouched until its vslam_finish.  vslam_sync does not complete pending calls; vslam_ctx_destroy drops them. */
+VSLAM_API int vslam_finish(vslam_ctx *ctx);
 
 /* ---- per-function entry points: the reference's own function granularity, for the C++17 mirror in
  *      visualslam_b200/host/ (HOST buffers, dense unless a pitch is given; each call synchronises).  The throughput

@@ -106,3 +106,11 @@ def test_fp32_tap_generator_and_descriptor_file_need_no_gpu(lib, tmp_path):
     assert np.frombuffer(p.read_bytes(), "<i4").tolist() == [0, 128, 24]
     with pytest.raises(api.VslamError):
         api.write_descriptor_file(str(tmp_path / "no_such_dir" / "x.dat"), d)
+
+
+def test_header_compiles_as_plain_c(tmp_path):
+    """include/vslam.h is the boundary a C (cgo / ctypes / JNI) binding includes: it must parse as C99 on its own."""
+    import subprocess
+    src = tmp_path / "t.c"
+    src.write_text('#include "vslam.h"\nint main(void) { vslam_corner8 c; c.row = 0; (void)c; return sizeof(vslam_keypoint) == 24 ? 0 : 1; }\n')
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-fsyntax-only", "-I", os.path.join(ROOT, "include"), str(src)])

@@ -657,3 +657,40 @@ def test_pipelined_uploads_two_ingest_buffers(ctx):
         if rnd == 1:                                   # separate calls on an uploaded batch too
             assert np.array_equal(ctx.harris(up, want_maps=False)["corners"], want[name][1])
         up = up_next
+
+
+def test_deferred_dog_harris_pipeline(ctx):
+    """VSLAM_DEFER + vslam_finish: batch i's call only enqueues, its lists are completed by finish() after batch i+1 has been
+    enqueued (two buffer sets); results equal the synchronous call's, a third pending call is refused, overflow is reported by finish."""
+    import torch
+    A = np.stack([synth.frame(i % 8, 270, 480) for i in range(20)], 0)
+    B = np.stack([synth.frame((i + 5) % 8, 270, 480)[:, ::-1].copy() for i in range(20)], 0)
+    want = {n: ctx.dog_harris(f, compact=True) for n, f in (("A", A), ("B", B))}
+    pin = {"A": torch.from_numpy(A).pin_memory().numpy(), "B": torch.from_numpy(B).pin_memory().numpy()}
+    bufs = [(torch.empty((1 << 18, 6), dtype=torch.int32, pin_memory=True).numpy(), torch.empty((1 << 20, 2), dtype=torch.int32, pin_memory=True).numpy())
+            for _ in range(2)]
+    order = ["A", "B", "B", "A", "A"]
+    up = ctx.upload(pin[order[0]])
+    done = []
+    for i, name in enumerate(order):
+        nxt = ctx.upload(pin[order[i + 1]]) if i + 1 < len(order) else None
+        assert ctx.dog_harris(up, kp_out=bufs[i & 1][0], co_out=bufs[i & 1][1], compact=True, defer=True) is None
+        if i:
+            done.append({k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in ctx.finish().items()})   # views of bufs: reused two steps on
+        up = nxt
+    done.append(ctx.finish())
+    assert ctx.finish() is None
+    for name, r in zip(order, done):
+        w = want[name]
+        assert r["kp_counts"] == w["kp_counts"] and r["co_counts"] == w["co_counts"] and not r["overflow"], name
+        assert np.array_equal(r["keypoints"], w["keypoints"]) and np.array_equal(r["corners"], w["corners"]), name
+    # a third pending call is refused; the two pending ones still complete
+    small_k = torch.empty((50, 6), dtype=torch.int32, pin_memory=True).numpy()
+    ctx.dog_harris(A, kp_out=small_k, co_out=bufs[0][1], compact=True, defer=True)
+    ctx.dog_harris(B, kp_out=bufs[1][0], co_out=bufs[1][1], compact=True, defer=True)
+    with pytest.raises(vs.VslamError):
+        ctx.dog_harris(A, kp_out=bufs[0][0], co_out=bufs[0][1], compact=True, defer=True)
+    r = ctx.finish()
+    assert r["overflow"] and r["kp_counts"] == want["A"]["kp_counts"] and np.array_equal(r["keypoints"], want["A"]["keypoints"][:50])
+    r = ctx.finish()
+    assert not r["overflow"] and np.array_equal(r["corners"], want["B"]["corners"])

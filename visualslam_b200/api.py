@@ -28,6 +28,7 @@ KEYPOINT_DTYPE = np.dtype([("row", "<i4"), ("col", "<i4"), ("value", "<i4"), ("p
 CORNER_DTYPE = np.dtype([("row", "<i4"), ("col", "<i4"), ("value", "<f4")])
 CORNER8_DTYPE = np.dtype([("row", "<u2"), ("col", "<u2"), ("value", "<f4")])      # vslam_corner8 (VSLAM_COMPACT)
 COMPACT = 0x100
+DEFER = 0x200
 
 
 class PyramidParams(C.Structure):
@@ -55,7 +56,7 @@ EXPORTS = [
     "vslam_version", "vslam_launch_count", "vslam_calculate_sigma", "vslam_calculate_num_octaves",
     "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_destroy",
     "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
-    "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris", "vslam_dog_harris",
+    "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris", "vslam_dog_harris", "vslam_finish",
     "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
     "vslam_bgr_to_gray", "vslam_rotate_mat_ccw", "vslam_rotated_window", "vslam_get_rotation_matrix_2d", "vslam_warp_affine", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
@@ -111,6 +112,7 @@ def load():
     L.vslam_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(HarrisParams), vp, vp, vp, vp, i, i, C.POINTER(i)]
     L.vslam_dog_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(DogParams), C.POINTER(HarrisParams),
                                    vp, i, C.POINTER(i), vp, i, C.POINTER(i), i]
+    L.vslam_finish.argtypes = [vp]
     L.vslam_upload_frames.argtypes = [vp, vp, i, i, i, sz, sz, C.POINTER(vp), C.POINTER(sz), C.POINTER(sz)]
     L.vslam_gauss_ksize_f32.argtypes = [C.c_double]
     L.vslam_gauss_taps_f32.argtypes = [C.c_double, i, C.POINTER(C.c_float)]
@@ -371,10 +373,11 @@ class Context:
                 "overflow": rc == E_CAPACITY}
 
     def dog_harris(self, frames, num_octaves=4, sigma0=1.6, contrast_thr=0.03, edge_r=10.0, k=0.04, nms2_window=5, kp_capacity=1 << 20,
-                   co_capacity=1 << 22, kp_out=None, co_out=None, compact=False):
+                   co_capacity=1 << 22, kp_out=None, co_out=None, compact=False, defer=False):
         """Both detectors over one batch (vslam_dog_harris): the lists of dog_keypoints and harris(want_maps=False), with the corner
         list draining under the DoG kernels.  kp_out / co_out: caller-owned host buffers (numpy, e.g. pinned) or torch cuda tensors
-        (both on the device then); compact: the corner list as vslam_corner8."""
+        (both on the device then); compact: the corner list as vslam_corner8.  defer=True (host kp_out and co_out required): the call
+        only enqueues; finish() completes the oldest pending call and returns its result dict (at most two calls pending)."""
         dev = self._torch_in(frames, kp_out, co_out)
         ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
         pp = PyramidParams(num_octaves, 3, sigma0, 0); dp = DogParams(3, contrast_thr, edge_r); hp = HarrisParams(k, nms2_window)
@@ -389,14 +392,32 @@ class Context:
             kh = np.zeros(kp_capacity, KEYPOINT_DTYPE) if kp_out is None else kp_out.view(KEYPOINT_DTYPE).reshape(-1)
             ch = np.zeros(co_capacity, cdt) if co_out is None else co_out.view(cdt).reshape(-1)
             kptr, cptr, kcap, ccap, ospace = kh.ctypes.data, ch.ctypes.data, kh.shape[0], ch.shape[0], HOST
+        if defer:
+            assert not on_dev and kp_out is not None and co_out is not None
         rc = load().vslam_dog_harris(self.h, ptr, n, h, w, pitch, stride, space, C.byref(pp), C.byref(dp), C.byref(hp), kptr, kcap, kc, cptr, ccap,
-                                     cc, ospace | (COMPACT if compact else 0))
+                                     cc, ospace | (COMPACT if compact else 0) | (DEFER if defer else 0))
         if rc and rc != E_CAPACITY:
             self._chk(rc)
+        if defer:
+            if not hasattr(self, "_pending"):
+                self._pending = []
+            self._pending.append((kh, ch, kc, cc, kcap, ccap, keep))       # keeps the buffers and count arrays alive until finish()
+            return None
         self._torch_out(dev)
         kl, cl = list(kc), list(cc)
         return {"keypoints": kh[:min(sum(kl), kcap)] if kh is not None else kp_out, "corners": ch[:min(sum(cl), ccap)] if ch is not None else co_out,
                 "kp_counts": kl, "co_counts": cl, "overflow": rc == E_CAPACITY}
+
+    def finish(self):
+        """vslam_finish: complete the oldest deferred dog_harris call; returns its result dict (None if nothing is pending)."""
+        if not getattr(self, "_pending", None):
+            return None
+        kh, ch, kc, cc, kcap, ccap, _ = self._pending.pop(0)
+        rc = load().vslam_finish(self.h)
+        if rc and rc != E_CAPACITY:
+            self._chk(rc)
+        kl, cl = list(kc), list(cc)
+        return {"keypoints": kh[:min(sum(kl), kcap)], "corners": ch[:min(sum(cl), ccap)], "kp_counts": kl, "co_counts": cl, "overflow": rc == E_CAPACITY}
 
     def assign_orientations(self, pyr, octave, keypoints, frame=0, histograms=False):
         """filterKeypoints' orientation stage (Diff_of_Gauss.cpp:340-369) for one octave's keypoints."""

@@ -107,12 +107,15 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     DevBuf *bufs[] = {&ctx->seg_off, &ctx->seg_cnt, &ctx->seg_dst, &ctx->seg_partial, &ctx->staging, &ctx->counters, &ctx->stage_counts,
                       &ctx->ingest, &ctx->ingest2, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev, &ctx->alt_seg_off, &ctx->alt_seg_cnt, &ctx->alt_seg_dst,
-                      &ctx->alt_seg_partial, &ctx->alt_staging, &ctx->alt_counters, &ctx->alt_out_dev};
+                      &ctx->alt_seg_partial, &ctx->alt_staging, &ctx->alt_counters, &ctx->alt_out_dev, &ctx->defer_kp[0], &ctx->defer_kp[1],
+                      &ctx->defer_co[0], &ctx->defer_co[1]};
     for (DevBuf *b : bufs) b->release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->up_ev) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->up_ev2) cudaEventDestroy(e);
+    for (auto &d : ctx->defer) if (d.ev) cudaEventDestroy(d.ev);
+    for (cudaEvent_t e : ctx->slot_done) if (e) cudaEventDestroy(e);
     if (ctx->up_start) cudaEventDestroy(ctx->up_start);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (cudaEvent_t e : ctx->down_ev) cudaEventDestroy(e);
@@ -250,7 +253,7 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
     if (!frames || n <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "frames null or n_frames <= 0");
     if (pitch < (size_t)cols) VS_FAIL(ctx, VSLAM_E_INVALID, "pitch %zu < cols %d", pitch, cols);
     if (n > 1 && frame_stride < pitch * (size_t)rows) VS_FAIL(ctx, VSLAM_E_INVALID, "frame_stride too small");
-    ctx->up_chunks = 0; ctx->up_foff = 0;
+    ctx->up_chunks = 0; ctx->up_foff = 0; ctx->consuming = -1;
     if (space == VSLAM_DEVICE) {
         *d_frames = frames; *d_pitch = pitch; *d_stride = frame_stride;
         // frames handed out by vslam_upload_frames: their chunks may still be in flight on the copy stream
@@ -261,6 +264,7 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
             if (!ctx->slot_total[sl] || !b || frames < b || frames >= b + buf.cap || frame_stride != ctx->slot_ds[sl]) continue;
             ctx->up_slot = sl; ctx->up_chunk = ctx->slot_chunk[sl]; ctx->up_total = ctx->slot_total[sl]; ctx->up_ds = ctx->slot_ds[sl];
             ctx->up_foff = (int)((size_t)(frames - b) / ctx->up_ds);
+            ctx->slot_busy[sl] = true; ctx->consuming = sl;
             // an upload that has already landed (started under the previous batch's kernels) needs no waits and no short first launches
             if (cudaEventQuery(ev[(size_t)ctx->up_total - 1]) != cudaSuccess) { cudaGetLastError(); ctx->up_chunks = ctx->up_total; }
             break;
@@ -286,9 +290,15 @@ static int ingest_frames(vslam_ctx *ctx, const u8 *frames, int n, int rows, int 
         VS_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         iev.push_back(e);
     }
-    // earlier work on the compute stream may still read the ingest buffer
-    VS_CUDA(ctx, cudaEventRecord(ctx->up_start, ctx->stream));
-    VS_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->up_start, 0));
+    // readers of the batch this buffer held may still be running: wait for the event behind the last of them, or -- when a reader has
+    // not recorded one -- for everything enqueued on the compute stream so far
+    if (!ctx->slot_busy[sl] && ctx->slot_done_set[sl]) {
+        VS_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->slot_done[sl], 0));
+    } else {
+        VS_CUDA(ctx, cudaEventRecord(ctx->up_start, ctx->stream));
+        VS_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->up_start, 0));
+    }
+    ctx->slot_busy[sl] = true; ctx->consuming = sl;             // the calling detector reads it (vslam_upload_frames clears this)
     for (int c = 0; c < chunks; ++c) {
         const int f0 = c * chunk, nf = n - f0 < chunk ? n - f0 : chunk;
         if (pitch == (size_t)cols && dp == pitch && frame_stride == ds) {
@@ -313,6 +323,15 @@ static int wait_ingest(vslam_ctx *ctx, int f0, int nf) {
     const int c0 = f0 / ctx->up_chunk, c1 = (f0 + nf - 1) / ctx->up_chunk;
     const std::vector<cudaEvent_t> &ev = ctx->up_slot ? ctx->up_ev2 : ctx->up_ev;
     for (int c = c0; c <= c1 && c < ctx->up_chunks; ++c) VS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ev[c], 0));
+    return VSLAM_OK;
+}
+// behind the last kernel of a detector call: the ingest buffer it read may be overwritten once this event has passed
+static int consume_end(vslam_ctx *ctx) {
+    const int sl = ctx->consuming;
+    if (sl < 0) return VSLAM_OK;
+    if (!ctx->slot_done[sl]) VS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->slot_done[sl], cudaEventDisableTiming));
+    VS_CUDA(ctx, cudaEventRecord(ctx->slot_done[sl], ctx->stream));
+    ctx->slot_done_set[sl] = true; ctx->slot_busy[sl] = false; ctx->consuming = -1;
     return VSLAM_OK;
 }
 // frames per compute launch when the input is being uploaded: ~128 MB of frames, and a short first launch so that the
@@ -790,6 +809,7 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
             VS_TRY(detect_frame(ctx, g, ctx->ws_maps.as<u8>(), dp, seg_base, n_seg, d_out, capacity, f, nullptr));
         }
     }
+    VS_TRY(consume_end(ctx));
     long long total = 0;
     VS_TRY(finish_counts(ctx, n_frames, capacity, counts, &total));
     VS_TRY(drain_end(ctx, drain));
@@ -905,6 +925,7 @@ int vslam_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, 
         VS_TRY(wait_ingest(ctx, f0, nf));
         VS_TRY(harris_chunk(ctx, j, f0, nf));
     }
+    VS_TRY(consume_end(ctx));
     return harris_end(ctx, j, counts);
 }
 
@@ -921,6 +942,73 @@ struct ListSetSwap {
     }
 };
 
+// pinned snapshot of a deferred call: [gen][kp counts n | co counts n] behind the drain slots
+static int *defer_pinned(vslam_ctx *ctx, int gen) { return (int *)((u8 *)ctx->pinned + (16 << 10) + (size_t)gen * (320 << 10)); }
+
+// VSLAM_DEFER: everything enqueued, nothing waited for.  The lists stay in the call's own device buffers; vslam_finish copies them.
+static int dog_harris_deferred(vslam_ctx *ctx, const Geometry &g, const u8 *d_frames, size_t d_pitch, size_t d_stride, int n_frames, int rows,
+                               int cols, const vslam_dog_params &dp, const vslam_harris_params *hparams, vslam_keypoint *keypoints, int kp_capacity,
+                               int *kp_counts, vslam_corner *corners, int co_capacity, int *co_counts, int out_space) {
+    const int gen = ctx->defer_next;
+    vslam_ctx::Deferred &D = ctx->defer[gen];
+    if (D.live) VS_FAIL(ctx, VSLAM_E_INVALID, "two deferred calls are pending: vslam_finish first");
+    const int compact = (out_space & VSLAM_COMPACT) ? 1 : 0;
+    const size_t centry = compact ? sizeof(vslam_corner8) : sizeof(vslam_corner);
+    if (ctx->defer_kp[gen].reserve(sizeof(vslam_keypoint) * (size_t)(kp_capacity + 1)) || ctx->defer_co[gen].reserve(centry * (size_t)(co_capacity + 1)))
+        VS_FAIL(ctx, VSLAM_E_NOMEM, "device lists of a deferred call");
+    if (!D.ev) VS_CUDA(ctx, cudaEventCreateWithFlags(&D.ev, cudaEventDisableTiming));
+    if (!ctx->down_stream) VS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking));
+    // A deferred caller runs ahead of the GPU: the previous call's kernels are usually still queued, so this batch's upload (started
+    // under them) will have landed before these launches reach the GPU.  One wait for the whole upload, then full-size launches --
+    // not the doubling launch sizes that chase an upload in progress.
+    VS_TRY(wait_ingest(ctx, 0, n_frames));
+    ctx->up_chunks = 0;
+    HarrisJob hj;
+    {
+        ListSetSwap sw(ctx);
+        VS_TRY(harris_begin(ctx, hj, d_frames, d_pitch, d_stride, n_frames, rows, cols, hparams, nullptr, nullptr, nullptr, ctx->defer_co[gen].p,
+                            co_capacity, VSLAM_DEVICE | (compact ? VSLAM_COMPACT : 0), n_frames, kDrainMax));
+    }
+    const std::function<int(int, int)> hook = [&](int f0, int nf) -> int {
+        ListSetSwap sw(ctx);
+        return harris_chunk(ctx, hj, f0, nf);
+    };
+    ListDrain kdrain;
+    VS_TRY(dog_keypoints_fused(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, dp, ctx->defer_kp[gen].as<vslam_keypoint>(), kp_capacity,
+                               &kdrain, nullptr, VSLAM_DEVICE, &hook));
+    VS_TRY(consume_end(ctx));
+    int *snap = defer_pinned(ctx, gen);
+    VS_CUDA(ctx, cudaMemcpyAsync(snap, ctx->counters.as<int>() + kCounterBase, sizeof(int) * (size_t)n_frames, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaMemcpyAsync(snap + n_frames, ctx->alt_counters.as<int>() + kCounterBase, sizeof(int) * (size_t)n_frames, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+    VS_CUDA(ctx, cudaEventRecord(D.ev, ctx->stream));
+    D.live = true; D.kp_host = keypoints; D.co_host = corners; D.kp_counts = kp_counts; D.co_counts = co_counts;
+    D.kp_cap = kp_capacity; D.co_cap = co_capacity; D.n_frames = n_frames; D.co_entry = centry;
+    ctx->defer_next ^= 1;
+    return VSLAM_OK;
+}
+
+int vslam_finish(vslam_ctx *ctx) {
+    if (!ctx) return VSLAM_E_INVALID;
+    int gen = ctx->defer_next;                                  // with two calls pending, the slot the next call would take is the older one
+    if (!ctx->defer[gen].live) gen ^= 1;
+    vslam_ctx::Deferred &D = ctx->defer[gen];
+    if (!D.live) return VSLAM_OK;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    D.live = false;
+    VS_CUDA(ctx, cudaEventSynchronize(D.ev));
+    const int *snap = defer_pinned(ctx, gen);
+    long long nk = 0, nc = 0;
+    for (int f = 0; f < D.n_frames; ++f) { D.kp_counts[f] = snap[f]; nk += snap[f]; D.co_counts[f] = snap[D.n_frames + f]; nc += snap[D.n_frames + f]; }
+    const size_t ck = (size_t)(nk < D.kp_cap ? nk : D.kp_cap), cc = (size_t)(nc < D.co_cap ? nc : D.co_cap);
+    if (ck) VS_CUDA(ctx, cudaMemcpyAsync(D.kp_host, ctx->defer_kp[gen].p, ck * sizeof(vslam_keypoint), cudaMemcpyDeviceToHost, ctx->down_stream));
+    if (cc) VS_CUDA(ctx, cudaMemcpyAsync(D.co_host, ctx->defer_co[gen].p, cc * D.co_entry, cudaMemcpyDeviceToHost, ctx->down_stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->down_stream));
+    if (nk > D.kp_cap || nc > D.co_cap)
+        VS_FAIL(ctx, VSLAM_E_CAPACITY, "deferred call: lists hold %d / %d entries, %lld / %lld produced", D.kp_cap, D.co_cap, nk, nc);
+    return VSLAM_OK;
+}
+
 int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride, int space,
                      const vslam_pyramid_params *pparams, const vslam_dog_params *dparams, const vslam_harris_params *hparams,
                      vslam_keypoint *keypoints, int kp_capacity, int *kp_counts, vslam_corner *corners, int co_capacity, int *co_counts,
@@ -929,9 +1017,14 @@ int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int ro
     VS_CUDA(ctx, cudaSetDevice(ctx->device));
     vslam_dog_params dp;
     VS_TRY(check_dog_params(ctx, dparams, &dp));
+    const bool defer = (out_space & VSLAM_DEFER) != 0;
+    out_space &= ~VSLAM_DEFER;
     const int kp_space = out_space & ~VSLAM_COMPACT;
+    if (defer && kp_space != VSLAM_HOST) VS_FAIL(ctx, VSLAM_E_INVALID, "VSLAM_DEFER goes with host lists (device lists are never waited for)");
+    if (defer && (!kp_counts || !co_counts || !ctx->pinned)) VS_FAIL(ctx, VSLAM_E_INVALID, "VSLAM_DEFER needs both count arrays");
     const size_t h_spf = (size_t)(rows > 0 ? rows : 1) * harris_strips(cols > 0 ? cols : 1);
     if (dp.window != 3 || (size_t)n_frames > ((size_t)1 << 30) / h_spf || n_frames > 32768) {
+        if (defer) VS_FAIL(ctx, VSLAM_E_INVALID, "VSLAM_DEFER: window 3 and at most 32768 frames per call");
         // shapes the interleaved loop does not take: the two calls one after the other (same results)
         const int rk = vslam_dog_keypoints(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, pparams, dparams, keypoints, kp_capacity,
                                            kp_space, kp_counts);
@@ -947,6 +1040,8 @@ int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int ro
     const u8 *d_frames; size_t d_pitch, d_stride;
     VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
     VS_TRY(reserve_counters(ctx, n_frames));
+    if (defer) return dog_harris_deferred(ctx, g, d_frames, d_pitch, d_stride, n_frames, rows, cols, dp, hparams, keypoints, kp_capacity, kp_counts,
+                                          corners, co_capacity, co_counts, out_space);
     vslam_keypoint *d_kp = keypoints;
     if (kp_space != VSLAM_DEVICE) {
         if (ctx->out_dev.reserve(sizeof(vslam_keypoint) * (size_t)(kp_capacity + 1))) VS_FAIL(ctx, VSLAM_E_NOMEM, "device keypoint list");
@@ -964,6 +1059,7 @@ int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int ro
     };
     ListDrain kdrain;
     VS_TRY(dog_keypoints_fused(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, dp, d_kp, kp_capacity, &kdrain, keypoints, kp_space, &hook));
+    VS_TRY(consume_end(ctx));
     long long total = 0;
     VS_TRY(finish_counts(ctx, n_frames, kp_capacity, kp_counts, &total));
     VS_TRY(drain_end(ctx, kdrain));
@@ -984,6 +1080,7 @@ int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
     if (rows <= 0 || cols <= 0) VS_FAIL(ctx, VSLAM_E_INVALID, "image size %dx%d", rows, cols);
     VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, VSLAM_HOST, d_frames, d_pitch, d_frame_stride));
     ctx->up_chunks = 0;                                          // the consumers re-arm the waits from the returned pointer
+    if (ctx->consuming >= 0) { ctx->slot_busy[ctx->consuming] = false; ctx->consuming = -1; }   // nobody reads the new batch yet
     return VSLAM_OK;
 }
 

@@ -50,6 +50,18 @@ struct vslam_ctx {
     // second set of the list workspace: vslam_dog_harris keeps two ordered lists growing at once (swap_list_sets, capi.cu)
     vslam::DevBuf alt_seg_off, alt_seg_cnt, alt_seg_dst, alt_seg_partial, alt_staging, alt_counters, alt_out_dev;
     int alt_staging_entries = 0;
+    // deferred completion (vslam_dog_harris with VSLAM_DEFER, vslam_finish): two calls may be in flight; each keeps its device
+    // lists, an event behind its last kernel and a pinned snapshot of its per-frame counts until vslam_finish copies the lists out
+    struct Deferred {
+        bool live = false;
+        cudaEvent_t ev = nullptr;
+        void *kp_host = nullptr, *co_host = nullptr;
+        int *kp_counts = nullptr, *co_counts = nullptr;
+        int kp_cap = 0, co_cap = 0, n_frames = 0;
+        size_t co_entry = 0;
+    } defer[2];
+    int defer_next = 0;
+    vslam::DevBuf defer_kp[2], defer_co[2];
     // throughput-path workspace: one frame's pyramid, reused
     vslam::DevBuf ingest;          // aligned copy of the input frame(s)
     vslam::DevBuf ws_maps;         // octave bases of a chunk of frames (or all planes of one frame)
@@ -72,6 +84,12 @@ struct vslam_ctx {
     int slot_chunk[2] = {0, 0}, slot_total[2] = {0, 0};
     size_t slot_ds[2] = {0, 0};
     int ingest_next = 0;
+    // an upload into a buffer has to wait for the readers of the batch it held, not for everything on the compute stream: every
+    // detector call records slot_done[buffer] behind its last kernel (consume_end, capi.cu).  slot_busy: a call has started reading the
+    // buffer and has not recorded yet (an entry point without consume_end, or an error path): the upload then waits conservatively.
+    cudaEvent_t slot_done[2] = {nullptr, nullptr};
+    bool slot_done_set[2] = {false, false}, slot_busy[2] = {false, false};
+    int consuming = -1;
     // host result lists leave chunk by chunk on a third stream while later chunks compute (capi.cu: ListDrain)
     cudaStream_t down_stream = nullptr;
     std::vector<cudaEvent_t> down_ev;

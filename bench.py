@@ -369,6 +369,16 @@ class Runner:
         return same, dig.hex(), len(a["keypoints"]), len(b["corners"])
 
 
+def measured_traffic(kernel, h, w, nf):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture of this workload (tools/prof_all.sh + tools/ncu_summary.py)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic_r2.json")))
+        key = {(1080, 1920, 256): "1080px256"}.get((h, w, nf))
+        return float(t[key][kernel]) if key and kernel in t.get(key, {}) else None
+    except Exception:
+        return None
+
+
 def roofline_block(res, steps, world):
     """roofline of the dominant kernel of the headline workload + HBM fractions of the other kernels on the timed path."""
     prof, h, w, nf = res["prof"], res["h"], res["w"], res["frames_per_gpu"]
@@ -395,12 +405,15 @@ def roofline_block(res, steps, world):
              "achieved": tops if dom in octave_kernels else hbm_ach,
              "peak": bf16_peak if dom in octave_kernels else hbm_peak, "unit": "TFLOP/s" if dom in octave_kernels else "GB/s",
              "frac": (tops / bf16_peak if tops else None) if dom in octave_kernels else (hbm_ach / hbm_peak if hbm_ach else None),
-             "traffic": None, "peak_source": peak_src,
+             "traffic": measured_traffic(dom, h, w, nf), "peak_source": peak_src,
              "mode": "keypoints-only (fused): octave bases are the only maps in HBM",
              "note": "achieved = useful integer ops of the blur (2 x 1738 MAC per input pixel: the banded-Toeplitz zeros the MMAs also multiply are "
                      "not counted) over the device time of the octave kernels; peak = the measured dense bf16 rate (sustained) of MEASURED_PEAKS.json "
                      "-- the u8 rate of the tensor pipe is nominally twice that, so the fraction is an upper bound of the pipe's utilisation. "
-                     "traffic: not measured in this run (ncu captures under profiles/ hold dram bytes per launch).",
+                     "traffic: dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel (mean of the four octave launches of a "
+                     "step) from the committed ncu --set full capture of the same command (profiles/traffic_r2.json, profiles/"
+                     "ncu_full_r2_summary.csv); null for a workload that has no capture.  hbm.algorithmic_bytes_per_launch is the figure it is "
+                     "compared with.",
              "tensor": {"useful_TMAC_s": tmac, "mma_sync_u8_peak_TMAC_s": IMMA_PEAK_TMAC, "frac_of_mma_sync_peak": tmac / IMMA_PEAK_TMAC if tmac else None,
                         "mac_per_input_px": MAC_PER_PX,
                         "peak_source": "mma.sync.m16n8k32 u8 issue peak measured on a B200 of this pool (tools/imma_peak.cu, profiles/imma_peak_r1.json)"},

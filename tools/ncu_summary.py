@@ -29,7 +29,8 @@ def val(r, n):
 tr = {}
 for r in rows[2:]:
     k = r[idx['Kernel Name']]
-    name = 'octave_fused_k' if 'octave_' in k else 'harris_fused_k' if 'harris' in k else 'upsample2x_k' if 'upsample' in k else 'reflect_pad_k'
+    name = ('octave_mma_k' if 'octave_mma' in k else 'octave_umma_k' if 'octave_umma' in k else 'octave_fused_k' if 'octave_' in k else
+            'harris_fast_k' if 'harris_fast' in k else 'harris_march_k' if 'harris' in k else 'upsample2x_k' if 'upsample' in k else 'reflect_pad_k')
     tr.setdefault(name, []).append(val(r, 'dram__bytes_read.sum') + val(r, 'dram__bytes_write.sum'))
 t = {k: sum(v) / len(v) for k, v in tr.items()}
 t['source'] = (f"{out_csv}: dram__bytes_read.sum + dram__bytes_write.sum per launch (octave and pad kernels: mean of the four launches of a "

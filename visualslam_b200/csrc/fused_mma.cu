@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
             if (zhat > a.contrast_thr && edge_pass(level, xc, yc, yb)) {             // :245
                 const int task = sr * 3 + level - 1;
                 s_res[task * NS + k] = (int)__fmul_rn(zhat, 255.0f);                 // :246
-                atomicOr(&s_mask[mp], 1ull << task);
+                atomicOr((unsigned *)&s_mask[mp] + (task >> 5), 1u << (task & 31));      // 32-bit halves: a native shared atomic, not a CAS loop
             }
         }
     };
@@ -425,7 +425,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
                                 // host with the same float ops: a.cmin, a.val_lut)
                                 if (c >= a.cmin && edge_pass(level, det_xc, yc, y0)) {
                                     res[level - 1] = a.val_lut[c];
-                                    atomicOr(&s_mask[par], 1ull << (det_sr * 3 + level - 1));
+                                    atomicOr((unsigned *)&s_mask[par] + ((det_sr * 3 + level - 1) >> 5), 1u << ((det_sr * 3 + level - 1) & 31));
                                 }
                             } else {
                                 s_queue[atomicAdd(&s_nq, 1)] = (unsigned short)(det_k | level << 5 | det_sr << 8);

@@ -196,6 +196,15 @@ VSLAM_API int vslam_upload_frames(vslam_ctx *ctx, const uint8_t *frames, int n_f
                                   size_t frame_stride, const uint8_t **d_frames, size_t *d_pitch,
                                   size_t *d_frame_stride);
 
+/* JPEG streams in host memory -> grey frames (imread(path, IMREAD_COLOR) + cvtColor(COLOR_BGR2GRAY), Diff_of_Gauss.cpp:730-739,
+ * Harris_corners.cpp:148-149): nvJPEG decodes to BGR on the device, the bit-exact cvtColor kernel turns it
+ * grey.  gray: n frames of rows x cols in `space`; pass VSLAM_DEVICE frames straight to the detectors.  Every stream must decode to
+ * rows x cols (vslam_jpeg_info).  NOT a parity target: a decoder's output differs from libjpeg's by a few grey levels.  libnvjpeg is
+ * opened at run time; without it both calls return VSLAM_E_CUDA and everything else works. */
+VSLAM_API int vslam_jpeg_info(vslam_ctx *ctx, const uint8_t *stream, size_t length, int *rows, int *cols, int *channels);
+VSLAM_API int vslam_decode_jpeg_gray(vslam_ctx *ctx, const uint8_t *const *streams, const size_t *lengths, int n, int rows,
+                                     int cols, uint8_t *gray, size_t gray_pitch, size_t gray_stride, int space);
+
 /* ---- Harris: main's pre-blur + Sobel, HarrisCorner, convertScaleAbs + NonMaximumSuppression, NMS2
  *      (Harris_corners.cpp:158-164, 31-68, 176-178, 83-129) ------------------------------------------------------ */
 /* Any of response / r8 / mask3 may be NULL (not materialised).  Maps are dense n_frames x rows x cols in `space`.

@@ -694,3 +694,37 @@ def test_deferred_dog_harris_pipeline(ctx):
     assert r["overflow"] and r["kp_counts"] == want["A"]["kp_counts"] and np.array_equal(r["keypoints"], want["A"]["keypoints"][:50])
     r = ctx.finish()
     assert not r["overflow"] and np.array_equal(r["corners"], want["B"]["corners"])
+
+
+def test_jpeg_ingest_decodes_to_grey_frames(ctx, images):
+    """vslam_decode_jpeg_gray (nvJPEG + the bit-exact BGR2GRAY kernel).  Not a parity target -- a decoder's
+    output is a fixture -- so the check is a tolerance against cv2's decode of the same stream (libjpeg-turbo): mean |diff| < 1 grey
+    level, 99.9 % of the pixels within 4; a grey-scale JPEG decodes exactly; the frames feed the detectors from device memory."""
+    import cv2
+    import torch
+    from conftest import GOLDEN
+    import os
+    with np.load(os.path.join(GOLDEN, "home_bgr.npz")) as z:
+        bgr = z[z.files[0]] if "bgr" not in z.files else z["bgr"]
+    assert bgr.ndim == 3 and bgr.shape[2] == 3
+    streams, want = [], []
+    for q in (95, 80):
+        ok, enc = cv2.imencode(".jpg", bgr, [cv2.IMWRITE_JPEG_QUALITY, q])
+        assert ok
+        streams.append(enc.tobytes())
+        want.append(cv2.cvtColor(cv2.imdecode(enc, cv2.IMREAD_COLOR), cv2.COLOR_BGR2GRAY))
+    got = ctx.decode_jpeg_gray(streams)
+    assert got.shape == (2,) + bgr.shape[:2]
+    for g, w in zip(got, want):
+        d = np.abs(g.astype(np.int32) - w.astype(np.int32))
+        assert d.mean() < 1.0 and (d <= 4).mean() > 0.999, (d.mean(), d.max(), (d <= 4).mean())
+    grey = images["home_gray"]
+    ok, enc = cv2.imencode(".jpg", grey, [cv2.IMWRITE_JPEG_QUALITY, 90])
+    ref = cv2.imdecode(enc, cv2.IMREAD_GRAYSCALE)
+    one = ctx.decode_jpeg_gray([enc.tobytes()])[0]
+    assert np.abs(one.astype(np.int32) - ref.astype(np.int32)).max() <= 2          # one component: only the IDCT rounding differs
+    dev = torch.empty(got.shape, dtype=torch.uint8, device="cuda")
+    ctx.decode_jpeg_gray(streams, out=dev)
+    assert np.array_equal(dev.cpu().numpy(), got)
+    a, b = ctx.dog_keypoints(dev), ctx.dog_keypoints(got)
+    assert a["counts"] == b["counts"] and np.array_equal(a["keypoints"], b["keypoints"]) and sum(a["counts"]) > 100

@@ -56,7 +56,7 @@ EXPORTS = [
     "vslam_version", "vslam_launch_count", "vslam_calculate_sigma", "vslam_calculate_num_octaves",
     "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_destroy",
     "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
-    "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris", "vslam_dog_harris", "vslam_finish",
+    "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris", "vslam_dog_harris", "vslam_finish", "vslam_jpeg_info", "vslam_decode_jpeg_gray",
     "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
     # per-function entry points used by the C++17 host layer (visualslam_b200/host)
     "vslam_bgr_to_gray", "vslam_rotate_mat_ccw", "vslam_rotated_window", "vslam_get_rotation_matrix_2d", "vslam_warp_affine", "vslam_gaussian_blur3", "vslam_sobel1", "vslam_harris_response", "vslam_convert_scale_abs", "vslam_nms3", "vslam_nms2",
@@ -113,6 +113,8 @@ def load():
     L.vslam_dog_harris.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(DogParams), C.POINTER(HarrisParams),
                                    vp, i, C.POINTER(i), vp, i, C.POINTER(i), i]
     L.vslam_finish.argtypes = [vp]
+    L.vslam_jpeg_info.argtypes = [vp, vp, sz, C.POINTER(i), C.POINTER(i), C.POINTER(i)]
+    L.vslam_decode_jpeg_gray.argtypes = [vp, C.POINTER(vp), C.POINTER(sz), i, i, i, vp, sz, sz, i]
     L.vslam_upload_frames.argtypes = [vp, vp, i, i, i, sz, sz, C.POINTER(vp), C.POINTER(sz), C.POINTER(sz)]
     L.vslam_gauss_ksize_f32.argtypes = [C.c_double]
     L.vslam_gauss_taps_f32.argtypes = [C.c_double, i, C.POINTER(C.c_float)]
@@ -491,6 +493,26 @@ class Context:
         out = np.empty((window, window), np.uint8)
         self._chk(load().vslam_rotated_window(self.h, a.ctypes.data, a.shape[0], a.shape[1], a.shape[1], int(center[0]), int(center[1]),
                                               int(window), float(cos_sin[0]), float(cos_sin[1]), out.ctypes.data, window))
+        return out
+
+    def decode_jpeg_gray(self, streams, out=None):
+        """JPEG byte strings (equal sizes) -> grey frames: numpy uint8 [n, h, w], or into `out`, a torch cuda uint8 tensor [n, h, w]
+        that the detectors take directly (vslam_decode_jpeg_gray: nvJPEG + the bit-exact BGR2GRAY kernel)."""
+        bufs = [np.frombuffer(bytes(s), np.uint8) for s in streams]
+        n = len(bufs)
+        r, c, ch = C.c_int(), C.c_int(), C.c_int()
+        self._chk(load().vslam_jpeg_info(self.h, bufs[0].ctypes.data, bufs[0].size, C.byref(r), C.byref(c), C.byref(ch)))
+        h, w = r.value, c.value
+        ptrs = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        lens = (C.c_size_t * n)(*[b.size for b in bufs])
+        if out is None:
+            res = np.empty((n, h, w), np.uint8)
+            self._chk(load().vslam_decode_jpeg_gray(self.h, ptrs, lens, n, h, w, res.ctypes.data, w, h * w, HOST))
+            return res
+        assert tuple(out.shape) == (n, h, w) and out.is_contiguous()
+        dev = self._torch_in(out)
+        self._chk(load().vslam_decode_jpeg_gray(self.h, ptrs, lens, n, h, w, out.data_ptr(), w, h * w, DEVICE))
+        self._torch_out(dev)
         return out
 
     def warp_affine(self, img, m, dsize):

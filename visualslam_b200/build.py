@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libvslam_b200.so")
-SOURCES = ["capi.cu", "taps.cu", "pyramid.cu", "fused.cu", "fused_mma.cu", "fused_umma.cu", "detect.cu", "harris.cu", "compaction.cu", "stages.cu", "descriptor.cu", "noalloc.cu"]
+SOURCES = ["capi.cu", "taps.cu", "pyramid.cu", "fused.cu", "fused_mma.cu", "fused_umma.cu", "detect.cu", "harris.cu", "compaction.cu", "stages.cu", "descriptor.cu", "noalloc.cu", "jpeg.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",
          "-Xcompiler", "-fPIC,-fvisibility=hidden,-O2", "-cudart", "static", "-Xptxas", "-v"] + os.environ.get("VSLAM_NVCC_EXTRA", "").split()
@@ -46,7 +46,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if verbose:
         print("\n".join(log))
     subprocess.check_call([NVCC, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a",
-                           "-o", OUT] + objs + ["-Xcompiler", "-fPIC"])
+                           "-o", OUT] + objs + ["-Xcompiler", "-fPIC", "-ldl"])
     return OUT
 
 

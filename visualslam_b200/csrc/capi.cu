@@ -116,6 +116,7 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     for (cudaEvent_t e : ctx->up_ev2) cudaEventDestroy(e);
     for (auto &d : ctx->defer) if (d.ev) cudaEventDestroy(d.ev);
     for (cudaEvent_t e : ctx->slot_done) if (e) cudaEventDestroy(e);
+    jpeg_release(ctx);
     if (ctx->up_start) cudaEventDestroy(ctx->up_start);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (cudaEvent_t e : ctx->down_ev) cudaEventDestroy(e);

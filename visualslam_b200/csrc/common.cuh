@@ -62,6 +62,9 @@ struct vslam_ctx {
     } defer[2];
     int defer_next = 0;
     vslam::DevBuf defer_kp[2], defer_co[2];
+    // JPEG ingest (jpeg.cu): nvJPEG handle + decoder state (opaque here), device staging of the decoded BGR frames
+    void *jpeg_handle = nullptr, *jpeg_state = nullptr;
+    vslam::DevBuf jpeg_bgr;
     // throughput-path workspace: one frame's pyramid, reused
     vslam::DevBuf ingest;          // aligned copy of the input frame(s)
     vslam::DevBuf ws_maps;         // octave bases of a chunk of frames (or all planes of one frame)
@@ -176,6 +179,9 @@ static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 constexpr int kMaxKsize = 255;              // radius <= 127
 int host_gauss_ksize(double sigma);
 int host_gauss_taps(double sigma, int n, int32_t *taps);
+
+// ---- JPEG ingest (jpeg.cu): releases a context's nvJPEG handle, decoder state and staging
+void jpeg_release(vslam_ctx *ctx);
 
 // ---- segment-ordered compaction (compaction.cu) -------------------------------------------------------------
 int seg_prepare(vslam_ctx *ctx, size_t n_segments, size_t entry_bytes, size_t entries);

@@ -113,8 +113,10 @@ typedef enum vslam_map_kind {
  * context on the caller's stream with vslam_ctx_create_on_stream, which orders everything with the caller's own work.
  * The GaussPyramid materialise mask (vslam_pyramid_params.materialise, VSLAM_MATERIALISE_*) makes the chosen fp32 gradient
  * maps of every level resident at build time; maps outside the mask are formed on demand by vslam_pyramid_get.
- * Kernel widths: the 8U Gaussian kernels of an octave must not exceed 247 taps (sigma <= ~41): with sigma0 = 1.6 that is
- * four octaves; a fifth octave (vslam_calculate_num_octaves on images whose short side is >= 512) returns VSLAM_E_INVALID. */
+ * Kernel widths: octaves whose 8U Gaussian kernels exceed 247 taps (sigma > ~41: the fifth octave and beyond at sigma0 = 1.6,
+ * i.e. vslam_calculate_num_octaves on images whose short side is >= 512) run on an exact but slow global-memory path; they are tiny,
+ * so a pyramid that has one is built frame by frame (vslam_dog_keypoints / vslam_dog_harris fall back to materialising each frame;
+ * VSLAM_DEFER is refused).  Four octaves -- what ./DoG uses (Diff_of_Gauss.cpp:742) -- stay on the fused kernels. */
 VSLAM_API int vslam_ctx_create(int device, vslam_ctx **out);
 /* Same, but work is enqueued on a caller-owned CUDA stream (cudaStream_t / CUstream passed as void*). */
 VSLAM_API int vslam_ctx_create_on_stream(int device, void *cuda_stream, vslam_ctx **out);

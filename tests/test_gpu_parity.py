@@ -728,3 +728,33 @@ def test_jpeg_ingest_decodes_to_grey_frames(ctx, images):
     assert np.array_equal(dev.cpu().numpy(), got)
     a, b = ctx.dog_keypoints(dev), ctx.dog_keypoints(got)
     assert a["counts"] == b["counts"] and np.array_equal(a["keypoints"], b["keypoints"]) and sum(a["counts"]) > 100
+
+
+def test_wide_kernel_octaves_match_oracle(ctx, images):
+    """Octaves whose Gaussian kernels exceed 247 taps (octave 4 and beyond at sigma0 = 1.6: the reference's two-argument
+    GaussPyramid(img, sigma) with calculateNumOctaves, GaussPyramid.cpp:150-152) run on the exact global-memory path: every map and
+    the keypoint lists equal the oracle's, through the pyramid API and through the throughput entry points."""
+    img = image_for(images, "building", "cvt")                       # 600 x 868: floor(log2(600)) - 4 = 5 octaves, kernels up to 489 taps
+    no = vs.load().vslam_calculate_num_octaves(*img.shape)
+    assert no == 5
+    pyr = ctx.build_pyramid(img, 0, 1.6)                            # num_octaves <= 0: the reference's own count
+    assert pyr.num_octaves == 5
+    opyr = O.build_pyramid(img, 5, 1.6)
+    for o in range(5):
+        for l in range(6):
+            assert np.array_equal(pyr.get(vs.MAP_GAUSS, o, l), opyr["gauss"][o][l]), (o, l)
+        for l in range(5):
+            assert np.array_equal(pyr.get(vs.MAP_DOG, o, l), opyr["dog"][o][l]), (o, l)
+    want = O.dog_keypoints(img, num_octaves=5)[0]
+    got = kp_array(ctx.dog_detect(pyr)["keypoints"])
+    assert np.array_equal(got, want) and (want[:, 4] == 4).sum() >= 0
+    assert np.array_equal(kp_array(ctx.dog_keypoints(img, num_octaves=5)["keypoints"]), want)          # throughput entry point
+    both = ctx.dog_harris(np.stack([img, img[::-1].copy()], 0), num_octaves=5)
+    assert np.array_equal(kp_array(both["keypoints"][:both["kp_counts"][0]]), want)
+    big = synth.frame(2, 1080, 1920)                                 # six octaves, kernels up to 977 taps on a 68 x 120 octave
+    p6 = ctx.build_pyramid(big, 0, 1.6)
+    assert p6.num_octaves == 6
+    o6 = O.build_pyramid(big, 6, 1.6)
+    for o in (4, 5):
+        for l in range(6):
+            assert np.array_equal(p6.get(vs.MAP_GAUSS, o, l), o6["gauss"][o][l]), (o, l)

@@ -106,7 +106,7 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf *bufs[] = {&ctx->seg_off, &ctx->seg_cnt, &ctx->seg_dst, &ctx->seg_partial, &ctx->staging, &ctx->counters, &ctx->stage_counts,
-                      &ctx->ingest, &ctx->ingest2, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev, &ctx->alt_seg_off, &ctx->alt_seg_cnt, &ctx->alt_seg_dst,
+                      &ctx->ingest, &ctx->ingest2, &ctx->wide_ws, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev, &ctx->alt_seg_off, &ctx->alt_seg_cnt, &ctx->alt_seg_dst,
                       &ctx->alt_seg_partial, &ctx->alt_staging, &ctx->alt_counters, &ctx->alt_out_dev, &ctx->defer_kp[0], &ctx->defer_kp[1],
                       &ctx->defer_co[0], &ctx->defer_co[1]};
     for (DevBuf *b : bufs) b->release();
@@ -189,11 +189,12 @@ static int ensure_taps(vslam_ctx *ctx, int num_octaves, double sigma0, int scale
     if (!ctx->h_taps) return VSLAM_E_NOMEM;
     ctx->taps_octaves = 0;
     FusedTaps *h = (FusedTaps *)ctx->h_taps;
+    ctx->any_wide = false;
     for (int o = 0; o < num_octaves; ++o) {
+        // kernels wider than 247 taps (or a stack that does not fit shared memory): the exact global-memory path takes the octave
         const int rc = build_fused_taps(sigma0, scale_samples, o, &h[o]);
-        if (rc) VS_FAIL(ctx, rc, "octave %d: Gaussian kernel wider than %d taps is not supported (sigma0=%g)", o, kMaxKsize - 8, sigma0);
-        if (fused_smem_bytes(h[o]) > 223 * 1024)
-            VS_FAIL(ctx, VSLAM_E_INVALID, "octave %d: the Gaussian stack needs %zu bytes of shared memory (sigma0=%g)", o, fused_smem_bytes(h[o]), sigma0);
+        ctx->wide_octave[o] = rc != 0 || fused_smem_bytes(h[o]) > 223 * 1024;
+        ctx->any_wide = ctx->any_wide || ctx->wide_octave[o];
     }
     ctx->taps_octaves = num_octaves; ctx->taps_sigma0 = sigma0; ctx->taps_scale_samples = scale_samples;
     return VSLAM_OK;
@@ -345,6 +346,24 @@ static int ingest_first(const vslam_ctx *ctx, long long fb) {
     return (int)(ctx->up_chunks > 1 && fb > 2LL * ctx->up_chunk ? 2LL * ctx->up_chunk : fb);
 }
 
+// an octave on the exact slow path: its taps go up, then launch_octave_wide (pyramid.cu)
+static int build_octave_wide(vslam_ctx *ctx, const OctavePlanes &op, size_t frame_stride, int octave, int n_frames) {
+    std::vector<int> taps;
+    int off[6], ks[6];
+    for (int l = 0; l < 6; ++l) {
+        const double sigma = vslam_calculate_sigma(octave, l, ctx->taps_sigma0, ctx->taps_scale_samples);
+        ks[l] = host_gauss_ksize(sigma);
+        off[l] = (int)taps.size();
+        taps.resize(taps.size() + (size_t)ks[l]);
+        if (host_gauss_taps(sigma, ks[l], taps.data() + off[l])) VS_FAIL(ctx, VSLAM_E_INVALID, "octave %d level %d: no Gaussian kernel for sigma %g", octave, l, sigma);
+    }
+    const size_t tb = round_up(taps.size() * sizeof(int), 256), hb = (size_t)n_frames * op.rows * op.cols * sizeof(u16);
+    if (ctx->wide_ws.reserve(tb + hb)) VS_FAIL(ctx, VSLAM_E_NOMEM, "wide-kernel scratch (%zu bytes)", tb + hb);
+    VS_CUDA(ctx, cudaMemcpyAsync(ctx->wide_ws.p, taps.data(), taps.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));            // `taps` is a local (and pageable) buffer
+    return launch_octave_wide(ctx, op, frame_stride, ctx->wide_ws.as<int>(), off, ks, (u16 *)(ctx->wide_ws.as<u8>() + tb), n_frames);
+}
+
 // rows A-D for n_frames frames into consecutive blocks laid out by Geometry (frame f at block + f * g.frame_bytes):
 // one batched upsample launch, then one fused launch per octave with every map materialised.
 static int build_frames(vslam_ctx *ctx, const Geometry &g, const u8 *frames, int n_frames, int rows, int cols, size_t pitch,
@@ -358,6 +377,10 @@ static int build_frames(vslam_ctx *ctx, const Geometry &g, const u8 *frames, int
         for (int o = 0; o < g.num_octaves; ++o) {
             OctavePlanes op;
             octave_planes(g, blk, o, &op);
+            if (ctx->wide_octave[o]) {
+                VS_TRY(build_octave_wide(ctx, op, g.frame_bytes, o, nf));
+                continue;
+            }
             FusedArgs a;
             memset(&a, 0, sizeof a);
             a.taps = h[o];
@@ -795,9 +818,10 @@ int vslam_dog_keypoints(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
         d_out = ctx->out_dev.as<vslam_keypoint>();
     }
     ListDrain drain;
-    if (dp.window == 3) {
+    if (dp.window == 3 && !ctx->any_wide) {
         VS_TRY(dog_keypoints_fused(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, dp, d_out, capacity, &drain, out, out_space));
     } else {
+        // (also: pyramids with an octave on the exact slow path, i.e. kernels wider than 247 taps)
         // other grid strides: materialise one frame at a time and run the stand-alone detector (detect.cu)
         if (ctx->ws_maps.reserve(g.frame_bytes)) VS_FAIL(ctx, VSLAM_E_NOMEM, "frame workspace (%zu bytes)", g.frame_bytes);
         int seg_base[16];
@@ -1024,8 +1048,12 @@ int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int ro
     if (defer && kp_space != VSLAM_HOST) VS_FAIL(ctx, VSLAM_E_INVALID, "VSLAM_DEFER goes with host lists (device lists are never waited for)");
     if (defer && (!kp_counts || !co_counts || !ctx->pinned)) VS_FAIL(ctx, VSLAM_E_INVALID, "VSLAM_DEFER needs both count arrays");
     const size_t h_spf = (size_t)(rows > 0 ? rows : 1) * harris_strips(cols > 0 ? cols : 1);
-    if (dp.window != 3 || (size_t)n_frames > ((size_t)1 << 30) / h_spf || n_frames > 32768) {
-        if (defer) VS_FAIL(ctx, VSLAM_E_INVALID, "VSLAM_DEFER: window 3 and at most 32768 frames per call");
+    Geometry g;
+    int no; double s0;
+    VS_TRY(make_geometry(ctx, rows, cols, pparams, &g, &no, &s0));
+    VS_TRY(ensure_taps(ctx, no, s0, 3));
+    if (dp.window != 3 || ctx->any_wide || (size_t)n_frames > ((size_t)1 << 30) / h_spf || n_frames > 32768) {
+        if (defer) VS_FAIL(ctx, VSLAM_E_INVALID, "VSLAM_DEFER: window 3, kernels of at most 247 taps and at most 32768 frames per call");
         // shapes the interleaved loop does not take: the two calls one after the other (same results)
         const int rk = vslam_dog_keypoints(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, pparams, dparams, keypoints, kp_capacity,
                                            kp_space, kp_counts);
@@ -1034,10 +1062,6 @@ int vslam_dog_harris(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int ro
                                     co_capacity, out_space, co_counts);
         return rk != VSLAM_OK ? rk : rc;
     }
-    Geometry g;
-    int no; double s0;
-    VS_TRY(make_geometry(ctx, rows, cols, pparams, &g, &no, &s0));
-    VS_TRY(ensure_taps(ctx, no, s0, 3));
     const u8 *d_frames; size_t d_pitch, d_stride;
     VS_TRY(ingest_frames(ctx, frames, n_frames, rows, cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
     VS_TRY(reserve_counters(ctx, n_frames));

@@ -101,6 +101,9 @@ struct vslam_ctx {
     // cached tap tables of the fused octave kernel (passed by value as kernel parameters)
     int taps_octaves = 0; double taps_sigma0 = 0; int taps_scale_samples = 0;
     void *h_taps = nullptr;        // FusedTaps[taps_octaves], malloc'd
+    bool wide_octave[16] = {false};   // octaves whose kernels the fused kernels do not take: the exact global-memory path (pyramid.cu)
+    bool any_wide = false;
+    vslam::DevBuf wide_ws;         // its scratch: the taps of an octave and the 8.8 horizontal sums
     // optional per-kernel CUDA-event timing (vslam_profile): events bracket every launch on ctx->stream
     bool profiling = false;
     std::vector<cudaEvent_t> ev_pool;

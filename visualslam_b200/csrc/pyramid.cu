@@ -205,4 +205,73 @@ int launch_gradients(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pit
     return VSLAM_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Exact slow path for the octaves whose 8U Gaussian kernels the fused kernels do not take (more than 247 taps: octave 4 and
+// beyond at sigma0 = 1.6, i.e. the reference's two-argument GaussPyramid(img, sigma) on anything larger than 511 pixels on its
+// short side).  Such octaves are tiny (at most 1/256 of the input's pixels), so this is OpenCV's arithmetic in its plainest form:
+// a horizontal pass u8 x 8-bit taps -> 8.8 sums (u16), a vertical pass 8.8 x taps -> 16.16 and one rounding, reflect-101 with
+// repeated bouncing (the kernels are several times wider than the image), saturating DoG, nearest decimation of level 3.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) wide_h_k(const u8 *__restrict__ base, int rows, int cols, size_t pitch, size_t stride,
+                                                const int *__restrict__ taps, int n, u16 *__restrict__ out) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, f = blockIdx.z;
+    if (x >= cols) return;
+    const u8 *r = base + (size_t)f * stride + (size_t)y * pitch;
+    const int h = n / 2;
+    int acc = 0;
+    for (int i = 0; i < n; ++i) acc += taps[i] * (int)r[refl101(x + i - h, cols)];
+    out[((size_t)f * rows + y) * cols + x] = (u16)acc;                     // <= 255 * 256
+}
+__global__ void __launch_bounds__(128) wide_v_k(const u16 *__restrict__ hsum, int rows, int cols, const int *__restrict__ taps, int n,
+                                                u8 *__restrict__ dst, size_t dpitch, size_t dstride) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, f = blockIdx.z;
+    if (x >= cols) return;
+    const u16 *p = hsum + (size_t)f * rows * cols + x;
+    const int h = n / 2;
+    unsigned acc = 0;
+    for (int i = 0; i < n; ++i) acc += (unsigned)taps[i] * (unsigned)p[(size_t)refl101(y + i - h, rows) * cols];
+    dst[(size_t)f * dstride + (size_t)y * dpitch + x] = (u8)((acc + 32768u) >> 16);
+}
+// out = saturate(cur - prev)  (GaussPyramid.cpp:197)
+__global__ void __launch_bounds__(128) wide_dog_k(const u8 *__restrict__ cur, const u8 *__restrict__ prev, int rows, int cols, size_t pitch, size_t stride,
+                                                  u8 *__restrict__ out) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= cols) return;
+    const size_t o = (size_t)blockIdx.z * stride + (size_t)y * pitch + x;
+    const int d = (int)cur[o] - (int)prev[o];
+    out[o] = (u8)(d > 0 ? d : 0);
+}
+// resize(level 3, 0.5, INTER_NEAREST)  (GaussPyramid.cpp:123-126)
+__global__ void __launch_bounds__(128) wide_decimate_k(const u8 *__restrict__ src, int srows, int scols, size_t spitch, size_t sstride, u8 *__restrict__ dst,
+                                                       int drows, int dcols, size_t dpitch, size_t dstride) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= dcols || y >= drows) return;
+    const int sx = min(2 * x, scols - 1), sy = min(2 * y, srows - 1);      // the rounded-up half size reaches one past the last even index
+    dst[(size_t)blockIdx.z * dstride + (size_t)y * dpitch + x] = src[(size_t)blockIdx.z * sstride + (size_t)sy * spitch + sx];
+}
+
+int launch_octave_wide(vslam_ctx *ctx, const OctavePlanes &op, size_t frame_stride, const int *d_taps, const int *tap_off, const int *ksize,
+                       u16 *d_hsum, int n_frames) {
+    if (n_frames <= 0 || n_frames > 65535 || op.rows > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "wide octave: %d frames of %d rows", n_frames, op.rows);
+    const dim3 grid((op.cols + 127) / 128, op.rows, n_frames);
+    KernelSpan span(ctx, VSLAM_K_FUSED);
+    for (int l = 0; l < 6; ++l) {
+        wide_h_k<<<grid, 128, 0, ctx->stream>>>(op.base, op.rows, op.cols, op.pitch, frame_stride, d_taps + tap_off[l], ksize[l], d_hsum);
+        VS_LAUNCH_CHECK(ctx);
+        wide_v_k<<<grid, 128, 0, ctx->stream>>>(d_hsum, op.rows, op.cols, d_taps + tap_off[l], ksize[l], op.gauss[l], op.pitch, frame_stride);
+        VS_LAUNCH_CHECK(ctx);
+        if (l >= 1) {
+            wide_dog_k<<<grid, 128, 0, ctx->stream>>>(op.gauss[l], op.gauss[l - 1], op.rows, op.cols, op.pitch, frame_stride, op.dog[l - 1]);
+            VS_LAUNCH_CHECK(ctx);
+        }
+    }
+    if (op.next_base) {
+        const dim3 g2((op.next_cols + 127) / 128, op.next_rows, n_frames);
+        wide_decimate_k<<<g2, 128, 0, ctx->stream>>>(op.gauss[3], op.rows, op.cols, op.pitch, frame_stride, op.next_base, op.next_rows, op.next_cols, op.next_pitch,
+                                                     frame_stride);
+        VS_LAUNCH_CHECK(ctx);
+    }
+    return VSLAM_OK;
+}
+
 }  // namespace vslam

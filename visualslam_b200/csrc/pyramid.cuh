@@ -37,4 +37,9 @@ int launch_gradients(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pit
 int launch_gradients_all(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pitch, size_t gplane, size_t gstride, float *out,
                          size_t oplane, size_t ostride, unsigned mask, int n_frames);
 
+// exact global-memory path for octaves whose kernels are wider than the fused kernels take (pyramid.cu): every map of the octave for
+// n_frames frames; d_taps: device ints, level l at d_taps + tap_off[l], ksize[l] taps; d_hsum: n_frames * rows * cols u16 of scratch
+int launch_octave_wide(vslam_ctx *ctx, const OctavePlanes &op, size_t frame_stride, const int *d_taps, const int *tap_off, const int *ksize,
+                       u16 *d_hsum, int n_frames);
+
 }  // namespace vslam

@@ -2,6 +2,7 @@
 // lines (octave / level counts, octave sizes, the three sigmas, the sigma count) and then checks them (exit code 1 on
 // a mismatch, which the reference leaves to the reader's eye).
 //   usage: Pyramid_Test [image.pgm]                                (default image: ../images/building.pgm)
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <iostream>
@@ -56,6 +57,15 @@ int main(int argc, char **argv) {
         bool threw = false;
         try { pyramid.octaveBlur(7); } catch (const std::out_of_range &) { threw = true; }
         bad += !threw;
+        // 4. the two-argument constructor (GaussPyramid.hpp:21): calculateNumOctaves = floor(log2(min side)) - 4 (GaussPyramid.cpp:150-152);
+        //    octaves beyond the fourth have kernels wider than 247 taps and run on the exact global-memory path
+        {
+            GaussPyramid autoPyr{img, sigma};
+            const int expect = (int)std::floor(std::log2((double)std::min(img.rows, img.cols))) - 4;
+            cout << "Number of octaves of GaussPyramid(img, sigma): " << autoPyr.getNumOctaves() << endl;
+            bad += autoPyr.getNumOctaves() != expect || (int)autoPyr.pyramidGauss().size() != expect;
+            if (expect > 4) bad += autoPyr.octaveBlur(expect - 1).size() != 6 || autoPyr.octaveBlur(expect - 1).at(5).empty();
+        }
         cout << (bad ? "FAILED" : "OK") << endl;
         return bad ? 1 : 0;
     } catch (const std::exception &e) {

@@ -1498,45 +1498,119 @@ int vslam_sift_descriptors(vslam_ctx *ctx, const vslam_pyramid *pyr, int frame, 
     return run_sift(ctx, pyr, frame, octave, oriented, nullptr, n, descriptors, valid);
 }
 
+// Every frame and octave of a pyramid: orientation histograms in width classes, the expansion of their masks ON THE DEVICE (count,
+// scan, scatter: the lists do not visit the host between the two kernels), SIFT in four launches whose descriptors leave on the
+// drain stream while the next launch computes.  One small synchronisation in the middle (the number of oriented points sizes the grid).
 int vslam_describe_keypoints(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_keypoint *keypoints, const int *counts, vslam_keypoint *oriented,
                              int capacity, int *oriented_counts, float *descriptors, uint8_t *valid) {
     if (!ctx || !pyr || !counts || !oriented_counts || capacity < 0 || (capacity > 0 && (!oriented || !descriptors || !valid))) return VSLAM_E_INVALID;
-    long long n = 0;
+    long long n64 = 0;
     for (int f = 0; f < pyr->n_frames; ++f) {
         if (counts[f] < 0) VS_FAIL(ctx, VSLAM_E_INVALID, "negative count for frame %d", f);
-        n += counts[f];
+        n64 += counts[f];
         oriented_counts[f] = 0;
     }
-    if (n > 0x7fffffff / 36) VS_FAIL(ctx, VSLAM_E_INVALID, "too many keypoints for one call (%lld)", n);
-    if (n == 0) return VSLAM_OK;
+    if (n64 > 0x7fffffff / 36) VS_FAIL(ctx, VSLAM_E_INVALID, "too many keypoints for one call (%lld)", n64);
+    if (n64 == 0) return VSLAM_OK;
     if (!keypoints) return VSLAM_E_INVALID;
     VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int n = (int)n64;
     std::vector<int> frame_of((size_t)n);
     {
         long long i = 0;
         for (int f = 0; f < pyr->n_frames; ++f)
             for (int c = 0; c < counts[f]; ++c) frame_of[(size_t)i++] = f;
     }
-    std::vector<unsigned long long> masks;
-    VS_TRY(run_orientations(ctx, pyr, 0, -1, keypoints, frame_of.data(), (int)n, masks, nullptr));
-    // expansion frame by frame: the reference's order inside a frame, frames back to back
-    std::vector<int> oframe;
-    long long m = 0, i0 = 0;
-    for (int f = 0; f < pyr->n_frames; ++f) {
-        const long long got = expand_orientations(keypoints + i0, masks.data() + i0, counts[f], oriented ? oriented + (m < capacity ? m : capacity) : nullptr,
-                                                  m < capacity ? capacity - m : 0);
-        oriented_counts[f] = (int)got;
-        i0 += counts[f];
-        m += got;
+    std::vector<float> h_taps;
+    DescPyr P;
+    int max_r = 0;
+    VS_TRY(desc_pyr(ctx, pyr, 0, -1, keypoints, n, h_taps, P, max_r));
+    // widest kernel first, list order inside one width (counting sort on the radius): the launch classes of run_orientations
+    std::vector<int> order((size_t)n), rad((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        const int o = keypoints[i].octave, l = keypoints[i].level;
+        rad[(size_t)i] = (o >= 0 && o < pyr->num_octaves && l >= 0 && l < 6 ? P.ksize[o][l] : 1) / 2;
     }
-    const long long stored = m < capacity ? m : capacity;
+    std::vector<int> start((size_t)max_r + 2, 0);
+    for (int i = 0; i < n; ++i) ++start[(size_t)(max_r - rad[(size_t)i]) + 1];
+    for (int b2 = 0; b2 <= max_r; ++b2) start[(size_t)b2 + 1] += start[(size_t)b2];
+    const std::vector<int> bucket0(start.begin(), start.end());            // first position of radius max_r - b
+    for (int i = 0; i < n; ++i) order[(size_t)start[(size_t)(max_r - rad[(size_t)i])]++] = i;
+    OrientLut lut;
+    for (int b2 = 0; b2 < 36; ++b2) {                                       // Rotation::cos_sin_of_angle (rotation.cpp:9-17) of bin * 10 degrees
+        const float angle = (float)((double)(float)(10 * b2) * (3.1415926535897932384626433832795 / (double)180.0f));
+        lut.cs[b2] = make_float2((float)cos((double)angle), (float)sin((double)angle));
+    }
+    const size_t cap = (size_t)capacity, nb = (size_t)n / 4096 + 8;
+    const size_t b[14] = {sizeof(vslam_keypoint) * (size_t)n, 8 * (size_t)n, 4 * h_taps.size(), 4 * (size_t)n, 4 * (size_t)n, 4 * (size_t)n + 64,
+                          4 * (size_t)n + 64, 4 * nb, 64, sizeof(vslam_keypoint) * cap, 8 * cap, 4 * cap, 512 * cap, cap};
+    u8 *d[14];
+    VS_TRY(stage_scratch(ctx, b, 14, d));
+    const vslam_keypoint *d_kp = (const vslam_keypoint *)d[0];
+    unsigned long long *d_masks = (unsigned long long *)d[1];
+    const int *d_frame = (const int *)d[3], *d_order = (const int *)d[4];
+    int *d_cnt = (int *)d[5], *d_pos = (int *)d[6], *d_partial = (int *)d[7], *d_total = (int *)d[8];
+    vslam_keypoint *d_ori = (vslam_keypoint *)d[9];
+    float2 *d_cs = (float2 *)d[10];
+    int *d_oframe = (int *)d[11];
+    float *d_desc = (float *)d[12];
+    u8 *d_valid = d[13];
+    H2D(d[0], keypoints, b[0]);
+    H2D(d[2], h_taps.data(), b[2]);
+    H2D(d[3], frame_of.data(), b[3]);
+    H2D(d[4], order.data(), b[4]);
+    P.taps = (const float *)d[2];
+    static const int kClassR[] = {80, 40, 20, 0};                           // class c holds the radii above kClassR[c]
+    for (int c = 0, i0 = 0; c < 4 && i0 < n; ++c) {
+        // keypoints with radius > kClassR[c]: the buckets of radii max_r .. kClassR[c] + 1
+        int i1 = c == 3 || kClassR[c] >= max_r ? (c == 3 ? n : i0) : bucket0[(size_t)(max_r - kClassR[c])];
+        if (i1 < i0) i1 = i0;
+        if (i1 > i0) VS_TRY(launch_orient_hist(ctx, d_kp, d_frame, d_order + i0, i1 - i0, P, rad[(size_t)order[(size_t)i0]], d_masks, nullptr));
+        i0 = i1;
+    }
+    VS_TRY(launch_orient_expand(ctx, d_kp, d_frame, d_masks, n, capacity, lut, d_cnt, d_pos, d_partial, d_total, d_ori, d_cs, d_oframe, 0));
+    int *h_total = (int *)ctx->pinned + 3000;                               // pinned: behind the drain slots (2 x 1024 ints), before the deferred snapshots (16 KB)
+    if (!ctx->pinned) VS_FAIL(ctx, VSLAM_E_NOMEM, "pinned staging");
+    VS_CUDA(ctx, cudaMemcpyAsync(h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));                       // the host vectors above are free from here on
+    const long long m = *h_total;
+    const int stored = (int)(m < capacity ? m : capacity);
+    std::vector<int> h_pos((size_t)n);
     if (stored > 0) {
-        oframe.resize((size_t)stored);
-        long long j = 0;
-        for (int f = 0; f < pyr->n_frames && j < stored; ++f)
-            for (int c = 0; c < oriented_counts[f] && j < stored; ++c) oframe[(size_t)j++] = f;
-        VS_TRY(run_sift(ctx, pyr, 0, -1, oriented, oframe.data(), (int)stored, descriptors, valid));
+        VS_TRY(launch_orient_expand(ctx, d_kp, d_frame, d_masks, n, capacity, lut, d_cnt, d_pos, d_partial, d_total, d_ori, d_cs, d_oframe, 1));
+        if (!ctx->down_stream) VS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking));
+        while (ctx->down_ev.size() < 8) {
+            cudaEvent_t e;
+            VS_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            ctx->down_ev.push_back(e);
+        }
+        VS_CUDA(ctx, cudaEventRecord(ctx->down_ev[0], ctx->stream));
+        VS_CUDA(ctx, cudaStreamWaitEvent(ctx->down_stream, ctx->down_ev[0], 0));
+        VS_CUDA(ctx, cudaMemcpyAsync(oriented, d_ori, sizeof(vslam_keypoint) * (size_t)stored, cudaMemcpyDeviceToHost, ctx->down_stream));
+        const int parts = stored >= 4096 ? 4 : 1;
+        for (int q = 0; q < parts; ++q) {
+            const int i0 = (int)((long long)stored * q / parts), i1 = (int)((long long)stored * (q + 1) / parts);
+            if (i1 <= i0) continue;
+            VS_TRY(launch_sift(ctx, d_ori + i0, d_oframe + i0, d_cs + i0, i1 - i0, P, max_r, d_desc + (size_t)i0 * 128, d_valid + i0));
+            VS_CUDA(ctx, cudaEventRecord(ctx->down_ev[1 + q], ctx->stream));
+            VS_CUDA(ctx, cudaStreamWaitEvent(ctx->down_stream, ctx->down_ev[1 + q], 0));
+            VS_CUDA(ctx, cudaMemcpyAsync(descriptors + (size_t)i0 * 128, d_desc + (size_t)i0 * 128, 512 * (size_t)(i1 - i0), cudaMemcpyDeviceToHost, ctx->down_stream));
+            VS_CUDA(ctx, cudaMemcpyAsync(valid + i0, d_valid + i0, (size_t)(i1 - i0), cudaMemcpyDeviceToHost, ctx->down_stream));
+        }
     }
+    // per-frame counts from the scanned positions (while the SIFT launches run)
+    VS_CUDA(ctx, cudaMemcpyAsync(h_pos.data(), d_pos, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    VS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    {
+        long long i0 = 0;
+        for (int f = 0; f < pyr->n_frames; ++f) {
+            const long long i1 = i0 + counts[f];
+            const long long lo = i0 < n ? h_pos[(size_t)i0] : m, hi = i1 < n ? h_pos[(size_t)i1] : m;
+            oriented_counts[f] = (int)(hi - lo);
+            i0 = i1;
+        }
+    }
+    if (ctx->down_stream) VS_CUDA(ctx, cudaStreamSynchronize(ctx->down_stream));
     return m > capacity ? VSLAM_E_CAPACITY : VSLAM_OK;
 }
 

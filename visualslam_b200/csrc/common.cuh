@@ -183,6 +183,9 @@ constexpr int kMaxKsize = 255;              // radius <= 127
 int host_gauss_ksize(double sigma);
 int host_gauss_taps(double sigma, int n, int32_t *taps);
 
+// exclusive scan of n ints (compaction.cu); partial: ceil(n / 4096) + 4 ints of workspace
+int device_exclusive_scan(vslam_ctx *ctx, const int *cnt, long long n, int *partial, int *dst, int *d_total);
+
 // ---- JPEG ingest (jpeg.cu): releases a context's nvJPEG handle, decoder state and staging
 void jpeg_release(vslam_ctx *ctx);
 

@@ -187,4 +187,18 @@ int seg_finalise(vslam_ctx *ctx, size_t n_segments, int entry_bytes, void *dst, 
     return VSLAM_OK;
 }
 
+// exclusive scan of n ints on the device (the three kernels above): dst[i] = sum of cnt[0 .. i-1], *d_total = the sum.
+// partial: at least ceil(n / 4096) + 4 ints of workspace; cnt / dst 16-byte aligned.
+int device_exclusive_scan(vslam_ctx *ctx, const int *cnt, long long n, int *partial, int *dst, int *d_total) {
+    const int nb = (int)((n + SCAN_ITEMS - 1) / SCAN_ITEMS);
+    VS_CUDA(ctx, cudaMemsetAsync(d_total, 0, sizeof(int), ctx->stream));
+    seg_reduce_k<<<nb, SCAN_T, 0, ctx->stream>>>(cnt, n, partial);
+    VS_LAUNCH_CHECK(ctx);
+    seg_spine_k<<<1, SCAN_T, 0, ctx->stream>>>(partial, nb, d_total);
+    VS_LAUNCH_CHECK(ctx);
+    seg_apply_k<<<nb, SCAN_T, 0, ctx->stream>>>(cnt, n, partial, dst);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
+
 }  // namespace vslam

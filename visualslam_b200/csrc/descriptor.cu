@@ -276,4 +276,41 @@ int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, c
     return VSLAM_OK;
 }
 
+// ---- filterKeypoints :362-368 on the device: one point per histogram bin above 0.8 of the peak, bins in ascending order ----------
+__global__ void __launch_bounds__(256) orient_count_k(const unsigned long long *__restrict__ masks, int n, int *__restrict__ cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) cnt[i] = __popcll(masks[i] & ((1ull << 36) - 1));
+}
+__global__ void __launch_bounds__(256) orient_expand_k(const vslam_keypoint *__restrict__ kp, const int *__restrict__ frame_of,
+                                                       const unsigned long long *__restrict__ masks, const int *__restrict__ pos, int n, int capacity,
+                                                       const OrientLut lut, vslam_keypoint *__restrict__ out, float2 *__restrict__ cs,
+                                                       int *__restrict__ oframe) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const vslam_keypoint k = kp[i];
+    int m = pos[i];
+    for (unsigned long long bits = masks[i] & ((1ull << 36) - 1); bits && m < capacity; bits &= bits - 1, ++m) {
+        const int bin = __ffsll((long long)bits) - 1;
+        vslam_keypoint o;
+        o.row = k.row; o.col = k.col; o.value = bin * 10; o.padding = 0; o.octave = k.octave; o.level = k.level;
+        out[m] = o;
+        cs[m] = lut.cs[bin];
+        oframe[m] = frame_of[i];
+    }
+}
+
+int launch_orient_expand(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const unsigned long long *masks, int n, int capacity,
+                         const OrientLut &lut, int *cnt, int *pos, int *partial, int *d_total, vslam_keypoint *out, float2 *cs, int *oframe,
+                         int phase) {
+    KernelSpan span(ctx, VSLAM_K_DESCRIPTOR);
+    if (phase == 0) {                                             // counts and their exclusive scan; *d_total = number of oriented points
+        orient_count_k<<<(n + 255) / 256, 256, 0, ctx->stream>>>(masks, n, cnt);
+        VS_LAUNCH_CHECK(ctx);
+        return device_exclusive_scan(ctx, cnt, n, partial, pos, d_total);
+    }
+    orient_expand_k<<<(n + 255) / 256, 256, 0, ctx->stream>>>(kp, frame_of, masks, pos, n, capacity, lut, out, cs, oframe);
+    VS_LAUNCH_CHECK(ctx);
+    return VSLAM_OK;
+}
+
 }  // namespace vslam

@@ -26,4 +26,11 @@ int launch_orient_hist(vslam_ctx *ctx, const vslam_keypoint *kp, const int *fram
                        unsigned long long *masks, float *histos);
 int launch_sift(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const float2 *cs, int n, const DescPyr &P, int max_r, float *desc,
                 u8 *valid);
+// filterKeypoints' expansion of the orientation masks on the device (:362-368).  phase 0: per-keypoint counts + exclusive scan
+// (pos, *d_total); phase 1: oriented points, their cos / sin (lut[bin], computed on the host like Rotation::cos_sin_of_angle) and
+// frames, at most `capacity` of them.  partial: ceil(n / 4096) + 4 ints.
+struct OrientLut { float2 cs[36]; };
+int launch_orient_expand(vslam_ctx *ctx, const vslam_keypoint *kp, const int *frame_of, const unsigned long long *masks, int n, int capacity,
+                         const OrientLut &lut, int *cnt, int *pos, int *partial, int *d_total, vslam_keypoint *out, float2 *cs, int *oframe,
+                         int phase);
 }  // namespace vslam

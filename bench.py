@@ -130,7 +130,10 @@ def cpu_reference_frames(frames):
             nc += len(O.harris(img)["corners"])
     dt = time.perf_counter() - t0
     cores = (cv2.getNumThreads() if have_cv2 else 1)
-    kind = "port"   # the reference cannot be compiled here (needs OpenCV C++); cv2 runs its OpenCV calls, C restates its loops
+    # kind "port": cv2 (the real, threaded OpenCV) runs the reference's OpenCV calls and plain C restates its loops.  oracle/_ref -- the
+    # reference's own translation units -- exists since round 2, but it is compiled against a stand-in for OpenCV whose imgproc is the
+    # single-threaded C oracle: right for parity, far slower than OpenCV, so timing it would flatter the GPU.
+    kind = "port"
     return dt, kind, cores, nk, nc
 
 

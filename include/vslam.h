@@ -153,6 +153,11 @@ VSLAM_API int vslam_gauss_taps(double sigma, int ksize, int32_t *taps);
 VSLAM_API int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols,
                                   size_t pitch, size_t frame_stride, int space,
                                   const vslam_pyramid_params *params, vslam_pyramid **out);
+/* The same pyramid object on a new batch of frames of the same number, size and parameters: every map is rebuilt in place and
+ * nothing is allocated (a stream of batches otherwise pays a multi-GB cudaMalloc / cudaFree per batch: 7.6 of 14.7 ms per eight
+ * 1080p frames with every gradient map resident).  Maps handed out by vslam_pyramid_device_map keep their addresses. */
+VSLAM_API int vslam_pyramid_rebuild(vslam_ctx *ctx, vslam_pyramid *pyr, const uint8_t *frames, size_t pitch, size_t frame_stride,
+                                    int space);
 VSLAM_API void vslam_pyramid_destroy(vslam_pyramid *pyr);
 VSLAM_API int vslam_pyramid_num_octaves(const vslam_pyramid *pyr);
 VSLAM_API int vslam_pyramid_num_frames(const vslam_pyramid *pyr);

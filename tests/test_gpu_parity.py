@@ -2,6 +2,7 @@
 inputs, and against the committed golden fixtures.  Integer / byte / index work is compared bit-exactly; the two fp32
 maps that are not hot-path decisions (magnitude, phase) carry a stated tolerance."""
 import hashlib
+from ctypes import c_size_t as C_size_t
 
 import numpy as np
 import pytest
@@ -758,3 +759,22 @@ def test_wide_kernel_octaves_match_oracle(ctx, images):
     for o in (4, 5):
         for l in range(6):
             assert np.array_equal(p6.get(vs.MAP_GAUSS, o, l), o6["gauss"][o][l]), (o, l)
+
+
+def test_pyramid_rebuild_in_place(ctx):
+    """vslam_pyramid_rebuild: the same pyramid object on new frames of the same shape gives the maps, gradient maps and keypoints of
+    a fresh build, at the same device addresses."""
+    a = np.stack([synth.frame(i, 135, 240) for i in (0, 5)], 0)
+    b = np.stack([synth.frame(i, 135, 240) for i in (6, 3)], 0)
+    pyr = ctx.build_pyramid(a, 4, 1.6, materialise=0x78)
+    sz = C_size_t()
+    addr = vs.load().vslam_pyramid_device_map(pyr.h, 1, vs.MAP_GAUSS, 2, 3, sz)
+    ctx.rebuild_pyramid(pyr, b)
+    assert vs.load().vslam_pyramid_device_map(pyr.h, 1, vs.MAP_GAUSS, 2, 3, sz) == addr
+    fresh = ctx.build_pyramid(b, 4, 1.6, materialise=0x78)
+    for f in (0, 1):
+        for o in range(4):
+            for kind, levels in ((vs.MAP_GAUSS, 6), (vs.MAP_DOG, 5), (vs.MAP_GRADX, 6), (vs.MAP_ORIENT, 6)):
+                for l in range(levels):
+                    assert np.array_equal(pyr.get(kind, o, l, f), fresh.get(kind, o, l, f)), (f, o, kind, l)
+    assert np.array_equal(ctx.dog_detect(pyr)["keypoints"], ctx.dog_detect(fresh)["keypoints"])

@@ -54,7 +54,7 @@ class VslamError(RuntimeError):
 EXPORTS = [
     "vslam_ctx_create", "vslam_ctx_create_on_stream", "vslam_ctx_destroy", "vslam_last_error", "vslam_sync",
     "vslam_version", "vslam_launch_count", "vslam_calculate_sigma", "vslam_calculate_num_octaves",
-    "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_destroy",
+    "vslam_gauss_ksize", "vslam_gauss_taps", "vslam_pyramid_build", "vslam_pyramid_rebuild", "vslam_pyramid_destroy",
     "vslam_pyramid_num_octaves", "vslam_pyramid_num_frames", "vslam_pyramid_octave_size", "vslam_pyramid_sigma",
     "vslam_pyramid_get", "vslam_pyramid_device_map", "vslam_dog_detect", "vslam_dog_keypoints", "vslam_harris", "vslam_dog_harris", "vslam_finish", "vslam_jpeg_info", "vslam_decode_jpeg_gray",
     "vslam_profile", "vslam_profile_read", "vslam_upload_frames",
@@ -99,6 +99,7 @@ def load():
     L.vslam_get_rotation_matrix_2d.argtypes = [C.c_float, C.c_float, C.c_double, C.c_double, C.POINTER(C.c_double)]
     L.vslam_warp_affine.argtypes = [vp, vp, i, i, sz, C.POINTER(C.c_double), vp, i, i, sz]
     L.vslam_pyramid_build.argtypes = [vp, vp, i, i, i, sz, sz, i, C.POINTER(PyramidParams), C.POINTER(vp)]
+    L.vslam_pyramid_rebuild.argtypes = [vp, vp, vp, sz, sz, i]
     L.vslam_pyramid_destroy.argtypes = [vp]; L.vslam_pyramid_destroy.restype = None
     L.vslam_pyramid_num_octaves.argtypes = [vp]
     L.vslam_pyramid_num_frames.argtypes = [vp]
@@ -333,6 +334,15 @@ class Context:
         self._chk(load().vslam_pyramid_build(self.h, ptr, n, h, w, pitch, stride, space, C.byref(pp), C.byref(ph)))
         self.sync()
         return Pyramid(self, ph)
+
+    def rebuild_pyramid(self, pyr, frames):
+        """vslam_pyramid_rebuild: the same pyramid object on a new batch of the same shape, in place, no allocation."""
+        dev = self._torch_in(frames)
+        ptr, n, h, w, pitch, stride, space, keep = _frames_arg(frames)
+        assert n == pyr.n_frames
+        self._chk(load().vslam_pyramid_rebuild(self.h, pyr.h, ptr, pitch, stride, space))
+        self._torch_out(dev)
+        return pyr
 
     def dog_detect(self, pyr, window=3, contrast_thr=0.03, edge_r=10.0, capacity=1 << 20, stage_counts=True):
         dp = DogParams(window, contrast_thr, edge_r)

@@ -464,6 +464,25 @@ static int reserve_counters(vslam_ctx *ctx, int n_frames) {
 
 extern "C" {
 
+// storage (grow-only: a rebuild allocates nothing) and every map of the pyramid's frames
+static int pyramid_fill(vslam_ctx *ctx, vslam_pyramid *p, const Geometry &g, const u8 *d_frames, size_t d_pitch, size_t d_stride) {
+    const int n_frames = p->n_frames, no = p->num_octaves;
+    if (p->maps.reserve(g.frame_bytes * (size_t)n_frames)) VS_FAIL(ctx, VSLAM_E_NOMEM, "pyramid of %d frames needs %zu bytes", n_frames, g.frame_bytes * (size_t)n_frames);
+    VS_TRY(build_frames(ctx, g, d_frames, n_frames, p->rows, p->cols, d_pitch, d_stride, p->maps.as<u8>()));
+    // the maps processGradients leaves behind (GaussPyramid.cpp:65-104), when the caller wants them resident
+    const unsigned gmask = (p->materialise >> VSLAM_MAP_GRADX) & 15u;
+    if (gmask) {
+        size_t fl = 0;
+        for (int o = 0; o < no; ++o) { p->goff[o] = fl; fl += (size_t)24 * g.orows[o] * g.ocols[o]; }
+        p->grad_frame_floats = fl;
+        if (p->grads.reserve(fl * 4 * (size_t)n_frames)) VS_FAIL(ctx, VSLAM_E_NOMEM, "gradient maps of %d frames need %zu bytes", n_frames, fl * 4 * (size_t)n_frames);
+        for (int o = 0; o < no; ++o)
+            VS_TRY(launch_gradients_all(ctx, p->plane(0, o, 1), g.orows[o], g.ocols[o], g.opitch[o], g.oplane[o], g.frame_bytes,
+                                        p->grads.as<float>() + p->goff[o], (size_t)g.orows[o] * g.ocols[o], fl, gmask, n_frames));
+    }
+    return VSLAM_OK;
+}
+
 int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int rows, int cols, size_t pitch,
                         size_t frame_stride, int space, const vslam_pyramid_params *params, vslam_pyramid **out) {
     if (!ctx || !out) return VSLAM_E_INVALID;
@@ -485,32 +504,25 @@ int vslam_pyramid_build(vslam_ctx *ctx, const uint8_t *frames, int n_frames, int
         for (int l = 0; l < 6; ++l) p->sigma[o][l] = vslam_calculate_sigma(o, l, s0, 3);
     }
     p->frame_bytes = g.frame_bytes;
-    if (p->maps.reserve(g.frame_bytes * (size_t)n_frames)) {
-        delete p;
-        VS_FAIL(ctx, VSLAM_E_NOMEM, "pyramid of %d frames needs %zu bytes", n_frames, g.frame_bytes * (size_t)n_frames);
-    }
-    {
-        const int rc = build_frames(ctx, g, d_frames, n_frames, rows, cols, d_pitch, d_stride, p->maps.as<u8>());
-        if (rc) { cudaStreamSynchronize(ctx->stream); p->maps.release(); delete p; return rc; }
-    }
-    // the maps processGradients leaves behind (GaussPyramid.cpp:65-104), when the caller wants them resident
-    const unsigned gmask = (p->materialise >> VSLAM_MAP_GRADX) & 15u;
-    if (gmask) {
-        size_t fl = 0;
-        for (int o = 0; o < no; ++o) { p->goff[o] = fl; fl += (size_t)24 * g.orows[o] * g.ocols[o]; }
-        p->grad_frame_floats = fl;
-        if (p->grads.reserve(fl * 4 * (size_t)n_frames)) {
-            cudaStreamSynchronize(ctx->stream); p->maps.release(); delete p;
-            VS_FAIL(ctx, VSLAM_E_NOMEM, "gradient maps of %d frames need %zu bytes", n_frames, fl * 4 * (size_t)n_frames);
-        }
-        for (int o = 0; o < no; ++o) {
-            const int rc = launch_gradients_all(ctx, p->plane(0, o, 1), g.orows[o], g.ocols[o], g.opitch[o], g.oplane[o], g.frame_bytes,
-                                                p->grads.as<float>() + p->goff[o], (size_t)g.orows[o] * g.ocols[o], fl, gmask, n_frames);
-            if (rc) { cudaStreamSynchronize(ctx->stream); p->maps.release(); p->grads.release(); delete p; return rc; }
-        }
-    }
+    const int rc = pyramid_fill(ctx, p, g, d_frames, d_pitch, d_stride);
+    if (rc) { cudaStreamSynchronize(ctx->stream); p->maps.release(); p->grads.release(); delete p; return rc; }
     *out = p;
     return VSLAM_OK;
+}
+
+int vslam_pyramid_rebuild(vslam_ctx *ctx, vslam_pyramid *pyr, const uint8_t *frames, size_t pitch, size_t frame_stride, int space) {
+    if (!ctx || !pyr) return VSLAM_E_INVALID;
+    VS_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (pyr->device != ctx->device) VS_FAIL(ctx, VSLAM_E_INVALID, "pyramid lives on device %d, context on %d", pyr->device, ctx->device);
+    vslam_pyramid_params pp;
+    pp.num_octaves = pyr->num_octaves; pp.scale_samples = 3; pp.sigma0 = pyr->sigma0; pp.materialise = pyr->materialise;
+    Geometry g;
+    int no; double s0;
+    VS_TRY(make_geometry(ctx, pyr->rows, pyr->cols, &pp, &g, &no, &s0));
+    VS_TRY(ensure_taps(ctx, no, s0, 3));
+    const u8 *d_frames; size_t d_pitch, d_stride;
+    VS_TRY(ingest_frames(ctx, frames, pyr->n_frames, pyr->rows, pyr->cols, pitch, frame_stride, space, &d_frames, &d_pitch, &d_stride));
+    return pyramid_fill(ctx, pyr, g, d_frames, d_pitch, d_stride);
 }
 
 void vslam_pyramid_destroy(vslam_pyramid *pyr) {

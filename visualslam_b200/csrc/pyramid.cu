@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(256) grad_all_k(const u8 *__restrict__ g, int 
     for (int k = 0; k < 4; ++k) {
         if (!(mask >> k & 1)) continue;
         float *ok = o + (size_t)k * oplane;
-        if (vec) *(float4 *)ok = make_float4(v[k][0], v[k][1], v[k][2], v[k][3]);
+        if (vec) __stcs((float4 *)ok, make_float4(v[k][0], v[k][1], v[k][2], v[k][3]));      // written once, read by later kernels: streaming
         else for (int j = 0; j < 4 && x + j < cols; ++j) ok[j] = v[k][j];
     }
 }

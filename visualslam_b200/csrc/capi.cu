@@ -106,7 +106,7 @@ void vslam_ctx_destroy(vslam_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf *bufs[] = {&ctx->seg_off, &ctx->seg_cnt, &ctx->seg_dst, &ctx->seg_partial, &ctx->staging, &ctx->counters, &ctx->stage_counts,
-                      &ctx->ingest, &ctx->ingest2, &ctx->wide_ws, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev, &ctx->alt_seg_off, &ctx->alt_seg_cnt, &ctx->alt_seg_dst,
+                      &ctx->ingest, &ctx->ingest2, &ctx->wide_ws, &ctx->grad_lut, &ctx->ws_maps, &ctx->out_dev, &ctx->maps_dev, &ctx->alt_seg_off, &ctx->alt_seg_cnt, &ctx->alt_seg_dst,
                       &ctx->alt_seg_partial, &ctx->alt_staging, &ctx->alt_counters, &ctx->alt_out_dev, &ctx->defer_kp[0], &ctx->defer_kp[1],
                       &ctx->defer_co[0], &ctx->defer_co[1]};
     for (DevBuf *b : bufs) b->release();

@@ -103,6 +103,7 @@ struct vslam_ctx {
     void *h_taps = nullptr;        // FusedTaps[taps_octaves], malloc'd
     bool wide_octave[16] = {false};   // octaves whose kernels the fused kernels do not take: the exact global-memory path (pyramid.cu)
     bool any_wide = false;
+    vslam::DevBuf grad_lut;        // magnitude / first-quadrant angle of every (|dx|, |dy|) (pyramid.cu: grad_all_k)
     vslam::DevBuf wide_ws;         // its scratch: the taps of an octave and the 8.8 horizontal sums
     // optional per-kernel CUDA-event timing (vslam_profile): events bracket every launch on ctx->stream
     bool profiling = false;

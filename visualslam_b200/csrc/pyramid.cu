@@ -135,34 +135,44 @@ __global__ void __launch_bounds__(256) grad_k(const u8 *__restrict__ g, int rows
     if (orient) orient[o] = fast_atan2_deg(dy, dx);
 }
 
+// magnitude and first-quadrant angle of every (|dx|, |dy|) in 0..255 x 0..255, filled by the functions grad_k evaluates per pixel
+// (correctly rounded square root, OpenCV's fastAtan2 polynomial with its IEEE division): 512 KB, L2 resident.  grad_all_k is
+// instruction bound without it (113 thread instructions per pixel, 90 % issue utilisation, two thirds of them this arithmetic).
+__global__ void __launch_bounds__(256) grad_lut_fill_k(float2 *__restrict__ lut) {
+    const int ax = threadIdx.x, ay = blockIdx.x;
+    const float fx = (float)ax, fy = (float)ay;
+    lut[ay * 256 + ax] = make_float2(__fsqrt_rn(__fadd_rn(__fmul_rn(fx, fx), __fmul_rn(fy, fy))), fast_atan2_deg(fy, fx));
+}
+
 // The same for every level of one octave of a batch of frames, into resident fp32 planes (vslam_pyramid_build with a
 // materialise mask: what processGradients leaves behind, GaussPyramid.cpp:65-104).  Thread = 4 adjacent pixels of one
 // level: 16-byte stores per map, 64 B written per 4 B read -- an HBM write stream.
 // grid = (column quads / 64, rows / 4, frames * 6); Gaussian level l of frame f at g + f * gstride + l * gplane.
 __global__ void __launch_bounds__(256) grad_all_k(const u8 *__restrict__ g, int rows, int cols, size_t pitch, size_t gplane, size_t gstride,
-                                                  float *__restrict__ out, size_t oplane, size_t ostride, unsigned mask) {
+                                                  float *__restrict__ out, size_t oplane, size_t ostride, unsigned mask,
+                                                  const float2 *__restrict__ lut) {
     const int xq = blockIdx.x * 64 + (threadIdx.x & 63), y = blockIdx.y * 4 + (threadIdx.x >> 6);
     const int x = 4 * xq;
     if (x >= cols || y >= rows) return;
     const int f = blockIdx.z / 6, l = blockIdx.z - 6 * f;
     const u8 *img = g + (size_t)f * gstride + (size_t)l * gplane;
     const u8 *row = img + (size_t)y * pitch, *up = img + (size_t)refl101(y - 1, rows) * pitch, *dn = img + (size_t)refl101(y + 1, rows) * pitch;
-    float dx[4], dy[4];
+    int ix[4], iy[4];
     if (x + 3 < cols) {                                 // planes are 128-byte pitched: aligned words
         const unsigned c = *(const unsigned *)(row + x), u = *(const unsigned *)(up + x), d = *(const unsigned *)(dn + x);
         const int left = row[refl101(x - 1, cols)], right = row[refl101(x + 4, cols)];
         const int p[6] = {left, (int)(c & 255), (int)(c >> 8 & 255), (int)(c >> 16 & 255), (int)(c >> 24), right};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            dx[j] = (float)(p[j + 2] - p[j]);
-            dy[j] = (float)((int)(d >> (8 * j) & 255) - (int)(u >> (8 * j) & 255));
+            ix[j] = p[j + 2] - p[j];
+            iy[j] = (int)(d >> (8 * j) & 255) - (int)(u >> (8 * j) & 255);
         }
     } else {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int xx = min(x + j, cols - 1);
-            dx[j] = (float)((int)row[refl101(xx + 1, cols)] - (int)row[refl101(xx - 1, cols)]);
-            dy[j] = (float)((int)dn[xx] - (int)up[xx]);
+            ix[j] = (int)row[refl101(xx + 1, cols)] - (int)row[refl101(xx - 1, cols)];
+            iy[j] = (int)dn[xx] - (int)up[xx];
         }
     }
     // maps of a level: [gx, gy, mag, orient] planes of oplane floats each, dense rows of `cols` floats
@@ -170,9 +180,12 @@ __global__ void __launch_bounds__(256) grad_all_k(const u8 *__restrict__ g, int 
     float v[4][4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        v[0][j] = dx[j]; v[1][j] = dy[j];
-        v[2][j] = __fsqrt_rn(__fadd_rn(__fmul_rn(dx[j], dx[j]), __fmul_rn(dy[j], dy[j])));
-        v[3][j] = fast_atan2_deg(dy[j], dx[j]);
+        v[0][j] = (float)ix[j]; v[1][j] = (float)iy[j];
+        const float2 e = __ldg(lut + (abs(iy[j]) << 8 | abs(ix[j])));       // magnitude, angle of (|dx|, |dy|)
+        float a = e.y;                                                     // fastAtan2's quadrant steps
+        if (ix[j] < 0) a = __fsub_rn(180.f, a);
+        if (iy[j] < 0) a = __fsub_rn(360.f, a);
+        v[2][j] = e.x; v[3][j] = a;
     }
     const bool vec = x + 3 < cols && !(cols & 3);
 #pragma unroll
@@ -186,11 +199,17 @@ __global__ void __launch_bounds__(256) grad_all_k(const u8 *__restrict__ g, int 
 
 int launch_gradients_all(vslam_ctx *ctx, const u8 *g, int rows, int cols, size_t pitch, size_t gplane, size_t gstride, float *out,
                          size_t oplane, size_t ostride, unsigned mask, int n_frames) {
+    if (!ctx->grad_lut.p) {                             // once per context
+        if (ctx->grad_lut.reserve(65536 * sizeof(float2))) VS_FAIL(ctx, VSLAM_E_NOMEM, "gradient table");
+        grad_lut_fill_k<<<256, 256, 0, ctx->stream>>>(ctx->grad_lut.as<float2>());
+        VS_LAUNCH_CHECK(ctx);
+    }
     for (int f0 = 0; f0 < n_frames; f0 += 10000) {      // gridDim.z <= 65535
         const int nf = n_frames - f0 < 10000 ? n_frames - f0 : 10000;
         dim3 grid(((cols + 3) / 4 + 63) / 64, (rows + 3) / 4, nf * 6);
         KernelSpan span(ctx, VSLAM_K_GRAD);
-        grad_all_k<<<grid, 256, 0, ctx->stream>>>(g + (size_t)f0 * gstride, rows, cols, pitch, gplane, gstride, out + (size_t)f0 * ostride, oplane, ostride, mask);
+        grad_all_k<<<grid, 256, 0, ctx->stream>>>(g + (size_t)f0 * gstride, rows, cols, pitch, gplane, gstride, out + (size_t)f0 * ostride, oplane, ostride, mask,
+                                                  ctx->grad_lut.as<float2>());
         VS_LAUNCH_CHECK(ctx);
     }
     return VSLAM_OK;

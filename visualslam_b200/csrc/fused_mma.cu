@@ -91,9 +91,11 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps
     }
     // tap copies (fused_mma.cuh): the left pad covers the H pass's chunks in front of the band, padl + r == 0 (mod 4)
     // rounded up to an instantiated chunk count: every chunk is multiplied, so the zero padding must cover all of them
-    out->nch = (8 + 2 * rmax + 31) / 32 + 1;
+    // a block's chunks start on the 16-byte group its widest band starts in (not on a 32-byte boundary): the band begins at most 15
+    // bytes into the first chunk, ceil((15 + 8 + 2 rmax) / 32) chunks cover it -- 2 / 3 / 5 / 9 for the default octaves
+    out->nch = (2 * rmax + 23 + 31) / 32;
     {
-        const int have64[] = {3, 4, 6}, have32[] = {6, 9};
+        const int have64[] = {2, 3, 5}, have32[] = {5, 9};
         int pick = 0;
         for (int c : have64) if (fw == 64 && !pick && c >= out->nch) pick = c;
         for (int c : have32) if (fw == 32 && !pick && c >= out->nch) pick = c;
@@ -181,12 +183,13 @@ __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1)
 
 }  // namespace
 
-// NCH = 32-byte chunks of a staged row that the bands of one 8-column block can touch: (8 + 2 rmax + 31) / 32 + 1
+// NCH = 32-byte chunks of a staged row that the bands of one 8-column block can touch, starting on the 16-byte group the
+//       widest band starts in: ceil((15 + 8 + 2 rmax) / 32)
 // GEO = the level geometry: MmaStaticGeom<n0..n5> (immediates) or MmaDynGeom (read from the argument)
 // FW  = columns a CTA computes: 64, or 32 with the warps regrouped (H pass: 4 column blocks x 2 groups of three levels;
 //       V pass: 2 column blocks x 4 row blocks)
 template <int NCH, class GEO, int FW>
-__global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(const __grid_constant__ MmaArgs a) {
+__global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(const __grid_constant__ MmaArgs a) {
     constexpr int NT = 256;
     extern __shared__ __align__(16) u32 smem[];
     constexpr int NW = NT / 32;
@@ -350,19 +353,19 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 4 ? 2 : 1) octave_mma_k(co
     const u32 stage_sa = (u32)__cvta_generic_to_shared(stage);
     const int hw = warp % HCB, hlg = warp / HCB;                              // H pass: warp = (8 output columns, group of levels)
     const int hcb = cboff + 8 * hw;                                           // staged column of the warp's first output column
-    const int c_lo = (hcb - geo.rmax()) >> 5;                                     // first 32-byte chunk any level's band touches
-    const bool h_short = hcb - 32 * c_lo + 7 + geo.rmax() < 32 * (NCH - 1);         // (warp-uniform) the widest band ends before the last chunk
+    const int c16 = (hcb - geo.rmax()) >> 4;                                      // 16-byte group of a staged row the widest band starts in: chunk 0 starts there
+    const bool h_short = hcb - 16 * c16 + 7 + geo.rmax() < 32 * (NCH - 1);          // (warp-uniform) the widest band ends before the last chunk
     u32 saA[NCH], saB[NCH];                                                   // ldmatrix addresses of the chunks (XOR swizzle resolved)
 #pragma unroll
     for (int ci = 0; ci < NCH; ++ci) {
-        const int ch = 2 * (c_lo + ci) + (lane >> 4);
+        const int ch = c16 + 2 * ci + (lane >> 4);
         saA[ci] = stage_sa + h_row * SP + ((ch ^ ((h_row >> 2) & 7)) << 4);
         saB[ci] = stage_sa + (h_row + 2) * SP + ((ch ^ (((h_row + 2) >> 2) & 7)) << 4);
     }
-    // B fragments: b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 ..; H pass idx0 = r + 32 c - hcb + 4 t - g,
+    // B fragments: b0 = taps idx0 .. idx0 + 3, b1 = taps idx0 + 16 ..; H pass idx0 = r + 16 c16 + 32 ci - hcb + 4 t - g,
     // V pass (K rows remapped so that a thread's 8 rows are consecutive) b1 = taps idx0 + 4 .., idx0 = 32 k + 8 t - g - sv.
     // One lane pointer per pass (byte-shifted copy + word offset); the level is an offset (fused_mma.cuh)
-    const int hu = 4 * t - g - hcb + 32 * c_lo, vu = 8 * t - g + geo.rv() % 4;
+    const int hu = 4 * t - g - hcb + 16 * c16, vu = 8 * t - g + geo.rv() % 4;
     const u8 *hbase = tab + (hu & 3) * geo.cp() + ((hu & 3) > geo.rv() % 4 ? 4 : 0) + (hu - (hu & 3));   // two's complement: fine for hu < 0
     const u8 *vbase = tab + (vu & 3) * geo.cp() + ((vu & 3) > geo.rv() % 4 ? 4 : 0) + (vu - (vu & 3));
     const int d_pi = (g >> 1) + 4 * (g & 1);                                  // quad of the H chunk this thread's D rows belong to
@@ -709,10 +712,10 @@ const MmaVariant *mma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int
     using G2 = MmaStaticGeom<64, 39, 49, 63, 79, 99, 123>;
     using G3 = MmaStaticGeom<32, 79, 99, 123, 155, 195, 245>;
     static const MmaVariant variants[] = {
-        {octave_mma_k<3, G0, 64>, 64, 3, G0::matches}, {octave_mma_k<4, G1, 64>, 64, 4, G1::matches},
-        {octave_mma_k<6, G2, 64>, 64, 6, G2::matches}, {octave_mma_k<9, G3, 32>, 32, 9, G3::matches},
-        {octave_mma_k<3, MmaDynGeom, 64>, 64, 3, nullptr}, {octave_mma_k<4, MmaDynGeom, 64>, 64, 4, nullptr},
-        {octave_mma_k<6, MmaDynGeom, 64>, 64, 6, nullptr}, {octave_mma_k<6, MmaDynGeom, 32>, 32, 6, nullptr},
+        {octave_mma_k<2, G0, 64>, 64, 2, G0::matches}, {octave_mma_k<3, G1, 64>, 64, 3, G1::matches},
+        {octave_mma_k<5, G2, 64>, 64, 5, G2::matches}, {octave_mma_k<9, G3, 32>, 32, 9, G3::matches},
+        {octave_mma_k<2, MmaDynGeom, 64>, 64, 2, nullptr}, {octave_mma_k<3, MmaDynGeom, 64>, 64, 3, nullptr},
+        {octave_mma_k<5, MmaDynGeom, 64>, 64, 5, nullptr}, {octave_mma_k<5, MmaDynGeom, 32>, 32, 5, nullptr},
         {octave_mma_k<9, MmaDynGeom, 32>, 32, 9, nullptr}};
     constexpr int NV = sizeof variants / sizeof variants[0];
     static const int mode = getenv("VSLAM_FUSED_MMA") ? atoi(getenv("VSLAM_FUSED_MMA")) : 1;

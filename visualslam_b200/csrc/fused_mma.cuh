@@ -32,7 +32,7 @@ struct MmaTaps {
     int spq_magic;                  // ceil(2^16 / (stage_pitch / 16)): flattened index -> row without a division
     int plane_words;                // all six planes
     int fw;                         // columns a CTA computes (64 or 32)
-    int nch;                        // 32-byte chunks of a staged row one 8-column block's bands can touch
+    int nch;                        // 32-byte chunks of a staged row one 8-column block's bands can touch (from the band's 16-byte group on)
     int cp;                         // bytes per tap copy
     int tab_bytes;                  // all tap copies (6 levels x 4 copies)
 };
@@ -80,8 +80,8 @@ struct MmaStaticGeom {
         return s;
     }
     __host__ __device__ static constexpr int nch() {                       // rounded up to an instantiated chunk count
-        const int c = (8 + 2 * rmax() + 31) / 32 + 1;
-        return FW_ == 64 ? (c <= 3 ? 3 : c <= 4 ? 4 : 6) : (c <= 6 ? 6 : 9);
+        const int c = (2 * rmax() + 23 + 31) / 32;
+        return FW_ == 64 ? (c <= 2 ? 2 : c <= 3 ? 3 : 5) : (c <= 5 ? 5 : 9);
     }
     __host__ __device__ static constexpr int padl(int l) { return rmax() - r(l) + 41 + (4 - (rmax() + 41) % 4) % 4; }
     __host__ __device__ static constexpr int cp_need(int l) {

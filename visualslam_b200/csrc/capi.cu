@@ -391,7 +391,10 @@ static int build_frames(vslam_ctx *ctx, const Geometry &g, const u8 *frames, int
             for (int l = 0; l < 6; ++l) a.gauss[l] = op.gauss[l];
             for (int l = 0; l < 5; ++l) a.dog[l] = op.dog[l];
             a.map_pitch = op.pitch; a.map_stride = g.frame_bytes;
-            VS_TRY(launch_octave_fused(ctx, a, nf));
+            // the tensor-pipe kernel when it has a materialising instantiation for this octave (the default pyramid), else dp4a / dp2a
+            const int rc = launch_octave_mma(ctx, a, nf, ctx->taps_sigma0, ctx->taps_scale_samples);
+            if (rc < 0) return rc;
+            if (rc == 1) VS_TRY(launch_octave_fused(ctx, a, nf));
         }
     }
     return VSLAM_OK;

@@ -188,7 +188,9 @@ __device__ __forceinline__ int trow(int ty) { return ((ty >> 1) << 2) + (ty & 1)
 // GEO = the level geometry: MmaStaticGeom<n0..n5> (immediates) or MmaDynGeom (read from the argument)
 // FW  = columns a CTA computes: 64, or 32 with the warps regrouped (H pass: 4 column blocks x 2 groups of three levels;
 //       V pass: 2 column blocks x 4 row blocks)
-template <int NCH, class GEO, int FW>
+// MAT = the launch materialises the octave (GaussPyramid's getters): every Gaussian level and every DoG level leaves the V pass's
+//       registers for its plane in HBM as well (rows in pairs, two columns per store)
+template <int NCH, class GEO, int FW, bool MAT = false>
 __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(const __grid_constant__ MmaArgs a) {
     constexpr int NT = 256;
     extern __shared__ __align__(16) u32 smem[];
@@ -378,6 +380,20 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
         voff[l] = (u32)(vjb + t) * (PPW * 4) + 16 * (8 * vcb + g);
     }
     const int wi0 = (8 * vcb + g) * TRP + vcb + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
+    // materialising launches: the thread's V outputs are columns mat_col, mat_col + 1 (rows 8 (vjb + rb) + 2t, + 1 of the step)
+    const int mat_col = X0c + 16 * vcb + 2 * g;
+    const bool mat_own = MAT && !svc && 16 * vcb + 2 * g >= 2 && 16 * vcb + 2 * g < 2 + FWO && mat_col < cols;
+    const bool mat_pair = mat_col + 1 < cols;
+    const size_t mat_fo = (size_t)frame * a.map_stride + (size_t)(mat_col < 0 ? 0 : mat_col);
+    auto mat_put = [&](u8 *p, int y, u32 q) {                                 // q = {row y: two columns, row y + 1: two columns}
+        if (mat_pair) {
+            if (y < ye) *(u16 *)p = (u16)q;
+            if (y + 1 < ye) *(u16 *)(p + a.map_pitch) = (u16)(q >> 16);
+        } else {
+            if (y < ye) *p = (u8)q;
+            if (y + 1 < ye) p[a.map_pitch] = (u8)(q >> 16);
+        }
+    };
     // detector: thread = (sample column det_k, sample row det_sr of the step)
     const int det_k = tid % NS, det_sr = tid / NS;                            // 256 threads: rows 0 .. 12 (at most 12 are live)
     const int det_xc = X0 + 3 * det_k;
@@ -573,9 +589,18 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
                     const u32 c0 = __byte_perm(v0, v1, 0x7632), c1 = __byte_perm(v2, v3, 0x7632);
                     const int wi = wi0 + 4 * rb;
                     if (l >= 1 && l <= 3) tiles32[(l - 1) * TILE_W + wi] = __byte_perm(c0, c1, 0x6420);
+                    u32 d0 = 0, d1 = 0;
                     if (l >= 1) {
-                        const u32 d0 = __vmaxu2(c0, prev0[rb]) - prev0[rb], d1 = __vmaxu2(c1, prev1[rb]) - prev1[rb];   // max(cur - prev, 0)
+                        d0 = __vmaxu2(c0, prev0[rb]) - prev0[rb]; d1 = __vmaxu2(c1, prev1[rb]) - prev1[rb];   // max(cur - prev, 0)
                         tiles32[(N_G + l - 1) * TILE_W + wi] = __byte_perm(d0, d1, 0x6420);
+                    }
+                    if constexpr (MAT) {
+                        if (mat_own && y0 >= ys) {                       // GaussPyramid::octaveBlur / octaveDiff planes (own rows of the segment)
+                            const int y = y0 + 8 * (vjb + rb) + 2 * t;
+                            const size_t o = mat_fo + (size_t)y * a.map_pitch;
+                            mat_put(a.gauss[l] + o, y, __byte_perm(c0, c1, 0x6240));
+                            if (l >= 1) mat_put(a.dog[l - 1] + o, y, __byte_perm(d0, d1, 0x6240));
+                        }
                     }
                     prev0[rb] = c0; prev1[rb] = c1;
                 }
@@ -702,7 +727,7 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
 // ---------------------------------------------------------------------------------------------------------------
 namespace {
 typedef void (*mma_kern_t)(const MmaArgs);
-struct MmaVariant { mma_kern_t k; int fw, nch; bool (*match)(const MmaTaps &); };
+struct MmaVariant { mma_kern_t k; int fw, nch; bool (*match)(const MmaTaps &); mma_kern_t k_mat; };
 
 // Which instantiation runs an octave: 64-column strips when the rings fit shared memory, else 32-column strips, else
 // none (the dp4a/dp2a kernel).  The default pyramid's octaves get the instantiations with compile-time geometry.
@@ -712,11 +737,13 @@ const MmaVariant *mma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int
     using G2 = MmaStaticGeom<64, 39, 49, 63, 79, 99, 123>;
     using G3 = MmaStaticGeom<32, 79, 99, 123, 155, 195, 245>;
     static const MmaVariant variants[] = {
-        {octave_mma_k<2, G0, 64>, 64, 2, G0::matches}, {octave_mma_k<3, G1, 64>, 64, 3, G1::matches},
-        {octave_mma_k<5, G2, 64>, 64, 5, G2::matches}, {octave_mma_k<9, G3, 32>, 32, 9, G3::matches},
-        {octave_mma_k<2, MmaDynGeom, 64>, 64, 2, nullptr}, {octave_mma_k<3, MmaDynGeom, 64>, 64, 3, nullptr},
-        {octave_mma_k<5, MmaDynGeom, 64>, 64, 5, nullptr}, {octave_mma_k<5, MmaDynGeom, 32>, 32, 5, nullptr},
-        {octave_mma_k<9, MmaDynGeom, 32>, 32, 9, nullptr}};
+        {octave_mma_k<2, G0, 64>, 64, 2, G0::matches, octave_mma_k<2, G0, 64, true>},
+        {octave_mma_k<3, G1, 64>, 64, 3, G1::matches, octave_mma_k<3, G1, 64, true>},
+        {octave_mma_k<5, G2, 64>, 64, 5, G2::matches, octave_mma_k<5, G2, 64, true>},
+        {octave_mma_k<9, G3, 32>, 32, 9, G3::matches, octave_mma_k<9, G3, 32, true>},
+        {octave_mma_k<2, MmaDynGeom, 64>, 64, 2, nullptr, nullptr}, {octave_mma_k<3, MmaDynGeom, 64>, 64, 3, nullptr, nullptr},
+        {octave_mma_k<5, MmaDynGeom, 64>, 64, 5, nullptr, nullptr}, {octave_mma_k<5, MmaDynGeom, 32>, 32, 5, nullptr, nullptr},
+        {octave_mma_k<9, MmaDynGeom, 32>, 32, 9, nullptr, nullptr}};      // materialising launches: the default pyramid's octaves only
     constexpr int NV = sizeof variants / sizeof variants[0];
     static const int mode = getenv("VSLAM_FUSED_MMA") ? atoi(getenv("VSLAM_FUSED_MMA")) : 1;
     static const int use_static = getenv("VSLAM_MMA_STATIC") ? atoi(getenv("VSLAM_MMA_STATIC")) : 1;
@@ -734,12 +761,15 @@ const MmaVariant *mma_plan(vslam_ctx *ctx, double sigma0, int scale_samples, int
         if (static_smem_dev[di] < 0) {
             cudaFuncAttributes fa;
             int mx = 0;
-            for (int i = 0; i < NV; ++i) {
-                if (cudaFuncGetAttributes(&fa, variants[i].k) != cudaSuccess) return nullptr;
-                if ((int)fa.sharedSizeBytes > mx) mx = (int)fa.sharedSizeBytes;
-            }
             for (int i = 0; i < NV; ++i)
-                if (cudaFuncSetAttribute(variants[i].k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - mx) != cudaSuccess) return nullptr;
+                for (mma_kern_t k : {variants[i].k, variants[i].k_mat}) {
+                    if (!k) continue;
+                    if (cudaFuncGetAttributes(&fa, k) != cudaSuccess) return nullptr;
+                    if ((int)fa.sharedSizeBytes > mx) mx = (int)fa.sharedSizeBytes;
+                }
+            for (int i = 0; i < NV; ++i)
+                for (mma_kern_t k : {variants[i].k, variants[i].k_mat})
+                    if (k && cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - mx) != cudaSuccess) return nullptr;
             static_smem_dev[di] = mx;
         }
         static_smem = static_smem_dev[di];
@@ -865,8 +895,8 @@ int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitc
 }
 
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples) {
-    if (io.gauss[0]) return 1;                                       // materialising launches stay on fused.cu
     if (n_frames <= 0 || n_frames > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: %d frames per launch", n_frames);
+    if (io.gauss[0] && ((io.map_pitch & 1) || (io.map_stride & 1))) return 1;   // the planes are written two columns per store
     if ((io.base_pitch & 15) || ((uintptr_t)io.base & 15) || (io.base_stride & 15))
         VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: base plane must be 16-byte aligned (pitch %zu)", io.base_pitch);
     MmaArgs a;
@@ -874,6 +904,7 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     size_t sm = 0;
     const MmaVariant *v = mma_plan(ctx, sigma0, scale_samples, io.octave, &a.mt, &sm);
     if (!v) return 1;
+    if (io.gauss[0] && !v->k_mat) return 1;                          // materialising launches of other pyramids stay on fused.cu
     static_cast<OctaveIO &>(a) = io;
     a.tab_image = mma_tab_image(ctx, sigma0, scale_samples, io.octave, a.mt);
     if (!a.tab_image) VS_FAIL(ctx, VSLAM_E_NOMEM, "tap table image of octave %d", io.octave);
@@ -890,7 +921,7 @@ int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double s
     a.n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid(a.n_strips, a.n_segs, n_frames);
     KernelSpan span(ctx, VSLAM_K_OCTAVE_MMA);
-    v->k<<<grid, kMmaThreads, sm, ctx->stream>>>(a);
+    (io.gauss[0] ? v->k_mat : v->k)<<<grid, kMmaThreads, sm, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);
     return VSLAM_OK;
 }

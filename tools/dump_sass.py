@@ -6,8 +6,11 @@ import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1] if len(sys.argv) > 1 else "r2"
 lib = os.path.join(ROOT, "visualslam_b200", "libvslam_b200.so")
-WANT = [("octave_mma_k<3, vslam::MmaStaticGeom<64, 11,", "octave_mma_o0"), ("octave_mma_k<4, vslam::MmaStaticGeom<64, 21,", "octave_mma_o1"),
-        ("octave_mma_k<6, vslam::MmaStaticGeom<64, 39,", "octave_mma_o2"), ("octave_mma_k<9, vslam::MmaStaticGeom<32, 79,", "octave_mma_o3"),
+WANT = [("octave_mma_k<2, vslam::MmaStaticGeom<64, 11, 13, 17, 21, 25, 31>, 64, false>", "octave_mma_o0"),
+        ("octave_mma_k<3, vslam::MmaStaticGeom<64, 21, 25, 31, 39, 49, 63>, 64, false>", "octave_mma_o1"),
+        ("octave_mma_k<5, vslam::MmaStaticGeom<64, 39, 49, 63, 79, 99, 123>, 64, false>", "octave_mma_o2"),
+        ("octave_mma_k<9, vslam::MmaStaticGeom<32, 79, 99, 123, 155, 195, 245>, 32, false>", "octave_mma_o3"),
+        ("octave_mma_k<2, vslam::MmaStaticGeom<64, 11, 13, 17, 21, 25, 31>, 64, true>", "octave_mma_o0_mat"),
         ("octave_umma_k<5, 3, 80, 2>", "octave_umma_o0"), ("octave_umma_k<6, 4, 112, 1>", "octave_umma_o1"),
         ("harris_fast_k<2, 3>", "harris_fast_p2"), ("harris_march_k<2>", "harris_march_p2"), ("upsample2x_k(", "upsample2x"),
         ("reflect_pad_k(", "reflect_pad"), ("reflect_pad_rows_k(", "reflect_pad_rows"), ("seg_reduce_k(", "seg_reduce"), ("seg_spine_k(", "seg_spine"),
@@ -43,6 +46,6 @@ for pat, short in WANT:
         for a, t in ins:
             fh.write(f"/*{a}*/ {t}\n")
     keyops = ", ".join(f"{k} {ops[k]}" for k in KEY if ops.get(k))
-    idx.append(f"| `{names[f][:70]}` | {fn} | {len(ins)} | {keyops} |")
+    idx.append(f"| `{names[f][:110]}` | {fn} | {len(ins)} | {keyops} |")
 open(os.path.join(ROOT, "profiles", f"sass_{tag}_index.md"), "w").write("\n".join(idx) + "\n")
 print("\n".join(idx))

@@ -381,18 +381,18 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
     }
     const int wi0 = (8 * vcb + g) * TRP + vcb + 2 + 4 * vjb + t;                    // tile word of the thread's first V output
     // materialising launches: the thread's V outputs are columns mat_col, mat_col + 1 (rows 8 (vjb + rb) + 2t, + 1 of the step)
+    // (cols is even: the launcher sends odd widths to fused.cu); per step: 32-bit plane offsets of the thread's row pairs and
+    // which of their rows are stored -- the map pointers themselves are CTA-uniform
     const int mat_col = X0c + 16 * vcb + 2 * g;
     const bool mat_own = MAT && !svc && 16 * vcb + 2 * g >= 2 && 16 * vcb + 2 * g < 2 + FWO && mat_col < cols;
-    const bool mat_pair = mat_col + 1 < cols;
-    const size_t mat_fo = (size_t)frame * a.map_stride + (size_t)(mat_col < 0 ? 0 : mat_col);
-    auto mat_put = [&](u8 *p, int y, u32 q) {                                 // q = {row y: two columns, row y + 1: two columns}
-        if (mat_pair) {
-            if (y < ye) *(u16 *)p = (u16)q;
-            if (y + 1 < ye) *(u16 *)(p + a.map_pitch) = (u16)(q >> 16);
-        } else {
-            if (y < ye) *p = (u8)q;
-            if (y + 1 < ye) p[a.map_pitch] = (u8)(q >> 16);
-        }
+    const size_t mat_fo = (size_t)blockIdx.z * a.map_stride;                  // (blockIdx, not `frame`: the compiler keeps the plane pointers uniform)
+    const u32 mat_pitch = (u32)a.map_pitch;
+    u32 mat_off[RBW];
+    unsigned mat_ok = 0;                                                      // bit 2 rb: row pair rb's first row is stored, bit 2 rb + 1: its second
+    auto mat_put = [&](u8 *plane, int rb, u32 q) {                            // q = {first row: two columns, second row: two columns}
+        u8 *p = plane + mat_off[rb];
+        if (mat_ok & (1u << (2 * rb))) *(u16 *)p = (u16)q;
+        if (mat_ok & (2u << (2 * rb))) *(u16 *)(p + mat_pitch) = (u16)(q >> 16);
     };
     // detector: thread = (sample column det_k, sample row det_sr of the step)
     const int det_k = tid % NS, det_sr = tid / NS;                            // 256 threads: rows 0 .. 12 (at most 12 are live)
@@ -569,6 +569,15 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
             u32 prev0[RBW], prev1[RBW];                          // previous level, columns 2g and 2g + 1, rows as 16-bit halves
 #pragma unroll
             for (int rb = 0; rb < RBW; ++rb) prev0[rb] = prev1[rb] = 0;
+            if constexpr (MAT) {
+                mat_ok = 0;
+#pragma unroll
+                for (int rb = 0; rb < RBW; ++rb) {
+                    const int y = y0 + 8 * (vjb + rb) + 2 * t;
+                    mat_off[rb] = (u32)y * mat_pitch + (u32)mat_col;             // < 2^32: checked by the launcher
+                    if (mat_own && y0 >= ys) mat_ok |= (y < ye ? 1u << (2 * rb) : 0u) | (y + 1 < ye ? 2u << (2 * rb) : 0u);
+                }
+            }
             {   // rows y0+28 .. y0+31 of the last step become the history of the G and D tiles (before anything is overwritten)
                 const int hrb = 3 - vjb;
                 if (hrb >= 0 && hrb < RBW && t >= 2) {
@@ -594,13 +603,9 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
                         d0 = __vmaxu2(c0, prev0[rb]) - prev0[rb]; d1 = __vmaxu2(c1, prev1[rb]) - prev1[rb];   // max(cur - prev, 0)
                         tiles32[(N_G + l - 1) * TILE_W + wi] = __byte_perm(d0, d1, 0x6420);
                     }
-                    if constexpr (MAT) {
-                        if (mat_own && y0 >= ys) {                       // GaussPyramid::octaveBlur / octaveDiff planes (own rows of the segment)
-                            const int y = y0 + 8 * (vjb + rb) + 2 * t;
-                            const size_t o = mat_fo + (size_t)y * a.map_pitch;
-                            mat_put(a.gauss[l] + o, y, __byte_perm(c0, c1, 0x6240));
-                            if (l >= 1) mat_put(a.dog[l - 1] + o, y, __byte_perm(d0, d1, 0x6240));
-                        }
+                    if constexpr (MAT) {                                 // GaussPyramid::octaveBlur / octaveDiff planes (own rows of the segment)
+                        mat_put(a.gauss[l] + mat_fo, rb, __byte_perm(c0, c1, 0x6240));
+                        if (l >= 1) mat_put(a.dog[l - 1] + mat_fo, rb, __byte_perm(d0, d1, 0x6240));
                     }
                     prev0[rb] = c0; prev1[rb] = c1;
                 }
@@ -896,7 +901,8 @@ int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitc
 
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples) {
     if (n_frames <= 0 || n_frames > 65535) VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: %d frames per launch", n_frames);
-    if (io.gauss[0] && ((io.map_pitch & 1) || (io.map_stride & 1))) return 1;   // the planes are written two columns per store
+    // materialising launches write two columns per store at 32-bit plane offsets: other shapes stay on fused.cu
+    if (io.gauss[0] && ((io.map_pitch & 1) || (io.map_stride & 1) || (io.cols & 1) || (unsigned long long)io.rows * io.map_pitch >= (1ull << 32))) return 1;
     if ((io.base_pitch & 15) || ((uintptr_t)io.base & 15) || (io.base_stride & 15))
         VS_FAIL(ctx, VSLAM_E_INVALID, "fused octave: base plane must be 16-byte aligned (pitch %zu)", io.base_pitch);
     MmaArgs a;

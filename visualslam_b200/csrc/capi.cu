@@ -419,10 +419,11 @@ static size_t detect_segments(const Geometry &g, int window, int *seg_base /*[nu
     return n;
 }
 
-// rows G-J for one frame whose planes are in `block`; appends to d_out in emission order.
+// rows G-J for n_frames frames whose plane blocks start at `block`, g.frame_bytes apart (frames frame .. frame + n_frames - 1 of the
+// call: one launch per octave for the batch); appends to d_out in emission order.  n_seg = segments of ONE frame.
 static int detect_frame(vslam_ctx *ctx, const Geometry &g, u8 *block, const vslam_dog_params &dp, const int *seg_base,
                         size_t n_seg, vslam_keypoint *d_out, int capacity, int frame, unsigned long long *d_stage,
-                        int only_octave = -1, int apply_edge = 1) {
+                        int only_octave = -1, int apply_edge = 1, int n_frames = 1) {
     int *cnt = ctx->counters.as<int>();
     VS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int), ctx->stream));
     for (int o = 0; o < g.num_octaves; ++o) {
@@ -441,9 +442,10 @@ static int detect_frame(vslam_ctx *ctx, const Geometry &g, u8 *block, const vsla
         a.cursor = cnt;
         a.staging = ctx->staging.as<vslam_keypoint>(); a.staging_cap = ctx->staging_entries;
         a.stage_counts = d_stage ? d_stage + ((size_t)frame * g.num_octaves + o) * 4 : nullptr;
+        a.n_frames = n_frames; a.frame_stride = g.frame_bytes; a.segs_per_frame = (int)n_seg; a.stage_stride = g.num_octaves * 4;
         VS_TRY(launch_detect(ctx, a, dp));
     }
-    return seg_finalise(ctx, n_seg, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + frame, 1);
+    return seg_finalise(ctx, n_seg * (size_t)n_frames, (int)sizeof(vslam_keypoint), d_out, capacity, cnt + 2, cnt + kCounterBase + frame, n_frames);
 }
 
 static int finish_counts(vslam_ctx *ctx, int n_frames, int capacity, int *counts, long long *total_out) {
@@ -694,7 +696,11 @@ int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_p
     }
     int seg_base[16];
     const size_t n_seg = detect_segments(g, dp.window, seg_base);
-    VS_TRY(seg_prepare(ctx, n_seg ? n_seg : 1, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256)));
+    // frames per launch: grid.z = 3 x frames <= 65535, segment arrays <= 2^28 entries
+    int fb = pyr->n_frames < 16384 ? pyr->n_frames : 16384;
+    if (n_seg && (size_t)fb > ((size_t)1 << 28) / n_seg) fb = (int)(((size_t)1 << 28) / n_seg);
+    if (fb < 1) fb = 1;
+    VS_TRY(seg_prepare(ctx, (n_seg ? n_seg : 1) * (size_t)fb, sizeof(vslam_keypoint), staging_entries(capacity, n_seg * 256 * (size_t)fb)));
     VS_TRY(reserve_counters(ctx, pyr->n_frames));
     vslam_keypoint *d_out = out;
     if (space != VSLAM_DEVICE) {
@@ -708,8 +714,9 @@ int vslam_dog_detect(vslam_ctx *ctx, const vslam_pyramid *pyr, const vslam_dog_p
         d_stage = ctx->stage_counts.as<unsigned long long>();
         VS_CUDA(ctx, cudaMemsetAsync(d_stage, 0, stage_n * 8, ctx->stream));
     }
-    for (int f = 0; f < pyr->n_frames; ++f)
-        VS_TRY(detect_frame(ctx, g, pyr->maps.as<u8>() + pyr->frame_bytes * f, dp, seg_base, n_seg, d_out, capacity, f, d_stage));
+    for (int f = 0; f < pyr->n_frames; f += fb)
+        VS_TRY(detect_frame(ctx, g, pyr->maps.as<u8>() + pyr->frame_bytes * f, dp, seg_base, n_seg, d_out, capacity, f, d_stage, -1, 1,
+                            pyr->n_frames - f < fb ? pyr->n_frames - f : fb));
     long long total = 0;
     if (stage_counts) VS_CUDA(ctx, cudaMemcpyAsync(stage_counts, d_stage, stage_n * 8, cudaMemcpyDeviceToHost, ctx->stream));
     VS_TRY(finish_counts(ctx, pyr->n_frames, capacity, counts, &total));

@@ -4,8 +4,9 @@
 //   FeaturePointLocalization   Diff_of_Gauss.cpp:223-251   exact IEEE sequence of OpenCV's gemm / invert(3x3)
 //   computeEdgeResponse + threshold  :79-109, :326-338     2x2 structure sums on the level's gradients, tr^2/det < 12.1
 //
-// One block = one segment = 256 consecutive grid samples of one (level, sample row): survivors are compacted in
-// j order with ballots, one atomicAdd per block reserves staging space, compaction.cu orders the segments.
+// One segment = 256 consecutive grid samples of one (frame, level, sample row): survivors are compacted in j order with
+// ballots, one atomicAdd per segment reserves staging space, compaction.cu orders the segments.  A block walks
+// kDetectRows sample rows (one segment each); one launch covers every frame of a batch (grid.z = level x frame).
 // Every float/double operation below uses the round-to-nearest intrinsics so that nvcc cannot contract to FMA.
 #include "detect.cuh"
 #include "detect_math.cuh"
@@ -32,23 +33,28 @@ __device__ float edge_response(const u8 *__restrict__ g, int rows, int cols, siz
     return __fdiv_rn(__fmul_rn(tr, tr), det);
 }
 
+constexpr int kDetectRows = 4;              // sample rows per block
+
 __global__ void __launch_bounds__(256) dog_detect_k(DetectArgs a) {
-    __shared__ int s_wcnt[8];
-    __shared__ int s_base;
+    __shared__ int s_wcnt[2][8];
+    __shared__ int s_base[2];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int level = blockIdx.z + 1;
+    const int level = blockIdx.z % 3 + 1, frame = blockIdx.z / 3;
     const int pad = a.pad, win = a.window;
-    const int i = pad + blockIdx.y * win;
     const int jj = blockIdx.x * 256 + tid;
     const int j = pad + jj * win;
     const int rows = a.rows, cols = a.cols;
-    const size_t pitch = a.pitch;
-    const bool valid = j < cols;            // i < rows by construction of the grid
+    const size_t pitch = a.pitch, fo = (size_t)frame * a.frame_stride;
+    const bool valid = j < cols;
+    const u8 *d0 = a.dog[level - 1] + fo, *d1 = a.dog[level] + fo, *d2 = a.dog[level + 1] + fo;
+    const int si_end = min(a.ni, (int)(blockIdx.y + 1) * kDetectRows);
+    for (int si = blockIdx.y * kDetectRows; si < si_end; ++si) {
+    const int i = pad + si * win;           // i < rows by construction of the grid
+    const int par = si & 1;                 // the shared slots alternate: one barrier less per row
 
     bool cand = false, pass_c = false, pass_e = false;
     int value = 0;
     if (valid && pad > 0) {
-        const u8 *d0 = a.dog[level - 1], *d1 = a.dog[level], *d2 = a.dog[level + 1];
         // padded (u,v) <-> original (clamp(u-pad), clamp(v-pad))   (padOctave = replicate, Diff_of_Gauss.cpp:260)
 #define PAD_AT(m, u, v) ((int)(m)[(size_t)clampi((u) - pad, 0, rows - 1) * pitch + clampi((v) - pad, 0, cols - 1)])
         const int c = PAD_AT(d1, i, j);
@@ -70,7 +76,7 @@ __global__ void __launch_bounds__(256) dog_detect_k(DetectArgs a) {
                 value = (int)__fmul_rn(zhat, 255.0f);                       // Diff_of_Gauss.cpp:246
                 pass_e = true;
                 if (a.apply_edge) {
-                    const float resp = edge_response(a.gauss[level], rows, cols, pitch, i, j, pad);
+                    const float resp = edge_response(a.gauss[level] + fo, rows, cols, pitch, i, j, pad);
                     pass_e = resp < a.edge_thr;                              // :336 (NaN and +inf fail)
                 }
             }
@@ -79,40 +85,47 @@ __global__ void __launch_bounds__(256) dog_detect_k(DetectArgs a) {
     }
     // ordered compaction inside the block
     const unsigned bal = __ballot_sync(0xffffffffu, pass_e);
-    const int n_cand = __syncthreads_count(cand);
-    const int n_con = __syncthreads_count(pass_c);
-    if (lane == 0) s_wcnt[wid] = __popc(bal);
+    int n_cand = 0, n_con = 0;
+    if (a.stage_counts) {                   // (block-uniform)
+        n_cand = __syncthreads_count(cand);
+        n_con = __syncthreads_count(pass_c);
+    }
+    if (lane == 0) s_wcnt[par][wid] = __popc(bal);
     __syncthreads();
     int before = 0, total = 0;
 #pragma unroll
     for (int w = 0; w < 8; ++w) {
-        const int c = s_wcnt[w];
+        const int c = s_wcnt[par][w];
         if (w < wid) before += c;
         total += c;
     }
-    const int seg = a.seg_base + ((level - 1) * a.ni + blockIdx.y) * a.nchunks + blockIdx.x;
+    const int seg = frame * a.segs_per_frame + a.seg_base + ((level - 1) * a.ni + si) * a.nchunks + blockIdx.x;
     if (tid == 0) {
         int off = 0;
         if (total) off = atomicAdd(a.cursor, total);
-        s_base = off;
+        s_base[par] = off;
         a.seg_off[seg] = off;
         a.seg_cnt[seg] = total;
         if (a.stage_counts) {
+            unsigned long long *sc = a.stage_counts + (size_t)frame * a.stage_stride;
             const int n_valid = min(256, a.nj - blockIdx.x * 256);
-            atomicAdd(&a.stage_counts[0], (unsigned long long)n_valid);
-            if (n_cand) atomicAdd(&a.stage_counts[1], (unsigned long long)n_cand);
-            if (n_con) atomicAdd(&a.stage_counts[2], (unsigned long long)n_con);
-            if (total) atomicAdd(&a.stage_counts[3], (unsigned long long)total);
+            atomicAdd(&sc[0], (unsigned long long)n_valid);
+            if (n_cand) atomicAdd(&sc[1], (unsigned long long)n_cand);
+            if (n_con) atomicAdd(&sc[2], (unsigned long long)n_con);
+            if (total) atomicAdd(&sc[3], (unsigned long long)total);
         }
     }
-    __syncthreads();
-    if (pass_e) {
-        const int pos = s_base + before + __popc(bal & ((1u << lane) - 1u));
-        if (pos < a.staging_cap) {
-            vslam_keypoint k;
-            k.row = i; k.col = j; k.value = value; k.padding = pad; k.octave = a.octave; k.level = level;
-            a.staging[pos] = k;
+    if (total) {                            // (block-uniform: every thread summed the same counts)
+        __syncthreads();
+        if (pass_e) {
+            const int pos = s_base[par] + before + __popc(bal & ((1u << lane) - 1u));
+            if (pos < a.staging_cap) {
+                vslam_keypoint k;
+                k.row = i; k.col = j; k.value = value; k.padding = pad; k.octave = a.octave; k.level = level;
+                a.staging[pos] = k;
+            }
         }
+    }
     }
 }
 
@@ -122,7 +135,9 @@ int launch_detect(vslam_ctx *ctx, DetectArgs &a, const vslam_dog_params &p) {
     a.contrast_thr = p.contrast_thr;
     const float rp1 = p.edge_r + 1.0f;
     a.edge_thr = (rp1 * rp1) / p.edge_r;                                    // Diff_of_Gauss.cpp:332-333
-    dim3 g(a.nchunks, a.ni, 3);
+    if (a.n_frames < 1) a.n_frames = 1;
+    if (a.n_frames > 21845) VS_FAIL(ctx, VSLAM_E_INVALID, "detector: %d frames per launch", a.n_frames);
+    dim3 g(a.nchunks, (a.ni + kDetectRows - 1) / kDetectRows, 3 * a.n_frames);
     KernelSpan span(ctx, VSLAM_K_DETECT);
     dog_detect_k<<<g, 256, 0, ctx->stream>>>(a);
     VS_LAUNCH_CHECK(ctx);

@@ -20,6 +20,11 @@ struct DetectArgs {
     vslam_keypoint *staging;
     int staging_cap;
     unsigned long long *stage_counts; // 4 counters of this (frame, octave) or nullptr
+    // batched launches: grid.z = 3 levels x n_frames; frame f's planes, segments and counters follow frame 0's at these strides
+    int n_frames;
+    size_t frame_stride;              // bytes between the frames' plane blocks
+    int segs_per_frame;
+    int stage_stride;                 // counters (u64) between the frames' stage_counts
 };
 
 void detect_grid(int rows, int cols, int window, int *ni, int *nj, int *nchunks);

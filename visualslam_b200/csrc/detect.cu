@@ -53,11 +53,28 @@ __global__ void __launch_bounds__(256) dog_detect_k(DetectArgs a) {
     const int par = si & 1;                 // the shared slots alternate: one barrier less per row
 
     bool cand = false, pass_c = false, pass_e = false;
-    int value = 0;
-    if (valid && pad > 0) {
-        // padded (u,v) <-> original (clamp(u-pad), clamp(v-pad))   (padOctave = replicate, Diff_of_Gauss.cpp:260)
+    int value = 0, c = 0, dx = 0, dy = 0, ds = 0;
+    // padded (u,v) <-> original (clamp(u-pad), clamp(v-pad))   (padOctave = replicate, Diff_of_Gauss.cpp:260)
 #define PAD_AT(m, u, v) ((int)(m)[(size_t)clampi((u) - pad, 0, rows - 1) * pitch + clampi((v) - pad, 0, cols - 1)])
-        const int c = PAD_AT(d1, i, j);
+    if (valid && pad == 1 && i >= 2 && i < rows && j >= 2 && j < cols) {
+        // window 3 away from the border (nearly every sample): the same reads without the clamps.  Centre = original (i - 1, j - 1);
+        // window rows i - 2, i - 1, columns j - 2, j - 1
+        const size_t o = (size_t)(i - 1) * pitch + (size_t)(j - 1);
+        const u8 *p0 = d0 + o, *p1 = d1 + o, *p2 = d2 + o, *q0 = p0 - pitch, *q1 = p1 - pitch, *q2 = p2 - pitch;
+        const int a0 = q0[-1], b0 = q0[0], e0 = p0[-1], f0 = p0[0];
+        const int a1 = q1[-1], b1 = q1[0], e1 = p1[-1], f1 = p1[0];
+        const int a2 = q2[-1], b2 = q2[0], e2 = p2[-1], f2 = p2[0];
+        c = f1;
+        const int mn = min(min(min(a0, b0), min(e0, f0)), min(min(min(a1, b1), min(e1, f1)), min(min(a2, b2), min(e2, f2))));
+        const int mx = max(max(max(a0, b0), max(e0, f0)), max(max(max(a1, b1), max(e1, f1)), max(max(a2, b2), max(e2, f2))));
+        cand = (c == mn) || (c == mx);
+        if (cand) {
+            dx = e1 - (int)p1[1];
+            dy = b1 - (int)p1[pitch];
+            ds = f0 - f2;
+        }
+    } else if (valid && pad > 0) {
+        c = PAD_AT(d1, i, j);
         int mn = c, mx = c;
         for (int u = i - pad; u < i + pad; ++u)
             for (int v = j - pad; v < j + pad; ++v) {
@@ -67,21 +84,23 @@ __global__ void __launch_bounds__(256) dog_detect_k(DetectArgs a) {
             }
         cand = (c == mn) || (c == mx);
         if (cand) {
-            const int dx = PAD_AT(d1, i, j - 1) - PAD_AT(d1, i, j + 1);
-            const int dy = PAD_AT(d1, i - 1, j) - PAD_AT(d1, i + 1, j);
-            const int ds = PAD_AT(d0, i, j) - PAD_AT(d2, i, j);
-            const float zhat = localize(dx, dy, ds, c);
-            pass_c = zhat > a.contrast_thr;
-            if (pass_c) {
-                value = (int)__fmul_rn(zhat, 255.0f);                       // Diff_of_Gauss.cpp:246
-                pass_e = true;
-                if (a.apply_edge) {
-                    const float resp = edge_response(a.gauss[level] + fo, rows, cols, pitch, i, j, pad);
-                    pass_e = resp < a.edge_thr;                              // :336 (NaN and +inf fail)
-                }
+            dx = PAD_AT(d1, i, j - 1) - PAD_AT(d1, i, j + 1);
+            dy = PAD_AT(d1, i - 1, j) - PAD_AT(d1, i + 1, j);
+            ds = PAD_AT(d0, i, j) - PAD_AT(d2, i, j);
+        }
+    }
+#undef PAD_AT
+    if (cand) {
+        const float zhat = localize(dx, dy, ds, c);
+        pass_c = zhat > a.contrast_thr;
+        if (pass_c) {
+            value = (int)__fmul_rn(zhat, 255.0f);                       // Diff_of_Gauss.cpp:246
+            pass_e = true;
+            if (a.apply_edge) {
+                const float resp = edge_response(a.gauss[level] + fo, rows, cols, pitch, i, j, pad);
+                pass_e = resp < a.edge_thr;                              // :336 (NaN and +inf fail)
             }
         }
-#undef PAD_AT
     }
     // ordered compaction inside the block
     const unsigned bal = __ballot_sync(0xffffffffu, pass_e);

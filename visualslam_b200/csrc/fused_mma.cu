@@ -107,7 +107,8 @@ int build_mma_taps(double sigma0, int scale_samples, int octave, int fw, MmaTaps
         MmaLevel &lv = out->lv[l];
         lv.padl = rmax - lv.r + 41 + (4 - (rmax + 41) % 4) % 4;
         const int need_h = lv.padl + lv.r - rmax + 12 + 32 * (out->nch - 1) + 20;
-        const int need_v = lv.padl + 24 + 32 * (lv.ksv - 1) + 8;
+        const int ksvs = (lv.n + 7 + lv.sv + 8 * (fw / 32 - 1) + 31) / 32;     // static kernels: the row blocks of a warp share a K step's A fragments
+        const int need_v = lv.padl + 24 + 32 * (ksvs - 1) + 8;
         const int need_t = lv.padl + lv.n + 3;
         cp = std::max(cp, std::max(need_h, std::max(need_v, need_t)));
     }
@@ -614,34 +615,33 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
             if constexpr (GEO::is_static) {
                 // every (level, K step) is an item of one unrolled pipeline: item i + 1's fragments are loaded before item
                 // i's MMAs are issued, level l - 1's epilogue (tile stores) follows level l's first MMAs
+                // Both row blocks of the warp read the SAME 32 ring rows per K step (row block rb through taps shifted by 8 rb: B_rb[k][n] =
+                // B_0[k - 8 rb][n]), so a step costs one pair of LDS.128 instead of one per block -- the h-plane loads were 45 % of the
+                // kernel's shared-memory wavefronts, and that pipe (68-72 % busy at octaves 0 / 1) is what bounds it.  (block, step)
+                // products whose taps are all zeros are left out at compile time.
                 constexpr int NI = GEO::items();
-                uint4 fl[2][RBW], fh[2][RBW];
-                u32 tb[2][2], off[RBW];
+                static_assert(GEO::rbw() == RBW, "row blocks per warp");
+                uint4 fl[2], fh[2];
+                u32 tb[2][RBW][2], off = 0;
                 int lo[2][RBW][4], hi[2][RBW][4];
                 auto load_item = [&](int i, int buf) {
                     const int l = GEO::item_l(i), k = GEO::item_k(i);
                     const u32 ring = (u32)geo.np(l) * (PPW * 4);
                     const u8 *plane = planes + 4 * geo.plane_off(l);
                     if (k == 0) {
-                        off[0] = voff[l];
-#pragma unroll
-                        for (int rb = 1; rb < RBW; ++rb) {
-                            const u32 nx = off[rb - 1] + PPW * 4;
-                            off[rb] = min(nx, nx - ring);
-                        }
+                        off = voff[l];
                     } else {
+                        const u32 nx = off + 4 * (PPW * 4);
+                        off = min(nx, nx - ring);                // wrap: nx - ring is huge (unsigned) unless nx >= ring
+                    }
 #pragma unroll
-                        for (int rb = 0; rb < RBW; ++rb) {
-                            const u32 nx = off[rb] + 4 * (PPW * 4);
-                            off[rb] = min(nx, nx - ring);        // wrap: nx - ring is huge (unsigned) unless nx >= ring
+                    for (int rb = 0; rb < RBW; ++rb)
+                        if (GEO::v_needed(l, k, rb)) {
+                            tb[buf][rb][0] = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k - 8 * rb);
+                            tb[buf][rb][1] = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k - 8 * rb + 4);
                         }
-                    }
-                    tb[buf][0] = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k); tb[buf][1] = *(const u32 *)(vbase + geo.tab_voff(l) + 32 * k + 4);
-#pragma unroll
-                    for (int rb = 0; rb < RBW; ++rb) {
-                        fl[buf][rb] = *(const uint4 *)(plane + off[rb]);
-                        fh[buf][rb] = *(const uint4 *)(plane + off[rb] + ring);
-                    }
+                    fl[buf] = *(const uint4 *)(plane + off);
+                    fh[buf] = *(const uint4 *)(plane + off + ring);
                 };
                 load_item(0, 0);
 #pragma unroll
@@ -651,11 +651,11 @@ __global__ void __launch_bounds__(kMmaThreads, NCH <= 3 ? 2 : 1) octave_mma_k(co
 #pragma unroll
                     for (int rb = 0; rb < RBW; ++rb) {
                         if (k == 0) {   // K step 0 seeds the accumulators: 32768 (rounding) for the low bytes, 0 for the high bytes
-                            imma_c(lo[lb][rb], fl[b][rb].x, fl[b][rb].y, fl[b][rb].z, fl[b][rb].w, tb[b][0], tb[b][1], 32768);
-                            imma_c(hi[lb][rb], fh[b][rb].x, fh[b][rb].y, fh[b][rb].z, fh[b][rb].w, tb[b][0], tb[b][1], 0);
-                        } else {
-                            imma(lo[lb][rb], fl[b][rb].x, fl[b][rb].y, fl[b][rb].z, fl[b][rb].w, tb[b][0], tb[b][1]);
-                            imma(hi[lb][rb], fh[b][rb].x, fh[b][rb].y, fh[b][rb].z, fh[b][rb].w, tb[b][0], tb[b][1]);
+                            imma_c(lo[lb][rb], fl[b].x, fl[b].y, fl[b].z, fl[b].w, tb[b][rb][0], tb[b][rb][1], 32768);
+                            imma_c(hi[lb][rb], fh[b].x, fh[b].y, fh[b].z, fh[b].w, tb[b][rb][0], tb[b][rb][1], 0);
+                        } else if (GEO::v_needed(l, k, rb)) {
+                            imma(lo[lb][rb], fl[b].x, fl[b].y, fl[b].z, fl[b].w, tb[b][rb][0], tb[b][rb][1]);
+                            imma(hi[lb][rb], fh[b].x, fh[b].y, fh[b].z, fh[b].w, tb[b][rb][0], tb[b][rb][1]);
                         }
                     }
                     if (k == 0 && l > 0) v_out(l - 1, lo[lb ^ 1], hi[lb ^ 1]);

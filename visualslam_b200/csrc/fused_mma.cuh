@@ -72,6 +72,12 @@ struct MmaStaticGeom {
     }
     __host__ __device__ static constexpr int sv(int l) { return sv_at(l, rv()); }
     __host__ __device__ static constexpr int ksv(int l) { return (n(l) + 7 + sv(l) + 31) / 32; }
+    // V pass of the static kernels: the row blocks of a warp (two at 64 columns, one at 32) share the A fragments of a K step -- row
+    // block rb reads the same 32 rows through taps shifted by 8 rb.  K steps that cover the last block's window; which (block, step)
+    // products are not all zeros
+    __host__ __device__ static constexpr int rbw() { return FW_ / 32; }
+    __host__ __device__ static constexpr int ksvs(int l) { return (n(l) + 7 + sv(l) + 8 * (rbw() - 1) + 31) / 32; }
+    __host__ __device__ static constexpr bool v_needed(int l, int k, int rb) { return 32 * k < n(l) + 7 + sv(l) + 8 * rb; }
     __host__ __device__ static constexpr int cq(int l) { return (rv() + r(l) + sv(l)) / 4; }
     __host__ __device__ static constexpr int np(int l) { return (cq(l) + 10) / 2 < 8 ? 8 : (cq(l) + 10) / 2; }
     __host__ __device__ static constexpr int plane_off(int l) {
@@ -86,7 +92,7 @@ struct MmaStaticGeom {
     __host__ __device__ static constexpr int padl(int l) { return rmax() - r(l) + 41 + (4 - (rmax() + 41) % 4) % 4; }
     __host__ __device__ static constexpr int cp_need(int l) {
         int a = padl(l) + r(l) - rmax() + 12 + 32 * (nch() - 1) + 20;     // H pass: last word of the last chunk
-        int b = padl(l) + 24 + 32 * (ksv(l) - 1) + 8;                     // V pass: last word of the last K step
+        int b = padl(l) + 24 + 32 * (ksvs(l) - 1) + 8;                    // V pass: last word of the last K step
         int c = padl(l) + n(l) + 3;                                       // the taps themselves, shifted by up to 3
         return a > b ? (a > c ? a : c) : (b > c ? b : c);
     }
@@ -101,15 +107,15 @@ struct MmaStaticGeom {
     __host__ __device__ static constexpr int tab_voff(int l) { return 4 * cp() * l + padl(l) - sv(l) - rv() % 4; }
     __host__ __device__ static constexpr int plane_words() { return plane_off(6); }
     // the V pass as a flat list of (level, K step) items
-    __host__ __device__ static constexpr int items() { return ksv(0) + ksv(1) + ksv(2) + ksv(3) + ksv(4) + ksv(5); }
+    __host__ __device__ static constexpr int items() { return ksvs(0) + ksvs(1) + ksvs(2) + ksvs(3) + ksvs(4) + ksvs(5); }
     __host__ __device__ static constexpr int item_l(int i) {
         int l = 0;
-        while (l < 5 && i >= ksv(l)) { i -= ksv(l); ++l; }
+        while (l < 5 && i >= ksvs(l)) { i -= ksvs(l); ++l; }
         return l;
     }
     __host__ __device__ static constexpr int item_k(int i) {
         int l = 0;
-        while (l < 5 && i >= ksv(l)) { i -= ksv(l); ++l; }
+        while (l < 5 && i >= ksvs(l)) { i -= ksvs(l); ++l; }
         return i;
     }
     __host__ __device__ static constexpr int stage_pitch() { return (2 * rmax() + 15 + FW_ + 127) / 128 * 128; }

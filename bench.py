@@ -402,7 +402,8 @@ def roofline_block(res, steps, world):
     dom = max(live, key=lambda k: live[k]["ms"])
     blur_ms = sum(live[k]["ms"] for k in octave_kernels)
     # The Gaussian stack is 1738 u8 MAC per input pixel evaluated exactly on the integer tensor pipe; the kernel
-    # is bound by the instructions around the MMAs (issue slots), not by HBM: the tensor fraction is the binding one.
+    # is bound by the shared-memory traffic and the instructions around the MMAs, not by HBM: of the two rooflines the contract
+    # offers, the tensor one is the binding one ("limiter" says what ncu shows).
     tmac = MAC_PER_PX * px_step * steps / (blur_ms * 1e-3) / 1e12 if blur_ms else None
     tops = 2.0 * tmac if tmac else None
     hbm_ach = alg.get(dom, 0.0) / 1e9 / (per_ms[dom] * 1e-3) if alg.get(dom) else None
@@ -412,6 +413,9 @@ def roofline_block(res, steps, world):
              "frac": (tops / bf16_peak if tops else None) if dom in octave_kernels else (hbm_ach / hbm_peak if hbm_ach else None),
              "traffic": measured_traffic(dom, h, w, nf), "peak_source": peak_src,
              "mode": "keypoints-only (fused): octave bases are the only maps in HBM",
+             "limiter": "shared-memory pipe, not HBM and not the tensor pipe: l1tex__data_pipe_lsu_wavefronts is 68 % / 72 % of its peak at octaves "
+                        "0 / 1 in the committed ncu capture of this command (profiles/ncu_full_r2_summary.csv, taken before the V pass shared its A "
+                        "fragments; DESIGN.md 4.1), issue slots 48 % busy, tensor pipe ~26 %, DRAM traffic = algorithmic bytes",
              "note": "achieved = useful integer ops of the blur (2 x 1738 MAC per input pixel: the banded-Toeplitz zeros the MMAs also multiply are "
                      "not counted) over the device time of the octave kernels; peak = the measured dense bf16 rate (sustained) of MEASURED_PEAKS.json "
                      "-- the u8 rate of the tensor pipe is nominally twice that, so the fraction is an upper bound of the pipe's utilisation. "

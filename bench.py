@@ -433,9 +433,9 @@ def roofline_block(res, steps, world):
              "frac": (tops / bf16_peak if tops else None) if dom in octave_kernels else (hbm_ach / hbm_peak if hbm_ach else None),
              "traffic": measured_traffic(dom, h, w, nf), "peak_source": peak_src,
              "mode": "keypoints-only (fused): octave bases are the only maps in HBM",
-             "limiter": "shared-memory pipe, not HBM and not the tensor pipe: l1tex__data_pipe_lsu_wavefronts is 68 % / 72 % of its peak at octaves "
-                        "0 / 1 in the committed ncu capture of this command (profiles/ncu_full_r2_summary.csv, taken before the V pass shared its A "
-                        "fragments; DESIGN.md 4.1), issue slots 48 % busy, tensor pipe ~26 %, DRAM traffic = algorithmic bytes",
+             "limiter": "shared-memory pipe, not HBM and not the tensor pipe: l1tex__data_pipe_lsu_wavefronts is 65 % / 67 % of its peak at octaves "
+                        "0 / 1 in the committed ncu capture of this command (profiles/ncu_full_r2_summary.csv; 68 % / 72 % before the V pass shared its "
+                        "A fragments, DESIGN.md 4.1), issue slots 50 % busy, tensor pipe 25-30 %, DRAM traffic = algorithmic bytes",
              "note": "achieved = useful integer ops of the blur (2 x 1738 MAC per input pixel: the banded-Toeplitz zeros the MMAs also multiply are "
                      "not counted) over the device time of the octave kernels; peak = the measured dense bf16 rate (sustained) of MEASURED_PEAKS.json "
                      "-- the u8 rate of the tensor pipe is nominally twice that, so the fraction is an upper bound of the pipe's utilisation. "

@@ -731,9 +731,10 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
     const FusedTaps *h = (const FusedTaps *)ctx->h_taps;
     // bases-only workspace layout of one frame; every row carries the reflect-101 margins its octave's kernel stages from
     size_t boff[16], bpitch[16], bbytes = 0;
-    int bpad[16], brp[16];
+    int bpad[16], bpadl[16], brp[16];
     for (int o = 0; o < g.num_octaves; ++o) {
         bpad[o] = octave_base_pad(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o);
+        bpadl[o] = octave_base_pad_left(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o);   // what of the left margin is written (the layout stays symmetric)
         brp[o] = octave_base_row_pad(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o);     // tcgen05 kernel: margins above / below too
         bpitch[o] = bpad[o] ? round_up((size_t)g.ocols[o] + 2 * (size_t)bpad[o] + 4, 16) : g.opitch[o];   // + 4: the right margin is written in words
         boff[o] = bbytes + (size_t)brp[o] * bpitch[o] + bpad[o];
@@ -799,7 +800,7 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
             memset(&a, 0, sizeof a);
             a.taps = h[o];
             a.base = ws + boff[o]; a.base_pitch = bpitch[o]; a.base_stride = bbytes; a.base_pad = bpad[o]; a.base_row_pad = brp[o];
-            VS_TRY(launch_reflect_pad(ctx, ws + boff[o], g.orows[o], g.ocols[o], bpitch[o], bbytes, bpad[o], brp[o], nf));
+            VS_TRY(launch_reflect_pad(ctx, ws + boff[o], g.orows[o], g.ocols[o], bpitch[o], bbytes, bpad[o], brp[o], nf, bpadl[o]));
             a.rows = g.orows[o]; a.cols = g.ocols[o]; a.octave = o;
             if (o + 1 < g.num_octaves) {
                 a.next_base = ws + boff[o + 1]; a.next_pitch = bpitch[o + 1]; a.next_stride = bbytes;

@@ -851,15 +851,25 @@ int octave_base_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave
     return (mt.stage_pitch - mt.rmax + 30) & ~15;
 }
 
-// thread = one aligned word of a margin; the right margin starts at the last aligned word that still holds image
-// columns (those bytes are rewritten with their own values)
-__global__ void reflect_pad_k(u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad) {
-    const int wl = pad >> 2, x_r = cols & ~3, wr = (cols + pad - x_r + 3) >> 2, wpr = wl + wr;
+// columns of the LEFT margin the kernel that runs the octave really stages: the mma.sync kernel's leftmost strip starts at
+// (-2 - rmax) & ~15, well inside the symmetric margin the layout reserves; the tcgen05 kernel's TMA boxes use all of theirs
+int octave_base_pad_left(vslam_ctx *ctx, double sigma0, int scale_samples, int octave) {
+    if (const int up = umma_base_pad(ctx, sigma0, scale_samples, octave)) return up;
+    MmaTaps mt;
+    size_t sm;
+    if (!mma_plan(ctx, sigma0, scale_samples, octave, &mt, &sm)) return 0;
+    return (mt.rmax + 2 + 15) & ~15;
+}
+
+// thread = one aligned word of a margin (pad_left columns on the left, pad on the right); the right margin starts at the last
+// aligned word that still holds image columns (those bytes are rewritten with their own values)
+__global__ void reflect_pad_k(u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int pad_left) {
+    const int wl = pad_left >> 2, x_r = cols & ~3, wr = (cols + pad - x_r + 3) >> 2, wpr = wl + wr;
     u8 *plane = base + (size_t)blockIdx.y * stride;
     const int n = rows * wpr;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const int y = i / wpr, w = i - y * wpr;
-        const int x = w < wl ? 4 * w - pad : x_r + 4 * (w - wl);
+        const int x = w < wl ? 4 * w - pad_left : x_r + 4 * (w - wl);
         u8 *row = plane + (size_t)y * pitch;
         const u32 v = (u32)row[refl101(x, cols)] | (u32)row[refl101(x + 1, cols)] << 8 | (u32)row[refl101(x + 2, cols)] << 16 |
                       (u32)row[refl101(x + 3, cols)] << 24;
@@ -881,14 +891,15 @@ __global__ void reflect_pad_rows_k(u8 *base, int rows, size_t pitch, size_t stri
     }
 }
 
-int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames) {
+int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames, int pad_left) {
     if (pad <= 0) return VSLAM_OK;
-    const int wpr = (pad >> 2) + ((cols + pad - (cols & ~3) + 3) >> 2);
+    if (pad_left <= 0 || pad_left > pad || row_pad > 0) pad_left = pad;      // (whole padded rows are copied when there are row margins)
+    const int wpr = (pad_left >> 2) + ((cols + pad - (cols & ~3) + 3) >> 2);
     int bx = (rows * wpr + 255) / 256;
     if (bx > 64) bx = 64;
     const dim3 grid(bx, n_frames);
     KernelSpan span(ctx, VSLAM_K_PAD);
-    reflect_pad_k<<<grid, 256, 0, ctx->stream>>>(base, rows, cols, pitch, stride, pad);
+    reflect_pad_k<<<grid, 256, 0, ctx->stream>>>(base, rows, cols, pitch, stride, pad, pad_left);
     VS_LAUNCH_CHECK(ctx);
     if (row_pad > 0) {
         int by = (int)((2 * row_pad * (pitch >> 4) + 255) / 256);

@@ -800,7 +800,8 @@ static int dog_keypoints_fused(vslam_ctx *ctx, const Geometry &g, const u8 *d_fr
             memset(&a, 0, sizeof a);
             a.taps = h[o];
             a.base = ws + boff[o]; a.base_pitch = bpitch[o]; a.base_stride = bbytes; a.base_pad = bpad[o]; a.base_row_pad = brp[o];
-            VS_TRY(launch_reflect_pad(ctx, ws + boff[o], g.orows[o], g.ocols[o], bpitch[o], bbytes, bpad[o], brp[o], nf, bpadl[o]));
+            VS_TRY(launch_reflect_pad(ctx, ws + boff[o], g.orows[o], g.ocols[o], bpitch[o], bbytes, bpad[o], brp[o], nf, bpadl[o],
+                                      octave_base_pad_right(ctx, ctx->taps_sigma0, ctx->taps_scale_samples, o, g.ocols[o])));
             a.rows = g.orows[o]; a.cols = g.ocols[o]; a.octave = o;
             if (o + 1 < g.num_octaves) {
                 a.next_base = ws + boff[o + 1]; a.next_pitch = bpitch[o + 1]; a.next_stride = bbytes;

@@ -79,8 +79,10 @@ int octave_base_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave
 int octave_base_row_pad(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);
 // fills them: base[y][-pad .. -1] and base[y][cols .. cols + pad - 1] of every frame, then rows -row_pad .. -1 and
 // rows .. rows + row_pad - 1 (whole padded rows, so the corners are reflections in both axes)
-int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames, int pad_left = 0);
+int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames, int pad_left = 0,
+                       int pad_right = 0);
 int octave_base_pad_left(vslam_ctx *ctx, double sigma0, int scale_samples, int octave);
+int octave_base_pad_right(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols);
 int launch_octave_mma(vslam_ctx *ctx, const OctaveIO &io, int n_frames, double sigma0, int scale_samples);
 // tap-table images cached per device: freed when the last context of the device goes (vslam_ctx_destroy)
 void mma_tab_release(int device);

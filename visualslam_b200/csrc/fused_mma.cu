@@ -861,6 +861,18 @@ int octave_base_pad_left(vslam_ctx *ctx, double sigma0, int scale_samples, int o
     return (mt.rmax + 2 + 15) & ~15;
 }
 
+// ... and of the RIGHT margin: the last strip's staged row ends at ((X0 - 2 - rmax) & ~15) + stage_pitch
+int octave_base_pad_right(vslam_ctx *ctx, double sigma0, int scale_samples, int octave, int cols) {
+    if (const int up = umma_base_pad(ctx, sigma0, scale_samples, octave)) return up;
+    MmaTaps mt;
+    size_t sm;
+    if (!mma_plan(ctx, sigma0, scale_samples, octave, &mt, &sm)) return 0;
+    const int x0 = (mma_strips(cols, mt.fw) - 1) * mma_fwo(mt.fw);
+    const int need = ((x0 - 2 - mt.rmax) & ~15) + mt.stage_pitch - cols;
+    const int full = (mt.stage_pitch - mt.rmax + 30) & ~15;
+    return need < 4 ? 4 : need > full ? full : (need + 3) & ~3;
+}
+
 // thread = one aligned word of a margin (pad_left columns on the left, pad on the right); the right margin starts at the last
 // aligned word that still holds image columns (those bytes are rewritten with their own values)
 __global__ void reflect_pad_k(u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int pad_left) {
@@ -891,9 +903,13 @@ __global__ void reflect_pad_rows_k(u8 *base, int rows, size_t pitch, size_t stri
     }
 }
 
-int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames, int pad_left) {
+int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitch, size_t stride, int pad, int row_pad, int n_frames, int pad_left,
+                       int pad_right) {
     if (pad <= 0) return VSLAM_OK;
     if (pad_left <= 0 || pad_left > pad || row_pad > 0) pad_left = pad;      // (whole padded rows are copied when there are row margins)
+    if (pad_right <= 0 || pad_right > pad || row_pad > 0) pad_right = pad;
+    const int full_pad = pad;
+    pad = pad_right;                                                         // the kernel's `pad` is the right margin it writes
     const int wpr = (pad_left >> 2) + ((cols + pad - (cols & ~3) + 3) >> 2);
     int bx = (rows * wpr + 255) / 256;
     if (bx > 64) bx = 64;
@@ -904,7 +920,7 @@ int launch_reflect_pad(vslam_ctx *ctx, u8 *base, int rows, int cols, size_t pitc
     if (row_pad > 0) {
         int by = (int)((2 * row_pad * (pitch >> 4) + 255) / 256);
         if (by > 64) by = 64;
-        reflect_pad_rows_k<<<dim3(by, n_frames), 256, 0, ctx->stream>>>(base, rows, pitch, stride, pad, row_pad);
+        reflect_pad_rows_k<<<dim3(by, n_frames), 256, 0, ctx->stream>>>(base, rows, pitch, stride, full_pad, row_pad);
         VS_LAUNCH_CHECK(ctx);
     }
     return VSLAM_OK;

@@ -778,3 +778,26 @@ def test_pyramid_rebuild_in_place(ctx):
                 for l in range(levels):
                     assert np.array_equal(pyr.get(kind, o, l, f), fresh.get(kind, o, l, f)), (f, o, kind, l)
     assert np.array_equal(ctx.dog_detect(pyr)["keypoints"], ctx.dog_detect(fresh)["keypoints"])
+
+
+def test_dog_detect_batch_matches_per_frame(ctx):
+    """vslam_dog_detect on a batch (one detector launch per octave for all frames, one compaction pass) gives, frame by frame, the
+    lists, counts and stage counters of single-frame calls -- and the list of the fused throughput path."""
+    ids = (0, 5, 6, 3, 2)
+    frames = np.stack([synth.frame(i, 135, 240) for i in ids], 0)
+    pyr = ctx.build_pyramid(frames, 4, 1.6)
+    batch = ctx.dog_detect(pyr)
+    assert len(batch["counts"]) == len(ids)
+    lists, at = [], 0
+    for f, i in enumerate(ids):
+        one = ctx.dog_detect(ctx.build_pyramid(frames[f], 4, 1.6))
+        n = batch["counts"][f]
+        assert one["counts"] == [n], f
+        assert np.array_equal(kp_array(batch["keypoints"][at:at + n]), kp_array(one["keypoints"])), f
+        assert np.array_equal(np.asarray(batch["stage_counts"][f]), np.asarray(one["stage_counts"][0])), f
+        lists.append(kp_array(one["keypoints"]))
+        at += n
+    assert at == len(batch["keypoints"])
+    fused = ctx.dog_keypoints(frames)
+    assert fused["counts"] == batch["counts"]
+    assert np.array_equal(kp_array(fused["keypoints"]), np.concatenate(lists, 0))
